@@ -1,0 +1,97 @@
+"""ctypes binding of libgantron_b200.so (the C ABI declared in include/gantron_b200.h).
+
+There is NO fallback: if the library is missing or a call fails, a RuntimeError is raised.
+Tensors are passed as raw device pointers (`tensor.data_ptr()`), the stream as torch's current
+CUDA stream handle.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgantron_b200.so")
+
+_lib: Optional[C.CDLL] = None
+
+c_p = C.c_void_p
+c_i = C.c_int
+c_ll = C.c_longlong
+c_ull = C.c_ulonglong
+c_f = C.c_float
+
+# name -> (restype, argtypes).  Must list every symbol declared in include/gantron_b200.h
+# (tests/test_abi.py cross-checks against the header).
+SIGNATURES = {
+    "gtn_last_error": (C.c_char_p, []),
+    "gtn_version": (c_i, []),
+    "gtn_launch_count": (c_ll, []),
+    "gtn_reset_launch_count": (None, []),
+    "gtn_device_info": (c_i, [C.POINTER(c_i)] * 4),
+    "gtn_gemm_bf16": (c_i, [c_p, c_p, c_i, c_i, c_i, c_ll, c_ll, c_i, c_ll, c_ll,
+                            c_p, c_i, c_ll, c_ll, c_i,
+                            c_p, c_i, c_ll, c_ll, c_i,
+                            c_p, c_p, c_i, c_i, c_f, c_ull, c_i, c_i, c_p, c_i, c_p]),
+    "gtn_conv1d_bf16": (c_i, [c_p, c_i, c_i, c_i, c_i, c_i, c_i,
+                              c_p, c_i, c_i, c_ll, c_ll,
+                              c_p, c_i, c_ll, c_ll,
+                              c_p, c_i, c_ll, c_ll,
+                              c_p, c_i, c_p, c_i, c_p]),
+    "gtn_conv1d_wgrad_bf16": (c_i, [c_p, c_p, c_i, c_i, c_i, c_i, c_ll, c_ll, c_ll, c_ll,
+                                    c_i, c_i, c_i, c_p, c_ll, c_i, c_i, c_p]),
+}
+
+
+def load() -> C.CDLL:
+    """Load the shared library (raises if it has not been built)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} not found: build it with `python -m gantron_b200.build` "
+            "(gantron_b200 has no CPU / eager fallback)")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def last_error() -> str:
+    return load().gtn_last_error().decode("utf-8", "replace")
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise RuntimeError(f"{what} failed (rc={rc}): {last_error()}")
+
+
+def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    if t is None:
+        return None
+    assert t.is_cuda, "gantron_b200 kernels take CUDA tensors only"
+    return t.data_ptr()
+
+
+def stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def launch_count() -> int:
+    return int(load().gtn_launch_count())
+
+
+def reset_launch_count() -> None:
+    load().gtn_reset_launch_count()
+
+
+def device_info() -> dict:
+    v = [c_i(0) for _ in range(4)]
+    check(load().gtn_device_info(*[C.byref(x) for x in v]), "gtn_device_info")
+    return dict(sm_count=v[0].value, cc_major=v[1].value, cc_minor=v[2].value, coop=v[3].value)

@@ -1,0 +1,340 @@
+// tcgen05 / TMEM / TMA GEMM for sm_100a: the dense-contraction workhorse of the training path.
+//
+//   D[m, n] = sum_k A[m, k] * B[n, k]          A, B bf16, K-major (K contiguous); fp32 accumulate in TMEM
+//
+// One kernel serves four addressing modes (all operands arrive through 3-D TMA tensor maps with
+// SWIZZLE_128B and zero OOB fill, so ragged M/N/K/T tails need no special casing):
+//   MODE_PLAIN  : (batched) GEMM.  Used for the Prenet linears (reference model.py:102-105), the
+//                 attention memory layer (model.py:326), and every *deferred weight-gradient* GEMM of
+//                 the LSTM cells / projections (K = T_out * B), and d(memory) = align^T . dctx.
+//   MODE_CONV   : implicit-GEMM conv1d, forward and data-gradient: M = C_out, N = time, K = taps x C_in;
+//                 the tap shift is a TMA coordinate offset on the time axis (zero padding = OOB fill).
+//                 Postnet (model.py:146-151) and Discriminator (model.py:514-527, layers.py:43-60).
+//   MODE_WGRAD  : conv1d weight gradient: M = C_out, N = C_in, K = (batch, time), one tap per blockIdx.z.
+//
+// Structure (one 128 x BN output tile per CTA): warp 0 = TMA producer, warp 1 = MMA issuer (a single
+// elected thread issues tcgen05.mma, accumulator in TMEM), warp 2 = TMEM allocator, warps 4-7 = epilogue
+// (tcgen05.ld -> registers -> fused bias / activation / dropout / BatchNorm-statistics -> global).
+// smem ring of `stages` x (A 128x64 + B BNx64) bf16 tiles guarded by full/empty mbarriers.
+#include "gtn_common.cuh"
+#include "gtn_internal.h"
+
+namespace gtn {
+
+static constexpr int BM = 128;
+static constexpr int BK = 64;  // 64 bf16 = 128 B = one SWIZZLE_128B row
+
+struct GemmKernelParams {
+  int mode;
+  int M, N;               // logical output extent per z (rows = M, cols = N)
+  int num_k_blocks;
+  // MODE_CONV
+  int ci_blocks, cin_pad, dil, pad;
+  // MODE_WGRAD
+  int t_blocks, taps_dil, taps_pad;  // shift = z * taps_dil - taps_pad
+  // outputs
+  void* C;  long long ldc, strideC;  int c_bf16, c_trans;
+  void* C2; long long ldc2, strideC2; int c2_bf16, c2_trans;
+  const float* bias_m; const float* bias_n;
+  int act;            // 0 none, 1 relu, 2 tanh
+  int accumulate;     // C += D (fp32 C only)
+  unsigned int drop_thr; float drop_scale; unsigned long long seed; unsigned int site, step;
+  float* stats;       // [2][M] per-row sum / sum of squares over valid n (all z), or nullptr
+  int stages;
+};
+
+GTN_DEVICE void wait_or_trap(uint64_t* bar, uint32_t parity) {
+  long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > 6000000000LL) __trap();   // ~3 s: a pipeline bug must not hang the GPU
+  }
+}
+
+template <int BN>
+__global__ void __launch_bounds__(256, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const GemmKernelParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr int A_BYTES = BM * BK * 2;
+  constexpr int B_BYTES = BN * BK * 2;
+  const int stages = p.stages;
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + (size_t)stages * A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(sB + (size_t)stages * B_BYTES);
+  uint64_t* empty = full + stages;
+  uint64_t* accum_full = empty + stages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_full + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * BN;
+  const int m0 = blockIdx.y * BM;
+  const int z = blockIdx.z;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    mbar_init(accum_full, 1);
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, BN);   // BN fp32 columns x 128 lanes
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_acc = *tmem_slot;
+  const int nk = p.num_k_blocks;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ------------------------------ TMA producer ------------------------------
+      for (int kb = 0; kb < nk; ++kb) {
+        const int s = kb % stages;
+        const uint32_t ph = (uint32_t)(kb / stages) & 1u;
+        wait_or_trap(&empty[s], ph ^ 1u);
+        mbar_expect_tx(&full[s], A_BYTES + B_BYTES);
+        int a0, a1, a2, b0, b1, b2;
+        if (p.mode == MODE_PLAIN) {
+          a0 = kb * BK; a1 = m0; a2 = z;
+          b0 = kb * BK; b1 = n0; b2 = z;
+        } else if (p.mode == MODE_CONV) {
+          const int tap = kb / p.ci_blocks, cib = kb - tap * p.ci_blocks;
+          a0 = tap * p.cin_pad + cib * BK; a1 = m0; a2 = 0;
+          b0 = cib * BK; b1 = n0 + tap * p.dil - p.pad; b2 = z;
+        } else {  // MODE_WGRAD: k-block -> (batch, time block); z = tap
+          const int bb = kb / p.t_blocks, tb = kb - bb * p.t_blocks;
+          a0 = tb * BK; a1 = m0; a2 = bb;
+          b0 = tb * BK + z * p.taps_dil - p.taps_pad; b1 = n0; b2 = bb;
+        }
+        tma_load_3d(sA + (size_t)s * A_BYTES, &tmA, &full[s], a0, a1, a2);
+        tma_load_3d(sB + (size_t)s * B_BYTES, &tmB, &full[s], b0, b1, b2);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ------------------------------ MMA issuer ------------------------------
+      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+      for (int kb = 0; kb < nk; ++kb) {
+        const int s = kb % stages;
+        const uint32_t ph = (uint32_t)(kb / stages) & 1u;
+        wait_or_trap(&full[s], ph);
+        tc_fence_after();
+        const uint64_t da = umma_desc_sw128(smem_u32(sA + (size_t)s * A_BYTES));
+        const uint64_t db = umma_desc_sw128(smem_u32(sB + (size_t)s * B_BYTES));
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k) {
+          // advance 16 bf16 = 32 B along K inside the 128 B swizzle row: +2 in the (addr >> 4) field
+          umma_bf16(tmem_acc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
+        }
+        umma_commit(&empty[s]);      // frees the smem slot once these MMAs retire
+      }
+      umma_commit(accum_full);       // accumulator complete
+    }
+  } else if (warp >= 4) {
+    // ------------------------------ epilogue ------------------------------
+    wait_or_trap(accum_full, 0);
+    tc_fence_after();
+    const int wq = warp & 3;                 // TMEM lane quarter this warp may touch
+    const int m = m0 + wq * 32 + lane;       // output row of this thread
+    const bool m_ok = m < p.M;
+    const float bm = (p.bias_m != nullptr && m_ok) ? p.bias_m[m] : 0.0f;
+    float s1 = 0.f, s2 = 0.f;
+    float* Cf = reinterpret_cast<float*>(p.C);
+    __nv_bfloat16* Cb = reinterpret_cast<__nv_bfloat16*>(p.C);
+    float* C2f = reinterpret_cast<float*>(p.C2);
+    __nv_bfloat16* C2b = reinterpret_cast<__nv_bfloat16*>(p.C2);
+    const long long zc = (long long)z * p.strideC, zc2 = (long long)z * p.strideC2;
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32(tmem_acc + ((uint32_t)(wq * 32) << 16) + (uint32_t)(c * 32), r);
+      tmem_ld_wait();
+      const int nb = n0 + c * 32;
+      if (nb >= p.N) continue;      // warp-uniform
+      float v[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        float x = __uint_as_float(r[j]) + bm;
+        const int n = nb + j;
+        if (p.bias_n != nullptr && n < p.N) x += p.bias_n[n];
+        if (p.accumulate && m_ok && n < p.N)
+          x += p.c_trans ? Cf[zc + (long long)n * p.ldc + m] : Cf[zc + (long long)m * p.ldc + n];
+        if (p.act == 1) x = fmaxf(x, 0.0f);
+        else if (p.act == 2) x = tanhf(x);
+        v[j] = x;
+      }
+      if (p.drop_thr != 0u && m_ok) {
+        // element numbering = row-major index in the stored (primary) output of slice z
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int n = nb + j;
+          if (n < p.N) {
+            const unsigned long long e = p.c_trans ? ((unsigned long long)n * p.M + m) : ((unsigned long long)m * p.N + n);
+            const uint32_t bits = philox_bits(p.seed, p.site, p.step, (uint32_t)(e + (unsigned long long)z * p.M * p.N));
+            v[j] = bits >= p.drop_thr ? v[j] * p.drop_scale : 0.0f;
+          }
+        }
+      }
+      if (p.stats != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (nb + j < p.N) { s1 += v[j]; s2 += v[j] * v[j]; }
+      }
+      if (!m_ok) continue;
+      // primary output
+      if (p.C != nullptr) {
+        if (!p.c_trans) {
+          const long long base = zc + (long long)m * p.ldc + nb;
+          const bool full32 = (nb + 32 <= p.N);
+          if (p.c_bf16) {
+            if (full32 && ((base & 7) == 0)) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                uint4 q = make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
+                                     pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
+                *reinterpret_cast<uint4*>(Cb + base + j) = q;
+              }
+            } else {
+              for (int j = 0; j < 32; ++j) if (nb + j < p.N) Cb[base + j] = __float2bfloat16_rn(v[j]);
+            }
+          } else {
+            if (full32 && ((base & 3) == 0)) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4)
+                *reinterpret_cast<float4*>(Cf + base + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            } else {
+              for (int j = 0; j < 32; ++j) if (nb + j < p.N) Cf[base + j] = v[j];
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int n = nb + j;
+            if (n < p.N) {
+              const long long a = zc + (long long)n * p.ldc + m;
+              if (p.c_bf16) Cb[a] = __float2bfloat16_rn(v[j]); else Cf[a] = v[j];
+            }
+          }
+        }
+      }
+      // secondary output (other layout / dtype of the same values)
+      if (p.C2 != nullptr) {
+        if (!p.c2_trans) {
+          const long long base = zc2 + (long long)m * p.ldc2 + nb;
+          for (int j = 0; j < 32; ++j)
+            if (nb + j < p.N) { if (p.c2_bf16) C2b[base + j] = __float2bfloat16_rn(v[j]); else C2f[base + j] = v[j]; }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int n = nb + j;
+            if (n < p.N) {
+              const long long a = zc2 + (long long)n * p.ldc2 + m;
+              if (p.c2_bf16) C2b[a] = __float2bfloat16_rn(v[j]); else C2f[a] = v[j];
+            }
+          }
+        }
+      }
+    }
+    if (p.stats != nullptr && m_ok) {
+      atomicAdd(&p.stats[m], s1);
+      atomicAdd(&p.stats[p.M + m], s2);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_acc, BN);
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* sym = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || sym == nullptr) {
+    set_error("cuTensorMapEncodeTiled entry point unavailable (%s)", cudaGetErrorString(e));
+    return nullptr;
+  }
+  fn = reinterpret_cast<EncodeTiledFn>(sym);
+  return fn;
+}
+
+// 3-D bf16 tensor map: dims (d0 inner, d1, d2), byte strides for d1 / d2, box (64, box1, 1), SWIZZLE_128B.
+static int make_map(CUtensorMap* out, const void* base, long long d0, long long d1, long long d2,
+                    long long stride1_elems, long long stride2_elems, int box1) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return -3;
+  GTN_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base %p not 16-byte aligned", base);
+  GTN_REQUIRE((stride1_elems % 8) == 0 && (d2 <= 1 || (stride2_elems % 8) == 0),
+              "TMA strides must be multiples of 8 bf16 (got %lld, %lld)", stride1_elems, stride2_elems);
+  cuuint64_t dims[3] = {(cuuint64_t)d0, (cuuint64_t)d1, (cuuint64_t)(d2 < 1 ? 1 : d2)};
+  cuuint64_t strides[2] = {(cuuint64_t)stride1_elems * 2, (cuuint64_t)(d2 <= 1 ? stride1_elems * d1 : stride2_elems) * 2};
+  cuuint32_t box[3] = {(cuuint32_t)BK, (cuuint32_t)box1, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  GTN_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (dims %lld,%lld,%lld strides %lld,%lld)",
+              (int)r, d0, d1, d2, stride1_elems, stride2_elems);
+  return 0;
+}
+
+template <int BN>
+static int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, GemmKernelParams kp, dim3 grid, cudaStream_t st) {
+  int stages = kp.num_k_blocks < 2 ? 2 : (kp.num_k_blocks > 6 ? 6 : kp.num_k_blocks);
+  const size_t per_stage = (size_t)BM * BK * 2 + (size_t)BN * BK * 2;
+  if (BN == 256 && stages > 4) stages = 4;
+  kp.stages = stages;
+  const size_t smem = stages * per_stage + (2 * stages + 1) * sizeof(uint64_t) + 16 + 1024;
+  static size_t configured = 0;
+  if (smem > configured) {
+    GTN_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024)));
+    configured = 227 * 1024;
+  }
+  gemm_tc_kernel<BN><<<grid, 256, smem, st>>>(ta, tb, kp);
+  GTN_CUDA_OK(cudaGetLastError());
+  count_launch();
+  return 0;
+}
+
+int gemm_launch(const GemmDesc& g, cudaStream_t st) {
+  GTN_REQUIRE(g.M > 0 && g.N > 0 && g.num_k_blocks > 0, "empty GEMM (M=%d N=%d kblocks=%d)", g.M, g.N, g.num_k_blocks);
+  const int BN = g.block_n;
+  GTN_REQUIRE(BN == 64 || BN == 128 || BN == 256, "block_n must be 64/128/256");
+  CUtensorMap ta, tb;
+  int rc = make_map(&ta, g.A, g.a_d0, g.a_d1, g.a_d2, g.a_s1, g.a_s2, BM);
+  if (rc) return rc;
+  rc = make_map(&tb, g.B, g.b_d0, g.b_d1, g.b_d2, g.b_s1, g.b_s2, BN);
+  if (rc) return rc;
+  GemmKernelParams kp;
+  kp.mode = g.mode; kp.M = g.M; kp.N = g.N; kp.num_k_blocks = g.num_k_blocks;
+  kp.ci_blocks = g.ci_blocks; kp.cin_pad = g.cin_pad; kp.dil = g.dil; kp.pad = g.pad;
+  kp.t_blocks = g.t_blocks; kp.taps_dil = g.dil; kp.taps_pad = g.pad;
+  kp.C = g.C; kp.ldc = g.ldc; kp.strideC = g.strideC; kp.c_bf16 = g.c_bf16; kp.c_trans = g.c_trans;
+  kp.C2 = g.C2; kp.ldc2 = g.ldc2; kp.strideC2 = g.strideC2; kp.c2_bf16 = g.c2_bf16; kp.c2_trans = g.c2_trans;
+  kp.bias_m = g.bias_m; kp.bias_n = g.bias_n; kp.act = g.act; kp.accumulate = g.accumulate;
+  if (g.drop_p > 0.f) {
+    double t = (double)g.drop_p * 4294967296.0;
+    kp.drop_thr = t >= 4294967295.0 ? 0xFFFFFFFFu : (unsigned int)t;
+    kp.drop_scale = 1.0f / (1.0f - g.drop_p);
+  } else { kp.drop_thr = 0; kp.drop_scale = 1.f; }
+  kp.seed = g.seed; kp.site = g.site; kp.step = g.step;
+  kp.stats = g.stats; kp.stages = 0;
+  GTN_REQUIRE(!(g.accumulate && g.c_bf16), "accumulate needs an fp32 primary output");
+  dim3 grid((g.N + BN - 1) / BN, (g.M + BM - 1) / BM, g.batch < 1 ? 1 : g.batch);
+  if (BN == 64) return launch_bn<64>(ta, tb, kp, grid, st);
+  if (BN == 128) return launch_bn<128>(ta, tb, kp, grid, st);
+  return launch_bn<256>(ta, tb, kp, grid, st);
+}
+
+}  // namespace gtn

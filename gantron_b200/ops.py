@@ -1,0 +1,130 @@
+"""Tensor-level wrappers over the C ABI (thin: shape checks, pointer extraction, launches).
+
+Every function here launches hand-written sm_100a kernels from libgantron_b200.so on torch's
+current stream; none has a torch/CPU fallback.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+
+ACT_NONE, ACT_RELU, ACT_TANH = 0, 1, 2
+_BF16 = torch.bfloat16
+
+
+def _dt(t: torch.Tensor) -> int:
+    if t.dtype == torch.float32:
+        return 0
+    if t.dtype == _BF16:
+        return 1
+    raise TypeError(f"output dtype must be fp32 or bf16, got {t.dtype}")
+
+
+def _rows_k(t: torch.Tensor, name: str) -> Tuple[int, int, int, int, int]:
+    """(batch, rows, K, ld, batch_stride) of a K-contiguous bf16 matrix (rows,K) or (Z,rows,K)."""
+    assert t.dtype == _BF16 and t.is_cuda, f"{name}: bf16 CUDA tensor expected"
+    assert t.stride(-1) == 1, f"{name}: K must be contiguous"
+    if t.dim() == 2:
+        return 1, t.shape[0], t.shape[1], t.stride(0), 0
+    assert t.dim() == 3
+    return t.shape[0], t.shape[1], t.shape[2], t.stride(1), t.stride(0)
+
+
+def gemm(A: torch.Tensor, B: torch.Tensor, out: torch.Tensor, *, trans_out: bool = False,
+         out2: Optional[torch.Tensor] = None, trans_out2: bool = False,
+         bias_m: Optional[torch.Tensor] = None, bias_n: Optional[torch.Tensor] = None, act: int = ACT_NONE,
+         accumulate: bool = False, dropout: Optional[Tuple[float, int, int, int]] = None,
+         stats: Optional[torch.Tensor] = None, block_n: int = 128) -> torch.Tensor:
+    """out[z,m,n] = sum_k A[z,m,k] B[z,n,k] with the fused epilogue of gtn_gemm_bf16.
+
+    out is (M,N) / (Z,M,N) (or (N,M) / (Z,N,M) when trans_out); dropout = (p, seed, site, step)."""
+    za, M, K, lda, sa = _rows_k(A, "A")
+    zb, N, Kb, ldb, sb = _rows_k(B, "B")
+    assert K == Kb and za == zb, f"GEMM shape mismatch A{tuple(A.shape)} B{tuple(B.shape)}"
+    Z = za
+
+    def out_geom(o, trans):
+        assert o.is_cuda and o.stride(-1) == 1
+        exp = (N, M) if trans else (M, N)
+        assert tuple(o.shape[-2:]) == exp, f"output shape {tuple(o.shape)} != {exp}"
+        if o.dim() == 2:
+            assert Z == 1
+            return o.stride(0), 0
+        assert o.shape[0] == Z
+        return o.stride(1), o.stride(0)
+
+    ldc, sc = out_geom(out, trans_out)
+    if out2 is not None:
+        ldc2, sc2 = out_geom(out2, trans_out2)
+    else:
+        ldc2, sc2 = 0, 0
+    p, seed, site, step = dropout if dropout is not None else (0.0, 0, 0, 0)
+    for b in (bias_m, bias_n, stats):
+        assert b is None or (b.dtype == torch.float32 and b.is_cuda and b.is_contiguous())
+    lib = _lib.load()
+    rc = lib.gtn_gemm_bf16(
+        _lib.ptr(A), _lib.ptr(B), M, N, K, lda, ldb, Z, sa, sb,
+        _lib.ptr(out), _dt(out), ldc, sc, int(trans_out),
+        _lib.ptr(out2), _dt(out2) if out2 is not None else 0, ldc2, sc2, int(trans_out2),
+        _lib.ptr(bias_m), _lib.ptr(bias_n), act, int(accumulate),
+        float(p), int(seed), int(site), int(step), _lib.ptr(stats), block_n, _lib.stream())
+    _lib.check(rc, "gtn_gemm_bf16")
+    return out
+
+
+def pack_conv_weight(w: torch.Tensor, transpose_for_dgrad: bool = False) -> Tuple[torch.Tensor, int]:
+    """(Cout,Cin,k) fp32 conv weight -> bf16 [Cout][k*cin_pad] K-major pack for gtn_conv1d_bf16.
+
+    transpose_for_dgrad: build the data-gradient operator instead, W'[ci][tap][co] = W[co][ci][k-1-tap]
+    (so that dgrad is the same implicit-GEMM kernel run on dY)."""
+    if transpose_for_dgrad:
+        w = w.flip(-1).permute(1, 0, 2)
+    co, ci, k = w.shape
+    cin_pad = (ci + 63) // 64 * 64
+    wp = torch.zeros(co, k, cin_pad, device=w.device, dtype=_BF16)
+    wp[:, :, :ci] = w.permute(0, 2, 1).to(_BF16)
+    return wp.reshape(co, k * cin_pad), cin_pad
+
+
+def conv1d(wp: torch.Tensor, cin: int, cin_pad: int, taps: int, dil: int, pad: int, x_cl: torch.Tensor,
+           out_cl: Optional[torch.Tensor], out_cf: Optional[torch.Tensor], bias: Optional[torch.Tensor] = None,
+           act: int = ACT_NONE, stats: Optional[torch.Tensor] = None, block_n: int = 128) -> None:
+    """Implicit-GEMM conv1d.  x_cl channels-last bf16 (B,T,>=cin) -> out_cl (B,T,Cout) and/or out_cf (B,Cout,T)."""
+    assert x_cl.dtype == _BF16 and x_cl.dim() == 3 and x_cl.stride(2) == 1
+    Bn, T, _ = x_cl.shape
+    cout = wp.shape[0]
+    assert wp.is_contiguous() and wp.shape[1] == taps * cin_pad
+    if out_cl is not None:
+        assert tuple(out_cl.shape[:2]) == (Bn, T) and out_cl.shape[2] >= cout and out_cl.stride(2) == 1
+    if out_cf is not None:
+        assert tuple(out_cf.shape[:2]) == (Bn, cout) and out_cf.shape[2] >= T and out_cf.stride(2) == 1
+    lib = _lib.load()
+    rc = lib.gtn_conv1d_bf16(
+        _lib.ptr(wp), cout, cin, cin_pad, taps, dil, pad,
+        _lib.ptr(x_cl), Bn, T, x_cl.stride(1), x_cl.stride(0),
+        _lib.ptr(out_cl), _dt(out_cl) if out_cl is not None else 0,
+        out_cl.stride(1) if out_cl is not None else 0, out_cl.stride(0) if out_cl is not None else 0,
+        _lib.ptr(out_cf), _dt(out_cf) if out_cf is not None else 0,
+        out_cf.stride(1) if out_cf is not None else 0, out_cf.stride(0) if out_cf is not None else 0,
+        _lib.ptr(bias), act, _lib.ptr(stats), block_n, _lib.stream())
+    _lib.check(rc, "gtn_conv1d_bf16")
+
+
+def conv1d_wgrad(dy_cf: torch.Tensor, x_cf: torch.Tensor, T: int, taps: int, dil: int, pad: int,
+                 dw: torch.Tensor, accumulate: bool = False, block_n: int = 128) -> torch.Tensor:
+    """dw[tap][co][ci] (+)= sum_{b,t} dy_cf[b,co,t] x_cf[b,ci,t+tap*dil-pad]; dy_cf/x_cf channels-first bf16
+    whose last dim (time, possibly padded to a multiple of 8) is contiguous; only the first T steps are read."""
+    assert dy_cf.dtype == _BF16 and x_cf.dtype == _BF16 and dy_cf.stride(2) == 1 and x_cf.stride(2) == 1
+    Bn, cout, _ = dy_cf.shape
+    cin = x_cf.shape[1]
+    assert dw.dtype == torch.float32 and tuple(dw.shape) == (taps, cout, cin) and dw.is_contiguous()
+    lib = _lib.load()
+    rc = lib.gtn_conv1d_wgrad_bf16(
+        _lib.ptr(dy_cf), _lib.ptr(x_cf), Bn, cout, cin, T,
+        dy_cf.stride(1), dy_cf.stride(0), x_cf.stride(1), x_cf.stride(0),
+        taps, dil, pad, _lib.ptr(dw), dw.stride(1), int(accumulate), block_n, _lib.stream())
+    _lib.check(rc, "gtn_conv1d_wgrad_bf16")
+    return dw
