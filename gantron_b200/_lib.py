@@ -42,6 +42,8 @@ SIGNATURES = {
                               c_p, c_i, c_p, c_i, c_p]),
     "gtn_conv1d_wgrad_bf16": (c_i, [c_p, c_p, c_i, c_i, c_i, c_i, c_ll, c_ll, c_ll, c_ll,
                                     c_i, c_i, c_i, c_p, c_ll, c_i, c_i, c_p]),
+    "gtn_gemm_tn_bf16": (c_i, [c_p, c_p, c_i, c_i, c_i, c_ll, c_ll, c_i, c_ll, c_ll,
+                               c_p, c_i, c_ll, c_ll, c_i, c_p, c_p, c_i, c_i, c_p]),
 }
 
 

@@ -84,12 +84,26 @@ int gtn_conv1d_wgrad_bf16(const void* dY, const void* X, int nbatch, int Cout, i
                           int taps, int dil, int pad, float* dW, long long ldw, int accumulate,
                           int block_n, void* stream) {
   GemmDesc g;
-  g.mode = MODE_WGRAD; g.M = Cout; g.N = Cin; g.batch = taps; g.block_n = block_n > 0 ? block_n : 128;
+  g.mode = MODE_WGRAD; g.mn_major = 1; g.M = Cout; g.N = Cin; g.batch = taps; g.block_n = block_n > 0 ? block_n : 128;
   g.t_blocks = (T + 63) / 64; g.num_k_blocks = nbatch * g.t_blocks; g.dil = dil; g.pad = pad;
-  g.A = dY; g.a_d0 = T; g.a_d1 = Cout; g.a_d2 = nbatch; g.a_s1 = ldy; g.a_s2 = strideYb;
-  g.B = X;  g.b_d0 = T; g.b_d1 = Cin;  g.b_d2 = nbatch; g.b_s1 = ldx; g.b_s2 = strideXb;
+  g.A = dY; g.a_d0 = Cout; g.a_d1 = T; g.a_d2 = nbatch; g.a_s1 = ldy; g.a_s2 = strideYb;
+  g.B = X;  g.b_d0 = Cin;  g.b_d1 = T; g.b_d2 = nbatch; g.b_s1 = ldx; g.b_s2 = strideXb;
   g.C = dW; g.ldc = ldw; g.strideC = (long long)Cout * ldw; g.c_bf16 = 0; g.c_trans = 0;
   g.accumulate = accumulate;
+  return gemm_launch(g, (cudaStream_t)stream);
+}
+
+int gtn_gemm_tn_bf16(const void* A, const void* B, int M, int N, int K, long long lda, long long ldb,
+                     int batch, long long strideA, long long strideB,
+                     void* C, int c_dtype, long long ldc, long long strideC, int c_trans,
+                     const float* bias_m, const float* bias_n, int accumulate, int block_n, void* stream) {
+  GemmDesc g;
+  g.mode = MODE_PLAIN; g.mn_major = 1; g.M = M; g.N = N; g.num_k_blocks = (K + 63) / 64; g.batch = batch < 1 ? 1 : batch;
+  g.block_n = block_n > 0 ? block_n : 128;
+  g.A = A; g.a_d0 = M; g.a_d1 = K; g.a_d2 = g.batch; g.a_s1 = lda; g.a_s2 = strideA;
+  g.B = B; g.b_d0 = N; g.b_d1 = K; g.b_d2 = g.batch; g.b_s1 = ldb; g.b_s2 = strideB;
+  g.C = C; g.ldc = ldc; g.strideC = strideC; g.c_bf16 = c_dtype; g.c_trans = c_trans;
+  g.bias_m = bias_m; g.bias_n = bias_n; g.accumulate = accumulate;
   return gemm_launch(g, (cudaStream_t)stream);
 }
 

@@ -192,6 +192,18 @@ GTN_DEVICE uint64_t umma_desc_sw128(uint32_t smem_addr_bytes) {
   d |= (uint64_t)2 << 61;                                      // [61,64) SWIZZLE_128B
   return d;
 }
+// MN-major operand, SWIZZLE_128B: a tile is stored as 64-element (128 B) MN-slices; inside a slice K-row k
+// lives at k*128 B (8-row swizzle atoms of 1024 B -> SBO); consecutive 64-wide MN slices are 8192 B apart
+// (64 K-rows x 128 B -> LBO).
+GTN_DEVICE uint64_t umma_desc_sw128_mn(uint32_t smem_addr_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr_bytes & 0x3FFFFu) >> 4);
+  d |= (uint64_t)(8192u >> 4) << 16;
+  d |= (uint64_t)(1024u >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
 // instruction descriptor: D=f32, A=B=bf16, both K-major, M x N
 GTN_DEVICE constexpr uint32_t umma_idesc_bf16(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);

@@ -11,6 +11,10 @@
 //                 the tap shift is a TMA coordinate offset on the time axis (zero padding = OOB fill).
 //                 Postnet (model.py:146-151) and Discriminator (model.py:514-527, layers.py:43-60).
 //   MODE_WGRAD  : conv1d weight gradient: M = C_out, N = C_in, K = (batch, time), one tap per blockIdx.z.
+// and two operand majors: K-major (rows of A/B are K-contiguous) or MN-major ("TN": A is [K][M], B is [K][N],
+// both row-major with K as the row index -- the natural layout of every weight gradient, where K is
+// (time, batch); the TMA box is then 64 K-rows x 64 MN-elements and the UMMA descriptors use the MN-major
+// canonical SWIZZLE_128B layout, so no transposed copy of any activation is ever materialised).
 //
 // Structure (one 128 x BN output tile per CTA): warp 0 = TMA producer, warp 1 = MMA issuer (a single
 // elected thread issues tcgen05.mma, accumulator in TMEM), warp 2 = TMEM allocator, warps 4-7 = epilogue
@@ -26,6 +30,7 @@ static constexpr int BK = 64;  // 64 bf16 = 128 B = one SWIZZLE_128B row
 
 struct GemmKernelParams {
   int mode;
+  int mn_major;           // 0: A[m][k], B[n][k]   1: A[k][m], B[k][n]
   int M, N;               // logical output extent per z (rows = M, cols = N)
   int num_k_blocks;
   // MODE_CONV
@@ -96,38 +101,60 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const uint32_t ph = (uint32_t)(kb / stages) & 1u;
         wait_or_trap(&empty[s], ph ^ 1u);
         mbar_expect_tx(&full[s], A_BYTES + B_BYTES);
-        int a0, a1, a2, b0, b1, b2;
-        if (p.mode == MODE_PLAIN) {
-          a0 = kb * BK; a1 = m0; a2 = z;
-          b0 = kb * BK; b1 = n0; b2 = z;
-        } else if (p.mode == MODE_CONV) {
-          const int tap = kb / p.ci_blocks, cib = kb - tap * p.ci_blocks;
-          a0 = tap * p.cin_pad + cib * BK; a1 = m0; a2 = 0;
-          b0 = cib * BK; b1 = n0 + tap * p.dil - p.pad; b2 = z;
-        } else {  // MODE_WGRAD: k-block -> (batch, time block); z = tap
-          const int bb = kb / p.t_blocks, tb = kb - bb * p.t_blocks;
-          a0 = tb * BK; a1 = m0; a2 = bb;
-          b0 = tb * BK + z * p.taps_dil - p.taps_pad; b1 = n0; b2 = bb;
+        uint8_t* dA = sA + (size_t)s * A_BYTES;
+        uint8_t* dB = sB + (size_t)s * B_BYTES;
+        if (!p.mn_major) {
+          int a0, a1, a2, b0, b1, b2;
+          if (p.mode == MODE_PLAIN) {
+            a0 = kb * BK; a1 = m0; a2 = z;
+            b0 = kb * BK; b1 = n0; b2 = z;
+          } else {  // MODE_CONV
+            const int tap = kb / p.ci_blocks, cib = kb - tap * p.ci_blocks;
+            a0 = tap * p.cin_pad + cib * BK; a1 = m0; a2 = 0;
+            b0 = cib * BK; b1 = n0 + tap * p.dil - p.pad; b2 = z;
+          }
+          tma_load_3d(dA, &tmA, &full[s], a0, a1, a2);
+          tma_load_3d(dB, &tmB, &full[s], b0, b1, b2);
+        } else {
+          // MN-major: boxes of 64 MN-elements (inner, 128 B) x 64 K-rows, one per 64-wide slice of the tile
+          int ka, kbr, za, zb;
+          if (p.mode == MODE_PLAIN) {
+            ka = kbr = kb * BK; za = zb = z;
+          } else {  // MODE_WGRAD: k-block -> (batch, time block); z = tap; the tap shift is a K-row offset of B
+            const int bb = kb / p.t_blocks, tb = kb - bb * p.t_blocks;
+            ka = tb * BK; kbr = tb * BK + z * p.taps_dil - p.taps_pad; za = zb = bb;
+          }
+#pragma unroll
+          for (int h = 0; h < BM / 64; ++h) tma_load_3d(dA + h * 8192, &tmA, &full[s], m0 + 64 * h, ka, za);
+#pragma unroll
+          for (int h = 0; h < BN / 64; ++h) tma_load_3d(dB + h * 8192, &tmB, &full[s], n0 + 64 * h, kbr, zb);
         }
-        tma_load_3d(sA + (size_t)s * A_BYTES, &tmA, &full[s], a0, a1, a2);
-        tma_load_3d(sB + (size_t)s * B_BYTES, &tmB, &full[s], b0, b1, b2);
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
       // ------------------------------ MMA issuer ------------------------------
-      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+      const uint32_t idesc = umma_idesc_bf16(BM, BN) | (p.mn_major ? ((1u << 15) | (1u << 16)) : 0u);
       for (int kb = 0; kb < nk; ++kb) {
         const int s = kb % stages;
         const uint32_t ph = (uint32_t)(kb / stages) & 1u;
         wait_or_trap(&full[s], ph);
         tc_fence_after();
-        const uint64_t da = umma_desc_sw128(smem_u32(sA + (size_t)s * A_BYTES));
-        const uint64_t db = umma_desc_sw128(smem_u32(sB + (size_t)s * B_BYTES));
+        const uint32_t aA = smem_u32(sA + (size_t)s * A_BYTES), aB = smem_u32(sB + (size_t)s * B_BYTES);
+        if (!p.mn_major) {
+          const uint64_t da = umma_desc_sw128(aA), db = umma_desc_sw128(aB);
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k) {
-          // advance 16 bf16 = 32 B along K inside the 128 B swizzle row: +2 in the (addr >> 4) field
-          umma_bf16(tmem_acc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
+          for (int k = 0; k < BK / 16; ++k) {
+            // advance 16 bf16 = 32 B along K inside the 128 B swizzle row: +2 in the (addr >> 4) field
+            umma_bf16(tmem_acc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
+          }
+        } else {
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            // 16 K-rows = two 8-row swizzle atoms = 2048 B per UMMA K step
+            umma_bf16(tmem_acc, umma_desc_sw128_mn(aA + k * 2048), umma_desc_sw128_mn(aB + k * 2048), idesc,
+                      (uint32_t)((kb | k) != 0));
+          }
         }
         umma_commit(&empty[s]);      // frees the smem slot once these MMAs retire
       }
@@ -272,6 +299,7 @@ static EncodeTiledFn get_encode_fn() {
 // 3-D bf16 tensor map: dims (d0 inner, d1, d2), byte strides for d1 / d2, box (64, box1, 1), SWIZZLE_128B.
 static int make_map(CUtensorMap* out, const void* base, long long d0, long long d1, long long d2,
                     long long stride1_elems, long long stride2_elems, int box1) {
+  // box is always 64 inner elements (128 B = one swizzle row) x box1 rows
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return -3;
   GTN_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base %p not 16-byte aligned", base);
@@ -312,12 +340,12 @@ int gemm_launch(const GemmDesc& g, cudaStream_t st) {
   const int BN = g.block_n;
   GTN_REQUIRE(BN == 64 || BN == 128 || BN == 256, "block_n must be 64/128/256");
   CUtensorMap ta, tb;
-  int rc = make_map(&ta, g.A, g.a_d0, g.a_d1, g.a_d2, g.a_s1, g.a_s2, BM);
+  int rc = make_map(&ta, g.A, g.a_d0, g.a_d1, g.a_d2, g.a_s1, g.a_s2, g.mn_major ? BK : BM);
   if (rc) return rc;
-  rc = make_map(&tb, g.B, g.b_d0, g.b_d1, g.b_d2, g.b_s1, g.b_s2, BN);
+  rc = make_map(&tb, g.B, g.b_d0, g.b_d1, g.b_d2, g.b_s1, g.b_s2, g.mn_major ? BK : BN);
   if (rc) return rc;
   GemmKernelParams kp;
-  kp.mode = g.mode; kp.M = g.M; kp.N = g.N; kp.num_k_blocks = g.num_k_blocks;
+  kp.mode = g.mode; kp.mn_major = g.mn_major; kp.M = g.M; kp.N = g.N; kp.num_k_blocks = g.num_k_blocks;
   kp.ci_blocks = g.ci_blocks; kp.cin_pad = g.cin_pad; kp.dil = g.dil; kp.pad = g.pad;
   kp.t_blocks = g.t_blocks; kp.taps_dil = g.dil; kp.taps_pad = g.pad;
   kp.C = g.C; kp.ldc = g.ldc; kp.strideC = g.strideC; kp.c_bf16 = g.c_bf16; kp.c_trans = g.c_trans;

@@ -10,6 +10,7 @@ enum { MODE_PLAIN = 0, MODE_CONV = 1, MODE_WGRAD = 2 };
 // Fully general description of one tcgen05 GEMM launch (see gtn_gemm.cu).
 struct GemmDesc {
   int mode = MODE_PLAIN;
+  int mn_major = 0;   // operands are [K][M] / [K][N] (MN contiguous) instead of [M][K] / [N][K]
   int M = 0, N = 0, num_k_blocks = 0, batch = 1, block_n = 128;
   // operand A / B as 3-D bf16 tensors: dims (d0 = K-contiguous inner, d1, d2), element strides of d1, d2
   const void* A = nullptr; long long a_d0 = 0, a_d1 = 0, a_d2 = 1, a_s1 = 0, a_s2 = 0;

@@ -113,18 +113,44 @@ def conv1d(wp: torch.Tensor, cin: int, cin_pad: int, taps: int, dil: int, pad: i
     _lib.check(rc, "gtn_conv1d_bf16")
 
 
-def conv1d_wgrad(dy_cf: torch.Tensor, x_cf: torch.Tensor, T: int, taps: int, dil: int, pad: int,
+def conv1d_wgrad(dy_cl: torch.Tensor, x_cl: torch.Tensor, cin: int, taps: int, dil: int, pad: int,
                  dw: torch.Tensor, accumulate: bool = False, block_n: int = 128) -> torch.Tensor:
-    """dw[tap][co][ci] (+)= sum_{b,t} dy_cf[b,co,t] x_cf[b,ci,t+tap*dil-pad]; dy_cf/x_cf channels-first bf16
-    whose last dim (time, possibly padded to a multiple of 8) is contiguous; only the first T steps are read."""
-    assert dy_cf.dtype == _BF16 and x_cf.dtype == _BF16 and dy_cf.stride(2) == 1 and x_cf.stride(2) == 1
-    Bn, cout, _ = dy_cf.shape
-    cin = x_cf.shape[1]
+    """dw[tap][co][ci] (+)= sum_{b,t} dy_cl[b,t,co] x_cl[b,t+tap*dil-pad,ci]; both channels-last bf16."""
+    assert dy_cl.dtype == _BF16 and x_cl.dtype == _BF16 and dy_cl.stride(2) == 1 and x_cl.stride(2) == 1
+    Bn, T, cout = dy_cl.shape
+    assert x_cl.shape[0] == Bn and x_cl.shape[1] == T and x_cl.shape[2] >= cin
     assert dw.dtype == torch.float32 and tuple(dw.shape) == (taps, cout, cin) and dw.is_contiguous()
     lib = _lib.load()
     rc = lib.gtn_conv1d_wgrad_bf16(
-        _lib.ptr(dy_cf), _lib.ptr(x_cf), Bn, cout, cin, T,
-        dy_cf.stride(1), dy_cf.stride(0), x_cf.stride(1), x_cf.stride(0),
+        _lib.ptr(dy_cl), _lib.ptr(x_cl), Bn, cout, cin, T,
+        dy_cl.stride(1), dy_cl.stride(0), x_cl.stride(1), x_cl.stride(0),
         taps, dil, pad, _lib.ptr(dw), dw.stride(1), int(accumulate), block_n, _lib.stream())
     _lib.check(rc, "gtn_conv1d_wgrad_bf16")
     return dw
+
+
+def gemm_tn(A: torch.Tensor, B: torch.Tensor, out: torch.Tensor, *, trans_out: bool = False,
+            bias_m: Optional[torch.Tensor] = None, bias_n: Optional[torch.Tensor] = None,
+            accumulate: bool = False, block_n: int = 128) -> torch.Tensor:
+    """out[z,m,n] (+)= sum_k A[z,k,m] B[z,k,n]; A (K,M)/(Z,K,M), B (K,N)/(Z,K,N) bf16 with the last dim contiguous."""
+    for t in (A, B):
+        assert t.dtype == _BF16 and t.is_cuda and t.stride(-1) == 1
+    if A.dim() == 2:
+        Z, (K, M), lda, sa = 1, A.shape, A.stride(0), 0
+        (Kb, N), ldb, sb = B.shape, B.stride(0), 0
+    else:
+        Z, K, M = A.shape
+        lda, sa = A.stride(1), A.stride(0)
+        Zb, Kb, N = B.shape
+        assert Zb == Z
+        ldb, sb = B.stride(1), B.stride(0)
+    assert K == Kb
+    exp = (N, M) if trans_out else (M, N)
+    assert tuple(out.shape[-2:]) == exp and out.stride(-1) == 1
+    ldc, sc = (out.stride(0), 0) if out.dim() == 2 else (out.stride(1), out.stride(0))
+    lib = _lib.load()
+    rc = lib.gtn_gemm_tn_bf16(_lib.ptr(A), _lib.ptr(B), M, N, K, lda, ldb, Z, sa, sb,
+                              _lib.ptr(out), _dt(out), ldc, sc, int(trans_out),
+                              _lib.ptr(bias_m), _lib.ptr(bias_n), int(accumulate), block_n, _lib.stream())
+    _lib.check(rc, "gtn_gemm_tn_bf16")
+    return out

@@ -53,12 +53,23 @@ int gtn_conv1d_bf16(const void* Wp, int Cout, int Cin, int cin_pad, int taps, in
                     void* C2, int c2_dtype, long long ldc2, long long strideC2b,
                     const float* bias_m, int act, float* stats, int block_n, void* stream);
 
-/* conv1d weight gradient: dW[tap][co][ci] (+)= sum_{b,t} dY[b][co][t] * X[b][ci][t + tap*dil - pad]
- * dY, X channels-first bf16 with time contiguous ([b][c][ld]); dW fp32 [taps][Cout][ldw]. */
+/* conv1d weight gradient: dW[tap][co][ci] (+)= sum_{b,t} dY[b][t][co] * X[b][t + tap*dil - pad][ci]
+ * dY, X channels-LAST bf16 ([b][t][ld], the same buffers forward/dgrad use: MN-major UMMA operands, the
+ * tap shift is a TMA row offset with zero fill); dW fp32 [taps][Cout][ldw].  Replaces autograd's
+ * conv weight gradients of model.py:146-151 / 506-512. */
 int gtn_conv1d_wgrad_bf16(const void* dY, const void* X, int nbatch, int Cout, int Cin, int T,
                           long long ldy, long long strideYb, long long ldx, long long strideXb,
                           int taps, int dil, int pad, float* dW, long long ldw, int accumulate,
                           int block_n, void* stream);
+
+/* "TN" GEMM on MN-major operands: D[z][m][n] (+)= sum_k A[z][k][m] * B[z][k][n]; A is [K][lda], B is [K][ldb]
+ * (row index = K).  This is the shape of every deferred weight gradient of the decoder (K = time x batch:
+ * dW = dGates^T . X replaces the ~800 per-step `mm` + `add_` accumulations autograd performs for
+ * model.py:391-392,406-407,413-416) and of d(memory)[b] = align[b]^T . dctx[b] (model.py:88). */
+int gtn_gemm_tn_bf16(const void* A, const void* B, int M, int N, int K, long long lda, long long ldb,
+                     int batch, long long strideA, long long strideB,
+                     void* C, int c_dtype, long long ldc, long long strideC, int c_trans,
+                     const float* bias_m, const float* bias_n, int accumulate, int block_n, void* stream);
 
 #ifdef __cplusplus
 }

@@ -115,10 +115,37 @@ def test_conv1d_dgrad_and_wgrad(cin, cout, k, dil, T):
     dx_cl = torch.empty(Bn, T, cin, device="cuda")
     ops.conv1d(wpt, cout, cpad, k, dil, pad, dy_cl, dx_cl, None)
     assert_close(dx_cl.transpose(1, 2), x.grad, "conv dgrad", atol=0.02, rtol=1e-3)
-    # wgrad from channels-first (time-contiguous, padded to 8) copies
-    Tp = (T + 7) // 8 * 8
-    dy_cf = torch.zeros(Bn, cout, Tp, device="cuda", dtype=BF); dy_cf[:, :, :T] = dy.to(BF)
-    x_cf = torch.zeros(Bn, cin, Tp, device="cuda", dtype=BF); x_cf[:, :, :T] = x.detach().to(BF)
+    # wgrad straight from the channels-last buffers (MN-major operands)
+    x_cl = x.detach().to(BF).transpose(1, 2).contiguous()
     dw = torch.empty(k, cout, cin, device="cuda")
-    ops.conv1d_wgrad(dy_cf, x_cf, T, k, dil, pad, dw)
+    ops.conv1d_wgrad(dy_cl, x_cl, cin, k, dil, pad, dw)
     assert_close(dw.permute(1, 2, 0), w.grad, "conv wgrad", atol=0.05, rtol=2e-3)
+    ops.conv1d_wgrad(dy_cl, x_cl, cin, k, dil, pad, dw, accumulate=True, block_n=64)
+    assert_close(dw.permute(1, 2, 0), 2 * w.grad, "conv wgrad accumulate bn64", atol=0.1, rtol=2e-3)
+
+
+@pytest.mark.parametrize("M,N,K,bn", [(128, 128, 64, 128), (4096, 2304, 640, 128), (4096, 3072, 520, 256),
+                                      (81, 2048, 200, 64), (150, 1024, 72, 128)])
+def test_gemm_tn(M, N, K, bn):
+    from gantron_b200 import ops
+    Mp, Np = (M + 7) // 8 * 8, (N + 7) // 8 * 8
+    A = _rand(K, Mp, seed=21).to(BF)[:, :M]
+    B = _rand(K, Np, seed=22).to(BF)[:, :N]
+    ref = A.float().t() @ B.float()
+    out = torch.empty(M, N, device="cuda")
+    ops.gemm_tn(A, B, out, block_n=bn)
+    assert_close(out, ref, f"gemm_tn {M}x{N}x{K}", atol=2e-3 * K ** 0.5, rtol=1e-3)
+    out_t = torch.zeros(N, M, device="cuda")
+    ops.gemm_tn(A, B, out_t, trans_out=True, block_n=bn)
+    ops.gemm_tn(A, B, out_t, trans_out=True, accumulate=True, block_n=bn)
+    assert_close(out_t, 2 * ref.t(), "gemm_tn transposed+accumulate", atol=4e-3 * K ** 0.5, rtol=1e-3)
+
+
+def test_gemm_tn_batched():
+    from gantron_b200 import ops
+    Z, M, N, K = 4, 152, 1024, 96     # d(memory)[b] = align[b]^T . dctx[b]
+    A = _rand(Z, K, M, seed=23).to(BF)
+    B = _rand(Z, K, N, seed=24).to(BF)
+    out = torch.empty(Z, M, N, device="cuda")
+    ops.gemm_tn(A, B, out)
+    assert_close(out, torch.einsum("zkm,zkn->zmn", A.float(), B.float()), "gemm_tn batched", atol=0.03, rtol=1e-3)
