@@ -44,7 +44,29 @@ SIGNATURES = {
                                     c_i, c_i, c_i, c_p, c_ll, c_i, c_i, c_p]),
     "gtn_gemm_tn_bf16": (c_i, [c_p, c_p, c_i, c_i, c_i, c_ll, c_ll, c_i, c_ll, c_ll,
                                c_p, c_i, c_ll, c_ll, c_i, c_p, c_p, c_i, c_i, c_p]),
+    "gtn_decoder_forward": (c_i, [c_p, c_p]),
+    "gtn_sizeof": (c_i, [c_i]),
 }
+
+
+c_u = C.c_uint
+
+
+class DecoderFwdParams(C.Structure):
+    """Mirror of `gtn_decoder_fwd_params` (include/gantron_b200.h) -- field order and types must match."""
+    _fields_ = (
+        [(n, c_i) for n in ("B", "Tin", "ldT", "n_steps", "E", "Cc", "D", "Dp", "Ha", "Hap", "Hd", "Hdp",
+                            "P", "Pp", "A", "F", "KS", "NM", "NMp", "prec", "mult", "train", "use_dropout",
+                            "mem_bf16", "ignore_stop")]
+        + [(n, c_f) for n in ("p_att", "p_dec", "gate_threshold")]
+        + [("thr_att", c_u), ("thr_dec", c_u), ("seed", c_ull)]
+        + [(n, c_p) for n in ("w_att", "w_dec", "w_proj", "w_pre1", "w_pre2", "b_att", "b_dec", "b_proj",
+                              "wq", "v", "wconv", "wdense", "mem_enc", "pm", "mem_const", "lengths", "pre_all",
+                              "xh_a", "xh_d", "xctx", "xmel", "xp1", "xp2", "c_a", "c_d", "w_prev", "w_cum",
+                              "qpart", "barrier", "done", "lengths_out", "stop", "steps_done",
+                              "align_out", "mel_out", "gate_out",
+                              "gates_a", "c_a_all", "h_a_all", "gates_d", "c_d_all", "h_d_all", "ctx_all")]
+    )
 
 
 def load() -> C.CDLL:

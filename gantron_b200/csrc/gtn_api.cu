@@ -30,6 +30,11 @@ int gtn_version(void) { return 100; }
 long long gtn_launch_count(void) { return g_launches.load(); }
 void gtn_reset_launch_count(void) { g_launches.store(0); }
 
+int gtn_sizeof(int which) {
+  if (which == 0) return (int)sizeof(gtn_decoder_fwd_params);
+  return -1;
+}
+
 int gtn_device_info(int* sm_count, int* cc_major, int* cc_minor, int* coop) {
   int dev = 0;
   GTN_CUDA_OK(cudaGetDevice(&dev));

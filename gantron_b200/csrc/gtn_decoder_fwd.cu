@@ -25,6 +25,7 @@
 namespace gtn {
 
 typedef gtn_decoder_fwd_params DecFwd;
+#define BFP(x) (reinterpret_cast<bf16*>(const_cast<void*>(static_cast<const void*>(x))))
 
 struct FwdSmem {
   float* red;    // [8][2][NT][4][32]
@@ -91,21 +92,21 @@ GTN_DEVICE void lstm_phase(const DecFwd& p, const FwdSmem& sm, int t, bool is_at
   const float* bias;
   if (is_att) {
     const int ldp = mult * p.Pp;
-    segs[0].x = p.train ? p.pre_all + (size_t)t * p.B * ldp : p.xp2; segs[0].ld = ldp; segs[0].nch = ldp / 32;
-    segs[1].x = p.xctx; segs[1].ld = mult * p.Dp; segs[1].nch = mult * p.Dp / 32;
-    segs[2].x = p.xh_a + (size_t)cur * p.B * mult * p.Hap; segs[2].ld = mult * p.Hap; segs[2].nch = mult * p.Hap / 32;
+    segs[0].x = p.train ? BFP(p.pre_all) + (size_t)t * p.B * ldp : BFP(p.xp2); segs[0].ld = ldp; segs[0].nch = ldp / 32;
+    segs[1].x = BFP(p.xctx); segs[1].ld = mult * p.Dp; segs[1].nch = mult * p.Dp / 32;
+    segs[2].x = BFP(p.xh_a) + (size_t)cur * p.B * mult * p.Hap; segs[2].ld = mult * p.Hap; segs[2].nch = mult * p.Hap / 32;
     Ktot = mult * (p.Pp + p.Dp + p.Hap);
-    W = p.w_att; bias = p.b_att;
+    W = BFP(p.w_att); bias = p.b_att;
   } else {
-    segs[0].x = p.xh_a + (size_t)nxt * p.B * mult * p.Hap; segs[0].ld = mult * p.Hap; segs[0].nch = mult * p.Hap / 32;
-    segs[1].x = p.xctx; segs[1].ld = mult * p.Dp; segs[1].nch = mult * p.Dp / 32;
-    segs[2].x = p.xh_d + (size_t)cur * p.B * mult * p.Hdp; segs[2].ld = mult * p.Hdp; segs[2].nch = mult * p.Hdp / 32;
+    segs[0].x = BFP(p.xh_a) + (size_t)nxt * p.B * mult * p.Hap; segs[0].ld = mult * p.Hap; segs[0].nch = mult * p.Hap / 32;
+    segs[1].x = BFP(p.xctx); segs[1].ld = mult * p.Dp; segs[1].nch = mult * p.Dp / 32;
+    segs[2].x = BFP(p.xh_d) + (size_t)cur * p.B * mult * p.Hdp; segs[2].ld = mult * p.Hdp; segs[2].nch = mult * p.Hdp / 32;
     Ktot = mult * (p.Hap + p.Dp + p.Hdp);
-    W = p.w_dec; bias = p.b_dec;
+    W = BFP(p.w_dec); bias = p.b_dec;
   }
   const int nch = Ktot / 32;
   const int c_begin = (int)((long long)warp * nch / 8), c_end = (int)((long long)(warp + 1) * nch / 8);
-  bf16* xh_next = (is_att ? p.xh_a : p.xh_d) + (size_t)nxt * p.B * mult * Hp;
+  bf16* xh_next = (is_att ? BFP(p.xh_a) : BFP(p.xh_d)) + (size_t)nxt * p.B * mult * Hp;
   float* cst = is_att ? p.c_a : p.c_d;
   const float pdrop = is_att ? p.p_att : p.p_dec;
   const unsigned thr = is_att ? p.thr_att : p.thr_dec;
@@ -191,16 +192,16 @@ GTN_DEVICE void small_linear_phase(const DecFwd& p, const FwdSmem& sm, int t, in
   int nseg, Ktot, rows;
   const bf16* W;
   if (kind == 0) {
-    segs[0].x = p.xmel; segs[0].ld = mult * p.NMp; segs[0].nch = mult * p.NMp / 32; nseg = 1;
-    Ktot = mult * p.NMp; rows = p.P; W = p.w_pre1;
+    segs[0].x = BFP(p.xmel); segs[0].ld = mult * p.NMp; segs[0].nch = mult * p.NMp / 32; nseg = 1;
+    Ktot = mult * p.NMp; rows = p.P; W = BFP(p.w_pre1);
   } else if (kind == 1) {
-    segs[0].x = p.xp1; segs[0].ld = mult * p.Pp; segs[0].nch = mult * p.Pp / 32; nseg = 1;
-    Ktot = mult * p.Pp; rows = p.P; W = p.w_pre2;
+    segs[0].x = BFP(p.xp1); segs[0].ld = mult * p.Pp; segs[0].nch = mult * p.Pp / 32; nseg = 1;
+    Ktot = mult * p.Pp; rows = p.P; W = BFP(p.w_pre2);
   } else {
     const int nxt = (t & 1) ^ 1;
-    segs[0].x = p.xh_d + (size_t)nxt * p.B * mult * p.Hdp; segs[0].ld = mult * p.Hdp; segs[0].nch = mult * p.Hdp / 32;
-    segs[1].x = p.xctx; segs[1].ld = mult * p.Dp; segs[1].nch = mult * p.Dp / 32; nseg = 2;
-    Ktot = mult * (p.Hdp + p.Dp); rows = p.NM + 1; W = p.w_proj;
+    segs[0].x = BFP(p.xh_d) + (size_t)nxt * p.B * mult * p.Hdp; segs[0].ld = mult * p.Hdp; segs[0].nch = mult * p.Hdp / 32;
+    segs[1].x = BFP(p.xctx); segs[1].ld = mult * p.Dp; segs[1].nch = mult * p.Dp / 32; nseg = 2;
+    Ktot = mult * (p.Hdp + p.Dp); rows = p.NM + 1; W = BFP(p.w_proj);
   }
   const int nch = Ktot / 32;
   const int c_begin = (int)((long long)warp * nch / 8), c_end = (int)((long long)(warp + 1) * nch / 8);
@@ -229,12 +230,12 @@ GTN_DEVICE void small_linear_phase(const DecFwd& p, const FwdSmem& sm, int t, in
           val = fmaxf(val, 0.f);
           const uint32_t bits = philox_bits(p.seed, kind == 0 ? 1u : 2u, (uint32_t)t, (uint32_t)(b * p.P + row));
           val = bits >= 0x80000000u ? val * 2.0f : 0.f;     // p = 0.5, always on (model.py:104)
-          store_act((kind == 0 ? p.xp1 : p.xp2) + (size_t)b * mult * p.Pp, row, p.Pp, p.prec, val);
+          store_act((kind == 0 ? BFP(p.xp1) : BFP(p.xp2)) + (size_t)b * mult * p.Pp, row, p.Pp, p.prec, val);
         } else {
           val += p.b_proj[row];
           if (row < p.NM) {
             p.mel_out[((size_t)b * p.NM + row) * p.n_steps + t] = val;
-            store_act(p.xmel + (size_t)b * mult * p.NMp, row, p.NMp, p.prec, val);
+            store_act(BFP(p.xmel) + (size_t)b * mult * p.NMp, row, p.NMp, p.prec, val);
           } else {
             p.gate_out[(size_t)b * p.n_steps + t] = val;
             if (sigmoid_acc(val) > p.gate_threshold && p.done[b] == 0) { p.done[b] = 1; p.lengths_out[b] = t + 1; }
@@ -336,7 +337,7 @@ GTN_DEVICE void attention_phase(const DecFwd& p, const FwdSmem& sm, int t) {
     wsum = block_reduce(wsum, sm.scr, false);   // also orders the e_s writes before the reads below
     // context over the time-varying (encoder) columns
     const int mult = p.mult;
-    bf16* xc = p.xctx + (size_t)b * mult * p.Dp;
+    bf16* xc = BFP(p.xctx) + (size_t)b * mult * p.Dp;
     float* call = p.train ? p.ctx_all + ((size_t)t * p.B + b) * p.D : nullptr;
     for (int d = threadIdx.x; d < p.E; d += blockDim.x) {
       const MT* mp = mem + (size_t)b * Tin * p.E + d;

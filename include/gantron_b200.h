@@ -25,6 +25,8 @@ long long gtn_launch_count(void);
 void gtn_reset_launch_count(void);
 /* fills sm_count, cc_major, cc_minor, cooperative-launch support of the current device */
 int gtn_device_info(int* sm_count, int* cc_major, int* cc_minor, int* coop);
+/* sizeof() of an ABI struct, for binding self-checks: which = 0 gtn_decoder_fwd_params, 1 gtn_decoder_bwd_params */
+int gtn_sizeof(int which);
 
 /* ---- tcgen05 GEMM family (gtn_gemm.cu) ------------------------------------------------------
  * D[z][m][n] = sum_k A[z][m][k] * B[z][n][k], bf16 operands with K contiguous, fp32 accumulate in
@@ -70,6 +72,65 @@ int gtn_gemm_tn_bf16(const void* A, const void* B, int M, int N, int K, long lon
                      int batch, long long strideA, long long strideB,
                      void* C, int c_dtype, long long ldc, long long strideC, int c_trans,
                      const float* bias_m, const float* bias_n, int accumulate, int block_n, void* stream);
+
+/* ---- persistent cooperative decoder, forward (gtn_decoder_fwd.cu) ------------------------------
+ * One launch = all frames of Decoder.inference (model.py:456-497; train = 0) or of the teacher-forced
+ * loop of Decoder.forward (model.py:419-454; train = 1).  The struct lives in HOST memory.
+ *
+ * Precision: prec = 1 -> bf16 operands / fp32 accumulate; prec = 3 -> every fp32 operand is carried as
+ * three bf16 planes (K expanded 6x), fp32-accurate.  `mult` below = 1 or 6 (filled in by the library).
+ * Packed weights: bf16 [rows][mult * sum(segment pads)], segments in the K order listed, each padded
+ * to a multiple of 32 and (prec 3) expanded in place; see gantron_b200/packing.py.
+ * Activation work buffers use the same segment layout ([B][mult * pad]) and must be zero-initialised. */
+typedef struct gtn_decoder_fwd_params {
+  /* dims */
+  int B, Tin, ldT, n_steps;
+  int E, Cc, D, Dp;          /* memory = [E time-varying | Cc time-constant] columns, D = E + Cc, Dp = pad32(D) */
+  int Ha, Hap, Hd, Hdp;      /* attention / decoder LSTM width and pad32 */
+  int P, Pp, A, F, KS, NM, NMp;
+  int prec, mult;
+  int train;                 /* 1 teacher-forced, 0 autoregressive */
+  int use_dropout;           /* recurrent-state dropout (model.py:393-394,408-409), i.e. module.training */
+  int mem_bf16;              /* element type of mem_enc / pm: 1 bf16, 0 fp32 */
+  int ignore_stop;           /* inference: run exactly n_steps frames (benchmarks) */
+  float p_att, p_dec, gate_threshold;
+  unsigned int thr_att, thr_dec;      /* filled in by the library */
+  unsigned long long seed;            /* Philox key; sites 1..4, see oracle/philox.py */
+  /* weights */
+  const void *w_att;         /* [4Ha][mult*(Pp+Dp+Hap)]  K = [prenet | ctx | h_att]     (attention_rnn.weight_ih|hh) */
+  const void *w_dec;         /* [4Hd][mult*(Hap+Dp+Hdp)] K = [h_att | ctx | h_dec]      (decoder_rnn.weight_ih|hh)  */
+  const void *w_proj;        /* [pad16(NM+1)][mult*(Hdp+Dp)] rows 0..NM-1 mel, NM gate  (linear_projection, gate_layer) */
+  const void *w_pre1;        /* [P][mult*NMp]   (prenet.layers.0) -- inference only */
+  const void *w_pre2;        /* [P][mult*Pp]    (prenet.layers.1) -- inference only */
+  const float *b_att, *b_dec;            /* [4H] = bias_ih + bias_hh */
+  const float *b_proj;                   /* [NM+1] */
+  const float *wq, *v, *wconv, *wdense;  /* query_layer [A][Ha], v [A], location_conv [F][2][KS], location_dense [A][F] */
+  /* inputs */
+  const void *mem_enc;       /* [B][Tin][E] */
+  const void *pm;            /* processed_memory [B][Tin][A] (model.py:326) */
+  const float *mem_const;    /* [B][Cc] */
+  const int *lengths;        /* [B] valid encoder positions, or NULL (inference: no mask) */
+  const void *pre_all;       /* train: prenet outputs, bf16 [n_steps+1][B][mult*Pp] */
+  /* state / workspace (zero-initialised by the caller) */
+  void *xh_a, *xh_d;         /* bf16 [2][B][mult*Hap], [2][B][mult*Hdp] */
+  void *xctx, *xmel, *xp1, *xp2; /* bf16 [B][mult*Dp], [B][mult*NMp], [B][mult*Pp] x2 */
+  float *c_a, *c_d;          /* [B][Ha], [B][Hd] */
+  float *w_prev, *w_cum;     /* [B][ldT] */
+  float *qpart;              /* [Ha/8][B][A] */
+  unsigned int *barrier;     /* 1 word */
+  int *done, *lengths_out;   /* [B] */
+  int *stop, *steps_done;    /* 1 word each */
+  /* outputs */
+  float *align_out;          /* [B][n_steps][Tin] */
+  float *mel_out;            /* inference: [B][NM][n_steps] */
+  float *gate_out;           /* inference: [B][n_steps] */
+  /* saved for backward (train) */
+  float *gates_a, *c_a_all, *h_a_all;   /* [T][B][4Ha] (i,f,g,o post-activation), [T][B][Ha] x2 (h post-dropout) */
+  float *gates_d, *c_d_all, *h_d_all;
+  float *ctx_all;                       /* [T][B][D] */
+} gtn_decoder_fwd_params;
+
+int gtn_decoder_forward(const gtn_decoder_fwd_params* params, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,94 @@
+"""Persistent decode kernel (autoregressive inference) vs the CPU oracle, step for step.
+
+fp32 mode (3-plane bf16 split) must match the fp32 oracle to ~1e-4; bf16 mode to a stated looser bound.
+Dropout masks are the shared Philox scheme (oracle/philox.py <-> gtn_common.cuh)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import assert_close
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(B, T_in, steps, prec_name, seed=0, style_const=True, hp_extra=""):
+    from gantron_b200.hparams import HParams
+    from gantron_b200.model import Decoder
+    torch.manual_seed(seed)
+    hp = HParams(f"use_noise=True,use_labels=False,max_decoder_steps={steps},b200_precision={prec_name}" + hp_extra)
+    dec = Decoder(hp).cuda().eval()
+    g = torch.Generator().manual_seed(seed + 1)
+    enc = torch.randn(B, T_in, hp.encoder_embedding_dim, generator=g) * 0.5
+    tail = dec.decoder_in_dim - hp.encoder_embedding_dim
+    if style_const:
+        style = torch.rand(B, 1, tail, generator=g).repeat_interleave(T_in, dim=1)
+    else:
+        style = torch.rand(B, T_in, tail, generator=g)
+    memory = torch.cat((enc, style), -1)
+    return hp, dec, memory
+
+
+def _oracle(hp, dec, memory, steps, seed, force=True):
+    from oracle import gantron_oracle as O, philox as PX
+    d = O.Dims.from_hparams(hp)
+    d.spk = 0; d.emo = 0
+    d.noise = dec.decoder_in_dim - hp.encoder_embedding_dim
+    sd = {"decoder." + k: v.detach().float().cpu() for k, v in dec.state_dict().items()}
+    B = memory.shape[0]
+
+    def keep_fn(t):
+        return (torch.from_numpy(PX.keep_mask(seed, PX.SITE_PRENET1, t, (B, hp.prenet_dim), 0.5)),
+                torch.from_numpy(PX.keep_mask(seed, PX.SITE_PRENET2, t, (B, hp.prenet_dim), 0.5)))
+    with torch.no_grad():
+        return O.decoder_inference(sd, memory, d, keep_fn, max_steps=steps, force_steps=steps if force else None)
+
+
+@pytest.mark.parametrize("B,T_in,steps", [(1, 17, 6), (3, 23, 5), (9, 40, 4)])
+def test_infer_fp32_mode_matches_oracle(B, T_in, steps):
+    from gantron_b200 import decoder_ops
+    hp, dec, memory = _setup(B, T_in, steps, "fp32")
+    seed = 0xABCDEF12345
+    mel, gate, align, lengths, n = decoder_ops.decoder_inference(
+        dec.packed(), memory.cuda(), max_steps=steps, gate_threshold=0.5, seed=seed, prec=3, ignore_stop=True)
+    om, og, oa, ol, _ = _oracle(hp, dec, memory, steps, seed)
+    assert n == steps
+    assert_close(align, oa, "alignments", atol=2e-5, rtol=1e-3)
+    assert_close(mel, om, "mel", atol=2e-4, rtol=1e-3)
+    assert_close(gate, og, "gate", atol=2e-4, rtol=1e-3)
+
+
+def test_infer_nonconstant_style_uses_full_memory():
+    from gantron_b200 import decoder_ops
+    hp, dec, memory = _setup(2, 19, 4, "fp32", style_const=False)
+    seed = 77
+    mel, gate, align, lengths, n = decoder_ops.decoder_inference(
+        dec.packed(), memory.cuda(), max_steps=4, gate_threshold=0.5, seed=seed, prec=3, ignore_stop=True)
+    om, og, oa, _, _ = _oracle(hp, dec, memory, 4, seed)
+    assert_close(align, oa, "alignments", atol=2e-5, rtol=1e-3)
+    assert_close(mel, om, "mel", atol=2e-4, rtol=1e-3)
+
+
+def test_infer_bf16_mode_close_to_oracle():
+    """bf16 tolerance: 3e-2 absolute on mel (|mel| ~ 1) over the first frames; alignments 2e-2."""
+    from gantron_b200 import decoder_ops
+    hp, dec, memory = _setup(4, 31, 5, "bf16")
+    seed = 4242
+    mel, gate, align, lengths, n = decoder_ops.decoder_inference(
+        dec.packed(), memory.cuda(), max_steps=5, gate_threshold=0.5, seed=seed, prec=1, ignore_stop=True)
+    om, og, oa, _, _ = _oracle(hp, dec, memory, 5, seed)
+    assert_close(align, oa, "alignments bf16", atol=2e-2, rtol=0)
+    assert_close(mel, om, "mel bf16", atol=3e-2, rtol=3e-2)
+
+
+def test_infer_stops_on_gate_like_reference():
+    """gate bias pushed high -> sigmoid(gate) > 0.5 on the first frame: output has exactly 1 frame (the frame
+    on which the gate fired is kept, model.py:482-487)."""
+    from gantron_b200 import decoder_ops
+    hp, dec, memory = _setup(1, 17, 8, "fp32")
+    dec.gate_layer.linear_layer.bias.data.fill_(30.0)
+    mel, gate, align, lengths, n = decoder_ops.decoder_inference(
+        dec.packed(), memory.cuda(), max_steps=8, gate_threshold=0.5, seed=5, prec=3)
+    om, og, oa, ol, _ = _oracle(hp, dec, memory, 8, 5, force=False)
+    assert n == om.shape[-1] == 1 and tuple(mel.shape) == tuple(om.shape)
+    assert int(lengths[0]) == int(ol[0]) == 1
+    assert_close(mel, om, "mel", atol=2e-4, rtol=1e-3)
