@@ -46,6 +46,8 @@ SIGNATURES = {
                                c_p, c_i, c_ll, c_ll, c_i, c_p, c_p, c_i, c_i, c_p]),
     "gtn_decoder_forward": (c_i, [c_p, c_p]),
     "gtn_sizeof": (c_i, [c_i]),
+    "gtn_decoder_bwd_grid": (c_i, []),
+    "gtn_decoder_backward": (c_i, [c_p, c_p]),
 }
 
 
@@ -65,7 +67,24 @@ class DecoderFwdParams(C.Structure):
                               "xh_a", "xh_d", "xctx", "xmel", "xp1", "xp2", "c_a", "c_d", "w_prev", "w_cum",
                               "qpart", "barrier", "done", "lengths_out", "stop", "steps_done",
                               "align_out", "mel_out", "gate_out",
-                              "gates_a", "c_a_all", "h_a_all", "gates_d", "c_d_all", "h_d_all", "ctx_all")]
+                              "gates_a", "c_a_all", "h_a_all", "gates_d", "c_d_all", "h_d_all", "ctx_all",
+                              "q_all", "th_all", "f_all", "cum_all")]
+    )
+
+
+class DecoderBwdParams(C.Structure):
+    """Mirror of `gtn_decoder_bwd_params` (include/gantron_b200.h)."""
+    _fields_ = (
+        [(n, c_i) for n in ("B", "Tin", "ldT", "T", "E", "Cc", "D", "Ha", "Hd", "P", "A", "Ap", "F", "KS",
+                            "prec", "mult", "use_dropout", "mem_bf16")]
+        + [("p_att", c_f), ("p_dec", c_f), ("thr_att", c_u), ("thr_dec", c_u), ("seed", c_ull)]
+        + [(n, c_p) for n in ("wT_att", "wT_dec", "wqT", "v", "wconv", "wdense", "mem_enc", "mem_const", "lengths",
+                              "gates_a", "c_a_all", "gates_d", "c_d_all", "align", "th_all", "f_all", "cum_all",
+                              "dproj_all", "dalign", "xdg_a", "xdg_d", "xdq", "carry_ha", "dha_dec", "dc_a",
+                              "carry_hd", "dc_d", "dctx_att", "dctx_dec", "dwprev", "dcum", "barrier",
+                              "dga_all", "dgd_all", "dq_all", "dpre_all", "dctx_all", "dpm",
+                              "dv_part", "dwd_part", "dwc_part")]
+        + [("grid", c_i)]
     )
 
 

@@ -279,10 +279,13 @@ GTN_DEVICE void attention_phase(const DecFwd& p, const FwdSmem& sm, int t) {
       float s = 0.f;
       for (int c = 0; c < nq; ++c) s += __ldcg(&p.qpart[((size_t)c * p.B + b) * A + a]);
       sm.q_s[a] = s;
+      if (p.train) p.q_all[((size_t)t * p.B + b) * A + a] = s;
     }
     for (int i = threadIdx.x; i < 2 * Wd; i += blockDim.x) {
       const int ch = i / Wd, j = i - ch * Wd - half;
-      sm.wcat[i] = (j >= 0 && j < Tin) ? (ch == 0 ? wprev[j] : wcum[j]) : 0.f;
+      const float val = (j >= 0 && j < Tin) ? (ch == 0 ? wprev[j] : wcum[j]) : 0.f;
+      sm.wcat[i] = val;
+      if (p.train && ch == 1 && j >= 0 && j < Tin) p.cum_all[((size_t)t * p.B + b) * Tin + j] = val;
     }
     __syncthreads();
     // location conv (2 -> F, kernel KS, zero padded): f[j][c]
@@ -295,6 +298,7 @@ GTN_DEVICE void attention_phase(const DecFwd& p, const FwdSmem& sm, int t) {
         for (int k = 0; k < KS; ++k) s += wc[k * F] * xw[k];
       }
       sm.f_s[idx] = s;
+      if (p.train) p.f_all[((size_t)t * p.B + b) * Tin * F + idx] = s;
     }
     __syncthreads();
     // energies: one warp per encoder position
@@ -306,7 +310,9 @@ GTN_DEVICE void attention_phase(const DecFwd& p, const FwdSmem& sm, int t) {
       for (int a = lane; a < A; a += 32) {
         float s = sm.q_s[a] + ld_mem<MT>(pmj + a);
         for (int c = 0; c < F; ++c) s += sm.wdT[c * A + a] * fj[c];
-        part += sm.v_s[a] * tanh_acc(s);
+        const float th = tanh_acc(s);
+        if (p.train) p.th_all[(((size_t)t * p.B + b) * Tin + j) * A + a] = th;
+        part += sm.v_s[a] * th;
       }
       part = warp_sum(part);
       if (lane == 0) sm.e_s[j] = part;

@@ -31,6 +31,7 @@ static constexpr int BK = 64;  // 64 bf16 = 128 B = one SWIZZLE_128B row
 struct GemmKernelParams {
   int mode;
   int mn_major;           // 0: A[m][k], B[n][k]   1: A[k][m], B[k][n]
+  int b_bcast;            // B operand is shared by all z (batch stride 0)
   int M, N;               // logical output extent per z (rows = M, cols = N)
   int num_k_blocks;
   // MODE_CONV
@@ -107,7 +108,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           int a0, a1, a2, b0, b1, b2;
           if (p.mode == MODE_PLAIN) {
             a0 = kb * BK; a1 = m0; a2 = z;
-            b0 = kb * BK; b1 = n0; b2 = z;
+            b0 = kb * BK; b1 = n0; b2 = p.b_bcast ? 0 : z;
           } else {  // MODE_CONV
             const int tap = kb / p.ci_blocks, cib = kb - tap * p.ci_blocks;
             a0 = tap * p.cin_pad + cib * BK; a1 = m0; a2 = 0;
@@ -119,7 +120,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           // MN-major: boxes of 64 MN-elements (inner, 128 B) x 64 K-rows, one per 64-wide slice of the tile
           int ka, kbr, za, zb;
           if (p.mode == MODE_PLAIN) {
-            ka = kbr = kb * BK; za = zb = z;
+            ka = kbr = kb * BK; za = z; zb = p.b_bcast ? 0 : z;
           } else {  // MODE_WGRAD: k-block -> (batch, time block); z = tap; the tap shift is a K-row offset of B
             const int bb = kb / p.t_blocks, tb = kb - bb * p.t_blocks;
             ka = tb * BK; kbr = tb * BK + z * p.taps_dil - p.taps_pad; za = zb = bb;
@@ -342,10 +343,11 @@ int gemm_launch(const GemmDesc& g, cudaStream_t st) {
   CUtensorMap ta, tb;
   int rc = make_map(&ta, g.A, g.a_d0, g.a_d1, g.a_d2, g.a_s1, g.a_s2, g.mn_major ? BK : BM);
   if (rc) return rc;
-  rc = make_map(&tb, g.B, g.b_d0, g.b_d1, g.b_d2, g.b_s1, g.b_s2, g.mn_major ? BK : BN);
+  const bool b_bcast = g.mode == MODE_PLAIN && g.batch > 1 && g.b_s2 == 0;
+  rc = make_map(&tb, g.B, g.b_d0, g.b_d1, b_bcast ? 1 : g.b_d2, g.b_s1, g.b_s2, g.mn_major ? BK : BN);
   if (rc) return rc;
   GemmKernelParams kp;
-  kp.mode = g.mode; kp.mn_major = g.mn_major; kp.M = g.M; kp.N = g.N; kp.num_k_blocks = g.num_k_blocks;
+  kp.mode = g.mode; kp.mn_major = g.mn_major; kp.b_bcast = b_bcast ? 1 : 0; kp.M = g.M; kp.N = g.N; kp.num_k_blocks = g.num_k_blocks;
   kp.ci_blocks = g.ci_blocks; kp.cin_pad = g.cin_pad; kp.dil = g.dil; kp.pad = g.pad;
   kp.t_blocks = g.t_blocks; kp.taps_dil = g.dil; kp.taps_pad = g.pad;
   kp.C = g.C; kp.ldc = g.ldc; kp.strideC = g.strideC; kp.c_bf16 = g.c_bf16; kp.c_trans = g.c_trans;

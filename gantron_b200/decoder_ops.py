@@ -186,3 +186,314 @@ def decoder_inference(pk: PackedDecoder, memory: torch.Tensor, *, max_steps: int
     lengths = st["lengths_out"].clone()
     lengths[st["done"] == 0] = steps
     return (mel[:, :, :steps], gate[:, :steps].unsqueeze(-1), align[:, :steps], lengths, steps)
+
+
+# ==========================================================================================
+# Training: teacher-forced forward + backward through time
+# ==========================================================================================
+def _bf(x: torch.Tensor, kpad: int, prec: int, is_weight: bool = False) -> torch.Tensor:
+    """(rows, K) fp32/bf16 -> GEMM operand (rows, mult*kpad) bf16."""
+    if prec == 1 and x.dtype == BF16 and x.shape[-1] == kpad and x.stride(-1) == 1:
+        return x
+    return packing.expand(x.float(), kpad, prec, is_weight)
+
+
+def _wgrad_tn(dy: torch.Tensor, x: torch.Tensor, out: torch.Tensor, prec: int, accumulate: bool = False) -> None:
+    """out[m][n] (+)= sum_r dy[r][m] x[r][n]: deferred weight gradient over r = (frame, batch) rows."""
+    if prec == 1:
+        ops.gemm_tn(_rows8(dy.to(BF16)), _rows8(x.to(BF16)), out, accumulate=accumulate)
+        return
+    # fp32 mode: stack the plane products along K (rows): (hi,hi),(lo,hi),(lo2,hi),(hi,lo),(lo,lo),(hi,lo2)
+    dh = packing.split3(dy)
+    xh = packing.split3(x)
+    A = _rows8(torch.cat([dh[i] for i in packing.W_PLANES], 0))
+    Bm = _rows8(torch.cat([xh[i] for i in packing.X_PLANES], 0))
+    ops.gemm_tn(A, Bm, out, accumulate=accumulate)
+
+
+def _rows8(t: torch.Tensor) -> torch.Tensor:
+    """Make the row stride a multiple of 8 elements (TMA needs 16-byte strides)."""
+    t = t if t.stride(-1) == 1 else t.contiguous()
+    if t.stride(0) % 8 == 0 and t.data_ptr() % 16 == 0:
+        return t
+    n = t.shape[1]
+    buf = torch.zeros(t.shape[0], pad_to(n, 8), device=t.device, dtype=t.dtype)
+    buf[:, :n] = t
+    return buf[:, :n]
+
+
+class _PackedBackward:
+    """Transposed packs used by the backward kernel; built lazily next to PackedDecoder."""
+
+    def __init__(self, dec, pk: PackedDecoder):
+        d, prec = pk.dims, pk.prec
+        P = PackedDecoder._params(dec)
+        f = lambda t: t.detach().float()
+        wa = torch.cat((f(P["w_ih_a"]), f(P["w_hh_a"])), 1).t().contiguous()     # [P+D+Ha][4Ha]
+        wd = torch.cat((f(P["w_ih_d"]), f(P["w_hh_d"])), 1).t().contiguous()     # [Ha+D+Hd][4Hd]
+        self.wT_att = packing.pack_weight([(wa, 4 * d.att_rnn)], prec, row_pad=pad_to(wa.shape[0], 32))
+        self.wT_dec = packing.pack_weight([(wd, 4 * d.dec_rnn)], prec, row_pad=pad_to(wd.shape[0], 32))
+        self.Ap = pad_to(d.att_dim, 32)
+        self.wqT = packing.pack_weight([(f(P["wq"]).t().contiguous(), self.Ap)], prec, row_pad=pad_to(d.att_rnn, 32))
+        wpg = torch.cat((f(P["w_proj"]), f(P["w_gate"])), 0)                       # [n_mel+1][Hd+D]
+        self.wpgT = wpg.t().contiguous()                                           # [Hd+D][n_mel+1]
+        self.wmemT = f(P["wmem"]).t().contiguous()                                 # [D][A]
+        self.w2T = f(P["w_pre2"]).t().contiguous()                                 # [P_in][P_out] -> rows = inputs
+        self.versions = pk._versions
+
+
+def _packed_bwd(dec, pk: PackedDecoder) -> _PackedBackward:
+    pb = getattr(pk, "_bwd", None)
+    if pb is None or pb.versions != pk._versions:
+        pb = _PackedBackward(dec, pk)
+        pk._bwd = pb
+    return pb
+
+
+def prenet_forward(prenet_mod, x: torch.Tensor, seed: int, prec: int = 1) -> torch.Tensor:
+    """Stand-alone Prenet.forward (model.py:102-105) on the tcgen05 GEMM with fused relu + Philox dropout."""
+    shp = x.shape
+    x2 = x.reshape(-1, shp[-1])
+    w1 = prenet_mod.layers[0].linear_layer.weight
+    w2 = prenet_mod.layers[1].linear_layer.weight
+    h1 = _prenet_layer(x2, w1, seed, SITE_PRENET1, prec)
+    h2 = _prenet_layer(h1, w2, seed, SITE_PRENET2, prec)
+    return h2.reshape(*shp[:-1], w2.shape[0])
+
+
+def _prenet_layer(x: torch.Tensor, w: torch.Tensor, seed: int, site: int, prec: int) -> torch.Tensor:
+    kp = pad_to(x.shape[1], 8)
+    out = torch.empty(x.shape[0], w.shape[0], device=x.device, dtype=torch.float32)
+    ops.gemm(packing.expand(x.float(), kp, prec, False), packing.expand(w.detach().float(), kp, prec, True), out,
+             act=ops.ACT_RELU, dropout=(0.5, seed, site, 0))
+    return out
+
+
+def _decoder_params_list(dec):
+    P = PackedDecoder._params(dec)
+    names = ["w_ih_a", "w_hh_a", "b_ih_a", "b_hh_a", "w_ih_d", "w_hh_d", "b_ih_d", "b_hh_d", "w_proj", "b_proj",
+             "w_gate", "b_gate", "w_pre1", "w_pre2", "wq", "wmem", "v", "wconv", "wdense"]
+    return names, [P[n] for n in names]
+
+
+class _DecoderTrainFn(torch.autograd.Function):
+    """Teacher-forced decoder pass as ONE autograd node (the reference builds ~22k nodes)."""
+
+    @staticmethod
+    def forward(ctx, dec, seed, memory, mels, memory_lengths, *params):
+        pk = dec.packed()
+        d, prec = pk.dims, pk.prec
+        mult = packing.mult_of(prec)
+        B, Tin, D = memory.shape
+        T = mels.shape[2]
+        dev = memory.device
+        training = dec.training
+        E = d.enc_dim if D > d.enc_dim else D
+        mdt = torch.float32 if prec == 3 else BF16
+        memory_f = memory.detach().float().contiguous()
+
+        # ---- time-independent GEMMs: prenet over all frames (model.py:435-438), memory layer (model.py:326)
+        frames = torch.cat((torch.zeros(1, B, d.n_mel, device=dev), mels.detach().float().permute(2, 0, 1)), 0)
+        frames2 = frames.reshape((T + 1) * B, d.n_mel)
+        h1 = _prenet_layer(frames2, params[12], seed, SITE_PRENET1, prec)          # fp32 [(T+1)B][P]
+        pre = _prenet_layer(h1, params[13], seed, SITE_PRENET2, prec)              # fp32 [(T+1)B][P]
+        pre_x = packing.expand(pre, d.Pp, prec, False)                             # kernel operand
+        pm = linear_nt(memory_f.reshape(B * Tin, D), pk.wmem, prec).reshape(B, Tin, d.att_dim)
+
+        p = _lib.DecoderFwdParams()
+        _fill_common(p, d, pk, B, Tin, T, E, prec)
+        p.train, p.use_dropout, p.mem_bf16, p.ignore_stop = 1, int(training), int(mdt == BF16), 0
+        p.p_att, p.p_dec = dec.p_attention_dropout, dec.p_decoder_dropout
+        p.gate_threshold = dec.gate_threshold
+        p.seed = seed
+        st = _alloc_state(p, d, B, mult, dev)
+        mem_enc = memory_f[:, :, :E].to(mdt).contiguous()
+        mem_const = memory_f[:, 0, E:].contiguous() if E < D else torch.zeros(B, 1, device=dev)
+        pm_k = pm.to(mdt).contiguous()
+        lengths = memory_lengths.to(device=dev, dtype=torch.int32).contiguous()
+        z = lambda *s: torch.zeros(*s, device=dev)
+        e = lambda *s: torch.empty(*s, device=dev)
+        sv = dict(
+            gates_a=e(T, B, 4 * d.att_rnn), c_a_all=e(T, B, d.att_rnn), h_a_buf=z(T + 1, B, d.att_rnn),
+            gates_d=e(T, B, 4 * d.dec_rnn), c_d_all=e(T, B, d.dec_rnn), h_d_buf=z(T + 1, B, d.dec_rnn),
+            ctx_buf=z(T + 1, B, D), q_all=e(T, B, d.att_dim), th_all=e(T, B, Tin, d.att_dim),
+            f_all=e(T, B, Tin, d.loc_filters), cum_all=e(T, B, Tin), align=z(B, T, Tin))
+        p.mem_enc, p.pm, p.mem_const, p.lengths = mem_enc.data_ptr(), pm_k.data_ptr(), mem_const.data_ptr(), lengths.data_ptr()
+        p.pre_all = pre_x.data_ptr()
+        p.align_out = sv["align"].data_ptr()
+        p.gates_a, p.c_a_all, p.h_a_all = sv["gates_a"].data_ptr(), sv["c_a_all"].data_ptr(), sv["h_a_buf"][1:].data_ptr()
+        p.gates_d, p.c_d_all, p.h_d_all = sv["gates_d"].data_ptr(), sv["c_d_all"].data_ptr(), sv["h_d_buf"][1:].data_ptr()
+        p.ctx_all = sv["ctx_buf"][1:].data_ptr()
+        p.q_all, p.th_all, p.f_all, p.cum_all = (sv["q_all"].data_ptr(), sv["th_all"].data_ptr(), sv["f_all"].data_ptr(),
+                                                 sv["cum_all"].data_ptr())
+        _lib.check(_lib.load().gtn_decoder_forward(C.byref(p), _lib.stream()), "gtn_decoder_forward")
+
+        # ---- deferred mel/gate projection over all frames (model.py:411-416): batched over b so the output is
+        # written directly as [B][T][n_mel+1] (channels-last); the API tensors are views of it
+        n_out = d.n_mel + 1
+        hd = sv["h_d_buf"][1:]            # [T][B][Hd]
+        cx = sv["ctx_buf"][1:]            # [T][B][D]
+        out_cl = torch.empty(B, T, n_out, device=dev)
+        wpg = torch.cat((params[8].detach().float(), params[10].detach().float()), 0)
+        bpg = pk.b_proj
+        _proj_gemm(hd, wpg[:, :d.dec_rnn], out_cl, prec, bias=bpg, accumulate=False)
+        _proj_gemm(cx, wpg[:, d.dec_rnn:], out_cl, prec, bias=None, accumulate=True)
+        mel = out_cl[:, :, :d.n_mel].transpose(1, 2)      # (B,n_mel,T) view, like the reference's transpose
+        gate = out_cl[:, :, d.n_mel]                      # (B,T)
+        align = sv["align"]
+
+        ctx.dec, ctx.seed, ctx.training = dec, seed, training
+        ctx.dims = (B, Tin, D, T, E, prec)
+        ctx.saved = dict(sv=sv, frames2=frames2, h1=h1, pre=pre, memory_f=memory_f, mem_enc=mem_enc, mem_const=mem_const,
+                         lengths=lengths, out_cl=out_cl)
+        return mel, gate, align
+
+    @staticmethod
+    def backward(ctx, d_mel, d_gate, d_align):
+        dec = ctx.dec
+        pk = dec.packed()
+        pb = _packed_bwd(dec, pk)
+        d = pk.dims
+        B, Tin, D, T, E, prec = ctx.dims
+        mult = packing.mult_of(prec)
+        S = ctx.saved
+        sv = S["sv"]
+        dev = sv["align"].device
+        n_out = d.n_mel + 1
+        z = lambda *s, dt=torch.float32: torch.zeros(*s, device=dev, dtype=dt)
+
+        # d(out)[t][b][n_mel+1]
+        dout = z(T, B, n_out)
+        if d_mel is not None:
+            dout[:, :, :d.n_mel] = d_mel.permute(2, 0, 1)
+        if d_gate is not None:
+            dout[:, :, d.n_mel] = d_gate.t()
+        dout2 = dout.reshape(T * B, n_out)
+        # hoisted projection backward: d[h_dec'|ctx'] for every frame
+        dproj = linear_nt(dout2, pb.wpgT, prec)                                   # [TB][Hd+D]
+
+        q = _lib.DecoderBwdParams()
+        q.B, q.Tin, q.ldT, q.T = B, Tin, pad_to(Tin, 4), T
+        q.E, q.Cc, q.D, q.Ha, q.Hd, q.P, q.A, q.Ap, q.F, q.KS = (E, D - E, D, d.att_rnn, d.dec_rnn, d.prenet, d.att_dim,
+                                                               pb.Ap, d.loc_filters, d.loc_kernel)
+        q.prec = prec
+        q.use_dropout = int(ctx.training)
+        q.mem_bf16 = int(S["mem_enc"].dtype == BF16)
+        q.p_att, q.p_dec, q.seed = dec.p_attention_dropout, dec.p_decoder_dropout, ctx.seed
+        grid = _lib.load().gtn_decoder_bwd_grid()
+        q.grid = grid
+        wk = dict(
+            xdg_a=z(B, mult * 4 * d.att_rnn, dt=BF16), xdg_d=z(B, mult * 4 * d.dec_rnn, dt=BF16), xdq=z(B, mult * pb.Ap, dt=BF16),
+            carry_ha=z(B, d.att_rnn), dha_dec=z(B, d.att_rnn), dc_a=z(B, d.att_rnn), carry_hd=z(B, d.dec_rnn),
+            dc_d=z(B, d.dec_rnn), dctx_att=z(B, D), dctx_dec=z(B, D), dwprev=z(B, q.ldT), dcum=z(B, q.ldT),
+            barrier=z(4, dt=torch.int32),
+            dga_all=torch.empty(T, B, 4 * d.att_rnn, device=dev), dgd_all=torch.empty(T, B, 4 * d.dec_rnn, device=dev),
+            dq_all=torch.empty(T, B, d.att_dim, device=dev), dpre_all=torch.empty(T, B, d.prenet, device=dev),
+            dctx_all=torch.empty(B, T, D, device=dev), dpm=z(B, Tin, d.att_dim),
+            dv_part=z(grid, d.att_dim), dwd_part=z(grid, d.att_dim * d.loc_filters),
+            dwc_part=z(grid, 2 * d.loc_filters * d.loc_kernel))
+        for k, v in wk.items():
+            setattr(q, k, v.data_ptr())
+        q.wT_att, q.wT_dec, q.wqT = pb.wT_att.data_ptr(), pb.wT_dec.data_ptr(), pb.wqT.data_ptr()
+        q.v, q.wconv, q.wdense = pk.v.data_ptr(), pk.wconv.data_ptr(), pk.wdense.data_ptr()
+        q.mem_enc, q.mem_const, q.lengths = S["mem_enc"].data_ptr(), S["mem_const"].data_ptr(), S["lengths"].data_ptr()
+        q.gates_a, q.c_a_all, q.gates_d, q.c_d_all = (sv["gates_a"].data_ptr(), sv["c_a_all"].data_ptr(),
+                                                      sv["gates_d"].data_ptr(), sv["c_d_all"].data_ptr())
+        q.align, q.th_all, q.f_all, q.cum_all = (sv["align"].data_ptr(), sv["th_all"].data_ptr(), sv["f_all"].data_ptr(),
+                                                 sv["cum_all"].data_ptr())
+        q.dproj_all = dproj.data_ptr()
+        d_align_c = None
+        if d_align is not None:
+            d_align_c = d_align.float().contiguous()
+            q.dalign = d_align_c.data_ptr()
+        _lib.check(_lib.load().gtn_decoder_backward(C.byref(q), _lib.stream()), "gtn_decoder_backward")
+
+        # ---- deferred weight gradients: K = T*B GEMMs on MN-major operands --------------------------------
+        TB = T * B
+        dga = wk["dga_all"].reshape(TB, -1)
+        dgd = wk["dgd_all"].reshape(TB, -1)
+        pre_T = S["pre"][:TB]                                   # prenet outputs of frames 0..T-1
+        h_a_prev, h_a_cur = sv["h_a_buf"][:T].reshape(TB, -1), sv["h_a_buf"][1:].reshape(TB, -1)
+        h_d_prev, h_d_cur = sv["h_d_buf"][:T].reshape(TB, -1), sv["h_d_buf"][1:].reshape(TB, -1)
+        ctx_prev, ctx_cur = sv["ctx_buf"][:T].reshape(TB, -1), sv["ctx_buf"][1:].reshape(TB, -1)
+        Ha, Hd, P = d.att_rnn, d.dec_rnn, d.prenet
+        g_w_ih_a = torch.empty(4 * Ha, P + D, device=dev)
+        _wgrad_tn(dga, pre_T, g_w_ih_a[:, :P], prec)
+        _wgrad_tn(dga, ctx_prev, g_w_ih_a[:, P:], prec)
+        g_w_hh_a = torch.empty(4 * Ha, Ha, device=dev)
+        _wgrad_tn(dga, h_a_prev, g_w_hh_a, prec)
+        g_w_ih_d = torch.empty(4 * Hd, Ha + D, device=dev)
+        _wgrad_tn(dgd, h_a_cur, g_w_ih_d[:, :Ha], prec)
+        _wgrad_tn(dgd, ctx_cur, g_w_ih_d[:, Ha:], prec)
+        g_w_hh_d = torch.empty(4 * Hd, Hd, device=dev)
+        _wgrad_tn(dgd, h_d_prev, g_w_hh_d, prec)
+        ones = torch.ones(TB, 8, device=dev)
+        g_b_a = torch.empty(4 * Ha, 8, device=dev); _wgrad_tn(dga, ones, g_b_a, prec); g_b_a = g_b_a[:, 0].contiguous()
+        g_b_d = torch.empty(4 * Hd, 8, device=dev); _wgrad_tn(dgd, ones, g_b_d, prec); g_b_d = g_b_d[:, 0].contiguous()
+        g_wpg = torch.empty(n_out, Hd + D, device=dev)
+        _wgrad_tn(dout2, h_d_cur, g_wpg[:, :Hd], prec)
+        _wgrad_tn(dout2, ctx_cur, g_wpg[:, Hd:], prec)
+        g_bpg = torch.empty(n_out, 8, device=dev); _wgrad_tn(dout2, ones, g_bpg, prec); g_bpg = g_bpg[:, 0]
+        g_wq = torch.empty(d.att_dim, Ha, device=dev)
+        _wgrad_tn(wk["dq_all"].reshape(TB, -1), h_a_cur, g_wq, prec)
+        # prenet backward (relu + always-on dropout: y = relu(x) * keep * 2  =>  dx = dy * 2 * [y > 0])
+        d2 = wk["dpre_all"].reshape(TB, P) * 2.0 * (pre_T > 0)
+        g_w_pre2 = torch.empty(P, P, device=dev)
+        _wgrad_tn(d2, S["h1"][:TB], g_w_pre2, prec)
+        dh1 = linear_nt(d2, pb.w2T, prec)
+        d1 = dh1 * 2.0 * (S["h1"][:TB] > 0)
+        g_w_pre1 = torch.empty(P, d.n_mel, device=dev)
+        _wgrad_tn(d1, S["frames2"][:TB], g_w_pre1, prec)
+        # memory layer and memory gradients
+        dpm2 = wk["dpm"].reshape(B * Tin, d.att_dim)
+        mem2 = S["memory_f"].reshape(B * Tin, D)
+        g_wmem = torch.empty(d.att_dim, D, device=dev)
+        _wgrad_tn(dpm2, mem2, g_wmem, prec)
+        g_memory = None
+        if ctx.needs_input_grad[2]:
+            g_memory = linear_nt(dpm2, pb.wmemT, prec).reshape(B, Tin, D)        # through processed_memory
+            _ctx_memory_grad(sv["align"], wk["dctx_all"], g_memory, prec)        # through the context bmm
+        g_v = wk["dv_part"].sum(0).reshape(1, -1)
+        g_wd = wk["dwd_part"].sum(0).reshape(d.att_dim, d.loc_filters)
+        g_wc = wk["dwc_part"].sum(0).reshape(d.loc_filters, 2, d.loc_kernel)
+        grads = [g_w_ih_a, g_w_hh_a, g_b_a, g_b_a.clone(), g_w_ih_d, g_w_hh_d, g_b_d, g_b_d.clone(),
+                 g_wpg[:d.n_mel].contiguous(), g_bpg[:d.n_mel].contiguous(), g_wpg[d.n_mel:].contiguous(),
+                 g_bpg[d.n_mel:].contiguous(), g_w_pre1, g_w_pre2, g_wq, g_wmem, g_v, g_wc, g_wd]
+        ctx.saved = None
+        return (None, None, g_memory, None, None) + tuple(grads)
+
+
+def _proj_gemm(x_tb: torch.Tensor, w: torch.Tensor, out_cl: torch.Tensor, prec: int, bias, accumulate: bool) -> None:
+    """out_cl[b][t][:] (+)= x_tb[t][b][:] @ w.T (+ bias): batched over b so that rows land in (b, t) order."""
+    T, B, K = x_tb.shape
+    kp = pad_to(K, 8)
+    xa = packing.expand(x_tb, kp, prec, False)                 # [T][B][mult*kp]
+    wa = packing.expand(w.float(), kp, prec, True)             # [N][mult*kp]
+    A = xa.permute(1, 0, 2)                                    # [B][T][K'] view: batch stride = K', row stride = B*K'
+    wz = wa.unsqueeze(0).expand(B, -1, -1)                     # batch stride 0
+    ops.gemm(A, wz, out_cl, bias_n=bias, accumulate=accumulate)
+
+
+def _ctx_memory_grad(align: torch.Tensor, dctx_all: torch.Tensor, g_memory: torch.Tensor, prec: int) -> None:
+    """g_memory[b] += align[b]^T (T_in x T) . dctx[b] (T x D)   (backward of the context bmm, model.py:88)."""
+    B, T, Tin = align.shape
+    D = dctx_all.shape[2]
+    tp, dp = pad_to(Tin, 8), pad_to(D, 8)
+
+    def planes(x, kp, which):
+        if prec == 1:
+            buf = torch.zeros(B, T, kp, device=x.device, dtype=BF16)
+            buf[:, :, :x.shape[2]] = x.to(BF16)
+            return buf[:, :, :x.shape[2]]
+        pl = packing.split3(x)
+        buf = torch.zeros(B, 6 * T, kp, device=x.device, dtype=BF16)
+        for s, i in enumerate(which):
+            buf[:, s * T:(s + 1) * T, :x.shape[2]] = pl[i]
+        return buf[:, :, :x.shape[2]]
+    ops.gemm_tn(planes(align, tp, packing.W_PLANES), planes(dctx_all, dp, packing.X_PLANES), g_memory, accumulate=True)
+
+
+def decoder_train_forward(dec, memory: torch.Tensor, decoder_inputs: torch.Tensor, memory_lengths: torch.Tensor, seed: int):
+    """Decoder.forward (model.py:419-454) on a `memory` that already has the noise columns appended."""
+    _, params = _decoder_params_list(dec)
+    return _DecoderTrainFn.apply(dec, seed, memory, decoder_inputs, memory_lengths, *params)

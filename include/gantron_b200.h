@@ -128,9 +128,64 @@ typedef struct gtn_decoder_fwd_params {
   float *gates_a, *c_a_all, *h_a_all;   /* [T][B][4Ha] (i,f,g,o post-activation), [T][B][Ha] x2 (h post-dropout) */
   float *gates_d, *c_d_all, *h_d_all;
   float *ctx_all;                       /* [T][B][D] */
+  float *q_all;                         /* [T][B][A]       attention query */
+  float *th_all;                        /* [T][B][Tin][A]  tanh(q + loc + processed_memory) */
+  float *f_all;                         /* [T][B][Tin][F]  location-conv outputs */
+  float *cum_all;                       /* [T][B][Tin]     cumulative weights BEFORE the step (conv input ch. 1) */
 } gtn_decoder_fwd_params;
 
 int gtn_decoder_forward(const gtn_decoder_fwd_params* params, void* stream);
+
+/* ---- persistent cooperative decoder, backward through time (gtn_decoder_bwd.cu) -----------------
+ * Replaces autograd's replay of the ~22k-node tape of model.py:444-449 (BPTT over T frames) with one
+ * cooperative launch.  Per frame (t = T-1 .. 0), three grid-synchronised phases:
+ *   1  data-gradient GEMMs  dX = dGates . W  for decoder_rnn(t) and attention_rnn(t+1)
+ *   2  attention backward per sequence (context, softmax, energies, location dense + conv)
+ *   3  query backward GEMM + attention LSTM cell backward  ||  decoder LSTM cell backward of frame t-1
+ * All WEIGHT gradients are deferred: the kernel only stores per-frame gate / query gradients, and the
+ * host issues a handful of K = T*B tcgen05 GEMMs afterwards (gtn_gemm_tn_bf16). */
+typedef struct gtn_decoder_bwd_params {
+  int B, Tin, ldT, T;
+  int E, Cc, D, Ha, Hd, P, A, Ap, F, KS;
+  int prec, mult;
+  int use_dropout, mem_bf16;
+  float p_att, p_dec;
+  unsigned int thr_att, thr_dec;
+  unsigned long long seed;
+  /* transposed packed weights: rows = LSTM input features, K = mult * 4H gate rows (padded to 32 rows) */
+  const void *wT_att;        /* [pad32(P+D+Ha)][mult*4Ha]  rows = [prenet | ctx | h_att] */
+  const void *wT_dec;        /* [pad32(Ha+D+Hd)][mult*4Hd] rows = [h_att | ctx | h_dec]  */
+  const void *wqT;           /* [Ha][mult*Ap]   wqT[u][a] = query_layer[a][u] */
+  const float *v, *wconv, *wdense;
+  /* forward inputs */
+  const void *mem_enc; const float *mem_const; const int *lengths;
+  /* saved by the forward kernel */
+  const float *gates_a, *c_a_all, *gates_d, *c_d_all;
+  const float *align;        /* [B][T][Tin] */
+  const float *th_all, *f_all, *cum_all;
+  /* upstream gradients */
+  const float *dproj_all;    /* [T][B][Hd + D]: d(loss)/d[h_dec' | ctx'] through the mel/gate projection */
+  const float *dalign;       /* [B][T][Tin] or NULL */
+  /* carried state / workspace (zero-initialised) */
+  void *xdg_a, *xdg_d;       /* bf16 [B][mult*4Ha], [B][mult*4Hd]: gate gradients as GEMM operands */
+  void *xdq;                 /* bf16 [B][mult*Ap] */
+  float *carry_ha, *dha_dec, *dc_a;     /* [B][Ha] */
+  float *carry_hd, *dc_d;               /* [B][Hd] */
+  float *dctx_att, *dctx_dec;           /* [B][D] */
+  float *dwprev, *dcum;                 /* [B][ldT] */
+  unsigned int *barrier;
+  /* outputs */
+  float *dga_all, *dgd_all;  /* [T][B][4Ha], [T][B][4Hd] pre-activation gate gradients */
+  float *dq_all;             /* [T][B][A] */
+  float *dpre_all;           /* [T][B][P] gradient w.r.t. the prenet outputs */
+  float *dctx_all;           /* [B][T][D] total context gradient per frame */
+  float *dpm;                /* [B][Tin][A] gradient w.r.t. processed_memory (accumulated over frames) */
+  float *dv_part, *dwd_part, *dwc_part; /* per-CTA partial sums: [grid][A], [grid][A*F], [grid][F*2*KS] */
+  int grid;                  /* filled in by gtn_decoder_bwd_grid() so the caller can size the partials */
+} gtn_decoder_bwd_params;
+
+int gtn_decoder_bwd_grid(void);   /* number of CTAs gtn_decoder_backward launches on the current device */
+int gtn_decoder_backward(const gtn_decoder_bwd_params* params, void* stream);
 
 #ifdef __cplusplus
 }

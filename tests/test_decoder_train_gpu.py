@@ -1,0 +1,113 @@
+"""Teacher-forced decoder: persistent forward + BPTT kernels + deferred tcgen05 weight-gradient GEMMs vs the
+CPU oracle (values AND every parameter / memory gradient), identical Philox dropout masks.
+
+fp32 mode (3 bf16 planes): <= 1e-3 relative (north star).  bf16 mode: stated looser bounds below."""
+import pytest
+import torch
+
+from conftest import assert_close
+
+pytestmark = pytest.mark.gpu
+
+
+def _build(B, T_in, T, prec_name, ragged=True, seed=0, train=True, extra=""):
+    from gantron_b200.hparams import HParams
+    from gantron_b200.model import Decoder
+    torch.manual_seed(seed)
+    hp = HParams(f"use_noise=True,use_labels=False,b200_precision={prec_name}" + extra)
+    dec = Decoder(hp).cuda()
+    dec.train(train)
+    g = torch.Generator().manual_seed(seed + 1)
+    enc = torch.randn(B, T_in, hp.encoder_embedding_dim, generator=g) * 0.5
+    tail = dec.decoder_in_dim - hp.encoder_embedding_dim
+    noise = torch.rand(B, 1, tail, generator=g).repeat_interleave(T_in, dim=1)
+    memory = torch.cat((enc, noise), -1)
+    mels = (torch.randn(B, hp.n_mel_channels, T, generator=g) * 2 - 5).clamp(-11.5, 2.0)
+    in_len = torch.tensor([max(T_in - i, 2) for i in range(B)]) if ragged else torch.full((B,), T_in)
+    R = [torch.randn(B, hp.n_mel_channels, T, generator=g), torch.randn(B, T, generator=g),
+         torch.randn(B, T, T_in, generator=g)]
+    return hp, dec, memory, mels, in_len.long(), R
+
+
+def _oracle(hp, dec, memory, mels, in_len, R, seed, train=True):
+    from oracle import gantron_oracle as O, philox as PX
+    d = O.Dims.from_hparams(hp)
+    d.spk = 0; d.emo = 0
+    d.noise = dec.decoder_in_dim - hp.encoder_embedding_dim
+    B, _, T = mels.shape
+    sd = {"decoder." + k: v.detach().float().cpu().clone().requires_grad_(True) for k, v in dec.state_dict().items()}
+    mem = memory.clone().requires_grad_(True)
+    m = lambda site, step, shape, p: torch.from_numpy(PX.keep_mask(seed, site, step, shape, p))
+    pre1 = m(PX.SITE_PRENET1, 0, (T + 1, B, hp.prenet_dim), 0.5)
+    pre2 = m(PX.SITE_PRENET2, 0, (T + 1, B, hp.prenet_dim), 0.5)
+    att = dec_m = None
+    if train:
+        att = torch.stack([m(PX.SITE_ATT_H, t, (B, hp.attention_rnn_dim), hp.p_attention_dropout) for t in range(T)])
+        dec_m = torch.stack([m(PX.SITE_DEC_H, t, (B, hp.decoder_rnn_dim), hp.p_decoder_dropout) for t in range(T)])
+    mel, gate, align = O.decoder_teacher_forced(sd, mem, mels, in_len, d, pre1, pre2, att, dec_m)
+    loss = (mel * R[0]).sum() + (gate * R[1]).sum() + (align * R[2]).sum()
+    loss.backward()
+    return mel.detach(), gate.detach(), align.detach(), sd, mem.grad
+
+
+def _run_ours(dec, memory, mels, in_len, R, seed):
+    from gantron_b200 import decoder_ops
+    mem = memory.cuda().requires_grad_(True)
+    dec.zero_grad()
+    mel, gate, align = decoder_ops.decoder_train_forward(dec, mem, mels.cuda(), in_len.cuda(), seed)
+    loss = (mel * R[0].cuda()).sum() + (gate * R[1].cuda()).sum() + (align * R[2].cuda()).sum()
+    loss.backward()
+    return mel.detach(), gate.detach(), align.detach(), mem.grad
+
+
+def _check_grads(dec, sd, mem_grad, o_mem_grad, rel, l2=False):
+    worst = []
+    for k, p in dec.named_parameters():
+        ref = sd["decoder." + k].grad
+        assert p.grad is not None, f"no grad for {k}"
+        if l2:   # relative Frobenius error (bf16 mode: a few relu decisions near 0 flip, max-abs is the wrong metric)
+            err = float((p.grad.detach().cpu() - ref).norm()) / (float(ref.norm()) + 1e-12)
+        else:
+            scale = float(ref.abs().max()) + 1e-12
+            err = float((p.grad.detach().cpu() - ref).abs().max()) / scale
+        worst.append((err, k))
+    worst.sort(reverse=True)
+    msg = "; ".join(f"{k}: {e:.2e}" for e, k in worst[:8])
+    assert worst[0][0] <= rel, "parameter gradient mismatch (max-abs err / max-abs ref): " + msg
+    scale = float(o_mem_grad.abs().max()) + 1e-12
+    e = float((mem_grad.cpu() - o_mem_grad).abs().max()) / scale
+    assert e <= rel, f"d(memory) mismatch {e:.3e}; params ok: {msg}"
+
+
+@pytest.mark.parametrize("B,T_in,T", [(3, 17, 7), (9, 24, 4), (20, 33, 3), (40, 21, 3)])
+def test_train_fp32_mode_values_and_grads(B, T_in, T):
+    seed = 0x5EED0000 + B
+    hp, dec, memory, mels, in_len, R = _build(B, T_in, T, "fp32")
+    mel, gate, align, g_mem = _run_ours(dec, memory, mels, in_len, R, seed)
+    om, og, oa, sd, o_gmem = _oracle(hp, dec, memory, mels, in_len, R, seed)
+    assert_close(align, oa, "alignments", atol=2e-5, rtol=1e-3)
+    assert_close(mel, om, "mel", atol=3e-4, rtol=1e-3)
+    assert_close(gate, og, "gate", atol=3e-4, rtol=1e-3)
+    _check_grads(dec, sd, g_mem, o_gmem, rel=1e-3)
+
+
+def test_train_eval_mode_no_recurrent_dropout():
+    """model.eval(): prenet dropout stays on, attention/decoder dropout off (model.py:104 vs 393,408)."""
+    seed = 99
+    hp, dec, memory, mels, in_len, R = _build(2, 15, 5, "fp32", train=False)
+    mel, gate, align, g_mem = _run_ours(dec, memory, mels, in_len, R, seed)
+    om, og, oa, sd, o_gmem = _oracle(hp, dec, memory, mels, in_len, R, seed, train=False)
+    assert_close(mel, om, "mel eval", atol=3e-4, rtol=1e-3)
+    _check_grads(dec, sd, g_mem, o_gmem, rel=1e-3)
+
+
+def test_train_bf16_mode_tolerance():
+    """bf16 operands / fp32 accumulate.  Stated tolerance: mel 5e-2 abs (|mel| ~ 1), alignments 2e-2 abs,
+    gradients 5e-2 relative Frobenius error per tensor (fp32 oracle as the reference)."""
+    seed = 4321
+    hp, dec, memory, mels, in_len, R = _build(6, 29, 6, "bf16")
+    mel, gate, align, g_mem = _run_ours(dec, memory, mels, in_len, R, seed)
+    om, og, oa, sd, o_gmem = _oracle(hp, dec, memory, mels, in_len, R, seed)
+    assert_close(align, oa, "alignments bf16", atol=2e-2, rtol=0)
+    assert_close(mel, om, "mel bf16", atol=5e-2, rtol=5e-2)
+    _check_grads(dec, sd, g_mem, o_gmem, rel=5e-2, l2=True)
