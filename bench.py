@@ -1,0 +1,411 @@
+#!/usr/bin/env python
+"""bench.py -- GANtron hot-path benchmark (contract: see the task statement / DESIGN.md section "Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Headline metric (BASELINE.json): training mel frames/s of the vanilla GANtron (use_labels=False, use_noise=True)
+teacher-forced training step WITH the Discriminator, per-GPU batch 64, synthetic LJSpeech-shaped batch
+(T_in = 150 characters, T_out = 800 frames, 80 mels), bf16 operands / fp32 accumulate.
+
+One "step" = one generator iteration (Tacotron2.forward -> Tacotron2Loss incl. guided attention ->
+Discriminator.adversarial_loss -> backward -> clip_grad_norm_ -> Adam), i.e. train.py:362-406, followed by one
+discriminator iteration on the same batch (real + fake adversarial losses -> backward -> Adam), train.py:301-345.
+Frames counted per step = sum(output_lengths) of the generator iteration only.
+
+  value : frames/s with the parsed batch already resident in HBM (CUDA events, max over ranks)
+  e2e   : the same through the public API from pinned HOST buffers: model.parse_batch (H2D) ... loss.item() (D2H)
+  infer : autoregressive Decoder.inference frames/s at batch 1 and 256 (1000 forced steps), single GPU
+  roofline / cpu_baseline / clocks : see DESIGN.md
+
+`--impl reference` times the CPU restatement of the reference path (oracle/, "port") on the box's host cores
+on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+B_PER_GPU, T_IN, T_OUT, N_MEL = 64, 150, 800, 80
+MFLOP_PER_FRAME_TRAIN = 169.6        # algorithmic FLOP per mel frame of the G step (decoder+postnet x3, D x2)
+DEC_STEP_MAC = 23_487_872            # forward MACs of one decoder step per sample
+INFER_BYTES_PER_FRAME = 44.85e6      # bf16 decoder weights touched per frame at batch 1
+
+
+def _peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return dict(hbm=float(p["hbm_gbs"]), tf_burst=float(p["bf16_tflops"]), tf_sust=float(p["bf16_tflops_sustained"]),
+                    src="measured")
+    except Exception:
+        return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.samples, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            parts = [x.strip() for x in s.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0])); mx = float(parts[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the oracle port on host cores (bounded sample)
+# ------------------------------------------------------------------------------------------------------
+def cpu_port_step(B: int, T_in: int, T_out: int, threads: int, seed: int = 1234):
+    """One CPU pass of the reference algorithm (oracle port): G forward from the encoder outputs on + losses +
+    frozen-D adversarial loss + backward.  Returns (seconds, frames)."""
+    from oracle import gantron_oracle as O
+    from gantron_b200.hparams import HParams
+    from gantron_b200 import model as M
+    torch.set_num_threads(threads)
+    torch.manual_seed(seed)
+    hp = HParams("use_noise=True,use_labels=False")
+    G = M.Tacotron2(hp)
+    Dm = M.Discriminator(hp)
+    d = O.Dims.from_hparams(hp)
+    sd = {k: v.detach().clone().requires_grad_(v.dtype.is_floating_point) for k, v in G.state_dict().items()}
+    sdd = {k: v.detach().clone() for k, v in Dm.state_dict().items()}
+    batch = O.synthetic_batch(B, T_in, T_out, seed=seed)
+    text, in_len, mel, gate, spk, emo, out_len = batch
+    g = torch.Generator().manual_seed(seed)
+    memory = torch.cat((torch.randn(B, T_in, 512, generator=g) * 0.5,
+                        torch.rand(B, 1, d.noise, generator=g).repeat_interleave(T_in, 1)), -1).requires_grad_(True)
+    keep = lambda *s: (torch.rand(*s, generator=g) > 0.5).float()
+    masks = dict(pre1=keep(T_out + 1, B, d.prenet), pre2=keep(T_out + 1, B, d.prenet),
+                 att=(torch.rand(T_out, B, d.att_rnn, generator=g) > d.p_att).float(),
+                 dec=(torch.rand(T_out, B, d.dec_rnn, generator=g) > d.p_dec).float(),
+                 post=[keep(B, c, T_out) for c in (512, 512, 512, 512, 80)])
+    P = (T_out + 19) // 20
+    dk = [keep(B, c[1], P) for c in O.disc_layer_dims(d)[:4]]
+    t0 = time.perf_counter()
+    mo, mpo, go, al = O.generator_from_memory(sd, memory, mel, in_len, out_len, d, masks, training=True)
+    ml, gl = O.tacotron2_losses(mo, mpo, go, mel, gate)
+    adv = O.adversarial_loss(sdd, mpo, out_len, d, dk)
+    (ml + gl + adv + 10 * O.attention_loss(al, in_len, out_len)).backward()
+    dt = time.perf_counter() - t0
+    return dt, int(out_len.sum())
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    Bs, Ts = 8, 100
+    for _ in range(max(args.warmup, 0) and 1):
+        cpu_port_step(Bs, T_IN, Ts, cores)
+    times, frames = [], 0
+    for _ in range(max(1, args.steps)):
+        dt, frames = cpu_port_step(Bs, T_IN, Ts, cores)
+        times.append(dt)
+    tot = sum(times)
+    val = frames * len(times) / tot
+    sample = f"B={Bs}, T_in={T_IN}, T_out={Ts} slice of the B={B_PER_GPU}, T_out={T_OUT} workload; G fwd+bwd from encoder outputs incl. losses and frozen-D adversarial loss"
+    line = {"impl": "reference", "metric": "train_mel_frames_per_s", "value": val, "unit": "frames/s", "n_gpus": args.gpus,
+            "steps": len(times), "warmup": 1 if args.warmup else 0, "ms_per_step": 1e3 * tot / len(times),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": _config(args.gpus),
+            "cpu_baseline": {"value": val, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def _config(n_gpus: int):
+    return {"workload": "configs[1]: vanilla GANtron (use_labels=False,use_noise=True) teacher-forced training step with "
+                        "Discriminator, per-GPU batch 64, T_in=150, T_out=800, 80 mels, bf16",
+            "per_gpu_batch": B_PER_GPU, "global_batch": B_PER_GPU * n_gpus, "t_in": T_IN, "t_out": T_OUT,
+            "parallelism": f"dp{n_gpus}", "l2": "per-step working set (saved activations ~4 GB) far exceeds the 126 MB L2",
+            "step": "1 generator iteration (train.py:362-406) + 1 discriminator iteration (train.py:301-345)"}
+
+
+# ------------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------------
+class Trainer:
+    """The body of train.py's loop (train.py:291-423) against gantron_b200's drop-in model surface."""
+
+    def __init__(self, distributed: bool, seed: int = 1234):
+        from gantron_b200.hparams import HParams
+        from gantron_b200 import model as M
+        from gantron_b200.loss_function import Tacotron2Loss
+        torch.manual_seed(seed)
+        self.hp = HParams("use_noise=True,use_labels=False,b200_precision=bf16")
+        self.G = M.Tacotron2(self.hp).cuda()
+        self.D = M.Discriminator(self.hp).cuda()
+        if distributed:
+            from gantron_b200.distributed import apply_gradient_allreduce
+            self.G = apply_gradient_allreduce(self.G)
+            self.D = apply_gradient_allreduce(self.D)
+        self.g_opt = torch.optim.Adam(self.G.parameters(), lr=self.hp.g_learning_rate, weight_decay=self.hp.weight_decay)
+        self.d_opt = torch.optim.Adam(self.D.parameters(), lr=self.hp.d_learning_rate, weight_decay=self.hp.weight_decay)
+        self.criterion = Tacotron2Loss()
+        self.G.train(); self.D.train()
+        self.real, self.fake = 1.0, -1.0
+
+    def step(self, x, y):
+        hp, G, D = self.hp, self.G, self.D
+        # ---- generator iteration (train.py:362-406)
+        for p in D.parameters():
+            p.requires_grad = False
+        G.zero_grad()
+        y_pred = G(x)
+        generated_mel, lengths = y_pred[1], x[-1]
+        mel_loss, gate_loss, attn_loss = self.criterion(y_pred, y, x[1], x[-1])
+        adv = self.real * D.adversarial_loss(generated_mel, lengths)
+        total = mel_loss + gate_loss + adv + 10 * attn_loss
+        total.backward()
+        torch.nn.utils.clip_grad_norm_(G.parameters(), hp.grad_clip_thresh)
+        self.g_opt.step()
+        # ---- discriminator iteration (train.py:301-345)
+        for p in D.parameters():
+            p.requires_grad = True
+        D.zero_grad()
+        real_loss = self.real * D.adversarial_loss(y[0], lengths)
+        fake_loss = self.fake * D.adversarial_loss(generated_mel.detach(), lengths)
+        d_loss = (real_loss + fake_loss) / 2
+        torch.nn.utils.clip_grad_norm_(D.parameters(), hp.clipping_value)     # before backward, as train.py:326-327
+        d_loss.backward()
+        self.d_opt.step()
+        return total.detach()
+
+
+def _pinned_batch(B, seed):
+    from gantron_b200.synth import synthetic_batch
+    return tuple(t.pin_memory() for t in synthetic_batch(B, T_IN, T_OUT, seed=seed))
+
+
+def bench_inference(steps_frames: int = 1000):
+    from gantron_b200.hparams import HParams
+    from gantron_b200.model import Decoder
+    from gantron_b200 import decoder_ops, _lib
+    torch.manual_seed(0)
+    hp = HParams("use_noise=True,use_labels=False,b200_precision=bf16,max_decoder_steps=1000")
+    dec = Decoder(hp).cuda().eval()
+    out = {}
+    for Bi in (1, 256):
+        mem = torch.cat((torch.randn(Bi, T_IN, 512).cuda() * 0.5, torch.rand(Bi, 1, 512).repeat_interleave(T_IN, 1).cuda()), -1)
+        best = None
+        for it in range(3):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record()
+            r = decoder_ops.decoder_inference(dec.packed(), mem, max_steps=steps_frames, gate_threshold=0.5, seed=7 + it,
+                                              prec=1, const_tail=True, ignore_stop=True)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1)
+            if it > 0:
+                best = ms if best is None else min(best, ms)
+        us = 1e3 * best / steps_frames
+        out[f"b{Bi}"] = {"frames_per_s": Bi * steps_frames / (best * 1e-3), "us_per_frame_step": us, "frames": steps_frames}
+    return out
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    from gantron_b200 import _lib
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py (impl ours) needs a CUDA device: gantron_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    distributed = world > 1
+    if distributed:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    _lib.load()
+    tr = Trainer(distributed)
+    batch = _pinned_batch(B_PER_GPU, seed=1234 + rank)
+    frames = int(batch[-1].sum())
+    h2d = sum(t.numel() * t.element_size() for t in batch)
+
+    def barrier():
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(k, e2e):
+        x = y = None
+        if not e2e:
+            x, y = tr.G.parse_batch(batch)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        last = None
+        for _ in range(k):
+            if e2e:
+                x, y = tr.G.parse_batch(batch)
+            loss = tr.step(x, y)
+            if e2e:
+                last = loss.item()
+        e1.record()
+        barrier()
+        wall = time.perf_counter() - t0
+        ms = e0.elapsed_time(e1)
+        if e2e:
+            ms = max(ms, wall * 1e3)        # e2e includes host work: take the larger of device span and wall clock
+        t = torch.tensor([ms], device="cuda")
+        if distributed:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), last
+
+    # warm-up (>= 3): also builds the weight packs / allocator pools
+    timed(max(args.warmup, 3), False)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    _lib.reset_launch_count()
+    ms_total, _ = timed(args.steps, False)
+    launches = _lib.launch_count()
+    clocks = sampler.stop() if rank == 0 else None
+    ms_e2e, last_loss = timed(args.steps, True)
+
+    value = frames * world * args.steps / (ms_total * 1e-3)
+    e2e_val = frames * world * args.steps / (ms_e2e * 1e-3)
+    line = None
+    if rank == 0:
+        pk = _peaks()
+        # dominant kernel: the persistent decoder forward/backward pair; measured live below
+        roof = kernel_roofline(tr, batch, pk)
+        line = {"metric": "train_mel_frames_per_s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": _config(world),
+                "e2e": {"value": e2e_val, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+                        "ms_per_step": ms_e2e / args.steps, "last_loss": last_loss},
+                "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
+                "step_roofline": {"bound": "tensor", "achieved": MFLOP_PER_FRAME_TRAIN * 1e6 * (value / world) / 1e12,
+                                  "peak": pk["tf_sust"], "unit": "TFLOP/s",
+                                  "frac": MFLOP_PER_FRAME_TRAIN * 1e6 * (value / world) / 1e12 / pk["tf_sust"],
+                                  "peak_source": pk["src"], "note": "whole G+D step, algorithmic 169.6 MFLOP/frame"}}
+    if world == 1 and rank == 0:
+        del tr
+        torch.cuda.empty_cache()
+        if not args.no_infer:
+            line["infer"] = bench_inference()
+            b1 = line["infer"]["b1"]
+            b1["roofline"] = {"bound": "hbm", "achieved": INFER_BYTES_PER_FRAME / (b1["us_per_frame_step"] * 1e-6) / 1e9,
+                              "peak": pk["hbm"], "unit": "GB/s",
+                              "frac": INFER_BYTES_PER_FRAME / (b1["us_per_frame_step"] * 1e-6) / 1e9 / pk["hbm"]}
+        if not args.no_cpu:
+            cores = os.cpu_count() or 1
+            dt, fr = cpu_port_step(4, T_IN, 100, cores)
+            line["cpu_baseline"] = {"value": fr / dt, "unit": "frames/s", "cores": cores, "kind": "port",
+                                    "sample": "B=4, T_in=150, T_out=100 slice of the workload, oracle port (torch CPU fp32), "
+                                              "G fwd+bwd from encoder outputs incl. losses and frozen-D adversarial loss, 1 pass"}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if distributed:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def kernel_roofline(tr, batch, pk):
+    """Live CUDA-event timing of the dominant kernels (the persistent decoder forward + BPTT launches) on the
+    stream they are launched on; algorithmic FLOPs = 3 x 2 x 23.49 M MAC per sample-frame (fwd + dgrad in the two
+    persistent kernels, wgrad in the deferred GEMMs is timed separately inside the step)."""
+    from gantron_b200 import decoder_ops
+    G = tr.G
+    x, y = G.parse_batch(batch)
+    text, text_lengths, mels, max_len, spk, emo, out_len = x
+    with torch.no_grad():
+        enc = G.encoder(G.embedding(text).transpose(1, 2), text_lengths)
+    dec = G.decoder
+    memory = dec.append_noise(enc).detach().requires_grad_(True)
+    res = {}
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    best_f = best_b = None
+    for it in range(3):
+        G.zero_grad()
+        torch.cuda.synchronize()
+        evs[0].record()
+        mel, gate, align = decoder_ops.decoder_train_forward(dec, memory, mels, text_lengths, 99 + it)
+        evs[1].record()
+        (mel.sum() + gate.sum()).backward()
+        evs[2].record()
+        torch.cuda.synchronize()
+        f, b = evs[0].elapsed_time(evs[1]), evs[1].elapsed_time(evs[2])
+        best_f = f if best_f is None else min(best_f, f)
+        best_b = b if best_b is None else min(best_b, b)
+    frames = mels.shape[0] * mels.shape[2]
+    flops = 3 * 2 * DEC_STEP_MAC * frames
+    ach = flops / ((best_f + best_b) * 1e-3) / 1e12
+    return {"bound": "tensor", "kernel": "decoder_fwd_kernel + decoder_bwd_kernel + deferred wgrad GEMMs (decoder fwd+bwd)",
+            "achieved": ach, "peak": pk["tf_sust"], "unit": "TFLOP/s", "frac": ach / pk["tf_sust"], "traffic": None,
+            "peak_source": pk["src"], "fwd_ms": best_f, "bwd_ms": best_b,
+            "note": "recurrent part is latency / weight-streaming bound (M = batch 64 per step), see DESIGN.md"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-infer", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+        return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus and world == 1 and args.gpus > 1:
+        # convenience: relaunch under torchrun
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29517"), __file__,
+               "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup)]
+        sys.exit(subprocess.call(cmd))
+    run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -39,11 +39,25 @@ SIGNATURES = {
                               c_p, c_i, c_i, c_ll, c_ll,
                               c_p, c_i, c_ll, c_ll,
                               c_p, c_i, c_ll, c_ll,
-                              c_p, c_i, c_p, c_i, c_p]),
+                              c_p, c_i, c_f, c_ull, c_i, c_i, c_p, c_i, c_p]),
     "gtn_conv1d_wgrad_bf16": (c_i, [c_p, c_p, c_i, c_i, c_i, c_i, c_ll, c_ll, c_ll, c_ll,
                                     c_i, c_i, c_i, c_p, c_ll, c_i, c_i, c_p]),
     "gtn_gemm_tn_bf16": (c_i, [c_p, c_p, c_i, c_i, c_i, c_ll, c_ll, c_i, c_ll, c_ll,
                                c_p, c_i, c_ll, c_ll, c_i, c_p, c_p, c_i, c_i, c_p]),
+    "gtn_bn_finalize": (c_i, [c_p, c_i, c_ll, c_f, c_f, c_p, c_p, c_p, c_p, c_p]),
+    "gtn_bn_act_fwd": (c_i, [c_p, c_i, c_ll, c_ll, c_i, c_p, c_p, c_p, c_p, c_i, c_f, c_ull, c_i, c_p, c_i, c_ll, c_p]),
+    "gtn_bn_act_bwd": (c_i, [c_p, c_i, c_ll, c_p, c_i, c_ll, c_ll, c_i, c_p, c_p, c_p, c_p, c_i, c_f, c_ull, c_i,
+                             c_p, c_p, c_p, c_i, c_ll, c_p, c_p]),
+    "gtn_drop_tanh_bwd": (c_i, [c_p, c_i, c_ll, c_p, c_i, c_ll, c_ll, c_i, c_f, c_ull, c_i, c_p, c_i, c_ll, c_p, c_p]),
+    "gtn_disc_head_fwd": (c_i, [c_p, c_i, c_ll, c_ll, c_i, c_p, c_p, c_p, c_p]),
+    "gtn_disc_head_bwd": (c_i, [c_p, c_p, c_i, c_ll, c_ll, c_i, c_p, c_p, c_i, c_ll, c_p, c_p, c_p]),
+    "gtn_window_mean_fwd": (c_i, [c_p, c_i, c_i, c_p, c_i, c_p, c_p]),
+    "gtn_window_mean_bwd": (c_i, [c_p, c_i, c_i, c_p, c_i, c_p, c_p]),
+    "gtn_taco_loss_fwd": (c_i, [c_p, c_p, c_p, C.POINTER(c_ll), c_i, c_i, c_i, c_p, c_ll, c_p, c_ll, c_p, c_p]),
+    "gtn_taco_loss_bwd": (c_i, [c_p, c_p, c_p, C.POINTER(c_ll), c_i, c_i, c_i, c_p, c_ll, c_p, c_ll, c_p, c_p,
+                                c_p, c_p, c_p, c_p]),
+    "gtn_attn_guide_loss_fwd": (c_i, [c_p, c_i, c_i, c_i, c_p, c_p, c_f, c_p, c_p]),
+    "gtn_attn_guide_loss_bwd": (c_i, [c_p, c_i, c_i, c_i, c_p, c_p, c_f, c_p, c_p, c_p]),
     "gtn_decoder_forward": (c_i, [c_p, c_p]),
     "gtn_sizeof": (c_i, [c_i]),
     "gtn_decoder_bwd_grid": (c_i, []),

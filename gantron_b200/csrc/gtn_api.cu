@@ -71,7 +71,8 @@ int gtn_conv1d_bf16(const void* Wp, int Cout, int Cin, int cin_pad, int taps, in
                     const void* X, int nbatch, int T, long long ldx, long long strideXb,
                     void* C, int c_dtype, long long ldc, long long strideCb,
                     void* C2, int c2_dtype, long long ldc2, long long strideC2b,
-                    const float* bias_m, int act, float* stats, int block_n, void* stream) {
+                    const float* bias_m, int act, float drop_p, unsigned long long seed, int site, int drop_first,
+                    float* stats, int block_n, void* stream) {
   GTN_REQUIRE(cin_pad % 64 == 0 && cin_pad >= Cin, "cin_pad must be Cin rounded up to a multiple of 64");
   GemmDesc g;
   g.mode = MODE_CONV; g.M = Cout; g.N = T; g.batch = nbatch; g.block_n = block_n > 0 ? block_n : 128;
@@ -82,6 +83,7 @@ int gtn_conv1d_bf16(const void* Wp, int Cout, int Cin, int cin_pad, int taps, in
   g.C = C; g.ldc = ldc; g.strideC = strideCb; g.c_bf16 = c_dtype; g.c_trans = 1;
   g.C2 = C2; g.ldc2 = ldc2; g.strideC2 = strideC2b; g.c2_bf16 = c2_dtype; g.c2_trans = 0;
   g.bias_m = bias_m; g.act = act; g.stats = stats;
+  g.drop_p = drop_p; g.seed = seed; g.site = (unsigned)site; g.step = 0; g.drop_first = drop_first;
   return gemm_launch(g, (cudaStream_t)stream);
 }
 

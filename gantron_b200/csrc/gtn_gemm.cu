@@ -43,6 +43,7 @@ struct GemmKernelParams {
   void* C2; long long ldc2, strideC2; int c2_bf16, c2_trans;
   const float* bias_m; const float* bias_n;
   int act;            // 0 none, 1 relu, 2 tanh
+  int drop_first;     // 1: dropout is applied BEFORE the activation (DiscConv1d: conv -> dropout -> tanh)
   int accumulate;     // C += D (fp32 C only)
   unsigned int drop_thr; float drop_scale; unsigned long long seed; unsigned int site, step;
   float* stats;       // [2][M] per-row sum / sum of squares over valid n (all z), or nullptr
@@ -190,8 +191,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (p.bias_n != nullptr && n < p.N) x += p.bias_n[n];
         if (p.accumulate && m_ok && n < p.N)
           x += p.c_trans ? Cf[zc + (long long)n * p.ldc + m] : Cf[zc + (long long)m * p.ldc + n];
-        if (p.act == 1) x = fmaxf(x, 0.0f);
-        else if (p.act == 2) x = tanhf(x);
+        if (!p.drop_first) {
+          if (p.act == 1) x = fmaxf(x, 0.0f);
+          else if (p.act == 2) x = tanhf(x);
+        }
         v[j] = x;
       }
       if (p.drop_thr != 0u && m_ok) {
@@ -204,6 +207,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const uint32_t bits = philox_bits(p.seed, p.site, p.step, (uint32_t)(e + (unsigned long long)z * p.M * p.N));
             v[j] = bits >= p.drop_thr ? v[j] * p.drop_scale : 0.0f;
           }
+        }
+      }
+      if (p.drop_first) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          if (p.act == 1) v[j] = fmaxf(v[j], 0.0f);
+          else if (p.act == 2) v[j] = tanhf(v[j]);
         }
       }
       if (p.stats != nullptr) {
@@ -352,7 +362,7 @@ int gemm_launch(const GemmDesc& g, cudaStream_t st) {
   kp.t_blocks = g.t_blocks; kp.taps_dil = g.dil; kp.taps_pad = g.pad;
   kp.C = g.C; kp.ldc = g.ldc; kp.strideC = g.strideC; kp.c_bf16 = g.c_bf16; kp.c_trans = g.c_trans;
   kp.C2 = g.C2; kp.ldc2 = g.ldc2; kp.strideC2 = g.strideC2; kp.c2_bf16 = g.c2_bf16; kp.c2_trans = g.c2_trans;
-  kp.bias_m = g.bias_m; kp.bias_n = g.bias_n; kp.act = g.act; kp.accumulate = g.accumulate;
+  kp.bias_m = g.bias_m; kp.bias_n = g.bias_n; kp.act = g.act; kp.drop_first = g.drop_first; kp.accumulate = g.accumulate;
   if (g.drop_p > 0.f) {
     double t = (double)g.drop_p * 4294967296.0;
     kp.drop_thr = t >= 4294967295.0 ? 0xFFFFFFFFu : (unsigned int)t;

@@ -19,7 +19,7 @@ struct GemmDesc {
   void* C = nullptr;  long long ldc = 0, strideC = 0;  int c_bf16 = 0, c_trans = 0;
   void* C2 = nullptr; long long ldc2 = 0, strideC2 = 0; int c2_bf16 = 0, c2_trans = 0;
   const float* bias_m = nullptr; const float* bias_n = nullptr;
-  int act = 0, accumulate = 0;
+  int act = 0, accumulate = 0, drop_first = 0;
   float drop_p = 0.f; unsigned long long seed = 0; unsigned int site = 0, step = 0;
   float* stats = nullptr;
 };

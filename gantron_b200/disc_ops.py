@@ -1,0 +1,153 @@
+"""Discriminator.forward / adversarial_loss (reference model.py:500-540, layers.py:43-60) on the sm_100a kernels.
+
+Forward: the reference's raw reshape (B,F',80) -> (B,1600,P) is kept as a zero-copy view; one transposing cast
+makes the channels-last bf16 operand (B,P,1600); four implicit-GEMM convs (tcgen05) with bias -> Philox
+dropout -> tanh fused in the epilogue (DiscConv1d order, layers.py:53-57); a warp-per-row head for the final
+Conv1d(80 -> 1, k=1); one masked-mean kernel for the loss (no per-sample host syncs, cf. model.py:533-537).
+Backward: gtn_drop_tanh_bwd + data-gradient convs (+ weight-gradient GEMMs when D's parameters require grad,
+i.e. in the discriminator step; they are frozen during the generator step, train.py:366-367).
+
+Dropout sites: oracle/philox.py SITE_DISC0 + layer; element numbering (b*P + p)*C + c.
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+from torch.autograd.function import once_differentiable
+
+from . import _lib, ops
+from .conv_ops import PackCache, act_operand, pack_conv_weight, wgrad_operands
+from .packing import BF16
+
+SITE_DISC0 = 32
+
+
+def _cache(mod) -> PackCache:
+    c = getattr(mod, "_gtn_pack_cache", None)
+    if c is None:
+        c = PackCache()
+        object.__setattr__(mod, "_gtn_pack_cache", c)
+    return c
+
+
+def _convs(disc):
+    seq = disc.discriminator
+    return [seq[i].module[0] for i in range(len(seq) - 1)], seq[len(seq) - 1]
+
+
+def _params(disc):
+    convs, head = _convs(disc)
+    out = []
+    for c in convs:
+        out += [c.weight, c.bias]
+    return out + [head.weight, head.bias]
+
+
+class _DiscFn(torch.autograd.Function):
+    """x (B, window*n_mel, P) [the raw-reshaped input] -> (B, P)."""
+
+    @staticmethod
+    def forward(ctx, disc, seed, prec, x, *params):
+        convs, head = _convs(disc)
+        B, C0, P = x.shape
+        dev = x.device
+        adt = BF16 if prec == 1 else torch.float32
+        cache = _cache(disc)
+        cur = x.detach().transpose(1, 2)
+        cur = cur.to(adt).contiguous() if prec == 1 else cur.float().contiguous()
+        saved = []
+        for i, conv in enumerate(convs):
+            w, b = params[2 * i], params[2 * i + 1]
+            k, dil, pad = conv.kernel_size[0], conv.dilation[0], conv.padding[0]
+            wp, cin_eff, cin_pad = cache.get(("fwd", i, prec), w, lambda w=w: pack_conv_weight(w, prec))
+            a = torch.empty(B, P, w.shape[0], device=dev, dtype=adt)
+            p_drop = disc.discriminator[i].module[1].p if disc.discriminator[i].module[1].training else 0.0
+            drop = (p_drop, seed, SITE_DISC0 + i)
+            ops.conv1d(wp, cin_eff, cin_pad, k, dil, pad, act_operand(cur, prec), a, None, bias=b.detach(),
+                       act=ops.ACT_TANH, dropout=drop, drop_first=True, block_n=64)
+            saved.append((cur, a, drop))
+            cur = a
+        hw, hb = params[-2], params[-1]
+        out = ops.disc_head_fwd(cur, hw.detach().reshape(-1).contiguous(), hb.detach())
+        ctx.disc, ctx.prec, ctx.saved, ctx.dims = disc, prec, saved, (B, C0, P)
+        return out
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        # NOTE: double backward (train.py:32-69 gradient_penalty, lambda = 0 by default) is not implemented: SURVEY 8 f2
+        disc, prec, saved = ctx.disc, ctx.prec, ctx.saved
+        convs, head = _convs(disc)
+        params = _params(disc)
+        B, C0, P = ctx.dims
+        dev = g.device
+        adt = BF16 if prec == 1 else torch.float32
+        cache = _cache(disc)
+        n = len(convs)
+        grads: List[Optional[torch.Tensor]] = [None] * len(params)
+        need_w = any(ctx.needs_input_grad[4:])
+        a_last = saved[-1][1]
+        dcur = torch.empty(B, P, a_last.shape[2], device=dev, dtype=torch.float32)
+        hw = params[-2]
+        dw, db = ops.disc_head_bwd(g.contiguous().float(), a_last, hw.detach().reshape(-1).contiguous(), dcur, need_w)
+        if need_w:
+            grads[-2], grads[-1] = dw.reshape(hw.shape), db
+        for i in reversed(range(n)):
+            conv = convs[i]
+            w = params[2 * i]
+            x_in, a, drop = saved[i]
+            k, dil, pad = conv.kernel_size[0], conv.dilation[0], conv.padding[0]
+            cout, cin = w.shape[0], w.shape[1]
+            dpre = torch.empty(B, P, cout, device=dev, dtype=adt)
+            dbias = ops.drop_tanh_bwd(dcur, a, drop, dpre, want_dbias=need_w)
+            if need_w:
+                dyo, xo = wgrad_operands(dpre, x_in, prec)
+                dwt = torch.empty(k, cout, cin, device=dev)
+                ops.conv1d_wgrad(dyo, xo, cin, k, dil, pad, dwt, block_n=128)
+                grads[2 * i], grads[2 * i + 1] = dwt.permute(1, 2, 0).contiguous(), dbias
+            if i > 0 or ctx.needs_input_grad[3]:
+                wT, ce, cp = cache.get(("dgrad", i, prec), w, lambda w=w: pack_conv_weight(w, prec, dgrad=True))
+                dcur = torch.empty(B, P, cin, device=dev, dtype=torch.float32)
+                ops.conv1d(wT, ce, cp, k, dil, dil * (k - 1) - pad, act_operand(dpre, prec), dcur, None, block_n=64)
+        ctx.saved = None
+        gx = dcur.transpose(1, 2) if ctx.needs_input_grad[3] else None
+        return (None, None, None, gx) + tuple(grads)
+
+
+def discriminator_forward(disc, inputs: torch.Tensor, seed: int, prec: int) -> torch.Tensor:
+    """inputs (B, frames, n_mel) -> (B, positions); tail handling and raw reshape as model.py:521-526."""
+    win = disc.window
+    r = inputs.shape[1] % win
+    if r != 0:
+        inputs = torch.cat((inputs[:, :-r], inputs[:, -win:]), dim=1)
+    x = inputs.reshape(inputs.shape[0], disc.in_dim, -1)          # raw memory reinterpretation (copy if strided)
+    return _DiscFn.apply(disc, seed, prec, x, *_params(disc))
+
+
+class _WindowMean(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, out, lengths, window):
+        out = out.contiguous().float()
+        B, P = out.shape
+        lengths = lengths.to(device=out.device, dtype=torch.int64).contiguous()
+        loss = torch.empty(1, device=out.device)
+        _lib.check(_lib.load().gtn_window_mean_fwd(_lib.ptr(out), B, P, _lib.ptr(lengths), int(window), _lib.ptr(loss),
+                                                   _lib.stream()), "gtn_window_mean_fwd")
+        ctx.lengths, ctx.window, ctx.dims = lengths, int(window), (B, P)
+        return loss.reshape(())
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        B, P = ctx.dims
+        dout = torch.empty(B, P, device=g.device)
+        gg = g.reshape(1).float().contiguous()
+        _lib.check(_lib.load().gtn_window_mean_bwd(_lib.ptr(gg), B, P, _lib.ptr(ctx.lengths), ctx.window, _lib.ptr(dout),
+                                                   _lib.stream()), "gtn_window_mean_bwd")
+        return dout, None, None
+
+
+def masked_window_mean(out: torch.Tensor, target_length: torch.Tensor, window: int) -> torch.Tensor:
+    """mean_b mean(out[b, :ceil(len_b / window)])  (model.py:531-540) as one kernel, lengths stay on the device."""
+    return _WindowMean.apply(out, target_length, window)

@@ -34,8 +34,12 @@ def _precision_of(hparams) -> int:
     return 1 if name == "bf16" else 3
 
 
-def _new_seed() -> int:
-    """Philox key for one pass, drawn from torch's CPU generator (so torch.manual_seed reproduces runs)."""
+def _new_seed(mod=None) -> int:
+    """Philox key for one pass, drawn from torch's CPU generator (so torch.manual_seed reproduces runs).
+    Tests pin it by setting `module._forced_seed`."""
+    forced = getattr(mod, "_forced_seed", None) if mod is not None else None
+    if forced is not None:
+        return int(forced)
     return int(torch.randint(0, 2 ** 62, (1,), dtype=torch.int64).item())
 
 
@@ -100,7 +104,7 @@ class Prenet(nn.Module):
     def forward(self, x):
         from . import decoder_ops
         _require_cuda(x, "Prenet")
-        return decoder_ops.prenet_forward(self, x, seed=_new_seed())
+        return decoder_ops.prenet_forward(self, x, seed=_new_seed(self))
 
 
 class Postnet(nn.Module):
@@ -123,7 +127,7 @@ class Postnet(nn.Module):
     def forward(self, x, wgrad_input=None):
         from . import postnet_ops
         _require_cuda(x, "Postnet")
-        return postnet_ops.postnet_forward(self, x, seed=_new_seed(), prec=self._prec, wgrad_input=wgrad_input)
+        return postnet_ops.postnet_forward(self, x, seed=_new_seed(self), prec=self._prec, wgrad_input=wgrad_input)
 
 
 class Encoder(nn.Module):
@@ -245,7 +249,7 @@ class Decoder(nn.Module):
         from . import decoder_ops
         _require_cuda(memory, "Decoder.forward")
         memory = self.append_noise(memory)
-        return decoder_ops.decoder_train_forward(self, memory, decoder_inputs, memory_lengths, seed=_new_seed())
+        return decoder_ops.decoder_train_forward(self, memory, decoder_inputs, memory_lengths, seed=_new_seed(self))
 
     def inference(self, memory, style):
         """Autoregressive pass (model.py:456-497) -> mel (B,n_mel,T'), gate (B,T',1), alignments (B,T',T_in).
@@ -260,7 +264,7 @@ class Decoder(nn.Module):
             memory = torch.cat([memory, style.to(memory.dtype)], dim=-1)
         mel, gate, align, lengths, steps = decoder_ops.decoder_inference(
             self.packed(), memory, max_steps=self.max_decoder_steps, gate_threshold=self.gate_threshold,
-            seed=_new_seed(), prec=self._prec, const_tail=const_tail)
+            seed=_new_seed(self), prec=self._prec, const_tail=const_tail)
         self.last_lengths = lengths
         if steps == self.max_decoder_steps and bool((lengths >= steps).any()) and not bool(
                 (torch.sigmoid(gate[:, -1, 0]) > self.gate_threshold).all()):
@@ -289,7 +293,7 @@ class Discriminator(nn.Module):
         """inputs (B, frames, n_mel) -> (B, positions)."""
         from . import disc_ops
         _require_cuda(inputs, "Discriminator.forward")
-        return disc_ops.discriminator_forward(self, inputs, seed=_new_seed(), prec=self._prec)
+        return disc_ops.discriminator_forward(self, inputs, seed=_new_seed(self), prec=self._prec)
 
     def adversarial_loss(self, inputs, target_length):
         """mean over the batch of the mean of the first ceil(len/window) outputs (model.py:529-540);

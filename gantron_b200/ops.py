@@ -91,8 +91,10 @@ def pack_conv_weight(w: torch.Tensor, transpose_for_dgrad: bool = False) -> Tupl
 
 def conv1d(wp: torch.Tensor, cin: int, cin_pad: int, taps: int, dil: int, pad: int, x_cl: torch.Tensor,
            out_cl: Optional[torch.Tensor], out_cf: Optional[torch.Tensor], bias: Optional[torch.Tensor] = None,
-           act: int = ACT_NONE, stats: Optional[torch.Tensor] = None, block_n: int = 128) -> None:
-    """Implicit-GEMM conv1d.  x_cl channels-last bf16 (B,T,>=cin) -> out_cl (B,T,Cout) and/or out_cf (B,Cout,T)."""
+           act: int = ACT_NONE, stats: Optional[torch.Tensor] = None, block_n: int = 128,
+           dropout: Optional[Tuple[float, int, int]] = None, drop_first: bool = False) -> None:
+    """Implicit-GEMM conv1d.  x_cl channels-last bf16 (B,T,>=cin) -> out_cl (B,T,Cout) and/or out_cf (B,Cout,T).
+    dropout = (p, seed, site), applied after the activation, or before it when drop_first."""
     assert x_cl.dtype == _BF16 and x_cl.dim() == 3 and x_cl.stride(2) == 1
     Bn, T, _ = x_cl.shape
     cout = wp.shape[0]
@@ -101,6 +103,7 @@ def conv1d(wp: torch.Tensor, cin: int, cin_pad: int, taps: int, dil: int, pad: i
         assert tuple(out_cl.shape[:2]) == (Bn, T) and out_cl.shape[2] >= cout and out_cl.stride(2) == 1
     if out_cf is not None:
         assert tuple(out_cf.shape[:2]) == (Bn, cout) and out_cf.shape[2] >= T and out_cf.stride(2) == 1
+    dp, dseed, dsite = dropout if dropout is not None else (0.0, 0, 0)
     lib = _lib.load()
     rc = lib.gtn_conv1d_bf16(
         _lib.ptr(wp), cout, cin, cin_pad, taps, dil, pad,
@@ -109,7 +112,8 @@ def conv1d(wp: torch.Tensor, cin: int, cin_pad: int, taps: int, dil: int, pad: i
         out_cl.stride(1) if out_cl is not None else 0, out_cl.stride(0) if out_cl is not None else 0,
         _lib.ptr(out_cf), _dt(out_cf) if out_cf is not None else 0,
         out_cf.stride(1) if out_cf is not None else 0, out_cf.stride(0) if out_cf is not None else 0,
-        _lib.ptr(bias), act, _lib.ptr(stats), block_n, _lib.stream())
+        _lib.ptr(bias), act, float(dp), int(dseed), int(dsite), int(drop_first),
+        _lib.ptr(stats), block_n, _lib.stream())
     _lib.check(rc, "gtn_conv1d_bf16")
 
 
@@ -154,3 +158,98 @@ def gemm_tn(A: torch.Tensor, B: torch.Tensor, out: torch.Tensor, *, trans_out: b
                               _lib.ptr(bias_m), _lib.ptr(bias_n), int(accumulate), block_n, _lib.stream())
     _lib.check(rc, "gtn_gemm_tn_bf16")
     return out
+
+
+# ==========================================================================================
+# elementwise / reduction kernels (gtn_eltwise.cu); activations channels-last (B,T,C) or (rows,C)
+# ==========================================================================================
+def _rows_c(t: torch.Tensor, name: str) -> Tuple[int, int, int]:
+    """(rows, C, ld) of a channels-last activation whose leading dims collapse to uniform rows."""
+    assert t.is_cuda and t.stride(-1) == 1 and t.dtype in (torch.float32, _BF16), f"{name}: bad tensor"
+    C = t.shape[-1]
+    ld = t.stride(-2)
+    rows = 1
+    for i in range(t.dim() - 1):
+        rows *= t.shape[i]
+    # leading dims must be collapsible: stride(i) == stride(i+1) * shape(i+1)
+    for i in range(t.dim() - 2):
+        assert t.stride(i) == t.stride(i + 1) * t.shape[i + 1], f"{name}: leading dims are not collapsible"
+    return rows, C, ld
+
+
+def bn_finalize(stats: torch.Tensor, count: int, eps: float, momentum: float,
+                running_mean: Optional[torch.Tensor], running_var: Optional[torch.Tensor]):
+    C = stats.shape[1]
+    mean = torch.empty(C, device=stats.device)
+    rstd = torch.empty(C, device=stats.device)
+    rc = _lib.load().gtn_bn_finalize(_lib.ptr(stats), C, int(count), float(eps), float(momentum), _lib.ptr(mean),
+                                     _lib.ptr(rstd), _lib.ptr(running_mean), _lib.ptr(running_var), _lib.stream())
+    _lib.check(rc, "gtn_bn_finalize")
+    return mean, rstd
+
+
+def bn_act_fwd(y: torch.Tensor, mean, rstd, gamma, beta, act: int, dropout: Tuple[float, int, int],
+               out: torch.Tensor) -> torch.Tensor:
+    rows, C, ldy = _rows_c(y, "y")
+    rows_o, C_o, ldo = _rows_c(out, "out")
+    assert rows == rows_o and C == C_o
+    p, seed, site = dropout
+    rc = _lib.load().gtn_bn_act_fwd(_lib.ptr(y), _dt(y), ldy, rows, C, _lib.ptr(mean), _lib.ptr(rstd), _lib.ptr(gamma),
+                                    _lib.ptr(beta), act, float(p), int(seed), int(site), _lib.ptr(out), _dt(out), ldo,
+                                    _lib.stream())
+    _lib.check(rc, "gtn_bn_act_fwd")
+    return out
+
+
+def bn_act_bwd(dx: torch.Tensor, y: torch.Tensor, mean, rstd, gamma, beta, act: int, dropout: Tuple[float, int, int],
+               dy: torch.Tensor, want_dbias: bool = True):
+    rows, C, lddx = _rows_c(dx, "dx")
+    r2, C2, ldy = _rows_c(y, "y")
+    r3, C3, lddy = _rows_c(dy, "dy")
+    assert rows == r2 == r3 and C == C2 == C3
+    dev = y.device
+    dgamma, dbeta = torch.empty(C, device=dev), torch.empty(C, device=dev)
+    dbias = torch.empty(C, device=dev) if want_dbias else None
+    p, seed, site = dropout
+    rc = _lib.load().gtn_bn_act_bwd(_lib.ptr(dx), _dt(dx), lddx, _lib.ptr(y), _dt(y), ldy, rows, C, _lib.ptr(mean),
+                                    _lib.ptr(rstd), _lib.ptr(gamma), _lib.ptr(beta), act, float(p), int(seed), int(site),
+                                    _lib.ptr(dgamma), _lib.ptr(dbeta), _lib.ptr(dy), _dt(dy), lddy, _lib.ptr(dbias),
+                                    _lib.stream())
+    _lib.check(rc, "gtn_bn_act_bwd")
+    return dgamma, dbeta, dbias
+
+
+def drop_tanh_bwd(dout: torch.Tensor, a: torch.Tensor, dropout: Tuple[float, int, int], dpre: torch.Tensor,
+                  want_dbias: bool = True):
+    rows, C, lddo = _rows_c(dout, "dout")
+    r2, C2, lda = _rows_c(a, "a")
+    r3, C3, lddp = _rows_c(dpre, "dpre")
+    assert rows == r2 == r3 and C == C2 == C3
+    dbias = torch.empty(C, device=a.device) if want_dbias else None
+    p, seed, site = dropout
+    rc = _lib.load().gtn_drop_tanh_bwd(_lib.ptr(dout), _dt(dout), lddo, _lib.ptr(a), _dt(a), lda, rows, C, float(p),
+                                       int(seed), int(site), _lib.ptr(dpre), _dt(dpre), lddp, _lib.ptr(dbias),
+                                       _lib.stream())
+    _lib.check(rc, "gtn_drop_tanh_bwd")
+    return dbias
+
+
+def disc_head_fwd(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor) -> torch.Tensor:
+    rows, C, ldx = _rows_c(x, "x")
+    out = torch.empty(x.shape[:-1], device=x.device)
+    rc = _lib.load().gtn_disc_head_fwd(_lib.ptr(x), _dt(x), ldx, rows, C, _lib.ptr(w), _lib.ptr(bias), _lib.ptr(out),
+                                       _lib.stream())
+    _lib.check(rc, "gtn_disc_head_fwd")
+    return out
+
+
+def disc_head_bwd(dout: torch.Tensor, x: torch.Tensor, w: torch.Tensor, dx: torch.Tensor, want_wgrad: bool):
+    rows, C, ldx = _rows_c(x, "x")
+    r2, C2, lddx = _rows_c(dx, "dx")
+    assert rows == r2 and C == C2 and dout.is_contiguous() and dout.numel() == rows
+    dw = torch.empty(C, device=x.device) if want_wgrad else None
+    db = torch.empty(1, device=x.device) if want_wgrad else None
+    rc = _lib.load().gtn_disc_head_bwd(_lib.ptr(dout), _lib.ptr(x), _dt(x), ldx, rows, C, _lib.ptr(w), _lib.ptr(dx),
+                                       _dt(dx), lddx, _lib.ptr(dw), _lib.ptr(db), _lib.stream())
+    _lib.check(rc, "gtn_disc_head_bwd")
+    return dw, db

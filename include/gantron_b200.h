@@ -48,12 +48,16 @@ int gtn_gemm_bf16(const void* A, const void* B, int M, int N, int K, long long l
  *   out[b][t][co] = bias[co] + sum_{tap,ci} Wp[co][tap*cin_pad + ci] * X[b][t + tap*dil - pad][ci]
  * X channels-last bf16 [b][t][ldx]; Wp bf16 [Cout][taps*cin_pad] (cin_pad = Cin rounded up to 64, zero
  * filled); outputs: C channels-last [b][t][ldc], C2 channels-first [b][co][ldc2] (either may be NULL).
+ * Epilogue: + bias -> act -> dropout(drop_p; Philox (seed, site), element = (b*T + t)*Cout + co), or with
+ * drop_first = 1: + bias -> dropout -> act (DiscConv1d's Conv -> Dropout -> Tanh, layers.py:53-57);
+ * stats (if non-NULL) accumulates per-channel sum / sum of squares of the stored values (BatchNorm).
  * Replaces ConvNorm/DiscConv1d convs: model.py:146-151 (Postnet), model.py:506-512 (Discriminator). */
 int gtn_conv1d_bf16(const void* Wp, int Cout, int Cin, int cin_pad, int taps, int dil, int pad,
                     const void* X, int nbatch, int T, long long ldx, long long strideXb,
                     void* C, int c_dtype, long long ldc, long long strideCb,
                     void* C2, int c2_dtype, long long ldc2, long long strideC2b,
-                    const float* bias_m, int act, float* stats, int block_n, void* stream);
+                    const float* bias_m, int act, float drop_p, unsigned long long seed, int site, int drop_first,
+                    float* stats, int block_n, void* stream);
 
 /* conv1d weight gradient: dW[tap][co][ci] (+)= sum_{b,t} dY[b][t][co] * X[b][t + tap*dil - pad][ci]
  * dY, X channels-LAST bf16 ([b][t][ld], the same buffers forward/dgrad use: MN-major UMMA operands, the
@@ -72,6 +76,56 @@ int gtn_gemm_tn_bf16(const void* A, const void* B, int M, int N, int K, long lon
                      int batch, long long strideA, long long strideB,
                      void* C, int c_dtype, long long ldc, long long strideC, int c_trans,
                      const float* bias_m, const float* bias_n, int accumulate, int block_n, void* stream);
+
+/* ---- Postnet / Discriminator / loss elementwise + reduction kernels (gtn_eltwise.cu) -------------------
+ * All activations are channels-last: `rows` = batch*time rows of C channels (C % 8 == 0), row stride ld
+ * (elements, % 8 == 0); dtype 0 = fp32, 1 = bf16.  Dropout: Philox (seed, site), element = row*C + c. */
+
+/* BatchNorm1d batch statistics (model.py:146-151, training mode): stats = [sum | sum of squares] over `count`
+ * samples per channel (accumulated by the conv epilogue) -> mean, rstd = 1/sqrt(biased var + eps); if
+ * running_mean != NULL also the momentum update of the running statistics (unbiased variance). */
+int gtn_bn_finalize(const float* stats, int C, long long count, float eps, float momentum, float* mean, float* rstd,
+                    float* running_mean, float* running_var, void* stream);
+/* out = dropout(act((y - mean) * rstd * gamma + beta)); act 0 none / 2 tanh; mean == NULL skips the affine. */
+int gtn_bn_act_fwd(const void* y, int y_dtype, long long ldy, long long rows, int C, const float* mean, const float* rstd,
+                   const float* gamma, const float* beta, int act, float drop_p, unsigned long long seed, int site,
+                   void* out, int out_dtype, long long ldo, void* stream);
+/* Backward of the same through batch statistics: given dx (gradient w.r.t. `out`) and the saved conv output y,
+ * writes dgamma, dbeta [C], dy (gradient w.r.t. y) and optionally dbias[c] = sum_rows dy (conv bias gradient). */
+int gtn_bn_act_bwd(const void* dx, int dx_dtype, long long lddx, const void* y, int y_dtype, long long ldy, long long rows,
+                   int C, const float* mean, const float* rstd, const float* gamma, const float* beta, int act,
+                   float drop_p, unsigned long long seed, int site, float* dgamma, float* dbeta, void* dy, int dy_dtype,
+                   long long lddy, float* dbias, void* stream);
+/* DiscConv1d backward through Tanh(Dropout(pre)) (layers.py:53-57): dpre = dout * (1 - a^2) * keep / (1 - p), a = the
+ * saved layer output; dbias[c] = sum_rows dpre (optional). */
+int gtn_drop_tanh_bwd(const void* dout, int dout_dtype, long long lddo, const void* a, int a_dtype, long long lda,
+                      long long rows, int C, float drop_p, unsigned long long seed, int site, void* dpre, int dpre_dtype,
+                      long long lddp, float* dbias, void* stream);
+/* Final Conv1d(n_mel -> 1, k = 1) of the Discriminator (model.py:512): out[row] = bias + w . x[row][:]; and its
+ * backward (dx = dout * w, dw += dout * x, db += dout; dw / db may be NULL for a frozen discriminator). */
+int gtn_disc_head_fwd(const void* x, int x_dtype, long long ldx, long long rows, int C, const float* w, const float* bias,
+                      float* out, void* stream);
+int gtn_disc_head_bwd(const float* dout, const void* x, int x_dtype, long long ldx, long long rows, int C, const float* w,
+                      void* dx, int dx_dtype, long long lddx, float* dw, float* db, void* stream);
+/* Discriminator.adversarial_loss reduction (model.py:529-540): loss = mean_b mean(out[b][0:ceil(len_b/window)]);
+ * lengths are int64 on the device (no host sync, unlike the reference's B `.to(FloatTensor)` round trips). */
+int gtn_window_mean_fwd(const float* out, int B, int P, const long long* lengths, int window, float* loss, void* stream);
+int gtn_window_mean_bwd(const float* gloss, int B, int P, const long long* lengths, int window, float* dout, void* stream);
+/* Tacotron2Loss (loss_function.py:10-22): sums[0..2] = sum (mel-tgt)^2, sum (mel_post-tgt)^2, sum BCE-with-logits(gate);
+ * strides9 (HOST array) = element strides (batch, channel, time) of mel, mel_post, target.  Backward writes dense
+ * channels-last dmel / dpost [b][t][c] and dgate [b][t], scaled by the device scalars g_mel / g_gate. */
+int gtn_taco_loss_fwd(const float* mel, const float* post, const float* tgt, const long long* strides9, int B, int C, int T,
+                      const float* gate, long long gate_sb, const float* gate_tgt, long long tgt_sb, float* sums,
+                      void* stream);
+int gtn_taco_loss_bwd(const float* mel, const float* post, const float* tgt, const long long* strides9, int B, int C, int T,
+                      const float* gate, long long gate_sb, const float* gate_tgt, long long tgt_sb, const float* g_mel,
+                      const float* g_gate, float* dmel, float* dpost, float* dgate, void* stream);
+/* Guided-attention loss (loss_function.py:25-52): loss = mean_b BCE(align[b].T[:enc_len_b, :dec_len_b], guide), align
+ * fp32 [B][T][Tin] contiguous, lengths int64 on the device, width = 0.5 in the reference.  bwd writes d(align). */
+int gtn_attn_guide_loss_fwd(const float* align, int B, int T, int Tin, const long long* enc_len, const long long* dec_len,
+                            float width, float* loss, void* stream);
+int gtn_attn_guide_loss_bwd(const float* align, int B, int T, int Tin, const long long* enc_len, const long long* dec_len,
+                            float width, const float* gloss, float* dalign, void* stream);
 
 /* ---- persistent cooperative decoder, forward (gtn_decoder_fwd.cu) ------------------------------
  * One launch = all frames of Decoder.inference (model.py:456-497; train = 0) or of the teacher-forced
