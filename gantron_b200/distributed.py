@@ -51,10 +51,11 @@ class _Bucket:
 class GradientAllReducer:
     """Holds the buckets and hooks of one module (returned module keeps a reference as `_gtn_reducer`)."""
 
-    def __init__(self, module: torch.nn.Module, bucket_bytes: int = BUCKET_BYTES, group=None):
+    def __init__(self, module: torch.nn.Module, bucket_bytes: int = None, group=None):
         if not dist.is_initialized():
             raise RuntimeError("apply_gradient_allreduce: torch.distributed is not initialised")
         self.module, self.group = module, group
+        bucket_bytes = BUCKET_BYTES if bucket_bytes is None else bucket_bytes
         self.world = dist.get_world_size(group)
         self.inv_world = 1.0 / self.world
         self._broadcast_state()

@@ -85,16 +85,29 @@ def reference_modules():
 def cpu_shims():
     """Make the reference's hard-coded `.cuda()` calls no-ops so it runs on CPU."""
     t_cuda, m_cuda = torch.Tensor.cuda, torch.nn.Module.cuda
-    had_long = getattr(torch.cuda, "LongTensor", None)
+    saved_types = {n: getattr(torch.cuda, n, None) for n in ("LongTensor", "IntTensor", "FloatTensor")}
+    t_zeros, t_linspace = torch.zeros, torch.linspace
+
+    def no_cuda_device(fn):
+        # loss_function.py:28,47,49 hard-code device='cuda'
+        def wrapped(*a, **k):
+            if str(k.get("device", "")) .startswith("cuda"):
+                k.pop("device")
+            return fn(*a, **k)
+        return wrapped
+
     torch.Tensor.cuda = lambda self, *a, **k: self
     torch.nn.Module.cuda = lambda self, *a, **k: self
-    torch.cuda.LongTensor = torch.LongTensor
+    torch.cuda.LongTensor, torch.cuda.IntTensor, torch.cuda.FloatTensor = torch.LongTensor, torch.IntTensor, torch.FloatTensor
+    torch.zeros, torch.linspace = no_cuda_device(t_zeros), no_cuda_device(t_linspace)
     try:
         yield
     finally:
         torch.Tensor.cuda, torch.nn.Module.cuda = t_cuda, m_cuda
-        if had_long is not None:
-            torch.cuda.LongTensor = had_long
+        torch.zeros, torch.linspace = t_zeros, t_linspace
+        for n, v in saved_types.items():
+            if v is not None:
+                setattr(torch.cuda, n, v)
 
 
 @contextlib.contextmanager
