@@ -1,0 +1,134 @@
+"""GPU: the CUDA path (through the drop-in model surface -> C ABI) against the committed REFERENCE outputs in
+tests/golden/ (produced by the unmodified reference with the kernels' Philox masks injected, oracle/make_golden.py).
+fp32-accurate mode; bound from the north star: 1e-3 relative."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+REL = 1e-3
+
+
+def _load(name):
+    return np.load(os.path.join(GOLDEN_DIR, name + ".npz"), allow_pickle=False)
+
+
+def _rel(got, ref):
+    got = torch.as_tensor(got).detach().float().cpu()
+    ref = torch.as_tensor(ref).float()
+    assert got.shape == ref.shape, f"shape {tuple(got.shape)} vs {tuple(ref.shape)}"
+    return float((got - ref).abs().max()) / (float(ref.abs().max()) + 1e-12)
+
+
+def _check_grads(z, grads, rel=REL):
+    n = 0
+    bad = []
+    for key in z.files:
+        if not key.startswith("gnorm/"):
+            continue
+        name = key[len("gnorm/"):]
+        if name not in grads:
+            continue
+        g = grads[name].detach().float().cpu().reshape(-1)
+        ref_norm = float(z[key])
+        rms = ref_norm / max(g.numel(), 1) ** 0.5
+        if f"grad/{name}" in z.files:
+            ref, got = torch.from_numpy(z[f"grad/{name}"]), g
+        else:
+            stride = int(z[f"gstride/{name}"])
+            ref, got = torch.from_numpy(z[f"gsample/{name}"]), g[::stride]
+        err = float((got - ref).abs().max())
+        if err > rel * max(float(ref.abs().max()), rms) + 2e-6:
+            bad.append(f"{name}: err {err:.3g} absmax {float(ref.abs().max()):.3g}")
+        n += 1
+    assert not bad, "; ".join(bad[:8])
+    return n
+
+
+@pytest.mark.parametrize("name", ["train_vanilla", "train_combined"])
+def test_training_step_matches_reference_golden(name):
+    from oracle import gantron_oracle as O
+    from gantron_b200.hparams import HParams
+    from gantron_b200 import model as M
+    from gantron_b200.loss_function import Tacotron2Loss
+    z = _load(name)
+    hp = HParams(str(z["hp_string"]) + ",b200_precision=fp32")
+    G, D = M.Tacotron2(hp), M.Discriminator(hp)
+    wseed, mseed = int(z["wseed"]), int(z["mseed"])
+    G.load_state_dict(O.seeded_state_dict({k: tuple(v) for k, v in json.loads(str(z["sd/G"])).items()}, seed=wseed))
+    D.load_state_dict(O.seeded_state_dict({k: tuple(v) for k, v in json.loads(str(z["sd/D"])).items()}, seed=wseed + 1))
+    G, D = G.cuda().train(), D.cuda().train()
+    for p in D.parameters():
+        p.requires_grad = False
+    G.decoder._forced_seed = G.postnet._forced_seed = D._forced_seed = mseed
+    memory = torch.from_numpy(z["in/memory"]).cuda()
+    enc = memory[:, :, :512].clone().requires_grad_(True)
+    noise = memory[:, :, -512:]
+    # the text encoder is out of scope (stock PyTorch): feed the reference's captured encoder outputs / noise draw
+    G.encoder.forward = lambda emb, lens: enc
+    G.decoder.append_noise = lambda x: torch.cat((x, noise), -1)
+    batch = tuple(torch.from_numpy(z[f"in/{n}"]) for n in ("text", "in_len", "mel_tgt", "gate_tgt", "spk", "emo", "out_len"))
+    x, y = G.parse_batch(batch)
+    y_pred = G(x)
+    for n, t in zip(("mel", "mel_post", "gate", "align"), y_pred):
+        e = _rel(t, z[f"out/{n}"])
+        assert e <= REL, f"{name}:{n} rel err {e:.3e}"
+    mel_loss, gate_loss, attn_loss = Tacotron2Loss()(y_pred, y, x[1], x[-1])
+    adv = D.adversarial_loss(y_pred[1], x[-1])
+    for n, t in (("mel_loss", mel_loss), ("gate_loss", gate_loss), ("attn_loss", attn_loss), ("adv", adv)):
+        ref = float(z[f"out/{n}"])
+        assert abs(float(t) - ref) <= REL * abs(ref) + 1e-6, f"{name}:{n} {float(t)} vs {ref}"
+    (mel_loss + gate_loss + adv + 10 * attn_loss).backward()
+    grads = {k: p.grad for k, p in G.named_parameters() if p.grad is not None}
+    if name == "train_vanilla":        # combined: the stored gradient also spans speaker / emotion columns
+        grads["enc_out"] = enc.grad
+    n = _check_grads(z, grads)
+    assert n >= 39
+    for i in range(5):
+        for s in ("running_mean", "running_var"):
+            k = f"postnet.convolutions.{i}.1.{s}"
+            assert _rel(G.state_dict()[k], z[f"bn/{k}"]) <= REL, k
+
+
+def test_inference_matches_reference_golden():
+    from oracle import gantron_oracle as O
+    from gantron_b200.hparams import HParams
+    from gantron_b200 import model as M
+    z = _load("infer_vanilla_b1")
+    hp = HParams(str(z["hp_string"]) + ",b200_precision=fp32")
+    G = M.Tacotron2(hp)
+    G.load_state_dict(O.seeded_state_dict({k: tuple(v.shape) for k, v in G.state_dict().items()}, seed=int(z["wseed"])))
+    G = G.cuda().eval()
+    G.decoder._forced_seed = int(z["mseed"])
+    with torch.no_grad():
+        mel, gate, align = G.decoder.inference(torch.from_numpy(z["in/memory"]).cuda(), torch.from_numpy(z["in/style"]).cuda())
+        post = mel + G.postnet(mel)
+    steps = int(z["steps"])
+    assert mel.shape == (1, 80, steps) and gate.shape == (1, steps, 1) and align.shape[:2] == (1, steps)
+    for n, t in (("mel", mel), ("gate", gate), ("align", align), ("mel_post", post)):
+        e = _rel(t, z[f"out/{n}"])
+        assert e <= REL, f"{n} rel err {e:.3e}"
+
+
+def test_discriminator_matches_reference_golden():
+    from oracle import gantron_oracle as O
+    from gantron_b200.hparams import HParams
+    from gantron_b200 import model as M
+    z = _load("disc_vanilla")
+    D = M.Discriminator(HParams("use_noise=True,use_labels=False,b200_precision=fp32"))
+    D.load_state_dict(O.seeded_state_dict({k: tuple(v.shape) for k, v in D.state_dict().items()}, seed=int(z["wseed"])))
+    D = D.cuda().train()
+    D._forced_seed = int(z["mseed"])
+    mel = torch.from_numpy(z["in/mel"]).cuda().requires_grad_(True)
+    loss = D.adversarial_loss(mel, torch.from_numpy(z["in/lengths"]).cuda())
+    ref = float(z["out/loss"])
+    assert abs(float(loss) - ref) <= REL * abs(ref) + 1e-6
+    loss.backward()
+    grads = {k: p.grad for k, p in D.named_parameters()}
+    grads["mel"] = mel.grad
+    assert _check_grads(z, grads) == 11
