@@ -59,6 +59,7 @@ SIGNATURES = {
     "gtn_attn_guide_loss_fwd": (c_i, [c_p, c_i, c_i, c_i, c_p, c_p, c_f, c_p, c_p]),
     "gtn_attn_guide_loss_bwd": (c_i, [c_p, c_i, c_i, c_i, c_p, c_p, c_f, c_p, c_p, c_p]),
     "gtn_decoder_forward": (c_i, [c_p, c_p]),
+    "gtn_decoder_forward2": (c_i, [c_p, c_p]),
     "gtn_sizeof": (c_i, [c_i]),
     "gtn_decoder_bwd_grid": (c_i, []),
     "gtn_decoder_backward": (c_i, [c_p, c_p]),
@@ -82,7 +83,8 @@ class DecoderFwdParams(C.Structure):
                               "qpart", "barrier", "done", "lengths_out", "stop", "steps_done",
                               "align_out", "mel_out", "gate_out",
                               "gates_a", "c_a_all", "h_a_all", "gates_d", "c_d_all", "h_d_all", "ctx_all",
-                              "q_all", "th_all", "f_all", "cum_all")]
+                              "q_all", "th_all", "f_all", "cum_all",
+                              "w_att2", "w_dec2", "u_loc", "wq_t", "prof")]
     )
 
 

@@ -1,0 +1,208 @@
+// Device machinery of the second-generation persistent decoder kernels (gtn_decoder_fwd2.cu / gtn_decoder_bwd2.cu):
+// thread-block clusters + distributed shared memory, the cluster-split skinny GEMM engine on tcgen05, and the
+// grid-wide barrier.
+//
+// Skinny GEMM engine.  Every per-frame matrix product of the decoder has the shape
+//        OUT[rows, B] = W[rows, K] . X[B, K]^T            B = batch (<= 256), K in the thousands
+// and is bound by how fast W and X reach the SMs, not by the tensor pipe.  A cluster of 4 CTAs owns one
+// 128-row tile of W and splits K four ways: each CTA streams ITS quarter of the tile's K (W k-blocks 128 x 64 and
+// the matching X k-blocks N x 64, bf16, SWIZZLE_128B, through a TMA ring) into tcgen05.mma (M = 128, N = batch,
+// fp32 accumulator in TMEM).  Compared with one CTA per row tile this divides the activation traffic per SM by 4
+// and lets all 128 clustered SMs pull weights concurrently.  The four partial accumulators are then exchanged
+// through distributed shared memory: CTA r receives, from every peer, the columns (batch rows) [r*N/4, (r+1)*N/4)
+// of the 128 x N partial tile, sums the four copies and runs the fused epilogue (LSTM cell, dropout, ...) on its
+// 128 x N/4 slice.  One cluster barrier per 64 batch columns; the receive buffer is double buffered so that no
+// second barrier is needed before the next exchange.
+#pragma once
+#include "gtn_common.cuh"
+#include "gtn_decoder.cuh"
+
+namespace gtn {
+
+static constexpr int CL = 4;           // CTAs per cluster (K split)
+static constexpr int TILE_M = 128;     // weight rows per cluster tile (UMMA M)
+static constexpr int KB = 64;          // K elements per k-block (one SWIZZLE_128B row of bf16)
+static constexpr int W_TILE_BYTES = TILE_M * KB * 2;
+
+GTN_DEVICE uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+GTN_DEVICE uint32_t cluster_idx() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%clusterid.x;" : "=r"(r));
+  return r;
+}
+GTN_DEVICE uint32_t cluster_count() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%nclusterid.x;" : "=r"(r));
+  return r;
+}
+// full cluster barrier with release/acquire semantics (orders st.shared::cluster before the peers' reads)
+GTN_DEVICE void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+GTN_DEVICE uint32_t map_to_rank(uint32_t smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
+  return r;
+}
+GTN_DEVICE void st_cluster_f4(uint32_t addr, float a, float b, float c, float d) {
+  asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+GTN_DEVICE void st_cluster_f1(uint32_t addr, float a) {
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(a) : "memory");
+}
+// generic-proxy writes (st.global / st.shared) -> async-proxy reads (TMA, tcgen05.mma operand fetch)
+GTN_DEVICE void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+GTN_DEVICE void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+GTN_DEVICE void wait_bar(uint64_t* bar, uint32_t parity) {
+  long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > 8000000000LL) __trap();   // ~4 s: a pipeline bug must not hang the GPU
+  }
+}
+
+// Grid-wide barrier for a co-resident launch; thread 0 (the TMA producer thread) carries the proxy fences.
+GTN_DEVICE void grid_sync2(unsigned int* counter, unsigned int& epoch, unsigned int nblocks) {
+  __syncthreads();
+  epoch += nblocks;
+  if (threadIdx.x == 0) {
+    fence_proxy_async();
+    __threadfence();
+    red_release_add(counter, 1u);
+    long long t0 = clock64();
+    while (ld_acquire_u32(counter) < epoch) {
+      if (clock64() - t0 > 20000000000LL) __trap();
+    }
+    __threadfence();
+    fence_proxy_async();
+  }
+  __syncthreads();
+}
+
+GTN_DEVICE float tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// swizzled byte offset of the 16-byte chunk `chunk` (8 bf16) of row `r` inside a K-major SWIZZLE_128B tile
+GTN_DEVICE uint32_t sw128_off(int r, int chunk) {
+  return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((chunk ^ (r & 7)) << 4));
+}
+
+// ---- ring pipeline state (meaningful in the producer / MMA threads only) ----
+struct Ring {
+  uint8_t* base;          // S stages of [W tile 16 KB | X tile N*128 B]
+  uint64_t* full;
+  uint64_t* empty;
+  int S;
+  uint32_t stage_bytes;
+  uint32_t prod_it, mma_it;
+};
+
+struct XSeg {
+  const CUtensorMap* map;
+  int nkb;                // k-blocks in this segment
+  int z;                  // third TMA coordinate (time step / double-buffer slot)
+};
+
+struct GemmJob {
+  const CUtensorMap* wmap;
+  int row0;               // first weight row of the tile
+  int nkb;                // total k-blocks over K (all 4 ranks)
+  int nseg;
+  XSeg seg[3];
+};
+
+// Issue one cluster-split GEMM: this CTA's quarter of K.  Producer = thread 0, MMA = thread 32.
+// Returns whether this CTA had any k-block (else its partial tile is all zeros).
+template <int N>
+GTN_DEVICE bool gemm_issue(const GemmJob& job, Ring& rg, uint32_t tmem_acc, uint64_t* acc_full, int rank) {
+  const int kb0 = rank * job.nkb / CL, kb1 = (rank + 1) * job.nkb / CL;
+  constexpr uint32_t X_BYTES = N * KB * 2;
+  if (threadIdx.x == 0) {
+    for (int kb = kb0; kb < kb1; ++kb) {
+      const int s = rg.prod_it % rg.S;
+      const uint32_t par = (rg.prod_it / rg.S) & 1u;
+      wait_bar(&rg.empty[s], par ^ 1u);
+      mbar_expect_tx(&rg.full[s], W_TILE_BYTES + X_BYTES);
+      uint8_t* st = rg.base + (size_t)s * rg.stage_bytes;
+      tma_load_3d(st, job.wmap, &rg.full[s], kb * KB, job.row0, 0);
+      int kk = kb, si = 0;
+      while (si < job.nseg - 1 && kk >= job.seg[si].nkb) { kk -= job.seg[si].nkb; ++si; }
+      tma_load_3d(st + W_TILE_BYTES, job.seg[si].map, &rg.full[s], kk * KB, 0, job.seg[si].z);
+      ++rg.prod_it;
+    }
+  } else if (threadIdx.x == 32) {
+    if (kb1 > kb0) {
+      const uint32_t idesc = umma_idesc_bf16(TILE_M, N);
+      for (int kb = kb0; kb < kb1; ++kb) {
+        const int s = rg.mma_it % rg.S;
+        const uint32_t par = (rg.mma_it / rg.S) & 1u;
+        wait_bar(&rg.full[s], par);
+        tc_fence_after();
+        const uint32_t a = smem_u32(rg.base + (size_t)s * rg.stage_bytes);
+        const uint64_t da = umma_desc_sw128(a), db = umma_desc_sw128(a + W_TILE_BYTES);
+#pragma unroll
+        for (int k = 0; k < KB / 16; ++k)
+          umma_bf16(tmem_acc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb > kb0) | (k > 0)));
+        umma_commit(&rg.empty[s]);
+        ++rg.mma_it;
+      }
+      umma_commit(acc_full);
+    }
+  }
+  return kb1 > kb0;
+}
+
+// Exchange one chunk (CH = min(N, 64) batch columns starting at column c0) of the partial accumulator:
+// warps 4..7 read their TMEM lane quarter and scatter column group r to rank r's receive buffer
+// recv[src rank][row 0..127][NC4 = CH/4 columns].  Every thread of the CTA then joins the cluster barrier.
+template <int CH>
+GTN_DEVICE void exchange_chunk(bool has_work, uint32_t tmem_acc, int c0, float* recv, int rank) {
+  constexpr int NC4 = CH / 4;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp >= 4) {
+    const int wq = warp & 3;
+    const int row = wq * 32 + lane;
+    const uint32_t my = smem_u32(recv + ((size_t)rank * TILE_M + row) * NC4);
+#pragma unroll
+    for (int h = 0; h < CH / 32; ++h) {
+      uint32_t r[32];
+      if (has_work) {
+        tmem_ld_32x32(tmem_acc + ((uint32_t)(wq * 32) << 16) + (uint32_t)(c0 + h * 32), r);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) r[j] = 0u;
+      }
+      // columns h*32 .. h*32+31 of the chunk: destination rank = column / NC4
+#pragma unroll
+      for (int g = 0; g < 32 / NC4; ++g) {
+        const int dst = (h * 32 + g * NC4) / NC4;
+        const uint32_t a = map_to_rank(my, (uint32_t)dst);
+#pragma unroll
+        for (int v = 0; v < NC4; v += 4)
+          st_cluster_f4(a + (uint32_t)(v * 4), __uint_as_float(r[g * NC4 + v]), __uint_as_float(r[g * NC4 + v + 1]),
+                        __uint_as_float(r[g * NC4 + v + 2]), __uint_as_float(r[g * NC4 + v + 3]));
+      }
+    }
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+}
+
+// sum of the four partials of element (row, col) of this CTA's slice
+template <int NC4>
+GTN_DEVICE float recv_sum(const float* recv, int row, int col) {
+  const float* p = recv + (size_t)row * NC4 + col;
+  return (p[0] + p[(size_t)TILE_M * NC4]) + (p[(size_t)2 * TILE_M * NC4] + p[(size_t)3 * TILE_M * NC4]);
+}
+
+}  // namespace gtn

@@ -1,0 +1,680 @@
+// Persistent clustered decoder kernel, forward (second generation).  ONE launch runs every frame of
+//   * Decoder.inference  (reference model.py:456-497): prenet -> decode() -> gate test, autoregressive
+//   * Decoder.forward    (reference model.py:419-454): the teacher-forced loop of decode() calls
+// decode() is model.py:378-417.  See gtn_decoder2.cuh for the cluster-split tcgen05 GEMM engine.
+//
+// Grid = NC clusters of 4 CTAs (one CTA per SM, all co-resident).  Phases of a frame:
+//   [infer] P1, P2  prenet layers (relu + always-on dropout, model.py:102-105) as 128-row GEMM tiles
+//   A   attention LSTM: cluster c owns hidden units [32c, 32c+32) (all four gates = one 128-row tile of
+//       W_att, rows permuted gate-major per tile); fused cell + dropout; partial attention query
+//       Wq[:, units] . h_att' for its 32 units                                   (model.py:391-394, 62)
+//   B   location-sensitive attention, one CTA PAIR per sequence (encoder positions split in halves):
+//       the location conv (2->F, k) and dense (F->A) are pre-multiplied into one 128 x 64 filter U and run
+//       as a tcgen05 GEMM over an im2col tile of [prev | cumulative] weights (hi/lo bf16 planes, fp32
+//       accumulate in TMEM), e = v.tanh(q + loc + processed_memory), energies exchanged through DSMEM,
+//       masked softmax, context over the time-varying memory columns (split by column halves), cum += w
+//                                                                                (model.py:27-31,62-89,403)
+//   C   decoder LSTM (model.py:404-409)
+//   [infer] D  mel/gate projection + stop test (model.py:411-416,486)
+// Grid barriers: after A, after B (training: C(t) and A(t+1) share an interval since A does not read h_dec).
+// Training additionally saves what the backward kernel needs.  The time-constant columns of `memory`
+// (noise / speaker / emotion: model.py:275-278,655-663) are not re-read per frame: context = const * sum_j w_j.
+#include "gtn_decoder2.cuh"
+#include "gtn_internal.h"
+#include "../../include/gantron_b200.h"
+
+namespace gtn {
+
+typedef gtn_decoder_fwd_params DecFwd;
+#define BFP(x) (reinterpret_cast<bf16*>(const_cast<void*>(static_cast<const void*>(x))))
+
+struct Fwd2Maps {
+  CUtensorMap w_att, w_dec, w_pre1, w_pre2, w_proj, uloc;
+  CUtensorMap pre, ctx, ha, hd, xmel, xp1, xp2;
+};
+
+#define PROF(slot)                                                                          \
+  do {                                                                                      \
+    if (p.prof != nullptr && blockIdx.x == 0 && threadIdx.x == 0 && t < 16) p.prof[t * 32 + (slot)] = clock64(); \
+  } while (0)
+#define PROF_T(thr, slot)                                                                   \
+  do {                                                                                      \
+    if (p.prof != nullptr && blockIdx.x == 0 && threadIdx.x == (thr) && t < 16) p.prof[t * 32 + (slot)] = clock64(); \
+  } while (0)
+
+enum { K_PRE1 = 0, K_PRE2 = 1, K_ATT = 2, K_DEC = 3, K_PROJ = 4 };
+
+struct Smem2 {
+  Ring ring;
+  uint8_t* u_s;        // [2][16 KB]  U_hi, U_lo (UMMA B operand of the location GEMM)
+  float* recv;         // [2][4][128][NC4]
+  float* wq_s;         // [32][A]
+  float* hs;           // [NC4][32]
+  float* q_s;          // [A]
+  float* v_s;          // [A]
+  float* wcat;         // [2][JH + KS - 1]
+  float* e_buf;        // [2][Tin_pad]
+  float* e_part;       // [2][128]
+  float* w_s;          // [Tin_pad]
+  float* red_s;        // [8][256]
+  float* scr;          // [64]
+  uint64_t* acc_full;
+  uint64_t* att_full;
+  uint64_t* u_full;
+  uint32_t* tmem_slot;
+};
+
+static constexpr int JH_MAX = 128;     // encoder positions per CTA of a pair (T_in <= 256)
+static constexpr int TIN_MAX = 256;
+static constexpr int KS_MAX = 63;
+
+template <int N>
+__host__ __device__ constexpr size_t fwd2_fixed_bytes() {
+  constexpr int NC4 = (N < 64 ? N : 64) / 4;
+  return (size_t)2 * W_TILE_BYTES                        // u_s
+         + (size_t)2 * 4 * TILE_M * NC4 * 4               // recv
+         + (size_t)32 * 128 * 4                           // wq_s
+         + (size_t)(NC4 * 32 + 128 + 128 + 2 * (JH_MAX + KS_MAX - 1) + 2 * TIN_MAX + 2 * 128 + TIN_MAX + 8 * 256 + 64) * 4
+         + 64 * 8 + 64;                                   // barriers + tmem slot
+}
+
+template <int N>
+GTN_DEVICE Smem2 carve2(uint8_t* base, int S) {
+  constexpr int NC4 = (N < 64 ? N : 64) / 4;
+  Smem2 m;
+  m.ring.base = base;
+  m.ring.S = S;
+  m.ring.stage_bytes = W_TILE_BYTES + N * KB * 2;
+  m.ring.prod_it = m.ring.mma_it = 0;
+  uint8_t* p = base + (size_t)S * m.ring.stage_bytes;
+  m.u_s = p; p += 2 * W_TILE_BYTES;
+  float* f = reinterpret_cast<float*>(p);
+  m.recv = f; f += 2 * 4 * TILE_M * NC4;
+  m.wq_s = f; f += 32 * 128;
+  m.hs = f; f += NC4 * 32;
+  m.q_s = f; f += 128;
+  m.v_s = f; f += 128;
+  m.wcat = f; f += 2 * (JH_MAX + KS_MAX - 1);
+  m.e_buf = f; f += 2 * TIN_MAX;
+  m.e_part = f; f += 2 * 128;
+  m.w_s = f; f += TIN_MAX;
+  m.red_s = f; f += 8 * 256;
+  m.scr = f; f += 64;
+  uint64_t* b = reinterpret_cast<uint64_t*>(f);
+  m.ring.full = b; b += 16;
+  m.ring.empty = b; b += 16;
+  m.acc_full = b++;
+  m.att_full = b++;
+  m.u_full = b++;
+  m.tmem_slot = reinterpret_cast<uint32_t*>(b + 1);
+  return m;
+}
+
+GTN_DEVICE float block_reduce2(float v, float* scr, bool is_max) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  v = is_max ? warp_max(v) : warp_sum(v);
+  __syncthreads();
+  if (lane == 0) scr[warp] = v;
+  __syncthreads();
+  float r = scr[0];
+#pragma unroll
+  for (int w = 1; w < 8; ++w) r = is_max ? fmaxf(r, scr[w]) : r + scr[w];
+  return r;
+}
+
+// ------------------------------------------------------------------------------------------------
+// GEMM phases: prenet layers, the two LSTM cells, the mel/gate projection
+// ------------------------------------------------------------------------------------------------
+template <int N>
+GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int kind, int t, int rank, int cid, int ncl,
+                           uint32_t tmem_base, uint32_t& acc_par, uint32_t& round) {
+  constexpr int CH = N < 64 ? N : 64;
+  constexpr int NC4 = CH / 4;
+  const int mult = p.mult, cur = t & 1, nxt = cur ^ 1;
+  GemmJob job;
+  int ntiles;
+  switch (kind) {
+    case K_PRE1:
+      job.wmap = &maps.w_pre1; ntiles = (p.P + TILE_M - 1) / TILE_M; job.nseg = 1;
+      job.seg[0] = {&maps.xmel, mult * p.NMp / KB, 0};
+      break;
+    case K_PRE2:
+      job.wmap = &maps.w_pre2; ntiles = (p.P + TILE_M - 1) / TILE_M; job.nseg = 1;
+      job.seg[0] = {&maps.xp1, mult * p.Pp / KB, 0};
+      break;
+    case K_ATT:
+      job.wmap = &maps.w_att; ntiles = p.Ha / 32; job.nseg = 3;
+      job.seg[0] = p.train ? XSeg{&maps.pre, mult * p.Pp / KB, t} : XSeg{&maps.xp2, mult * p.Pp / KB, 0};
+      job.seg[1] = {&maps.ctx, mult * p.Dp / KB, 0};
+      job.seg[2] = {&maps.ha, mult * p.Hap / KB, cur};
+      break;
+    case K_DEC:
+      job.wmap = &maps.w_dec; ntiles = p.Hd / 32; job.nseg = 3;
+      job.seg[0] = {&maps.ha, mult * p.Hap / KB, nxt};
+      job.seg[1] = {&maps.ctx, mult * p.Dp / KB, 0};
+      job.seg[2] = {&maps.hd, mult * p.Hdp / KB, cur};
+      break;
+    default:
+      job.wmap = &maps.w_proj; ntiles = 1; job.nseg = 2;
+      job.seg[0] = {&maps.hd, mult * p.Hdp / KB, nxt};
+      job.seg[1] = {&maps.ctx, mult * p.Dp / KB, 0};
+      break;
+  }
+  job.nkb = 0;
+  for (int i = 0; i < job.nseg; ++i) job.nkb += job.seg[i].nkb;
+  const bool is_lstm = kind == K_ATT || kind == K_DEC;
+  const bool is_att = kind == K_ATT;
+  const int H = is_att ? p.Ha : p.Hd, Hp = is_att ? p.Hap : p.Hdp;
+
+  for (int tile = cid; tile < ntiles; tile += ncl) {
+    job.row0 = tile * TILE_M;
+    if (is_att && (ntiles > ncl || t == 0)) {
+      // query-weight slice of this tile's 32 units: wq_s[ul][a] = Wq[a][32*tile + ul]  (wq_t is [Ha][A])
+      for (int i = threadIdx.x; i < 32 * p.A; i += blockDim.x) sm.wq_s[i] = p.wq_t[(size_t)tile * 32 * p.A + i];
+    }
+    const int ps = kind == K_ATT ? 1 : (kind == K_DEC ? 9 : (kind == K_PROJ ? 14 : 20));
+    const bool has_work = gemm_issue<N>(job, sm.ring, tmem_base, sm.acc_full, rank);
+    PROF(ps);                                    // producer: all TMA loads issued
+    __syncwarp();
+    if ((threadIdx.x >> 5) >= 4 && has_work) {
+      wait_bar(sm.acc_full, acc_par);
+      tc_fence_after();
+    }
+    PROF_T(128, ps + 1);                         // epilogue warp: accumulator complete
+    if (has_work) acc_par ^= 1u;
+    for (int c0 = 0; c0 < N; c0 += CH) {
+      float* recv = sm.recv + (size_t)(round & 1u) * 4 * TILE_M * NC4;
+      ++round;
+      exchange_chunk<CH>(has_work, tmem_base, c0, recv, rank);
+      PROF(ps + 2);                              // DSMEM exchange + cluster barrier done
+      const int bbase = c0 + rank * NC4;
+      if (is_lstm) {
+        float* cst = is_att ? p.c_a : p.c_d;
+        const float* bias = is_att ? p.b_att : p.b_dec;
+        const float pdrop = is_att ? p.p_att : p.p_dec;
+        const unsigned thr = is_att ? p.thr_att : p.thr_dec;
+        const float dscale = 1.0f / (1.0f - pdrop);
+        const unsigned site = is_att ? 3u : 4u;
+        bf16* xh_next = (is_att ? BFP(p.xh_a) : BFP(p.xh_d)) + (size_t)nxt * p.B * mult * Hp;
+        float* gates_all = is_att ? p.gates_a : p.gates_d;
+        float* c_all = is_att ? p.c_a_all : p.c_d_all;
+        float* h_all = is_att ? p.h_a_all : p.h_d_all;
+        for (int idx = threadIdx.x; idx < 32 * NC4; idx += blockDim.x) {
+          const int bl = idx % NC4, ul = idx / NC4, b = bbase + bl, unit = tile * 32 + ul;
+          float h = 0.f;
+          if (b < p.B) {
+            const float gi = recv_sum<NC4>(recv, ul, bl) + bias[unit];
+            const float gf = recv_sum<NC4>(recv, 32 + ul, bl) + bias[H + unit];
+            const float gg = recv_sum<NC4>(recv, 64 + ul, bl) + bias[2 * H + unit];
+            const float go = recv_sum<NC4>(recv, 96 + ul, bl) + bias[3 * H + unit];
+            const float i_ = sigmoid_acc(gi), f_ = sigmoid_acc(gf), g_ = tanh_acc(gg), o_ = sigmoid_acc(go);
+            const size_t ci = (size_t)b * H + unit;
+            const float c_new = f_ * cst[ci] + i_ * g_;
+            cst[ci] = c_new;
+            h = o_ * tanh_acc(c_new);
+            if (p.use_dropout && thr != 0u) {
+              const uint32_t bits = philox_bits(p.seed, site, (uint32_t)t, (uint32_t)ci);
+              h = bits >= thr ? h * dscale : 0.f;
+            }
+            store_act(xh_next + (size_t)b * mult * Hp, unit, Hp, p.prec, h);
+            if (p.train) {
+              const size_t g0 = ((size_t)t * p.B + b) * 4 * H + unit;
+              gates_all[g0] = i_; gates_all[g0 + H] = f_; gates_all[g0 + 2 * H] = g_; gates_all[g0 + 3 * H] = o_;
+              c_all[((size_t)t * p.B + b) * H + unit] = c_new;
+              h_all[((size_t)t * p.B + b) * H + unit] = h;
+            }
+          }
+          if (is_att) sm.hs[bl * 32 + ul] = h;
+        }
+        if (is_att) {
+          __syncthreads();
+          // partial query of this tile: qpart[tile][b][a] = sum_ul Wq[a][32 tile + ul] h[b][ul]
+          for (int idx = threadIdx.x; idx < NC4 * p.A; idx += blockDim.x) {
+            const int bl = idx / p.A, a = idx - bl * p.A, b = bbase + bl;
+            if (b >= p.B) continue;
+            float s = 0.f;
+#pragma unroll 8
+            for (int u = 0; u < 32; ++u) s += sm.wq_s[u * p.A + a] * sm.hs[bl * 32 + u];
+            p.qpart[((size_t)tile * p.B + b) * p.A + a] = s;
+          }
+        }
+      } else {
+        const int rows = kind == K_PROJ ? p.NM + 1 : p.P;
+        for (int idx = threadIdx.x; idx < TILE_M * NC4; idx += blockDim.x) {
+          const int bl = idx % NC4, r = idx / NC4, b = bbase + bl, row = tile * TILE_M + r;
+          if (b >= p.B || row >= rows) continue;
+          float val = recv_sum<NC4>(recv, r, bl);
+          if (kind != K_PROJ) {
+            val = fmaxf(val, 0.f);
+            const uint32_t bits = philox_bits(p.seed, kind == K_PRE1 ? 1u : 2u, (uint32_t)t, (uint32_t)(b * p.P + row));
+            val = bits >= 0x80000000u ? val * 2.0f : 0.f;     // p = 0.5, always on (model.py:104)
+            store_act((kind == K_PRE1 ? BFP(p.xp1) : BFP(p.xp2)) + (size_t)b * mult * p.Pp, row, p.Pp, p.prec, val);
+          } else {
+            val += p.b_proj[row];
+            if (row < p.NM) {
+              p.mel_out[((size_t)b * p.NM + row) * p.n_steps + t] = val;
+              store_act(BFP(p.xmel) + (size_t)b * mult * p.NMp, row, p.NMp, p.prec, val);
+            } else {
+              p.gate_out[(size_t)b * p.n_steps + t] = val;
+              if (sigmoid_acc(val) > p.gate_threshold && p.done[b] == 0) { p.done[b] = 1; p.lengths_out[b] = t + 1; }
+            }
+          }
+        }
+      }
+    }
+    if (kind == K_PROJ) {
+      // the cluster that owns the projection decides whether every sequence has fired its gate (model.py:486)
+      cluster_sync_all();                                  // the four ranks' done[] writes
+      if (rank == 0) {
+        __threadfence();
+        int all = 1;
+        for (int b = threadIdx.x; b < p.B; b += blockDim.x) all &= (__ldcg(&p.done[b]) != 0);
+        all = __syncthreads_and(all);
+        if (threadIdx.x == 0 && all && !p.ignore_stop) *p.stop = 1;
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// attention phase: one CTA pair per sequence
+// ------------------------------------------------------------------------------------------------
+template <typename MT>
+GTN_DEVICE void ld8(const MT* p, float (&o)[8]);
+template <>
+GTN_DEVICE void ld8<float>(const float* p, float (&o)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+}
+template <>
+GTN_DEVICE void ld8<bf16>(const bf16* p, float (&o)[8]) {
+  const uint4 q = __ldg(reinterpret_cast<const uint4*>(p));
+  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    o[2 * i] = __uint_as_float(w[i] << 16);
+    o[2 * i + 1] = __uint_as_float(w[i] & 0xFFFF0000u);
+  }
+}
+
+template <typename MT>
+GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, int cid, int ncl, uint32_t tmem_att,
+                                 uint32_t& att_par, uint32_t& eround) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int Tin = p.Tin, A = p.A, KS = p.KS, hk = (p.KS - 1) / 2;
+  const int half = rank & 1, peer = rank ^ 1;
+  const int pair = cid * 2 + (rank >> 1), npairs = ncl * 2;
+  const int JH = (Tin + 1) / 2;
+  const int j0 = half * JH, jn = min(Tin, j0 + JH) - j0;
+  const int Wd = jn + KS - 1;
+  const MT* mem = reinterpret_cast<const MT*>(p.mem_enc);
+  const MT* pm = reinterpret_cast<const MT*>(p.pm);
+  uint8_t* a_hi = sm.ring.base;                          // im2col tiles alias ring stage 0 (idle during this phase)
+  uint8_t* a_lo = sm.ring.base + W_TILE_BYTES;
+  const int niter = (p.B + npairs - 1) / npairs;
+  for (int it = 0; it < niter; ++it) {
+    const int b = pair + it * npairs;
+    const bool active = b < p.B;
+    const int L = active ? (p.lengths ? min(p.lengths[b], Tin) : Tin) : 0;
+    float* e_buf = sm.e_buf + (size_t)(eround & 1u) * TIN_MAX;
+    ++eround;
+    if (active) {
+      const int ntq = p.Ha / 32;
+      for (int a = threadIdx.x; a < A; a += blockDim.x) {
+        float s = 0.f;
+        for (int c = 0; c < ntq; ++c) s += __ldcg(&p.qpart[((size_t)c * p.B + b) * A + a]);
+        sm.q_s[a] = s;
+        if (p.train && half == 0) p.q_all[((size_t)t * p.B + b) * A + a] = s;
+      }
+      const float* wprev = p.w_prev + (size_t)b * p.ldT;
+      const float* wcum = p.w_cum + (size_t)b * p.ldT;
+      for (int i = threadIdx.x; i < 2 * Wd; i += blockDim.x) {
+        const int ch = i / Wd, jj = i - ch * Wd, j = j0 + jj - hk;
+        const float val = (j >= 0 && j < Tin) ? __ldcg(ch == 0 ? &wprev[j] : &wcum[j]) : 0.f;
+        sm.wcat[i] = val;
+        if (p.train && ch == 1 && jj >= hk && jj < hk + jn) p.cum_all[((size_t)t * p.B + b) * Tin + j] = val;
+      }
+    }
+    __syncthreads();
+    if (active) {
+      // im2col: row r = local encoder position, K index kk = ch*KS + k  ->  wcat[ch][r + k]; bf16 hi / lo planes
+      for (int i = threadIdx.x; i < jn * 8; i += blockDim.x) {
+        const int r = i >> 3, chunk = i & 7;
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          float v2[2];
+#pragma unroll
+          for (int q = 0; q < 2; ++q) {
+            const int kk = chunk * 8 + e * 2 + q;
+            float v = 0.f;
+            if (kk < 2 * KS) {
+              const int ch = kk >= KS ? 1 : 0, k = kk - ch * KS;
+              v = sm.wcat[ch * Wd + r + k];
+            }
+            v2[q] = v;
+          }
+          const float h0 = bf16_round(v2[0]), h1 = bf16_round(v2[1]);
+          hi[e] = pack_bf16x2(h0, h1);
+          lo[e] = pack_bf16x2(v2[0] - h0, v2[1] - h1);
+        }
+        const uint32_t off = sw128_off(r, chunk);
+        *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+      }
+      fence_proxy_async_smem();
+    }
+    __syncthreads();
+    if (active && threadIdx.x == 32) {
+      tc_fence_after();
+      const uint32_t idesc = umma_idesc_bf16(TILE_M, 128);
+      const uint64_t dah = umma_desc_sw128(smem_u32(a_hi)), dal = umma_desc_sw128(smem_u32(a_lo));
+      const uint64_t duh = umma_desc_sw128(smem_u32(sm.u_s)), dul = umma_desc_sw128(smem_u32(sm.u_s + W_TILE_BYTES));
+#pragma unroll
+      for (int k = 0; k < KB / 16; ++k) umma_bf16(tmem_att, dah + (uint64_t)(2 * k), duh + (uint64_t)(2 * k), idesc, (uint32_t)(k > 0));
+#pragma unroll
+      for (int k = 0; k < KB / 16; ++k) umma_bf16(tmem_att, dal + (uint64_t)(2 * k), duh + (uint64_t)(2 * k), idesc, 1u);
+#pragma unroll
+      for (int k = 0; k < KB / 16; ++k) umma_bf16(tmem_att, dah + (uint64_t)(2 * k), dul + (uint64_t)(2 * k), idesc, 1u);
+      umma_commit(sm.att_full);
+    }
+    __syncwarp();
+    PROF(24);                                    // q / window / im2col built, MMAs issued
+    if (active) {
+      wait_bar(sm.att_full, att_par);
+      att_par ^= 1u;
+      tc_fence_after();
+      // thread = (row j = TMEM lane, 64-column half of the attention dimension)
+      const int wq = warp & 3, a0 = (warp >> 2) * 64;
+      const int jl = wq * 32 + lane;
+      const bool valid = jl < jn && (j0 + jl) < L;
+      float part = 0.f;
+      const MT* pmj = pm + ((size_t)b * Tin + (j0 + jl)) * A + a0;
+      float* thj = p.train ? p.th_all + (((size_t)t * p.B + b) * Tin + (j0 + jl)) * A + a0 : nullptr;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_att + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a0 + h * 32), r);
+        tmem_ld_wait();
+        if (valid) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const int ab = h * 32 + g * 8;
+            if (a0 + ab < A) {
+              float pmv[8];
+              ld8<MT>(pmj + ab, pmv);
+              float th[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) {
+                const float s = __uint_as_float(r[g * 8 + e]) + sm.q_s[a0 + ab + e] + pmv[e];
+                th[e] = p.prec == 1 ? tanh_fast(s) : tanh_acc(s);
+                part += sm.v_s[a0 + ab + e] * th[e];
+              }
+              if (thj) {
+                *reinterpret_cast<float4*>(thj + ab) = make_float4(th[0], th[1], th[2], th[3]);
+                *reinterpret_cast<float4*>(thj + ab + 4) = make_float4(th[4], th[5], th[6], th[7]);
+              }
+            }
+          }
+        }
+      }
+      sm.e_part[(warp >> 2) * 128 + jl] = valid ? part : -INFINITY;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (active) {
+      const uint32_t peer_e = map_to_rank(smem_u32(e_buf), (uint32_t)peer);
+      for (int jl = threadIdx.x; jl < jn; jl += blockDim.x) {
+        const float e = sm.e_part[jl] + sm.e_part[128 + jl];      // -inf + -inf = -inf for masked positions
+        e_buf[j0 + jl] = e;
+        st_cluster_f1(peer_e + (uint32_t)((j0 + jl) * 4), e);
+      }
+    }
+    PROF(25);                                    // energies done
+    cluster_sync_all();
+    PROF(26);
+    if (active) {
+      // masked softmax over all encoder positions (both halves compute it redundantly)
+      float mx = -INFINITY;
+      for (int j = threadIdx.x; j < Tin; j += blockDim.x) mx = fmaxf(mx, e_buf[j]);
+      mx = block_reduce2(mx, sm.scr, true);
+      float sum = 0.f;
+      for (int j = threadIdx.x; j < Tin; j += blockDim.x) {
+        const float e = e_buf[j] == -INFINITY ? 0.f : expf(e_buf[j] - mx);
+        sm.w_s[j] = e;
+        sum += e;
+      }
+      sum = block_reduce2(sum, sm.scr, false);
+      const float inv = 1.0f / sum;
+      float wsum = 0.f;
+      for (int j = threadIdx.x; j < Tin; j += blockDim.x) {
+        const float w = sm.w_s[j] * inv;
+        sm.w_s[j] = w;
+        wsum += w;
+      }
+      wsum = block_reduce2(wsum, sm.scr, false);     // also orders the w_s writes before the reads below
+      float* wprev = p.w_prev + (size_t)b * p.ldT;
+      float* wcum = p.w_cum + (size_t)b * p.ldT;
+      float* aout = p.align_out + ((size_t)b * p.n_steps + t) * Tin;
+      for (int jl = threadIdx.x; jl < jn; jl += blockDim.x) {
+        const int j = j0 + jl;
+        const float w = sm.w_s[j];
+        wprev[j] = w;
+        wcum[j] = sm.wcat[Wd + hk + jl] + w;            // cumulative weights before the step live in wcat ch. 1
+        aout[j] = w;
+      }
+      PROF(27);                                  // softmax + weight outputs done
+      // context over this CTA's half of the time-varying columns: 8 columns per thread, warps split j
+      const int E8 = p.E / 8, Eh8 = (E8 + 1) / 2;
+      const int c8_0 = half * Eh8, c8_n = min(E8, c8_0 + Eh8) - c8_0;      // in units of 8 columns
+      const int mult = p.mult;
+      bf16* xc = BFP(p.xctx) + (size_t)b * mult * p.Dp;
+      float* call = p.train ? p.ctx_all + ((size_t)t * p.B + b) * p.D : nullptr;
+      for (int cb = 0; cb < c8_n; cb += 32) {
+        const int c8 = cb + lane;
+        float acc[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+        if (c8 < c8_n) {
+          const MT* mp = mem + (size_t)b * Tin * p.E + (size_t)(c8_0 + c8) * 8;
+          for (int j = warp; j < L; j += 8) {
+            float mv[8];
+            ld8<MT>(mp + (size_t)j * p.E, mv);
+            const float w = sm.w_s[j];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[e] += w * mv[e];
+          }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int e = 0; e < 8; ++e) sm.red_s[warp * 256 + lane * 8 + e] = acc[e];
+        __syncthreads();
+        for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+          const int c8i = cb + (i >> 3);
+          if (c8i < c8_n) {
+            float s = 0.f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) s += sm.red_s[w * 256 + i];
+            const int d = (c8_0 + c8i) * 8 + (i & 7);
+            store_act(xc, d, p.Dp, p.prec, s);
+            if (call) call[d] = s;
+          }
+        }
+      }
+      // time-constant columns: context = const * sum_j w_j  (second CTA of the pair)
+      if (half == 1 || Tin == 1) {
+        for (int i = threadIdx.x; i < p.Cc; i += blockDim.x) {
+          const float val = p.mem_const[(size_t)b * p.Cc + i] * wsum;
+          store_act(xc, p.E + i, p.Dp, p.prec, val);
+          if (call) call[p.E + i] = val;
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+template <int N>
+__global__ void __launch_bounds__(256, 1)
+decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const int S) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  Smem2 sm = carve2<N>(base, S);
+  const int warp = threadIdx.x >> 5;
+  const int rank = (int)cluster_ctarank(), cid = (int)cluster_idx(), ncl = (int)cluster_count();
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) { mbar_init(&sm.ring.full[s], 1); mbar_init(&sm.ring.empty[s], 1); }
+    mbar_init(sm.acc_full, 1);
+    mbar_init(sm.att_full, 1);
+    mbar_init(sm.u_full, 1);
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc(sm.tmem_slot, 512);
+  for (int i = threadIdx.x; i < p.A; i += blockDim.x) sm.v_s[i] = p.v[i];
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *sm.tmem_slot;
+  const uint32_t tmem_att = tmem_base + 256u;
+  if (threadIdx.x == 0) {
+    // the pre-multiplied location filter, hi and lo planes: resident for the whole kernel
+    mbar_expect_tx(sm.u_full, 2 * W_TILE_BYTES);
+    tma_load_3d(sm.u_s, &maps.uloc, sm.u_full, 0, 0, 0);
+    tma_load_3d(sm.u_s + W_TILE_BYTES, &maps.uloc, sm.u_full, KB, 0, 0);
+    wait_bar(sm.u_full, 0);
+  }
+  cluster_sync_all();     // peers' barriers / smem are initialised before any DSMEM traffic
+
+  unsigned int epoch = 0;
+  uint32_t acc_par = 0, att_par = 0, round = 0, eround = 0;
+  const unsigned int nblocks = gridDim.x;
+  int t = 0;
+  for (; t < p.n_steps; ++t) {
+    if (!p.train) {
+      gemm_phase<N>(p, maps, sm, K_PRE1, t, rank, cid, ncl, tmem_base, acc_par, round);
+      grid_sync2(p.barrier, epoch, nblocks);
+      gemm_phase<N>(p, maps, sm, K_PRE2, t, rank, cid, ncl, tmem_base, acc_par, round);
+      grid_sync2(p.barrier, epoch, nblocks);
+    }
+    PROF(0);
+    gemm_phase<N>(p, maps, sm, K_ATT, t, rank, cid, ncl, tmem_base, acc_par, round);
+    PROF(4);
+    grid_sync2(p.barrier, epoch, nblocks);
+    PROF(5);
+    if (p.mem_bf16) attention_phase2<bf16>(p, sm, t, rank, cid, ncl, tmem_att, att_par, eround);
+    else attention_phase2<float>(p, sm, t, rank, cid, ncl, tmem_att, att_par, eround);
+    PROF(6);
+    grid_sync2(p.barrier, epoch, nblocks);
+    PROF(8);
+    gemm_phase<N>(p, maps, sm, K_DEC, t, rank, cid, ncl, tmem_base, acc_par, round);
+    PROF(13);
+    if (!p.train) {
+      grid_sync2(p.barrier, epoch, nblocks);
+      gemm_phase<N>(p, maps, sm, K_PROJ, t, rank, cid, ncl, tmem_base, acc_par, round);
+      grid_sync2(p.barrier, epoch, nblocks);
+      if (__ldcg(p.stop) != 0) { ++t; break; }
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && p.steps_done) *p.steps_done = t;
+  tc_fence_before();
+  cluster_sync_all();     // no CTA exits while a peer may still write into its shared memory
+  if (warp == 2) tmem_dealloc(tmem_base, 512);
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+template <int N>
+static int launch_fwd2(const Fwd2Maps& maps, const DecFwd& p, int max_clusters_wanted, cudaStream_t st) {
+  const size_t stage = (size_t)W_TILE_BYTES + (size_t)N * KB * 2;
+  const size_t fixed = fwd2_fixed_bytes<N>() + 1024;
+  int S = (int)((227 * 1024 - fixed) / stage);
+  if (S > 12) S = 12;
+  GTN_REQUIRE(S >= 2, "decoder forward: not enough shared memory for the TMA ring (N=%d)", N);
+  const size_t smem = fixed + (size_t)S * stage;
+  auto kern = decoder_fwd2_kernel<N>;
+  GTN_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(256);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attrs[2];
+  attrs[0].id = cudaLaunchAttributeClusterDimension;
+  attrs[0].val.clusterDim.x = CL; attrs[0].val.clusterDim.y = 1; attrs[0].val.clusterDim.z = 1;
+  attrs[1].id = cudaLaunchAttributeCooperative;
+  attrs[1].val.cooperative = 1;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 1;
+  cfg.gridDim = dim3(CL * max_clusters_wanted);
+  int max_cl = 0;
+  GTN_CUDA_OK(cudaOccupancyMaxActiveClusters(&max_cl, kern, &cfg));
+  GTN_REQUIRE(max_cl >= 1, "decoder forward: no cluster of %d CTAs fits on this device", CL);
+  const int ncl = max_cl < max_clusters_wanted ? max_cl : max_clusters_wanted;
+  cfg.gridDim = dim3(CL * ncl);
+  cfg.numAttrs = 2;
+  GTN_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, maps, p, S));
+  count_launch();
+  return 0;
+}
+
+int make_tma_map_3d(CUtensorMap* out, const void* base, long long d0, long long d1, long long d2, long long stride1_elems,
+                    long long stride2_elems, int box1);
+
+}  // namespace gtn
+
+using namespace gtn;
+
+extern "C" int gtn_decoder_forward2(const gtn_decoder_fwd_params* hp, void* stream) {
+  GTN_REQUIRE(hp != nullptr, "null params");
+  DecFwd p = *hp;
+  GTN_REQUIRE(p.prec == 1 || p.prec == 3, "prec must be 1 (bf16) or 3 (fp32 via 3 bf16 planes)");
+  p.mult = p.prec == 1 ? 1 : 6;
+  GTN_REQUIRE(p.Ha % 32 == 0 && p.Hd % 32 == 0, "LSTM widths must be multiples of 32");
+  GTN_REQUIRE(p.Hap % 64 == 0 && p.Hdp % 64 == 0 && p.Dp % 64 == 0 && p.Pp % 64 == 0 && p.NMp % 64 == 0,
+              "padded K segments must be multiples of 64");
+  GTN_REQUIRE(p.Hap >= p.Ha && p.Hdp >= p.Hd && p.Dp >= p.D && p.Pp >= p.P && p.NMp >= p.NM, "padded dims too small");
+  GTN_REQUIRE(p.D == p.E + p.Cc && p.E % 8 == 0, "D must equal E + Cc and E must be a multiple of 8");
+  GTN_REQUIRE(p.KS % 2 == 1 && 2 * p.KS <= 64, "location kernel size must be odd and <= 31");
+  GTN_REQUIRE(p.A <= 128 && p.A % 8 == 0, "attention_dim must be a multiple of 8 and <= 128");
+  GTN_REQUIRE(p.Tin >= 1 && p.Tin <= TIN_MAX, "T_in must be in [1, %d]", TIN_MAX);
+  GTN_REQUIRE(p.B >= 1 && p.B <= 256 && p.n_steps >= 1, "batch must be in [1, 256]");
+  GTN_REQUIRE(p.NM + 1 <= TILE_M, "n_mel + 1 must fit one 128-row tile");
+  GTN_REQUIRE(p.w_att2 && p.w_dec2 && p.u_loc && p.wq_t, "second-generation weight packs missing");
+  auto thr = [](float pr) -> unsigned { double t = (double)pr * 4294967296.0; return t >= 4294967295.0 ? 0xFFFFFFFFu : (unsigned)t; };
+  p.thr_att = p.use_dropout ? thr(p.p_att) : 0u;
+  p.thr_dec = p.use_dropout ? thr(p.p_dec) : 0u;
+  const int N = p.B <= 32 ? 32 : (p.B <= 64 ? 64 : (p.B <= 128 ? 128 : 256));
+  const int m = p.mult;
+  const long long Ka = (long long)m * (p.Pp + p.Dp + p.Hap), Kd = (long long)m * (p.Hap + p.Dp + p.Hdp);
+  Fwd2Maps maps;
+  int rc = 0;
+  rc |= make_tma_map_3d(&maps.w_att, p.w_att2, Ka, 4 * p.Ha, 1, Ka, 0, TILE_M);
+  rc |= make_tma_map_3d(&maps.w_dec, p.w_dec2, Kd, 4 * p.Hd, 1, Kd, 0, TILE_M);
+  rc |= make_tma_map_3d(&maps.uloc, p.u_loc, 2 * KB, p.A, 1, 2 * KB, 0, TILE_M);
+  rc |= make_tma_map_3d(&maps.ctx, p.xctx, (long long)m * p.Dp, p.B, 1, (long long)m * p.Dp, 0, N);
+  rc |= make_tma_map_3d(&maps.ha, p.xh_a, (long long)m * p.Hap, p.B, 2, (long long)m * p.Hap, (long long)p.B * m * p.Hap, N);
+  rc |= make_tma_map_3d(&maps.hd, p.xh_d, (long long)m * p.Hdp, p.B, 2, (long long)m * p.Hdp, (long long)p.B * m * p.Hdp, N);
+  if (p.train) {
+    rc |= make_tma_map_3d(&maps.pre, p.pre_all, (long long)m * p.Pp, p.B, p.n_steps + 1, (long long)m * p.Pp,
+                          (long long)p.B * m * p.Pp, N);
+    maps.w_pre1 = maps.w_pre2 = maps.w_proj = maps.w_att;
+    maps.xmel = maps.xp1 = maps.xp2 = maps.ctx;
+  } else {
+    const long long Kp = (long long)m * (p.Hdp + p.Dp);
+    rc |= make_tma_map_3d(&maps.w_pre1, p.w_pre1, (long long)m * p.NMp, p.P, 1, (long long)m * p.NMp, 0, TILE_M);
+    rc |= make_tma_map_3d(&maps.w_pre2, p.w_pre2, (long long)m * p.Pp, p.P, 1, (long long)m * p.Pp, 0, TILE_M);
+    rc |= make_tma_map_3d(&maps.w_proj, p.w_proj, Kp, p.NM + 1, 1, Kp, 0, TILE_M);
+    rc |= make_tma_map_3d(&maps.xmel, p.xmel, (long long)m * p.NMp, p.B, 1, (long long)m * p.NMp, 0, N);
+    rc |= make_tma_map_3d(&maps.xp1, p.xp1, (long long)m * p.Pp, p.B, 1, (long long)m * p.Pp, 0, N);
+    rc |= make_tma_map_3d(&maps.xp2, p.xp2, (long long)m * p.Pp, p.B, 1, (long long)m * p.Pp, 0, N);
+    maps.pre = maps.xp2;
+  }
+  if (rc) return rc;
+  const int want = (p.Ha > p.Hd ? p.Ha : p.Hd) / 32;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (N == 32) return launch_fwd2<32>(maps, p, want, st);
+  if (N == 64) return launch_fwd2<64>(maps, p, want, st);
+  if (N == 128) return launch_fwd2<128>(maps, p, want, st);
+  return launch_fwd2<256>(maps, p, want, st);
+}

@@ -328,6 +328,11 @@ static int make_map(CUtensorMap* out, const void* base, long long d0, long long 
   return 0;
 }
 
+int make_tma_map_3d(CUtensorMap* out, const void* base, long long d0, long long d1, long long d2, long long stride1_elems,
+                    long long stride2_elems, int box1) {
+  return make_map(out, base, d0, d1, d2, stride1_elems, stride2_elems, box1);
+}
+
 template <int BN>
 static int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, GemmKernelParams kp, dim3 grid, cudaStream_t st) {
   int stages = kp.num_k_blocks < 2 ? 2 : (kp.num_k_blocks > 6 ? 6 : kp.num_k_blocks);

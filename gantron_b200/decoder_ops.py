@@ -32,15 +32,15 @@ class DecoderDims:
     d_mem: int          # all columns (encoder + speaker + emotion + noise)
 
     @property
-    def Pp(self): return pad_to(self.prenet, 32)
+    def Pp(self): return pad_to(self.prenet, 64)
     @property
-    def Hap(self): return pad_to(self.att_rnn, 32)
+    def Hap(self): return pad_to(self.att_rnn, 64)
     @property
-    def Hdp(self): return pad_to(self.dec_rnn, 32)
+    def Hdp(self): return pad_to(self.dec_rnn, 64)
     @property
-    def Dp(self): return pad_to(self.d_mem, 32)
+    def Dp(self): return pad_to(self.d_mem, 64)
     @property
-    def NMp(self): return pad_to(self.n_mel, 32)
+    def NMp(self): return pad_to(self.n_mel, 64)
 
 
 class PackedDecoder:
@@ -95,6 +95,17 @@ class PackedDecoder:
         self.wconv = f(P["wconv"]).contiguous()
         self.wdense = f(P["wdense"]).contiguous()
         self.wmem = f(P["wmem"]).contiguous()
+        # ---- second-generation (clustered tcgen05) kernel packs ----
+        # LSTM weight rows regrouped per 32-unit tile: row tile*128 + gate*32 + u  <-  gate*H + 32*tile + u
+        self.w_att2 = _tile_rows(self.w_att, d.att_rnn)
+        self.w_dec2 = _tile_rows(self.w_dec, d.dec_rnn)
+        # location conv (F,2,KS) and dense (A,F) pre-multiplied: U[a][ch*KS + k] = sum_c dense[a][c] conv[c][ch][k]
+        U = self.wdense @ self.wconv.reshape(d.loc_filters, 2 * d.loc_kernel)
+        Up = torch.zeros(d.att_dim, 64, device=U.device)
+        Up[:, :2 * d.loc_kernel] = U
+        hi = Up.to(BF16)
+        self.u_loc = torch.cat((hi, (Up - hi.float()).to(BF16)), 1).contiguous()      # [A][hi 64 | lo 64]
+        self.wq_t = self.wq.t().contiguous()                                           # [Ha][A]
 
 
 def linear_nt(x: torch.Tensor, w: torch.Tensor, prec: int, bias: Optional[torch.Tensor] = None,
@@ -110,8 +121,19 @@ def linear_nt(x: torch.Tensor, w: torch.Tensor, prec: int, bias: Optional[torch.
     return out
 
 
-class FwdResult:
-    pass
+def _tile_rows(w: torch.Tensor, H: int) -> torch.Tensor:
+    K = w.shape[1]
+    return w.view(4, H // 32, 32, K).permute(1, 0, 2, 3).reshape(4 * H, K).contiguous()
+
+
+def decoder_version() -> int:
+    """Which persistent decoder kernel generation to launch (2 = clustered tcgen05, the default)."""
+    import os
+    return int(os.environ.get("GANTRON_B200_DECODER", "2"))
+
+
+TRAIN_FWD2 = False     # dev switch until the second-generation backward kernel lands
+PROF_BUFFER = None     # dev tool: int64 [16*32] device tensor receiving clock64() stamps of CTA 0 (tools/time_infer.py)
 
 
 def _fill_common(p: _lib.DecoderFwdParams, d: DecoderDims, pk: PackedDecoder, B: int, Tin: int, n_steps: int,
@@ -121,7 +143,9 @@ def _fill_common(p: _lib.DecoderFwdParams, d: DecoderDims, pk: PackedDecoder, B:
     p.Ha, p.Hap, p.Hd, p.Hdp = d.att_rnn, d.Hap, d.dec_rnn, d.Hdp
     p.P, p.Pp, p.A, p.F, p.KS, p.NM, p.NMp = d.prenet, d.Pp, d.att_dim, d.loc_filters, d.loc_kernel, d.n_mel, d.NMp
     p.prec = prec
-    for name in ("w_att", "w_dec", "w_proj", "w_pre1", "w_pre2", "b_att", "b_dec", "b_proj", "wq", "v", "wconv", "wdense"):
+    p.prof = PROF_BUFFER.data_ptr() if PROF_BUFFER is not None else None
+    for name in ("w_att", "w_dec", "w_proj", "w_pre1", "w_pre2", "b_att", "b_dec", "b_proj", "wq", "v", "wconv", "wdense",
+                 "w_att2", "w_dec2", "u_loc", "wq_t"):
         setattr(p, name, getattr(pk, name).data_ptr())
 
 
@@ -181,7 +205,10 @@ def decoder_inference(pk: PackedDecoder, memory: torch.Tensor, *, max_steps: int
     p.mem_enc, p.pm, p.mem_const = mem_enc.data_ptr(), pm.data_ptr(), mem_const.data_ptr()
     p.lengths = None
     p.align_out, p.mel_out, p.gate_out = align.data_ptr(), mel.data_ptr(), gate.data_ptr()
-    _lib.check(_lib.load().gtn_decoder_forward(C.byref(p), _lib.stream()), "gtn_decoder_forward")
+    if decoder_version() >= 2:
+        _lib.check(_lib.load().gtn_decoder_forward2(C.byref(p), _lib.stream()), "gtn_decoder_forward2")
+    else:
+        _lib.check(_lib.load().gtn_decoder_forward(C.byref(p), _lib.stream()), "gtn_decoder_forward")
     steps = int(st["steps_done"][0].item())          # the single host sync of the whole decode
     lengths = st["lengths_out"].clone()
     lengths[st["done"] == 0] = steps
@@ -326,7 +353,10 @@ class _DecoderTrainFn(torch.autograd.Function):
         p.ctx_all = sv["ctx_buf"][1:].data_ptr()
         p.q_all, p.th_all, p.f_all, p.cum_all = (sv["q_all"].data_ptr(), sv["th_all"].data_ptr(), sv["f_all"].data_ptr(),
                                                  sv["cum_all"].data_ptr())
-        _lib.check(_lib.load().gtn_decoder_forward(C.byref(p), _lib.stream()), "gtn_decoder_forward")
+        if TRAIN_FWD2:
+            _lib.check(_lib.load().gtn_decoder_forward2(C.byref(p), _lib.stream()), "gtn_decoder_forward2")
+        else:
+            _lib.check(_lib.load().gtn_decoder_forward(C.byref(p), _lib.stream()), "gtn_decoder_forward")
 
         # ---- deferred mel/gate projection over all frames (model.py:411-416): batched over b so the output is
         # written directly as [B][T][n_mel+1] (channels-last); the API tensors are views of it

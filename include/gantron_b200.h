@@ -186,9 +186,18 @@ typedef struct gtn_decoder_fwd_params {
   float *th_all;                        /* [T][B][Tin][A]  tanh(q + loc + processed_memory) */
   float *f_all;                         /* [T][B][Tin][F]  location-conv outputs */
   float *cum_all;                       /* [T][B][Tin]     cumulative weights BEFORE the step (conv input ch. 1) */
+  /* second-generation (clustered tcgen05) kernel: gtn_decoder_forward2 */
+  const void *w_att2, *w_dec2;          /* w_att / w_dec with rows permuted per 32-unit tile: row tile*128 + gate*32 + u */
+  const void *u_loc;                    /* bf16 [A][128]: location conv x dense pre-multiplied, U[a][ch*KS+k], hi | lo planes */
+  const float *wq_t;                    /* [Ha][A] = query_layer weight transposed */
+  long long *prof;                      /* optional [16][32] clock64() stamps of CTA 0 for the first 16 frames (NULL = off) */
 } gtn_decoder_fwd_params;
 
 int gtn_decoder_forward(const gtn_decoder_fwd_params* params, void* stream);
+/* Same contract, second generation: clusters of 4 CTAs split K of every per-frame GEMM and run it on tcgen05 with
+ * TMA-fed operands (gtn_decoder_fwd2.cu); requires all K pads to be multiples of 64 and qpart sized [Ha/32][B][A].
+ * Does not write f_all (the location filter is pre-multiplied; the backward pass works on U). */
+int gtn_decoder_forward2(const gtn_decoder_fwd_params* params, void* stream);
 
 /* ---- persistent cooperative decoder, backward through time (gtn_decoder_bwd.cu) -----------------
  * Replaces autograd's replay of the ~22k-node tape of model.py:444-449 (BPTT over T frames) with one
