@@ -63,6 +63,8 @@ SIGNATURES = {
     "gtn_sizeof": (c_i, [c_i]),
     "gtn_decoder_bwd_grid": (c_i, []),
     "gtn_decoder_backward": (c_i, [c_p, c_p]),
+    "gtn_decoder_bwd2_grid": (c_i, [c_i, c_i, c_i, c_i]),
+    "gtn_decoder_backward2": (c_i, [c_p, c_p]),
 }
 
 
@@ -84,7 +86,8 @@ class DecoderFwdParams(C.Structure):
                               "align_out", "mel_out", "gate_out",
                               "gates_a", "c_a_all", "h_a_all", "gates_d", "c_d_all", "h_d_all", "ctx_all",
                               "q_all", "th_all", "f_all", "cum_all",
-                              "w_att2", "w_dec2", "u_loc", "wq_t", "prof")]
+                              "w_att2", "w_dec2", "u_loc", "wq_t", "prof", "gbias_a", "gbias_d", "pbias")]
+        + [("Ep", c_i), ("reserved0", c_i)]
     )
 
 
@@ -101,6 +104,20 @@ class DecoderBwdParams(C.Structure):
                               "dga_all", "dgd_all", "dq_all", "dpre_all", "dctx_all", "dpm",
                               "dv_part", "dwd_part", "dwc_part")]
         + [("grid", c_i)]
+    )
+
+
+class DecoderBwd2Params(C.Structure):
+    """Mirror of `gtn_decoder_bwd2_params` (include/gantron_b200.h)."""
+    _fields_ = (
+        [(n, c_i) for n in ("B", "Tin", "ldT", "T", "E", "Ep", "D", "Ha", "Hd", "A", "KS", "prec", "mult",
+                            "use_dropout", "mem_bf16", "grid")]
+        + [("p_att", c_f), ("p_dec", c_f), ("thr_att", c_u), ("thr_dec", c_u), ("seed", c_ull)]
+        + [(n, c_p) for n in ("wT_att2", "wT_dec2", "ut_loc", "wq_t", "v", "mem_enc", "lengths",
+                              "gates_a", "c_a_all", "gates_d", "c_d_all", "align", "th_all", "cum_all",
+                              "dproj_all", "dalign", "xdg_a", "xdg_d", "carry_ha", "dha_dec", "dc_a", "dc_d",
+                              "dctx_att", "dctx_dec", "dwprev", "dcum", "dq_sum", "barrier",
+                              "dga_all", "dgd_all", "dq_all", "dctx_all", "dpm", "dv_part", "dU_part")]
     )
 
 

@@ -71,14 +71,13 @@ GTN_DEVICE void grid_sync2(unsigned int* counter, unsigned int& epoch, unsigned 
   __syncthreads();
   epoch += nblocks;
   if (threadIdx.x == 0) {
+    // red.release.gpu is cumulative over everything this CTA stored before the bar.sync above; ld.acquire.gpu pairs with it
     fence_proxy_async();
-    __threadfence();
     red_release_add(counter, 1u);
     long long t0 = clock64();
     while (ld_acquire_u32(counter) < epoch) {
       if (clock64() - t0 > 20000000000LL) __trap();
     }
-    __threadfence();
     fence_proxy_async();
   }
   __syncthreads();
@@ -93,6 +92,62 @@ GTN_DEVICE float tanh_fast(float x) {
 // swizzled byte offset of the 16-byte chunk `chunk` (8 bf16) of row `r` inside a K-major SWIZZLE_128B tile
 GTN_DEVICE uint32_t sw128_off(int r, int chunk) {
   return (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((chunk ^ (r & 7)) << 4));
+}
+
+// im2col tile of the location conv input for rows r < jn: K index kk = ch*KS + k  ->  wcat[ch*Wd + r + k]; written as
+// two K-major SWIZZLE_128B bf16 tiles (hi plane, lo = residual plane).  Doubles as an MN-major operand with K = rows.
+GTN_DEVICE void build_im2col(const float* wcat, int Wd, int KS, int jn, uint8_t* a_hi, uint8_t* a_lo) {
+  for (int i = threadIdx.x; i < jn * 8; i += blockDim.x) {
+    const int r = i >> 3, chunk = i & 7;
+    uint32_t hi[4], lo[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      float v2[2];
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int kk = chunk * 8 + e * 2 + q;
+        float v = 0.f;
+        if (kk < 2 * KS) {
+          const int ch = kk >= KS ? 1 : 0, k = kk - ch * KS;
+          v = wcat[ch * Wd + r + k];
+        }
+        v2[q] = v;
+      }
+      const float h0 = bf16_round(v2[0]), h1 = bf16_round(v2[1]);
+      hi[e] = pack_bf16x2(h0, h1);
+      lo[e] = pack_bf16x2(v2[0] - h0, v2[1] - h1);
+    }
+    const uint32_t off = sw128_off(r, chunk);
+    *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+  }
+}
+
+// MN-major SWIZZLE_128B descriptor with an explicit distance between consecutive 64-element MN slices
+GTN_DEVICE uint64_t umma_desc_sw128_mn_lbo(uint32_t smem_addr_bytes, uint32_t lbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr_bytes & 0x3FFFFu) >> 4);
+  d |= (uint64_t)(lbo_bytes >> 4) << 16;
+  d |= (uint64_t)(1024u >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+// Sum v[c] over the 32 lanes of a warp for 64 columns; on return lane l holds the totals of columns 2l and 2l+1
+// in v[0], v[1] (butterfly reduce-scatter: 62 shuffles instead of 320).
+GTN_DEVICE void warp_reduce_scatter64(float (&v)[64]) {
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int off = 16, n = 32; off >= 1; off >>= 1, n >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < n; ++i) {
+      const float keep = up ? v[i + n] : v[i];
+      const float send = up ? v[i] : v[i + n];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
 }
 
 // ---- ring pipeline state (meaningful in the producer / MMA threads only) ----

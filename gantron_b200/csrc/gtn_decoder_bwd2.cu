@@ -1,0 +1,709 @@
+// Persistent clustered decoder kernel, backward through time (second generation).  Reverse of decode()
+// (reference model.py:378-417) for t = T-1 .. 0, replacing autograd's replay of the per-frame tape built by
+// model.py:444-449.  Same machinery as gtn_decoder_fwd2.cu (gtn_decoder2.cuh): clusters of 4 CTAs split K of
+// every per-frame GEMM, operands arrive by TMA, tcgen05.mma accumulates in TMEM, partial tiles are exchanged
+// through distributed shared memory.
+//
+// Per frame, three grid-synchronised phases:
+//   P1  data-gradient GEMMs, one 128-row tile per cluster:
+//         dX_dec = W_dec^T . dGates_dec(t)   rows [h_att | ctx_enc | h_dec]     (model.py:406-407)
+//         dX_att = W_att^T . dGates_att(t+1) rows [ctx_enc | h_att]             (model.py:391-392)
+//       the h_dec rows feed the decoder LSTM cell backward of frame t-1 directly in the epilogue; the prenet rows and
+//       the time-constant context columns are not computed per frame (deferred to K = T*B GEMMs on the host).
+//   P2  attention backward, one CTA pair per sequence: context bmm, softmax, e = v.tanh(q + loc + pm), and the
+//       pre-multiplied location filter U: d[prev | cum] = dth . U and dU += dth^T . im2col both on tcgen05, reusing
+//       the SAME shared-memory tiles (a K-major tile with rows = positions is an MN-major tile with K = positions);
+//       dU stays in TMEM for the whole pass                                      (model.py:27-31,62-89,396-403)
+//   P3  query backward (Wq^T dq) + attention LSTM cell backward, spread over all CTAs by hidden unit (model.py:391-394)
+// All WEIGHT gradients are deferred: the kernel stores per-frame gate / query gradients and the host issues a
+// handful of K = T*B tcgen05 GEMMs afterwards (gtn_gemm_tn_bf16).
+#include "gtn_decoder2.cuh"
+#include "gtn_internal.h"
+#include "../../include/gantron_b200.h"
+
+namespace gtn {
+
+typedef gtn_decoder_bwd2_params DecBwd2;
+#define BFP(x) (reinterpret_cast<bf16*>(const_cast<void*>(static_cast<const void*>(x))))
+
+struct Bwd2Maps {
+  CUtensorMap wT_att, wT_dec, ut;      // weights (A operands) and U^T (B operand of d[prev|cum] = dth . U)
+  CUtensorMap xdg_a, xdg_d;            // gate gradients as X operands
+};
+
+static constexpr int B2_TIN_MAX = 256;
+static constexpr int B2_JH = 128;
+static constexpr int P2_RING_BYTES = 6 * W_TILE_BYTES;     // dth hi (2 blocks) + dth lo (2) + im2col hi + lo
+
+struct SmemB {
+  Ring ring;
+  float* recv;         // [2][4][128][NC4]   (P2: G_s [128][64] swizzled)
+  uint8_t* ut_s;       // [4][8 KB]: U^T hi a<64, hi a>=64, lo a<64, lo a>=64  (N = 64 rows kk, K = 64 a)
+  float* dctx_s;       // [E <= 1024]
+  float* w_s;          // [Tin]
+  float* dw_s;         // [Tin]   dw, then de
+  float* wcat;         // [2][JH + KS - 1]
+  float* dwc_s;        // [2][JH + KS - 1]   d wcat (own window)
+  float* halo_s;       // [2][2][KS]         halo contributions received from the peer
+  float* v_s;          // [128]
+  float* part_s;       // [8][64]
+  float* dqp_s;        // [2][128]           dq partial: own, peer
+  float* dv_acc;       // [128]
+  float* dot_s;        // [4]                softmax dot partial: own, peer (double buffered)
+  float* scr;          // [64]
+  uint64_t* acc_full;
+  uint64_t* g_full;
+  uint64_t* ut_full;
+  uint32_t* tmem_slot;
+};
+
+template <int N>
+__host__ __device__ constexpr size_t bwd2_fixed_bytes() {
+  constexpr int NC4 = (N < 64 ? N : 64) / 4;
+  constexpr size_t recv_b = (size_t)2 * 4 * TILE_M * NC4 * 4;
+  return (recv_b < 32768 ? 32768 : recv_b) + 4 * 8192 +
+         (size_t)(1024 + 2 * B2_TIN_MAX + 4 * (B2_JH + 62) + 4 * 32 + 128 + 8 * 64 + 256 + 128 + 4 + 64) * 4 + 64 * 8 + 64;
+}
+
+template <int N>
+GTN_DEVICE SmemB carveB(uint8_t* base, int S) {
+  constexpr int NC4 = (N < 64 ? N : 64) / 4;
+  constexpr size_t recv_b = (size_t)2 * 4 * TILE_M * NC4 * 4;
+  SmemB m;
+  m.ring.base = base;
+  m.ring.S = S;
+  m.ring.stage_bytes = W_TILE_BYTES + N * KB * 2;
+  m.ring.prod_it = m.ring.mma_it = 0;
+  size_t ring_b = (size_t)S * m.ring.stage_bytes;
+  if (ring_b < (size_t)P2_RING_BYTES) ring_b = P2_RING_BYTES;
+  uint8_t* p = base + ring_b;
+  m.recv = reinterpret_cast<float*>(p); p += (recv_b < 32768 ? 32768 : recv_b);
+  m.ut_s = p; p += 4 * 8192;
+  float* f = reinterpret_cast<float*>(p);
+  m.dctx_s = f; f += 1024;
+  m.w_s = f; f += B2_TIN_MAX;
+  m.dw_s = f; f += B2_TIN_MAX;
+  m.wcat = f; f += 2 * (B2_JH + 62);
+  m.dwc_s = f; f += 2 * (B2_JH + 62);
+  m.halo_s = f; f += 4 * 32;
+  m.v_s = f; f += 128;
+  m.part_s = f; f += 8 * 64;
+  m.dqp_s = f; f += 256;
+  m.dv_acc = f; f += 128;
+  m.dot_s = f; f += 4;
+  m.scr = f; f += 64;
+  uint64_t* b = reinterpret_cast<uint64_t*>(f);
+  m.ring.full = b; b += 16;
+  m.ring.empty = b; b += 16;
+  m.acc_full = b++;
+  m.g_full = b++;
+  m.ut_full = b++;
+  m.tmem_slot = reinterpret_cast<uint32_t*>(b + 1);
+  return m;
+}
+
+GTN_DEVICE float block_sum2(float v, float* scr) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  v = warp_sum(v);
+  __syncthreads();
+  if (lane == 0) scr[warp] = v;
+  __syncthreads();
+  float r = 0.f;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) r += scr[w];
+  return r;
+}
+
+// LSTM cell backward for one (b, unit) of frame t: dh = gradient w.r.t. the (post-dropout) hidden output.
+// Writes the four pre-activation gate gradients (gate-major K order g*H + unit) as GEMM operand and as fp32 save.
+GTN_DEVICE void cell_backward2(const DecBwd2& p, int t, int b, int unit, int H, float dh, const float* gates_all,
+                               const float* c_all, float* dc_carry, float* dg_all, bf16* xdg, unsigned site, unsigned thr,
+                               float pdrop) {
+  const size_t ci = (size_t)b * H + unit;
+  if (p.use_dropout && thr != 0u) {
+    const uint32_t bits = philox_bits(p.seed, site, (uint32_t)t, (uint32_t)ci);
+    dh = bits >= thr ? dh * (1.0f / (1.0f - pdrop)) : 0.f;
+  }
+  const size_t cell = ((size_t)t * p.B + b) * H + unit;
+  const float4 g = __ldg(reinterpret_cast<const float4*>(gates_all) + cell);      // i, f, g, o
+  const float c = __ldg(&c_all[cell]);
+  const float cprev = t > 0 ? __ldg(&c_all[cell - (size_t)p.B * H]) : 0.f;
+  const float tc = tanh_acc(c);
+  const float d_o = dh * tc;
+  const float dc = dh * g.w * (1.f - tc * tc) + dc_carry[ci];
+  dc_carry[ci] = dc * g.y;
+  const float dgi = dc * g.z * g.x * (1.f - g.x);
+  const float dgf = dc * cprev * g.y * (1.f - g.y);
+  const float dgg = dc * g.x * (1.f - g.z * g.z);
+  const float dgo = d_o * g.w * (1.f - g.w);
+  const size_t g0 = ((size_t)t * p.B + b) * 4 * H + unit;
+  dg_all[g0] = dgi; dg_all[g0 + H] = dgf; dg_all[g0 + 2 * H] = dgg; dg_all[g0 + 3 * H] = dgo;
+  bf16* xr = xdg + (size_t)b * p.mult * 4 * H;
+  store_act(xr, unit, 4 * H, p.prec, dgi);
+  store_act(xr, H + unit, 4 * H, p.prec, dgf);
+  store_act(xr, 2 * H + unit, 4 * H, p.prec, dgg);
+  store_act(xr, 3 * H + unit, 4 * H, p.prec, dgo);
+}
+
+// decoder LSTM cell backward of frame t (prologue only: frame T-1 has no recurrent carry), spread over the grid
+GTN_DEVICE void dec_cell_prologue(const DecBwd2& p, int t) {
+  const int n = p.B * p.Hd;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
+    const int b = idx / p.Hd, u = idx - b * p.Hd;
+    const float dh = p.dproj_all[((size_t)t * p.B + b) * (p.Hd + p.D) + u];
+    cell_backward2(p, t, b, u, p.Hd, dh, p.gates_d, p.c_d_all, p.dc_d, p.dgd_all, BFP(p.xdg_d), 4u, p.thr_dec, p.p_dec);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// P1: data-gradient GEMM tiles
+// ------------------------------------------------------------------------------------------------
+template <int N>
+GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, int t, int it, int rank, int cid, int ncl,
+                             uint32_t tmem_base, uint32_t& acc_par, uint32_t& round) {
+  constexpr int CH = N < 64 ? N : 64;
+  constexpr int NC4 = CH / 4;
+  const int R_dec = p.Ha + p.E + p.Hd, R_att = p.E + p.Ha;
+  const int nD = (R_dec + TILE_M - 1) / TILE_M;
+  const int nA = (t + 1 < p.T) ? (R_att + TILE_M - 1) / TILE_M : 0;
+  const int cur = it & 1, nxt = cur ^ 1;
+  for (int tile = cid; tile < nD + nA; tile += ncl) {
+    const bool dec = tile < nD;
+    const int row0 = (dec ? tile : tile - nD) * TILE_M;
+    GemmJob job;
+    job.wmap = dec ? &maps.wT_dec : &maps.wT_att;
+    job.row0 = row0;
+    job.nseg = 1;
+    job.seg[0] = dec ? XSeg{&maps.xdg_d, p.mult * 4 * p.Hd / KB, cur} : XSeg{&maps.xdg_a, p.mult * 4 * p.Ha / KB, 0};
+    job.nkb = job.seg[0].nkb;
+    const bool has_work = gemm_issue<N>(job, sm.ring, tmem_base, sm.acc_full, rank);
+    __syncwarp();
+    if ((threadIdx.x >> 5) >= 4 && has_work) {
+      wait_bar(sm.acc_full, acc_par);
+      tc_fence_after();
+    }
+    if (has_work) acc_par ^= 1u;
+    for (int c0 = 0; c0 < N; c0 += CH) {
+      float* recv = sm.recv + (size_t)(round & 1u) * 4 * TILE_M * NC4;
+      ++round;
+      exchange_chunk<CH>(has_work, tmem_base, c0, recv, rank);
+      const int bbase = c0 + rank * NC4;
+      for (int idx = threadIdx.x; idx < TILE_M * NC4; idx += blockDim.x) {
+        const int bl = idx % NC4, r = idx / NC4, b = bbase + bl, row = row0 + r;
+        if (b >= p.B) continue;
+        const float val = recv_sum<NC4>(recv, r, bl);
+        if (dec) {
+          if (row < p.Ha) p.dha_dec[(size_t)b * p.Ha + row] = val;
+          else if (row < p.Ha + p.E) p.dctx_dec[(size_t)b * p.Ep + row - p.Ha] = val;
+          else if (row < R_dec) {
+            if (t > 0) {      // fused decoder LSTM cell backward of frame t-1
+              const int u = row - p.Ha - p.E;
+              const float dh = val + p.dproj_all[((size_t)(t - 1) * p.B + b) * (p.Hd + p.D) + u];
+              cell_backward2(p, t - 1, b, u, p.Hd, dh, p.gates_d, p.c_d_all, p.dc_d, p.dgd_all,
+                             BFP(p.xdg_d) + (size_t)nxt * p.B * p.mult * 4 * p.Hd, 4u, p.thr_dec, p.p_dec);
+            }
+          }
+        } else {
+          if (row < p.E) p.dctx_att[(size_t)b * p.Ep + row] = val;
+          else if (row < R_att) p.carry_ha[(size_t)b * p.Ha + row - p.E] = val;
+        }
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// P2: attention backward, one CTA pair per sequence
+// ------------------------------------------------------------------------------------------------
+template <typename MT>
+GTN_DEVICE void ld8b(const MT* p, float (&o)[8]);
+template <>
+GTN_DEVICE void ld8b<float>(const float* p, float (&o)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+}
+template <>
+GTN_DEVICE void ld8b<bf16>(const bf16* p, float (&o)[8]) {
+  const uint4 q = __ldg(reinterpret_cast<const uint4*>(p));
+  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    o[2 * i] = __uint_as_float(w[i] << 16);
+    o[2 * i + 1] = __uint_as_float(w[i] & 0xFFFF0000u);
+  }
+}
+
+template <typename MT>
+GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, bool first, int rank, int cid, int ncl, uint32_t tmem_g,
+                                uint32_t tmem_du, uint32_t& g_par, uint32_t& xround) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int Tin = p.Tin, A = p.A, KS = p.KS, hk = (p.KS - 1) / 2, E = p.E;
+  const int half = rank & 1, peer = rank ^ 1;
+  const int pair = cid * 2 + (rank >> 1), npairs = ncl * 2;
+  const int JH = (Tin + 1) / 2;
+  const int j0 = half * JH, jn = min(Tin, j0 + JH) - j0;
+  const int Wd = jn + KS - 1;
+  const MT* mem = reinterpret_cast<const MT*>(p.mem_enc);
+  uint8_t* dth_hi = sm.ring.base;                        // 2 blocks of [128 rows j][64 a] (a < 64, a >= 64)
+  uint8_t* dth_lo = sm.ring.base + 2 * W_TILE_BYTES;
+  uint8_t* im_hi = sm.ring.base + 4 * W_TILE_BYTES;
+  uint8_t* im_lo = sm.ring.base + 5 * W_TILE_BYTES;
+  float* G_s = sm.recv;                                  // [128][64], column index XOR (row & 31)
+  const int niter = (p.B + npairs - 1) / npairs;
+  for (int itb = 0; itb < niter; ++itb) {
+    const int b = pair + itb * npairs;
+    const bool active = b < p.B;
+    const int L = active ? (p.lengths ? min(p.lengths[b], Tin) : Tin) : 0;
+    const size_t tb = (size_t)t * p.B + b, bt = (size_t)b * p.T + t;
+    const uint32_t xb = xround & 1u;
+    ++xround;
+    if (active) {
+      for (int j = threadIdx.x; j < Tin; j += blockDim.x) sm.w_s[j] = p.align[bt * Tin + j];
+      for (int d = threadIdx.x; d < E; d += blockDim.x) {
+        const float val = p.dproj_all[tb * (p.Hd + p.D) + p.Hd + d] + __ldcg(&p.dctx_dec[(size_t)b * p.Ep + d]) +
+                          __ldcg(&p.dctx_att[(size_t)b * p.Ep + d]);
+        sm.dctx_s[d] = val;
+        if (half == 0) p.dctx_all[bt * E + d] = val;
+      }
+      for (int i = threadIdx.x; i < 2 * Wd; i += blockDim.x) {
+        const int ch = i / Wd, jj = i - ch * Wd, j = j0 + jj - hk;
+        float val = 0.f;
+        if (j >= 0 && j < Tin) val = ch == 0 ? (t > 0 ? p.align[(bt - 1) * Tin + j] : 0.f) : p.cum_all[tb * Tin + j];
+        sm.wcat[i] = val;
+      }
+    }
+    __syncthreads();
+    float dot_part = 0.f;
+    if (active) {
+      build_im2col(sm.wcat, Wd, KS, jn, im_hi, im_lo);
+      // zero the K-rows of the im2col tiles beyond jn (they are the K extent of dU += dth^T . im2col)
+      for (int i = threadIdx.x; i < (TILE_M - jn) * 8; i += blockDim.x) {
+        const int r = jn + (i >> 3), chunk = i & 7;
+        const uint32_t off = sw128_off(r, chunk);
+        *reinterpret_cast<uint4*>(im_hi + off) = make_uint4(0u, 0u, 0u, 0u);
+        *reinterpret_cast<uint4*>(im_lo + off) = make_uint4(0u, 0u, 0u, 0u);
+      }
+      // d w_j over this CTA's positions: one warp per position, lanes over the time-varying columns
+      for (int jl = warp; jl < jn; jl += 8) {
+        const int j = j0 + jl;
+        float s = 0.f;
+        if (j < L) {
+          const MT* mj = mem + ((size_t)b * Tin + j) * E;
+          for (int d = lane * 8; d < E; d += 256) {
+            float mv[8];
+            ld8b<MT>(mj + d, mv);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) s += sm.dctx_s[d + e] * mv[e];
+          }
+          s = warp_sum(s);
+          s += __ldcg(&p.dwprev[(size_t)b * p.ldT + j]) + __ldcg(&p.dcum[(size_t)b * p.ldT + j]);
+          if (p.dalign) s += p.dalign[bt * Tin + j];
+        }
+        if (lane == 0) { sm.dw_s[j] = s; }
+      }
+    }
+    __syncthreads();
+    if (active) {
+      for (int jl = threadIdx.x; jl < jn; jl += blockDim.x) dot_part += sm.w_s[j0 + jl] * sm.dw_s[j0 + jl];
+    }
+    dot_part = block_sum2(dot_part, sm.scr);
+    if (active && threadIdx.x == 0) {
+      sm.dot_s[xb * 2] = dot_part;
+      st_cluster_f1(map_to_rank(smem_u32(&sm.dot_s[xb * 2 + 1]), (uint32_t)peer), dot_part);
+    }
+    cluster_sync_all();                                              // #1: softmax dot product of the pair
+    if (active) {
+      const float dot = sm.dot_s[xb * 2] + sm.dot_s[xb * 2 + 1];
+      // softmax backward: de_j = w_j (dw_j - sum_k w_k dw_k)
+      for (int jl = threadIdx.x; jl < jn; jl += blockDim.x) {
+        const int j = j0 + jl;
+        sm.dw_s[j] = sm.w_s[j] * (sm.dw_s[j] - dot);
+      }
+    }
+    __syncthreads();
+    if (active) {
+      // thread = (position row = TMEM lane, 64-column half of the attention dimension)
+      const int wq = warp & 3, ah = warp >> 2, a0 = ah * 64;
+      const int jl = wq * 32 + lane;
+      const bool valid = jl < jn && (j0 + jl) < L;
+      const float de = valid ? sm.dw_s[j0 + jl] : 0.f;
+      float dth[64], pv[64];
+      const float* thj = p.th_all + ((tb * Tin + (j0 + jl)) * A + a0);
+      float* dpmj = p.dpm + (((size_t)b * Tin + (j0 + jl)) * A + a0);
+#pragma unroll
+      for (int g = 0; g < 16; ++g) {
+        float4 th = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (valid && a0 + g * 4 < A) th = __ldg(reinterpret_cast<const float4*>(thj) + g);
+        const float t4[4] = {th.x, th.y, th.z, th.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int a = g * 4 + e;
+          dth[a] = de * sm.v_s[a0 + a] * (1.f - t4[e] * t4[e]);
+          pv[a] = de * t4[e];
+        }
+        if (valid && a0 + g * 4 < A) {
+          float4 acc = *(reinterpret_cast<float4*>(dpmj) + g);
+          acc.x += dth[g * 4]; acc.y += dth[g * 4 + 1]; acc.z += dth[g * 4 + 2]; acc.w += dth[g * 4 + 3];
+          *(reinterpret_cast<float4*>(dpmj) + g) = acc;
+        }
+      }
+      // dth as bf16 hi / lo planes: K-major tile rows = positions (block ah), also the MN-major operand of dU
+#pragma unroll
+      for (int chunk = 0; chunk < 8; ++chunk) {
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float x0 = dth[chunk * 8 + 2 * e], x1 = dth[chunk * 8 + 2 * e + 1];
+          const float h0 = bf16_round(x0), h1 = bf16_round(x1);
+          hi[e] = pack_bf16x2(h0, h1);
+          lo[e] = pack_bf16x2(x0 - h0, x1 - h1);
+        }
+        const uint32_t off = (uint32_t)ah * W_TILE_BYTES + sw128_off(jl, chunk);
+        *reinterpret_cast<uint4*>(dth_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(dth_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+      }
+      fence_proxy_async_smem();
+      // column sums over positions: dq[a] = sum_j dth[j][a], dv[a] += sum_j de_j th[j][a]
+      warp_reduce_scatter64(dth);
+      warp_reduce_scatter64(pv);
+      // part_s[warp][0..63]: lanes hold columns 2l, 2l+1
+      sm.part_s[warp * 64 + 2 * lane] = dth[0];
+      sm.part_s[warp * 64 + 2 * lane + 1] = dth[1];
+      __syncthreads();
+      float dqv = 0.f;
+      if (threadIdx.x < 128) {
+        const int a = threadIdx.x, hh = a >> 6, c = a & 63;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) dqv += sm.part_s[(hh * 4 + w) * 64 + c];
+      }
+      __syncthreads();
+      sm.part_s[warp * 64 + 2 * lane] = pv[0];
+      sm.part_s[warp * 64 + 2 * lane + 1] = pv[1];
+      __syncthreads();
+      if (threadIdx.x < 128) {
+        const int a = threadIdx.x, hh = a >> 6, c = a & 63;
+        float dvv = 0.f;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) dvv += sm.part_s[(hh * 4 + w) * 64 + c];
+        sm.dv_acc[a] += dvv;
+        sm.dqp_s[a] = dqv;               // own partial (slot 0); the peer's lands in slot 1 (dqp_s + 128)
+        st_cluster_f1(map_to_rank(smem_u32(&sm.dqp_s[128 + a]), (uint32_t)peer), dqv);
+      }
+    }
+    __syncthreads();
+    if (active && threadIdx.x == 32) {
+      tc_fence_after();
+      // G[j][kk] = sum_a dth[j][a] U[a][kk]   (M = positions, N = 64 filter taps, K = attention dim, 2 k-blocks)
+      const uint32_t idesc = umma_idesc_bf16(TILE_M, 64);
+      const uint32_t uts = smem_u32(sm.ut_s);
+      for (int pl = 0; pl < 3; ++pl) {             // (dth_hi, U_hi), (dth_lo, U_hi), (dth_hi, U_lo)
+        const uint32_t abase = smem_u32(pl == 1 ? dth_lo : dth_hi);
+        const uint32_t bbase = uts + (pl == 2 ? 2u * 8192u : 0u);
+#pragma unroll
+        for (int kb = 0; kb < 2; ++kb) {
+          const uint64_t da = umma_desc_sw128(abase + kb * W_TILE_BYTES), db = umma_desc_sw128(bbase + kb * 8192u);
+#pragma unroll
+          for (int k = 0; k < KB / 16; ++k)
+            umma_bf16(tmem_g, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((pl | kb | k) != 0));
+        }
+      }
+      umma_commit(sm.g_full);
+      // dU[a][kk] += sum_j dth[j][a] im2col[j][kk]   (M = attention dim: 2 MN slices 16 KB apart, N = taps, K = positions)
+      const uint32_t idesc_mn = umma_idesc_bf16(TILE_M, 64) | (1u << 15) | (1u << 16);
+      for (int pl = 0; pl < 3; ++pl) {             // (dth_hi, im_hi), (dth_lo, im_hi), (dth_hi, im_lo)
+        const uint32_t abase = smem_u32(pl == 1 ? dth_lo : dth_hi);
+        const uint32_t bbase = smem_u32(pl == 2 ? im_lo : im_hi);
+#pragma unroll
+        for (int k = 0; k < TILE_M / 16; ++k) {
+          const uint64_t da = umma_desc_sw128_mn_lbo(abase + k * 2048u, W_TILE_BYTES);
+          const uint64_t db = umma_desc_sw128_mn_lbo(bbase + k * 2048u, W_TILE_BYTES);
+          umma_bf16(tmem_du, da, db, idesc_mn, (uint32_t)(!(first && itb == 0) || (pl | k) != 0));
+        }
+      }
+      // (no commit needed for dU: it is only read at the very end, after later commits / barriers)
+    }
+    __syncwarp();
+    if (active) {
+      wait_bar(sm.g_full, g_par);
+      g_par ^= 1u;
+      tc_fence_after();
+      if (warp >= 4) {
+        const int wq = warp & 3;
+        const int jl = wq * 32 + lane;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_g + ((uint32_t)(wq * 32) << 16) + (uint32_t)(h * 32), r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int c = 0; c < 32; ++c) G_s[jl * 64 + ((h * 32 + c) ^ (jl & 31))] = __uint_as_float(r[c]);
+        }
+      }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (active) {
+      // d wcat[ch][jj] = sum_k G[jj - k][ch*KS + k]  over this CTA's positions
+      for (int i = threadIdx.x; i < 2 * Wd; i += blockDim.x) {
+        const int ch = i / Wd, jj = i - ch * Wd;
+        float s = 0.f;
+        for (int k = 0; k < KS; ++k) {
+          const int jl = jj - k;
+          if (jl >= 0 && jl < jn) s += G_s[jl * 64 + ((ch * KS + k) ^ (jl & 31))];
+        }
+        sm.dwc_s[i] = s;
+      }
+    }
+    __syncthreads();
+    if (active) {
+      // positions outside this CTA's range belong to the peer: send them (window index jj <-> position j0 + jj - hk)
+      float* hal = sm.halo_s + xb * 2 * 32;
+      const uint32_t peer_h = map_to_rank(smem_u32(hal), (uint32_t)peer);
+      for (int i = threadIdx.x; i < 2 * hk; i += blockDim.x) {
+        const int ch = i / hk, q = i - ch * hk;
+        // half 0 sends its upper halo (jj = hk + jn + q), half 1 its lower halo (jj = q)
+        const int jj = half == 0 ? hk + jn + q : q;
+        st_cluster_f1(peer_h + (uint32_t)((ch * 32 + q) * 4), sm.dwc_s[ch * Wd + jj]);
+      }
+    }
+    cluster_sync_all();                                              // #2: halos and dq partials of the pair
+    if (active) {
+      const float* hal = sm.halo_s + xb * 2 * 32;
+      for (int i = threadIdx.x; i < 2 * jn; i += blockDim.x) {
+        const int ch = i / jn, jl = i - ch * jn, j = j0 + jl;
+        float s = sm.dwc_s[ch * Wd + hk + jl];
+        // the peer's halo covers my first hk positions (I am half 1) or my last hk positions (I am half 0)
+        if (half == 1 && jl < hk && Tin > JH) s += hal[ch * 32 + jl];
+        if (half == 0) {
+          const int q = jl - (jn - hk);            // peer's lower halo q <-> its position j0' + q - hk = my position jn - hk + q
+          if (q >= 0 && q < hk && Tin > JH) s += hal[ch * 32 + q];
+        }
+        if (ch == 0) p.dwprev[(size_t)b * p.ldT + j] = s;
+        else p.dcum[(size_t)b * p.ldT + j] += s;
+      }
+      if (half == 0) {
+        for (int a = threadIdx.x; a < A; a += blockDim.x) {
+          const float s = sm.dqp_s[a] + ((Tin > JH) ? sm.dqp_s[128 + a] : 0.f);
+          p.dq_all[tb * A + a] = s;
+          p.dq_sum[(size_t)b * A + a] = s;
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// P3: query backward + attention LSTM cell backward of frame t, all CTAs, split by hidden unit
+// ------------------------------------------------------------------------------------------------
+GTN_DEVICE void att_cell_phase2(const DecBwd2& p, SmemB& sm, int t) {
+  // cells are dealt out as (unit, batch) with the unit slowest so a CTA touches few rows of Wq^T; dq of a 64-sequence
+  // chunk is staged transposed in shared memory ([a][65]: conflict-free for consecutive sequences)
+  const int ncell = p.Ha * p.B;
+  const int per_cta = (ncell + gridDim.x - 1) / gridDim.x;
+  const int c_begin = blockIdx.x * per_cta, c_end = min(ncell, c_begin + per_cta);
+  float* dq_s = reinterpret_cast<float*>(sm.ring.base);      // the TMA ring is idle in this phase
+  for (int bc0 = 0; bc0 < p.B; bc0 += 64) {
+    const int nb = min(64, p.B - bc0);
+    __syncthreads();
+    for (int i = threadIdx.x; i < nb * p.A; i += blockDim.x) {
+      const int bl = i / p.A, a = i - bl * p.A;
+      dq_s[a * 65 + bl] = __ldcg(&p.dq_sum[(size_t)(bc0 + bl) * p.A + a]);
+    }
+    __syncthreads();
+    for (int c = c_begin + threadIdx.x; c < c_end; c += blockDim.x) {
+      const int u = c / p.B, b = c - u * p.B;
+      if (b < bc0 || b >= bc0 + nb) continue;
+      const float* wq = p.wq_t + (size_t)u * p.A;
+      const float* dq = dq_s + (b - bc0);
+      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+      for (int a = 0; a < p.A; a += 4) {
+        const float4 w4 = __ldg(reinterpret_cast<const float4*>(wq + a));
+        s0 += w4.x * dq[a * 65]; s1 += w4.y * dq[(a + 1) * 65]; s2 += w4.z * dq[(a + 2) * 65]; s3 += w4.w * dq[(a + 3) * 65];
+      }
+      const size_t ci = (size_t)b * p.Ha + u;
+      const float dh = (s0 + s1) + (s2 + s3) + __ldcg(&p.dha_dec[ci]) + __ldcg(&p.carry_ha[ci]);
+      cell_backward2(p, t, b, u, p.Ha, dh, p.gates_a, p.c_a_all, p.dc_a, p.dga_all, BFP(p.xdg_a), 3u, p.thr_att, p.p_att);
+    }
+  }
+}
+
+template <int N>
+__global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_constant__ Bwd2Maps maps, const DecBwd2 p, const int S) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  SmemB sm = carveB<N>(base, S);
+  const int warp = threadIdx.x >> 5;
+  const int rank = (int)cluster_ctarank(), cid = (int)cluster_idx(), ncl = (int)cluster_count();
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) { mbar_init(&sm.ring.full[s], 1); mbar_init(&sm.ring.empty[s], 1); }
+    mbar_init(sm.acc_full, 1);
+    mbar_init(sm.g_full, 1);
+    mbar_init(sm.ut_full, 1);
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc(sm.tmem_slot, 512);
+  for (int i = threadIdx.x; i < 128; i += blockDim.x) { sm.v_s[i] = i < p.A ? p.v[i] : 0.f; sm.dv_acc[i] = 0.f; }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *sm.tmem_slot;
+  const uint32_t tmem_g = tmem_base + 256u, tmem_du = tmem_base + 320u;
+  if (threadIdx.x == 0) {
+    // U^T hi / lo planes, two 64-wide k-blocks each: resident for the whole kernel
+    mbar_expect_tx(sm.ut_full, 4 * 8192);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) tma_load_3d(sm.ut_s + i * 8192, &maps.ut, sm.ut_full, i * KB, 0, 0);
+    wait_bar(sm.ut_full, 0);
+  }
+  cluster_sync_all();
+
+  unsigned int epoch = 0;
+  uint32_t acc_par = 0, g_par = 0, round = 0, xround = 0;
+  const unsigned int nblocks = gridDim.x;
+  dec_cell_prologue(p, p.T - 1);
+  grid_sync2(p.barrier, epoch, nblocks);
+  int it = 0;
+  for (int t = p.T - 1; t >= 0; --t, ++it) {
+    dgrad_phase2<N>(p, maps, sm, t, it, rank, cid, ncl, tmem_base, acc_par, round);
+    grid_sync2(p.barrier, epoch, nblocks);
+    if (p.mem_bf16) attn_bwd_phase2<bf16>(p, sm, t, it == 0, rank, cid, ncl, tmem_g, tmem_du, g_par, xround);
+    else attn_bwd_phase2<float>(p, sm, t, it == 0, rank, cid, ncl, tmem_g, tmem_du, g_par, xround);
+    grid_sync2(p.barrier, epoch, nblocks);
+    att_cell_phase2(p, sm, t);
+    grid_sync2(p.barrier, epoch, nblocks);
+  }
+  // per-CTA partial sums of the small attention weight gradients
+  for (int i = threadIdx.x; i < p.A; i += blockDim.x) p.dv_part[(size_t)blockIdx.x * p.A + i] = sm.dv_acc[i];
+  {
+    // dU accumulator [128 lanes = attention dim][64 taps] -> dU_part[cta][a][kk]; make sure the last MMAs retired
+    if (threadIdx.x == 32) umma_commit(sm.g_full);
+    __syncwarp();
+    const int pair = cid * 2 + (rank >> 1);
+    const bool used = pair < p.B;                     // CTAs that never ran an attention step hold no accumulator
+    wait_bar(sm.g_full, g_par);
+    tc_fence_after();
+    if (warp >= 4) {
+      const int wq = warp & 3, lane = threadIdx.x & 31;
+      const int a = wq * 32 + lane;
+      float* out = p.dU_part + ((size_t)blockIdx.x * TILE_M + a) * 64;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_du + ((uint32_t)(wq * 32) << 16) + (uint32_t)(h * 32), r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int c = 0; c < 32; ++c) out[h * 32 + c] = used ? __uint_as_float(r[c]) : 0.f;
+      }
+    }
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) tmem_dealloc(tmem_base, 512);
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+int make_tma_map_3d(CUtensorMap* out, const void* base, long long d0, long long d1, long long d2, long long stride1_elems,
+                    long long stride2_elems, int box1);
+
+template <int N>
+static int bwd2_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attrs, int& S, size_t& smem) {
+  const size_t stage = (size_t)W_TILE_BYTES + (size_t)N * KB * 2;
+  const size_t fixed = bwd2_fixed_bytes<N>() + 1024;
+  S = (int)((227 * 1024 - fixed) / stage);
+  if (S > 12) S = 12;
+  GTN_REQUIRE(S >= 2, "decoder backward: not enough shared memory for the TMA ring (N=%d)", N);
+  size_t ring_b = (size_t)S * stage;
+  if (ring_b < (size_t)P2_RING_BYTES) ring_b = P2_RING_BYTES;
+  smem = fixed + ring_b;
+  GTN_REQUIRE(smem <= 227 * 1024, "decoder backward: shared memory budget exceeded (%zu B, N=%d)", smem, N);
+  GTN_CUDA_OK(cudaFuncSetAttribute(decoder_bwd2_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cfg = cudaLaunchConfig_t{};
+  cfg.blockDim = dim3(256);
+  cfg.dynamicSmemBytes = smem;
+  attrs[0].id = cudaLaunchAttributeClusterDimension;
+  attrs[0].val.clusterDim.x = CL; attrs[0].val.clusterDim.y = 1; attrs[0].val.clusterDim.z = 1;
+  attrs[1].id = cudaLaunchAttributeCooperative;
+  attrs[1].val.cooperative = 1;
+  cfg.attrs = attrs;
+  return 0;
+}
+
+template <int N>
+static int bwd2_grid(int want, int* ncl_out) {
+  cudaLaunchConfig_t cfg; cudaLaunchAttribute attrs[2]; int S; size_t smem;
+  int rc = bwd2_config<N>(cfg, attrs, S, smem);
+  if (rc) return rc;
+  cfg.numAttrs = 1;
+  cfg.gridDim = dim3(CL * want);
+  int max_cl = 0;
+  GTN_CUDA_OK(cudaOccupancyMaxActiveClusters(&max_cl, decoder_bwd2_kernel<N>, &cfg));
+  GTN_REQUIRE(max_cl >= 1, "decoder backward: no cluster of %d CTAs fits on this device", CL);
+  *ncl_out = max_cl < want ? max_cl : want;
+  return 0;
+}
+
+template <int N>
+static int launch_bwd2(const Bwd2Maps& maps, const DecBwd2& p, int ncl, cudaStream_t st) {
+  cudaLaunchConfig_t cfg; cudaLaunchAttribute attrs[2]; int S; size_t smem;
+  int rc = bwd2_config<N>(cfg, attrs, S, smem);
+  if (rc) return rc;
+  cfg.stream = st;
+  cfg.numAttrs = 2;
+  cfg.gridDim = dim3(CL * ncl);
+  GTN_CUDA_OK(cudaLaunchKernelEx(&cfg, decoder_bwd2_kernel<N>, maps, p, S));
+  count_launch();
+  return 0;
+}
+
+static int pick_n(int B) { return B <= 32 ? 32 : (B <= 64 ? 64 : (B <= 128 ? 128 : 256)); }
+
+}  // namespace gtn
+
+using namespace gtn;
+
+extern "C" int gtn_decoder_bwd2_grid(int B, int Ha, int Hd, int E) {
+  const int want0 = ((Ha + E + Hd + TILE_M - 1) / TILE_M) + ((E + Ha + TILE_M - 1) / TILE_M);
+  const int want = want0 > 32 ? 32 : want0;
+  int ncl = 0, rc;
+  const int N = pick_n(B);
+  if (N == 32) rc = bwd2_grid<32>(want, &ncl);
+  else if (N == 64) rc = bwd2_grid<64>(want, &ncl);
+  else if (N == 128) rc = bwd2_grid<128>(want, &ncl);
+  else rc = bwd2_grid<256>(want, &ncl);
+  return rc ? -1 : CL * ncl;
+}
+
+extern "C" int gtn_decoder_backward2(const gtn_decoder_bwd2_params* hp, void* stream) {
+  GTN_REQUIRE(hp != nullptr, "null params");
+  DecBwd2 p = *hp;
+  GTN_REQUIRE(p.prec == 1 || p.prec == 3, "prec must be 1 or 3");
+  p.mult = p.prec == 1 ? 1 : 6;
+  GTN_REQUIRE(p.Ha % 32 == 0 && p.Hd % 32 == 0 && p.A <= 128 && p.A % 8 == 0, "unsupported dims");
+  GTN_REQUIRE(p.E % 8 == 0 && p.E <= 1024 && p.Ep >= p.E && p.D >= p.E, "E must be a multiple of 8, <= 1024");
+  GTN_REQUIRE(p.KS % 2 == 1 && 2 * p.KS <= 64, "location kernel size must be odd and <= 31");
+  GTN_REQUIRE(p.Tin >= 1 && p.Tin <= B2_TIN_MAX && p.T >= 1 && p.B >= 1 && p.B <= 256, "bad dims");
+  auto thr = [](float pr) -> unsigned { double t = (double)pr * 4294967296.0; return t >= 4294967295.0 ? 0xFFFFFFFFu : (unsigned)t; };
+  p.thr_att = p.use_dropout ? thr(p.p_att) : 0u;
+  p.thr_dec = p.use_dropout ? thr(p.p_dec) : 0u;
+  const int grid = gtn_decoder_bwd2_grid(p.B, p.Ha, p.Hd, p.E);
+  GTN_REQUIRE(grid > 0 && p.grid == grid, "params.grid (%d) must equal gtn_decoder_bwd2_grid() (%d)", p.grid, grid);
+  const int N = pick_n(p.B);
+  const int m = p.mult;
+  Bwd2Maps maps;
+  int rc = 0;
+  rc |= make_tma_map_3d(&maps.wT_att, p.wT_att2, (long long)m * 4 * p.Ha, p.E + p.Ha, 1, (long long)m * 4 * p.Ha, 0, TILE_M);
+  rc |= make_tma_map_3d(&maps.wT_dec, p.wT_dec2, (long long)m * 4 * p.Hd, p.Ha + p.E + p.Hd, 1, (long long)m * 4 * p.Hd, 0, TILE_M);
+  rc |= make_tma_map_3d(&maps.ut, p.ut_loc, 4 * KB, 64, 1, 4 * KB, 0, 64);
+  rc |= make_tma_map_3d(&maps.xdg_a, p.xdg_a, (long long)m * 4 * p.Ha, p.B, 1, (long long)m * 4 * p.Ha, 0, N);
+  rc |= make_tma_map_3d(&maps.xdg_d, p.xdg_d, (long long)m * 4 * p.Hd, p.B, 2, (long long)m * 4 * p.Hd, (long long)p.B * m * 4 * p.Hd, N);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int ncl = grid / CL;
+  if (N == 32) return launch_bwd2<32>(maps, p, ncl, st);
+  if (N == 64) return launch_bwd2<64>(maps, p, ncl, st);
+  if (N == 128) return launch_bwd2<128>(maps, p, ncl, st);
+  return launch_bwd2<256>(maps, p, ncl, st);
+}

@@ -48,8 +48,7 @@ struct Smem2 {
   Ring ring;
   uint8_t* u_s;        // [2][16 KB]  U_hi, U_lo (UMMA B operand of the location GEMM)
   float* recv;         // [2][4][128][NC4]
-  float* wq_s;         // [32][A]
-  float* hs;           // [NC4][32]
+  float* hs;           // [32][NC4]
   float* q_s;          // [A]
   float* v_s;          // [A]
   float* wcat;         // [2][JH + KS - 1]
@@ -73,7 +72,6 @@ __host__ __device__ constexpr size_t fwd2_fixed_bytes() {
   constexpr int NC4 = (N < 64 ? N : 64) / 4;
   return (size_t)2 * W_TILE_BYTES                        // u_s
          + (size_t)2 * 4 * TILE_M * NC4 * 4               // recv
-         + (size_t)32 * 128 * 4                           // wq_s
          + (size_t)(NC4 * 32 + 128 + 128 + 2 * (JH_MAX + KS_MAX - 1) + 2 * TIN_MAX + 2 * 128 + TIN_MAX + 8 * 256 + 64) * 4
          + 64 * 8 + 64;                                   // barriers + tmem slot
 }
@@ -90,7 +88,6 @@ GTN_DEVICE Smem2 carve2(uint8_t* base, int S) {
   m.u_s = p; p += 2 * W_TILE_BYTES;
   float* f = reinterpret_cast<float*>(p);
   m.recv = f; f += 2 * 4 * TILE_M * NC4;
-  m.wq_s = f; f += 32 * 128;
   m.hs = f; f += NC4 * 32;
   m.q_s = f; f += 128;
   m.v_s = f; f += 128;
@@ -127,7 +124,7 @@ GTN_DEVICE float block_reduce2(float v, float* scr, bool is_max) {
 // ------------------------------------------------------------------------------------------------
 template <int N>
 GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int kind, int t, int rank, int cid, int ncl,
-                           uint32_t tmem_base, uint32_t& acc_par, uint32_t& round) {
+                           uint32_t tmem_base, uint32_t& acc_par, uint32_t& round, float (&wqr)[32]) {
   constexpr int CH = N < 64 ? N : 64;
   constexpr int NC4 = CH / 4;
   const int mult = p.mult, cur = t & 1, nxt = cur ^ 1;
@@ -145,19 +142,19 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
     case K_ATT:
       job.wmap = &maps.w_att; ntiles = p.Ha / 32; job.nseg = 3;
       job.seg[0] = p.train ? XSeg{&maps.pre, mult * p.Pp / KB, t} : XSeg{&maps.xp2, mult * p.Pp / KB, 0};
-      job.seg[1] = {&maps.ctx, mult * p.Dp / KB, 0};
+      job.seg[1] = {&maps.ctx, mult * p.Ep / KB, 0};
       job.seg[2] = {&maps.ha, mult * p.Hap / KB, cur};
       break;
     case K_DEC:
       job.wmap = &maps.w_dec; ntiles = p.Hd / 32; job.nseg = 3;
       job.seg[0] = {&maps.ha, mult * p.Hap / KB, nxt};
-      job.seg[1] = {&maps.ctx, mult * p.Dp / KB, 0};
+      job.seg[1] = {&maps.ctx, mult * p.Ep / KB, 0};
       job.seg[2] = {&maps.hd, mult * p.Hdp / KB, cur};
       break;
     default:
       job.wmap = &maps.w_proj; ntiles = 1; job.nseg = 2;
       job.seg[0] = {&maps.hd, mult * p.Hdp / KB, nxt};
-      job.seg[1] = {&maps.ctx, mult * p.Dp / KB, 0};
+      job.seg[1] = {&maps.ctx, mult * p.Ep / KB, 0};
       break;
   }
   job.nkb = 0;
@@ -169,8 +166,10 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
   for (int tile = cid; tile < ntiles; tile += ncl) {
     job.row0 = tile * TILE_M;
     if (is_att && (ntiles > ncl || t == 0)) {
-      // query-weight slice of this tile's 32 units: wq_s[ul][a] = Wq[a][32*tile + ul]  (wq_t is [Ha][A])
-      for (int i = threadIdx.x; i < 32 * p.A; i += blockDim.x) sm.wq_s[i] = p.wq_t[(size_t)tile * 32 * p.A + i];
+      // query-weight column of this thread (a = tid % 128) for the tile's 32 units, kept in registers: Wq[a][32 tile + u]
+      const int a = threadIdx.x & 127;
+#pragma unroll
+      for (int u = 0; u < 32; ++u) wqr[u] = a < p.A ? p.wq_t[((size_t)tile * 32 + u) * p.A + a] : 0.f;
     }
     const int ps = kind == K_ATT ? 1 : (kind == K_DEC ? 9 : (kind == K_PROJ ? 14 : 20));
     const bool has_work = gemm_issue<N>(job, sm.ring, tmem_base, sm.acc_full, rank);
@@ -185,12 +184,31 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
     for (int c0 = 0; c0 < N; c0 += CH) {
       float* recv = sm.recv + (size_t)(round & 1u) * 4 * TILE_M * NC4;
       ++round;
+      const int bbase = c0 + rank * NC4;
+      // operands of the fused epilogue that do not depend on the GEMM are fetched while the exchange is in flight
+      constexpr int CPT = 32 * NC4 / 256;          // LSTM cells per thread (NC4 = 8 or 16)
+      float4 gb[CPT];
+      float cprev[CPT];
+      float* cst = is_att ? p.c_a : p.c_d;
+      if (is_lstm) {
+        const float4* gbias = reinterpret_cast<const float4*>(is_att ? p.gbias_a : p.gbias_d);
+#pragma unroll
+        for (int q = 0; q < CPT; ++q) {
+          const int idx = threadIdx.x + q * 256;
+          const int bl = idx % NC4, ul = idx / NC4, b = bbase + bl, unit = tile * 32 + ul;
+          gb[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+          cprev[q] = 0.f;
+          if (b < p.B) {
+            // frame 0 of the attention LSTM sees the zero initial context (model.py:314-316): no constant-column term
+            if (is_att && t == 0) gb[q] = make_float4(p.b_att[unit], p.b_att[H + unit], p.b_att[2 * H + unit], p.b_att[3 * H + unit]);
+            else gb[q] = __ldg(&gbias[(size_t)b * H + unit]);
+            cprev[q] = cst[(size_t)b * H + unit];
+          }
+        }
+      }
       exchange_chunk<CH>(has_work, tmem_base, c0, recv, rank);
       PROF(ps + 2);                              // DSMEM exchange + cluster barrier done
-      const int bbase = c0 + rank * NC4;
       if (is_lstm) {
-        float* cst = is_att ? p.c_a : p.c_d;
-        const float* bias = is_att ? p.b_att : p.b_dec;
         const float pdrop = is_att ? p.p_att : p.p_dec;
         const unsigned thr = is_att ? p.thr_att : p.thr_dec;
         const float dscale = 1.0f / (1.0f - pdrop);
@@ -199,17 +217,18 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
         float* gates_all = is_att ? p.gates_a : p.gates_d;
         float* c_all = is_att ? p.c_a_all : p.c_d_all;
         float* h_all = is_att ? p.h_a_all : p.h_d_all;
-        for (int idx = threadIdx.x; idx < 32 * NC4; idx += blockDim.x) {
+#pragma unroll
+        for (int q = 0; q < CPT; ++q) {
+          const int idx = threadIdx.x + q * 256;
           const int bl = idx % NC4, ul = idx / NC4, b = bbase + bl, unit = tile * 32 + ul;
           float h = 0.f;
           if (b < p.B) {
-            const float gi = recv_sum<NC4>(recv, ul, bl) + bias[unit];
-            const float gf = recv_sum<NC4>(recv, 32 + ul, bl) + bias[H + unit];
-            const float gg = recv_sum<NC4>(recv, 64 + ul, bl) + bias[2 * H + unit];
-            const float go = recv_sum<NC4>(recv, 96 + ul, bl) + bias[3 * H + unit];
-            const float i_ = sigmoid_acc(gi), f_ = sigmoid_acc(gf), g_ = tanh_acc(gg), o_ = sigmoid_acc(go);
+            const float i_ = sigmoid_acc(recv_sum<NC4>(recv, ul, bl) + gb[q].x);
+            const float f_ = sigmoid_acc(recv_sum<NC4>(recv, 32 + ul, bl) + gb[q].y);
+            const float g_ = tanh_acc(recv_sum<NC4>(recv, 64 + ul, bl) + gb[q].z);
+            const float o_ = sigmoid_acc(recv_sum<NC4>(recv, 96 + ul, bl) + gb[q].w);
             const size_t ci = (size_t)b * H + unit;
-            const float c_new = f_ * cst[ci] + i_ * g_;
+            const float c_new = f_ * cprev[q] + i_ * g_;
             cst[ci] = c_new;
             h = o_ * tanh_acc(c_new);
             if (p.use_dropout && thr != 0u) {
@@ -218,24 +237,38 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
             }
             store_act(xh_next + (size_t)b * mult * Hp, unit, Hp, p.prec, h);
             if (p.train) {
-              const size_t g0 = ((size_t)t * p.B + b) * 4 * H + unit;
-              gates_all[g0] = i_; gates_all[g0 + H] = f_; gates_all[g0 + 2 * H] = g_; gates_all[g0 + 3 * H] = o_;
-              c_all[((size_t)t * p.B + b) * H + unit] = c_new;
-              h_all[((size_t)t * p.B + b) * H + unit] = h;
+              const size_t cell = ((size_t)t * p.B + b) * H + unit;
+              reinterpret_cast<float4*>(gates_all)[cell] = make_float4(i_, f_, g_, o_);
+              c_all[cell] = c_new;
+              h_all[cell] = h;
             }
           }
-          if (is_att) sm.hs[bl * 32 + ul] = h;
+          if (is_att) sm.hs[ul * NC4 + bl] = h;
         }
         if (is_att) {
           __syncthreads();
-          // partial query of this tile: qpart[tile][b][a] = sum_ul Wq[a][32 tile + ul] h[b][ul]
-          for (int idx = threadIdx.x; idx < NC4 * p.A; idx += blockDim.x) {
-            const int bl = idx / p.A, a = idx - bl * p.A, b = bbase + bl;
-            if (b >= p.B) continue;
-            float s = 0.f;
-#pragma unroll 8
-            for (int u = 0; u < 32; ++u) s += sm.wq_s[u * p.A + a] * sm.hs[bl * 32 + u];
-            p.qpart[((size_t)tile * p.B + b) * p.A + a] = s;
+          // partial query of this tile: qpart[tile][b][a] = sum_u Wq[a][32 tile + u] h[b][u]; thread = (a, half of the columns)
+          constexpr int HB = NC4 / 2;
+          const int a = threadIdx.x & 127, g = threadIdx.x >> 7;
+          float acc[HB];
+#pragma unroll
+          for (int j = 0; j < HB; ++j) acc[j] = 0.f;
+#pragma unroll
+          for (int u = 0; u < 32; ++u) {
+            const float4* hr = reinterpret_cast<const float4*>(sm.hs + u * NC4 + g * HB);
+#pragma unroll
+            for (int j4 = 0; j4 < HB / 4; ++j4) {
+              const float4 hv = hr[j4];
+              acc[4 * j4] += wqr[u] * hv.x; acc[4 * j4 + 1] += wqr[u] * hv.y;
+              acc[4 * j4 + 2] += wqr[u] * hv.z; acc[4 * j4 + 3] += wqr[u] * hv.w;
+            }
+          }
+          if (a < p.A) {
+#pragma unroll
+            for (int j = 0; j < HB; ++j) {
+              const int b = bbase + g * HB + j;
+              if (b < p.B) p.qpart[((size_t)tile * p.B + b) * p.A + a] = acc[j];
+            }
           }
         }
       } else {
@@ -250,7 +283,7 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
             val = bits >= 0x80000000u ? val * 2.0f : 0.f;     // p = 0.5, always on (model.py:104)
             store_act((kind == K_PRE1 ? BFP(p.xp1) : BFP(p.xp2)) + (size_t)b * mult * p.Pp, row, p.Pp, p.prec, val);
           } else {
-            val += p.b_proj[row];
+            val += p.pbias[(size_t)b * (p.NM + 1) + row];
             if (row < p.NM) {
               p.mel_out[((size_t)b * p.NM + row) * p.n_steps + t] = val;
               store_act(BFP(p.xmel) + (size_t)b * mult * p.NMp, row, p.NMp, p.prec, val);
@@ -321,8 +354,17 @@ GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, in
     if (active) {
       const int ntq = p.Ha / 32;
       for (int a = threadIdx.x; a < A; a += blockDim.x) {
-        float s = 0.f;
-        for (int c = 0; c < ntq; ++c) s += __ldcg(&p.qpart[((size_t)c * p.B + b) * A + a]);
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        const float* qp = p.qpart + (size_t)b * A + a;
+        const size_t qs = (size_t)p.B * A;
+        int c = 0;
+#pragma unroll 2
+        for (; c + 4 <= ntq; c += 4) {
+          s0 += __ldcg(qp + (size_t)c * qs); s1 += __ldcg(qp + (size_t)(c + 1) * qs);
+          s2 += __ldcg(qp + (size_t)(c + 2) * qs); s3 += __ldcg(qp + (size_t)(c + 3) * qs);
+        }
+        for (; c < ntq; ++c) s0 += __ldcg(qp + (size_t)c * qs);
+        const float s = (s0 + s1) + (s2 + s3);
         sm.q_s[a] = s;
         if (p.train && half == 0) p.q_all[((size_t)t * p.B + b) * A + a] = s;
       }
@@ -338,30 +380,7 @@ GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, in
     __syncthreads();
     if (active) {
       // im2col: row r = local encoder position, K index kk = ch*KS + k  ->  wcat[ch][r + k]; bf16 hi / lo planes
-      for (int i = threadIdx.x; i < jn * 8; i += blockDim.x) {
-        const int r = i >> 3, chunk = i & 7;
-        uint32_t hi[4], lo[4];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          float v2[2];
-#pragma unroll
-          for (int q = 0; q < 2; ++q) {
-            const int kk = chunk * 8 + e * 2 + q;
-            float v = 0.f;
-            if (kk < 2 * KS) {
-              const int ch = kk >= KS ? 1 : 0, k = kk - ch * KS;
-              v = sm.wcat[ch * Wd + r + k];
-            }
-            v2[q] = v;
-          }
-          const float h0 = bf16_round(v2[0]), h1 = bf16_round(v2[1]);
-          hi[e] = pack_bf16x2(h0, h1);
-          lo[e] = pack_bf16x2(v2[0] - h0, v2[1] - h1);
-        }
-        const uint32_t off = sw128_off(r, chunk);
-        *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-        *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-      }
+      build_im2col(sm.wcat, Wd, KS, jn, a_hi, a_lo);
       fence_proxy_async_smem();
     }
     __syncthreads();
@@ -468,7 +487,7 @@ GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, in
       const int E8 = p.E / 8, Eh8 = (E8 + 1) / 2;
       const int c8_0 = half * Eh8, c8_n = min(E8, c8_0 + Eh8) - c8_0;      // in units of 8 columns
       const int mult = p.mult;
-      bf16* xc = BFP(p.xctx) + (size_t)b * mult * p.Dp;
+      bf16* xc = BFP(p.xctx) + (size_t)b * mult * p.Ep;
       float* call = p.train ? p.ctx_all + ((size_t)t * p.B + b) * p.D : nullptr;
       for (int cb = 0; cb < c8_n; cb += 32) {
         const int c8 = cb + lane;
@@ -496,18 +515,15 @@ GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, in
 #pragma unroll
             for (int w = 0; w < 8; ++w) s += sm.red_s[w * 256 + i];
             const int d = (c8_0 + c8i) * 8 + (i & 7);
-            store_act(xc, d, p.Dp, p.prec, s);
+            store_act(xc, d, p.Ep, p.prec, s);
             if (call) call[d] = s;
           }
         }
       }
       // time-constant columns: context = const * sum_j w_j  (second CTA of the pair)
-      if (half == 1 || Tin == 1) {
-        for (int i = threadIdx.x; i < p.Cc; i += blockDim.x) {
-          const float val = p.mem_const[(size_t)b * p.Cc + i] * wsum;
-          store_act(xc, p.E + i, p.Dp, p.prec, val);
-          if (call) call[p.E + i] = val;
-        }
+      if (call && (half == 1 || Tin == 1)) {
+        // (saved for the weight-gradient GEMMs only: the per-frame GEMMs see these columns as a per-sequence bias)
+        for (int i = threadIdx.x; i < p.Cc; i += blockDim.x) call[p.E + i] = p.mem_const[(size_t)b * p.Cc + i] * wsum;
       }
     }
     __syncthreads();
@@ -548,17 +564,20 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
 
   unsigned int epoch = 0;
   uint32_t acc_par = 0, att_par = 0, round = 0, eround = 0;
+  float wqr[32];
+#pragma unroll
+  for (int u = 0; u < 32; ++u) wqr[u] = 0.f;
   const unsigned int nblocks = gridDim.x;
   int t = 0;
   for (; t < p.n_steps; ++t) {
     if (!p.train) {
-      gemm_phase<N>(p, maps, sm, K_PRE1, t, rank, cid, ncl, tmem_base, acc_par, round);
+      gemm_phase<N>(p, maps, sm, K_PRE1, t, rank, cid, ncl, tmem_base, acc_par, round, wqr);
       grid_sync2(p.barrier, epoch, nblocks);
-      gemm_phase<N>(p, maps, sm, K_PRE2, t, rank, cid, ncl, tmem_base, acc_par, round);
+      gemm_phase<N>(p, maps, sm, K_PRE2, t, rank, cid, ncl, tmem_base, acc_par, round, wqr);
       grid_sync2(p.barrier, epoch, nblocks);
     }
     PROF(0);
-    gemm_phase<N>(p, maps, sm, K_ATT, t, rank, cid, ncl, tmem_base, acc_par, round);
+    gemm_phase<N>(p, maps, sm, K_ATT, t, rank, cid, ncl, tmem_base, acc_par, round, wqr);
     PROF(4);
     grid_sync2(p.barrier, epoch, nblocks);
     PROF(5);
@@ -567,11 +586,11 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
     PROF(6);
     grid_sync2(p.barrier, epoch, nblocks);
     PROF(8);
-    gemm_phase<N>(p, maps, sm, K_DEC, t, rank, cid, ncl, tmem_base, acc_par, round);
+    gemm_phase<N>(p, maps, sm, K_DEC, t, rank, cid, ncl, tmem_base, acc_par, round, wqr);
     PROF(13);
     if (!p.train) {
       grid_sync2(p.barrier, epoch, nblocks);
-      gemm_phase<N>(p, maps, sm, K_PROJ, t, rank, cid, ncl, tmem_base, acc_par, round);
+      gemm_phase<N>(p, maps, sm, K_PROJ, t, rank, cid, ncl, tmem_base, acc_par, round, wqr);
       grid_sync2(p.barrier, epoch, nblocks);
       if (__ldcg(p.stop) != 0) { ++t; break; }
     }
@@ -640,19 +659,20 @@ extern "C" int gtn_decoder_forward2(const gtn_decoder_fwd_params* hp, void* stre
   GTN_REQUIRE(p.Tin >= 1 && p.Tin <= TIN_MAX, "T_in must be in [1, %d]", TIN_MAX);
   GTN_REQUIRE(p.B >= 1 && p.B <= 256 && p.n_steps >= 1, "batch must be in [1, 256]");
   GTN_REQUIRE(p.NM + 1 <= TILE_M, "n_mel + 1 must fit one 128-row tile");
-  GTN_REQUIRE(p.w_att2 && p.w_dec2 && p.u_loc && p.wq_t, "second-generation weight packs missing");
+  GTN_REQUIRE(p.w_att2 && p.w_dec2 && p.u_loc && p.wq_t && p.gbias_a && p.gbias_d, "second-generation weight packs missing");
+  GTN_REQUIRE(p.Ep % 64 == 0 && p.Ep >= p.E && (p.train || p.pbias), "Ep must be E padded to 64 (and pbias set for inference)");
   auto thr = [](float pr) -> unsigned { double t = (double)pr * 4294967296.0; return t >= 4294967295.0 ? 0xFFFFFFFFu : (unsigned)t; };
   p.thr_att = p.use_dropout ? thr(p.p_att) : 0u;
   p.thr_dec = p.use_dropout ? thr(p.p_dec) : 0u;
   const int N = p.B <= 32 ? 32 : (p.B <= 64 ? 64 : (p.B <= 128 ? 128 : 256));
   const int m = p.mult;
-  const long long Ka = (long long)m * (p.Pp + p.Dp + p.Hap), Kd = (long long)m * (p.Hap + p.Dp + p.Hdp);
+  const long long Ka = (long long)m * (p.Pp + p.Ep + p.Hap), Kd = (long long)m * (p.Hap + p.Ep + p.Hdp);
   Fwd2Maps maps;
   int rc = 0;
   rc |= make_tma_map_3d(&maps.w_att, p.w_att2, Ka, 4 * p.Ha, 1, Ka, 0, TILE_M);
   rc |= make_tma_map_3d(&maps.w_dec, p.w_dec2, Kd, 4 * p.Hd, 1, Kd, 0, TILE_M);
   rc |= make_tma_map_3d(&maps.uloc, p.u_loc, 2 * KB, p.A, 1, 2 * KB, 0, TILE_M);
-  rc |= make_tma_map_3d(&maps.ctx, p.xctx, (long long)m * p.Dp, p.B, 1, (long long)m * p.Dp, 0, N);
+  rc |= make_tma_map_3d(&maps.ctx, p.xctx, (long long)m * p.Ep, p.B, 1, (long long)m * p.Ep, 0, N);
   rc |= make_tma_map_3d(&maps.ha, p.xh_a, (long long)m * p.Hap, p.B, 2, (long long)m * p.Hap, (long long)p.B * m * p.Hap, N);
   rc |= make_tma_map_3d(&maps.hd, p.xh_d, (long long)m * p.Hdp, p.B, 2, (long long)m * p.Hdp, (long long)p.B * m * p.Hdp, N);
   if (p.train) {
@@ -661,7 +681,7 @@ extern "C" int gtn_decoder_forward2(const gtn_decoder_fwd_params* hp, void* stre
     maps.w_pre1 = maps.w_pre2 = maps.w_proj = maps.w_att;
     maps.xmel = maps.xp1 = maps.xp2 = maps.ctx;
   } else {
-    const long long Kp = (long long)m * (p.Hdp + p.Dp);
+    const long long Kp = (long long)m * (p.Hdp + p.Ep);
     rc |= make_tma_map_3d(&maps.w_pre1, p.w_pre1, (long long)m * p.NMp, p.P, 1, (long long)m * p.NMp, 0, TILE_M);
     rc |= make_tma_map_3d(&maps.w_pre2, p.w_pre2, (long long)m * p.Pp, p.P, 1, (long long)m * p.Pp, 0, TILE_M);
     rc |= make_tma_map_3d(&maps.w_proj, p.w_proj, Kp, p.NM + 1, 1, Kp, 0, TILE_M);

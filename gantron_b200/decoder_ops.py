@@ -52,6 +52,8 @@ class PackedDecoder:
     def __init__(self, dec: torch.nn.Module, dims: DecoderDims, prec: int):
         self.dims, self.prec = dims, prec
         self._versions = None
+        import weakref
+        self._dec = weakref.ref(dec)
         self.refresh(dec)
 
     @staticmethod
@@ -96,9 +98,6 @@ class PackedDecoder:
         self.wdense = f(P["wdense"]).contiguous()
         self.wmem = f(P["wmem"]).contiguous()
         # ---- second-generation (clustered tcgen05) kernel packs ----
-        # LSTM weight rows regrouped per 32-unit tile: row tile*128 + gate*32 + u  <-  gate*H + 32*tile + u
-        self.w_att2 = _tile_rows(self.w_att, d.att_rnn)
-        self.w_dec2 = _tile_rows(self.w_dec, d.dec_rnn)
         # location conv (F,2,KS) and dense (A,F) pre-multiplied: U[a][ch*KS + k] = sum_c dense[a][c] conv[c][ch][k]
         U = self.wdense @ self.wconv.reshape(d.loc_filters, 2 * d.loc_kernel)
         Up = torch.zeros(d.att_dim, 64, device=U.device)
@@ -119,6 +118,51 @@ def linear_nt(x: torch.Tensor, w: torch.Tensor, prec: int, bias: Optional[torch.
     out = torch.empty(M, N, device=x.device, dtype=out_dtype)
     ops.gemm(xa, wa, out, bias_n=bias)
     return out
+
+
+class PackV2:
+    """Weight packs of the second-generation kernels for a given split of `memory` into E time-varying and
+    D - E time-constant columns.  The constant columns never enter a per-frame GEMM: their products with the
+    (per-sequence constant) context are folded into per-sequence biases (`seq_biases`)."""
+
+    def __init__(self, dec, pk: "PackedDecoder", E: int):
+        d, prec = pk.dims, pk.prec
+        P = PackedDecoder._params(dec)
+        f = lambda t: t.detach().float()
+        self.E, self.Ep, self.versions = E, pad_to(E, 64), pk._versions
+        Pn, Ha, Hd = d.prenet, d.att_rnn, d.dec_rnn
+        wa, wha, wd, whd = f(P["w_ih_a"]), f(P["w_hh_a"]), f(P["w_ih_d"]), f(P["w_hh_d"])
+        wpg = torch.cat((f(P["w_proj"]), f(P["w_gate"])), 0)
+        self.w_att2 = _tile_rows(packing.pack_weight([(wa[:, :Pn], d.Pp), (wa[:, Pn:Pn + E], self.Ep), (wha, d.Hap)], prec), Ha)
+        self.w_dec2 = _tile_rows(packing.pack_weight([(wd[:, :Ha], d.Hap), (wd[:, Ha:Ha + E], self.Ep), (whd, d.Hdp)], prec), Hd)
+        self.w_proj2 = packing.pack_weight([(wpg[:, :Hd], d.Hdp), (wpg[:, Hd:Hd + E], self.Ep)], prec)
+        self.wa_const = wa[:, Pn + E:].contiguous()
+        self.wd_const = wd[:, Ha + E:].contiguous()
+        self.wp_const = wpg[:, Hd + E:].contiguous()
+        self.b_att, self.b_dec, self.b_proj = pk.b_att, pk.b_dec, pk.b_proj
+
+    def seq_biases(self, mem_const: torch.Tensor, prec: int, B: int, want_proj: bool):
+        """gbias_a / gbias_d [B][H][4] and pbias [B][n_mel+1]: bias + W[:, const columns] . mem_const[b]."""
+        def one(wc, bias):
+            if wc.shape[1] == 0:
+                return bias[None, :].expand(B, -1)
+            return linear_nt(mem_const, wc, prec, bias=bias)
+        ga = one(self.wa_const, self.b_att)
+        gd = one(self.wd_const, self.b_dec)
+        ga = ga.reshape(B, 4, -1).permute(0, 2, 1).contiguous()
+        gd = gd.reshape(B, 4, -1).permute(0, 2, 1).contiguous()
+        pb = one(self.wp_const, self.b_proj).contiguous() if want_proj else None
+        return ga, gd, pb
+
+
+def pack_v2(dec, pk: "PackedDecoder", E: int) -> PackV2:
+    cache = getattr(pk, "_v2", None)
+    if cache is None or cache.get("versions") != pk._versions:
+        cache = {"versions": pk._versions}
+        pk._v2 = cache
+    if E not in cache:
+        cache[E] = PackV2(dec, pk, E)
+    return cache[E]
 
 
 def _tile_rows(w: torch.Tensor, H: int) -> torch.Tensor:
@@ -145,14 +189,26 @@ def _fill_common(p: _lib.DecoderFwdParams, d: DecoderDims, pk: PackedDecoder, B:
     p.prec = prec
     p.prof = PROF_BUFFER.data_ptr() if PROF_BUFFER is not None else None
     for name in ("w_att", "w_dec", "w_proj", "w_pre1", "w_pre2", "b_att", "b_dec", "b_proj", "wq", "v", "wconv", "wdense",
-                 "w_att2", "w_dec2", "u_loc", "wq_t"):
+                 "u_loc", "wq_t"):
         setattr(p, name, getattr(pk, name).data_ptr())
 
 
-def _alloc_state(p: _lib.DecoderFwdParams, d: DecoderDims, B: int, mult: int, dev) -> Dict[str, torch.Tensor]:
+def _fill_v2(p: _lib.DecoderFwdParams, v2: PackV2, mem_const: torch.Tensor, prec: int, B: int, want_proj: bool):
+    """Second-generation packs + per-sequence biases; returns the tensors that must stay alive during the launch."""
+    ga, gd, pb = v2.seq_biases(mem_const, prec, B, want_proj)
+    p.w_att2, p.w_dec2, p.Ep = v2.w_att2.data_ptr(), v2.w_dec2.data_ptr(), v2.Ep
+    p.w_proj = v2.w_proj2.data_ptr()
+    p.gbias_a, p.gbias_d = ga.data_ptr(), gd.data_ptr()
+    p.pbias = pb.data_ptr() if pb is not None else None
+    return ga, gd, pb
+
+
+def _alloc_state(p: _lib.DecoderFwdParams, d: DecoderDims, B: int, mult: int, dev, ctx_cols: Optional[int] = None
+                 ) -> Dict[str, torch.Tensor]:
     z = lambda *s, dt=torch.float32: torch.zeros(*s, device=dev, dtype=dt)
     st = dict(
-        xh_a=z(2, B, mult * d.Hap, dt=BF16), xh_d=z(2, B, mult * d.Hdp, dt=BF16), xctx=z(B, mult * d.Dp, dt=BF16),
+        xh_a=z(2, B, mult * d.Hap, dt=BF16), xh_d=z(2, B, mult * d.Hdp, dt=BF16),
+        xctx=z(B, mult * (ctx_cols or d.Dp), dt=BF16),
         xmel=z(B, mult * d.NMp, dt=BF16), xp1=z(B, mult * d.Pp, dt=BF16), xp2=z(B, mult * d.Pp, dt=BF16),
         c_a=z(B, d.att_rnn), c_d=z(B, d.dec_rnn), w_prev=z(B, p.ldT), w_cum=z(B, p.ldT),
         qpart=z(d.att_rnn // 8, B, d.att_dim), barrier=z(4, dt=torch.int32), done=z(B, dt=torch.int32),
@@ -193,7 +249,8 @@ def decoder_inference(pk: PackedDecoder, memory: torch.Tensor, *, max_steps: int
     p.p_att = p.p_dec = 0.0
     p.gate_threshold = gate_threshold
     p.seed = seed
-    st = _alloc_state(p, d, B, mult, dev)
+    v2 = decoder_version() >= 2
+    st = _alloc_state(p, d, B, mult, dev, pad_to(E, 64) if v2 else None)
     memory = memory.float()
     pm = linear_nt(memory.reshape(B * Tin, D), pk.wmem, prec).reshape(B, Tin, d.att_dim)
     mem_enc = memory[:, :, :E].to(mdt).contiguous()
@@ -205,7 +262,8 @@ def decoder_inference(pk: PackedDecoder, memory: torch.Tensor, *, max_steps: int
     p.mem_enc, p.pm, p.mem_const = mem_enc.data_ptr(), pm.data_ptr(), mem_const.data_ptr()
     p.lengths = None
     p.align_out, p.mel_out, p.gate_out = align.data_ptr(), mel.data_ptr(), gate.data_ptr()
-    if decoder_version() >= 2:
+    if v2:
+        keep = _fill_v2(p, pack_v2(pk._dec(), pk, E), mem_const[:, :D - E], prec, B, True)   # noqa: F841 (kept alive)
         _lib.check(_lib.load().gtn_decoder_forward2(C.byref(p), _lib.stream()), "gtn_decoder_forward2")
     else:
         _lib.check(_lib.load().gtn_decoder_forward(C.byref(p), _lib.stream()), "gtn_decoder_forward")
@@ -333,7 +391,7 @@ class _DecoderTrainFn(torch.autograd.Function):
         p.p_att, p.p_dec = dec.p_attention_dropout, dec.p_decoder_dropout
         p.gate_threshold = dec.gate_threshold
         p.seed = seed
-        st = _alloc_state(p, d, B, mult, dev)
+        st = _alloc_state(p, d, B, mult, dev, pad_to(E, 64) if TRAIN_FWD2 else None)
         mem_enc = memory_f[:, :, :E].to(mdt).contiguous()
         mem_const = memory_f[:, 0, E:].contiguous() if E < D else torch.zeros(B, 1, device=dev)
         pm_k = pm.to(mdt).contiguous()
@@ -354,6 +412,7 @@ class _DecoderTrainFn(torch.autograd.Function):
         p.q_all, p.th_all, p.f_all, p.cum_all = (sv["q_all"].data_ptr(), sv["th_all"].data_ptr(), sv["f_all"].data_ptr(),
                                                  sv["cum_all"].data_ptr())
         if TRAIN_FWD2:
+            keep = _fill_v2(p, pack_v2(dec, pk, E), mem_const[:, :D - E], prec, B, False)   # noqa: F841 (kept alive)
             _lib.check(_lib.load().gtn_decoder_forward2(C.byref(p), _lib.stream()), "gtn_decoder_forward2")
         else:
             _lib.check(_lib.load().gtn_decoder_forward(C.byref(p), _lib.stream()), "gtn_decoder_forward")

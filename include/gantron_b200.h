@@ -25,7 +25,8 @@ long long gtn_launch_count(void);
 void gtn_reset_launch_count(void);
 /* fills sm_count, cc_major, cc_minor, cooperative-launch support of the current device */
 int gtn_device_info(int* sm_count, int* cc_major, int* cc_minor, int* coop);
-/* sizeof() of an ABI struct, for binding self-checks: which = 0 gtn_decoder_fwd_params, 1 gtn_decoder_bwd_params */
+/* sizeof() of an ABI struct, for binding self-checks: which = 0 gtn_decoder_fwd_params, 1 gtn_decoder_bwd_params,
+ * 2 gtn_decoder_bwd2_params */
 int gtn_sizeof(int which);
 
 /* ---- tcgen05 GEMM family (gtn_gemm.cu) ------------------------------------------------------
@@ -191,12 +192,20 @@ typedef struct gtn_decoder_fwd_params {
   const void *u_loc;                    /* bf16 [A][128]: location conv x dense pre-multiplied, U[a][ch*KS+k], hi | lo planes */
   const float *wq_t;                    /* [Ha][A] = query_layer weight transposed */
   long long *prof;                      /* optional [16][32] clock64() stamps of CTA 0 for the first 16 frames (NULL = off) */
+  /* forward2 drops the time-constant memory columns from every per-frame GEMM: their contribution to the LSTM
+   * gates / projection is a per-sequence bias computed once (context_const = mem_const * sum_j w_j, sum_j w_j = 1):
+   *   K(att) = [prenet Pp | ctx_enc Ep | h_att Hap], K(dec) = [h_att | ctx_enc Ep | h_dec], K(proj) = [h_dec | ctx_enc Ep],
+   *   xctx is [B][mult*Ep], Ep = pad64(E). */
+  const float *gbias_a, *gbias_d;       /* [B][H][4] (i,f,g,o): bias_ih + bias_hh + W[:, const cols] . mem_const[b] */
+  const float *pbias;                   /* [B][NM+1]: projection / gate bias + W[:, const cols] . mem_const[b] (inference) */
+  int Ep, reserved0;
 } gtn_decoder_fwd_params;
 
 int gtn_decoder_forward(const gtn_decoder_fwd_params* params, void* stream);
 /* Same contract, second generation: clusters of 4 CTAs split K of every per-frame GEMM and run it on tcgen05 with
  * TMA-fed operands (gtn_decoder_fwd2.cu); requires all K pads to be multiples of 64 and qpart sized [Ha/32][B][A].
- * Does not write f_all (the location filter is pre-multiplied; the backward pass works on U). */
+ * Does not write f_all (the location filter is pre-multiplied; the backward pass works on U); gates_a / gates_d are
+ * saved as [T][B][H][4] (i,f,g,o per unit). */
 int gtn_decoder_forward2(const gtn_decoder_fwd_params* params, void* stream);
 
 /* ---- persistent cooperative decoder, backward through time (gtn_decoder_bwd.cu) -----------------
@@ -249,6 +258,60 @@ typedef struct gtn_decoder_bwd_params {
 
 int gtn_decoder_bwd_grid(void);   /* number of CTAs gtn_decoder_backward launches on the current device */
 int gtn_decoder_backward(const gtn_decoder_bwd_params* params, void* stream);
+
+/* ---- persistent clustered decoder, backward through time, second generation (gtn_decoder_bwd2.cu) ----
+ * Counterpart of gtn_decoder_forward2 (same cluster-split tcgen05 GEMM engine).  Per frame t = T-1 .. 0:
+ *   P1  dX_dec = W_dec^T dGates_dec(t) (rows [h_att | ctx_enc | h_dec]) and dX_att = W_att^T dGates_att(t+1)
+ *       (rows [ctx_enc | h_att]); the decoder LSTM cell backward of frame t-1 is fused into the h_dec rows' epilogue
+ *   P2  attention backward per sequence; d[prev | cum] = dth . U and dU += dth^T . im2col on tcgen05
+ *   P3  Wq^T dq + attention LSTM cell backward
+ * Not computed per frame (the host derives them with K = T*B GEMMs from dga_all / dgd_all): prenet-output gradients,
+ * gradients w.r.t. the time-constant memory columns, every weight gradient.  Replaces autograd's replay of the
+ * ~22k-node tape of model.py:444-449. */
+typedef struct gtn_decoder_bwd2_params {
+  int B, Tin, ldT, T;
+  int E, Ep, D, Ha, Hd, A, KS;
+  int prec, mult;
+  int use_dropout, mem_bf16;
+  int grid;                  /* = gtn_decoder_bwd2_grid(B, Ha, Hd, E): sizes dv_part / dU_part */
+  float p_att, p_dec;
+  unsigned int thr_att, thr_dec;
+  unsigned long long seed;
+  /* weights */
+  const void *wT_att2;       /* bf16 [E + Ha][mult*4Ha]: rows = attention_rnn inputs [ctx_enc | h_att], K = gate rows g*Ha+u */
+  const void *wT_dec2;       /* bf16 [Ha + E + Hd][mult*4Hd]: rows = decoder_rnn inputs [h_att | ctx_enc | h_dec] */
+  const void *ut_loc;        /* bf16 [64][256]: U^T[kk][a], hi plane (a 0..127) | lo plane; U = location dense x conv */
+  const float *wq_t;         /* [Ha][A] */
+  const float *v;            /* [A] */
+  /* forward inputs / saved by gtn_decoder_forward2 */
+  const void *mem_enc; const int *lengths;
+  const float *gates_a, *c_a_all, *gates_d, *c_d_all;    /* [T][B][H][4], [T][B][H] */
+  const float *align;        /* [B][T][Tin] */
+  const float *th_all;       /* [T][B][Tin][A] */
+  const float *cum_all;      /* [T][B][Tin] */
+  /* upstream gradients */
+  const float *dproj_all;    /* [T][B][Hd + D]: d(loss)/d[h_dec' | ctx'] through the mel/gate projection */
+  const float *dalign;       /* [B][T][Tin] or NULL */
+  /* carried state / workspace (zero-initialised) */
+  void *xdg_a;               /* bf16 [B][mult*4Ha] */
+  void *xdg_d;               /* bf16 [2][B][mult*4Hd] */
+  float *carry_ha, *dha_dec, *dc_a;     /* [B][Ha] */
+  float *dc_d;                          /* [B][Hd] */
+  float *dctx_att, *dctx_dec;           /* [B][Ep] */
+  float *dwprev, *dcum;                 /* [B][ldT] */
+  float *dq_sum;                        /* [B][A] */
+  unsigned int *barrier;
+  /* outputs */
+  float *dga_all, *dgd_all;  /* [T][B][4Ha], [T][B][4Hd] pre-activation gate gradients (gate-major) */
+  float *dq_all;             /* [T][B][A] */
+  float *dctx_all;           /* [B][T][E] total gradient of the time-varying context columns per frame */
+  float *dpm;                /* [B][Tin][A] gradient w.r.t. processed_memory (accumulated over frames) */
+  float *dv_part;            /* [grid][A] */
+  float *dU_part;            /* [grid][128][64]: per-CTA partial of dU[a][ch*KS+k] */
+} gtn_decoder_bwd2_params;
+
+int gtn_decoder_bwd2_grid(int B, int Ha, int Hd, int E);   /* CTAs gtn_decoder_backward2 launches, or -1 */
+int gtn_decoder_backward2(const gtn_decoder_bwd2_params* params, void* stream);
 
 #ifdef __cplusplus
 }
