@@ -141,6 +141,28 @@ class PackV2:
         self.wp_const = wpg[:, Hd + E:].contiguous()
         self.b_att, self.b_dec, self.b_proj = pk.b_att, pk.b_dec, pk.b_proj
 
+    def backward_packs(self, dec, pk: "PackedDecoder"):
+        """Transposed packs of the BPTT kernel (rows = LSTM input features without the prenet rows and without the
+        time-constant context columns; K = gate rows g*H + u) and U^T for d[prev | cum] = dth . U."""
+        if getattr(self, "_bwd", None) is None:
+            d, prec = pk.dims, pk.prec
+            P = PackedDecoder._params(dec)
+            f = lambda t: t.detach().float()
+            E, Pn, Ha, Hd = self.E, d.prenet, d.att_rnn, d.dec_rnn
+            wa, wha, wd, whd = f(P["w_ih_a"]), f(P["w_hh_a"]), f(P["w_ih_d"]), f(P["w_hh_d"])
+            wta = torch.cat((wa[:, Pn:Pn + E], wha), 1).t().contiguous()                 # [E + Ha][4Ha]
+            wtd = torch.cat((wd[:, :Ha + E], whd), 1).t().contiguous()                   # [Ha + E + Hd][4Hd]
+            U = pk.wdense @ pk.wconv.reshape(d.loc_filters, 2 * d.loc_kernel)            # [A][2KS]
+            UT = torch.zeros(64, 128, device=U.device)
+            UT[:2 * d.loc_kernel, :d.att_dim] = U.t()
+            hi = UT.to(BF16)
+            self._bwd = dict(
+                wT_att2=packing.pack_weight([(wta, 4 * Ha)], prec), wT_dec2=packing.pack_weight([(wtd, 4 * Hd)], prec),
+                ut_loc=torch.cat((hi, (UT - hi.float()).to(BF16)), 1).contiguous(),       # [64][hi 128 | lo 128]
+                wa_pre_T=wa[:, :Pn].t().contiguous(),                                     # [P][4Ha]
+                wa_const_T=self.wa_const.t().contiguous(), wd_const_T=self.wd_const.t().contiguous())
+        return self._bwd
+
     def seq_biases(self, mem_const: torch.Tensor, prec: int, B: int, want_proj: bool):
         """gbias_a / gbias_d [B][H][4] and pbias [B][n_mel+1]: bias + W[:, const columns] . mem_const[b]."""
         def one(wc, bias):
@@ -176,7 +198,6 @@ def decoder_version() -> int:
     return int(os.environ.get("GANTRON_B200_DECODER", "2"))
 
 
-TRAIN_FWD2 = False     # dev switch until the second-generation backward kernel lands
 PROF_BUFFER = None     # dev tool: int64 [16*32] device tensor receiving clock64() stamps of CTA 0 (tools/time_infer.py)
 
 
@@ -310,16 +331,18 @@ def _rows8(t: torch.Tensor) -> torch.Tensor:
 class _PackedBackward:
     """Transposed packs used by the backward kernel; built lazily next to PackedDecoder."""
 
-    def __init__(self, dec, pk: PackedDecoder):
+    def __init__(self, dec, pk: PackedDecoder, v1: bool):
         d, prec = pk.dims, pk.prec
         P = PackedDecoder._params(dec)
         f = lambda t: t.detach().float()
-        wa = torch.cat((f(P["w_ih_a"]), f(P["w_hh_a"])), 1).t().contiguous()     # [P+D+Ha][4Ha]
-        wd = torch.cat((f(P["w_ih_d"]), f(P["w_hh_d"])), 1).t().contiguous()     # [Ha+D+Hd][4Hd]
-        self.wT_att = packing.pack_weight([(wa, 4 * d.att_rnn)], prec, row_pad=pad_to(wa.shape[0], 32))
-        self.wT_dec = packing.pack_weight([(wd, 4 * d.dec_rnn)], prec, row_pad=pad_to(wd.shape[0], 32))
-        self.Ap = pad_to(d.att_dim, 32)
-        self.wqT = packing.pack_weight([(f(P["wq"]).t().contiguous(), self.Ap)], prec, row_pad=pad_to(d.att_rnn, 32))
+        self.v1 = v1
+        if v1:   # transposed LSTM / query packs of the first-generation BPTT kernel
+            wa = torch.cat((f(P["w_ih_a"]), f(P["w_hh_a"])), 1).t().contiguous()     # [P+D+Ha][4Ha]
+            wd = torch.cat((f(P["w_ih_d"]), f(P["w_hh_d"])), 1).t().contiguous()     # [Ha+D+Hd][4Hd]
+            self.wT_att = packing.pack_weight([(wa, 4 * d.att_rnn)], prec, row_pad=pad_to(wa.shape[0], 32))
+            self.wT_dec = packing.pack_weight([(wd, 4 * d.dec_rnn)], prec, row_pad=pad_to(wd.shape[0], 32))
+            self.Ap = pad_to(d.att_dim, 32)
+            self.wqT = packing.pack_weight([(f(P["wq"]).t().contiguous(), self.Ap)], prec, row_pad=pad_to(d.att_rnn, 32))
         wpg = torch.cat((f(P["w_proj"]), f(P["w_gate"])), 0)                       # [n_mel+1][Hd+D]
         self.wpgT = wpg.t().contiguous()                                           # [Hd+D][n_mel+1]
         self.wmemT = f(P["wmem"]).t().contiguous()                                 # [D][A]
@@ -327,10 +350,10 @@ class _PackedBackward:
         self.versions = pk._versions
 
 
-def _packed_bwd(dec, pk: PackedDecoder) -> _PackedBackward:
+def _packed_bwd(dec, pk: PackedDecoder, v1: bool = True) -> _PackedBackward:
     pb = getattr(pk, "_bwd", None)
-    if pb is None or pb.versions != pk._versions:
-        pb = _PackedBackward(dec, pk)
+    if pb is None or pb.versions != pk._versions or (v1 and not pb.v1):
+        pb = _PackedBackward(dec, pk, v1)
         pk._bwd = pb
     return pb
 
@@ -391,7 +414,8 @@ class _DecoderTrainFn(torch.autograd.Function):
         p.p_att, p.p_dec = dec.p_attention_dropout, dec.p_decoder_dropout
         p.gate_threshold = dec.gate_threshold
         p.seed = seed
-        st = _alloc_state(p, d, B, mult, dev, pad_to(E, 64) if TRAIN_FWD2 else None)
+        v2 = decoder_version() >= 2
+        st = _alloc_state(p, d, B, mult, dev, pad_to(E, 64) if v2 else None)
         mem_enc = memory_f[:, :, :E].to(mdt).contiguous()
         mem_const = memory_f[:, 0, E:].contiguous() if E < D else torch.zeros(B, 1, device=dev)
         pm_k = pm.to(mdt).contiguous()
@@ -402,7 +426,7 @@ class _DecoderTrainFn(torch.autograd.Function):
             gates_a=e(T, B, 4 * d.att_rnn), c_a_all=e(T, B, d.att_rnn), h_a_buf=z(T + 1, B, d.att_rnn),
             gates_d=e(T, B, 4 * d.dec_rnn), c_d_all=e(T, B, d.dec_rnn), h_d_buf=z(T + 1, B, d.dec_rnn),
             ctx_buf=z(T + 1, B, D), q_all=e(T, B, d.att_dim), th_all=e(T, B, Tin, d.att_dim),
-            f_all=e(T, B, Tin, d.loc_filters), cum_all=e(T, B, Tin), align=z(B, T, Tin))
+            f_all=e(T, B, Tin, d.loc_filters) if not v2 else e(1), cum_all=e(T, B, Tin), align=z(B, T, Tin))
         p.mem_enc, p.pm, p.mem_const, p.lengths = mem_enc.data_ptr(), pm_k.data_ptr(), mem_const.data_ptr(), lengths.data_ptr()
         p.pre_all = pre_x.data_ptr()
         p.align_out = sv["align"].data_ptr()
@@ -411,7 +435,7 @@ class _DecoderTrainFn(torch.autograd.Function):
         p.ctx_all = sv["ctx_buf"][1:].data_ptr()
         p.q_all, p.th_all, p.f_all, p.cum_all = (sv["q_all"].data_ptr(), sv["th_all"].data_ptr(), sv["f_all"].data_ptr(),
                                                  sv["cum_all"].data_ptr())
-        if TRAIN_FWD2:
+        if v2:
             keep = _fill_v2(p, pack_v2(dec, pk, E), mem_const[:, :D - E], prec, B, False)   # noqa: F841 (kept alive)
             _lib.check(_lib.load().gtn_decoder_forward2(C.byref(p), _lib.stream()), "gtn_decoder_forward2")
         else:
@@ -433,6 +457,7 @@ class _DecoderTrainFn(torch.autograd.Function):
 
         ctx.dec, ctx.seed, ctx.training = dec, seed, training
         ctx.dims = (B, Tin, D, T, E, prec)
+        ctx.v2 = v2
         ctx.saved = dict(sv=sv, frames2=frames2, h1=h1, pre=pre, memory_f=memory_f, mem_enc=mem_enc, mem_const=mem_const,
                          lengths=lengths, out_cl=out_cl)
         return mel, gate, align
@@ -441,7 +466,7 @@ class _DecoderTrainFn(torch.autograd.Function):
     def backward(ctx, d_mel, d_gate, d_align):
         dec = ctx.dec
         pk = dec.packed()
-        pb = _packed_bwd(dec, pk)
+        pb = _packed_bwd(dec, pk, v1=not ctx.v2)
         d = pk.dims
         B, Tin, D, T, E, prec = ctx.dims
         mult = packing.mult_of(prec)
@@ -461,41 +486,44 @@ class _DecoderTrainFn(torch.autograd.Function):
         # hoisted projection backward: d[h_dec'|ctx'] for every frame
         dproj = linear_nt(dout2, pb.wpgT, prec)                                   # [TB][Hd+D]
 
-        q = _lib.DecoderBwdParams()
-        q.B, q.Tin, q.ldT, q.T = B, Tin, pad_to(Tin, 4), T
-        q.E, q.Cc, q.D, q.Ha, q.Hd, q.P, q.A, q.Ap, q.F, q.KS = (E, D - E, D, d.att_rnn, d.dec_rnn, d.prenet, d.att_dim,
-                                                               pb.Ap, d.loc_filters, d.loc_kernel)
-        q.prec = prec
-        q.use_dropout = int(ctx.training)
-        q.mem_bf16 = int(S["mem_enc"].dtype == BF16)
-        q.p_att, q.p_dec, q.seed = dec.p_attention_dropout, dec.p_decoder_dropout, ctx.seed
-        grid = _lib.load().gtn_decoder_bwd_grid()
-        q.grid = grid
-        wk = dict(
-            xdg_a=z(B, mult * 4 * d.att_rnn, dt=BF16), xdg_d=z(B, mult * 4 * d.dec_rnn, dt=BF16), xdq=z(B, mult * pb.Ap, dt=BF16),
-            carry_ha=z(B, d.att_rnn), dha_dec=z(B, d.att_rnn), dc_a=z(B, d.att_rnn), carry_hd=z(B, d.dec_rnn),
-            dc_d=z(B, d.dec_rnn), dctx_att=z(B, D), dctx_dec=z(B, D), dwprev=z(B, q.ldT), dcum=z(B, q.ldT),
-            barrier=z(4, dt=torch.int32),
-            dga_all=torch.empty(T, B, 4 * d.att_rnn, device=dev), dgd_all=torch.empty(T, B, 4 * d.dec_rnn, device=dev),
-            dq_all=torch.empty(T, B, d.att_dim, device=dev), dpre_all=torch.empty(T, B, d.prenet, device=dev),
-            dctx_all=torch.empty(B, T, D, device=dev), dpm=z(B, Tin, d.att_dim),
-            dv_part=z(grid, d.att_dim), dwd_part=z(grid, d.att_dim * d.loc_filters),
-            dwc_part=z(grid, 2 * d.loc_filters * d.loc_kernel))
-        for k, v in wk.items():
-            setattr(q, k, v.data_ptr())
-        q.wT_att, q.wT_dec, q.wqT = pb.wT_att.data_ptr(), pb.wT_dec.data_ptr(), pb.wqT.data_ptr()
-        q.v, q.wconv, q.wdense = pk.v.data_ptr(), pk.wconv.data_ptr(), pk.wdense.data_ptr()
-        q.mem_enc, q.mem_const, q.lengths = S["mem_enc"].data_ptr(), S["mem_const"].data_ptr(), S["lengths"].data_ptr()
-        q.gates_a, q.c_a_all, q.gates_d, q.c_d_all = (sv["gates_a"].data_ptr(), sv["c_a_all"].data_ptr(),
-                                                      sv["gates_d"].data_ptr(), sv["c_d_all"].data_ptr())
-        q.align, q.th_all, q.f_all, q.cum_all = (sv["align"].data_ptr(), sv["th_all"].data_ptr(), sv["f_all"].data_ptr(),
-                                                 sv["cum_all"].data_ptr())
-        q.dproj_all = dproj.data_ptr()
-        d_align_c = None
-        if d_align is not None:
-            d_align_c = d_align.float().contiguous()
-            q.dalign = d_align_c.data_ptr()
-        _lib.check(_lib.load().gtn_decoder_backward(C.byref(q), _lib.stream()), "gtn_decoder_backward")
+        if ctx.v2:
+            wk = _bptt_v2(dec, pk, d, ctx, S, sv, dproj, d_align, prec)
+        else:
+            q = _lib.DecoderBwdParams()
+            q.B, q.Tin, q.ldT, q.T = B, Tin, pad_to(Tin, 4), T
+            q.E, q.Cc, q.D, q.Ha, q.Hd, q.P, q.A, q.Ap, q.F, q.KS = (E, D - E, D, d.att_rnn, d.dec_rnn, d.prenet, d.att_dim,
+                                                                   pb.Ap, d.loc_filters, d.loc_kernel)
+            q.prec = prec
+            q.use_dropout = int(ctx.training)
+            q.mem_bf16 = int(S["mem_enc"].dtype == BF16)
+            q.p_att, q.p_dec, q.seed = dec.p_attention_dropout, dec.p_decoder_dropout, ctx.seed
+            grid = _lib.load().gtn_decoder_bwd_grid()
+            q.grid = grid
+            wk = dict(
+                xdg_a=z(B, mult * 4 * d.att_rnn, dt=BF16), xdg_d=z(B, mult * 4 * d.dec_rnn, dt=BF16), xdq=z(B, mult * pb.Ap, dt=BF16),
+                carry_ha=z(B, d.att_rnn), dha_dec=z(B, d.att_rnn), dc_a=z(B, d.att_rnn), carry_hd=z(B, d.dec_rnn),
+                dc_d=z(B, d.dec_rnn), dctx_att=z(B, D), dctx_dec=z(B, D), dwprev=z(B, q.ldT), dcum=z(B, q.ldT),
+                barrier=z(4, dt=torch.int32),
+                dga_all=torch.empty(T, B, 4 * d.att_rnn, device=dev), dgd_all=torch.empty(T, B, 4 * d.dec_rnn, device=dev),
+                dq_all=torch.empty(T, B, d.att_dim, device=dev), dpre_all=torch.empty(T, B, d.prenet, device=dev),
+                dctx_all=torch.empty(B, T, D, device=dev), dpm=z(B, Tin, d.att_dim),
+                dv_part=z(grid, d.att_dim), dwd_part=z(grid, d.att_dim * d.loc_filters),
+                dwc_part=z(grid, 2 * d.loc_filters * d.loc_kernel))
+            for k, v in wk.items():
+                setattr(q, k, v.data_ptr())
+            q.wT_att, q.wT_dec, q.wqT = pb.wT_att.data_ptr(), pb.wT_dec.data_ptr(), pb.wqT.data_ptr()
+            q.v, q.wconv, q.wdense = pk.v.data_ptr(), pk.wconv.data_ptr(), pk.wdense.data_ptr()
+            q.mem_enc, q.mem_const, q.lengths = S["mem_enc"].data_ptr(), S["mem_const"].data_ptr(), S["lengths"].data_ptr()
+            q.gates_a, q.c_a_all, q.gates_d, q.c_d_all = (sv["gates_a"].data_ptr(), sv["c_a_all"].data_ptr(),
+                                                          sv["gates_d"].data_ptr(), sv["c_d_all"].data_ptr())
+            q.align, q.th_all, q.f_all, q.cum_all = (sv["align"].data_ptr(), sv["th_all"].data_ptr(), sv["f_all"].data_ptr(),
+                                                     sv["cum_all"].data_ptr())
+            q.dproj_all = dproj.data_ptr()
+            d_align_c = None
+            if d_align is not None:
+                d_align_c = d_align.float().contiguous()
+                q.dalign = d_align_c.data_ptr()
+            _lib.check(_lib.load().gtn_decoder_backward(C.byref(q), _lib.stream()), "gtn_decoder_backward")
 
         # ---- deferred weight gradients: K = T*B GEMMs on MN-major operands --------------------------------
         TB = T * B
@@ -543,13 +571,76 @@ class _DecoderTrainFn(torch.autograd.Function):
             g_memory = linear_nt(dpm2, pb.wmemT, prec).reshape(B, Tin, D)        # through processed_memory
             _ctx_memory_grad(sv["align"], wk["dctx_all"], g_memory, prec)        # through the context bmm
         g_v = wk["dv_part"].sum(0).reshape(1, -1)
-        g_wd = wk["dwd_part"].sum(0).reshape(d.att_dim, d.loc_filters)
-        g_wc = wk["dwc_part"].sum(0).reshape(d.loc_filters, 2, d.loc_kernel)
+        if ctx.v2:
+            # chain rule through the pre-multiplied location filter U[a][ch*KS+k] = sum_c dense[a][c] conv[c][ch][k]
+            dU = wk["dU_part"].sum(0)[:d.att_dim, :2 * d.loc_kernel]
+            g_wd = dU @ pk.wconv.reshape(d.loc_filters, 2 * d.loc_kernel).t()
+            g_wc = (pk.wdense.t() @ dU).reshape(d.loc_filters, 2, d.loc_kernel)
+        else:
+            g_wd = wk["dwd_part"].sum(0).reshape(d.att_dim, d.loc_filters)
+            g_wc = wk["dwc_part"].sum(0).reshape(d.loc_filters, 2, d.loc_kernel)
         grads = [g_w_ih_a, g_w_hh_a, g_b_a, g_b_a.clone(), g_w_ih_d, g_w_hh_d, g_b_d, g_b_d.clone(),
                  g_wpg[:d.n_mel].contiguous(), g_bpg[:d.n_mel].contiguous(), g_wpg[d.n_mel:].contiguous(),
                  g_bpg[d.n_mel:].contiguous(), g_w_pre1, g_w_pre2, g_wq, g_wmem, g_v, g_wc, g_wd]
         ctx.saved = None
         return (None, None, g_memory, None, None) + tuple(grads)
+
+
+def _bptt_v2(dec, pk, d, ctx, S, sv, dproj, d_align, prec):
+    """Launch gtn_decoder_backward2 and derive what it leaves to K = T*B GEMMs: prenet-output gradients and the
+    gradients of the time-constant context columns.  Returns the same dict layout as the v1 path."""
+    B, Tin, D, T, E, _ = ctx.dims
+    mult = packing.mult_of(prec)
+    dev = sv["align"].device
+    v2p = pack_v2(dec, pk, E)
+    bp = v2p.backward_packs(dec, pk)
+    Ha, Hd, A, Ep = d.att_rnn, d.dec_rnn, d.att_dim, v2p.Ep
+    z = lambda *s, dt=torch.float32: torch.zeros(*s, device=dev, dtype=dt)
+    lib = _lib.load()
+    grid = lib.gtn_decoder_bwd2_grid(B, Ha, Hd, E)
+    if grid <= 0:
+        raise RuntimeError("gtn_decoder_bwd2_grid failed: " + _lib.last_error())
+    q = _lib.DecoderBwd2Params()
+    q.B, q.Tin, q.ldT, q.T = B, Tin, pad_to(Tin, 4), T
+    q.E, q.Ep, q.D, q.Ha, q.Hd, q.A, q.KS = E, Ep, D, Ha, Hd, A, d.loc_kernel
+    q.prec, q.use_dropout, q.mem_bf16, q.grid = prec, int(ctx.training), int(S["mem_enc"].dtype == BF16), grid
+    q.p_att, q.p_dec, q.seed = dec.p_attention_dropout, dec.p_decoder_dropout, ctx.seed
+    wk = dict(
+        xdg_a=z(B, mult * 4 * Ha, dt=BF16), xdg_d=z(2, B, mult * 4 * Hd, dt=BF16),
+        carry_ha=z(B, Ha), dha_dec=z(B, Ha), dc_a=z(B, Ha), dc_d=z(B, Hd), dctx_att=z(B, Ep), dctx_dec=z(B, Ep),
+        dwprev=z(B, q.ldT), dcum=z(B, q.ldT), dq_sum=z(B, A), barrier=z(4, dt=torch.int32),
+        dga_all=torch.empty(T, B, 4 * Ha, device=dev), dgd_all=torch.empty(T, B, 4 * Hd, device=dev),
+        dq_all=torch.empty(T, B, A, device=dev), dctx_all=torch.empty(B, T, E, device=dev), dpm=z(B, Tin, A),
+        dv_part=z(grid, A), dU_part=z(grid, 128, 64))
+    for k, v in wk.items():
+        setattr(q, k, v.data_ptr())
+    q.wT_att2, q.wT_dec2, q.ut_loc = bp["wT_att2"].data_ptr(), bp["wT_dec2"].data_ptr(), bp["ut_loc"].data_ptr()
+    q.wq_t, q.v = pk.wq_t.data_ptr(), pk.v.data_ptr()
+    q.mem_enc, q.lengths = S["mem_enc"].data_ptr(), S["lengths"].data_ptr()
+    q.gates_a, q.c_a_all, q.gates_d, q.c_d_all = (sv["gates_a"].data_ptr(), sv["c_a_all"].data_ptr(),
+                                                  sv["gates_d"].data_ptr(), sv["c_d_all"].data_ptr())
+    q.align, q.th_all, q.cum_all = sv["align"].data_ptr(), sv["th_all"].data_ptr(), sv["cum_all"].data_ptr()
+    q.dproj_all = dproj.data_ptr()
+    d_align_c = None
+    if d_align is not None:
+        d_align_c = d_align.float().contiguous()
+        q.dalign = d_align_c.data_ptr()
+    _lib.check(lib.gtn_decoder_backward2(C.byref(q), _lib.stream()), "gtn_decoder_backward2")
+    TB = T * B
+    dga, dgd = wk["dga_all"].reshape(TB, 4 * Ha), wk["dgd_all"].reshape(TB, 4 * Hd)
+    # d prenet outputs: dGates_att . W_ih_att[:, :P]
+    wk["dpre_all"] = linear_nt(dga, bp["wa_pre_T"], prec).reshape(T, B, d.prenet)
+    # total context gradient incl. the time-constant columns (needed for d(memory) of the speaker / emotion columns)
+    Cc = D - E
+    dctx_full = torch.empty(B, T, D, device=dev)
+    dctx_full[:, :, :E] = wk["dctx_all"]
+    if Cc > 0:
+        dc = dproj.reshape(T, B, Hd + D)[:, :, Hd + E:] + linear_nt(dgd, bp["wd_const_T"], prec).reshape(T, B, Cc)
+        if T > 1:   # attention LSTM of frame t+1 consumed the context of frame t
+            dc[:T - 1] += linear_nt(dga[B:], bp["wa_const_T"], prec).reshape(T - 1, B, Cc)
+        dctx_full[:, :, E:] = dc.permute(1, 0, 2)
+    wk["dctx_all"] = dctx_full
+    return wk
 
 
 def _proj_gemm(x_tb: torch.Tensor, w: torch.Tensor, out_cl: torch.Tensor, prec: int, bias, accumulate: bool) -> None:

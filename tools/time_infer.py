@@ -43,7 +43,6 @@ if os.environ.get("GTN_PROF"):
         prof = torch.zeros(16 * 32, dtype=torch.int64, device="cuda")
         decoder_ops.PROF_BUFFER = prof
         if train:
-            decoder_ops.TRAIN_FWD2 = True
             dec.train()
             mem = torch.cat((torch.randn(B, 150, 512).cuda() * 0.5, torch.rand(B, 1, 512).repeat_interleave(150, 1).cuda()), -1)
             mels = (torch.randn(B, 80, 16) * 2 - 5).clamp(-11.5, 2).cuda()
