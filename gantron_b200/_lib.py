@@ -117,7 +117,7 @@ class DecoderBwd2Params(C.Structure):
                               "gates_a", "c_a_all", "gates_d", "c_d_all", "align", "th_all", "cum_all",
                               "dproj_all", "dalign", "xdg_a", "xdg_d", "carry_ha", "dha_dec", "dc_a", "dc_d",
                               "dctx_att", "dctx_dec", "dwprev", "dcum", "dq_sum", "barrier",
-                              "dga_all", "dgd_all", "dq_all", "dctx_all", "dpm", "dv_part", "dU_part")]
+                              "dga_all", "dgd_all", "dq_all", "dctx_all", "dpm", "dv_part", "dU_part", "prof")]
     )
 
 

@@ -218,7 +218,9 @@ GTN_DEVICE bool gemm_issue(const GemmJob& job, Ring& rg, uint32_t tmem_acc, uint
 // Exchange one chunk (CH = min(N, 64) batch columns starting at column c0) of the partial accumulator:
 // warps 4..7 read their TMEM lane quarter and scatter column group r to rank r's receive buffer
 // recv[src rank][row 0..127][NC4 = CH/4 columns].  Every thread of the CTA then joins the cluster barrier.
-template <int CH>
+// SWZ: the float4 slots of a row are XOR-permuted by (row >> 1) so that the slice can afterwards be read with threads
+// running over consecutive ROWS (coalesced global stores along the row dimension) at a 4-way instead of 16-way conflict.
+template <int CH, bool SWZ = false>
 GTN_DEVICE void exchange_chunk(bool has_work, uint32_t tmem_acc, int c0, float* recv, int rank) {
   constexpr int NC4 = CH / 4;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -243,7 +245,7 @@ GTN_DEVICE void exchange_chunk(bool has_work, uint32_t tmem_acc, int c0, float* 
         const uint32_t a = map_to_rank(my, (uint32_t)dst);
 #pragma unroll
         for (int v = 0; v < NC4; v += 4)
-          st_cluster_f4(a + (uint32_t)(v * 4), __uint_as_float(r[g * NC4 + v]), __uint_as_float(r[g * NC4 + v + 1]),
+          st_cluster_f4(a + (uint32_t)((SWZ ? (v ^ (((row >> 1) & (NC4 / 4 - 1)) << 2)) : v) * 4), __uint_as_float(r[g * NC4 + v]), __uint_as_float(r[g * NC4 + v + 1]),
                         __uint_as_float(r[g * NC4 + v + 2]), __uint_as_float(r[g * NC4 + v + 3]));
       }
     }
@@ -254,9 +256,9 @@ GTN_DEVICE void exchange_chunk(bool has_work, uint32_t tmem_acc, int c0, float* 
 }
 
 // sum of the four partials of element (row, col) of this CTA's slice
-template <int NC4>
+template <int NC4, bool SWZ = false>
 GTN_DEVICE float recv_sum(const float* recv, int row, int col) {
-  const float* p = recv + (size_t)row * NC4 + col;
+  const float* p = recv + (size_t)row * NC4 + (SWZ ? (col ^ (((row >> 1) & (NC4 / 4 - 1)) << 2)) : col);
   return (p[0] + p[(size_t)TILE_M * NC4]) + (p[(size_t)2 * TILE_M * NC4] + p[(size_t)3 * TILE_M * NC4]);
 }
 

@@ -17,6 +17,7 @@
 //   P3  query backward (Wq^T dq) + attention LSTM cell backward, spread over all CTAs by hidden unit (model.py:391-394)
 // All WEIGHT gradients are deferred: the kernel stores per-frame gate / query gradients and the host issues a
 // handful of K = T*B tcgen05 GEMMs afterwards (gtn_gemm_tn_bf16).
+#include <cstdlib>
 #include "gtn_decoder2.cuh"
 #include "gtn_internal.h"
 #include "../../include/gantron_b200.h"
@@ -25,6 +26,17 @@ namespace gtn {
 
 typedef gtn_decoder_bwd2_params DecBwd2;
 #define BFP(x) (reinterpret_cast<bf16*>(const_cast<void*>(static_cast<const void*>(x))))
+
+// dev instrumentation: CTA 0 -> prof[0..511], CTA 48 (first h_dec tile at the default dims) -> prof[512..1023]
+#define PROFB(slot)                                                                         \
+  do {                                                                                      \
+    if (p.prof != nullptr && (blockIdx.x == 0 || blockIdx.x == 48) && threadIdx.x == 0 && it < 16)                 \
+      p.prof[(blockIdx.x ? 512 : 0) + it * 32 + (slot)] = clock64();                        \
+  } while (0)
+#define PROFB_T(thr, slot)                                                                  \
+  do {                                                                                      \
+    if (p.prof != nullptr && blockIdx.x == 0 && threadIdx.x == (thr) && it < 16) p.prof[it * 32 + (slot)] = clock64(); \
+  } while (0)
 
 struct Bwd2Maps {
   CUtensorMap wT_att, wT_dec, ut;      // weights (A operands) and U^T (B operand of d[prev|cum] = dth . U)
@@ -114,26 +126,37 @@ GTN_DEVICE float block_sum2(float v, float* scr) {
   return r;
 }
 
-// LSTM cell backward for one (b, unit) of frame t: dh = gradient w.r.t. the (post-dropout) hidden output.
+// LSTM cell backward for one (b, unit) of frame t, split into an operand fetch (issued early so that several cells'
+// global loads overlap) and the arithmetic.  dh = gradient w.r.t. the (post-dropout) hidden output.
+struct CellIn {
+  float4 g;            // i, f, g, o (post-activation) of frame t
+  float c, cprev, dc;  // c(t), c(t-1), carried d c
+};
+GTN_DEVICE CellIn cell_load(const DecBwd2& p, int t, int b, int unit, int H, const float* gates_all, const float* c_all,
+                            const float* dc_carry) {
+  CellIn in;
+  const size_t cell = ((size_t)t * p.B + b) * H + unit;
+  in.g = __ldg(reinterpret_cast<const float4*>(gates_all) + cell);
+  in.c = __ldg(&c_all[cell]);
+  in.cprev = t > 0 ? __ldg(&c_all[cell - (size_t)p.B * H]) : 0.f;
+  in.dc = dc_carry[(size_t)b * H + unit];
+  return in;
+}
 // Writes the four pre-activation gate gradients (gate-major K order g*H + unit) as GEMM operand and as fp32 save.
-GTN_DEVICE void cell_backward2(const DecBwd2& p, int t, int b, int unit, int H, float dh, const float* gates_all,
-                               const float* c_all, float* dc_carry, float* dg_all, bf16* xdg, unsigned site, unsigned thr,
-                               float pdrop) {
+GTN_DEVICE void cell_apply(const DecBwd2& p, const CellIn& in, int t, int b, int unit, int H, float dh, float* dc_carry,
+                           float* dg_all, bf16* xdg, unsigned site, unsigned thr, float pdrop) {
   const size_t ci = (size_t)b * H + unit;
   if (p.use_dropout && thr != 0u) {
     const uint32_t bits = philox_bits(p.seed, site, (uint32_t)t, (uint32_t)ci);
     dh = bits >= thr ? dh * (1.0f / (1.0f - pdrop)) : 0.f;
   }
-  const size_t cell = ((size_t)t * p.B + b) * H + unit;
-  const float4 g = __ldg(reinterpret_cast<const float4*>(gates_all) + cell);      // i, f, g, o
-  const float c = __ldg(&c_all[cell]);
-  const float cprev = t > 0 ? __ldg(&c_all[cell - (size_t)p.B * H]) : 0.f;
-  const float tc = tanh_acc(c);
+  const float4 g = in.g;
+  const float tc = p.prec == 1 ? tanh_fast(in.c) : tanh_acc(in.c);
   const float d_o = dh * tc;
-  const float dc = dh * g.w * (1.f - tc * tc) + dc_carry[ci];
+  const float dc = dh * g.w * (1.f - tc * tc) + in.dc;
   dc_carry[ci] = dc * g.y;
   const float dgi = dc * g.z * g.x * (1.f - g.x);
-  const float dgf = dc * cprev * g.y * (1.f - g.y);
+  const float dgf = dc * in.cprev * g.y * (1.f - g.y);
   const float dgg = dc * g.x * (1.f - g.z * g.z);
   const float dgo = d_o * g.w * (1.f - g.w);
   const size_t g0 = ((size_t)t * p.B + b) * 4 * H + unit;
@@ -143,6 +166,12 @@ GTN_DEVICE void cell_backward2(const DecBwd2& p, int t, int b, int unit, int H, 
   store_act(xr, H + unit, 4 * H, p.prec, dgf);
   store_act(xr, 2 * H + unit, 4 * H, p.prec, dgg);
   store_act(xr, 3 * H + unit, 4 * H, p.prec, dgo);
+}
+GTN_DEVICE void cell_backward2(const DecBwd2& p, int t, int b, int unit, int H, float dh, const float* gates_all,
+                               const float* c_all, float* dc_carry, float* dg_all, bf16* xdg, unsigned site, unsigned thr,
+                               float pdrop) {
+  const CellIn in = cell_load(p, t, b, unit, H, gates_all, c_all, dc_carry);
+  cell_apply(p, in, t, b, unit, H, dh, dc_carry, dg_all, xdg, site, thr, pdrop);
 }
 
 // decoder LSTM cell backward of frame t (prologue only: frame T-1 has no recurrent carry), spread over the grid
@@ -177,21 +206,52 @@ GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, 
     job.seg[0] = dec ? XSeg{&maps.xdg_d, p.mult * 4 * p.Hd / KB, cur} : XSeg{&maps.xdg_a, p.mult * 4 * p.Ha / KB, 0};
     job.nkb = job.seg[0].nkb;
     const bool has_work = gemm_issue<N>(job, sm.ring, tmem_base, sm.acc_full, rank);
+    PROFB(1);
     __syncwarp();
     if ((threadIdx.x >> 5) >= 4 && has_work) {
       wait_bar(sm.acc_full, acc_par);
       tc_fence_after();
     }
+    PROFB_T(128, 2);
     if (has_work) acc_par ^= 1u;
     for (int c0 = 0; c0 < N; c0 += CH) {
       float* recv = sm.recv + (size_t)(round & 1u) * 4 * TILE_M * NC4;
       ++round;
-      exchange_chunk<CH>(has_work, tmem_base, c0, recv, rank);
       const int bbase = c0 + rank * NC4;
+      constexpr int CPT = TILE_M * NC4 / 256;      // elements of the 128 x NC4 slice per thread
+      const bool cell_tile = dec && t > 0 && row0 >= p.Ha + p.E;
+      CellIn cin[CPT];
+      float dpj[CPT];
+      if (cell_tile) {
+#pragma unroll
+        for (int q = 0; q < CPT; ++q) {
+          const int idx = threadIdx.x + q * 256;
+          const int r = idx % TILE_M, bl = idx / TILE_M, b = bbase + bl, u = row0 + r - p.Ha - p.E;
+          if (b < p.B && u < p.Hd) {
+            cin[q] = cell_load(p, t - 1, b, u, p.Hd, p.gates_d, p.c_d_all, p.dc_d);
+            dpj[q] = __ldg(&p.dproj_all[((size_t)(t - 1) * p.B + b) * (p.Hd + p.D) + u]);
+          }
+        }
+      }
+      exchange_chunk<CH, true>(has_work, tmem_base, c0, recv, rank);
+      PROFB(3);
+      if (cell_tile) {
+        // fused decoder LSTM cell backward of frame t-1 on a tile made of h_dec rows only: operands were prefetched
+        bf16* xnext = BFP(p.xdg_d) + (size_t)nxt * p.B * p.mult * 4 * p.Hd;
+#pragma unroll
+        for (int q = 0; q < CPT; ++q) {
+          const int idx = threadIdx.x + q * 256;
+          const int r = idx % TILE_M, bl = idx / TILE_M, b = bbase + bl, u = row0 + r - p.Ha - p.E;
+          if (b < p.B && u < p.Hd)
+            cell_apply(p, cin[q], t - 1, b, u, p.Hd, recv_sum<NC4, true>(recv, r, bl) + dpj[q], p.dc_d, p.dgd_all, xnext, 4u,
+                       p.thr_dec, p.p_dec);
+        }
+        continue;
+      }
       for (int idx = threadIdx.x; idx < TILE_M * NC4; idx += blockDim.x) {
-        const int bl = idx % NC4, r = idx / NC4, b = bbase + bl, row = row0 + r;
+        const int r = idx % TILE_M, bl = idx / TILE_M, b = bbase + bl, row = row0 + r;
         if (b >= p.B) continue;
-        const float val = recv_sum<NC4>(recv, r, bl);
+        const float val = recv_sum<NC4, true>(recv, r, bl);
         if (dec) {
           if (row < p.Ha) p.dha_dec[(size_t)b * p.Ha + row] = val;
           else if (row < p.Ha + p.E) p.dctx_dec[(size_t)b * p.Ep + row - p.Ha] = val;
@@ -234,7 +294,7 @@ GTN_DEVICE void ld8b<bf16>(const bf16* p, float (&o)[8]) {
 }
 
 template <typename MT>
-GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, bool first, int rank, int cid, int ncl, uint32_t tmem_g,
+GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int rank, int cid, int ncl, uint32_t tmem_g,
                                 uint32_t tmem_du, uint32_t& g_par, uint32_t& xround) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int Tin = p.Tin, A = p.A, KS = p.KS, hk = (p.KS - 1) / 2, E = p.E;
@@ -273,6 +333,7 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, bool first, 
       }
     }
     __syncthreads();
+    PROFB(10);
     float dot_part = 0.f;
     if (active) {
       build_im2col(sm.wcat, Wd, KS, jn, im_hi, im_lo);
@@ -284,22 +345,44 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, bool first, 
         *reinterpret_cast<uint4*>(im_lo + off) = make_uint4(0u, 0u, 0u, 0u);
       }
       // d w_j over this CTA's positions: one warp per position, lanes over the time-varying columns
-      for (int jl = warp; jl < jn; jl += 8) {
-        const int j = j0 + jl;
-        float s = 0.f;
-        if (j < L) {
-          const MT* mj = mem + ((size_t)b * Tin + j) * E;
-          for (int d = lane * 8; d < E; d += 256) {
-            float mv[8];
-            ld8b<MT>(mj + d, mv);
+      for (int jl0 = warp; jl0 < jn; jl0 += 32) {
+        // four positions per warp in flight (rows jl0, +8, +16, +24): all loads first, then the reductions
+        float s[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int d = lane * 8; d < E; d += 256) {
+          float mv[4][8];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) s += sm.dctx_s[d + e] * mv[e];
+          for (int r = 0; r < 4; ++r) {
+            const int j = j0 + jl0 + 8 * r;
+            if (jl0 + 8 * r < jn && j < L) ld8b<MT>(mem + ((size_t)b * Tin + j) * E + d, mv[r]);
+            else {
+#pragma unroll
+              for (int e = 0; e < 8; ++e) mv[r][e] = 0.f;
+            }
           }
-          s = warp_sum(s);
-          s += __ldcg(&p.dwprev[(size_t)b * p.ldT + j]) + __ldcg(&p.dcum[(size_t)b * p.ldT + j]);
-          if (p.dalign) s += p.dalign[bt * Tin + j];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const float dc = sm.dctx_s[d + e];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) s[r] += dc * mv[r][e];
+          }
         }
-        if (lane == 0) { sm.dw_s[j] = s; }
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const float tot = warp_sum(s[r]);
+          if (lane == 0 && jl0 + 8 * r < jn) sm.dw_s[j0 + jl0 + 8 * r] = tot;
+        }
+      }
+    }
+    __syncthreads();
+    if (active) {
+      // + what reaches w_j through the next frame's location features and the upstream alignment gradient
+      for (int jl = threadIdx.x; jl < jn; jl += blockDim.x) {
+        const int j = j0 + jl;
+        if (j < L) {
+          float s = sm.dw_s[j] + __ldcg(&p.dwprev[(size_t)b * p.ldT + j]) + __ldcg(&p.dcum[(size_t)b * p.ldT + j]);
+          if (p.dalign) s += p.dalign[bt * Tin + j];
+          sm.dw_s[j] = s;
+        }
       }
     }
     __syncthreads();
@@ -311,7 +394,9 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, bool first, 
       sm.dot_s[xb * 2] = dot_part;
       st_cluster_f1(map_to_rank(smem_u32(&sm.dot_s[xb * 2 + 1]), (uint32_t)peer), dot_part);
     }
+    PROFB(11);
     cluster_sync_all();                                              // #1: softmax dot product of the pair
+    PROFB(12);
     if (active) {
       const float dot = sm.dot_s[xb * 2] + sm.dot_s[xb * 2 + 1];
       // softmax backward: de_j = w_j (dw_j - sum_k w_k dw_k)
@@ -322,75 +407,76 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, bool first, 
     }
     __syncthreads();
     if (active) {
-      // thread = (position row = TMEM lane, 64-column half of the attention dimension)
-      const int wq = warp & 3, ah = warp >> 2, a0 = ah * 64;
-      const int jl = wq * 32 + lane;
-      const bool valid = jl < jn && (j0 + jl) < L;
-      const float de = valid ? sm.dw_s[j0 + jl] : 0.f;
-      float dth[64], pv[64];
-      const float* thj = p.th_all + ((tb * Tin + (j0 + jl)) * A + a0);
-      float* dpmj = p.dpm + (((size_t)b * Tin + (j0 + jl)) * A + a0);
+      // thread = (two adjacent attention columns, one of four row groups): th / dpm traffic is coalesced along the
+      // attention dimension, dq[a] = sum_j dth[j][a] and dv[a] += sum_j de_j th[j][a] accumulate in registers over rows.
+      // dth goes to shared memory as bf16 hi / lo planes: K-major tile rows = positions (block = a / 64), which is also
+      // the MN-major operand of dU.  Rows beyond jn / masked positions are written as zeros.
+      const int ap = (threadIdx.x & 63) * 2, rg = threadIdx.x >> 6;
+      const bool a_ok = ap < A;
+      const float v0 = sm.v_s[ap], v1 = sm.v_s[ap + 1];
+      const uint32_t toff = (uint32_t)(ap >> 6) * W_TILE_BYTES + (uint32_t)((ap & 7) * 2);
+      const int chunk = (ap & 63) >> 3;
+      float dq0 = 0.f, dq1 = 0.f, dv0 = 0.f, dv1 = 0.f;
+      for (int jb = rg; jb < TILE_M; jb += 16) {
+        float2 th[4], dp[4];
+        float de[4];
+        bool ok[4];
 #pragma unroll
-      for (int g = 0; g < 16; ++g) {
-        float4 th = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (valid && a0 + g * 4 < A) th = __ldg(reinterpret_cast<const float4*>(thj) + g);
-        const float t4[4] = {th.x, th.y, th.z, th.w};
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int a = g * 4 + e;
-          dth[a] = de * sm.v_s[a0 + a] * (1.f - t4[e] * t4[e]);
-          pv[a] = de * t4[e];
+        for (int r = 0; r < 4; ++r) {
+          const int jl = jb + 4 * r, j = j0 + jl;
+          ok[r] = a_ok && jl < jn && j < L;
+          th[r] = make_float2(0.f, 0.f);
+          de[r] = 0.f;
+          if (ok[r]) {
+            th[r] = __ldg(reinterpret_cast<const float2*>(p.th_all + ((tb * Tin + j) * A + ap)));
+            de[r] = sm.dw_s[j];
+          }
         }
-        if (valid && a0 + g * 4 < A) {
-          float4 acc = *(reinterpret_cast<float4*>(dpmj) + g);
-          acc.x += dth[g * 4]; acc.y += dth[g * 4 + 1]; acc.z += dth[g * 4 + 2]; acc.w += dth[g * 4 + 3];
-          *(reinterpret_cast<float4*>(dpmj) + g) = acc;
-        }
-      }
-      // dth as bf16 hi / lo planes: K-major tile rows = positions (block ah), also the MN-major operand of dU
 #pragma unroll
-      for (int chunk = 0; chunk < 8; ++chunk) {
-        uint32_t hi[4], lo[4];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float x0 = dth[chunk * 8 + 2 * e], x1 = dth[chunk * 8 + 2 * e + 1];
-          const float h0 = bf16_round(x0), h1 = bf16_round(x1);
-          hi[e] = pack_bf16x2(h0, h1);
-          lo[e] = pack_bf16x2(x0 - h0, x1 - h1);
+        for (int r = 0; r < 4; ++r) {
+          dp[r] = make_float2(0.f, 0.f);
+          if (ok[r]) dp[r] = *reinterpret_cast<const float2*>(p.dpm + (((size_t)b * Tin + (j0 + jb + 4 * r)) * A + ap));
         }
-        const uint32_t off = (uint32_t)ah * W_TILE_BYTES + sw128_off(jl, chunk);
-        *reinterpret_cast<uint4*>(dth_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-        *reinterpret_cast<uint4*>(dth_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const int jl = jb + 4 * r;
+          const float d0 = de[r] * v0 * (1.f - th[r].x * th[r].x), d1 = de[r] * v1 * (1.f - th[r].y * th[r].y);
+          if (ok[r])
+            *reinterpret_cast<float2*>(p.dpm + (((size_t)b * Tin + (j0 + jl)) * A + ap)) = make_float2(dp[r].x + d0, dp[r].y + d1);
+          dq0 += d0; dq1 += d1;
+          dv0 += de[r] * th[r].x; dv1 += de[r] * th[r].y;
+          const float h0 = bf16_round(d0), h1 = bf16_round(d1);
+          const uint32_t off = toff + sw128_off(jl, chunk);
+          *reinterpret_cast<uint32_t*>(dth_hi + off) = pack_bf16x2(h0, h1);
+          *reinterpret_cast<uint32_t*>(dth_lo + off) = pack_bf16x2(d0 - h0, d1 - h1);
+        }
       }
       fence_proxy_async_smem();
-      // column sums over positions: dq[a] = sum_j dth[j][a], dv[a] += sum_j de_j th[j][a]
-      warp_reduce_scatter64(dth);
-      warp_reduce_scatter64(pv);
-      // part_s[warp][0..63]: lanes hold columns 2l, 2l+1
-      sm.part_s[warp * 64 + 2 * lane] = dth[0];
-      sm.part_s[warp * 64 + 2 * lane + 1] = dth[1];
+      // combine the four row groups: part_s[rg][0..127] (dq), then the same for dv
+      sm.part_s[rg * 128 + ap] = dq0;
+      sm.part_s[rg * 128 + ap + 1] = dq1;
       __syncthreads();
       float dqv = 0.f;
       if (threadIdx.x < 128) {
-        const int a = threadIdx.x, hh = a >> 6, c = a & 63;
 #pragma unroll
-        for (int w = 0; w < 4; ++w) dqv += sm.part_s[(hh * 4 + w) * 64 + c];
+        for (int w = 0; w < 4; ++w) dqv += sm.part_s[w * 128 + threadIdx.x];
       }
       __syncthreads();
-      sm.part_s[warp * 64 + 2 * lane] = pv[0];
-      sm.part_s[warp * 64 + 2 * lane + 1] = pv[1];
+      sm.part_s[rg * 128 + ap] = dv0;
+      sm.part_s[rg * 128 + ap + 1] = dv1;
       __syncthreads();
       if (threadIdx.x < 128) {
-        const int a = threadIdx.x, hh = a >> 6, c = a & 63;
+        const int a = threadIdx.x;
         float dvv = 0.f;
 #pragma unroll
-        for (int w = 0; w < 4; ++w) dvv += sm.part_s[(hh * 4 + w) * 64 + c];
+        for (int w = 0; w < 4; ++w) dvv += sm.part_s[w * 128 + a];
         sm.dv_acc[a] += dvv;
         sm.dqp_s[a] = dqv;               // own partial (slot 0); the peer's lands in slot 1 (dqp_s + 128)
         st_cluster_f1(map_to_rank(smem_u32(&sm.dqp_s[128 + a]), (uint32_t)peer), dqv);
       }
     }
     __syncthreads();
+    PROFB(13);
     if (active && threadIdx.x == 32) {
       tc_fence_after();
       // G[j][kk] = sum_a dth[j][a] U[a][kk]   (M = positions, N = 64 filter taps, K = attention dim, 2 k-blocks)
@@ -417,7 +503,7 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, bool first, 
         for (int k = 0; k < TILE_M / 16; ++k) {
           const uint64_t da = umma_desc_sw128_mn_lbo(abase + k * 2048u, W_TILE_BYTES);
           const uint64_t db = umma_desc_sw128_mn_lbo(bbase + k * 2048u, W_TILE_BYTES);
-          umma_bf16(tmem_du, da, db, idesc_mn, (uint32_t)(!(first && itb == 0) || (pl | k) != 0));
+          umma_bf16(tmem_du, da, db, idesc_mn, (uint32_t)(!(it == 0 && itb == 0) || (pl | k) != 0));
         }
       }
       // (no commit needed for dU: it is only read at the very end, after later commits / barriers)
@@ -442,6 +528,7 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, bool first, 
     }
     tc_fence_before();
     __syncthreads();
+    PROFB(15);
     if (active) {
       // d wcat[ch][jj] = sum_k G[jj - k][ch*KS + k]  over this CTA's positions
       for (int i = threadIdx.x; i < 2 * Wd; i += blockDim.x) {
@@ -466,7 +553,9 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, bool first, 
         st_cluster_f1(peer_h + (uint32_t)((ch * 32 + q) * 4), sm.dwc_s[ch * Wd + jj]);
       }
     }
+    PROFB(16);
     cluster_sync_all();                                              // #2: halos and dq partials of the pair
+    PROFB(17);
     if (active) {
       const float* hal = sm.halo_s + xb * 2 * 32;
       for (int i = threadIdx.x; i < 2 * jn; i += blockDim.x) {
@@ -496,34 +585,74 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, bool first, 
 // ------------------------------------------------------------------------------------------------
 // P3: query backward + attention LSTM cell backward of frame t, all CTAs, split by hidden unit
 // ------------------------------------------------------------------------------------------------
-GTN_DEVICE void att_cell_phase2(const DecBwd2& p, SmemB& sm, int t) {
-  // cells are dealt out as (unit, batch) with the unit slowest so a CTA touches few rows of Wq^T; dq of a 64-sequence
-  // chunk is staged transposed in shared memory ([a][65]: conflict-free for consecutive sequences)
-  const int ncell = p.Ha * p.B;
-  const int per_cta = (ncell + gridDim.x - 1) / gridDim.x;
-  const int c_begin = blockIdx.x * per_cta, c_end = min(ncell, c_begin + per_cta);
+GTN_DEVICE void att_cell_phase2(const DecBwd2& p, SmemB& sm, int t, int it) {
+  // CTA i owns hidden units [i*UPC, (i+1)*UPC) for every sequence.  Threads run unit-fastest so that the gate saves /
+  // gate-gradient stores of a sequence are contiguous; dq of a 64-sequence chunk is staged transposed in shared memory
+  // ([a][65]) and this CTA's rows of Wq^T as [unit][A + 1].
+  const int UPC = (p.Ha + gridDim.x - 1) / gridDim.x;
+  const int u_begin = blockIdx.x * UPC, nu = max(0, min(p.Ha, u_begin + UPC) - u_begin);
   float* dq_s = reinterpret_cast<float*>(sm.ring.base);      // the TMA ring is idle in this phase
+  float* wq_s = dq_s + 128 * 65;
+  const int Ap = p.A + 1;
+  for (int i = threadIdx.x; i < nu * p.A; i += blockDim.x) {
+    const int ul = i / p.A, a = i - ul * p.A;
+    wq_s[ul * Ap + a] = __ldg(&p.wq_t[(size_t)(u_begin + ul) * p.A + a]);
+  }
   for (int bc0 = 0; bc0 < p.B; bc0 += 64) {
     const int nb = min(64, p.B - bc0);
     __syncthreads();
-    for (int i = threadIdx.x; i < nb * p.A; i += blockDim.x) {
-      const int bl = i / p.A, a = i - bl * p.A;
-      dq_s[a * 65 + bl] = __ldcg(&p.dq_sum[(size_t)(bc0 + bl) * p.A + a]);
+    const int ntot = nb * p.A;
+    for (int i0 = 0; i0 < ntot; i0 += 8 * 256) {
+      float v[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int i = i0 + k * 256 + threadIdx.x;
+        v[k] = i < ntot ? __ldcg(&p.dq_sum[(size_t)bc0 * p.A + i]) : 0.f;
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int i = i0 + k * 256 + threadIdx.x;
+        if (i < ntot) { const int bl = i / p.A, a = i - bl * p.A; dq_s[a * 65 + bl] = v[k]; }
+      }
     }
     __syncthreads();
-    for (int c = c_begin + threadIdx.x; c < c_end; c += blockDim.x) {
-      const int u = c / p.B, b = c - u * p.B;
-      if (b < bc0 || b >= bc0 + nb) continue;
-      const float* wq = p.wq_t + (size_t)u * p.A;
-      const float* dq = dq_s + (b - bc0);
-      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-      for (int a = 0; a < p.A; a += 4) {
-        const float4 w4 = __ldg(reinterpret_cast<const float4*>(wq + a));
-        s0 += w4.x * dq[a * 65]; s1 += w4.y * dq[(a + 1) * 65]; s2 += w4.z * dq[(a + 2) * 65]; s3 += w4.w * dq[(a + 3) * 65];
+    PROFB(22);
+    const int ncell = nu * nb;
+    for (int c0 = 0; c0 < ncell; c0 += 2 * 256) {
+      // two cells per thread per round: fetch both cells' operands, then the dot products, then the cell arithmetic
+      CellIn cin[2];
+      float add[2];
+      bool ok[2];
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int c = c0 + k * 256 + threadIdx.x;
+        ok[k] = c < ncell;
+        if (ok[k]) {
+          const int ul = c % nu, b = bc0 + c / nu, u = u_begin + ul;
+          cin[k] = cell_load(p, t, b, u, p.Ha, p.gates_a, p.c_a_all, p.dc_a);
+          const size_t ci = (size_t)b * p.Ha + u;
+          add[k] = __ldcg(&p.dha_dec[ci]) + __ldcg(&p.carry_ha[ci]);
+        }
       }
-      const size_t ci = (size_t)b * p.Ha + u;
-      const float dh = (s0 + s1) + (s2 + s3) + __ldcg(&p.dha_dec[ci]) + __ldcg(&p.carry_ha[ci]);
-      cell_backward2(p, t, b, u, p.Ha, dh, p.gates_a, p.c_a_all, p.dc_a, p.dga_all, BFP(p.xdg_a), 3u, p.thr_att, p.p_att);
+      PROFB(23);
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        if (!ok[k]) continue;
+        const int c = c0 + k * 256 + threadIdx.x;
+        const int ul = c % nu, bl = c / nu;
+        const float* wq = wq_s + ul * Ap;
+        const float* dq = dq_s + bl;
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll 4
+        for (int a = 0; a < p.A; a += 4) {
+          s0 += wq[a] * dq[a * 65]; s1 += wq[a + 1] * dq[(a + 1) * 65];
+          s2 += wq[a + 2] * dq[(a + 2) * 65]; s3 += wq[a + 3] * dq[(a + 3) * 65];
+        }
+        if (k == 0) PROFB(24);
+        cell_apply(p, cin[k], t, bc0 + bl, u_begin + ul, p.Ha, (s0 + s1) + (s2 + s3) + add[k], p.dc_a, p.dga_all,
+                   BFP(p.xdg_a), 3u, p.thr_att, p.p_att);
+        if (k == 0) PROFB(25);
+      }
     }
   }
 }
@@ -565,13 +694,20 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
   grid_sync2(p.barrier, epoch, nblocks);
   int it = 0;
   for (int t = p.T - 1; t >= 0; --t, ++it) {
+    PROFB(0);
     dgrad_phase2<N>(p, maps, sm, t, it, rank, cid, ncl, tmem_base, acc_par, round);
+    PROFB(4);
     grid_sync2(p.barrier, epoch, nblocks);
-    if (p.mem_bf16) attn_bwd_phase2<bf16>(p, sm, t, it == 0, rank, cid, ncl, tmem_g, tmem_du, g_par, xround);
-    else attn_bwd_phase2<float>(p, sm, t, it == 0, rank, cid, ncl, tmem_g, tmem_du, g_par, xround);
+    PROFB(5);
+    if (p.mem_bf16) attn_bwd_phase2<bf16>(p, sm, t, it, rank, cid, ncl, tmem_g, tmem_du, g_par, xround);
+    else attn_bwd_phase2<float>(p, sm, t, it, rank, cid, ncl, tmem_g, tmem_du, g_par, xround);
+    PROFB(18);
     grid_sync2(p.barrier, epoch, nblocks);
-    att_cell_phase2(p, sm, t);
+    PROFB(19);
+    att_cell_phase2(p, sm, t, it);
+    PROFB(20);
     grid_sync2(p.barrier, epoch, nblocks);
+    PROFB(21);
   }
   // per-CTA partial sums of the small attention weight gradients
   for (int i = threadIdx.x; i < p.A; i += blockDim.x) p.dv_part[(size_t)blockIdx.x * p.A + i] = sm.dv_acc[i];
@@ -651,7 +787,7 @@ static int launch_bwd2(const Bwd2Maps& maps, const DecBwd2& p, int ncl, cudaStre
   int rc = bwd2_config<N>(cfg, attrs, S, smem);
   if (rc) return rc;
   cfg.stream = st;
-  cfg.numAttrs = 2;
+  cfg.numAttrs = getenv("GTN_NO_COOP") ? 1 : 2;   // profilers that cannot replay cooperative launches
   cfg.gridDim = dim3(CL * ncl);
   GTN_CUDA_OK(cudaLaunchKernelEx(&cfg, decoder_bwd2_kernel<N>, maps, p, S));
   count_launch();
@@ -690,6 +826,7 @@ extern "C" int gtn_decoder_backward2(const gtn_decoder_bwd2_params* hp, void* st
   p.thr_dec = p.use_dropout ? thr(p.p_dec) : 0u;
   const int grid = gtn_decoder_bwd2_grid(p.B, p.Ha, p.Hd, p.E);
   GTN_REQUIRE(grid > 0 && p.grid == grid, "params.grid (%d) must equal gtn_decoder_bwd2_grid() (%d)", p.grid, grid);
+  GTN_REQUIRE((p.Ha + grid - 1) / grid <= 64, "decoder backward: too few CTAs (%d) for attention_rnn_dim %d", grid, p.Ha);
   const int N = pick_n(p.B);
   const int m = p.mult;
   Bwd2Maps maps;

@@ -19,6 +19,7 @@
 // Grid barriers: after A, after B (training: C(t) and A(t+1) share an interval since A does not read h_dec).
 // Training additionally saves what the backward kernel needs.  The time-constant columns of `memory`
 // (noise / speaker / emotion: model.py:275-278,655-663) are not re-read per frame: context = const * sum_j w_j.
+#include <cstdlib>
 #include "gtn_decoder2.cuh"
 #include "gtn_internal.h"
 #include "../../include/gantron_b200.h"
@@ -631,7 +632,7 @@ static int launch_fwd2(const Fwd2Maps& maps, const DecFwd& p, int max_clusters_w
   GTN_REQUIRE(max_cl >= 1, "decoder forward: no cluster of %d CTAs fits on this device", CL);
   const int ncl = max_cl < max_clusters_wanted ? max_cl : max_clusters_wanted;
   cfg.gridDim = dim3(CL * ncl);
-  cfg.numAttrs = 2;
+  cfg.numAttrs = getenv("GTN_NO_COOP") ? 1 : 2;   // profilers that cannot replay cooperative launches
   GTN_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, maps, p, S));
   count_launch();
   return 0;

@@ -198,6 +198,7 @@ def decoder_version() -> int:
     return int(os.environ.get("GANTRON_B200_DECODER", "2"))
 
 
+PROF_BUFFER_BWD = None
 PROF_BUFFER = None     # dev tool: int64 [16*32] device tensor receiving clock64() stamps of CTA 0 (tools/time_infer.py)
 
 
@@ -621,6 +622,7 @@ def _bptt_v2(dec, pk, d, ctx, S, sv, dproj, d_align, prec):
                                                   sv["gates_d"].data_ptr(), sv["c_d_all"].data_ptr())
     q.align, q.th_all, q.cum_all = sv["align"].data_ptr(), sv["th_all"].data_ptr(), sv["cum_all"].data_ptr()
     q.dproj_all = dproj.data_ptr()
+    q.prof = PROF_BUFFER_BWD.data_ptr() if PROF_BUFFER_BWD is not None else None
     d_align_c = None
     if d_align is not None:
         d_align_c = d_align.float().contiguous()

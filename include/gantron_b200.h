@@ -308,6 +308,7 @@ typedef struct gtn_decoder_bwd2_params {
   float *dpm;                /* [B][Tin][A] gradient w.r.t. processed_memory (accumulated over frames) */
   float *dv_part;            /* [grid][A] */
   float *dU_part;            /* [grid][128][64]: per-CTA partial of dU[a][ch*KS+k] */
+  long long *prof;           /* optional [16][32] clock64() stamps of CTA 0 for the first 16 processed frames (NULL = off) */
 } gtn_decoder_bwd2_params;
 
 int gtn_decoder_bwd2_grid(int B, int Ha, int Hd, int E);   /* CTAs gtn_decoder_backward2 launches, or -1 */

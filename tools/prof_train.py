@@ -1,0 +1,45 @@
+"""Per-phase clock64() profile of CTA 0 of the persistent decoder kernels in training (dev tool)."""
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from gantron_b200 import decoder_ops  # noqa: E402
+from gantron_b200.hparams import HParams  # noqa: E402
+from gantron_b200.model import Decoder  # noqa: E402
+
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 64
+T = int(sys.argv[2]) if len(sys.argv) > 2 else 32
+torch.manual_seed(0)
+hp = HParams("use_noise=True,use_labels=False,b200_precision=bf16")
+dec = Decoder(hp).cuda().train()
+mem = torch.cat((torch.randn(B, 150, 512).cuda() * 0.5, torch.rand(B, 1, 512).repeat_interleave(150, 1).cuda()), -1).requires_grad_(True)
+mels = (torch.randn(B, 80, T) * 2 - 5).clamp(-11.5, 2).cuda()
+FW = {0: "step start", 1: "att: TMA issued", 2: "att: acc done", 3: "att: exchange done", 4: "att: epilogue done",
+      5: "gsync1 done", 24: "attn: mma issued", 25: "attn: energies", 26: "attn: cluster sync", 27: "attn: softmax",
+      6: "attn done", 8: "gsync2 done", 9: "dec: TMA issued", 10: "dec: acc done", 11: "dec: exchange done", 13: "dec done"}
+FO = [0, 1, 2, 3, 4, 5, 24, 25, 26, 27, 6, 8, 9, 10, 11, 13]
+BW = {0: "step start", 1: "P1: TMA issued", 2: "P1: acc done", 3: "P1: exchange done", 4: "P1: epilogue done", 5: "gsync done",
+      10: "P2: loads + window", 11: "P2: dw + dot", 12: "P2: cluster sync 1", 13: "P2: dth tiles + dq/dv", 15: "P2: MMA + G to smem",
+      16: "P2: d wcat", 17: "P2: cluster sync 2", 18: "P2 done", 19: "gsync done", 22: "P3: dq staged", 23: "P3: cell loads issued", 24: "P3: dot 0 done", 25: "P3: apply 0 done", 20: "P3 done", 21: "gsync done"}
+BO = [0, 1, 2, 3, 4, 5, 10, 11, 12, 13, 15, 16, 17, 18, 19, 22, 23, 24, 25, 20, 21]
+for rep in range(2):
+    pf = torch.zeros(16 * 32, dtype=torch.int64, device="cuda")
+    pb = torch.zeros(2 * 16 * 32, dtype=torch.int64, device="cuda")
+    decoder_ops.PROF_BUFFER, decoder_ops.PROF_BUFFER_BWD = pf, pb
+    dec.zero_grad()
+    mel, gate, align = decoder_ops.decoder_train_forward(dec, mem, mels, torch.full((B,), 150).cuda(), 5)
+    (mel.square().mean() + gate.square().mean()).backward()
+    torch.cuda.synchronize()
+for name, buf, names, order in (("forward", pf, FW, FO), ("backward CTA 0", pb[:512], BW, BO), ("backward CTA 48", pb[512:], BW, BO)):
+    pr = buf.cpu().view(16, 32)
+    t = 8
+    print(f"--- {name} B={B}: cycles since step start (frame slot {t})")
+    prev = 0
+    for sl in order:
+        if int(pr[t, sl]):
+            v = int(pr[t, sl] - pr[t, 0])
+            print(f"   {names[sl]:24s} {v:8d}  (+{v - prev})")
+            prev = v
+    print(f"   next step start          {int(pr[t + 1, 0] - pr[t, 0]):8d}")
