@@ -45,7 +45,8 @@ struct Bwd2Maps {
 
 static constexpr int B2_TIN_MAX = 256;
 static constexpr int B2_JH = 128;
-static constexpr int P2_RING_BYTES = 6 * W_TILE_BYTES;     // dth hi (2 blocks) + dth lo (2) + im2col hi + lo
+static constexpr int P2_RING_BYTES = 6 * W_TILE_BYTES;
+static constexpr int WQ_UNITS = 16;        // hidden units per CTA in P3 (attention_rnn_dim / grid, rounded up) must not exceed this     // dth hi (2 blocks) + dth lo (2) + im2col hi + lo
 
 struct SmemB {
   Ring ring;
@@ -63,6 +64,7 @@ struct SmemB {
   float* dv_acc;       // [128]
   float* dot_s;        // [4]                softmax dot partial: own, peer (double buffered)
   float* scr;          // [64]
+  float* wq_s;         // [WQ_UNITS][129]   Wq^T rows of this CTA's hidden units (P3)
   uint64_t* acc_full;
   uint64_t* g_full;
   uint64_t* ut_full;
@@ -74,7 +76,7 @@ __host__ __device__ constexpr size_t bwd2_fixed_bytes() {
   constexpr int NC4 = (N < 64 ? N : 64) / 4;
   constexpr size_t recv_b = (size_t)2 * 4 * TILE_M * NC4 * 4;
   return (recv_b < 32768 ? 32768 : recv_b) + 4 * 8192 +
-         (size_t)(1024 + 2 * B2_TIN_MAX + 4 * (B2_JH + 62) + 4 * 32 + 128 + 8 * 64 + 256 + 128 + 4 + 64) * 4 + 64 * 8 + 64;
+         (size_t)(1024 + 2 * B2_TIN_MAX + 4 * (B2_JH + 62) + 4 * 32 + 128 + 8 * 64 + 256 + 128 + 4 + 64 + WQ_UNITS * 129) * 4 + 64 * 8 + 64;
 }
 
 template <int N>
@@ -104,6 +106,7 @@ GTN_DEVICE SmemB carveB(uint8_t* base, int S) {
   m.dv_acc = f; f += 128;
   m.dot_s = f; f += 4;
   m.scr = f; f += 64;
+  m.wq_s = f; f += WQ_UNITS * 129;
   uint64_t* b = reinterpret_cast<uint64_t*>(f);
   m.ring.full = b; b += 16;
   m.ring.empty = b; b += 16;
@@ -218,36 +221,8 @@ GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, 
       float* recv = sm.recv + (size_t)(round & 1u) * 4 * TILE_M * NC4;
       ++round;
       const int bbase = c0 + rank * NC4;
-      constexpr int CPT = TILE_M * NC4 / 256;      // elements of the 128 x NC4 slice per thread
-      const bool cell_tile = dec && t > 0 && row0 >= p.Ha + p.E;
-      CellIn cin[CPT];
-      float dpj[CPT];
-      if (cell_tile) {
-#pragma unroll
-        for (int q = 0; q < CPT; ++q) {
-          const int idx = threadIdx.x + q * 256;
-          const int r = idx % TILE_M, bl = idx / TILE_M, b = bbase + bl, u = row0 + r - p.Ha - p.E;
-          if (b < p.B && u < p.Hd) {
-            cin[q] = cell_load(p, t - 1, b, u, p.Hd, p.gates_d, p.c_d_all, p.dc_d);
-            dpj[q] = __ldg(&p.dproj_all[((size_t)(t - 1) * p.B + b) * (p.Hd + p.D) + u]);
-          }
-        }
-      }
       exchange_chunk<CH, true>(has_work, tmem_base, c0, recv, rank);
       PROFB(3);
-      if (cell_tile) {
-        // fused decoder LSTM cell backward of frame t-1 on a tile made of h_dec rows only: operands were prefetched
-        bf16* xnext = BFP(p.xdg_d) + (size_t)nxt * p.B * p.mult * 4 * p.Hd;
-#pragma unroll
-        for (int q = 0; q < CPT; ++q) {
-          const int idx = threadIdx.x + q * 256;
-          const int r = idx % TILE_M, bl = idx / TILE_M, b = bbase + bl, u = row0 + r - p.Ha - p.E;
-          if (b < p.B && u < p.Hd)
-            cell_apply(p, cin[q], t - 1, b, u, p.Hd, recv_sum<NC4, true>(recv, r, bl) + dpj[q], p.dc_d, p.dgd_all, xnext, 4u,
-                       p.thr_dec, p.p_dec);
-        }
-        continue;
-      }
       for (int idx = threadIdx.x; idx < TILE_M * NC4; idx += blockDim.x) {
         const int r = idx % TILE_M, bl = idx / TILE_M, b = bbase + bl, row = row0 + r;
         if (b >= p.B) continue;
@@ -255,14 +230,7 @@ GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, 
         if (dec) {
           if (row < p.Ha) p.dha_dec[(size_t)b * p.Ha + row] = val;
           else if (row < p.Ha + p.E) p.dctx_dec[(size_t)b * p.Ep + row - p.Ha] = val;
-          else if (row < R_dec) {
-            if (t > 0) {      // fused decoder LSTM cell backward of frame t-1
-              const int u = row - p.Ha - p.E;
-              const float dh = val + p.dproj_all[((size_t)(t - 1) * p.B + b) * (p.Hd + p.D) + u];
-              cell_backward2(p, t - 1, b, u, p.Hd, dh, p.gates_d, p.c_d_all, p.dc_d, p.dgd_all,
-                             BFP(p.xdg_d) + (size_t)nxt * p.B * p.mult * 4 * p.Hd, 4u, p.thr_dec, p.p_dec);
-            }
-          }
+          else if (row < R_dec) p.dhd_rec[(size_t)b * p.Hd + row - p.Ha - p.E] = val;   // consumed by P3 (cell backward of t-1)
         } else {
           if (row < p.E) p.dctx_att[(size_t)b * p.Ep + row] = val;
           else if (row < R_att) p.carry_ha[(size_t)b * p.Ha + row - p.E] = val;
@@ -585,56 +553,85 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
 // ------------------------------------------------------------------------------------------------
 // P3: query backward + attention LSTM cell backward of frame t, all CTAs, split by hidden unit
 // ------------------------------------------------------------------------------------------------
-GTN_DEVICE void att_cell_phase2(const DecBwd2& p, SmemB& sm, int t, int it) {
-  // CTA i owns hidden units [i*UPC, (i+1)*UPC) for every sequence.  Threads run unit-fastest so that the gate saves /
-  // gate-gradient stores of a sequence are contiguous; dq of a 64-sequence chunk is staged transposed in shared memory
-  // ([a][65]) and this CTA's rows of Wq^T as [unit][A + 1].
+// Wq^T rows of this CTA's hidden units, staged once per launch: wq_s[unit][A + 1]
+GTN_DEVICE void stage_wq(const DecBwd2& p, SmemB& sm) {
   const int UPC = (p.Ha + gridDim.x - 1) / gridDim.x;
   const int u_begin = blockIdx.x * UPC, nu = max(0, min(p.Ha, u_begin + UPC) - u_begin);
-  float* dq_s = reinterpret_cast<float*>(sm.ring.base);      // the TMA ring is idle in this phase
-  float* wq_s = dq_s + 128 * 65;
   const int Ap = p.A + 1;
   for (int i = threadIdx.x; i < nu * p.A; i += blockDim.x) {
     const int ul = i / p.A, a = i - ul * p.A;
-    wq_s[ul * Ap + a] = __ldg(&p.wq_t[(size_t)(u_begin + ul) * p.A + a]);
+    sm.wq_s[ul * Ap + a] = __ldg(&p.wq_t[(size_t)(u_begin + ul) * p.A + a]);
   }
+}
+
+GTN_DEVICE void att_cell_phase2(const DecBwd2& p, SmemB& sm, int t, int it) {
+  // CTA i owns hidden units [i*UPC, (i+1)*UPC) of BOTH LSTMs for every sequence.  Threads run unit-fastest so that the
+  // gate saves / gate-gradient stores of a sequence are contiguous; dq of a 64-sequence chunk is staged transposed in
+  // shared memory ([a][65]); this CTA's rows of Wq^T live in wq_s for the whole launch.
+  //   * attention LSTM cell backward of frame t:   dh = Wq^T dq + dha_dec + carry_ha            (model.py:391-394)
+  //   * decoder LSTM cell backward of frame t - 1: dh = dhd_rec (P1 of this frame) + dproj(t-1)  (model.py:404-409)
+  // Every global operand of the first round (dq, both cells' saves) is requested before anything is consumed, so the
+  // phase pays one memory round trip instead of three.
+  const int UPC = (p.Ha + gridDim.x - 1) / gridDim.x;
+  const int u_begin = blockIdx.x * UPC, nu = max(0, min(p.Ha, u_begin + UPC) - u_begin);
+  const int UPCd = (p.Hd + gridDim.x - 1) / gridDim.x;
+  const int ud_begin = blockIdx.x * UPCd, nud = max(0, min(p.Hd, ud_begin + UPCd) - ud_begin);
+  float* dq_s = reinterpret_cast<float*>(sm.ring.base);      // the TMA ring is idle in this phase
+  const float* wq_s = sm.wq_s;
+  const int Ap = p.A + 1;
+  const int nxt = (it & 1) ^ 1;
+  bf16* xnext_d = BFP(p.xdg_d) + (size_t)nxt * p.B * p.mult * 4 * p.Hd;
   for (int bc0 = 0; bc0 < p.B; bc0 += 64) {
     const int nb = min(64, p.B - bc0);
+    const int ntot = nb * p.A;                               // <= 64 * 128 = 32 * 256
     __syncthreads();
-    const int ntot = nb * p.A;
-    for (int i0 = 0; i0 < ntot; i0 += 8 * 256) {
-      float v[8];
+    float v[32];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const int i = i0 + k * 256 + threadIdx.x;
-        v[k] = i < ntot ? __ldcg(&p.dq_sum[(size_t)bc0 * p.A + i]) : 0.f;
-      }
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const int i = i0 + k * 256 + threadIdx.x;
-        if (i < ntot) { const int bl = i / p.A, a = i - bl * p.A; dq_s[a * 65 + bl] = v[k]; }
-      }
+    for (int k = 0; k < 32; ++k) {
+      const int i = k * 256 + threadIdx.x;
+      v[k] = i < ntot ? __ldcg(&p.dq_sum[(size_t)bc0 * p.A + i]) : 0.f;
     }
-    __syncthreads();
-    PROFB(22);
-    const int ncell = nu * nb;
-    for (int c0 = 0; c0 < ncell; c0 += 2 * 256) {
-      // two cells per thread per round: fetch both cells' operands, then the dot products, then the cell arithmetic
-      CellIn cin[2];
-      float add[2];
-      bool ok[2];
+    const int ncell = nu * nb, ncelld = t > 0 ? nud * nb : 0;
+    const int nround = max((ncell + 511) / 512, (ncelld + 511) / 512);
+    for (int rd = 0; rd < nround; ++rd) {
+      const int c0 = rd * 512;
+      CellIn cin[2], cid_[2];
+      float add[2], ddh[2];
+      bool ok[2], okd[2];
 #pragma unroll
       for (int k = 0; k < 2; ++k) {
         const int c = c0 + k * 256 + threadIdx.x;
         ok[k] = c < ncell;
+        okd[k] = c < ncelld;
         if (ok[k]) {
           const int ul = c % nu, b = bc0 + c / nu, u = u_begin + ul;
           cin[k] = cell_load(p, t, b, u, p.Ha, p.gates_a, p.c_a_all, p.dc_a);
           const size_t ci = (size_t)b * p.Ha + u;
           add[k] = __ldcg(&p.dha_dec[ci]) + __ldcg(&p.carry_ha[ci]);
         }
+        if (okd[k]) {
+          const int ul = c % nud, b = bc0 + c / nud, u = ud_begin + ul;
+          cid_[k] = cell_load(p, t - 1, b, u, p.Hd, p.gates_d, p.c_d_all, p.dc_d);
+          ddh[k] = __ldcg(&p.dhd_rec[(size_t)b * p.Hd + u]) + __ldg(&p.dproj_all[((size_t)(t - 1) * p.B + b) * (p.Hd + p.D) + u]);
+        }
       }
       PROFB(23);
+      if (rd == 0) {
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+          const int i = k * 256 + threadIdx.x;
+          if (i < ntot) { const int bl = i / p.A, a = i - bl * p.A; dq_s[a * 65 + bl] = v[k]; }
+        }
+      }
+      // decoder cells first: they need nothing from shared memory
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        if (!okd[k]) continue;
+        const int c = c0 + k * 256 + threadIdx.x;
+        const int ul = c % nud, b = bc0 + c / nud;
+        cell_apply(p, cid_[k], t - 1, b, ud_begin + ul, p.Hd, ddh[k], p.dc_d, p.dgd_all, xnext_d, 4u, p.thr_dec, p.p_dec);
+      }
+      if (rd == 0) { __syncthreads(); PROFB(22); }
 #pragma unroll
       for (int k = 0; k < 2; ++k) {
         if (!ok[k]) continue;
@@ -690,6 +687,7 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
   unsigned int epoch = 0;
   uint32_t acc_par = 0, g_par = 0, round = 0, xround = 0;
   const unsigned int nblocks = gridDim.x;
+  stage_wq(p, sm);
   dec_cell_prologue(p, p.T - 1);
   grid_sync2(p.barrier, epoch, nblocks);
   int it = 0;
@@ -826,7 +824,8 @@ extern "C" int gtn_decoder_backward2(const gtn_decoder_bwd2_params* hp, void* st
   p.thr_dec = p.use_dropout ? thr(p.p_dec) : 0u;
   const int grid = gtn_decoder_bwd2_grid(p.B, p.Ha, p.Hd, p.E);
   GTN_REQUIRE(grid > 0 && p.grid == grid, "params.grid (%d) must equal gtn_decoder_bwd2_grid() (%d)", p.grid, grid);
-  GTN_REQUIRE((p.Ha + grid - 1) / grid <= 64, "decoder backward: too few CTAs (%d) for attention_rnn_dim %d", grid, p.Ha);
+  GTN_REQUIRE((p.Ha + grid - 1) / grid <= WQ_UNITS, "decoder backward: too few CTAs (%d) for attention_rnn_dim %d", grid, p.Ha);
+  GTN_REQUIRE(p.dhd_rec != nullptr, "dhd_rec workspace missing");
   const int N = pick_n(p.B);
   const int m = p.mult;
   Bwd2Maps maps;

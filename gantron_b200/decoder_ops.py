@@ -608,7 +608,7 @@ def _bptt_v2(dec, pk, d, ctx, S, sv, dproj, d_align, prec):
     q.p_att, q.p_dec, q.seed = dec.p_attention_dropout, dec.p_decoder_dropout, ctx.seed
     wk = dict(
         xdg_a=z(B, mult * 4 * Ha, dt=BF16), xdg_d=z(2, B, mult * 4 * Hd, dt=BF16),
-        carry_ha=z(B, Ha), dha_dec=z(B, Ha), dc_a=z(B, Ha), dc_d=z(B, Hd), dctx_att=z(B, Ep), dctx_dec=z(B, Ep),
+        carry_ha=z(B, Ha), dha_dec=z(B, Ha), dc_a=z(B, Ha), dc_d=z(B, Hd), dhd_rec=z(B, Hd), dctx_att=z(B, Ep), dctx_dec=z(B, Ep),
         dwprev=z(B, q.ldT), dcum=z(B, q.ldT), dq_sum=z(B, A), barrier=z(4, dt=torch.int32),
         dga_all=torch.empty(T, B, 4 * Ha, device=dev), dgd_all=torch.empty(T, B, 4 * Hd, device=dev),
         dq_all=torch.empty(T, B, A, device=dev), dctx_all=torch.empty(B, T, E, device=dev), dpm=z(B, Tin, A),

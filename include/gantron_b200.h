@@ -297,6 +297,7 @@ typedef struct gtn_decoder_bwd2_params {
   void *xdg_d;               /* bf16 [2][B][mult*4Hd] */
   float *carry_ha, *dha_dec, *dc_a;     /* [B][Ha] */
   float *dc_d;                          /* [B][Hd] */
+  float *dhd_rec;                       /* [B][Hd] d h_dec(t-1) through the recurrent weights (P1 -> P3 of a frame) */
   float *dctx_att, *dctx_dec;           /* [B][Ep] */
   float *dwprev, *dcum;                 /* [B][ldT] */
   float *dq_sum;                        /* [B][A] */
