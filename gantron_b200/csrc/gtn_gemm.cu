@@ -48,6 +48,9 @@ struct GemmKernelParams {
   unsigned int drop_thr; float drop_scale; unsigned long long seed; unsigned int site, step;
   float* stats;       // [2][M] per-row sum / sum of squares over valid n (all z), or nullptr
   int stages;
+  // split-K: blockIdx.z = split * zdiv + z; split s covers k-blocks [s * kps, min(nk, (s + 1) * kps)) and ADDS its
+  // partial tile to the fp32 output with red.global.add (the host zeroes C first unless it accumulates)
+  int zdiv, kps, splits;
 };
 
 GTN_DEVICE void wait_or_trap(uint64_t* bar, uint32_t parity) {
@@ -58,7 +61,7 @@ GTN_DEVICE void wait_or_trap(uint64_t* bar, uint32_t parity) {
 }
 
 template <int BN>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(256, 2)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const GemmKernelParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -77,7 +80,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int lane = threadIdx.x & 31;
   const int n0 = blockIdx.x * BN;
   const int m0 = blockIdx.y * BM;
-  const int z = blockIdx.z;
+  const int z = (int)blockIdx.z % p.zdiv;
+  const int split = (int)blockIdx.z / p.zdiv;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -93,14 +97,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_acc = *tmem_slot;
-  const int nk = p.num_k_blocks;
+  const int kb0 = split * p.kps;
+  const int kb1 = min(p.num_k_blocks, kb0 + p.kps);
 
   if (warp == 0) {
     if (lane == 0) {
       // ------------------------------ TMA producer ------------------------------
-      for (int kb = 0; kb < nk; ++kb) {
-        const int s = kb % stages;
-        const uint32_t ph = (uint32_t)(kb / stages) & 1u;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        const int s = (kb - kb0) % stages;
+        const uint32_t ph = (uint32_t)((kb - kb0) / stages) & 1u;
         wait_or_trap(&empty[s], ph ^ 1u);
         mbar_expect_tx(&full[s], A_BYTES + B_BYTES);
         uint8_t* dA = sA + (size_t)s * A_BYTES;
@@ -137,9 +142,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (lane == 0) {
       // ------------------------------ MMA issuer ------------------------------
       const uint32_t idesc = umma_idesc_bf16(BM, BN) | (p.mn_major ? ((1u << 15) | (1u << 16)) : 0u);
-      for (int kb = 0; kb < nk; ++kb) {
-        const int s = kb % stages;
-        const uint32_t ph = (uint32_t)(kb / stages) & 1u;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        const int s = (kb - kb0) % stages;
+        const uint32_t ph = (uint32_t)((kb - kb0) / stages) & 1u;
         wait_or_trap(&full[s], ph);
         tc_fence_after();
         const uint32_t aA = smem_u32(sA + (size_t)s * A_BYTES), aB = smem_u32(sB + (size_t)s * B_BYTES);
@@ -148,14 +153,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
             // advance 16 bf16 = 32 B along K inside the 128 B swizzle row: +2 in the (addr >> 4) field
-            umma_bf16(tmem_acc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
+            umma_bf16(tmem_acc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb > kb0) | (k > 0)));
           }
         } else {
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
             // 16 K-rows = two 8-row swizzle atoms = 2048 B per UMMA K step
             umma_bf16(tmem_acc, umma_desc_sw128_mn(aA + k * 2048), umma_desc_sw128_mn(aB + k * 2048), idesc,
-                      (uint32_t)((kb | k) != 0));
+                      (uint32_t)((kb > kb0) | (k > 0)));
           }
         }
         umma_commit(&empty[s]);      // frees the smem slot once these MMAs retire
@@ -183,6 +188,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tmem_ld_wait();
       const int nb = n0 + c * 32;
       if (nb >= p.N) continue;      // warp-uniform
+      if (p.splits > 1) {
+        // partial tile of one K split: fp32 reduction in L2 (no bias / activation / second output in this mode)
+        if (m_ok) {
+          float* dst = Cf + zc + (long long)m * p.ldc + nb;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (nb + j < p.N) atomicAdd(dst + j, __uint_as_float(r[j]));
+        }
+        continue;
+      }
       float v[32];
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
@@ -335,9 +350,12 @@ int make_tma_map_3d(CUtensorMap* out, const void* base, long long d0, long long 
 
 template <int BN>
 static int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, GemmKernelParams kp, dim3 grid, cudaStream_t st) {
-  int stages = kp.num_k_blocks < 2 ? 2 : (kp.num_k_blocks > 6 ? 6 : kp.num_k_blocks);
+  // BN <= 128: shallow ring (<= 112 KB) so that TWO CTAs share an SM and one tile's epilogue overlaps the other's main
+  // loop; BN = 256: one CTA per SM with a 4-deep ring
   const size_t per_stage = (size_t)BM * BK * 2 + (size_t)BN * BK * 2;
-  if (BN == 256 && stages > 4) stages = 4;
+  const int max_stages = BN == 256 ? 4 : (BN == 128 ? 3 : 4);
+  const int nkb = kp.kps > 0 ? kp.kps : kp.num_k_blocks;
+  int stages = nkb < 2 ? 2 : (nkb > max_stages ? max_stages : nkb);
   kp.stages = stages;
   const size_t smem = stages * per_stage + (2 * stages + 1) * sizeof(uint64_t) + 16 + 1024;
   static size_t configured = 0;
@@ -376,7 +394,29 @@ int gemm_launch(const GemmDesc& g, cudaStream_t st) {
   kp.seed = g.seed; kp.site = g.site; kp.step = g.step;
   kp.stats = g.stats; kp.stages = 0;
   GTN_REQUIRE(!(g.accumulate && g.c_bf16), "accumulate needs an fp32 primary output");
-  dim3 grid((g.N + BN - 1) / BN, (g.M + BM - 1) / BM, g.batch < 1 ? 1 : g.batch);
+  const int batch = g.batch < 1 ? 1 : g.batch;
+  const int gx = (g.N + BN - 1) / BN, gy = (g.M + BM - 1) / BM;
+  // split-K for GEMMs whose tile count cannot fill the 148 SMs (weight gradients with K = T*B and a small M x N):
+  // only for a plain fp32, non-transposed primary output without fused epilogue terms
+  int splits = 1;
+  const long long tiles = (long long)gx * gy * batch;
+  const bool splittable = g.mn_major && !g.c_bf16 && !g.c_trans && g.C2 == nullptr && g.bias_m == nullptr &&
+                          g.bias_n == nullptr && g.act == 0 && g.drop_p <= 0.f && g.stats == nullptr && g.C != nullptr;
+  if (splittable && tiles < 100 && g.num_k_blocks >= 16) {
+    long long want = 296 / tiles;
+    const long long maxs = g.num_k_blocks / 8;
+    if (want > maxs) want = maxs;
+    if (want > 1) splits = (int)want;
+  }
+  kp.kps = (g.num_k_blocks + splits - 1) / splits;
+  splits = (g.num_k_blocks + kp.kps - 1) / kp.kps;
+  kp.splits = splits; kp.zdiv = batch;
+  if (splits > 1 && !g.accumulate) {
+    for (int zz = 0; zz < batch; ++zz)
+      GTN_CUDA_OK(cudaMemset2DAsync(reinterpret_cast<float*>(g.C) + (long long)zz * g.strideC, (size_t)g.ldc * 4, 0,
+                                    (size_t)g.N * 4, (size_t)g.M, st));
+  }
+  dim3 grid(gx, gy, batch * splits);
   if (BN == 64) return launch_bn<64>(ta, tb, kp, grid, st);
   if (BN == 128) return launch_bn<128>(ta, tb, kp, grid, st);
   return launch_bn<256>(ta, tb, kp, grid, st);

@@ -308,7 +308,9 @@ def _bf(x: torch.Tensor, kpad: int, prec: int, is_weight: bool = False) -> torch
 def _wgrad_tn(dy: torch.Tensor, x: torch.Tensor, out: torch.Tensor, prec: int, accumulate: bool = False) -> None:
     """out[m][n] (+)= sum_r dy[r][m] x[r][n]: deferred weight gradient over r = (frame, batch) rows."""
     if prec == 1:
-        ops.gemm_tn(_rows8(dy.to(BF16)), _rows8(x.to(BF16)), out, accumulate=accumulate)
+        # (.to is a no-op for operands the caller already converted once)
+        ops.gemm_tn(_rows8(dy.to(BF16)), _rows8(x.to(BF16)), out, accumulate=accumulate,
+                    block_n=256 if out.shape[1] >= 512 else 128)
         return
     # fp32 mode: stack the plane products along K (rows): (hi,hi),(lo,hi),(lo2,hi),(hi,lo),(lo,lo),(hi,lo2)
     dh = packing.split3(dy)
@@ -531,27 +533,36 @@ class _DecoderTrainFn(torch.autograd.Function):
         dga = wk["dga_all"].reshape(TB, -1)
         dgd = wk["dgd_all"].reshape(TB, -1)
         pre_T = S["pre"][:TB]                                   # prenet outputs of frames 0..T-1
-        h_a_prev, h_a_cur = sv["h_a_buf"][:T].reshape(TB, -1), sv["h_a_buf"][1:].reshape(TB, -1)
-        h_d_prev, h_d_cur = sv["h_d_buf"][:T].reshape(TB, -1), sv["h_d_buf"][1:].reshape(TB, -1)
-        ctx_prev, ctx_cur = sv["ctx_buf"][:T].reshape(TB, -1), sv["ctx_buf"][1:].reshape(TB, -1)
+        bf = (lambda x: x.to(BF16)) if prec == 1 else (lambda x: x)    # bf16 mode: every GEMM operand is converted ONCE
+        dga_o, dgd_o, dout_o = bf(dga), bf(dgd), bf(dout2)
+        ha_o, hd_o, cx_o = bf(sv["h_a_buf"]), bf(sv["h_d_buf"]), bf(sv["ctx_buf"])
+        h_a_prev, h_a_cur = ha_o[:T].reshape(TB, -1), ha_o[1:].reshape(TB, -1)
+        h_d_prev, h_d_cur = hd_o[:T].reshape(TB, -1), hd_o[1:].reshape(TB, -1)
+        ctx_prev, ctx_cur = cx_o[:T].reshape(TB, -1), cx_o[1:].reshape(TB, -1)
         Ha, Hd, P = d.att_rnn, d.dec_rnn, d.prenet
         g_w_ih_a = torch.empty(4 * Ha, P + D, device=dev)
-        _wgrad_tn(dga, pre_T, g_w_ih_a[:, :P], prec)
-        _wgrad_tn(dga, ctx_prev, g_w_ih_a[:, P:], prec)
+        _wgrad_tn(dga_o, pre_T, g_w_ih_a[:, :P], prec)
+        _wgrad_tn(dga_o, ctx_prev, g_w_ih_a[:, P:], prec)
         g_w_hh_a = torch.empty(4 * Ha, Ha, device=dev)
-        _wgrad_tn(dga, h_a_prev, g_w_hh_a, prec)
+        _wgrad_tn(dga_o, h_a_prev, g_w_hh_a, prec)
         g_w_ih_d = torch.empty(4 * Hd, Ha + D, device=dev)
-        _wgrad_tn(dgd, h_a_cur, g_w_ih_d[:, :Ha], prec)
-        _wgrad_tn(dgd, ctx_cur, g_w_ih_d[:, Ha:], prec)
+        _wgrad_tn(dgd_o, h_a_cur, g_w_ih_d[:, :Ha], prec)
+        _wgrad_tn(dgd_o, ctx_cur, g_w_ih_d[:, Ha:], prec)
         g_w_hh_d = torch.empty(4 * Hd, Hd, device=dev)
-        _wgrad_tn(dgd, h_d_prev, g_w_hh_d, prec)
-        ones = torch.ones(TB, 8, device=dev)
-        g_b_a = torch.empty(4 * Ha, 8, device=dev); _wgrad_tn(dga, ones, g_b_a, prec); g_b_a = g_b_a[:, 0].contiguous()
-        g_b_d = torch.empty(4 * Hd, 8, device=dev); _wgrad_tn(dgd, ones, g_b_d, prec); g_b_d = g_b_d[:, 0].contiguous()
+        _wgrad_tn(dgd_o, h_d_prev, g_w_hh_d, prec)
+        if prec == 1:
+            # bias gradients = column sums of the (bf16-rounded, as in the GEMMs) gate gradients, fp32 accumulate
+            g_b_a = dga_o.sum(0, dtype=torch.float32)
+            g_b_d = dgd_o.sum(0, dtype=torch.float32)
+            g_bpg = dout_o.sum(0, dtype=torch.float32)
+        else:
+            ones = torch.ones(TB, 8, device=dev)
+            g_b_a = torch.empty(4 * Ha, 8, device=dev); _wgrad_tn(dga, ones, g_b_a, prec); g_b_a = g_b_a[:, 0].contiguous()
+            g_b_d = torch.empty(4 * Hd, 8, device=dev); _wgrad_tn(dgd, ones, g_b_d, prec); g_b_d = g_b_d[:, 0].contiguous()
+            g_bpg = torch.empty(n_out, 8, device=dev); _wgrad_tn(dout2, ones, g_bpg, prec); g_bpg = g_bpg[:, 0]
         g_wpg = torch.empty(n_out, Hd + D, device=dev)
-        _wgrad_tn(dout2, h_d_cur, g_wpg[:, :Hd], prec)
-        _wgrad_tn(dout2, ctx_cur, g_wpg[:, Hd:], prec)
-        g_bpg = torch.empty(n_out, 8, device=dev); _wgrad_tn(dout2, ones, g_bpg, prec); g_bpg = g_bpg[:, 0]
+        _wgrad_tn(dout_o, h_d_cur, g_wpg[:, :Hd], prec)
+        _wgrad_tn(dout_o, ctx_cur, g_wpg[:, Hd:], prec)
         g_wq = torch.empty(d.att_dim, Ha, device=dev)
         _wgrad_tn(wk["dq_all"].reshape(TB, -1), h_a_cur, g_wq, prec)
         # prenet backward (relu + always-on dropout: y = relu(x) * keep * 2  =>  dx = dy * 2 * [y > 0])
