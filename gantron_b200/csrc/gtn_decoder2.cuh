@@ -158,6 +158,7 @@ struct Ring {
   int S;
   uint32_t stage_bytes;
   uint32_t prod_it, mma_it;
+  int pre;                // k-blocks of the NEXT job already issued by gemm_preissue (producer thread only)
 };
 
 struct XSeg {
@@ -174,25 +175,42 @@ struct GemmJob {
   XSeg seg[3];
 };
 
+// producer step: TMA loads of k-block kb (weights + the matching activation segment) into the next ring slot
+template <int N>
+GTN_DEVICE void produce_kblock(const GemmJob& job, Ring& rg, int kb) {
+  constexpr uint32_t X_BYTES = N * KB * 2;
+  const int s = rg.prod_it % rg.S;
+  const uint32_t par = (rg.prod_it / rg.S) & 1u;
+  wait_bar(&rg.empty[s], par ^ 1u);
+  mbar_expect_tx(&rg.full[s], W_TILE_BYTES + X_BYTES);
+  uint8_t* st = rg.base + (size_t)s * rg.stage_bytes;
+  tma_load_3d(st, job.wmap, &rg.full[s], kb * KB, job.row0, 0);
+  int kk = kb, si = 0;
+  while (si < job.nseg - 1 && kk >= job.seg[si].nkb) { kk -= job.seg[si].nkb; ++si; }
+  tma_load_3d(st + W_TILE_BYTES, job.seg[si].map, &rg.full[s], kk * KB, 0, job.seg[si].z);
+  ++rg.prod_it;
+}
+
+// Start the loads of a job whose operands are already final while the CTA is still busy with the previous job's
+// exchange / epilogue: fills up to S ring slots (all free once the previous accumulator is complete).  The matching
+// gemm_issue call continues after the pre-issued k-blocks.  Producer thread only.
+template <int N>
+GTN_DEVICE void gemm_preissue(const GemmJob& job, Ring& rg, int rank) {
+  const int kb0 = rank * job.nkb / CL, kb1 = (rank + 1) * job.nkb / CL;
+  int n = kb1 - kb0;
+  if (n > rg.S) n = rg.S;
+  for (int i = 0; i < n; ++i) produce_kblock<N>(job, rg, kb0 + i);
+  rg.pre = n;
+}
+
 // Issue one cluster-split GEMM: this CTA's quarter of K.  Producer = thread 0, MMA = thread 32.
 // Returns whether this CTA had any k-block (else its partial tile is all zeros).
 template <int N>
 GTN_DEVICE bool gemm_issue(const GemmJob& job, Ring& rg, uint32_t tmem_acc, uint64_t* acc_full, int rank) {
   const int kb0 = rank * job.nkb / CL, kb1 = (rank + 1) * job.nkb / CL;
-  constexpr uint32_t X_BYTES = N * KB * 2;
   if (threadIdx.x == 0) {
-    for (int kb = kb0; kb < kb1; ++kb) {
-      const int s = rg.prod_it % rg.S;
-      const uint32_t par = (rg.prod_it / rg.S) & 1u;
-      wait_bar(&rg.empty[s], par ^ 1u);
-      mbar_expect_tx(&rg.full[s], W_TILE_BYTES + X_BYTES);
-      uint8_t* st = rg.base + (size_t)s * rg.stage_bytes;
-      tma_load_3d(st, job.wmap, &rg.full[s], kb * KB, job.row0, 0);
-      int kk = kb, si = 0;
-      while (si < job.nseg - 1 && kk >= job.seg[si].nkb) { kk -= job.seg[si].nkb; ++si; }
-      tma_load_3d(st + W_TILE_BYTES, job.seg[si].map, &rg.full[s], kk * KB, 0, job.seg[si].z);
-      ++rg.prod_it;
-    }
+    for (int kb = kb0 + rg.pre; kb < kb1; ++kb) produce_kblock<N>(job, rg, kb);
+    rg.pre = 0;
   } else if (threadIdx.x == 32) {
     if (kb1 > kb0) {
       const uint32_t idesc = umma_idesc_bf16(TILE_M, N);

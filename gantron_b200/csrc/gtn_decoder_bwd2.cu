@@ -88,6 +88,7 @@ GTN_DEVICE SmemB carveB(uint8_t* base, int S) {
   m.ring.S = S;
   m.ring.stage_bytes = W_TILE_BYTES + N * KB * 2;
   m.ring.prod_it = m.ring.mma_it = 0;
+  m.ring.pre = 0;
   size_t ring_b = (size_t)S * m.ring.stage_bytes;
   if (ring_b < (size_t)P2_RING_BYTES) ring_b = P2_RING_BYTES;
   uint8_t* p = base + ring_b;

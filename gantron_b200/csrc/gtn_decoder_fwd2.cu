@@ -85,6 +85,7 @@ GTN_DEVICE Smem2 carve2(uint8_t* base, int S) {
   m.ring.S = S;
   m.ring.stage_bytes = W_TILE_BYTES + N * KB * 2;
   m.ring.prod_it = m.ring.mma_it = 0;
+  m.ring.pre = 0;
   uint8_t* p = base + (size_t)S * m.ring.stage_bytes;
   m.u_s = p; p += 2 * W_TILE_BYTES;
   float* f = reinterpret_cast<float*>(p);
@@ -123,13 +124,9 @@ GTN_DEVICE float block_reduce2(float v, float* scr, bool is_max) {
 // ------------------------------------------------------------------------------------------------
 // GEMM phases: prenet layers, the two LSTM cells, the mel/gate projection
 // ------------------------------------------------------------------------------------------------
-template <int N>
-GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int kind, int t, int rank, int cid, int ncl,
-                           uint32_t tmem_base, uint32_t& acc_par, uint32_t& round, float (&wqr)[32]) {
-  constexpr int CH = N < 64 ? N : 64;
-  constexpr int NC4 = CH / 4;
+// Operands of the GEMM phase `kind` of frame t; returns the number of 128-row tiles.
+GTN_DEVICE int make_job(const DecFwd& p, const Fwd2Maps& maps, int kind, int t, GemmJob& job) {
   const int mult = p.mult, cur = t & 1, nxt = cur ^ 1;
-  GemmJob job;
   int ntiles;
   switch (kind) {
     case K_PRE1:
@@ -160,6 +157,17 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
   }
   job.nkb = 0;
   for (int i = 0; i < job.nseg; ++i) job.nkb += job.seg[i].nkb;
+  return ntiles;
+}
+
+template <int N>
+GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int kind, int t, int rank, int cid, int ncl,
+                           uint32_t tmem_base, uint32_t& acc_par, uint32_t& round, float (&wqr)[32]) {
+  constexpr int CH = N < 64 ? N : 64;
+  constexpr int NC4 = CH / 4;
+  const int mult = p.mult, cur = t & 1, nxt = cur ^ 1;
+  GemmJob job;
+  const int ntiles = make_job(p, maps, kind, t, job);
   const bool is_lstm = kind == K_ATT || kind == K_DEC;
   const bool is_att = kind == K_ATT;
   const int H = is_att ? p.Ha : p.Hd, Hp = is_att ? p.Hap : p.Hdp;
@@ -196,7 +204,7 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
 #pragma unroll
         for (int q = 0; q < CPT; ++q) {
           const int idx = threadIdx.x + q * 256;
-          const int bl = idx % NC4, ul = idx / NC4, b = bbase + bl, unit = tile * 32 + ul;
+          const int ul = idx & 31, bl = idx >> 5, b = bbase + bl, unit = tile * 32 + ul;   // lanes run over hidden units
           gb[q] = make_float4(0.f, 0.f, 0.f, 0.f);
           cprev[q] = 0.f;
           if (b < p.B) {
@@ -207,7 +215,7 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
           }
         }
       }
-      exchange_chunk<CH>(has_work, tmem_base, c0, recv, rank);
+      exchange_chunk<CH, true>(has_work, tmem_base, c0, recv, rank);
       PROF(ps + 2);                              // DSMEM exchange + cluster barrier done
       if (is_lstm) {
         const float pdrop = is_att ? p.p_att : p.p_dec;
@@ -221,13 +229,13 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
 #pragma unroll
         for (int q = 0; q < CPT; ++q) {
           const int idx = threadIdx.x + q * 256;
-          const int bl = idx % NC4, ul = idx / NC4, b = bbase + bl, unit = tile * 32 + ul;
+          const int ul = idx & 31, bl = idx >> 5, b = bbase + bl, unit = tile * 32 + ul;
           float h = 0.f;
           if (b < p.B) {
-            const float i_ = sigmoid_acc(recv_sum<NC4>(recv, ul, bl) + gb[q].x);
-            const float f_ = sigmoid_acc(recv_sum<NC4>(recv, 32 + ul, bl) + gb[q].y);
-            const float g_ = tanh_acc(recv_sum<NC4>(recv, 64 + ul, bl) + gb[q].z);
-            const float o_ = sigmoid_acc(recv_sum<NC4>(recv, 96 + ul, bl) + gb[q].w);
+            const float i_ = sigmoid_acc(recv_sum<NC4, true>(recv, ul, bl) + gb[q].x);
+            const float f_ = sigmoid_acc(recv_sum<NC4, true>(recv, 32 + ul, bl) + gb[q].y);
+            const float g_ = tanh_acc(recv_sum<NC4, true>(recv, 64 + ul, bl) + gb[q].z);
+            const float o_ = sigmoid_acc(recv_sum<NC4, true>(recv, 96 + ul, bl) + gb[q].w);
             const size_t ci = (size_t)b * H + unit;
             const float c_new = f_ * cprev[q] + i_ * g_;
             cst[ci] = c_new;
@@ -247,7 +255,9 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
           if (is_att) sm.hs[ul * NC4 + bl] = h;
         }
         if (is_att) {
+          if (p.train) PROF(14);
           __syncthreads();
+          if (p.train) PROF(15);
           // partial query of this tile: qpart[tile][b][a] = sum_u Wq[a][32 tile + u] h[b][u]; thread = (a, half of the columns)
           constexpr int HB = NC4 / 2;
           const int a = threadIdx.x & 127, g = threadIdx.x >> 7;
@@ -264,6 +274,7 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
               acc[4 * j4 + 2] += wqr[u] * hv.z; acc[4 * j4 + 3] += wqr[u] * hv.w;
             }
           }
+          if (p.train) PROF(16);
           if (a < p.A) {
 #pragma unroll
             for (int j = 0; j < HB; ++j) {
@@ -277,7 +288,7 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
         for (int idx = threadIdx.x; idx < TILE_M * NC4; idx += blockDim.x) {
           const int bl = idx % NC4, r = idx / NC4, b = bbase + bl, row = tile * TILE_M + r;
           if (b >= p.B || row >= rows) continue;
-          float val = recv_sum<NC4>(recv, r, bl);
+          float val = recv_sum<NC4, true>(recv, r, bl);
           if (kind != K_PROJ) {
             val = fmaxf(val, 0.f);
             const uint32_t bits = philox_bits(p.seed, kind == K_PRE1 ? 1u : 2u, (uint32_t)t, (uint32_t)(b * p.P + row));
@@ -352,23 +363,42 @@ GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, in
     const int L = active ? (p.lengths ? min(p.lengths[b], Tin) : Tin) : 0;
     float* e_buf = sm.e_buf + (size_t)(eround & 1u) * TIN_MAX;
     ++eround;
+    // this thread's slice of processed_memory (row = encoder position, 64 attention columns) does not depend on the frame's
+    // recurrent state: requested first so that its latency hides behind the query gather / im2col / MMA  (bf16 only)
+    constexpr bool PM_PRE = sizeof(MT) == 2;
+    uint4 pmq[PM_PRE ? 8 : 1];
+    {
+      const int wq_ = warp & 3, a0_ = (warp >> 2) * 64, jl_ = wq_ * 32 + lane;
+      if (PM_PRE && active && jl_ < jn && (j0 + jl_) < L) {
+        const uint4* src = reinterpret_cast<const uint4*>(pm + ((size_t)b * Tin + (j0 + jl_)) * A + a0_);
+#pragma unroll
+        for (int g = 0; g < 8; ++g)
+          if (a0_ + g * 8 < A) pmq[g] = __ldg(src + g);
+      }
+    }
     if (active) {
       const int ntq = p.Ha / 32;
       for (int a = threadIdx.x; a < A; a += blockDim.x) {
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        // every partial of the query in flight at once: one L2 round trip instead of ntq / 8
         const float* qp = p.qpart + (size_t)b * A + a;
         const size_t qs = (size_t)p.B * A;
-        int c = 0;
-#pragma unroll 2
-        for (; c + 4 <= ntq; c += 4) {
-          s0 += __ldcg(qp + (size_t)c * qs); s1 += __ldcg(qp + (size_t)(c + 1) * qs);
-          s2 += __ldcg(qp + (size_t)(c + 2) * qs); s3 += __ldcg(qp + (size_t)(c + 3) * qs);
+        float s = 0.f;
+        for (int c0 = 0; c0 < ntq; c0 += 32) {
+          float qv[32];
+#pragma unroll
+          for (int c = 0; c < 32; ++c) qv[c] = (c0 + c < ntq) ? __ldcg(qp + (size_t)(c0 + c) * qs) : 0.f;
+#pragma unroll
+          for (int c = 0; c < 16; ++c) qv[c] += qv[c + 16];
+#pragma unroll
+          for (int c = 0; c < 8; ++c) qv[c] += qv[c + 8];
+#pragma unroll
+          for (int c = 0; c < 4; ++c) qv[c] += qv[c + 4];
+          s += (qv[0] + qv[1]) + (qv[2] + qv[3]);
         }
-        for (; c < ntq; ++c) s0 += __ldcg(qp + (size_t)c * qs);
-        const float s = (s0 + s1) + (s2 + s3);
         sm.q_s[a] = s;
         if (p.train && half == 0) p.q_all[((size_t)t * p.B + b) * A + a] = s;
       }
+      if (p.train) PROF(7);
       const float* wprev = p.w_prev + (size_t)b * p.ldT;
       const float* wcum = p.w_cum + (size_t)b * p.ldT;
       for (int i = threadIdx.x; i < 2 * Wd; i += blockDim.x) {
@@ -378,13 +408,17 @@ GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, in
         if (p.train && ch == 1 && jj >= hk && jj < hk + jn) p.cum_all[((size_t)t * p.B + b) * Tin + j] = val;
       }
     }
+    if (p.train) PROF(12);
     __syncthreads();
+    if (p.train) PROF(20);
     if (active) {
       // im2col: row r = local encoder position, K index kk = ch*KS + k  ->  wcat[ch][r + k]; bf16 hi / lo planes
       build_im2col(sm.wcat, Wd, KS, jn, a_hi, a_lo);
       fence_proxy_async_smem();
     }
+    if (p.train) PROF(21);
     __syncthreads();
+    if (p.train) PROF(22);
     if (active && threadIdx.x == 32) {
       tc_fence_after();
       const uint32_t idesc = umma_idesc_bf16(TILE_M, 128);
@@ -422,7 +456,17 @@ GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, in
             const int ab = h * 32 + g * 8;
             if (a0 + ab < A) {
               float pmv[8];
-              ld8<MT>(pmj + ab, pmv);
+              if (PM_PRE) {
+                const uint4 qq = pmq[h * 4 + g];
+                const uint32_t ww[4] = {qq.x, qq.y, qq.z, qq.w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  pmv[2 * i] = __uint_as_float(ww[i] << 16);
+                  pmv[2 * i + 1] = __uint_as_float(ww[i] & 0xFFFF0000u);
+                }
+              } else {
+                ld8<MT>(pmj + ab, pmv);
+              }
               float th[8];
 #pragma unroll
               for (int e = 0; e < 8; ++e) {
@@ -497,7 +541,19 @@ GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, in
         for (int e = 0; e < 8; ++e) acc[e] = 0.f;
         if (c8 < c8_n) {
           const MT* mp = mem + (size_t)b * Tin * p.E + (size_t)(c8_0 + c8) * 8;
-          for (int j = warp; j < L; j += 8) {
+          int j = warp;
+          for (; j + 24 < L; j += 32) {              // four rows of this warp in flight
+            float mv[4][8];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) ld8<MT>(mp + (size_t)(j + 8 * r) * p.E, mv[r]);
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+              const float w = sm.w_s[j + 8 * r];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) acc[e] += w * mv[r][e];
+            }
+          }
+          for (; j < L; j += 8) {
             float mv[8];
             ld8<MT>(mp + (size_t)j * p.E, mv);
             const float w = sm.w_s[j];
@@ -572,9 +628,13 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
   int t = 0;
   for (; t < p.n_steps; ++t) {
     if (!p.train) {
+      PROF(28);
       gemm_phase<N>(p, maps, sm, K_PRE1, t, rank, cid, ncl, tmem_base, acc_par, round, wqr);
+      PROF(29);
       grid_sync2(p.barrier, epoch, nblocks);
+      PROF(30);
       gemm_phase<N>(p, maps, sm, K_PRE2, t, rank, cid, ncl, tmem_base, acc_par, round, wqr);
+      PROF(31);
       grid_sync2(p.barrier, epoch, nblocks);
     }
     PROF(0);
@@ -591,8 +651,11 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
     PROF(13);
     if (!p.train) {
       grid_sync2(p.barrier, epoch, nblocks);
+      PROF(18);
       gemm_phase<N>(p, maps, sm, K_PROJ, t, rank, cid, ncl, tmem_base, acc_par, round, wqr);
+      PROF(19);
       grid_sync2(p.barrier, epoch, nblocks);
+      PROF(23);
       if (__ldcg(p.stop) != 0) { ++t; break; }
     }
   }

@@ -16,10 +16,11 @@ hp = HParams("use_noise=True,use_labels=False,b200_precision=bf16")
 dec = Decoder(hp).cuda().train()
 mem = torch.cat((torch.randn(B, 150, 512).cuda() * 0.5, torch.rand(B, 1, 512).repeat_interleave(150, 1).cuda()), -1).requires_grad_(True)
 mels = (torch.randn(B, 80, T) * 2 - 5).clamp(-11.5, 2).cuda()
-FW = {0: "step start", 1: "att: TMA issued", 2: "att: acc done", 3: "att: exchange done", 4: "att: epilogue done",
+FW = {14: "att: cells done", 15: "att: sync", 16: "att: qpart computed", 7: "attn: q gathered", 12: "attn: window loaded", 20: "attn: sync", 21: "attn: im2col built", 22: "attn: sync2",
+      0: "step start", 1: "att: TMA issued", 2: "att: acc done", 3: "att: exchange done", 4: "att: epilogue done",
       5: "gsync1 done", 24: "attn: mma issued", 25: "attn: energies", 26: "attn: cluster sync", 27: "attn: softmax",
       6: "attn done", 8: "gsync2 done", 9: "dec: TMA issued", 10: "dec: acc done", 11: "dec: exchange done", 13: "dec done"}
-FO = [0, 1, 2, 3, 4, 5, 24, 25, 26, 27, 6, 8, 9, 10, 11, 13]
+FO = [0, 1, 2, 3, 14, 15, 16, 4, 5, 7, 12, 20, 21, 22, 24, 25, 26, 27, 6, 8, 9, 10, 11, 13]
 BW = {0: "step start", 1: "P1: TMA issued", 2: "P1: acc done", 3: "P1: exchange done", 4: "P1: epilogue done", 5: "gsync done",
       10: "P2: loads + window", 11: "P2: dw + dot", 12: "P2: cluster sync 1", 13: "P2: dth tiles + dq/dv", 15: "P2: MMA + G to smem",
       16: "P2: d wcat", 17: "P2: cluster sync 2", 18: "P2 done", 19: "gsync done", 22: "P3: dq staged", 23: "P3: cell loads issued", 24: "P3: dot 0 done", 25: "P3: apply 0 done", 20: "P3 done", 21: "gsync done"}

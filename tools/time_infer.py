@@ -13,7 +13,7 @@ steps = int(sys.argv[1]) if len(sys.argv) > 1 else 200
 torch.manual_seed(0)
 hp = HParams(f"use_noise=True,use_labels=False,b200_precision=bf16,max_decoder_steps={steps}")
 dec = Decoder(hp).cuda().eval()
-for ver in ("1", "2"):
+for ver in ("2",):
     os.environ["GANTRON_B200_DECODER"] = ver
     for B in (1, 64, 256):
         mem = torch.cat((torch.randn(B, 150, 512).cuda() * 0.5, torch.rand(B, 1, 512).repeat_interleave(150, 1).cuda()), -1)
@@ -37,8 +37,9 @@ if os.environ.get("GTN_PROF"):
     names = {0: "step start", 1: "att: TMA issued", 2: "att: acc done", 3: "att: exchange done", 4: "att: epilogue done",
              5: "gsync1 done", 24: "attn: mma issued", 25: "attn: energies", 26: "attn: cluster sync", 27: "attn: softmax",
              6: "attn done", 8: "gsync2 done", 9: "dec: TMA issued", 10: "dec: acc done", 11: "dec: exchange done",
-             13: "dec done"}
-    order = [0, 1, 2, 3, 4, 5, 24, 25, 26, 27, 6, 8, 9, 10, 11, 13]
+             13: "dec done", 28: "frame start (pre1)", 29: "pre1 done", 30: "gsync done", 31: "pre2 done",
+             18: "gsync3 done", 14: "proj: TMA issued", 15: "proj: acc done", 16: "proj: exchange done", 19: "proj done", 23: "gsync4 done"}
+    order = [28, 29, 30, 31, 0, 1, 2, 3, 4, 5, 24, 25, 26, 27, 6, 8, 9, 10, 11, 13, 18, 14, 15, 16, 19, 23]
     for B, train in ((1, False), (64, False), (64, True)):
         prof = torch.zeros(16 * 32, dtype=torch.int64, device="cuda")
         decoder_ops.PROF_BUFFER = prof
@@ -57,8 +58,13 @@ if os.environ.get("GTN_PROF"):
         pr = prof.cpu().view(16, 32)
         print(f"--- B={B} train={train}: cycles since step start, frame 8 (and frame 9 start)")
         t = 8
+        base = int(pr[t, 28]) if int(pr[t, 28]) else int(pr[t, 0])
+        prev = base
         for sl in order:
             if int(pr[t, sl]):
-                print(f"   {names[sl]:22s} {int(pr[t, sl] - pr[t, 0]):8d}")
-        print(f"   next step start        {int(pr[t + 1, 0] - pr[t, 0]):8d}")
+                v = int(pr[t, sl])
+                print(f"   {names[sl]:22s} {v - base:8d}  (+{v - prev})")
+                prev = v
+        nxt = int(pr[t + 1, 28]) if int(pr[t + 1, 28]) else int(pr[t + 1, 0])
+        print(f"   next frame start       {nxt - base:8d}")
     decoder_ops.PROF_BUFFER = None
