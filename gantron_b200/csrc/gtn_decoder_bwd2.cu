@@ -655,6 +655,50 @@ GTN_DEVICE void att_cell_phase2(const DecBwd2& p, SmemB& sm, int t, int it) {
   }
 }
 
+// The saves of the forward pass stream from HBM exactly once and their addresses are known a whole frame ahead: at the
+// top of frame t every CTA asks L2 for what ITS P2 (attention backward of its sequence) and P3 (cell backward of its
+// hidden units) will read, so that those phases see L2 latency instead of a dependent HBM round trip.
+GTN_DEVICE void prefetch_l2(const void* ptr) { asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr)); }
+
+GTN_DEVICE void prefetch_frame(const DecBwd2& p, int t, int rank, int cid, int ncl) {
+  const int Tin = p.Tin, A = p.A;
+  // ---- P2 operands of this CTA's sequence(s)
+  const int half = rank & 1, pair = cid * 2 + (rank >> 1), npairs = ncl * 2;
+  const int JH = (Tin + 1) / 2, j0 = half * JH, jn = min(Tin, j0 + JH) - j0;
+  for (int b = pair; b < p.B; b += npairs) {
+    const size_t tb = (size_t)t * p.B + b, bt = (size_t)b * p.T + t;
+    const char* th = reinterpret_cast<const char*>(p.th_all + (tb * Tin + j0) * A);
+    const int th_lines = (jn * A * 4 + 127) / 128;
+    for (int i = threadIdx.x; i < th_lines; i += blockDim.x) prefetch_l2(th + (size_t)i * 128);
+    const int row_lines = (Tin * 4 + 127) / 128 + 1;
+    if ((int)threadIdx.x < row_lines) {
+      prefetch_l2(reinterpret_cast<const char*>(p.align + bt * Tin) + threadIdx.x * 128);
+      prefetch_l2(reinterpret_cast<const char*>(p.cum_all + tb * Tin) + threadIdx.x * 128);
+      if (p.dalign) prefetch_l2(reinterpret_cast<const char*>(p.dalign + bt * Tin) + threadIdx.x * 128);
+    }
+    const int dp_lines = (p.E * 4 + 127) / 128 + 1;
+    if ((int)threadIdx.x >= 32 && (int)threadIdx.x < 32 + dp_lines)
+      prefetch_l2(reinterpret_cast<const char*>(p.dproj_all + tb * (p.Hd + p.D) + p.Hd) + (threadIdx.x - 32) * 128);
+  }
+  // ---- P3 operands of this CTA's hidden units: one (or two) 128-byte lines per sequence and array
+  const int UPC = (p.Ha + gridDim.x - 1) / gridDim.x, ua = blockIdx.x * UPC;
+  const int UPCd = (p.Hd + gridDim.x - 1) / gridDim.x, ud = blockIdx.x * UPCd;
+  for (int b = threadIdx.x >> 2; b < p.B; b += blockDim.x >> 2) {
+    const int which = threadIdx.x & 3;
+    if (ua < p.Ha) {
+      const size_t cell = ((size_t)t * p.B + b) * p.Ha + ua;
+      if (which == 0) prefetch_l2(reinterpret_cast<const float4*>(p.gates_a) + cell);
+      if (which == 1) { prefetch_l2(p.c_a_all + cell); if (t > 0) prefetch_l2(p.c_a_all + cell - (size_t)p.B * p.Ha); }
+    }
+    if (t > 0 && ud < p.Hd) {
+      const size_t cell = ((size_t)(t - 1) * p.B + b) * p.Hd + ud;
+      if (which == 2) prefetch_l2(reinterpret_cast<const float4*>(p.gates_d) + cell);
+      if (which == 2 && t > 1) prefetch_l2(p.c_d_all + cell - (size_t)p.B * p.Hd);
+      if (which == 3) { prefetch_l2(p.c_d_all + cell); prefetch_l2(p.dproj_all + ((size_t)(t - 1) * p.B + b) * (p.Hd + p.D) + ud); }
+    }
+  }
+}
+
 template <int N>
 __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_constant__ Bwd2Maps maps, const DecBwd2 p, const int S) {
   extern __shared__ uint8_t smem_raw[];
@@ -694,6 +738,7 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
   int it = 0;
   for (int t = p.T - 1; t >= 0; --t, ++it) {
     PROFB(0);
+    prefetch_frame(p, t, rank, cid, ncl);
     dgrad_phase2<N>(p, maps, sm, t, it, rank, cid, ncl, tmem_base, acc_par, round);
     PROFB(4);
     grid_sync2(p.barrier, epoch, nblocks);
