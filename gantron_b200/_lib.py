@@ -118,6 +118,7 @@ class DecoderBwd2Params(C.Structure):
                               "dproj_all", "dalign", "xdg_a", "xdg_d", "carry_ha", "dha_dec", "dc_a", "dc_d", "dhd_rec",
                               "dctx_att", "dctx_dec", "dwprev", "dcum", "dq_sum", "barrier",
                               "dga_all", "dgd_all", "dq_all", "dctx_all", "dpm", "dv_part", "dU_part", "prof")]
+        + [("flags", c_i)]
     )
 
 

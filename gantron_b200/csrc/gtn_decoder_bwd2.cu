@@ -702,7 +702,8 @@ GTN_DEVICE void prefetch_frame(const DecBwd2& p, int t, int rank, int cid, int n
 template <int N>
 __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_constant__ Bwd2Maps maps, const DecBwd2 p, const int S) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // align by pointer arithmetic (no integer round trip) so that the compiler keeps the shared address space: LDS / STS, not generic LD / ST
+  uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   SmemB sm = carveB<N>(base, S);
   const int warp = threadIdx.x >> 5;
   const int rank = (int)cluster_ctarank(), cid = (int)cluster_idx(), ncl = (int)cluster_count();
@@ -738,7 +739,7 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
   int it = 0;
   for (int t = p.T - 1; t >= 0; --t, ++it) {
     PROFB(0);
-    prefetch_frame(p, t, rank, cid, ncl);
+    if (p.flags & 1) prefetch_frame(p, t, rank, cid, ncl);
     dgrad_phase2<N>(p, maps, sm, t, it, rank, cid, ncl, tmem_base, acc_par, round);
     PROFB(4);
     grid_sync2(p.barrier, epoch, nblocks);

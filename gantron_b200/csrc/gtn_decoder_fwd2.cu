@@ -591,7 +591,8 @@ template <int N>
 __global__ void __launch_bounds__(256, 1)
 decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const int S) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // align by pointer arithmetic (no integer round trip) so that the compiler keeps the shared address space: LDS / STS, not generic LD / ST
+  uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   Smem2 sm = carve2<N>(base, S);
   const int warp = threadIdx.x >> 5;
   const int rank = (int)cluster_ctarank(), cid = (int)cluster_idx(), ncl = (int)cluster_count();

@@ -7,6 +7,8 @@ one cooperative kernel launch.
 """
 from __future__ import annotations
 
+import os
+
 import ctypes as C
 from dataclasses import dataclass
 from typing import Dict, Optional, Tuple
@@ -634,6 +636,7 @@ def _bptt_v2(dec, pk, d, ctx, S, sv, dproj, d_align, prec):
     q.align, q.th_all, q.cum_all = sv["align"].data_ptr(), sv["th_all"].data_ptr(), sv["cum_all"].data_ptr()
     q.dproj_all = dproj.data_ptr()
     q.prof = PROF_BUFFER_BWD.data_ptr() if PROF_BUFFER_BWD is not None else None
+    q.flags = int(os.environ.get("GTN_BWD_FLAGS", "0"))
     d_align_c = None
     if d_align is not None:
         d_align_c = d_align.float().contiguous()
