@@ -400,6 +400,7 @@ def kernel_roofline(tr, batch, pk):
         if it:
             best = e0.elapsed_time(e1) if best is None else min(best, e0.elapsed_time(e1))
     tf = 2.0 * 4096 * 1024 * TB / (best * 1e-3) / 1e12
+    assert out, "kernel timing hook recorded no launch of the persistent decoder kernels"
     roof = out.get("decoder_bwd2_kernel") or next(iter(out.values()))
     roof["other_kernels"] = {k: v for k, v in out.items() if k != roof["kernel"]}
     roof["batched_gemm"] = {"kernel": "gemm_tc_kernel<256> weight gradient M=4096 N=1024 K=51200 (MN-major bf16)", "bound": "tensor",

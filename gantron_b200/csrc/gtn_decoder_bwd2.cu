@@ -386,28 +386,27 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
       const uint32_t toff = (uint32_t)(ap >> 6) * W_TILE_BYTES + (uint32_t)((ap & 7) * 2);
       const int chunk = (ap & 63) >> 3;
       float dq0 = 0.f, dq1 = 0.f, dv0 = 0.f, dv1 = 0.f;
-      for (int jb = rg; jb < TILE_M; jb += 16) {
-        float2 th[4], dp[4];
-        float de[4];
-        bool ok[4];
+      for (int jb = rg; jb < TILE_M; jb += 32) {
+        // eight rows per trip (jb, jb + 4, ..., jb + 28): all of their loads are issued before any is consumed
+        constexpr int RW = 8;
+        float2 th[RW], dp[RW];
+        float de[RW];
+        bool ok[RW];
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
+        for (int r = 0; r < RW; ++r) {
           const int jl = jb + 4 * r, j = j0 + jl;
           ok[r] = a_ok && jl < jn && j < L;
           th[r] = make_float2(0.f, 0.f);
+          dp[r] = make_float2(0.f, 0.f);
           de[r] = 0.f;
           if (ok[r]) {
             th[r] = __ldg(reinterpret_cast<const float2*>(p.th_all + ((tb * Tin + j) * A + ap)));
+            dp[r] = *reinterpret_cast<const float2*>(p.dpm + (((size_t)b * Tin + j) * A + ap));
             de[r] = sm.dw_s[j];
           }
         }
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-          dp[r] = make_float2(0.f, 0.f);
-          if (ok[r]) dp[r] = *reinterpret_cast<const float2*>(p.dpm + (((size_t)b * Tin + (j0 + jb + 4 * r)) * A + ap));
-        }
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
+        for (int r = 0; r < RW; ++r) {
           const int jl = jb + 4 * r;
           const float d0 = de[r] * v0 * (1.f - th[r].x * th[r].x), d1 = de[r] * v1 * (1.f - th[r].y * th[r].y);
           if (ok[r])
@@ -590,9 +589,9 @@ GTN_DEVICE void att_cell_phase2(const DecBwd2& p, SmemB& sm, int t, int it) {
 #pragma unroll
     for (int k = 0; k < 32; ++k) {
       const int i = k * 256 + threadIdx.x;
-      v[k] = i < ntot ? __ldcg(&p.dq_sum[(size_t)bc0 * p.A + i]) : 0.f;
+      v[k] = (i < ntot && !(p.flags & 2)) ? __ldcg(&p.dq_sum[(size_t)bc0 * p.A + i]) : 0.f;
     }
-    const int ncell = nu * nb, ncelld = t > 0 ? nud * nb : 0;
+    const int ncell = (p.flags & 8) ? 0 : nu * nb, ncelld = (t > 0 && !(p.flags & 4)) ? nud * nb : 0;
     const int nround = max((ncell + 511) / 512, (ncelld + 511) / 512);
     for (int rd = 0; rd < nround; ++rd) {
       const int c0 = rd * 512;
@@ -642,7 +641,7 @@ GTN_DEVICE void att_cell_phase2(const DecBwd2& p, SmemB& sm, int t, int it) {
         const float* dq = dq_s + bl;
         float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll 4
-        for (int a = 0; a < p.A; a += 4) {
+        for (int a = 0; a < ((p.flags & 16) ? 4 : p.A); a += 4) {
           s0 += wq[a] * dq[a * 65]; s1 += wq[a + 1] * dq[(a + 1) * 65];
           s2 += wq[a + 2] * dq[(a + 2) * 65]; s3 += wq[a + 3] * dq[(a + 3) * 65];
         }

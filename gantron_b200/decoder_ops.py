@@ -201,6 +201,19 @@ def decoder_version() -> int:
 
 
 PROF_BUFFER_BWD = None
+KERNEL_EVENTS = None     # measurement hook (bench.py): dict name -> [(start_event, end_event)] around the persistent kernels
+
+
+def _timed_call(name, fn):
+    """Run fn(); when KERNEL_EVENTS is set, bracket it with CUDA events on the launching (current) stream."""
+    if KERNEL_EVENTS is None:
+        return fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    r = fn()
+    e1.record()
+    KERNEL_EVENTS.setdefault(name, []).append((e0, e1))
+    return r
 PROF_BUFFER = None     # dev tool: int64 [16*32] device tensor receiving clock64() stamps of CTA 0 (tools/time_infer.py)
 
 
@@ -442,7 +455,8 @@ class _DecoderTrainFn(torch.autograd.Function):
                                                  sv["cum_all"].data_ptr())
         if v2:
             keep = _fill_v2(p, pack_v2(dec, pk, E), mem_const[:, :D - E], prec, B, False)   # noqa: F841 (kept alive)
-            _lib.check(_lib.load().gtn_decoder_forward2(C.byref(p), _lib.stream()), "gtn_decoder_forward2")
+            _lib.check(_timed_call("decoder_fwd2_kernel", lambda: _lib.load().gtn_decoder_forward2(C.byref(p), _lib.stream())),
+                       "gtn_decoder_forward2")
         else:
             _lib.check(_lib.load().gtn_decoder_forward(C.byref(p), _lib.stream()), "gtn_decoder_forward")
 
@@ -636,12 +650,13 @@ def _bptt_v2(dec, pk, d, ctx, S, sv, dproj, d_align, prec):
     q.align, q.th_all, q.cum_all = sv["align"].data_ptr(), sv["th_all"].data_ptr(), sv["cum_all"].data_ptr()
     q.dproj_all = dproj.data_ptr()
     q.prof = PROF_BUFFER_BWD.data_ptr() if PROF_BUFFER_BWD is not None else None
-    q.flags = int(os.environ.get("GTN_BWD_FLAGS", "0"))
+    q.flags = int(os.environ.get("GTN_BWD_FLAGS", "1"))     # bit 0: L2 prefetch of the saves (bits 1-4: dev-only ablations)
     d_align_c = None
     if d_align is not None:
         d_align_c = d_align.float().contiguous()
         q.dalign = d_align_c.data_ptr()
-    _lib.check(lib.gtn_decoder_backward2(C.byref(q), _lib.stream()), "gtn_decoder_backward2")
+    _lib.check(_timed_call("decoder_bwd2_kernel", lambda: lib.gtn_decoder_backward2(C.byref(q), _lib.stream())),
+               "gtn_decoder_backward2")
     TB = T * B
     dga, dgd = wk["dga_all"].reshape(TB, 4 * Ha), wk["dgd_all"].reshape(TB, 4 * Hd)
     # d prenet outputs: dGates_att . W_ih_att[:, :P]
