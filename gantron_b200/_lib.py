@@ -113,10 +113,10 @@ class DecoderBwd2Params(C.Structure):
         [(n, c_i) for n in ("B", "Tin", "ldT", "T", "E", "Ep", "D", "Ha", "Hd", "A", "KS", "prec", "mult",
                             "use_dropout", "mem_bf16", "grid")]
         + [("p_att", c_f), ("p_dec", c_f), ("thr_att", c_u), ("thr_dec", c_u), ("seed", c_ull)]
-        + [(n, c_p) for n in ("wT_att2", "wT_dec2", "ut_loc", "wq_t", "v", "mem_enc", "lengths",
+        + [(n, c_p) for n in ("wT_att2", "wT_dec2", "ut_loc", "wq_au", "v", "mem_enc", "lengths",
                               "gates_a", "c_a_all", "gates_d", "c_d_all", "align", "th_all", "cum_all",
                               "dproj_all", "dalign", "xdg_a", "xdg_d", "carry_ha", "dha_dec", "dc_a", "dc_d", "dhd_rec",
-                              "dctx_att", "dctx_dec", "dwprev", "dcum", "dq_sum", "barrier",
+                              "dctx_att", "dctx_dec", "dwprev", "dcum", "barrier",
                               "dga_all", "dgd_all", "dq_all", "dctx_all", "dpm", "dv_part", "dU_part", "prof")]
         + [("flags", c_i)]
     )

@@ -64,7 +64,7 @@ struct SmemB {
   float* dv_acc;       // [128]
   float* dot_s;        // [4]                softmax dot partial: own, peer (double buffered)
   float* scr;          // [64]
-  float* wq_s;         // [WQ_UNITS][129]   Wq^T rows of this CTA's hidden units (P3)
+  float* dqf_s;        // [128]  full d query of the current sequence (cell backward)
   uint64_t* acc_full;
   uint64_t* g_full;
   uint64_t* ut_full;
@@ -76,7 +76,7 @@ __host__ __device__ constexpr size_t bwd2_fixed_bytes() {
   constexpr int NC4 = (N < 64 ? N : 64) / 4;
   constexpr size_t recv_b = (size_t)2 * 4 * TILE_M * NC4 * 4;
   return (recv_b < 32768 ? 32768 : recv_b) + 4 * 8192 +
-         (size_t)(1024 + 2 * B2_TIN_MAX + 4 * (B2_JH + 62) + 4 * 32 + 128 + 8 * 64 + 256 + 128 + 4 + 64 + WQ_UNITS * 129) * 4 + 64 * 8 + 64;
+         (size_t)(1024 + 2 * B2_TIN_MAX + 4 * (B2_JH + 62) + 4 * 32 + 128 + 8 * 64 + 256 + 128 + 4 + 64 + 128) * 4 + 64 * 8 + 64;
 }
 
 template <int N>
@@ -107,7 +107,7 @@ GTN_DEVICE SmemB carveB(uint8_t* base, int S) {
   m.dv_acc = f; f += 128;
   m.dot_s = f; f += 4;
   m.scr = f; f += 64;
-  m.wq_s = f; f += WQ_UNITS * 129;
+  m.dqf_s = f; f += 128;
   uint64_t* b = reinterpret_cast<uint64_t*>(f);
   m.ring.full = b; b += 16;
   m.ring.empty = b; b += 16;
@@ -237,6 +237,74 @@ GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, 
           else if (row < R_att) p.carry_ha[(size_t)b * p.Ha + row - p.E] = val;
         }
       }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Cell backward of ONE sequence, run by the CTA pair that owns the sequence right after its attention backward
+// (this used to be a third, unit-sliced phase behind a grid barrier; per sequence it needs no other CTA's results):
+//   * attention LSTM cell of frame t:     dh = Wq^T dq + dha_dec + carry_ha                   (model.py:391-394, 62)
+//   * decoder LSTM cell of frame t - 1:   dh = dhd_rec (P1 of this frame) + dproj(t-1)         (model.py:404-409)
+// CTA `half` of the pair takes one half of the hidden units; a thread owns two ADJACENT units, so every save / gradient
+// access of a warp is one contiguous 128..512-byte run.  Wq ([A][Ha], bf16 in bf16 mode) streams from L2: 128 coalesced
+// 4-byte loads per thread against the full dq of the sequence held in shared memory.
+// ------------------------------------------------------------------------------------------------
+GTN_DEVICE void pair_cells(const DecBwd2& p, const float* dqf, int t, int it, int b, int half) {
+  const int nxt = (it & 1) ^ 1;
+  bf16* xnext_d = BFP(p.xdg_d) + (size_t)nxt * p.B * p.mult * 4 * p.Hd;
+  const int Hh_a = ((p.Ha / 2 + 1) / 2) * 2, ua_end = min(p.Ha, (half + 1) * Hh_a);
+  const int Hh_d = ((p.Hd / 2 + 1) / 2) * 2, ud_end = min(p.Hd, (half + 1) * Hh_d);
+  const int na = (ua_end - half * Hh_a + 511) / 512, nd = t > 0 ? (ud_end - half * Hh_d + 511) / 512 : 0;
+  for (int rd = 0; rd < max(na, nd); ++rd) {
+    const int ua = half * Hh_a + rd * 512 + 2 * threadIdx.x;
+    const int ud = half * Hh_d + rd * 512 + 2 * threadIdx.x;
+    const bool oka = rd < na && ua < ua_end, okd = rd < nd && ud < ud_end;
+    CellIn ca[2], cd[2];
+    float2 adda = make_float2(0.f, 0.f), addd = make_float2(0.f, 0.f);
+    if (okd) {
+      cd[0] = cell_load(p, t - 1, b, ud, p.Hd, p.gates_d, p.c_d_all, p.dc_d);
+      cd[1] = cell_load(p, t - 1, b, ud + 1, p.Hd, p.gates_d, p.c_d_all, p.dc_d);
+      const float2 r = __ldcg(reinterpret_cast<const float2*>(p.dhd_rec + (size_t)b * p.Hd + ud));
+      const float* q = p.dproj_all + ((size_t)(t - 1) * p.B + b) * (p.Hd + p.D) + ud;     // row stride Hd + D may be odd
+      addd = make_float2(r.x + __ldg(q), r.y + __ldg(q + 1));
+    }
+    float s0 = 0.f, s1 = 0.f;
+    if (oka) {
+      ca[0] = cell_load(p, t, b, ua, p.Ha, p.gates_a, p.c_a_all, p.dc_a);
+      ca[1] = cell_load(p, t, b, ua + 1, p.Ha, p.gates_a, p.c_a_all, p.dc_a);
+      const size_t ci = (size_t)b * p.Ha + ua;
+      const float2 x = __ldcg(reinterpret_cast<const float2*>(p.dha_dec + ci)), y = __ldcg(reinterpret_cast<const float2*>(p.carry_ha + ci));
+      adda = make_float2(x.x + y.x, x.y + y.y);
+      if (p.prec == 1) {
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(p.wq_au) + (ua >> 1);
+        const int ld = p.Ha >> 1;
+        float t0 = 0.f, t1 = 0.f;
+#pragma unroll 16
+        for (int a = 0; a < p.A; a += 2) {
+          const uint32_t w0 = __ldg(w + (size_t)a * ld), w1 = __ldg(w + (size_t)(a + 1) * ld);
+          const float d0 = dqf[a], d1 = dqf[a + 1];
+          s0 += __uint_as_float(w0 << 16) * d0; s1 += __uint_as_float(w0 & 0xFFFF0000u) * d0;
+          t0 += __uint_as_float(w1 << 16) * d1; t1 += __uint_as_float(w1 & 0xFFFF0000u) * d1;
+        }
+        s0 += t0; s1 += t1;
+      } else {
+        const float2* w = reinterpret_cast<const float2*>(p.wq_au) + (ua >> 1);
+        const int ld = p.Ha >> 1;
+#pragma unroll 8
+        for (int a = 0; a < p.A; ++a) {
+          const float2 wv = __ldg(w + (size_t)a * ld);
+          s0 += wv.x * dqf[a]; s1 += wv.y * dqf[a];
+        }
+      }
+    }
+    if (okd) {
+      cell_apply(p, cd[0], t - 1, b, ud, p.Hd, addd.x, p.dc_d, p.dgd_all, xnext_d, 4u, p.thr_dec, p.p_dec);
+      cell_apply(p, cd[1], t - 1, b, ud + 1, p.Hd, addd.y, p.dc_d, p.dgd_all, xnext_d, 4u, p.thr_dec, p.p_dec);
+    }
+    if (oka) {
+      cell_apply(p, ca[0], t, b, ua, p.Ha, s0 + adda.x, p.dc_a, p.dga_all, BFP(p.xdg_a), 3u, p.thr_att, p.p_att);
+      cell_apply(p, ca[1], t, b, ua + 1, p.Ha, s1 + adda.y, p.dc_a, p.dga_all, BFP(p.xdg_a), 3u, p.thr_att, p.p_att);
     }
   }
 }
@@ -538,119 +606,16 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
         if (ch == 0) p.dwprev[(size_t)b * p.ldT + j] = s;
         else p.dcum[(size_t)b * p.ldT + j] += s;
       }
-      if (half == 0) {
-        for (int a = threadIdx.x; a < A; a += blockDim.x) {
-          const float s = sm.dqp_s[a] + ((Tin > JH) ? sm.dqp_s[128 + a] : 0.f);
-          p.dq_all[tb * A + a] = s;
-          p.dq_sum[(size_t)b * A + a] = s;
-        }
+      for (int a = threadIdx.x; a < 128; a += blockDim.x) {
+        const float s = a < A ? sm.dqp_s[a] + ((Tin > JH) ? sm.dqp_s[128 + a] : 0.f) : 0.f;
+        sm.dqf_s[a] = s;                                     // full d query of the sequence, both CTAs of the pair
+        if (half == 0 && a < A) p.dq_all[tb * A + a] = s;
       }
     }
     __syncthreads();
-  }
-}
-
-// ------------------------------------------------------------------------------------------------
-// P3: query backward + attention LSTM cell backward of frame t, all CTAs, split by hidden unit
-// ------------------------------------------------------------------------------------------------
-// Wq^T rows of this CTA's hidden units, staged once per launch: wq_s[unit][A + 1]
-GTN_DEVICE void stage_wq(const DecBwd2& p, SmemB& sm) {
-  const int UPC = (p.Ha + gridDim.x - 1) / gridDim.x;
-  const int u_begin = blockIdx.x * UPC, nu = max(0, min(p.Ha, u_begin + UPC) - u_begin);
-  const int Ap = p.A + 1;
-  for (int i = threadIdx.x; i < nu * p.A; i += blockDim.x) {
-    const int ul = i / p.A, a = i - ul * p.A;
-    sm.wq_s[ul * Ap + a] = __ldg(&p.wq_t[(size_t)(u_begin + ul) * p.A + a]);
-  }
-}
-
-GTN_DEVICE void att_cell_phase2(const DecBwd2& p, SmemB& sm, int t, int it) {
-  // CTA i owns hidden units [i*UPC, (i+1)*UPC) of BOTH LSTMs for every sequence.  Threads run unit-fastest so that the
-  // gate saves / gate-gradient stores of a sequence are contiguous; dq of a 64-sequence chunk is staged transposed in
-  // shared memory ([a][65]); this CTA's rows of Wq^T live in wq_s for the whole launch.
-  //   * attention LSTM cell backward of frame t:   dh = Wq^T dq + dha_dec + carry_ha            (model.py:391-394)
-  //   * decoder LSTM cell backward of frame t - 1: dh = dhd_rec (P1 of this frame) + dproj(t-1)  (model.py:404-409)
-  // Every global operand of the first round (dq, both cells' saves) is requested before anything is consumed, so the
-  // phase pays one memory round trip instead of three.
-  const int UPC = (p.Ha + gridDim.x - 1) / gridDim.x;
-  const int u_begin = blockIdx.x * UPC, nu = max(0, min(p.Ha, u_begin + UPC) - u_begin);
-  const int UPCd = (p.Hd + gridDim.x - 1) / gridDim.x;
-  const int ud_begin = blockIdx.x * UPCd, nud = max(0, min(p.Hd, ud_begin + UPCd) - ud_begin);
-  float* dq_s = reinterpret_cast<float*>(sm.ring.base);      // the TMA ring is idle in this phase
-  const float* wq_s = sm.wq_s;
-  const int Ap = p.A + 1;
-  const int nxt = (it & 1) ^ 1;
-  bf16* xnext_d = BFP(p.xdg_d) + (size_t)nxt * p.B * p.mult * 4 * p.Hd;
-  for (int bc0 = 0; bc0 < p.B; bc0 += 64) {
-    const int nb = min(64, p.B - bc0);
-    const int ntot = nb * p.A;                               // <= 64 * 128 = 32 * 256
+    PROFB(19);
+    if (active) pair_cells(p, sm.dqf_s, t, it, b, half);
     __syncthreads();
-    float v[32];
-#pragma unroll
-    for (int k = 0; k < 32; ++k) {
-      const int i = k * 256 + threadIdx.x;
-      v[k] = (i < ntot && !(p.flags & 2)) ? __ldcg(&p.dq_sum[(size_t)bc0 * p.A + i]) : 0.f;
-    }
-    const int ncell = (p.flags & 8) ? 0 : nu * nb, ncelld = (t > 0 && !(p.flags & 4)) ? nud * nb : 0;
-    const int nround = max((ncell + 511) / 512, (ncelld + 511) / 512);
-    for (int rd = 0; rd < nround; ++rd) {
-      const int c0 = rd * 512;
-      CellIn cin[2], cid_[2];
-      float add[2], ddh[2];
-      bool ok[2], okd[2];
-#pragma unroll
-      for (int k = 0; k < 2; ++k) {
-        const int c = c0 + k * 256 + threadIdx.x;
-        ok[k] = c < ncell;
-        okd[k] = c < ncelld;
-        if (ok[k]) {
-          const int ul = c % nu, b = bc0 + c / nu, u = u_begin + ul;
-          cin[k] = cell_load(p, t, b, u, p.Ha, p.gates_a, p.c_a_all, p.dc_a);
-          const size_t ci = (size_t)b * p.Ha + u;
-          add[k] = __ldcg(&p.dha_dec[ci]) + __ldcg(&p.carry_ha[ci]);
-        }
-        if (okd[k]) {
-          const int ul = c % nud, b = bc0 + c / nud, u = ud_begin + ul;
-          cid_[k] = cell_load(p, t - 1, b, u, p.Hd, p.gates_d, p.c_d_all, p.dc_d);
-          ddh[k] = __ldcg(&p.dhd_rec[(size_t)b * p.Hd + u]) + __ldg(&p.dproj_all[((size_t)(t - 1) * p.B + b) * (p.Hd + p.D) + u]);
-        }
-      }
-      PROFB(23);
-      if (rd == 0) {
-#pragma unroll
-        for (int k = 0; k < 32; ++k) {
-          const int i = k * 256 + threadIdx.x;
-          if (i < ntot) { const int bl = i / p.A, a = i - bl * p.A; dq_s[a * 65 + bl] = v[k]; }
-        }
-      }
-      // decoder cells first: they need nothing from shared memory
-#pragma unroll
-      for (int k = 0; k < 2; ++k) {
-        if (!okd[k]) continue;
-        const int c = c0 + k * 256 + threadIdx.x;
-        const int ul = c % nud, b = bc0 + c / nud;
-        cell_apply(p, cid_[k], t - 1, b, ud_begin + ul, p.Hd, ddh[k], p.dc_d, p.dgd_all, xnext_d, 4u, p.thr_dec, p.p_dec);
-      }
-      if (rd == 0) { __syncthreads(); PROFB(22); }
-#pragma unroll
-      for (int k = 0; k < 2; ++k) {
-        if (!ok[k]) continue;
-        const int c = c0 + k * 256 + threadIdx.x;
-        const int ul = c % nu, bl = c / nu;
-        const float* wq = wq_s + ul * Ap;
-        const float* dq = dq_s + bl;
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-#pragma unroll 4
-        for (int a = 0; a < ((p.flags & 16) ? 4 : p.A); a += 4) {
-          s0 += wq[a] * dq[a * 65]; s1 += wq[a + 1] * dq[(a + 1) * 65];
-          s2 += wq[a + 2] * dq[(a + 2) * 65]; s3 += wq[a + 3] * dq[(a + 3) * 65];
-        }
-        if (k == 0) PROFB(24);
-        cell_apply(p, cin[k], t, bc0 + bl, u_begin + ul, p.Ha, (s0 + s1) + (s2 + s3) + add[k], p.dc_a, p.dga_all,
-                   BFP(p.xdg_a), 3u, p.thr_att, p.p_att);
-        if (k == 0) PROFB(25);
-      }
-    }
   }
 }
 
@@ -679,21 +644,22 @@ GTN_DEVICE void prefetch_frame(const DecBwd2& p, int t, int rank, int cid, int n
     if ((int)threadIdx.x >= 32 && (int)threadIdx.x < 32 + dp_lines)
       prefetch_l2(reinterpret_cast<const char*>(p.dproj_all + tb * (p.Hd + p.D) + p.Hd) + (threadIdx.x - 32) * 128);
   }
-  // ---- P3 operands of this CTA's hidden units: one (or two) 128-byte lines per sequence and array
-  const int UPC = (p.Ha + gridDim.x - 1) / gridDim.x, ua = blockIdx.x * UPC;
-  const int UPCd = (p.Hd + gridDim.x - 1) / gridDim.x, ud = blockIdx.x * UPCd;
-  for (int b = threadIdx.x >> 2; b < p.B; b += blockDim.x >> 2) {
-    const int which = threadIdx.x & 3;
-    if (ua < p.Ha) {
-      const size_t cell = ((size_t)t * p.B + b) * p.Ha + ua;
-      if (which == 0) prefetch_l2(reinterpret_cast<const float4*>(p.gates_a) + cell);
-      if (which == 1) { prefetch_l2(p.c_a_all + cell); if (t > 0) prefetch_l2(p.c_a_all + cell - (size_t)p.B * p.Ha); }
-    }
-    if (t > 0 && ud < p.Hd) {
-      const size_t cell = ((size_t)(t - 1) * p.B + b) * p.Hd + ud;
-      if (which == 2) prefetch_l2(reinterpret_cast<const float4*>(p.gates_d) + cell);
-      if (which == 2 && t > 1) prefetch_l2(p.c_d_all + cell - (size_t)p.B * p.Hd);
-      if (which == 3) { prefetch_l2(p.c_d_all + cell); prefetch_l2(p.dproj_all + ((size_t)(t - 1) * p.B + b) * (p.Hd + p.D) + ud); }
+  // ---- cell-backward operands of this CTA's half of the hidden units of its sequence(s): contiguous runs
+  const int Hh_a = ((p.Ha / 2 + 1) / 2) * 2, Hh_d = ((p.Hd / 2 + 1) / 2) * 2;
+  for (int b = pair; b < p.B; b += npairs) {
+    const size_t ca = ((size_t)t * p.B + b) * p.Ha + half * Hh_a;
+    const int tid = threadIdx.x;
+    if (tid < 128) {
+      if (tid * 8 < Hh_a) prefetch_l2(reinterpret_cast<const float4*>(p.gates_a) + ca + tid * 8);            // 8 cells x 16 B per line
+      if (tid < 32 && tid * 32 < Hh_a && t > 0) prefetch_l2(p.c_a_all + ca - (size_t)p.B * p.Ha + tid * 32);
+      if (tid >= 32 && tid < 64 && (tid - 32) * 32 < Hh_a) prefetch_l2(p.c_a_all + ca + (tid - 32) * 32);
+    } else if (t > 0) {
+      const int i = tid - 128;
+      const size_t cd = ((size_t)(t - 1) * p.B + b) * p.Hd + half * Hh_d;
+      if (i * 8 < Hh_d) prefetch_l2(reinterpret_cast<const float4*>(p.gates_d) + cd + i * 8);
+      if (i < 32 && i * 32 < Hh_d && t > 1) prefetch_l2(p.c_d_all + cd - (size_t)p.B * p.Hd + i * 32);
+      if (i >= 32 && i < 64 && (i - 32) * 32 < Hh_d) prefetch_l2(p.c_d_all + cd + (i - 32) * 32);
+      if (i >= 64 && i < 96 && (i - 64) * 32 < Hh_d) prefetch_l2(p.dproj_all + ((size_t)(t - 1) * p.B + b) * (p.Hd + p.D) + half * Hh_d + (i - 64) * 32);
     }
   }
 }
@@ -732,7 +698,6 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
   unsigned int epoch = 0;
   uint32_t acc_par = 0, g_par = 0, round = 0, xround = 0;
   const unsigned int nblocks = gridDim.x;
-  stage_wq(p, sm);
   dec_cell_prologue(p, p.T - 1);
   grid_sync2(p.barrier, epoch, nblocks);
   int it = 0;
@@ -745,10 +710,6 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
     PROFB(5);
     if (p.mem_bf16) attn_bwd_phase2<bf16>(p, sm, t, it, rank, cid, ncl, tmem_g, tmem_du, g_par, xround);
     else attn_bwd_phase2<float>(p, sm, t, it, rank, cid, ncl, tmem_g, tmem_du, g_par, xround);
-    PROFB(18);
-    grid_sync2(p.barrier, epoch, nblocks);
-    PROFB(19);
-    att_cell_phase2(p, sm, t, it);
     PROFB(20);
     grid_sync2(p.barrier, epoch, nblocks);
     PROFB(21);
@@ -870,7 +831,7 @@ extern "C" int gtn_decoder_backward2(const gtn_decoder_bwd2_params* hp, void* st
   p.thr_dec = p.use_dropout ? thr(p.p_dec) : 0u;
   const int grid = gtn_decoder_bwd2_grid(p.B, p.Ha, p.Hd, p.E);
   GTN_REQUIRE(grid > 0 && p.grid == grid, "params.grid (%d) must equal gtn_decoder_bwd2_grid() (%d)", p.grid, grid);
-  GTN_REQUIRE((p.Ha + grid - 1) / grid <= WQ_UNITS, "decoder backward: too few CTAs (%d) for attention_rnn_dim %d", grid, p.Ha);
+  GTN_REQUIRE(p.wq_au != nullptr, "wq_au pack missing");
   GTN_REQUIRE(p.dhd_rec != nullptr, "dhd_rec workspace missing");
   const int N = pick_n(p.B);
   const int m = p.mult;

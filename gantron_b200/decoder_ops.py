@@ -162,6 +162,7 @@ class PackV2:
                 wT_att2=packing.pack_weight([(wta, 4 * Ha)], prec), wT_dec2=packing.pack_weight([(wtd, 4 * Hd)], prec),
                 ut_loc=torch.cat((hi, (UT - hi.float()).to(BF16)), 1).contiguous(),       # [64][hi 128 | lo 128]
                 wa_pre_T=wa[:, :Pn].t().contiguous(),                                     # [P][4Ha]
+                wq_au=(pk.wq.to(BF16) if prec == 1 else pk.wq.float()).contiguous(),      # [A][Ha] for the cell backward
                 wa_const_T=self.wa_const.t().contiguous(), wd_const_T=self.wd_const.t().contiguous())
         return self._bwd
 
@@ -636,14 +637,14 @@ def _bptt_v2(dec, pk, d, ctx, S, sv, dproj, d_align, prec):
     wk = dict(
         xdg_a=z(B, mult * 4 * Ha, dt=BF16), xdg_d=z(2, B, mult * 4 * Hd, dt=BF16),
         carry_ha=z(B, Ha), dha_dec=z(B, Ha), dc_a=z(B, Ha), dc_d=z(B, Hd), dhd_rec=z(B, Hd), dctx_att=z(B, Ep), dctx_dec=z(B, Ep),
-        dwprev=z(B, q.ldT), dcum=z(B, q.ldT), dq_sum=z(B, A), barrier=z(4, dt=torch.int32),
+        dwprev=z(B, q.ldT), dcum=z(B, q.ldT), barrier=z(4, dt=torch.int32),
         dga_all=torch.empty(T, B, 4 * Ha, device=dev), dgd_all=torch.empty(T, B, 4 * Hd, device=dev),
         dq_all=torch.empty(T, B, A, device=dev), dctx_all=torch.empty(B, T, E, device=dev), dpm=z(B, Tin, A),
         dv_part=z(grid, A), dU_part=z(grid, 128, 64))
     for k, v in wk.items():
         setattr(q, k, v.data_ptr())
     q.wT_att2, q.wT_dec2, q.ut_loc = bp["wT_att2"].data_ptr(), bp["wT_dec2"].data_ptr(), bp["ut_loc"].data_ptr()
-    q.wq_t, q.v = pk.wq_t.data_ptr(), pk.v.data_ptr()
+    q.wq_au, q.v = bp["wq_au"].data_ptr(), pk.v.data_ptr()
     q.mem_enc, q.lengths = S["mem_enc"].data_ptr(), S["lengths"].data_ptr()
     q.gates_a, q.c_a_all, q.gates_d, q.c_d_all = (sv["gates_a"].data_ptr(), sv["c_a_all"].data_ptr(),
                                                   sv["gates_d"].data_ptr(), sv["c_d_all"].data_ptr())

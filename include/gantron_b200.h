@@ -281,7 +281,7 @@ typedef struct gtn_decoder_bwd2_params {
   const void *wT_att2;       /* bf16 [E + Ha][mult*4Ha]: rows = attention_rnn inputs [ctx_enc | h_att], K = gate rows g*Ha+u */
   const void *wT_dec2;       /* bf16 [Ha + E + Hd][mult*4Hd]: rows = decoder_rnn inputs [h_att | ctx_enc | h_dec] */
   const void *ut_loc;        /* bf16 [64][256]: U^T[kk][a], hi plane (a 0..127) | lo plane; U = location dense x conv */
-  const float *wq_t;         /* [Ha][A] */
+  const void *wq_au;         /* [A][Ha] query_layer weight (model.py:62): bf16 when prec == 1, fp32 when prec == 3 */
   const float *v;            /* [A] */
   /* forward inputs / saved by gtn_decoder_forward2 */
   const void *mem_enc; const int *lengths;
@@ -300,7 +300,6 @@ typedef struct gtn_decoder_bwd2_params {
   float *dhd_rec;                       /* [B][Hd] d h_dec(t-1) through the recurrent weights (P1 -> P3 of a frame) */
   float *dctx_att, *dctx_dec;           /* [B][Ep] */
   float *dwprev, *dcum;                 /* [B][ldT] */
-  float *dq_sum;                        /* [B][A] */
   unsigned int *barrier;
   /* outputs */
   float *dga_all, *dgd_all;  /* [T][B][4Ha], [T][B][4Hd] pre-activation gate gradients (gate-major) */

@@ -23,8 +23,8 @@ FW = {14: "att: cells done", 15: "att: sync", 16: "att: qpart computed", 7: "att
 FO = [0, 1, 2, 3, 14, 15, 16, 4, 5, 7, 12, 20, 21, 22, 24, 25, 26, 27, 6, 8, 9, 10, 11, 13]
 BW = {0: "step start", 1: "P1: TMA issued", 2: "P1: acc done", 3: "P1: exchange done", 4: "P1: epilogue done", 5: "gsync done",
       10: "P2: loads + window", 11: "P2: dw + dot", 12: "P2: cluster sync 1", 13: "P2: dth tiles + dq/dv", 15: "P2: MMA + G to smem",
-      16: "P2: d wcat", 17: "P2: cluster sync 2", 18: "P2 done", 19: "gsync done", 22: "P3: dq staged", 23: "P3: cell loads issued", 24: "P3: dot 0 done", 25: "P3: apply 0 done", 20: "P3 done", 21: "gsync done"}
-BO = [0, 1, 2, 3, 4, 5, 10, 11, 12, 13, 15, 16, 17, 18, 19, 22, 23, 24, 25, 20, 21]
+      16: "P2: d wcat", 17: "P2: cluster sync 2", 18: "P2 done", 19: "P2: dq in smem", 20: "cells done", 21: "gsync done"}
+BO = [0, 1, 2, 3, 4, 5, 10, 11, 12, 13, 15, 16, 17, 19, 20, 21]
 for rep in range(2):
     pf = torch.zeros(16 * 32, dtype=torch.int64, device="cuda")
     pb = torch.zeros(2 * 16 * 32, dtype=torch.int64, device="cuda")
