@@ -74,7 +74,9 @@ struct SmemB {
 template <int N>
 __host__ __device__ constexpr size_t bwd2_fixed_bytes() {
   constexpr int NC4 = (N < 64 ? N : 64) / 4;
-  constexpr size_t recv_b = (size_t)2 * 4 * TILE_M * NC4 * 4;
+  // N <= 64: one exchange per frame and a grid barrier before the next one, so a single receive buffer is safe and the
+  // 32 KB saved buys two more TMA stages; N > 64: back-to-back chunk exchanges need the double buffer
+  constexpr size_t recv_b = (size_t)(N > 64 ? 2 : 1) * 4 * TILE_M * NC4 * 4;
   return (recv_b < 32768 ? 32768 : recv_b) + 4 * 8192 +
          (size_t)(1024 + 2 * B2_TIN_MAX + 4 * (B2_JH + 62) + 4 * 32 + 128 + 8 * 64 + 256 + 128 + 4 + 64 + 128) * 4 + 64 * 8 + 64;
 }
@@ -82,7 +84,7 @@ __host__ __device__ constexpr size_t bwd2_fixed_bytes() {
 template <int N>
 GTN_DEVICE SmemB carveB(uint8_t* base, int S) {
   constexpr int NC4 = (N < 64 ? N : 64) / 4;
-  constexpr size_t recv_b = (size_t)2 * 4 * TILE_M * NC4 * 4;
+  constexpr size_t recv_b = (size_t)(N > 64 ? 2 : 1) * 4 * TILE_M * NC4 * 4;
   SmemB m;
   m.ring.base = base;
   m.ring.S = S;
@@ -219,7 +221,7 @@ GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, 
     PROFB_T(128, 2);
     if (has_work) acc_par ^= 1u;
     for (int c0 = 0; c0 < N; c0 += CH) {
-      float* recv = sm.recv + (size_t)(round & 1u) * 4 * TILE_M * NC4;
+      float* recv = sm.recv + (size_t)(N > 64 ? (round & 1u) : 0u) * 4 * TILE_M * NC4;
       ++round;
       const int bbase = c0 + rank * NC4;
       exchange_chunk<CH, true>(has_work, tmem_base, c0, recv, rank);
