@@ -158,7 +158,6 @@ struct Ring {
   int S;
   uint32_t stage_bytes;
   uint32_t prod_it, mma_it;
-  int pre;                // k-blocks of the NEXT job already issued by gemm_preissue (producer thread only)
 };
 
 struct XSeg {
@@ -173,57 +172,119 @@ struct GemmJob {
   int nkb;                // total k-blocks over K (all 4 ranks)
   int nseg;
   XSeg seg[3];
+  int res_n = 0;          // leading k-blocks of THIS CTA's K range whose weights are resident in TMEM (no W load)
+  int res_slot0 = 0;      // first resident slot
 };
 
-// producer step: TMA loads of k-block kb (weights + the matching activation segment) into the next ring slot
+// ---- TMEM-resident weight k-blocks -------------------------------------------------------------------------------
+// A cluster keeps the same 128-row weight tile and a CTA the same K quarter of it for the whole launch, and the SM's L2
+// port (~30 B/clk) is what bounds the per-frame GEMM phases.  Tensor memory has 512 columns; beyond the accumulator(s)
+// the free columns hold weight k-blocks (128 rows x 64 bf16 = 128 lanes x 32 columns) loaded ONCE, used as the A operand
+// of tcgen05.mma straight from TMEM.  Slot i lives at columns N + 32 i (below column 256) or 384 + 32 (i - n1): columns
+// [256, 384) belong to the attention GEMMs of both kernels.
 template <int N>
-GTN_DEVICE void produce_kblock(const GemmJob& job, Ring& rg, int kb) {
-  constexpr uint32_t X_BYTES = N * KB * 2;
-  const int s = rg.prod_it % rg.S;
-  const uint32_t par = (rg.prod_it / rg.S) & 1u;
-  wait_bar(&rg.empty[s], par ^ 1u);
-  mbar_expect_tx(&rg.full[s], W_TILE_BYTES + X_BYTES);
-  uint8_t* st = rg.base + (size_t)s * rg.stage_bytes;
-  tma_load_3d(st, job.wmap, &rg.full[s], kb * KB, job.row0, 0);
-  int kk = kb, si = 0;
-  while (si < job.nseg - 1 && kk >= job.seg[si].nkb) { kk -= job.seg[si].nkb; ++si; }
-  tma_load_3d(st + W_TILE_BYTES, job.seg[si].map, &rg.full[s], kk * KB, 0, job.seg[si].z);
-  ++rg.prod_it;
+GTN_DEVICE constexpr int res_slots() { return (N < 256 ? (256 - N) / 32 : 0) + 4; }
+template <int N>
+GTN_DEVICE uint32_t res_col(int slot) {
+  constexpr int n1 = N < 256 ? (256 - N) / 32 : 0;
+  return slot < n1 ? (uint32_t)(N + 32 * slot) : (uint32_t)(384 + 32 * (slot - n1));
+}
+// warps 4..7 copy `count` k-blocks (first global k-block kb_first) of rows [row0, row0 + 128) of the K-major bf16 matrix W
+// (row stride ldw elements) into slots slot0.. ; rows >= nrows are zero.  Ends with tcgen05.wait::st.
+template <int N>
+GTN_DEVICE void load_resident(const void* W, long long ldw, int nrows, int row0, int kb_first, int count, int slot0,
+                              uint32_t tmem_base) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp < 4) return;
+  const int q = warp & 3, row = row0 + q * 32 + lane;
+  for (int i = 0; i < count; ++i) {
+    uint32_t r[32];
+    if (row < nrows) {
+      const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(W) + (size_t)row * ldw + (size_t)(kb_first + i) * KB);
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const uint4 v = __ldg(src + c);
+        r[4 * c] = v.x; r[4 * c + 1] = v.y; r[4 * c + 2] = v.z; r[4 * c + 3] = v.w;
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < 32; ++c) r[c] = 0u;
+    }
+    tmem_st_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + res_col<N>(slot0 + i), r);
+  }
+  tmem_st_wait();
 }
 
-// Start the loads of a job whose operands are already final while the CTA is still busy with the previous job's
-// exchange / epilogue: fills up to S ring slots (all free once the previous accumulator is complete).  The matching
-// gemm_issue call continues after the pre-issued k-blocks.  Producer thread only.
+// TMA load of the activation k-block kb (global index over the concatenated K segments) into `dst`
 template <int N>
-GTN_DEVICE void gemm_preissue(const GemmJob& job, Ring& rg, int rank) {
-  const int kb0 = rank * job.nkb / CL, kb1 = (rank + 1) * job.nkb / CL;
-  int n = kb1 - kb0;
-  if (n > rg.S) n = rg.S;
-  for (int i = 0; i < n; ++i) produce_kblock<N>(job, rg, kb0 + i);
-  rg.pre = n;
+GTN_DEVICE void load_x_kblock(const GemmJob& job, uint8_t* dst, uint64_t* bar, int kb) {
+  int kk = kb, si = 0;
+  while (si < job.nseg - 1 && kk >= job.seg[si].nkb) { kk -= job.seg[si].nkb; ++si; }
+  tma_load_3d(dst, job.seg[si].map, bar, kk * KB, 0, job.seg[si].z);
 }
 
 // Issue one cluster-split GEMM: this CTA's quarter of K.  Producer = thread 0, MMA = thread 32.
+// A ring stage is [W tile 16 KB | X tile N*128 B].  The first job.res_n k-blocks of the CTA's range have their weights
+// resident in TMEM and need only the X tile, so G = stage_bytes / X_BYTES of them share ONE stage (fewer stages per
+// GEMM = fewer load -> MMA -> free-slot round trips; the phases are bound by those chains, not by bytes).
 // Returns whether this CTA had any k-block (else its partial tile is all zeros).
 template <int N>
-GTN_DEVICE bool gemm_issue(const GemmJob& job, Ring& rg, uint32_t tmem_acc, uint64_t* acc_full, int rank) {
+GTN_DEVICE bool gemm_issue(const GemmJob& job, Ring& rg, uint32_t tmem_acc, uint64_t* acc_full, int rank,
+                           uint32_t tmem_res = 0u) {
+  constexpr uint32_t X_BYTES = N * KB * 2;
+  constexpr int G = (W_TILE_BYTES + X_BYTES) / X_BYTES;       // resident k-blocks per stage
   const int kb0 = rank * job.nkb / CL, kb1 = (rank + 1) * job.nkb / CL;
+  const int res_n = min(job.res_n, kb1 - kb0);
+  const int res_stages = (res_n + G - 1) / G;
+  const int nstages = res_stages + (kb1 - kb0 - res_n);
   if (threadIdx.x == 0) {
-    for (int kb = kb0 + rg.pre; kb < kb1; ++kb) produce_kblock<N>(job, rg, kb);
-    rg.pre = 0;
+    for (int sg = 0; sg < nstages; ++sg) {
+      const int s = rg.prod_it % rg.S;
+      const uint32_t par = (rg.prod_it / rg.S) & 1u;
+      wait_bar(&rg.empty[s], par ^ 1u);
+      uint8_t* st = rg.base + (size_t)s * rg.stage_bytes;
+      if (sg < res_stages) {
+        const int n = min(G, res_n - sg * G);
+        mbar_expect_tx(&rg.full[s], (uint32_t)n * X_BYTES);
+        for (int j = 0; j < n; ++j) load_x_kblock<N>(job, st + (size_t)j * X_BYTES, &rg.full[s], kb0 + sg * G + j);
+      } else {
+        const int kb = kb0 + res_n + (sg - res_stages);
+        mbar_expect_tx(&rg.full[s], W_TILE_BYTES + X_BYTES);
+        tma_load_3d(st, job.wmap, &rg.full[s], kb * KB, job.row0, 0);
+        load_x_kblock<N>(job, st + W_TILE_BYTES, &rg.full[s], kb);
+      }
+      ++rg.prod_it;
+    }
   } else if (threadIdx.x == 32) {
     if (kb1 > kb0) {
       const uint32_t idesc = umma_idesc_bf16(TILE_M, N);
-      for (int kb = kb0; kb < kb1; ++kb) {
+      uint32_t started = 0u;
+      for (int sg = 0; sg < nstages; ++sg) {
         const int s = rg.mma_it % rg.S;
         const uint32_t par = (rg.mma_it / rg.S) & 1u;
         wait_bar(&rg.full[s], par);
         tc_fence_after();
         const uint32_t a = smem_u32(rg.base + (size_t)s * rg.stage_bytes);
-        const uint64_t da = umma_desc_sw128(a), db = umma_desc_sw128(a + W_TILE_BYTES);
+        if (sg < res_stages) {
+          // weights from TMEM: 16 K elements = 8 columns per UMMA
+          const int n = min(G, res_n - sg * G);
+          for (int j = 0; j < n; ++j) {
+            const uint32_t ta = tmem_res + res_col<N>(job.res_slot0 + sg * G + j);
+            const uint64_t db = umma_desc_sw128(a + (uint32_t)j * X_BYTES);
 #pragma unroll
-        for (int k = 0; k < KB / 16; ++k)
-          umma_bf16(tmem_acc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb > kb0) | (k > 0)));
+            for (int k = 0; k < KB / 16; ++k) {
+              umma_bf16_ts(tmem_acc, ta + (uint32_t)(8 * k), db + (uint64_t)(2 * k), idesc, started);
+              started = 1u;
+            }
+          }
+        } else {
+          const uint64_t da = umma_desc_sw128(a), db = umma_desc_sw128(a + W_TILE_BYTES);
+#pragma unroll
+          for (int k = 0; k < KB / 16; ++k) {
+            umma_bf16(tmem_acc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, started);
+            started = 1u;
+          }
+        }
         umma_commit(&rg.empty[s]);
         ++rg.mma_it;
       }

@@ -90,7 +90,6 @@ GTN_DEVICE SmemB carveB(uint8_t* base, int S) {
   m.ring.S = S;
   m.ring.stage_bytes = W_TILE_BYTES + N * KB * 2;
   m.ring.prod_it = m.ring.mma_it = 0;
-  m.ring.pre = 0;
   size_t ring_b = (size_t)S * m.ring.stage_bytes;
   if (ring_b < (size_t)P2_RING_BYTES) ring_b = P2_RING_BYTES;
   uint8_t* p = base + ring_b;
@@ -195,7 +194,7 @@ GTN_DEVICE void dec_cell_prologue(const DecBwd2& p, int t) {
 // ------------------------------------------------------------------------------------------------
 template <int N>
 GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, int t, int it, int rank, int cid, int ncl,
-                             uint32_t tmem_base, uint32_t& acc_par, uint32_t& round) {
+                             uint32_t tmem_base, uint32_t& acc_par, uint32_t& round, int res_n) {
   constexpr int CH = N < 64 ? N : 64;
   constexpr int NC4 = CH / 4;
   const int R_dec = p.Ha + p.E + p.Hd, R_att = p.E + p.Ha;
@@ -211,7 +210,9 @@ GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, 
     job.nseg = 1;
     job.seg[0] = dec ? XSeg{&maps.xdg_d, p.mult * 4 * p.Hd / KB, cur} : XSeg{&maps.xdg_a, p.mult * 4 * p.Ha / KB, 0};
     job.nkb = job.seg[0].nkb;
-    const bool has_work = gemm_issue<N>(job, sm.ring, tmem_base, sm.acc_full, rank);
+    job.res_n = tile == cid ? res_n : 0;
+    job.res_slot0 = 0;
+    const bool has_work = gemm_issue<N>(job, sm.ring, tmem_base, sm.acc_full, rank, tmem_base);
     PROFB(1);
     __syncwarp();
     if ((threadIdx.x >> 5) >= 4 && has_work) {
@@ -695,7 +696,24 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
     for (int i = 0; i < 4; ++i) tma_load_3d(sm.ut_s + i * 8192, &maps.ut, sm.ut_full, i * KB, 0, 0);
     wait_bar(sm.ut_full, 0);
   }
+  int res_n = 0;
+  {
+    // every cluster owns one 128-row tile of W_dec^T / W_att^T for the whole launch: park the leading weight k-blocks of
+    // this CTA's K quarter in the free TMEM columns
+    const int R_dec = p.Ha + p.E + p.Hd, R_att = p.E + p.Ha;
+    const int nD = (R_dec + TILE_M - 1) / TILE_M, nA = (R_att + TILE_M - 1) / TILE_M;
+    if (nD + nA <= ncl && cid < nD + nA) {
+      const bool dec = cid < nD;
+      const int H = dec ? p.Hd : p.Ha;
+      const int nkb = p.mult * 4 * H / KB, kb0 = rank * nkb / CL;
+      res_n = min((rank + 1) * nkb / CL - kb0, res_slots<N>());
+      load_resident<N>(dec ? p.wT_dec2 : p.wT_att2, (long long)nkb * KB, dec ? R_dec : R_att, (dec ? cid : cid - nD) * TILE_M, kb0,
+                       res_n, 0, tmem_base);
+    }
+  }
+  tc_fence_before();
   cluster_sync_all();
+  tc_fence_after();
 
   unsigned int epoch = 0;
   uint32_t acc_par = 0, g_par = 0, round = 0, xround = 0;
@@ -706,7 +724,7 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
   for (int t = p.T - 1; t >= 0; --t, ++it) {
     PROFB(0);
     if (p.flags & 1) prefetch_frame(p, t, rank, cid, ncl);
-    dgrad_phase2<N>(p, maps, sm, t, it, rank, cid, ncl, tmem_base, acc_par, round);
+    dgrad_phase2<N>(p, maps, sm, t, it, rank, cid, ncl, tmem_base, acc_par, round, res_n);
     PROFB(4);
     grid_sync2(p.barrier, epoch, nblocks);
     PROFB(5);

@@ -62,6 +62,7 @@ struct Smem2 {
   uint64_t* att_full;
   uint64_t* u_full;
   uint32_t* tmem_slot;
+  int res_a, res_d;    // weight k-blocks of this CTA's attention / decoder LSTM K quarter that are resident in TMEM
 };
 
 static constexpr int JH_MAX = 128;     // encoder positions per CTA of a pair (T_in <= 256)
@@ -85,7 +86,7 @@ GTN_DEVICE Smem2 carve2(uint8_t* base, int S) {
   m.ring.S = S;
   m.ring.stage_bytes = W_TILE_BYTES + N * KB * 2;
   m.ring.prod_it = m.ring.mma_it = 0;
-  m.ring.pre = 0;
+  m.res_a = m.res_d = 0;
   uint8_t* p = base + (size_t)S * m.ring.stage_bytes;
   m.u_s = p; p += 2 * W_TILE_BYTES;
   float* f = reinterpret_cast<float*>(p);
@@ -181,7 +182,10 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
       for (int u = 0; u < 32; ++u) wqr[u] = a < p.A ? p.wq_t[((size_t)tile * 32 + u) * p.A + a] : 0.f;
     }
     const int ps = kind == K_ATT ? 1 : (kind == K_DEC ? 9 : (kind == K_PROJ ? 14 : 20));
-    const bool has_work = gemm_issue<N>(job, sm.ring, tmem_base, sm.acc_full, rank);
+    if (tile == cid && kind == K_ATT) { job.res_n = sm.res_a; job.res_slot0 = 0; }
+    else if (tile == cid && kind == K_DEC) { job.res_n = sm.res_d; job.res_slot0 = sm.res_a; }
+    else job.res_n = 0;
+    const bool has_work = gemm_issue<N>(job, sm.ring, tmem_base, sm.acc_full, rank, tmem_base);
     PROF(ps);                                    // producer: all TMA loads issued
     __syncwarp();
     if ((threadIdx.x >> 5) >= 4 && has_work) {
@@ -618,7 +622,19 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
     tma_load_3d(sm.u_s + W_TILE_BYTES, &maps.uloc, sm.u_full, KB, 0, 0);
     wait_bar(sm.u_full, 0);
   }
+  if (p.Ha / 32 == ncl && p.Hd / 32 == ncl) {
+    // one attention-LSTM tile and one decoder-LSTM tile per cluster for the whole launch: park weight k-blocks of this
+    // CTA's K quarters in the free TMEM columns, split so that each phase's remaining stages fit the ring in one round
+    const int nka = p.mult * (p.Pp + p.Ep + p.Hap) / KB, nkd = p.mult * (p.Hap + p.Ep + p.Hdp) / KB;
+    const int ka0 = rank * nka / CL, kd0 = rank * nkd / CL;
+    sm.res_a = min((rank + 1) * nka / CL - ka0, (res_slots<N>() * 2 + 2) / 5);
+    sm.res_d = min((rank + 1) * nkd / CL - kd0, res_slots<N>() - sm.res_a);
+    load_resident<N>(p.w_att2, (long long)nka * KB, 4 * p.Ha, cid * TILE_M, ka0, sm.res_a, 0, tmem_base);
+    load_resident<N>(p.w_dec2, (long long)nkd * KB, 4 * p.Hd, cid * TILE_M, kd0, sm.res_d, sm.res_a, tmem_base);
+  }
+  tc_fence_before();
   cluster_sync_all();     // peers' barriers / smem are initialised before any DSMEM traffic
+  tc_fence_after();
 
   unsigned int epoch = 0;
   uint32_t acc_par = 0, att_par = 0, round = 0, eround = 0;
