@@ -43,7 +43,7 @@ def _oracle(hp, dec, memory, steps, seed, force=True):
         return O.decoder_inference(sd, memory, d, keep_fn, max_steps=steps, force_steps=steps if force else None)
 
 
-@pytest.mark.parametrize("B,T_in,steps", [(1, 17, 6), (3, 23, 5), (9, 40, 4)])
+@pytest.mark.parametrize("B,T_in,steps", [(1, 17, 6), (3, 23, 5), (9, 40, 4), (70, 12, 3), (130, 11, 3)])
 def test_infer_fp32_mode_matches_oracle(B, T_in, steps):
     from gantron_b200 import decoder_ops
     hp, dec, memory = _setup(B, T_in, steps, "fp32")

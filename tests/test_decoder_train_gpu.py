@@ -79,7 +79,8 @@ def _check_grads(dec, sd, mem_grad, o_mem_grad, rel, l2=False):
     assert e <= rel, f"d(memory) mismatch {e:.3e}; params ok: {msg}"
 
 
-@pytest.mark.parametrize("B,T_in,T", [(3, 17, 7), (9, 24, 4), (20, 33, 3), (40, 21, 3)])
+# B = 70 and 130 exercise the N = 128 / 256 tile variants (chunked exchanges, fewer TMEM-resident weight slots)
+@pytest.mark.parametrize("B,T_in,T", [(3, 17, 7), (9, 24, 4), (20, 33, 3), (40, 21, 3), (70, 12, 3), (130, 10, 2)])
 def test_train_fp32_mode_values_and_grads(B, T_in, T):
     seed = 0x5EED0000 + B
     hp, dec, memory, mels, in_len, R = _build(B, T_in, T, "fp32")
