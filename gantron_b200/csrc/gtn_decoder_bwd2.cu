@@ -165,7 +165,13 @@ GTN_DEVICE void cell_apply(const DecBwd2& p, const CellIn& in, int t, int b, int
   const float dgg = dc * g.x * (1.f - g.z * g.z);
   const float dgo = d_o * g.w * (1.f - g.w);
   const size_t g0 = ((size_t)t * p.B + b) * 4 * H + unit;
-  dg_all[g0] = dgi; dg_all[g0 + H] = dgf; dg_all[g0 + 2 * H] = dgg; dg_all[g0 + 3 * H] = dgo;
+  if (p.flags & 2) {
+    bf16* dgb = reinterpret_cast<bf16*>(dg_all);          // bf16 mode: the saves are GEMM operands only
+    dgb[g0] = __float2bfloat16_rn(dgi); dgb[g0 + H] = __float2bfloat16_rn(dgf);
+    dgb[g0 + 2 * H] = __float2bfloat16_rn(dgg); dgb[g0 + 3 * H] = __float2bfloat16_rn(dgo);
+  } else {
+    dg_all[g0] = dgi; dg_all[g0 + H] = dgf; dg_all[g0 + 2 * H] = dgg; dg_all[g0 + 3 * H] = dgo;
+  }
   bf16* xr = xdg + (size_t)b * p.mult * 4 * H;
   store_act(xr, unit, 4 * H, p.prec, dgi);
   store_act(xr, H + unit, 4 * H, p.prec, dgf);

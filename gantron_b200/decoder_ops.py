@@ -115,7 +115,7 @@ def linear_nt(x: torch.Tensor, w: torch.Tensor, prec: int, bias: Optional[torch.
     M, K = x.shape
     N = w.shape[0]
     kp = pad_to(K, 8) if prec == 1 else pad_to(K, 8)
-    xa = packing.expand(x.float(), kp, prec, False)
+    xa = packing.expand(x, kp, prec, False)          # (a bf16 x stays bf16 in bf16 mode)
     wa = packing.expand(w.float(), kp, prec, True)
     out = torch.empty(M, N, device=x.device, dtype=out_dtype)
     ops.gemm(xa, wa, out, bias_n=bias)
@@ -638,7 +638,9 @@ def _bptt_v2(dec, pk, d, ctx, S, sv, dproj, d_align, prec):
         xdg_a=z(B, mult * 4 * Ha, dt=BF16), xdg_d=z(2, B, mult * 4 * Hd, dt=BF16),
         carry_ha=z(B, Ha), dha_dec=z(B, Ha), dc_a=z(B, Ha), dc_d=z(B, Hd), dhd_rec=z(B, Hd), dctx_att=z(B, Ep), dctx_dec=z(B, Ep),
         dwprev=z(B, q.ldT), dcum=z(B, q.ldT), barrier=z(4, dt=torch.int32),
-        dga_all=torch.empty(T, B, 4 * Ha, device=dev), dgd_all=torch.empty(T, B, 4 * Hd, device=dev),
+        # pre-activation gate gradients: consumed only as GEMM operands, so bf16 mode stores them as bf16
+        dga_all=torch.empty(T, B, 4 * Ha, device=dev, dtype=BF16 if prec == 1 else torch.float32),
+        dgd_all=torch.empty(T, B, 4 * Hd, device=dev, dtype=BF16 if prec == 1 else torch.float32),
         dq_all=torch.empty(T, B, A, device=dev), dctx_all=torch.empty(B, T, E, device=dev), dpm=z(B, Tin, A),
         dv_part=z(grid, A), dU_part=z(grid, 128, 64))
     for k, v in wk.items():
@@ -651,7 +653,7 @@ def _bptt_v2(dec, pk, d, ctx, S, sv, dproj, d_align, prec):
     q.align, q.th_all, q.cum_all = sv["align"].data_ptr(), sv["th_all"].data_ptr(), sv["cum_all"].data_ptr()
     q.dproj_all = dproj.data_ptr()
     q.prof = PROF_BUFFER_BWD.data_ptr() if PROF_BUFFER_BWD is not None else None
-    q.flags = int(os.environ.get("GTN_BWD_FLAGS", "1"))     # bit 0: L2 prefetch of the saves (bits 1-4: dev-only ablations)
+    q.flags = (int(os.environ.get("GTN_BWD_FLAGS", "1")) & 1) | (2 if prec == 1 else 0)   # bit 0: L2 prefetch, bit 1: bf16 dga/dgd
     d_align_c = None
     if d_align is not None:
         d_align_c = d_align.float().contiguous()

@@ -43,6 +43,8 @@ def expand(x: torch.Tensor, kpad: int, prec: int, is_weight: bool) -> torch.Tens
     K = x.shape[-1]
     assert kpad >= K
     if prec == 1:
+        if kpad == K:                       # nothing to pad: one conversion kernel (none if x is already bf16)
+            return x.to(BF16).contiguous()
         out = torch.zeros(*x.shape[:-1], kpad, device=x.device, dtype=BF16)
         out[..., :K] = x.to(BF16)
         return out

@@ -302,14 +302,14 @@ typedef struct gtn_decoder_bwd2_params {
   float *dwprev, *dcum;                 /* [B][ldT] */
   unsigned int *barrier;
   /* outputs */
-  float *dga_all, *dgd_all;  /* [T][B][4Ha], [T][B][4Hd] pre-activation gate gradients (gate-major) */
+  float *dga_all, *dgd_all;  /* [T][B][4Ha], [T][B][4Hd] pre-activation gate gradients (gate-major); bf16 when flags & 2 */
   float *dq_all;             /* [T][B][A] */
   float *dctx_all;           /* [B][T][E] total gradient of the time-varying context columns per frame */
   float *dpm;                /* [B][Tin][A] gradient w.r.t. processed_memory (accumulated over frames) */
   float *dv_part;            /* [grid][A] */
   float *dU_part;            /* [grid][128][64]: per-CTA partial of dU[a][ch*KS+k] */
   long long *prof;           /* optional [16][32] clock64() stamps of CTA 0 for the first 16 processed frames (NULL = off) */
-  int flags;                 /* bit 0: prefetch each frame's saves into L2 one frame ahead */
+  int flags;                 /* bit 0: prefetch each frame's saves into L2 one frame ahead; bit 1: dga_all / dgd_all are bf16 */
 } gtn_decoder_bwd2_params;
 
 int gtn_decoder_bwd2_grid(int B, int Ha, int Hd, int E);   /* CTAs gtn_decoder_backward2 launches, or -1 */
