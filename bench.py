@@ -357,7 +357,7 @@ def run_ours(args):
 BWD_KERNEL_MAC = (2560 + 1536) * 4096 + 131_072 + 2 * 912_000 + 2 * 172_800
 FWD_KERNEL_MAC = DEC_STEP_MAC - 86_016 - 165_888 - 4096 * 256 - 4096 * 1024 - 0   # minus prenet, projection, hoisted prenet/constant columns
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture (profiles/r1_ncu_decoder_full.md)
-NCU_TRAFFIC = {"decoder_fwd2_kernel": 8.46e9, "decoder_bwd2_kernel": 9.58e9}
+NCU_TRAFFIC = {"decoder_fwd2_kernel": 6.93e9, "decoder_bwd2_kernel": 8.31e9}
 
 
 def kernel_roofline(tr, batch, pk):
