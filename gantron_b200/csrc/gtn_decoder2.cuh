@@ -223,7 +223,7 @@ GTN_DEVICE void load_x_kblock(const GemmJob& job, uint8_t* dst, uint64_t* bar, i
   tma_load_3d(dst, job.seg[si].map, bar, kk * KB, 0, job.seg[si].z);
 }
 
-// Issue one cluster-split GEMM: this CTA's quarter of K.  Producer = thread 0, MMA = thread 32.
+// Issue one cluster-split GEMM: this CTA's quarter of K.  Producer = warp 0, MMA issuer = warp 1 (one elected lane each).
 // A ring stage is [W tile 16 KB | X tile N*128 B].  The first job.res_n k-blocks of the CTA's range have their weights
 // resident in TMEM and need only the X tile, so G = stage_bytes / X_BYTES of them share ONE stage (fewer stages per
 // GEMM = fewer load -> MMA -> free-slot round trips; the phases are bound by those chains, not by bytes).
@@ -237,7 +237,12 @@ GTN_DEVICE bool gemm_issue(const GemmJob& job, Ring& rg, uint32_t tmem_acc, uint
   const int res_n = min(job.res_n, kb1 - kb0);
   const int res_stages = (res_n + G - 1) / G;
   const int nstages = res_stages + (kb1 - kb0 - res_n);
-  if (threadIdx.x == 0) {
+  // Both roles run in WARP-UNIFORM control flow (the warp index comes out of a shuffle, every lane walks the loop, one
+  // elected lane issues): the TMA / tcgen05 instructions take their operands from uniform registers, and inside a
+  // divergent `threadIdx.x == k` branch the compiler wraps every single one in an ELECT / R2UR / branch waterfall
+  // (~100 cycles per tcgen05.mma, ~700 per ring stage on the producer side).
+  const int warp_u = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  if (warp_u == 0) {
     for (int sg = 0; sg < nstages; ++sg) {
       const int s = rg.prod_it % rg.S;
       const uint32_t par = (rg.prod_it / rg.S) & 1u;
@@ -245,17 +250,22 @@ GTN_DEVICE bool gemm_issue(const GemmJob& job, Ring& rg, uint32_t tmem_acc, uint
       uint8_t* st = rg.base + (size_t)s * rg.stage_bytes;
       if (sg < res_stages) {
         const int n = min(G, res_n - sg * G);
-        mbar_expect_tx(&rg.full[s], (uint32_t)n * X_BYTES);
-        for (int j = 0; j < n; ++j) load_x_kblock<N>(job, st + (size_t)j * X_BYTES, &rg.full[s], kb0 + sg * G + j);
+        if (elect_one()) {
+          mbar_expect_tx(&rg.full[s], (uint32_t)n * X_BYTES);
+          for (int j = 0; j < n; ++j) load_x_kblock<N>(job, st + (size_t)j * X_BYTES, &rg.full[s], kb0 + sg * G + j);
+        }
       } else {
         const int kb = kb0 + res_n + (sg - res_stages);
-        mbar_expect_tx(&rg.full[s], W_TILE_BYTES + X_BYTES);
-        tma_load_3d(st, job.wmap, &rg.full[s], kb * KB, job.row0, 0);
-        load_x_kblock<N>(job, st + W_TILE_BYTES, &rg.full[s], kb);
+        if (elect_one()) {
+          mbar_expect_tx(&rg.full[s], W_TILE_BYTES + X_BYTES);
+          tma_load_3d(st, job.wmap, &rg.full[s], kb * KB, job.row0, 0);
+          load_x_kblock<N>(job, st + W_TILE_BYTES, &rg.full[s], kb);
+        }
       }
+      __syncwarp();
       ++rg.prod_it;
     }
-  } else if (threadIdx.x == 32) {
+  } else if (warp_u == 1) {
     if (kb1 > kb0) {
       const uint32_t idesc = umma_idesc_bf16(TILE_M, N);
       uint32_t started = 0u;
@@ -271,24 +281,28 @@ GTN_DEVICE bool gemm_issue(const GemmJob& job, Ring& rg, uint32_t tmem_acc, uint
           for (int j = 0; j < n; ++j) {
             const uint32_t ta = tmem_res + res_col<N>(job.res_slot0 + sg * G + j);
             const uint64_t db = umma_desc_sw128(a + (uint32_t)j * X_BYTES);
+            if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < KB / 16; ++k) {
-              umma_bf16_ts(tmem_acc, ta + (uint32_t)(8 * k), db + (uint64_t)(2 * k), idesc, started);
-              started = 1u;
+              for (int k = 0; k < KB / 16; ++k)
+                umma_bf16_ts(tmem_acc, ta + (uint32_t)(8 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)(started | (k > 0)));
             }
+            started = 1u;
           }
         } else {
           const uint64_t da = umma_desc_sw128(a), db = umma_desc_sw128(a + W_TILE_BYTES);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < KB / 16; ++k) {
-            umma_bf16(tmem_acc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, started);
-            started = 1u;
+            for (int k = 0; k < KB / 16; ++k)
+              umma_bf16(tmem_acc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)(started | (k > 0)));
           }
+          started = 1u;
         }
-        umma_commit(&rg.empty[s]);
+        if (elect_one()) umma_commit(&rg.empty[s]);
+        __syncwarp();
         ++rg.mma_it;
       }
-      umma_commit(acc_full);
+      if (elect_one()) umma_commit(acc_full);
+      __syncwarp();
     }
   }
   return kb1 > kb0;
