@@ -60,6 +60,7 @@ GTN_DEVICE void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "mem
 GTN_DEVICE void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 GTN_DEVICE void wait_bar(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;       // common case on the issue chains: no clock read
   long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
     if (clock64() - t0 > 8000000000LL) __trap();   // ~4 s: a pipeline bug must not hang the GPU
@@ -242,39 +243,60 @@ GTN_DEVICE bool gemm_issue(const GemmJob& job, Ring& rg, uint32_t tmem_acc, uint
   // divergent `threadIdx.x == k` branch the compiler wraps every single one in an ELECT / R2UR / branch waterfall
   // (~100 cycles per tcgen05.mma, ~700 per ring stage on the producer side).
   const int warp_u = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  // The issue loops are serial chains on the phase's critical path (measured: ~700 cycles per stage, of which only
+  // ~130 per TMA instruction): ring fields are hoisted into locals, slot / parity advance incrementally (no integer
+  // division per stage), the activation-segment cursor is walked once, and wait_bar reads no clock when the first
+  // try succeeds.
+  const int S = rg.S;
+  const uint32_t stage_bytes = rg.stage_bytes;
+  uint8_t* const base = rg.base;
+  uint64_t* const full = rg.full;
+  uint64_t* const empty = rg.empty;
   if (warp_u == 0) {
+    const uint32_t it0 = rg.prod_it;
+    int s = (int)(it0 % (uint32_t)S);
+    uint32_t par = (it0 / (uint32_t)S) & 1u;
+    // activation cursor: segment si, k-block kk inside it, for global k-block kb0
+    int si = 0, kk = kb0;
+    while (si < job.nseg - 1 && kk >= job.seg[si].nkb) { kk -= job.seg[si].nkb; ++si; }
+    const CUtensorMap* xmap = job.seg[si].map;
+    int xz = job.seg[si].z, xn = job.seg[si].nkb;
+    // every lane advances the cursor, one elected lane issues
+    auto load_x = [&](uint8_t* dst, uint64_t* bar) {
+      if (elect_one()) tma_load_3d(dst, xmap, bar, kk * KB, 0, xz);
+      ++kk;
+      while (si < job.nseg - 1 && kk >= xn) { kk -= xn; ++si; xmap = job.seg[si].map; xz = job.seg[si].z; xn = job.seg[si].nkb; }
+    };
     for (int sg = 0; sg < nstages; ++sg) {
-      const int s = rg.prod_it % rg.S;
-      const uint32_t par = (rg.prod_it / rg.S) & 1u;
-      wait_bar(&rg.empty[s], par ^ 1u);
-      uint8_t* st = rg.base + (size_t)s * rg.stage_bytes;
+      wait_bar(&empty[s], par ^ 1u);
+      uint8_t* st = base + (size_t)s * stage_bytes;
       if (sg < res_stages) {
         const int n = min(G, res_n - sg * G);
-        if (elect_one()) {
-          mbar_expect_tx(&rg.full[s], (uint32_t)n * X_BYTES);
-          for (int j = 0; j < n; ++j) load_x_kblock<N>(job, st + (size_t)j * X_BYTES, &rg.full[s], kb0 + sg * G + j);
-        }
+        if (elect_one()) mbar_expect_tx(&full[s], (uint32_t)n * X_BYTES);
+        for (int j = 0; j < n; ++j) load_x(st + (size_t)j * X_BYTES, &full[s]);
       } else {
         const int kb = kb0 + res_n + (sg - res_stages);
         if (elect_one()) {
-          mbar_expect_tx(&rg.full[s], W_TILE_BYTES + X_BYTES);
-          tma_load_3d(st, job.wmap, &rg.full[s], kb * KB, job.row0, 0);
-          load_x_kblock<N>(job, st + W_TILE_BYTES, &rg.full[s], kb);
+          mbar_expect_tx(&full[s], W_TILE_BYTES + X_BYTES);
+          tma_load_3d(st, job.wmap, &full[s], kb * KB, job.row0, 0);
         }
+        load_x(st + W_TILE_BYTES, &full[s]);
       }
       __syncwarp();
-      ++rg.prod_it;
+      if (++s == S) { s = 0; par ^= 1u; }
     }
+    rg.prod_it = it0 + (uint32_t)nstages;          // Ring is per-thread state: every lane keeps its copy in step
   } else if (warp_u == 1) {
     if (kb1 > kb0) {
       const uint32_t idesc = umma_idesc_bf16(TILE_M, N);
+      const uint32_t it0 = rg.mma_it;
+      int s = (int)(it0 % (uint32_t)S);
+      uint32_t par = (it0 / (uint32_t)S) & 1u;
       uint32_t started = 0u;
       for (int sg = 0; sg < nstages; ++sg) {
-        const int s = rg.mma_it % rg.S;
-        const uint32_t par = (rg.mma_it / rg.S) & 1u;
-        wait_bar(&rg.full[s], par);
+        wait_bar(&full[s], par);
         tc_fence_after();
-        const uint32_t a = smem_u32(rg.base + (size_t)s * rg.stage_bytes);
+        const uint32_t a = smem_u32(base + (size_t)s * stage_bytes);
         if (sg < res_stages) {
           // weights from TMEM: 16 K elements = 8 columns per UMMA
           const int n = min(G, res_n - sg * G);
@@ -297,11 +319,12 @@ GTN_DEVICE bool gemm_issue(const GemmJob& job, Ring& rg, uint32_t tmem_acc, uint
           }
           started = 1u;
         }
-        if (elect_one()) umma_commit(&rg.empty[s]);
+        if (elect_one()) umma_commit(&empty[s]);
         __syncwarp();
-        ++rg.mma_it;
+        if (++s == S) { s = 0; par ^= 1u; }
       }
       if (elect_one()) umma_commit(acc_full);
+      rg.mma_it = it0 + (uint32_t)nstages;
       __syncwarp();
     }
   }
