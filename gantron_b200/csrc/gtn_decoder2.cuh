@@ -229,6 +229,9 @@ GTN_DEVICE void load_x_kblock(const GemmJob& job, uint8_t* dst, uint64_t* bar, i
 // resident in TMEM and need only the X tile, so G = stage_bytes / X_BYTES of them share ONE stage (fewer stages per
 // GEMM = fewer load -> MMA -> free-slot round trips; the phases are bound by those chains, not by bytes).
 // Returns whether this CTA had any k-block (else its partial tile is all zeros).
+#ifndef GTN_NPROD
+#define GTN_NPROD 1
+#endif
 template <int N>
 GTN_DEVICE bool gemm_issue(const GemmJob& job, Ring& rg, uint32_t tmem_acc, uint64_t* acc_full, int rank,
                            uint32_t tmem_res = 0u) {
@@ -252,7 +255,11 @@ GTN_DEVICE bool gemm_issue(const GemmJob& job, Ring& rg, uint32_t tmem_acc, uint
   uint8_t* const base = rg.base;
   uint64_t* const full = rg.full;
   uint64_t* const empty = rg.empty;
-  if (warp_u == 0) {
+  // NPROD producer warps (0, 2, 3) take the ring stages round-robin: a stage costs its issuer several hundred cycles of
+  // serial mbarrier / elect / TMA-issue latency, so splitting the stages over warps shortens the chain the MMA waits on.
+  constexpr int NPROD = GTN_NPROD;
+  const int pw = warp_u == 0 ? 0 : warp_u - 1;             // producer index of warps 0, 2, 3
+  if (warp_u != 1 && pw < NPROD) {
     const uint32_t it0 = rg.prod_it;
     int s = (int)(it0 % (uint32_t)S);
     uint32_t par = (it0 / (uint32_t)S) & 1u;
@@ -261,26 +268,27 @@ GTN_DEVICE bool gemm_issue(const GemmJob& job, Ring& rg, uint32_t tmem_acc, uint
     while (si < job.nseg - 1 && kk >= job.seg[si].nkb) { kk -= job.seg[si].nkb; ++si; }
     const CUtensorMap* xmap = job.seg[si].map;
     int xz = job.seg[si].z, xn = job.seg[si].nkb;
-    // every lane advances the cursor, one elected lane issues
-    auto load_x = [&](uint8_t* dst, uint64_t* bar) {
-      if (elect_one()) tma_load_3d(dst, xmap, bar, kk * KB, 0, xz);
+    // every lane of every producer warp advances the cursor; one elected lane of the stage's warp issues
+    auto load_x = [&](bool mine, uint8_t* dst, uint64_t* bar) {
+      if (mine && elect_one()) tma_load_3d(dst, xmap, bar, kk * KB, 0, xz);
       ++kk;
       while (si < job.nseg - 1 && kk >= xn) { kk -= xn; ++si; xmap = job.seg[si].map; xz = job.seg[si].z; xn = job.seg[si].nkb; }
     };
     for (int sg = 0; sg < nstages; ++sg) {
-      wait_bar(&empty[s], par ^ 1u);
+      const bool mine = (sg % NPROD) == pw;
+      if (mine) wait_bar(&empty[s], par ^ 1u);
       uint8_t* st = base + (size_t)s * stage_bytes;
       if (sg < res_stages) {
         const int n = min(G, res_n - sg * G);
-        if (elect_one()) mbar_expect_tx(&full[s], (uint32_t)n * X_BYTES);
-        for (int j = 0; j < n; ++j) load_x(st + (size_t)j * X_BYTES, &full[s]);
+        if (mine && elect_one()) mbar_expect_tx(&full[s], (uint32_t)n * X_BYTES);
+        for (int j = 0; j < n; ++j) load_x(mine, st + (size_t)j * X_BYTES, &full[s]);
       } else {
         const int kb = kb0 + res_n + (sg - res_stages);
-        if (elect_one()) {
+        if (mine && elect_one()) {
           mbar_expect_tx(&full[s], W_TILE_BYTES + X_BYTES);
           tma_load_3d(st, job.wmap, &full[s], kb * KB, job.row0, 0);
         }
-        load_x(st + W_TILE_BYTES, &full[s]);
+        load_x(mine, st + W_TILE_BYTES, &full[s]);
       }
       __syncwarp();
       if (++s == S) { s = 0; par ^= 1u; }

@@ -54,6 +54,7 @@ struct GemmKernelParams {
 };
 
 GTN_DEVICE void wait_or_trap(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
   long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
     if (clock64() - t0 > 6000000000LL) __trap();   // ~3 s: a pipeline bug must not hang the GPU
@@ -101,73 +102,89 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int kb0 = split * p.kps;
   const int kb1 = min(p.num_k_blocks, kb0 + p.kps);
 
-  if (warp == 0) {
-    if (lane == 0) {
-      // ------------------------------ TMA producer ------------------------------
-      for (int kb = kb0; kb < kb1; ++kb) {
-        const int s = (kb - kb0) % stages;
-        const uint32_t ph = (uint32_t)((kb - kb0) / stages) & 1u;
-        wait_or_trap(&empty[s], ph ^ 1u);
-        mbar_expect_tx(&full[s], A_BYTES + B_BYTES);
-        uint8_t* dA = sA + (size_t)s * A_BYTES;
-        uint8_t* dB = sB + (size_t)s * B_BYTES;
-        if (!p.mn_major) {
-          int a0, a1, a2, b0, b1, b2;
-          if (p.mode == MODE_PLAIN) {
-            a0 = kb * BK; a1 = m0; a2 = z;
-            b0 = kb * BK; b1 = n0; b2 = p.b_bcast ? 0 : z;
-          } else {  // MODE_CONV
-            const int tap = kb / p.ci_blocks, cib = kb - tap * p.ci_blocks;
-            a0 = tap * p.cin_pad + cib * BK; a1 = m0; a2 = 0;
-            b0 = cib * BK; b1 = n0 + tap * p.dil - p.pad; b2 = z;
-          }
+  // Producer and MMA issuer run in WARP-UNIFORM control flow (warp index out of a shuffle, all lanes walk the loop, one
+  // elected lane issues): TMA / tcgen05 instructions take uniform-register operands, and under a divergent `lane == 0`
+  // branch the compiler wraps each of them in an ELECT / R2UR / branch loop (~100 cycles per tcgen05.mma).
+  const int warp_u = __shfl_sync(0xffffffffu, warp, 0);
+  if (warp_u == 0) {
+    // ------------------------------ TMA producer ------------------------------
+    int s = 0;
+    uint32_t ph = 0u;
+    for (int kb = kb0; kb < kb1; ++kb) {
+      wait_or_trap(&empty[s], ph ^ 1u);
+      uint8_t* dA = sA + (size_t)s * A_BYTES;
+      uint8_t* dB = sB + (size_t)s * B_BYTES;
+      if (!p.mn_major) {
+        int a0, a1, a2, b0, b1, b2;
+        if (p.mode == MODE_PLAIN) {
+          a0 = kb * BK; a1 = m0; a2 = z;
+          b0 = kb * BK; b1 = n0; b2 = p.b_bcast ? 0 : z;
+        } else {  // MODE_CONV
+          const int tap = kb / p.ci_blocks, cib = kb - tap * p.ci_blocks;
+          a0 = tap * p.cin_pad + cib * BK; a1 = m0; a2 = 0;
+          b0 = cib * BK; b1 = n0 + tap * p.dil - p.pad; b2 = z;
+        }
+        if (elect_one()) {
+          mbar_expect_tx(&full[s], A_BYTES + B_BYTES);
           tma_load_3d(dA, &tmA, &full[s], a0, a1, a2);
           tma_load_3d(dB, &tmB, &full[s], b0, b1, b2);
-        } else {
-          // MN-major: boxes of 64 MN-elements (inner, 128 B) x 64 K-rows, one per 64-wide slice of the tile
-          int ka, kbr, za, zb;
-          if (p.mode == MODE_PLAIN) {
-            ka = kbr = kb * BK; za = z; zb = p.b_bcast ? 0 : z;
-          } else {  // MODE_WGRAD: k-block -> (batch, time block); z = tap; the tap shift is a K-row offset of B
-            const int bb = kb / p.t_blocks, tb = kb - bb * p.t_blocks;
-            ka = tb * BK; kbr = tb * BK + z * p.taps_dil - p.taps_pad; za = zb = bb;
-          }
+        }
+      } else {
+        // MN-major: boxes of 64 MN-elements (inner, 128 B) x 64 K-rows, one per 64-wide slice of the tile
+        int ka, kbr, za, zb;
+        if (p.mode == MODE_PLAIN) {
+          ka = kbr = kb * BK; za = z; zb = p.b_bcast ? 0 : z;
+        } else {  // MODE_WGRAD: k-block -> (batch, time block); z = tap; the tap shift is a K-row offset of B
+          const int bb = kb / p.t_blocks, tb = kb - bb * p.t_blocks;
+          ka = tb * BK; kbr = tb * BK + z * p.taps_dil - p.taps_pad; za = zb = bb;
+        }
+        if (elect_one()) {
+          mbar_expect_tx(&full[s], A_BYTES + B_BYTES);
 #pragma unroll
           for (int h = 0; h < BM / 64; ++h) tma_load_3d(dA + h * 8192, &tmA, &full[s], m0 + 64 * h, ka, za);
 #pragma unroll
           for (int h = 0; h < BN / 64; ++h) tma_load_3d(dB + h * 8192, &tmB, &full[s], n0 + 64 * h, kbr, zb);
         }
       }
+      __syncwarp();
+      if (++s == stages) { s = 0; ph ^= 1u; }
     }
-  } else if (warp == 1) {
-    if (lane == 0) {
-      // ------------------------------ MMA issuer ------------------------------
-      const uint32_t idesc = umma_idesc_bf16(BM, BN) | (p.mn_major ? ((1u << 15) | (1u << 16)) : 0u);
-      for (int kb = kb0; kb < kb1; ++kb) {
-        const int s = (kb - kb0) % stages;
-        const uint32_t ph = (uint32_t)((kb - kb0) / stages) & 1u;
-        wait_or_trap(&full[s], ph);
-        tc_fence_after();
-        const uint32_t aA = smem_u32(sA + (size_t)s * A_BYTES), aB = smem_u32(sB + (size_t)s * B_BYTES);
-        if (!p.mn_major) {
-          const uint64_t da = umma_desc_sw128(aA), db = umma_desc_sw128(aB);
+  } else if (warp_u == 1) {
+    // ------------------------------ MMA issuer ------------------------------
+    const uint32_t idesc = umma_idesc_bf16(BM, BN) | (p.mn_major ? ((1u << 15) | (1u << 16)) : 0u);
+    int s = 0;
+    uint32_t ph = 0u;
+    for (int kb = kb0; kb < kb1; ++kb) {
+      wait_or_trap(&full[s], ph);
+      tc_fence_after();
+      const uint32_t aA = smem_u32(sA + (size_t)s * A_BYTES), aB = smem_u32(sB + (size_t)s * B_BYTES);
+      const uint32_t acc0 = (uint32_t)(kb > kb0);
+      if (!p.mn_major) {
+        const uint64_t da = umma_desc_sw128(aA), db = umma_desc_sw128(aB);
+        if (elect_one()) {
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
             // advance 16 bf16 = 32 B along K inside the 128 B swizzle row: +2 in the (addr >> 4) field
-            umma_bf16(tmem_acc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb > kb0) | (k > 0)));
+            umma_bf16(tmem_acc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, acc0 | (uint32_t)(k > 0));
           }
-        } else {
+          umma_commit(&empty[s]);      // frees the smem slot once these MMAs retire
+        }
+      } else {
+        const uint64_t da = umma_desc_sw128_mn(aA), db = umma_desc_sw128_mn(aB);
+        if (elect_one()) {
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
-            // 16 K-rows = two 8-row swizzle atoms = 2048 B per UMMA K step
-            umma_bf16(tmem_acc, umma_desc_sw128_mn(aA + k * 2048), umma_desc_sw128_mn(aB + k * 2048), idesc,
-                      (uint32_t)((kb > kb0) | (k > 0)));
+            // 16 K-rows = two 8-row swizzle atoms = 2048 B per UMMA K step (+128 in the (addr >> 4) field)
+            umma_bf16(tmem_acc, da + (uint64_t)(128 * k), db + (uint64_t)(128 * k), idesc, acc0 | (uint32_t)(k > 0));
           }
+          umma_commit(&empty[s]);
         }
-        umma_commit(&empty[s]);      // frees the smem slot once these MMAs retire
       }
-      umma_commit(accum_full);       // accumulator complete
+      __syncwarp();
+      if (++s == stages) { s = 0; ph ^= 1u; }
     }
+    if (elect_one()) umma_commit(accum_full);       // accumulator complete
+    __syncwarp();
   } else if (warp >= 4) {
     // ------------------------------ epilogue ------------------------------
     wait_or_trap(accum_full, 0);
