@@ -522,36 +522,44 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
     }
     __syncthreads();
     PROFB(13);
-    if (active && threadIdx.x == 32) {
+    // warp 1 issues in warp-uniform control flow (one elected lane; see gemm_issue)
+    if (active && __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0) == 1) {
       tc_fence_after();
       // G[j][kk] = sum_a dth[j][a] U[a][kk]   (M = positions, N = 64 filter taps, K = attention dim, 2 k-blocks)
       const uint32_t idesc = umma_idesc_bf16(TILE_M, 64);
       const uint32_t uts = smem_u32(sm.ut_s);
-      for (int pl = 0; pl < 3; ++pl) {             // (dth_hi, U_hi), (dth_lo, U_hi), (dth_hi, U_lo)
-        const uint32_t abase = smem_u32(pl == 1 ? dth_lo : dth_hi);
-        const uint32_t bbase = uts + (pl == 2 ? 2u * 8192u : 0u);
-#pragma unroll
-        for (int kb = 0; kb < 2; ++kb) {
-          const uint64_t da = umma_desc_sw128(abase + kb * W_TILE_BYTES), db = umma_desc_sw128(bbase + kb * 8192u);
-#pragma unroll
-          for (int k = 0; k < KB / 16; ++k)
-            umma_bf16(tmem_g, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((pl | kb | k) != 0));
-        }
-      }
-      umma_commit(sm.g_full);
+      const uint32_t a_hi = smem_u32(dth_hi), a_lo = smem_u32(dth_lo);
+      const uint32_t acc_du = (uint32_t)(!(it == 0 && itb == 0));
       // dU[a][kk] += sum_j dth[j][a] im2col[j][kk]   (M = attention dim: 2 MN slices 16 KB apart, N = taps, K = positions)
       const uint32_t idesc_mn = umma_idesc_bf16(TILE_M, 64) | (1u << 15) | (1u << 16);
-      for (int pl = 0; pl < 3; ++pl) {             // (dth_hi, im_hi), (dth_lo, im_hi), (dth_hi, im_lo)
-        const uint32_t abase = smem_u32(pl == 1 ? dth_lo : dth_hi);
-        const uint32_t bbase = smem_u32(pl == 2 ? im_lo : im_hi);
+      const uint32_t b_hi = smem_u32(im_hi), b_lo = smem_u32(im_lo);
+      if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < TILE_M / 16; ++k) {
-          const uint64_t da = umma_desc_sw128_mn_lbo(abase + k * 2048u, W_TILE_BYTES);
-          const uint64_t db = umma_desc_sw128_mn_lbo(bbase + k * 2048u, W_TILE_BYTES);
-          umma_bf16(tmem_du, da, db, idesc_mn, (uint32_t)(!(it == 0 && itb == 0) || (pl | k) != 0));
+        for (int pl = 0; pl < 3; ++pl) {             // (dth_hi, U_hi), (dth_lo, U_hi), (dth_hi, U_lo)
+          const uint32_t abase = pl == 1 ? a_lo : a_hi;
+          const uint32_t bbase = uts + (pl == 2 ? 2u * 8192u : 0u);
+#pragma unroll
+          for (int kb = 0; kb < 2; ++kb) {
+            const uint64_t da = umma_desc_sw128(abase + kb * W_TILE_BYTES), db = umma_desc_sw128(bbase + kb * 8192u);
+#pragma unroll
+            for (int k = 0; k < KB / 16; ++k)
+              umma_bf16(tmem_g, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((pl | kb | k) != 0));
+          }
         }
+        umma_commit(sm.g_full);
+#pragma unroll
+        for (int pl = 0; pl < 3; ++pl) {             // (dth_hi, im_hi), (dth_lo, im_hi), (dth_hi, im_lo)
+          const uint32_t abase = pl == 1 ? a_lo : a_hi;
+          const uint32_t bbase = pl == 2 ? b_lo : b_hi;
+#pragma unroll
+          for (int k = 0; k < TILE_M / 16; ++k) {
+            const uint64_t da = umma_desc_sw128_mn_lbo(abase + k * 2048u, W_TILE_BYTES);
+            const uint64_t db = umma_desc_sw128_mn_lbo(bbase + k * 2048u, W_TILE_BYTES);
+            umma_bf16(tmem_du, da, db, idesc_mn, (pl | k) != 0 ? 1u : acc_du);
+          }
+        }
+        // (no commit needed for dU: it is only read at the very end, after later commits / barriers)
       }
-      // (no commit needed for dU: it is only read at the very end, after later commits / barriers)
     }
     __syncwarp();
     if (active) {
@@ -744,7 +752,7 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
   for (int i = threadIdx.x; i < p.A; i += blockDim.x) p.dv_part[(size_t)blockIdx.x * p.A + i] = sm.dv_acc[i];
   {
     // dU accumulator [128 lanes = attention dim][64 taps] -> dU_part[cta][a][kk]; make sure the last MMAs retired
-    if (threadIdx.x == 32) umma_commit(sm.g_full);
+    if (__shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0) == 1 && elect_one()) umma_commit(sm.g_full);
     __syncwarp();
     const int pair = cid * 2 + (rank >> 1);
     const bool used = pair < p.B;                     // CTAs that never ran an attention step hold no accumulator

@@ -423,18 +423,21 @@ GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, in
     if (p.train) PROF(21);
     __syncthreads();
     if (p.train) PROF(22);
-    if (active && threadIdx.x == 32) {
+    // warp 1 issues in warp-uniform control flow (one elected lane; see gemm_issue)
+    if (active && __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0) == 1) {
       tc_fence_after();
       const uint32_t idesc = umma_idesc_bf16(TILE_M, 128);
       const uint64_t dah = umma_desc_sw128(smem_u32(a_hi)), dal = umma_desc_sw128(smem_u32(a_lo));
       const uint64_t duh = umma_desc_sw128(smem_u32(sm.u_s)), dul = umma_desc_sw128(smem_u32(sm.u_s + W_TILE_BYTES));
+      if (elect_one()) {
 #pragma unroll
-      for (int k = 0; k < KB / 16; ++k) umma_bf16(tmem_att, dah + (uint64_t)(2 * k), duh + (uint64_t)(2 * k), idesc, (uint32_t)(k > 0));
+        for (int k = 0; k < KB / 16; ++k) umma_bf16(tmem_att, dah + (uint64_t)(2 * k), duh + (uint64_t)(2 * k), idesc, (uint32_t)(k > 0));
 #pragma unroll
-      for (int k = 0; k < KB / 16; ++k) umma_bf16(tmem_att, dal + (uint64_t)(2 * k), duh + (uint64_t)(2 * k), idesc, 1u);
+        for (int k = 0; k < KB / 16; ++k) umma_bf16(tmem_att, dal + (uint64_t)(2 * k), duh + (uint64_t)(2 * k), idesc, 1u);
 #pragma unroll
-      for (int k = 0; k < KB / 16; ++k) umma_bf16(tmem_att, dah + (uint64_t)(2 * k), dul + (uint64_t)(2 * k), idesc, 1u);
-      umma_commit(sm.att_full);
+        for (int k = 0; k < KB / 16; ++k) umma_bf16(tmem_att, dah + (uint64_t)(2 * k), dul + (uint64_t)(2 * k), idesc, 1u);
+        umma_commit(sm.att_full);
+      }
     }
     __syncwarp();
     PROF(24);                                    // q / window / im2col built, MMAs issued
