@@ -326,6 +326,120 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
 }
 
 // ------------------------------------------------------------------------------------------------
+// Prenet of autoregressive inference at small batch (B <= PRE_LOCAL_BMAX), computed inside EVERY cluster with plain FMAs:
+// at B = 1 a prenet layer is a 256 x 80..256 mat-vec, and running it as two cluster-split GEMM phases costs two TMA ->
+// tcgen05 -> DSMEM-exchange chains plus two grid barriers (~20k of the frame's ~85k cycles).  Here each CTA computes all
+// of layer 1 (32 KB of bf16 weights from L2) and its quarter of the layer-2 rows; the four quarters meet in global memory
+// behind one cluster barrier.  All clusters write the same bits to xp2, so no grid barrier is needed before the attention
+// LSTM GEMM reads it.  Same operands as the GEMM path (bf16 planes of weights and activations, fp32 accumulate); only the
+// summation order differs.  (model.py:97-106)
+// ------------------------------------------------------------------------------------------------
+static constexpr int PRE_LOCAL_BMAX = 4;
+
+GTN_DEVICE void store_act_f(float* x, int k, int kpad, int prec, float v) {     // store_act into an fp32 staging buffer
+  const bf16 hi = __float2bfloat16_rn(v);
+  const float fh = __bfloat162float(hi);
+  if (prec == 1) { x[k] = fh; return; }
+  const float r1 = v - fh;
+  const bf16 lo = __float2bfloat16_rn(r1);
+  const float fl = __bfloat162float(lo);
+  const float fl2 = __bfloat162float(__float2bfloat16_rn(r1 - fl));
+  x[k] = fh; x[kpad + k] = fh; x[2 * kpad + k] = fh;
+  x[3 * kpad + k] = fl; x[4 * kpad + k] = fl;
+  x[5 * kpad + k] = fl2;
+}
+
+// y[row][b] = sum_k W[row][k] xs[b][k] for rows [row_begin, row_end), K a multiple of 64; a group of G lanes owns a row,
+// U rows per group are in flight at once (the loads are L2 latency bound).  Raw sums go to y[b * ldy + row].  Deliberately
+// NOT inlined: both prenet layers run the same (instruction-cache warm) copy.
+__device__ __noinline__ void matvec_rows(const bf16* W, int K, const float* xs, int B, int row_begin, int row_end, float* y,
+                                         int ldy) {
+  constexpr int U = 8;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int C = K >> 3;                                   // 16-byte chunks per row
+  const int G = C >= 32 ? 32 : (C >= 16 ? 16 : 8);
+  const int RP = 32 / G, sub = lane / G, gl = lane % G;
+  for (int r0 = row_begin + warp * RP * U; r0 < row_end; r0 += 8 * RP * U) {
+    float acc[U][PRE_LOCAL_BMAX];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+      for (int b = 0; b < PRE_LOCAL_BMAX; ++b) acc[u][b] = 0.f;
+    for (int c = gl; c < C; c += G) {
+      uint4 q[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int row = r0 + u * RP + sub;
+        q[u] = row < row_end ? __ldg(reinterpret_cast<const uint4*>(W + (size_t)row * K) + c) : make_uint4(0u, 0u, 0u, 0u);
+      }
+#pragma unroll
+      for (int b = 0; b < PRE_LOCAL_BMAX; ++b) {
+        if (b >= B) break;
+        const float4 x0 = *reinterpret_cast<const float4*>(xs + (size_t)b * K + c * 8);
+        const float4 x1 = *reinterpret_cast<const float4*>(xs + (size_t)b * K + c * 8 + 4);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const uint32_t w[4] = {q[u].x, q[u].y, q[u].z, q[u].w};
+          float a = acc[u][b];
+          a += __uint_as_float(w[0] << 16) * x0.x; a += __uint_as_float(w[0] & 0xFFFF0000u) * x0.y;
+          a += __uint_as_float(w[1] << 16) * x0.z; a += __uint_as_float(w[1] & 0xFFFF0000u) * x0.w;
+          a += __uint_as_float(w[2] << 16) * x1.x; a += __uint_as_float(w[2] & 0xFFFF0000u) * x1.y;
+          a += __uint_as_float(w[3] << 16) * x1.z; a += __uint_as_float(w[3] & 0xFFFF0000u) * x1.w;
+          acc[u][b] = a;
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int row = r0 + u * RP + sub;
+#pragma unroll
+      for (int b = 0; b < PRE_LOCAL_BMAX; ++b) {
+        if (b >= B) break;
+        float a = acc[u][b];
+        for (int off = G >> 1; off > 0; off >>= 1) a += __shfl_xor_sync(0xffffffffu, a, off);
+        if (gl == 0 && row < row_end) y[b * ldy + row] = a;
+      }
+    }
+  }
+}
+
+GTN_DEVICE void prenet_local(const DecFwd& p, Smem2& sm, int t, int rank) {
+  const int mult = p.mult, K1 = mult * p.NMp, K2 = mult * p.Pp, P = p.P, B = p.B;
+  float* x1 = reinterpret_cast<float*>(sm.ring.base);      // [B][K1]  (the TMA ring is idle between the GEMM phases)
+  float* x2 = x1 + (size_t)B * K1;                         // [B][K2]
+  float* y = x2 + (size_t)B * K2;                          // [B][P] raw sums of the layer in flight
+  for (int i = threadIdx.x; i < B * K1; i += blockDim.x) x1[i] = __bfloat162float(__ldcg(BFP(p.xmel) + i));
+  for (int i = threadIdx.x; i < B * K2; i += blockDim.x) x2[i] = 0.f;      // padded columns P..Pp of every plane
+  __syncthreads();
+  // the mat-vecs only drop raw sums into shared memory; relu + dropout + plane split run afterwards, one (row, b) per
+  // thread, as ONE compact loop (inlined into the unrolled mat-vec the Philox code is replicated U x B times, and a code
+  // path that runs once per frame pays an instruction-cache miss for every line of it)
+  auto act = [&](float v, uint32_t site, int b, int row) {
+    v = fmaxf(v, 0.f);
+    const uint32_t bits = philox_bits(p.seed, site, (uint32_t)t, (uint32_t)(b * P + row));
+    return bits >= 0x80000000u ? v * 2.0f : 0.f;           // p = 0.5, always on (model.py:104)
+  };
+  matvec_rows(BFP(p.w_pre1), K1, x1, B, 0, P, y, P);
+  __syncthreads();
+  for (int i = threadIdx.x; i < B * P; i += blockDim.x) {
+    const int b = i / P, row = i - b * P;
+    store_act_f(x2 + (size_t)b * K2, row, p.Pp, p.prec, act(y[i], 1u, b, row));
+  }
+  __syncthreads();
+  PROF(29);
+  const int q = (P + CL - 1) / CL, r_lo = rank * q, r_hi = min(P, (rank + 1) * q);
+  matvec_rows(BFP(p.w_pre2), K2, x2, B, r_lo, r_hi, y, P);
+  __syncthreads();
+  for (int i = threadIdx.x; i < B * (r_hi - r_lo); i += blockDim.x) {
+    const int b = i / (r_hi - r_lo), row = r_lo + i - b * (r_hi - r_lo);
+    store_act(BFP(p.xp2) + (size_t)b * K2, row, p.Pp, p.prec, act(y[b * P + row], 2u, b, row));
+  }
+  PROF(30);
+  fence_proxy_async();          // xp2 (global) is read by TMA next; the staging area is overwritten by TMA
+  cluster_sync_all();
+}
+
+// ------------------------------------------------------------------------------------------------
 // attention phase: one CTA pair per sequence
 // ------------------------------------------------------------------------------------------------
 template <typename MT>
@@ -647,7 +761,11 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
   const unsigned int nblocks = gridDim.x;
   int t = 0;
   for (; t < p.n_steps; ++t) {
-    if (!p.train) {
+    if (!p.train && p.B <= PRE_LOCAL_BMAX) {
+      PROF(28);
+      prenet_local(p, sm, t, rank);
+      PROF(31);
+    } else if (!p.train) {
       PROF(28);
       gemm_phase<N>(p, maps, sm, K_PRE1, t, rank, cid, ncl, tmem_base, acc_par, round, wqr);
       PROF(29);
