@@ -53,46 +53,89 @@ def _peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    """SM clocks / throttle reasons sampled DURING the timed region (every 50 ms).
+
+    NVML (the library behind nvidia-smi) is polled from a thread of this process; it is initialised and the thread is
+    started BEFORE the warm-up, and samples are only kept between begin() and stop(): spawning `nvidia-smi -lms` at the
+    start of the timed region costs the region the tool's start-up (NVML / driver initialisation, seen as a 25 % slower
+    step on a busy host).  Falls back to an `nvidia-smi -lms 100` subprocess (also started before the warm-up)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int):
-        self.index, self.samples, self.proc = index, [], None
+        self.index, self.samples, self.proc, self.nvml = index, [], None, None
+        self.active, self.done, self.source = False, False, None
 
     def start(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            # CUDA_VISIBLE_DEVICES remaps CUDA indices; NVML wants the physical device
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = self.index
+            if vis:
+                ids = [v.strip() for v in vis.split(",") if v.strip()]
+                if self.index < len(ids) and ids[self.index].isdigit():
+                    phys = int(ids[self.index])
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nvml, self.source = pynvml, "nvml"
+            threading.Thread(target=self._poll_nvml, daemon=True).start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
+            self.source = "nvidia-smi"
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
             self.proc = None
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.samples.append(line.strip())
+    def begin(self):
+        self.samples, self.active = [], True
 
-    def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        sm, mx, reasons = [], None, set()
+    def _poll_nvml(self):
+        n = self.nvml
+        names = {"hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40, "sw_power_cap": 0x4}
+        while not self.done:
+            if self.active:
+                try:
+                    sm = n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)
+                    mx = n.nvmlDeviceGetMaxClockInfo(self.handle, n.NVML_CLOCK_SM)
+                    try:
+                        r = n.nvmlDeviceGetCurrentClocksEventReasons(self.handle)
+                    except Exception:
+                        r = n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+                    self.samples.append((float(sm), float(mx), [k for k, bit in names.items() if r & bit]))
+                except Exception:
+                    pass
+            time.sleep(0.05)
+
+    def _read(self):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for s in self.samples:
-            parts = [x.strip() for x in s.split(",")]
+        for line in self.proc.stdout:
+            if not self.active:
+                continue
+            parts = [x.strip() for x in line.strip().split(",")]
             if len(parts) < 6:
                 continue
             try:
-                sm.append(float(parts[0])); mx = float(parts[1])
+                self.samples.append((float(parts[0]), float(parts[1]),
+                                     [n for n, v in zip(names, parts[2:6]) if v.lower().startswith("active")]))
             except ValueError:
                 continue
-            for n, v in zip(names, parts[2:6]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
-                "samples": len(sm)}
+
+    def stop(self):
+        self.active, self.done = False, True
+        if self.proc is not None:
+            self.proc.terminate()
+        if self.source is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi / NVML unavailable"]}
+        sm = sorted(s[0] for s in self.samples)
+        reasons = sorted({r for s in self.samples for r in s[2]})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.samples[-1][1] if self.samples else None,
+                "reasons": reasons, "samples": len(sm), "source": self.source}
 
 
 # ------------------------------------------------------------------------------------------------------
@@ -302,10 +345,12 @@ def run_ours(args):
         return float(t.item()), last
 
     # warm-up (>= 3): also builds the weight packs / allocator pools
-    timed(max(args.warmup, 3), False)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    timed(max(args.warmup, 3), False)
+    if rank == 0:
+        sampler.begin()
     _lib.reset_launch_count()
     ms_total, _ = timed(args.steps, False)
     launches = _lib.launch_count()
@@ -357,7 +402,7 @@ def run_ours(args):
 BWD_KERNEL_MAC = (2560 + 1536) * 4096 + 131_072 + 2 * 912_000 + 2 * 172_800
 FWD_KERNEL_MAC = DEC_STEP_MAC - 86_016 - 165_888 - 4096 * 256 - 4096 * 1024 - 0   # minus prenet, projection, hoisted prenet/constant columns
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture (profiles/r1_ncu_decoder_full.md)
-NCU_TRAFFIC = {"decoder_fwd2_kernel": 6.93e9, "decoder_bwd2_kernel": 8.31e9}
+NCU_TRAFFIC = {"decoder_fwd2_kernel": 6.94e9, "decoder_bwd2_kernel": 7.48e9}   # profiles/r1_ncu_decoder_full.md, fourth capture
 
 
 def kernel_roofline(tr, batch, pk):
