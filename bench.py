@@ -53,7 +53,7 @@ def _peaks():
 
 
 class ClockSampler:
-    """SM clocks / throttle reasons sampled DURING the timed region (every 50 ms).
+    """SM clocks / throttle reasons sampled DURING the timed region (every 100 ms).
 
     NVML (the library behind nvidia-smi) is polled from a thread of this process; it is initialised and the thread is
     started BEFORE the warm-up, and samples are only kept between begin() and stop(): spawning `nvidia-smi -lms` at the
@@ -110,7 +110,7 @@ class ClockSampler:
                     self.samples.append((float(sm), float(mx), [k for k, bit in names.items() if r & bit]))
                 except Exception:
                     pass
-            time.sleep(0.05)
+            time.sleep(0.1)
 
     def _read(self):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
