@@ -359,7 +359,7 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
   for (int itb = 0; itb < niter; ++itb) {
     const int b = pair + itb * npairs;
     const bool active = b < p.B;
-    const int L = active ? (p.lengths ? min(p.lengths[b], Tin) : Tin) : 0;
+    const int L = active ? reinterpret_cast<const int*>(sm.scr + 48)[itb] : 0;   // staged once at kernel start
     const size_t tb = (size_t)t * p.B + b, bt = (size_t)b * p.T + t;
     const uint32_t xb = xround & 1u;
     ++xround;
@@ -391,13 +391,16 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
         *reinterpret_cast<uint4*>(im_lo + off) = make_uint4(0u, 0u, 0u, 0u);
       }
       // d w_j over this CTA's positions: one warp per position, lanes over the time-varying columns
-      for (int jl0 = warp; jl0 < jn; jl0 += 32) {
-        // four positions per warp in flight (rows jl0, +8, +16, +24): all loads first, then the reductions
-        float s[4] = {0.f, 0.f, 0.f, 0.f};
-        for (int d = lane * 8; d < E; d += 256) {
-          float mv[4][8];
+      constexpr int RD = 4;
+      for (int jl0 = warp; jl0 < jn; jl0 += 8 * RD) {
+        // RD positions per warp in flight (rows jl0, +8, ...): all loads first, then the reductions
+        float s[RD];
 #pragma unroll
-          for (int r = 0; r < 4; ++r) {
+        for (int r = 0; r < RD; ++r) s[r] = 0.f;
+        for (int d = lane * 8; d < E; d += 256) {
+          float mv[RD][8];
+#pragma unroll
+          for (int r = 0; r < RD; ++r) {
             const int j = j0 + jl0 + 8 * r;
             if (jl0 + 8 * r < jn && j < L) ld8b<MT>(mem + ((size_t)b * Tin + j) * E + d, mv[r]);
             else {
@@ -409,11 +412,11 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
           for (int e = 0; e < 8; ++e) {
             const float dc = sm.dctx_s[d + e];
 #pragma unroll
-            for (int r = 0; r < 4; ++r) s[r] += dc * mv[r][e];
+            for (int r = 0; r < RD; ++r) s[r] += dc * mv[r][e];
           }
         }
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
+        for (int r = 0; r < RD; ++r) {
           const float tot = warp_sum(s[r]);
           if (lane == 0 && jl0 + 8 * r < jn) sm.dw_s[j0 + jl0 + 8 * r] = tot;
         }
@@ -724,6 +727,11 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
       load_resident<N>(dec ? p.wT_dec2 : p.wT_att2, (long long)nkb * KB, dec ? R_dec : R_att, (dec ? cid : cid - nD) * TILE_M, kb0,
                        res_n, 0, tmem_base);
     }
+  }
+  if (threadIdx.x < 8) {
+    // encoder lengths of the sequences this CTA pair serves (constant for the launch; a global load per frame otherwise)
+    const int b = cid * 2 + (rank >> 1) + (int)threadIdx.x * ncl * 2;
+    reinterpret_cast<int*>(sm.scr + 48)[threadIdx.x] = b < p.B ? (p.lengths ? min(p.lengths[b], p.Tin) : p.Tin) : 0;
   }
   tc_fence_before();
   cluster_sync_all();

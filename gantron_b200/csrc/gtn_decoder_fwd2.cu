@@ -478,7 +478,7 @@ GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, in
   for (int it = 0; it < niter; ++it) {
     const int b = pair + it * npairs;
     const bool active = b < p.B;
-    const int L = active ? (p.lengths ? min(p.lengths[b], Tin) : Tin) : 0;
+    const int L = active ? reinterpret_cast<const int*>(sm.scr + 48)[it] : 0;   // sequence lengths: staged once at kernel start
     float* e_buf = sm.e_buf + (size_t)(eround & 1u) * TIN_MAX;
     ++eround;
     // this thread's slice of processed_memory (row = encoder position, 64 attention columns) does not depend on the frame's
@@ -748,6 +748,11 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
     sm.res_d = min((rank + 1) * nkd / CL - kd0, res_slots<N>() - sm.res_a);
     load_resident<N>(p.w_att2, (long long)nka * KB, 4 * p.Ha, cid * TILE_M, ka0, sm.res_a, 0, tmem_base);
     load_resident<N>(p.w_dec2, (long long)nkd * KB, 4 * p.Hd, cid * TILE_M, kd0, sm.res_d, sm.res_a, tmem_base);
+  }
+  if (threadIdx.x < 8) {
+    // encoder lengths of the sequences this CTA pair serves (constant for the launch; a global load per frame otherwise)
+    const int b = cid * 2 + (rank >> 1) + (int)threadIdx.x * ncl * 2;
+    reinterpret_cast<int*>(sm.scr + 48)[threadIdx.x] = b < p.B ? (p.lengths ? min(p.lengths[b], p.Tin) : p.Tin) : 0;
   }
   tc_fence_before();
   cluster_sync_all();     // peers' barriers / smem are initialised before any DSMEM traffic
