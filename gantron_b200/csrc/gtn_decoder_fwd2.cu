@@ -765,41 +765,34 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
   for (int u = 0; u < 32; ++u) wqr[u] = 0.f;
   const unsigned int nblocks = gridDim.x;
   int t = 0;
-  for (; t < p.n_steps; ++t) {
-    if (!p.train && p.B <= PRE_LOCAL_BMAX) {
+  // The GEMM phases of a frame go through ONE call site of gemm_phase (runtime `kind`): five specialised inlined copies made
+  // the per-frame code path larger than the instruction cache holds, and a phase that runs once per frame then runs cold.
+  const bool pre_local = !p.train && p.B <= PRE_LOCAL_BMAX;
+  const int k_first = (p.train || pre_local) ? K_ATT : K_PRE1, k_last = p.train ? K_DEC : K_PROJ;
+  bool stopped = false;
+  for (; t < p.n_steps && !stopped; ++t) {
+    if (pre_local) {
       PROF(28);
       prenet_local(p, sm, t, rank);
       PROF(31);
-    } else if (!p.train) {
-      PROF(28);
-      gemm_phase<N>(p, maps, sm, K_PRE1, t, rank, cid, ncl, tmem_base, acc_par, round, wqr);
-      PROF(29);
-      grid_sync2(p.barrier, epoch, nblocks);
-      PROF(30);
-      gemm_phase<N>(p, maps, sm, K_PRE2, t, rank, cid, ncl, tmem_base, acc_par, round, wqr);
-      PROF(31);
-      grid_sync2(p.barrier, epoch, nblocks);
     }
-    PROF(0);
-    gemm_phase<N>(p, maps, sm, K_ATT, t, rank, cid, ncl, tmem_base, acc_par, round, wqr);
-    PROF(4);
-    grid_sync2(p.barrier, epoch, nblocks);
-    PROF(5);
-    if (p.mem_bf16) attention_phase2<bf16>(p, sm, t, rank, cid, ncl, tmem_att, att_par, eround);
-    else attention_phase2<float>(p, sm, t, rank, cid, ncl, tmem_att, att_par, eround);
-    PROF(6);
-    grid_sync2(p.barrier, epoch, nblocks);
-    PROF(8);
-    gemm_phase<N>(p, maps, sm, K_DEC, t, rank, cid, ncl, tmem_base, acc_par, round, wqr);
-    PROF(13);
-    if (!p.train) {
+#pragma unroll 1
+    for (int kind = k_first; kind <= k_last; ++kind) {
+      if (kind == K_PRE1) PROF(28);
+      if (kind == K_ATT) PROF(0);
+      gemm_phase<N>(p, maps, sm, kind, t, rank, cid, ncl, tmem_base, acc_par, round, wqr);
+      PROF(kind == K_PRE1 ? 29 : (kind == K_PRE2 ? 31 : (kind == K_ATT ? 4 : (kind == K_DEC ? 13 : 19))));
+      if (kind == K_DEC && p.train) break;        // C(t) and A(t+1) share an interval: no barrier in between
       grid_sync2(p.barrier, epoch, nblocks);
-      PROF(18);
-      gemm_phase<N>(p, maps, sm, K_PROJ, t, rank, cid, ncl, tmem_base, acc_par, round, wqr);
-      PROF(19);
-      grid_sync2(p.barrier, epoch, nblocks);
-      PROF(23);
-      if (__ldcg(p.stop) != 0) { ++t; break; }
+      PROF(kind == K_PRE1 ? 30 : (kind == K_ATT ? 5 : (kind == K_DEC ? 18 : 23)));
+      if (kind == K_ATT) {
+        if (p.mem_bf16) attention_phase2<bf16>(p, sm, t, rank, cid, ncl, tmem_att, att_par, eround);
+        else attention_phase2<float>(p, sm, t, rank, cid, ncl, tmem_att, att_par, eround);
+        PROF(6);
+        grid_sync2(p.barrier, epoch, nblocks);
+        PROF(8);
+      }
+      if (kind == K_PROJ && __ldcg(p.stop) != 0) stopped = true;
     }
   }
   if (blockIdx.x == 0 && threadIdx.x == 0 && p.steps_done) *p.steps_done = t;
