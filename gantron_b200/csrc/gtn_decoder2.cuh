@@ -379,6 +379,68 @@ GTN_DEVICE void exchange_chunk(bool has_work, uint32_t tmem_acc, int c0, float* 
   tc_fence_after();
 }
 
+// Same exchange through the bulk-copy engine.  Individual st.shared::cluster stores move the 24 KB a CTA owes its peers at
+// ~10 B/clk, and the cluster barrier behind them adds ~1k cycles.  Here warps 4..7 drop the three peer-bound blocks into a
+// local staging area (plain st.shared), ONE thread sends each as a cp.async.bulk shared::cta -> shared::cluster copy that
+// signals the RECEIVER's mbarrier (complete_tx), and every thread waits on its own CTA's mbarrier: no cluster barrier.
+// recv / stage / full_bar alternate between two buffers from one exchange to the next, and stage is the buffer this CTA
+// received into one exchange earlier.  That is race-free without further synchronisation: peer q overwrites my
+// stage[q] block only in its NEXT exchange, which it enters after it has received this exchange's blocks (mine included, so
+// my copy out of stage[q] has completed); and I overwrite a peer's buffer only two exchanges after it was filled, which I
+// reach only after that peer has sent the exchange in between, i.e. after it finished reading.
+template <int CH>
+GTN_DEVICE void exchange_bulk(bool has_work, uint32_t tmem_acc, int c0, float* recv, float* stage, uint64_t* full_bar,
+                              uint32_t parity, int rank) {
+  constexpr int NC4 = CH / 4;
+  constexpr uint32_t BLK = (uint32_t)TILE_M * NC4 * 4;           // bytes of one [128 rows][NC4] block
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  __syncthreads();        // stage is the buffer the previous exchange's epilogue read: every warp is done with it
+  if (threadIdx.x == 0) mbar_expect_tx(full_bar, 3u * BLK);       // arm this exchange's receive (may trail the first bytes)
+  if (warp >= 4) {
+    const int wq = warp & 3;
+    const int row = wq * 32 + lane;
+#pragma unroll
+    for (int h = 0; h < CH / 32; ++h) {
+      uint32_t r[32];
+      if (has_work) {
+        tmem_ld_32x32(tmem_acc + ((uint32_t)(wq * 32) << 16) + (uint32_t)(c0 + h * 32), r);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) r[j] = 0u;
+      }
+#pragma unroll
+      for (int g = 0; g < 32 / NC4; ++g) {
+        const int dst = (h * 32 + g * NC4) / NC4;
+        float* blk = (dst == rank ? recv + (size_t)rank * TILE_M * NC4 : stage + (size_t)dst * TILE_M * NC4) + (size_t)row * NC4;
+#pragma unroll
+        for (int v = 0; v < NC4; v += 4)
+          *reinterpret_cast<float4*>(blk + (v ^ (((row >> 1) & (NC4 / 4 - 1)) << 2))) =
+              make_float4(__uint_as_float(r[g * NC4 + v]), __uint_as_float(r[g * NC4 + v + 1]),
+                          __uint_as_float(r[g * NC4 + v + 2]), __uint_as_float(r[g * NC4 + v + 3]));
+      }
+    }
+    fence_proxy_async_smem();                                     // staging writes -> bulk-copy (async proxy) reads
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (__shfl_sync(0xffffffffu, warp, 0) == 0) {
+    if (elect_one()) {
+#pragma unroll
+      for (int d = 1; d < CL; ++d) {
+        const uint32_t dst = (uint32_t)((rank + d) % CL);
+        asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(map_to_rank(smem_u32(recv + (size_t)rank * TILE_M * NC4), dst)),
+                       "r"(smem_u32(stage + (size_t)dst * TILE_M * NC4)), "r"(BLK), "r"(map_to_rank(smem_u32(full_bar), dst))
+                     : "memory");
+      }
+    }
+    __syncwarp();
+  }
+  wait_bar(full_bar, parity);
+  tc_fence_after();
+}
+
 // sum of the four partials of element (row, col) of this CTA's slice
 template <int NC4, bool SWZ = false>
 GTN_DEVICE float recv_sum(const float* recv, int row, int col) {

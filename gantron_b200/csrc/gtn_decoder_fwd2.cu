@@ -61,6 +61,7 @@ struct Smem2 {
   uint64_t* acc_full;
   uint64_t* att_full;
   uint64_t* u_full;
+  uint64_t* recv_full;  // [2] bulk-copy exchange: one per receive buffer
   uint32_t* tmem_slot;
   int res_a, res_d;    // weight k-blocks of this CTA's attention / decoder LSTM K quarter that are resident in TMEM
 };
@@ -106,6 +107,7 @@ GTN_DEVICE Smem2 carve2(uint8_t* base, int S) {
   m.acc_full = b++;
   m.att_full = b++;
   m.u_full = b++;
+  m.recv_full = b; b += 2;
   m.tmem_slot = reinterpret_cast<uint32_t*>(b + 1);
   return m;
 }
@@ -219,7 +221,12 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
           }
         }
       }
-      exchange_chunk<CH, true>(has_work, tmem_base, c0, recv, rank);
+      {
+        // (`round` was advanced when recv was picked: this exchange is number round - 1)
+        const uint32_t xr = round - 1u;
+        float* stage = sm.recv + (size_t)((xr & 1u) ^ 1u) * 4 * TILE_M * NC4;
+        exchange_bulk<CH>(has_work, tmem_base, c0, recv, stage, &sm.recv_full[xr & 1u], (xr >> 1) & 1u, rank);
+      }
       PROF(ps + 2);                              // DSMEM exchange + cluster barrier done
       if (is_lstm) {
         const float pdrop = is_att ? p.p_att : p.p_dec;
@@ -723,6 +730,8 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
     mbar_init(sm.acc_full, 1);
     mbar_init(sm.att_full, 1);
     mbar_init(sm.u_full, 1);
+    mbar_init(&sm.recv_full[0], 1);
+    mbar_init(&sm.recv_full[1], 1);
     mbar_fence_init();
   }
   if (warp == 2) tmem_alloc(sm.tmem_slot, 512);
