@@ -68,6 +68,7 @@ struct SmemB {
   uint64_t* acc_full;
   uint64_t* g_full;
   uint64_t* ut_full;
+  uint64_t* recv_full;  // [2] bulk-copy exchange: one per receive buffer
   uint32_t* tmem_slot;
 };
 
@@ -115,6 +116,7 @@ GTN_DEVICE SmemB carveB(uint8_t* base, int S) {
   m.acc_full = b++;
   m.g_full = b++;
   m.ut_full = b++;
+  m.recv_full = b; b += 2;
   m.tmem_slot = reinterpret_cast<uint32_t*>(b + 1);
   return m;
 }
@@ -229,9 +231,18 @@ GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, 
     if (has_work) acc_par ^= 1u;
     for (int c0 = 0; c0 < N; c0 += CH) {
       float* recv = sm.recv + (size_t)(N > 64 ? (round & 1u) : 0u) * 4 * TILE_M * NC4;
-      ++round;
       const int bbase = c0 + rank * NC4;
-      exchange_chunk<CH, true>(has_work, tmem_base, c0, recv, rank);
+      if (N > 64) {
+        // two receive buffers: the other one is the staging area (see exchange_bulk)
+        exchange_bulk<CH>(has_work, tmem_base, c0, recv, sm.recv + (size_t)((round & 1u) ^ 1u) * 4 * TILE_M * NC4,
+                          &sm.recv_full[round & 1u], (round >> 1) & 1u, rank);
+      } else if (nD + nA <= ncl) {
+        // one receive buffer, one exchange per frame with grid barriers in between: stage in the (idle) TMA ring
+        exchange_bulk<CH>(has_work, tmem_base, c0, recv, reinterpret_cast<float*>(sm.ring.base), &sm.recv_full[0], round & 1u, rank);
+      } else {
+        exchange_chunk<CH, true>(has_work, tmem_base, c0, recv, rank);
+      }
+      ++round;
       PROFB(3);
       for (int idx = threadIdx.x; idx < TILE_M * NC4; idx += blockDim.x) {
         const int r = idx % TILE_M, bl = idx / TILE_M, b = bbase + bl, row = row0 + r;
@@ -697,6 +708,8 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
     mbar_init(sm.acc_full, 1);
     mbar_init(sm.g_full, 1);
     mbar_init(sm.ut_full, 1);
+    mbar_init(&sm.recv_full[0], 1);
+    mbar_init(&sm.recv_full[1], 1);
     mbar_fence_init();
   }
   if (warp == 2) tmem_alloc(sm.tmem_slot, 512);
