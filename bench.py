@@ -55,10 +55,9 @@ def _peaks():
 class ClockSampler:
     """SM clocks / throttle reasons sampled DURING the timed region (every 100 ms).
 
-    NVML (the library behind nvidia-smi) is polled from a thread of this process; it is initialised and the thread is
-    started BEFORE the warm-up, and samples are only kept between begin() and stop(): spawning `nvidia-smi -lms` at the
-    start of the timed region costs the region the tool's start-up (NVML / driver initialisation, seen as a 25 % slower
-    step on a busy host).  Falls back to an `nvidia-smi -lms 100` subprocess (also started before the warm-up)."""
+    An `nvidia-smi -lms 100` process is started BEFORE the warm-up and its samples are only kept between begin() and stop():
+    spawning it at the start of the timed region costs the region the tool's start-up (NVML / driver initialisation, seen
+    as a 25 % slower step on a busy host).  Falls back to polling NVML from a thread of this process."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -67,6 +66,17 @@ class ClockSampler:
         self.active, self.done, self.source = False, False, None
 
     def start(self):
+        # preferred: a separate nvidia-smi process (its NVML polling shares neither the GIL nor this process's driver
+        # locks with the launch loop: the in-process NVML thread made the timed region 2-15 % slower than the e2e leg)
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.source = "nvidia-smi"
+            threading.Thread(target=self._read, daemon=True).start()
+            return
+        except Exception:
+            self.proc = None
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -80,17 +90,8 @@ class ClockSampler:
             self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
             self.nvml, self.source = pynvml, "nvml"
             threading.Thread(target=self._poll_nvml, daemon=True).start()
-            return
         except Exception:
             self.nvml = None
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
-                                         stderr=subprocess.DEVNULL, text=True)
-            self.source = "nvidia-smi"
-            threading.Thread(target=self._read, daemon=True).start()
-        except Exception:
-            self.proc = None
 
     def begin(self):
         self.samples, self.active = [], True
@@ -402,7 +403,7 @@ def run_ours(args):
 BWD_KERNEL_MAC = (2560 + 1536) * 4096 + 131_072 + 2 * 912_000 + 2 * 172_800
 FWD_KERNEL_MAC = DEC_STEP_MAC - 86_016 - 165_888 - 4096 * 256 - 4096 * 1024 - 0   # minus prenet, projection, hoisted prenet/constant columns
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture (profiles/r1_ncu_decoder_full.md)
-NCU_TRAFFIC = {"decoder_fwd2_kernel": 6.94e9, "decoder_bwd2_kernel": 7.48e9}   # profiles/r1_ncu_decoder_full.md, fourth capture
+NCU_TRAFFIC = {"decoder_fwd2_kernel": 6.90e9, "decoder_bwd2_kernel": 7.48e9}   # profiles/r1_ncu_decoder_full.md, fifth capture
 
 
 def kernel_roofline(tr, batch, pk):
