@@ -60,11 +60,11 @@ struct SmemB {
   float* halo_s;       // [2][2][KS]         halo contributions received from the peer
   float* v_s;          // [128]
   float* part_s;       // [8][64]
-  float* dqp_s;        // [2][128]           dq partial: own, peer
+  float* dqp_s;        // [4][128]           dq partials of the cluster's two sequences, slot = source rank
   float* dv_acc;       // [128]
   float* dot_s;        // [4]                softmax dot partial: own, peer (double buffered)
   float* scr;          // [64]
-  float* dqf_s;        // [128]  full d query of the current sequence (cell backward)
+  float* dqf_s;        // [2][128]  full d query of the cluster's two sequences (cell backward)
   uint64_t* acc_full;
   uint64_t* g_full;
   uint64_t* ut_full;
@@ -79,7 +79,7 @@ __host__ __device__ constexpr size_t bwd2_fixed_bytes() {
   // 32 KB saved buys two more TMA stages; N > 64: back-to-back chunk exchanges need the double buffer
   constexpr size_t recv_b = (size_t)(N > 64 ? 2 : 1) * 4 * TILE_M * NC4 * 4;
   return (recv_b < 32768 ? 32768 : recv_b) + 4 * 8192 +
-         (size_t)(1024 + 2 * B2_TIN_MAX + 4 * (B2_JH + 62) + 4 * 32 + 128 + 8 * 64 + 256 + 128 + 4 + 64 + 128) * 4 + 64 * 8 + 64;
+         (size_t)(1024 + 2 * B2_TIN_MAX + 4 * (B2_JH + 62) + 4 * 32 + 128 + 8 * 64 + 512 + 128 + 4 + 64 + 256) * 4 + 64 * 8 + 64;
 }
 
 template <int N>
@@ -105,11 +105,11 @@ GTN_DEVICE SmemB carveB(uint8_t* base, int S) {
   m.halo_s = f; f += 4 * 32;
   m.v_s = f; f += 128;
   m.part_s = f; f += 8 * 64;
-  m.dqp_s = f; f += 256;
+  m.dqp_s = f; f += 512;
   m.dv_acc = f; f += 128;
   m.dot_s = f; f += 4;
   m.scr = f; f += 64;
-  m.dqf_s = f; f += 128;
+  m.dqf_s = f; f += 256;
   uint64_t* b = reinterpret_cast<uint64_t*>(f);
   m.ring.full = b; b += 16;
   m.ring.empty = b; b += 16;
@@ -262,24 +262,33 @@ GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, 
 }
 
 // ------------------------------------------------------------------------------------------------
-// Cell backward of ONE sequence, run by the CTA pair that owns the sequence right after its attention backward
-// (this used to be a third, unit-sliced phase behind a grid barrier; per sequence it needs no other CTA's results):
+// Cell backward of the cluster's TWO sequences, run right after their attention backward (this used to be a third,
+// unit-sliced phase behind a grid barrier; per sequence it needs no other cluster's results):
 //   * attention LSTM cell of frame t:     dh = Wq^T dq + dha_dec + carry_ha                   (model.py:391-394, 62)
 //   * decoder LSTM cell of frame t - 1:   dh = dhd_rec (P1 of this frame) + dproj(t-1)         (model.py:404-409)
-// CTA `half` of the pair takes one half of the hidden units; a thread owns two ADJACENT units, so every save / gradient
-// access of a warp is one contiguous 128..512-byte run.  Wq ([A][Ha], bf16 in bf16 mode) streams from L2: 128 coalesced
-// 4-byte loads per thread against the full dq of the sequence held in shared memory.
+// A thread owns two ADJACENT units, so every save / gradient access of a warp is one contiguous 128..512-byte run.
+// Wq ([A][Ha], bf16 in bf16 mode) streams from L2 against the d query of both sequences held in shared memory.
 // ------------------------------------------------------------------------------------------------
-GTN_DEVICE void pair_cells(const DecBwd2& p, const float* dqf, int t, int it, int b, int half) {
+// Work split over the whole CLUSTER: rank r takes quarter r of the hidden units for BOTH sequences of the cluster, so
+// that a Wq value fetched from L2 is used for two sequences (the Wq stream is the largest single item of the phase:
+// 128 KB per CTA per frame through a ~30 B/clk port; 64 KB this way).  Thread = (unit pair pr, half h): during the Wq
+// product h selects the half of the attention dimension (both sequences), partial sums meet in shared memory, and for the
+// cell arithmetic h selects the sequence.  dq2 = [2][128] full d query of the two sequences, part = [2][2][128][2] scratch.
+GTN_DEVICE void quad_cells(const DecBwd2& p, const float* dq2, float* part, int t, int it, int b0, int b1, int rank) {
   const int nxt = (it & 1) ^ 1;
   bf16* xnext_d = BFP(p.xdg_d) + (size_t)nxt * p.B * p.mult * 4 * p.Hd;
-  const int Hh_a = ((p.Ha / 2 + 1) / 2) * 2, ua_end = min(p.Ha, (half + 1) * Hh_a);
-  const int Hh_d = ((p.Hd / 2 + 1) / 2) * 2, ud_end = min(p.Hd, (half + 1) * Hh_d);
-  const int na = (ua_end - half * Hh_a + 511) / 512, nd = t > 0 ? (ud_end - half * Hh_d + 511) / 512 : 0;
+  const int Hq_a = ((p.Ha / CL + 1) / 2) * 2, ua_beg = rank * Hq_a, ua_end = min(p.Ha, (rank + 1) * Hq_a);
+  const int Hq_d = ((p.Hd / CL + 1) / 2) * 2, ud_beg = rank * Hq_d, ud_end = min(p.Hd, (rank + 1) * Hq_d);
+  const int na = (max(ua_end - ua_beg, 0) + 255) / 256, nd = t > 0 ? (max(ud_end - ud_beg, 0) + 255) / 256 : 0;
+  const int pr = threadIdx.x & 127, h = threadIdx.x >> 7;
+  const int b = h == 0 ? b0 : b1;
+  const bool seq_ok = b < p.B;
+  const int A2 = p.A / 2, a_lo = h * A2;
   for (int rd = 0; rd < max(na, nd); ++rd) {
-    const int ua = half * Hh_a + rd * 512 + 2 * threadIdx.x;
-    const int ud = half * Hh_d + rd * 512 + 2 * threadIdx.x;
-    const bool oka = rd < na && ua < ua_end, okd = rd < nd && ud < ud_end;
+    const int ua = ua_beg + rd * 256 + 2 * pr;
+    const int ud = ud_beg + rd * 256 + 2 * pr;
+    const bool oka_u = rd < na && ua < ua_end;                       // unit pair exists (Wq product: both sequences)
+    const bool oka = oka_u && seq_ok, okd = rd < nd && ud < ud_end && seq_ok;
     CellIn ca[2], cd[2];
     float2 adda = make_float2(0.f, 0.f), addd = make_float2(0.f, 0.f);
     if (okd) {
@@ -289,35 +298,47 @@ GTN_DEVICE void pair_cells(const DecBwd2& p, const float* dqf, int t, int it, in
       const float* q = p.dproj_all + ((size_t)(t - 1) * p.B + b) * (p.Hd + p.D) + ud;     // row stride Hd + D may be odd
       addd = make_float2(r.x + __ldg(q), r.y + __ldg(q + 1));
     }
-    float s0 = 0.f, s1 = 0.f;
     if (oka) {
       ca[0] = cell_load(p, t, b, ua, p.Ha, p.gates_a, p.c_a_all, p.dc_a);
       ca[1] = cell_load(p, t, b, ua + 1, p.Ha, p.gates_a, p.c_a_all, p.dc_a);
       const size_t ci = (size_t)b * p.Ha + ua;
       const float2 x = __ldcg(reinterpret_cast<const float2*>(p.dha_dec + ci)), y = __ldcg(reinterpret_cast<const float2*>(p.carry_ha + ci));
       adda = make_float2(x.x + y.x, x.y + y.y);
+    }
+    // Wq^T dq over this thread's half of the attention dimension, for both sequences
+    float s00 = 0.f, s01 = 0.f, s10 = 0.f, s11 = 0.f;                // [sequence][unit of the pair]
+    if (oka_u) {
+      const float* d0 = dq2 + a_lo;
+      const float* d1 = dq2 + 128 + a_lo;
+      const int ld = p.Ha >> 1;
       if (p.prec == 1) {
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(p.wq_au) + (ua >> 1);
-        const int ld = p.Ha >> 1;
-        float t0 = 0.f, t1 = 0.f;
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(p.wq_au) + (size_t)a_lo * ld + (ua >> 1);
+        // (16 rows in flight; 32 measured slower, like every other attempt to deepen the load queues of these phases)
 #pragma unroll 16
-        for (int a = 0; a < p.A; a += 2) {
-          const uint32_t w0 = __ldg(w + (size_t)a * ld), w1 = __ldg(w + (size_t)(a + 1) * ld);
-          const float d0 = dqf[a], d1 = dqf[a + 1];
-          s0 += __uint_as_float(w0 << 16) * d0; s1 += __uint_as_float(w0 & 0xFFFF0000u) * d0;
-          t0 += __uint_as_float(w1 << 16) * d1; t1 += __uint_as_float(w1 & 0xFFFF0000u) * d1;
+        for (int a = 0; a < A2; ++a) {
+          const uint32_t wv = __ldg(w + (size_t)a * ld);
+          const float w0 = __uint_as_float(wv << 16), w1 = __uint_as_float(wv & 0xFFFF0000u);
+          s00 += w0 * d0[a]; s01 += w1 * d0[a];
+          s10 += w0 * d1[a]; s11 += w1 * d1[a];
         }
-        s0 += t0; s1 += t1;
       } else {
-        const float2* w = reinterpret_cast<const float2*>(p.wq_au) + (ua >> 1);
-        const int ld = p.Ha >> 1;
+        const float2* w = reinterpret_cast<const float2*>(p.wq_au) + (size_t)a_lo * ld + (ua >> 1);
 #pragma unroll 8
-        for (int a = 0; a < p.A; ++a) {
+        for (int a = 0; a < A2; ++a) {
           const float2 wv = __ldg(w + (size_t)a * ld);
-          s0 += wv.x * dqf[a]; s1 += wv.y * dqf[a];
+          s00 += wv.x * d0[a]; s01 += wv.y * d0[a];
+          s10 += wv.x * d1[a]; s11 += wv.y * d1[a];
         }
       }
     }
+    // part[h][seq][pr] (float2): this thread's half-sums for both sequences
+    __syncthreads();                                                 // previous round's readers are done
+    reinterpret_cast<float2*>(part)[(h * 2 + 0) * 128 + pr] = make_float2(s00, s01);
+    reinterpret_cast<float2*>(part)[(h * 2 + 1) * 128 + pr] = make_float2(s10, s11);
+    __syncthreads();
+    const float2 h0 = reinterpret_cast<const float2*>(part)[(0 * 2 + h) * 128 + pr];
+    const float2 h1 = reinterpret_cast<const float2*>(part)[(1 * 2 + h) * 128 + pr];
+    const float s0 = h0.x + h1.x, s1 = h0.y + h1.y;                  // sequence h, units ua, ua + 1
     if (okd) {
       cell_apply(p, cd[0], t - 1, b, ud, p.Hd, addd.x, p.dc_d, p.dgd_all, xnext_d, 4u, p.thr_dec, p.p_dec);
       cell_apply(p, cd[1], t - 1, b, ud + 1, p.Hd, addd.y, p.dc_d, p.dgd_all, xnext_d, 4u, p.thr_dec, p.p_dec);
@@ -530,8 +551,9 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
 #pragma unroll
         for (int w = 0; w < 4; ++w) dvv += sm.part_s[w * 128 + a];
         sm.dv_acc[a] += dvv;
-        sm.dqp_s[a] = dqv;               // own partial (slot 0); the peer's lands in slot 1 (dqp_s + 128)
-        st_cluster_f1(map_to_rank(smem_u32(&sm.dqp_s[128 + a]), (uint32_t)peer), dqv);
+        // every CTA of the cluster receives every partial (slot = source rank): the cell backward is split over the cluster
+#pragma unroll
+        for (int r = 0; r < CL; ++r) st_cluster_f1(map_to_rank(smem_u32(&sm.dqp_s[rank * 128 + a]), (uint32_t)r), dqv);
       }
     }
     __syncthreads();
@@ -637,15 +659,20 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
         if (ch == 0) p.dwprev[(size_t)b * p.ldT + j] = s;
         else p.dcum[(size_t)b * p.ldT + j] += s;
       }
-      for (int a = threadIdx.x; a < 128; a += blockDim.x) {
-        const float s = a < A ? sm.dqp_s[a] + ((Tin > JH) ? sm.dqp_s[128 + a] : 0.f) : 0.f;
-        sm.dqf_s[a] = s;                                     // full d query of the sequence, both CTAs of the pair
-        if (half == 0 && a < A) p.dq_all[tb * A + a] = s;
-      }
+    }
+    {
+      // full d query of BOTH sequences of the cluster (pair 0: ranks 0, 1; pair 1: ranks 2, 3); the pair's first CTA saves its own
+      const int sq = threadIdx.x >> 7, a = threadIdx.x & 127;
+      const float s = a < A ? sm.dqp_s[(2 * sq) * 128 + a] + ((Tin > JH) ? sm.dqp_s[(2 * sq + 1) * 128 + a] : 0.f) : 0.f;
+      sm.dqf_s[sq * 128 + a] = s;
+      if (active && half == 0 && sq == (rank >> 1) && a < A) p.dq_all[tb * A + a] = s;
     }
     __syncthreads();
     PROFB(19);
-    if (active) pair_cells(p, sm.dqf_s, t, it, b, half);
+    {
+      const int b0 = cid * 2 + itb * npairs, b1 = b0 + 1;
+      if (b0 < p.B) quad_cells(p, sm.dqf_s, sm.dctx_s, t, it, b0, b1, rank);
+    }
     __syncthreads();
   }
 }
