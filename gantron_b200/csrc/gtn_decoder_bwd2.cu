@@ -121,6 +121,10 @@ GTN_DEVICE SmemB carveB(uint8_t* base, int S) {
   return m;
 }
 
+GTN_DEVICE void red_add_f2(float* addr, float a, float b) {
+  asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(a), "f"(b) : "memory");
+}
+
 GTN_DEVICE float block_sum2(float v, float* scr) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   v = warp_sum(v);
@@ -501,7 +505,7 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
       for (int jb = rg; jb < TILE_M; jb += 32) {
         // eight rows per trip (jb, jb + 4, ..., jb + 28): all of their loads are issued before any is consumed
         constexpr int RW = 8;
-        float2 th[RW], dp[RW];
+        float2 th[RW];
         float de[RW];
         bool ok[RW];
 #pragma unroll
@@ -509,11 +513,9 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
           const int jl = jb + 4 * r, j = j0 + jl;
           ok[r] = a_ok && jl < jn && j < L;
           th[r] = make_float2(0.f, 0.f);
-          dp[r] = make_float2(0.f, 0.f);
           de[r] = 0.f;
           if (ok[r]) {
             th[r] = __ldg(reinterpret_cast<const float2*>(p.th_all + ((tb * Tin + j) * A + ap)));
-            dp[r] = *reinterpret_cast<const float2*>(p.dpm + (((size_t)b * Tin + j) * A + ap));
             de[r] = sm.dw_s[j];
           }
         }
@@ -521,8 +523,9 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
         for (int r = 0; r < RW; ++r) {
           const int jl = jb + 4 * r;
           const float d0 = de[r] * v0 * (1.f - th[r].x * th[r].x), d1 = de[r] * v1 * (1.f - th[r].y * th[r].y);
-          if (ok[r])
-            *reinterpret_cast<float2*>(p.dpm + (((size_t)b * Tin + (j0 + jl)) * A + ap)) = make_float2(dp[r].x + d0, dp[r].y + d1);
+          // d processed_memory accumulates over the frames: a fire-and-forget L2 reduction instead of load + add + store
+          // (this thread is the only writer of the address, frames are ordered by the grid barriers: same sums, no read)
+          if (ok[r]) red_add_f2(p.dpm + (((size_t)b * Tin + (j0 + jl)) * A + ap), d0, d1);
           dq0 += d0; dq1 += d1;
           dv0 += de[r] * th[r].x; dv1 += de[r] * th[r].y;
           const float h0 = bf16_round(d0), h1 = bf16_round(d1);
