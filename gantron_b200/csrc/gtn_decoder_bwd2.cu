@@ -184,6 +184,44 @@ GTN_DEVICE void cell_apply(const DecBwd2& p, const CellIn& in, int t, int b, int
   store_act(xr, 2 * H + unit, 4 * H, p.prec, dgg);
   store_act(xr, 3 * H + unit, 4 * H, p.prec, dgo);
 }
+// Two ADJACENT units (unit even) at once: in bf16 mode the eight bf16 saves / GEMM operands of the pair go out as four + four
+// 32-bit stores instead of sixteen 16-bit ones, and the carried dc as one float2.
+struct CellGrad { float dgi, dgf, dgg, dgo, dcn; };
+GTN_DEVICE CellGrad cell_math(const DecBwd2& p, const CellIn& in, int t, size_t ci, float dh, unsigned site, unsigned thr,
+                              float pdrop) {
+  if (p.use_dropout && thr != 0u) {
+    const uint32_t bits = philox_bits(p.seed, site, (uint32_t)t, (uint32_t)ci);
+    dh = bits >= thr ? dh * (1.0f / (1.0f - pdrop)) : 0.f;
+  }
+  const float4 g = in.g;
+  const float tc = p.prec == 1 ? tanh_fast(in.c) : tanh_acc(in.c);
+  const float d_o = dh * tc;
+  const float dc = dh * g.w * (1.f - tc * tc) + in.dc;
+  CellGrad r;
+  r.dcn = dc * g.y;
+  r.dgi = dc * g.z * g.x * (1.f - g.x);
+  r.dgf = dc * in.cprev * g.y * (1.f - g.y);
+  r.dgg = dc * g.x * (1.f - g.z * g.z);
+  r.dgo = d_o * g.w * (1.f - g.w);
+  return r;
+}
+GTN_DEVICE void cell_apply2(const DecBwd2& p, const CellIn (&in)[2], int t, int b, int unit, int H, float dh0, float dh1,
+                            float* dc_carry, float* dg_all, bf16* xdg, unsigned site, unsigned thr, float pdrop) {
+  if (!(p.prec == 1 && (p.flags & 2))) {          // fp32 mode: per-unit path (three planes per operand)
+    cell_apply(p, in[0], t, b, unit, H, dh0, dc_carry, dg_all, xdg, site, thr, pdrop);
+    cell_apply(p, in[1], t, b, unit + 1, H, dh1, dc_carry, dg_all, xdg, site, thr, pdrop);
+    return;
+  }
+  const size_t ci = (size_t)b * H + unit;
+  const CellGrad a = cell_math(p, in[0], t, ci, dh0, site, thr, pdrop), c = cell_math(p, in[1], t, ci + 1, dh1, site, thr, pdrop);
+  *reinterpret_cast<float2*>(dc_carry + ci) = make_float2(a.dcn, c.dcn);
+  const uint32_t pi = pack_bf16x2(a.dgi, c.dgi), pf = pack_bf16x2(a.dgf, c.dgf), pg = pack_bf16x2(a.dgg, c.dgg),
+                 po = pack_bf16x2(a.dgo, c.dgo);
+  uint32_t* dgb = reinterpret_cast<uint32_t*>(reinterpret_cast<bf16*>(dg_all) + ((size_t)t * p.B + b) * 4 * H + unit);
+  dgb[0] = pi; dgb[H >> 1] = pf; dgb[H] = pg; dgb[3 * (H >> 1)] = po;
+  uint32_t* xr = reinterpret_cast<uint32_t*>(xdg + (size_t)b * 4 * H + unit);
+  xr[0] = pi; xr[H >> 1] = pf; xr[H] = pg; xr[3 * (H >> 1)] = po;
+}
 GTN_DEVICE void cell_backward2(const DecBwd2& p, int t, int b, int unit, int H, float dh, const float* gates_all,
                                const float* c_all, float* dc_carry, float* dg_all, bf16* xdg, unsigned site, unsigned thr,
                                float pdrop) {
@@ -344,12 +382,10 @@ GTN_DEVICE void quad_cells(const DecBwd2& p, const float* dq2, float* part, int 
     const float2 h1 = reinterpret_cast<const float2*>(part)[(1 * 2 + h) * 128 + pr];
     const float s0 = h0.x + h1.x, s1 = h0.y + h1.y;                  // sequence h, units ua, ua + 1
     if (okd) {
-      cell_apply(p, cd[0], t - 1, b, ud, p.Hd, addd.x, p.dc_d, p.dgd_all, xnext_d, 4u, p.thr_dec, p.p_dec);
-      cell_apply(p, cd[1], t - 1, b, ud + 1, p.Hd, addd.y, p.dc_d, p.dgd_all, xnext_d, 4u, p.thr_dec, p.p_dec);
+      cell_apply2(p, cd, t - 1, b, ud, p.Hd, addd.x, addd.y, p.dc_d, p.dgd_all, xnext_d, 4u, p.thr_dec, p.p_dec);
     }
     if (oka) {
-      cell_apply(p, ca[0], t, b, ua, p.Ha, s0 + adda.x, p.dc_a, p.dga_all, BFP(p.xdg_a), 3u, p.thr_att, p.p_att);
-      cell_apply(p, ca[1], t, b, ua + 1, p.Ha, s1 + adda.y, p.dc_a, p.dga_all, BFP(p.xdg_a), 3u, p.thr_att, p.p_att);
+      cell_apply2(p, ca, t, b, ua, p.Ha, s0 + adda.x, s1 + adda.y, p.dc_a, p.dga_all, BFP(p.xdg_a), 3u, p.thr_att, p.p_att);
     }
   }
 }
