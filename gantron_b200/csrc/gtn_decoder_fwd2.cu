@@ -243,14 +243,19 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
           const int ul = idx & 31, bl = idx >> 5, b = bbase + bl, unit = tile * 32 + ul;
           float h = 0.f;
           if (b < p.B) {
-            const float i_ = sigmoid_acc(recv_sum<NC4, true>(recv, ul, bl) + gb[q].x);
-            const float f_ = sigmoid_acc(recv_sum<NC4, true>(recv, 32 + ul, bl) + gb[q].y);
-            const float g_ = tanh_acc(recv_sum<NC4, true>(recv, 64 + ul, bl) + gb[q].z);
-            const float o_ = sigmoid_acc(recv_sum<NC4, true>(recv, 96 + ul, bl) + gb[q].w);
+            // bf16 mode: hardware tanh (tanh.approx, rel. error ~2^-11, below the bf16 rounding of every operand; the energies
+            // and the backward's tanh(c) use it too); fp32 mode: libm
+            const bool fast = p.prec == 1;
+            const float zi = recv_sum<NC4, true>(recv, ul, bl) + gb[q].x, zf = recv_sum<NC4, true>(recv, 32 + ul, bl) + gb[q].y;
+            const float zg = recv_sum<NC4, true>(recv, 64 + ul, bl) + gb[q].z, zo = recv_sum<NC4, true>(recv, 96 + ul, bl) + gb[q].w;
+            const float i_ = fast ? 0.5f * tanh_fast(0.5f * zi) + 0.5f : sigmoid_acc(zi);
+            const float f_ = fast ? 0.5f * tanh_fast(0.5f * zf) + 0.5f : sigmoid_acc(zf);
+            const float g_ = fast ? tanh_fast(zg) : tanh_acc(zg);
+            const float o_ = fast ? 0.5f * tanh_fast(0.5f * zo) + 0.5f : sigmoid_acc(zo);
             const size_t ci = (size_t)b * H + unit;
             const float c_new = f_ * cprev[q] + i_ * g_;
             cst[ci] = c_new;
-            h = o_ * tanh_acc(c_new);
+            h = o_ * (fast ? tanh_fast(c_new) : tanh_acc(c_new));
             if (p.use_dropout && thr != 0u) {
               const uint32_t bits = philox_bits(p.seed, site, (uint32_t)t, (uint32_t)ci);
               h = bits >= thr ? h * dscale : 0.f;
