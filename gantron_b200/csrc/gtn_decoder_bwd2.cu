@@ -541,6 +541,16 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
       for (int jb = rg; jb < TILE_M; jb += 32) {
         // eight rows per trip (jb, jb + 4, ..., jb + 28): all of their loads are issued before any is consumed
         constexpr int RW = 8;
+        if (jb >= jn) {
+          // a whole trip beyond this CTA's positions (warp-uniform): the tile rows only need their zeros
+#pragma unroll
+          for (int r = 0; r < RW; ++r) {
+            const uint32_t off = toff + sw128_off(jb + 4 * r, chunk);
+            *reinterpret_cast<uint32_t*>(dth_hi + off) = 0u;
+            *reinterpret_cast<uint32_t*>(dth_lo + off) = 0u;
+          }
+          continue;
+        }
         float2 th[RW];
         float de[RW];
         bool ok[RW];
