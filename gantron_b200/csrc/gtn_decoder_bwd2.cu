@@ -355,10 +355,12 @@ GTN_DEVICE void quad_cells(const DecBwd2& p, const float* dq2, float* part, int 
       const int ld = p.Ha >> 1;
       if (p.prec == 1) {
         const uint32_t* w = reinterpret_cast<const uint32_t*>(p.wq_au) + (size_t)a_lo * ld + (ua >> 1);
-        // (16 rows in flight; 32 measured slower, like every other attempt to deepen the load queues of these phases)
-#pragma unroll 16
+#pragma unroll 32
         for (int a = 0; a < A2; ++a) {
-          const uint32_t wv = __ldg(w + (size_t)a * ld);
+          // 32 rows in flight, WITHOUT L1 allocation: with allocating loads (__ldg) 32 in flight ran slower than 16 (the ~28 KB
+          // of L1 left beside the shared-memory carve-out cannot hold 8 warps x 32 lines)
+          uint32_t wv;
+          asm volatile("ld.global.nc.L1::no_allocate.b32 %0, [%1];" : "=r"(wv) : "l"(w + (size_t)a * ld));
           const float w0 = __uint_as_float(wv << 16), w1 = __uint_as_float(wv & 0xFFFF0000u);
           s00 += w0 * d0[a]; s01 += w1 * d0[a];
           s10 += w0 * d1[a]; s11 += w1 * d1[a];
