@@ -75,6 +75,7 @@ class GradientAllReducer:
         if cur:
             self.buckets.append(_Bucket(cur))
         self._callback_queued = False
+        self._task_id = None             # autograd graph-task id of the backward pass the bucket state belongs to
         self.launched_early = 0          # buckets whose all-reduce started before backward finished (overlap evidence)
         self._hooks = []
         for b in self.buckets:
@@ -82,14 +83,17 @@ class GradientAllReducer:
                 self._hooks.append(p.register_post_accumulate_grad_hook(self._make_hook(b, i)))
 
     # ---- start-up ------------------------------------------------------------------------------
+    @torch.no_grad()
     def _broadcast_state(self):
-        tensors = [p.data for p in self.module.parameters()]
-        tensors += [b.data for b in self.module.buffers() if b.is_floating_point()]
+        # copy INTO the Parameters / buffers themselves (not through `.data`): the in-place copy bumps their version
+        # counters, which is what invalidates the kernels' bf16 weight packs (decoder_ops.PackedDecoder.stale)
+        tensors = list(self.module.parameters())
+        tensors += [b for b in self.module.buffers() if b.is_floating_point()]
         by_key = {}
         for t in tensors:
             by_key.setdefault((t.device, t.dtype), []).append(t)
         for ts in by_key.values():
-            flat = torch.cat([t.reshape(-1) for t in ts])
+            flat = torch.cat([t.detach().reshape(-1) for t in ts])
             dist.broadcast(flat, 0, group=self.group)
             off = 0
             for t in ts:
@@ -102,6 +106,14 @@ class GradientAllReducer:
             g = param.grad
             if g is None:
                 return
+            tid = torch._C._current_graph_task_id()
+            if tid != self._task_id:
+                # first gradient of a NEW backward pass.  If the previous pass raised before the engine ran its final
+                # callbacks, its bucket state (ready flags, launched reductions, the queued flag) is still around: drop it,
+                # or no later pass would ever queue _finalize again and the ranks would silently diverge.
+                if self._callback_queued or any(b.n_ready or b.work is not None for b in self.buckets):
+                    self._abandon()
+                self._task_id = tid
             view = bucket.views[idx]
             if g.data_ptr() != view.data_ptr():
                 torch.mul(g, self.inv_world, out=view)     # scale while moving into the bucket slot
@@ -122,6 +134,7 @@ class GradientAllReducer:
     # ---- end of backward -----------------------------------------------------------------------
     def _finalize(self):
         self._callback_queued = False
+        self._task_id = None
         for b in self.buckets:
             if b.n_ready == 0:
                 continue                                   # e.g. the frozen Discriminator during a generator step
@@ -136,6 +149,17 @@ class GradientAllReducer:
             if b.work is not None:
                 b.work.wait()
             b.reset()
+
+    def _abandon(self):
+        """Forget a backward pass that never reached _finalize (it raised): wait for what was launched, reset the rest."""
+        for b in self.buckets:
+            if b.work is not None:
+                try:
+                    b.work.wait()
+                except Exception:
+                    pass
+            b.reset()
+        self._callback_queued = False
 
     def remove(self):
         for h in self._hooks:

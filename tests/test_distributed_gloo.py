@@ -63,6 +63,33 @@ def _worker(rank, world, port, tmp):
                 dist.all_reduce(want)
                 want /= world
                 assert torch.allclose(p.grad, want, atol=1e-6, rtol=1e-5), f"step {step} {n}"
+        # 2b. a backward pass that raises half way (after some gradients were bucketed) must not poison later passes
+        class _Boom(torch.autograd.Function):
+            @staticmethod
+            def forward(ctx, x):
+                return x.clone()
+
+            @staticmethod
+            def backward(ctx, g):
+                raise RuntimeError("boom")
+        net.zero_grad()
+        x = torch.randn(6, 7, generator=torch.Generator().manual_seed(5 + rank))
+        h = torch.tanh(net.bn(_Boom.apply(net.a(x))))
+        with pytest.raises(RuntimeError, match="boom"):
+            net.b(h).square().sum().backward()          # net.b got its gradients, net.a never did
+        net.zero_grad()
+        net(x).square().sum().backward()                 # a clean step afterwards is averaged again
+        local = _Net()
+        local.load_state_dict(net.state_dict())
+        local.train()
+        local(x).square().sum().backward()
+        for (n, p), (_, q) in zip(net.named_parameters(), local.named_parameters()):
+            if q.grad is None:
+                continue
+            want = q.grad.clone()
+            dist.all_reduce(want)
+            want /= world
+            assert torch.allclose(p.grad, want, atol=1e-6, rtol=1e-5), f"after aborted backward: {n}"
         # 3. a module whose forward hook never fires (the reference's Discriminator bug) still reduces
         assert net._gtn_reducer.launched_early >= 1
         t = reduce_tensor(torch.tensor([float(rank + 1)]), world)

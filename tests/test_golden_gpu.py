@@ -68,13 +68,19 @@ def test_training_step_matches_reference_golden(name):
     G.decoder._forced_seed = G.postnet._forced_seed = D._forced_seed = mseed
     memory = torch.from_numpy(z["in/memory"]).cuda()
     enc = memory[:, :, :512].clone().requires_grad_(True)
-    noise = memory[:, :, -512:]
-    # the text encoder is out of scope (stock PyTorch): feed the reference's captured encoder outputs / noise draw
+    # the text encoder is out of scope (stock PyTorch): feed the reference's captured encoder outputs
     G.encoder.forward = lambda emb, lens: enc
-    G.decoder.append_noise = lambda x: torch.cat((x, noise), -1)
+    # Decoder.append_noise is NOT replaced: the reference draws the noise with CPU torch.rand as the first draw after
+    # torch.manual_seed(mseed + 1) (model.py:275, oracle/make_golden.py), and so must the drop-in
+    seen = {}
+    orig_append = G.decoder.append_noise
+    G.decoder.append_noise = lambda x: seen.setdefault("memory", orig_append(x))
     batch = tuple(torch.from_numpy(z[f"in/{n}"]) for n in ("text", "in_len", "mel_tgt", "gate_tgt", "spk", "emo", "out_len"))
     x, y = G.parse_batch(batch)
+    torch.manual_seed(mseed + 1)
     y_pred = G(x)
+    assert torch.equal(seen["memory"][:, :, -512:].cpu(), torch.from_numpy(z["in/memory"])[:, :, -512:]), "noise draw order"
+    assert _rel(seen["memory"], z["in/memory"]) <= 1e-6, "speaker / emotion / noise columns of the decoder memory"
     for n, t in zip(("mel", "mel_post", "gate", "align"), y_pred):
         e = _rel(t, z[f"out/{n}"])
         assert e <= REL, f"{name}:{n} rel err {e:.3e}"
@@ -132,3 +138,115 @@ def test_discriminator_matches_reference_golden():
     grads = {k: p.grad for k, p in D.named_parameters()}
     grads["mel"] = mel.grad
     assert _check_grads(z, grads) == 11
+
+
+def test_training_step_benchmark_shape_matches_reference_golden():
+    """T_in = 150 (ragged), 208 frames, fp32-accurate mode, against the unmodified reference (train_vanilla_long):
+    75 encoder positions per CTA of a sequence pair, multi-trip attention-backward loops, long-T accumulation."""
+    from oracle import gantron_oracle as O
+    from oracle.make_golden import seeded_encoder_outputs
+    from gantron_b200.hparams import HParams
+    from gantron_b200 import model as M
+    from gantron_b200.loss_function import Tacotron2Loss
+    z = _load("train_vanilla_long")
+    hp = HParams(str(z["hp_string"]) + ",b200_precision=fp32")
+    B, T_in, T_out, wseed, mseed = (int(z[k]) for k in ("B", "T_in", "T_out", "wseed", "mseed"))
+    G, D = M.Tacotron2(hp), M.Discriminator(hp)
+    G.load_state_dict(O.seeded_state_dict({k: tuple(v.shape) for k, v in G.state_dict().items()}, seed=wseed))
+    D.load_state_dict(O.seeded_state_dict({k: tuple(v.shape) for k, v in D.state_dict().items()}, seed=wseed + 1))
+    G, D = G.cuda().train(), D.cuda().train()
+    for p in D.parameters():
+        p.requires_grad = False
+    G.decoder._forced_seed = G.postnet._forced_seed = D._forced_seed = mseed
+    enc = seeded_encoder_outputs(B, T_in, 512, wseed + 3).cuda().requires_grad_(True)
+    G.encoder.forward = lambda emb, lens: enc
+    seen = {}
+    orig_append = G.decoder.append_noise
+    G.decoder.append_noise = lambda x: seen.setdefault("memory", orig_append(x))
+    batch = O.synthetic_batch(B, T_in, T_out, seed=wseed + 2, ragged=True, n_symbols=hp.n_symbols)
+    x, y = G.parse_batch(batch)
+    torch.manual_seed(mseed + 1)
+    y_pred = G(x)
+    assert torch.equal(seen["memory"][:, 0, 512:].cpu(), torch.from_numpy(z["in/noise"])), "noise draw order (model.py:275)"
+    s = int(z["align_stride"])
+    mel, mel_post, gate, align = y_pred
+    for n, t in (("mel", mel), ("mel_post", mel_post), ("gate", gate), ("align_strided", align[:, ::s]),
+                 ("align_colsum", align.sum(1))):
+        e = _rel(t, z[f"out/{n}"])
+        assert e <= REL, f"long:{n} rel err {e:.3e}"
+    mel_loss, gate_loss, attn_loss = Tacotron2Loss()(y_pred, y, x[1], x[-1])
+    adv = D.adversarial_loss(y_pred[1], x[-1])
+    for n, t in (("mel_loss", mel_loss), ("gate_loss", gate_loss), ("attn_loss", attn_loss), ("adv", adv)):
+        ref = float(z[f"out/{n}"])
+        assert abs(float(t) - ref) <= REL * abs(ref) + 1e-6, f"long:{n} {float(t)} vs {ref}"
+    (mel_loss + gate_loss + adv + 10 * attn_loss).backward()
+    grads = {k: p.grad for k, p in G.named_parameters() if p.grad is not None}
+    grads["enc_out"] = enc.grad
+    assert _check_grads(z, grads) >= 40
+
+
+def _wrapper_model(z):
+    from oracle import gantron_oracle as O
+    from gantron_b200.hparams import HParams
+    from gantron_b200 import model as M
+    hp = HParams(str(z["hp_string"]) + ",b200_precision=fp32")
+    G = M.Tacotron2(hp)
+    G.load_state_dict(O.seeded_state_dict({k: tuple(v.shape) for k, v in G.state_dict().items()}, seed=int(z["wseed"])))
+    G = G.cuda().eval()
+    G.decoder._forced_seed = int(z["mseed"])
+    enc = torch.from_numpy(z["in/enc"]).cuda()
+    G.encoder.inference = lambda emb, style=None: enc          # the text encoder is out of scope: captured outputs
+    return G
+
+
+def test_tacotron2_inference_wrapper_matches_reference_golden(capsys):
+    """Tacotron2.inference ITSELF (model.py:675-723) in the combined labels+noise configuration: random emotion draw,
+    speaker embedding, emotion columns, the decoder's own style draw -- same CPU RNG order as the reference -- then the
+    persistent decode kernel and the eval-mode Postnet; return conventions of model.py:483 (gate (B,T,1))."""
+    z = _load("infer_combined_wrapper")
+    G = _wrapper_model(z)
+    steps = int(z["steps"])
+    seen = {}
+    orig = G.decoder.inference
+    G.decoder.inference = lambda memory, style: (seen.setdefault("memory", memory), orig(memory, style))[1]
+    torch.manual_seed(int(z["mseed"]) + 1)
+    with torch.no_grad():
+        out = G.inference(torch.from_numpy(z["in/text"]).cuda(), style=None, emotions=None,
+                          speaker=torch.from_numpy(z["in/speaker"]).cuda())
+    assert isinstance(out, list) and len(out) == 4
+    mel, mel_post, gate, align = out
+    assert _rel(seen["memory"], z["in/decoder_memory"]) <= 1e-6, "speaker / emotion columns or their draw order"
+    assert mel.shape == (1, 80, steps) and gate.shape == (1, steps, 1) and align.shape == (1, steps, z["in/text"].shape[1])
+    for n, t in (("mel", mel), ("gate", gate), ("align", align), ("mel_post", mel_post)):
+        e = _rel(t, z[f"out/{n}"])
+        assert e <= REL, f"{n} rel err {e:.3e}"
+    assert "Warning! Reached max decoder steps" in capsys.readouterr().out        # model.py:489 (gate_threshold = 1.0)
+
+
+def test_tacotron2_inference_wrapper_str_and_explicit_inputs():
+    """The remaining branches of the wrapper: a raw string goes through the reference's text front-end (model.py:687-689;
+    stubbed here, the front-end is out of scope) and explicit style / emotions reproduce the implicit draws."""
+    import sys
+    import types
+    z = _load("infer_combined_wrapper")
+    G = _wrapper_model(z)
+    ids = [int(i) for i in z["in/text"][0]]
+    fake = types.ModuleType("text")
+    fake.text_to_sequence = lambda s, cleaners: ids if (s == "hello b200" and cleaners == ['english_cleaners']) else None
+    saved = sys.modules.get("text")
+    sys.modules["text"] = fake
+    try:
+        torch.manual_seed(int(z["mseed"]) + 1)
+        emotions = torch.rand(1, 5)
+        style = torch.rand(1, 1, 512).repeat_interleave(len(ids), dim=1)
+        with torch.no_grad():
+            mel, mel_post, gate, align = G.inference("hello b200", style=style.cuda(), emotions=emotions.cuda(),
+                                                     speaker=torch.from_numpy(z["in/speaker"]).cuda())
+    finally:
+        if saved is None:
+            del sys.modules["text"]
+        else:
+            sys.modules["text"] = saved
+    for n, t in (("mel", mel), ("gate", gate), ("align", align), ("mel_post", mel_post)):
+        e = _rel(t, z[f"out/{n}"])
+        assert e <= REL, f"{n} rel err {e:.3e}"

@@ -173,3 +173,71 @@ def test_state_dict_contract_matches_reference_golden():
         assert ours_g == json.loads(str(z["sd/G"])), name
         assert ours_d == json.loads(str(z["sd/D"])), name
         assert list(ours_g) == list(json.loads(str(z["sd/G"]))), "key order differs"
+
+
+def test_oracle_train_step_long_matches_reference_golden():
+    """The benchmark's sequence shape (T_in = 150 ragged, 208 frames): inputs, encoder stand-in and Philox masks are
+    regenerated from the recorded seeds; the reference's noise draw order (model.py:275) is checked on the way."""
+    from oracle.make_golden import philox_train_masks, seeded_encoder_outputs
+    import gantron_b200.model as M
+    z = _load("train_vanilla_long")
+    hp = HParams(str(z["hp_string"]))
+    d = O.Dims.from_hparams(hp)
+    B, T_in, T_out, wseed, mseed = (int(z[k]) for k in ("B", "T_in", "T_out", "wseed", "mseed"))
+    shapes_g = {k: tuple(v.shape) for k, v in M.Tacotron2(HParams(str(z["hp_string"]))).state_dict().items()}
+    shapes_d = {k: tuple(v.shape) for k, v in M.Discriminator(hp).state_dict().items()}
+    sd = {k: (v.clone().requires_grad_(True) if v.dtype.is_floating_point and "running" not in k else v)
+          for k, v in O.seeded_state_dict(shapes_g, seed=wseed).items()}
+    sdd = O.seeded_state_dict(shapes_d, seed=wseed + 1)
+    text, in_len, mel_tgt, gate_tgt, spk, emo, out_len = O.synthetic_batch(B, T_in, T_out, seed=wseed + 2, ragged=True,
+                                                                           n_symbols=hp.n_symbols)
+    enc = seeded_encoder_outputs(B, T_in, d.enc_dim, wseed + 3).requires_grad_(True)
+    torch.manual_seed(mseed + 1)
+    noise = torch.rand(B, 1, d.noise)                        # Decoder.append_noise: first CPU draw of the pass
+    _close(noise[:, 0], z["in/noise"], "noise draw", atol=0, rtol=0)
+    memory = torch.cat((enc, noise.repeat_interleave(T_in, dim=1)), -1)
+    mk, dk = philox_train_masks(mseed, B, T_out, d, (T_out + d.disc_window - 1) // d.disc_window)
+    mel, mel_post, gate, align = O.generator_from_memory(sd, memory, mel_tgt, in_len, out_len, d, mk, training=True)
+    s = int(z["align_stride"])
+    for n, t in (("mel", mel), ("mel_post", mel_post), ("gate", gate), ("align_strided", align[:, ::s]),
+                 ("align_colsum", align.sum(1))):
+        _close(t, z[f"out/{n}"], f"long:{n}", atol=5e-5, rtol=5e-4)
+    mel_loss, gate_loss = O.tacotron2_losses(mel, mel_post, gate, mel_tgt, gate_tgt)
+    attn = O.attention_loss(align, in_len, out_len)
+    adv = O.adversarial_loss(sdd, mel_post, out_len, d, dk)
+    for n, t in (("mel_loss", mel_loss), ("gate_loss", gate_loss), ("attn_loss", attn), ("adv", adv)):
+        _close(t, z[f"out/{n}"], f"long:{n}", atol=1e-6, rtol=1e-4)
+    (mel_loss + gate_loss + adv + 10 * attn).backward()
+    grads = {k: v.grad for k, v in sd.items() if getattr(v, "grad", None) is not None}
+    grads["enc_out"] = enc.grad
+    assert _check_grads(z, grads) >= 40
+
+
+def test_oracle_wrapper_inference_matches_reference_golden():
+    """Tacotron2.inference, combined labels+noise config: the wrapper's random emotion draw (model.py:691-692), speaker
+    and emotion columns (model.py:704-712) and the decoder's own style draw (model.py:468-469), in that RNG order."""
+    import gantron_b200.model as M
+    from oracle import philox as PX
+    z = _load("infer_combined_wrapper")
+    hp = HParams(str(z["hp_string"]))
+    shapes = {k: tuple(v.shape) for k, v in M.Tacotron2(HParams(str(z["hp_string"]))).state_dict().items()}
+    d = O.Dims.from_hparams(hp)
+    assert (d.spk, d.emo, d.noise, d.d_mem) == (64, 5, 512, 1093)
+    sd = O.seeded_state_dict(shapes, seed=int(z["wseed"]))
+    mseed, steps = int(z["mseed"]), int(z["steps"])
+    enc = torch.from_numpy(z["in/enc"])
+    T_in = enc.shape[1]
+    torch.manual_seed(mseed + 1)
+    emotions = torch.rand(1, 5)
+    spk = sd["speaker_embedding.weight"][torch.from_numpy(z["in/speaker"])]
+    mem_in = torch.cat((enc, spk[:, None].repeat(1, T_in, 1), emotions[:, None].repeat(1, T_in, 1)), 2)
+    _close(mem_in, z["in/decoder_memory"], "decoder memory (speaker / emotion columns)", atol=0, rtol=0)
+    style = torch.rand(1, 1, d.noise).repeat_interleave(T_in, dim=1)
+    memory = torch.cat((mem_in, style), -1)
+    keep = lambda s: (torch.from_numpy(PX.keep_mask(mseed, PX.SITE_PRENET1, s, (1, d.prenet), 0.5)),
+                      torch.from_numpy(PX.keep_mask(mseed, PX.SITE_PRENET2, s, (1, d.prenet), 0.5)))
+    mel, gate, align, lengths, _ = O.decoder_inference(sd, memory, d, keep, max_steps=steps)
+    _close(mel, z["out/mel"], "mel")
+    _close(gate, z["out/gate"], "gate")
+    _close(align, z["out/align"], "align")
+    _close(mel + O.postnet(sd, mel, d, None, training=False), z["out/mel_post"], "mel_post")
