@@ -281,7 +281,7 @@ def bench_inference(steps_frames: int = 1000):
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             torch.cuda.synchronize()
             e0.record()
-            r = decoder_ops.decoder_inference(dec.packed(), mem, max_steps=steps_frames, gate_threshold=0.5, seed=7 + it,
+            r = decoder_ops.decoder_inference(dec, mem, max_steps=steps_frames, gate_threshold=0.5, seed=7 + it,
                                               prec=1, const_tail=True, ignore_stop=True)
             e1.record()
             torch.cuda.synchronize()

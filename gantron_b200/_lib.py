@@ -48,6 +48,8 @@ SIGNATURES = {
     "gtn_bn_act_fwd": (c_i, [c_p, c_i, c_ll, c_ll, c_i, c_p, c_p, c_p, c_p, c_i, c_f, c_ull, c_i, c_p, c_i, c_ll, c_p]),
     "gtn_bn_act_bwd": (c_i, [c_p, c_i, c_ll, c_p, c_i, c_ll, c_ll, c_i, c_p, c_p, c_p, c_p, c_i, c_f, c_ull, c_i,
                              c_p, c_p, c_p, c_i, c_ll, c_p, c_p]),
+    "gtn_bn_act_bwd_eval": (c_i, [c_p, c_i, c_ll, c_p, c_i, c_ll, c_ll, c_i, c_p, c_p, c_p, c_p, c_i, c_f, c_ull, c_i,
+                                  c_p, c_p, c_p, c_i, c_ll, c_p, c_p]),
     "gtn_drop_tanh_bwd": (c_i, [c_p, c_i, c_ll, c_p, c_i, c_ll, c_ll, c_i, c_f, c_ull, c_i, c_p, c_i, c_ll, c_p, c_p]),
     "gtn_disc_head_fwd": (c_i, [c_p, c_i, c_ll, c_ll, c_i, c_p, c_p, c_p, c_p]),
     "gtn_disc_head_bwd": (c_i, [c_p, c_p, c_i, c_ll, c_ll, c_i, c_p, c_p, c_i, c_ll, c_p, c_p, c_p]),
@@ -58,11 +60,8 @@ SIGNATURES = {
                                 c_p, c_p, c_p, c_p]),
     "gtn_attn_guide_loss_fwd": (c_i, [c_p, c_i, c_i, c_i, c_p, c_p, c_f, c_p, c_p]),
     "gtn_attn_guide_loss_bwd": (c_i, [c_p, c_i, c_i, c_i, c_p, c_p, c_f, c_p, c_p, c_p]),
-    "gtn_decoder_forward": (c_i, [c_p, c_p]),
     "gtn_decoder_forward2": (c_i, [c_p, c_p]),
     "gtn_sizeof": (c_i, [c_i]),
-    "gtn_decoder_bwd_grid": (c_i, []),
-    "gtn_decoder_backward": (c_i, [c_p, c_p]),
     "gtn_decoder_bwd2_grid": (c_i, [c_i, c_i, c_i, c_i]),
     "gtn_decoder_backward2": (c_i, [c_p, c_p]),
 }
@@ -88,22 +87,6 @@ class DecoderFwdParams(C.Structure):
                               "q_all", "th_all", "f_all", "cum_all",
                               "w_att2", "w_dec2", "u_loc", "wq_t", "prof", "gbias_a", "gbias_d", "pbias")]
         + [("Ep", c_i), ("reserved0", c_i)]
-    )
-
-
-class DecoderBwdParams(C.Structure):
-    """Mirror of `gtn_decoder_bwd_params` (include/gantron_b200.h)."""
-    _fields_ = (
-        [(n, c_i) for n in ("B", "Tin", "ldT", "T", "E", "Cc", "D", "Ha", "Hd", "P", "A", "Ap", "F", "KS",
-                            "prec", "mult", "use_dropout", "mem_bf16")]
-        + [("p_att", c_f), ("p_dec", c_f), ("thr_att", c_u), ("thr_dec", c_u), ("seed", c_ull)]
-        + [(n, c_p) for n in ("wT_att", "wT_dec", "wqT", "v", "wconv", "wdense", "mem_enc", "mem_const", "lengths",
-                              "gates_a", "c_a_all", "gates_d", "c_d_all", "align", "th_all", "f_all", "cum_all",
-                              "dproj_all", "dalign", "xdg_a", "xdg_d", "xdq", "carry_ha", "dha_dec", "dc_a",
-                              "carry_hd", "dc_d", "dctx_att", "dctx_dec", "dwprev", "dcum", "barrier",
-                              "dga_all", "dgd_all", "dq_all", "dpre_all", "dctx_all", "dpm",
-                              "dv_part", "dwd_part", "dwc_part")]
-        + [("grid", c_i)]
     )
 
 

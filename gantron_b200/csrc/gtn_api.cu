@@ -32,7 +32,6 @@ void gtn_reset_launch_count(void) { g_launches.store(0); }
 
 int gtn_sizeof(int which) {
   if (which == 0) return (int)sizeof(gtn_decoder_fwd_params);
-  if (which == 1) return (int)sizeof(gtn_decoder_bwd_params);
   if (which == 2) return (int)sizeof(gtn_decoder_bwd2_params);
   return -1;
 }

@@ -926,6 +926,9 @@ static int launch_bwd2(const Bwd2Maps& maps, const DecBwd2& p, int ncl, cudaStre
   if (rc) return rc;
   cfg.stream = st;
   cfg.numAttrs = getenv("GTN_NO_COOP") ? 1 : 2;   // profilers that cannot replay cooperative launches
+  // each CTA pair stages the encoder lengths of at most 8 sequences (scr + 48): B <= 16 * clusters
+  GTN_REQUIRE((p.B + 2 * ncl - 1) / (2 * ncl) <= 8, "decoder backward: batch %d needs more than 8 sequences per CTA pair on %d clusters",
+              p.B, ncl);
   cfg.gridDim = dim3(CL * ncl);
   GTN_CUDA_OK(cudaLaunchKernelEx(&cfg, decoder_bwd2_kernel<N>, maps, p, S));
   count_launch();

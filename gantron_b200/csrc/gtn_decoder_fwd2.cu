@@ -844,6 +844,9 @@ static int launch_fwd2(const Fwd2Maps& maps, const DecFwd& p, int max_clusters_w
   GTN_CUDA_OK(cudaOccupancyMaxActiveClusters(&max_cl, kern, &cfg));
   GTN_REQUIRE(max_cl >= 1, "decoder forward: no cluster of %d CTAs fits on this device", CL);
   const int ncl = max_cl < max_clusters_wanted ? max_cl : max_clusters_wanted;
+  // each CTA pair stages the encoder lengths of at most 8 sequences (scr + 48): B <= 16 * clusters
+  GTN_REQUIRE((p.B + 2 * ncl - 1) / (2 * ncl) <= 8, "decoder forward: batch %d needs more than 8 sequences per CTA pair on %d clusters",
+              p.B, ncl);
   cfg.gridDim = dim3(CL * ncl);
   cfg.numAttrs = getenv("GTN_NO_COOP") ? 1 : 2;   // profilers that cannot replay cooperative launches
   GTN_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, maps, p, S));

@@ -492,10 +492,10 @@ int gtn_bn_act_fwd(const void* y, int y_dtype, long long ldy, long long rows, in
   return 0;
 }
 
-int gtn_bn_act_bwd(const void* dx, int dx_dtype, long long lddx, const void* y, int y_dtype, long long ldy, long long rows,
-                   int C, const float* mean, const float* rstd, const float* gamma, const float* beta, int act,
-                   float drop_p, unsigned long long seed, int site, float* dgamma, float* dbeta, void* dy, int dy_dtype,
-                   long long lddy, float* dbias, void* stream) {
+static int bn_act_bwd_impl(const void* dx, int dx_dtype, long long lddx, const void* y, int y_dtype, long long ldy, long long rows,
+                           int C, const float* mean, const float* rstd, const float* gamma, const float* beta, int act,
+                           float drop_p, unsigned long long seed, int site, float* dgamma, float* dbeta, void* dy, int dy_dtype,
+                           long long lddy, float* dbias, void* stream, bool batch_stats) {
   EltGeom g; int th, bl;
   if (int rc = make_geom(&g, rows, C, &th, &bl)) return rc;
   GTN_REQUIRE(lddx % 8 == 0 && ldy % 8 == 0 && lddy % 8 == 0, "row strides must be multiples of 8 elements");
@@ -510,11 +510,28 @@ int gtn_bn_act_bwd(const void* dx, int dx_dtype, long long lddx, const void* y, 
                                                  ds, seed, (uint32_t)site, dgamma, dbeta);
   GTN_CUDA_OK(cudaGetLastError());
   bn_act_bwd_apply_kernel<<<bl, th, smem, st>>>(dx, dx_dtype, lddx, y, y_dtype, ldy, g, mean, rstd, gamma, beta, act, thr,
-                                                ds, seed, (uint32_t)site, dgamma, dbeta, 1.f / (float)rows, dy, dy_dtype,
-                                                lddy, dbias);
+                                                ds, seed, (uint32_t)site, dgamma, dbeta, batch_stats ? 1.f / (float)rows : 0.f,
+                                                dy, dy_dtype, lddy, dbias);
   GTN_CUDA_OK(cudaGetLastError());
   count_launch(2);
   return 0;
+}
+
+int gtn_bn_act_bwd(const void* dx, int dx_dtype, long long lddx, const void* y, int y_dtype, long long ldy, long long rows,
+                   int C, const float* mean, const float* rstd, const float* gamma, const float* beta, int act,
+                   float drop_p, unsigned long long seed, int site, float* dgamma, float* dbeta, void* dy, int dy_dtype,
+                   long long lddy, float* dbias, void* stream) {
+  return bn_act_bwd_impl(dx, dx_dtype, lddx, y, y_dtype, ldy, rows, C, mean, rstd, gamma, beta, act, drop_p, seed, site, dgamma,
+                         dbeta, dy, dy_dtype, lddy, dbias, stream, true);
+}
+
+// module.eval(): mean / rstd are the running statistics, i.e. constants: the batch-coupling terms vanish (inv_n = 0)
+int gtn_bn_act_bwd_eval(const void* dx, int dx_dtype, long long lddx, const void* y, int y_dtype, long long ldy, long long rows,
+                        int C, const float* mean, const float* rstd, const float* gamma, const float* beta, int act,
+                        float drop_p, unsigned long long seed, int site, float* dgamma, float* dbeta, void* dy, int dy_dtype,
+                        long long lddy, float* dbias, void* stream) {
+  return bn_act_bwd_impl(dx, dx_dtype, lddx, y, y_dtype, ldy, rows, C, mean, rstd, gamma, beta, act, drop_p, seed, site, dgamma,
+                         dbeta, dy, dy_dtype, lddy, dbias, stream, false);
 }
 
 int gtn_drop_tanh_bwd(const void* dout, int dout_dtype, long long lddo, const void* a, int a_dtype, long long lda,

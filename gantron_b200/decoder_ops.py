@@ -54,8 +54,6 @@ class PackedDecoder:
     def __init__(self, dec: torch.nn.Module, dims: DecoderDims, prec: int):
         self.dims, self.prec = dims, prec
         self._versions = None
-        import weakref
-        self._dec = weakref.ref(dec)
         self.refresh(dec)
 
     @staticmethod
@@ -73,22 +71,21 @@ class PackedDecoder:
             v=al.v.linear_layer.weight, wconv=al.location_layer.location_conv.conv.weight,
             wdense=al.location_layer.location_dense.linear_layer.weight)
 
+    @staticmethod
+    def _key(dec):
+        # version counters catch optimizer steps / in-place copies; data_ptr catches parameters that were re-pointed
+        # (`p.data = ...`, module.to(), a deep copy of the module)
+        return tuple((p._version, p.data_ptr()) for p in PackedDecoder._params(dec).values())
+
     def stale(self, dec) -> bool:
-        return self._versions != tuple(p._version for p in self._params(dec).values())
+        return self._versions != self._key(dec)
 
     @torch.no_grad()
     def refresh(self, dec) -> None:
         d, prec = self.dims, self.prec
         P = self._params(dec)
-        self._versions = tuple(p._version for p in P.values())
+        self._versions = self._key(dec)
         f = lambda t: t.detach().float()
-        wa, wha = f(P["w_ih_a"]), f(P["w_hh_a"])
-        self.w_att = packing.pack_weight([(wa[:, :d.prenet], d.Pp), (wa[:, d.prenet:], d.Dp), (wha, d.Hap)], prec)
-        wd, whd = f(P["w_ih_d"]), f(P["w_hh_d"])
-        self.w_dec = packing.pack_weight([(wd[:, :d.att_rnn], d.Hap), (wd[:, d.att_rnn:], d.Dp), (whd, d.Hdp)], prec)
-        wpg = torch.cat((f(P["w_proj"]), f(P["w_gate"])), 0)           # rows 0..n_mel-1 mel, n_mel = gate
-        self.w_proj = packing.pack_weight([(wpg[:, :d.dec_rnn], d.Hdp), (wpg[:, d.dec_rnn:], d.Dp)], prec,
-                                          row_pad=pad_to(d.n_mel + 1, 16))
         self.b_proj = torch.cat((f(P["b_proj"]), f(P["b_gate"]))).contiguous()
         self.w_pre1 = packing.pack_weight([(f(P["w_pre1"]), d.NMp)], prec)
         self.w_pre2 = packing.pack_weight([(f(P["w_pre2"]), d.Pp)], prec)
@@ -99,7 +96,6 @@ class PackedDecoder:
         self.wconv = f(P["wconv"]).contiguous()
         self.wdense = f(P["wdense"]).contiguous()
         self.wmem = f(P["wmem"]).contiguous()
-        # ---- second-generation (clustered tcgen05) kernel packs ----
         # location conv (F,2,KS) and dense (A,F) pre-multiplied: U[a][ch*KS + k] = sum_c dense[a][c] conv[c][ch][k]
         U = self.wdense @ self.wconv.reshape(d.loc_filters, 2 * d.loc_kernel)
         Up = torch.zeros(d.att_dim, 64, device=U.device)
@@ -195,12 +191,6 @@ def _tile_rows(w: torch.Tensor, H: int) -> torch.Tensor:
     return w.view(4, H // 32, 32, K).permute(1, 0, 2, 3).reshape(4 * H, K).contiguous()
 
 
-def decoder_version() -> int:
-    """Which persistent decoder kernel generation to launch (2 = clustered tcgen05, the default)."""
-    import os
-    return int(os.environ.get("GANTRON_B200_DECODER", "2"))
-
-
 PROF_BUFFER_BWD = None
 KERNEL_EVENTS = None     # measurement hook (bench.py): dict name -> [(start_event, end_event)] around the persistent kernels
 
@@ -226,8 +216,7 @@ def _fill_common(p: _lib.DecoderFwdParams, d: DecoderDims, pk: PackedDecoder, B:
     p.P, p.Pp, p.A, p.F, p.KS, p.NM, p.NMp = d.prenet, d.Pp, d.att_dim, d.loc_filters, d.loc_kernel, d.n_mel, d.NMp
     p.prec = prec
     p.prof = PROF_BUFFER.data_ptr() if PROF_BUFFER is not None else None
-    for name in ("w_att", "w_dec", "w_proj", "w_pre1", "w_pre2", "b_att", "b_dec", "b_proj", "wq", "v", "wconv", "wdense",
-                 "u_loc", "wq_t"):
+    for name in ("w_pre1", "w_pre2", "b_att", "b_dec", "b_proj", "wq", "v", "wconv", "wdense", "u_loc", "wq_t"):
         setattr(p, name, getattr(pk, name).data_ptr())
 
 
@@ -269,11 +258,15 @@ def split_memory(memory: torch.Tensor, enc_dim: int, const_tail: Optional[bool])
 
 
 @torch.no_grad()
-def decoder_inference(pk: PackedDecoder, memory: torch.Tensor, *, max_steps: int, gate_threshold: float,
+def decoder_inference(dec, memory: torch.Tensor, *, max_steps: int, gate_threshold: float,
                       seed: int, prec: int, const_tail: Optional[bool] = None, ignore_stop: bool = False,
                       mem_dtype: Optional[torch.dtype] = None):
-    """Autoregressive decode (model.py:456-497) of `memory` (B,T_in,D) that already carries the style columns.
+    """Autoregressive decode (model.py:456-497) of `memory` (B,T_in,D) that already carries the style columns, with the
+    parameters of the Decoder module `dec`.
     Returns mel (B,n_mel,T'), gate (B,T',1), alignments (B,T',T_in), lengths (B,) int32, steps."""
+    pk = dec.packed()
+    if pk.prec != prec:
+        raise ValueError(f"decoder_inference: prec={prec} but the module's packs were built for prec={pk.prec}")
     d = pk.dims
     B, Tin, D = memory.shape
     assert D == d.d_mem, f"memory has {D} columns, decoder expects {d.d_mem}"
@@ -287,8 +280,7 @@ def decoder_inference(pk: PackedDecoder, memory: torch.Tensor, *, max_steps: int
     p.p_att = p.p_dec = 0.0
     p.gate_threshold = gate_threshold
     p.seed = seed
-    v2 = decoder_version() >= 2
-    st = _alloc_state(p, d, B, mult, dev, pad_to(E, 64) if v2 else None)
+    st = _alloc_state(p, d, B, mult, dev, pad_to(E, 64))
     memory = memory.float()
     pm = linear_nt(memory.reshape(B * Tin, D), pk.wmem, prec).reshape(B, Tin, d.att_dim)
     mem_enc = memory[:, :, :E].to(mdt).contiguous()
@@ -300,11 +292,8 @@ def decoder_inference(pk: PackedDecoder, memory: torch.Tensor, *, max_steps: int
     p.mem_enc, p.pm, p.mem_const = mem_enc.data_ptr(), pm.data_ptr(), mem_const.data_ptr()
     p.lengths = None
     p.align_out, p.mel_out, p.gate_out = align.data_ptr(), mel.data_ptr(), gate.data_ptr()
-    if v2:
-        keep = _fill_v2(p, pack_v2(pk._dec(), pk, E), mem_const[:, :D - E], prec, B, True)   # noqa: F841 (kept alive)
-        _lib.check(_lib.load().gtn_decoder_forward2(C.byref(p), _lib.stream()), "gtn_decoder_forward2")
-    else:
-        _lib.check(_lib.load().gtn_decoder_forward(C.byref(p), _lib.stream()), "gtn_decoder_forward")
+    keep = _fill_v2(p, pack_v2(dec, pk, E), mem_const[:, :D - E], prec, B, True)   # noqa: F841 (kept alive)
+    _lib.check(_lib.load().gtn_decoder_forward2(C.byref(p), _lib.stream()), "gtn_decoder_forward2")
     steps = int(st["steps_done"][0].item())          # the single host sync of the whole decode
     lengths = st["lengths_out"].clone()
     lengths[st["done"] == 0] = steps
@@ -350,18 +339,9 @@ def _rows8(t: torch.Tensor) -> torch.Tensor:
 class _PackedBackward:
     """Transposed packs used by the backward kernel; built lazily next to PackedDecoder."""
 
-    def __init__(self, dec, pk: PackedDecoder, v1: bool):
-        d, prec = pk.dims, pk.prec
+    def __init__(self, dec, pk: PackedDecoder):
         P = PackedDecoder._params(dec)
         f = lambda t: t.detach().float()
-        self.v1 = v1
-        if v1:   # transposed LSTM / query packs of the first-generation BPTT kernel
-            wa = torch.cat((f(P["w_ih_a"]), f(P["w_hh_a"])), 1).t().contiguous()     # [P+D+Ha][4Ha]
-            wd = torch.cat((f(P["w_ih_d"]), f(P["w_hh_d"])), 1).t().contiguous()     # [Ha+D+Hd][4Hd]
-            self.wT_att = packing.pack_weight([(wa, 4 * d.att_rnn)], prec, row_pad=pad_to(wa.shape[0], 32))
-            self.wT_dec = packing.pack_weight([(wd, 4 * d.dec_rnn)], prec, row_pad=pad_to(wd.shape[0], 32))
-            self.Ap = pad_to(d.att_dim, 32)
-            self.wqT = packing.pack_weight([(f(P["wq"]).t().contiguous(), self.Ap)], prec, row_pad=pad_to(d.att_rnn, 32))
         wpg = torch.cat((f(P["w_proj"]), f(P["w_gate"])), 0)                       # [n_mel+1][Hd+D]
         self.wpgT = wpg.t().contiguous()                                           # [Hd+D][n_mel+1]
         self.wmemT = f(P["wmem"]).t().contiguous()                                 # [D][A]
@@ -369,23 +349,47 @@ class _PackedBackward:
         self.versions = pk._versions
 
 
-def _packed_bwd(dec, pk: PackedDecoder, v1: bool = True) -> _PackedBackward:
+def _packed_bwd(dec, pk: PackedDecoder) -> _PackedBackward:
     pb = getattr(pk, "_bwd", None)
-    if pb is None or pb.versions != pk._versions or (v1 and not pb.v1):
-        pb = _PackedBackward(dec, pk, v1)
+    if pb is None or pb.versions != pk._versions:
+        pb = _PackedBackward(dec, pk)
         pk._bwd = pb
     return pb
 
 
+class _PrenetFn(torch.autograd.Function):
+    """Stand-alone Prenet (model.py:102-105): two tcgen05 GEMMs with fused relu + always-on Philox dropout, and the
+    matching backward (y = relu(x W^T) * keep * 2  =>  d(pre-activation) = dy * 2 * [y > 0])."""
+
+    @staticmethod
+    def forward(ctx, x2, w1, w2, seed, prec):
+        h1 = _prenet_layer(x2, w1, seed, SITE_PRENET1, prec)
+        h2 = _prenet_layer(h1, w2, seed, SITE_PRENET2, prec)
+        ctx.save_for_backward(x2, w1, w2, h1, h2)
+        ctx.prec = prec
+        return h2
+
+    @staticmethod
+    def backward(ctx, g):
+        x2, w1, w2, h1, h2 = ctx.saved_tensors
+        prec = ctx.prec
+        d2 = g.float() * 2.0 * (h2 > 0)
+        g_w2 = torch.empty_like(w2, dtype=torch.float32)
+        _wgrad_tn(d2, h1, g_w2, prec)
+        d1 = linear_nt(d2, w2.detach().float().t().contiguous(), prec) * 2.0 * (h1 > 0)
+        g_w1 = torch.empty_like(w1, dtype=torch.float32)
+        _wgrad_tn(d1, x2.float(), g_w1, prec)
+        g_x = linear_nt(d1, w1.detach().float().t().contiguous(), prec) if ctx.needs_input_grad[0] else None
+        return g_x, g_w1, g_w2, None, None
+
+
 def prenet_forward(prenet_mod, x: torch.Tensor, seed: int, prec: int = 1) -> torch.Tensor:
-    """Stand-alone Prenet.forward (model.py:102-105) on the tcgen05 GEMM with fused relu + Philox dropout."""
+    """Stand-alone Prenet.forward (model.py:102-105); differentiable w.r.t. the input and both weights."""
     shp = x.shape
-    x2 = x.reshape(-1, shp[-1])
+    x2 = x.reshape(-1, shp[-1]).float()
     w1 = prenet_mod.layers[0].linear_layer.weight
     w2 = prenet_mod.layers[1].linear_layer.weight
-    h1 = _prenet_layer(x2, w1, seed, SITE_PRENET1, prec)
-    h2 = _prenet_layer(h1, w2, seed, SITE_PRENET2, prec)
-    return h2.reshape(*shp[:-1], w2.shape[0])
+    return _PrenetFn.apply(x2, w1, w2, seed, prec).reshape(*shp[:-1], w2.shape[0])
 
 
 def _prenet_layer(x: torch.Tensor, w: torch.Tensor, seed: int, site: int, prec: int) -> torch.Tensor:
@@ -433,8 +437,7 @@ class _DecoderTrainFn(torch.autograd.Function):
         p.p_att, p.p_dec = dec.p_attention_dropout, dec.p_decoder_dropout
         p.gate_threshold = dec.gate_threshold
         p.seed = seed
-        v2 = decoder_version() >= 2
-        st = _alloc_state(p, d, B, mult, dev, pad_to(E, 64) if v2 else None)
+        st = _alloc_state(p, d, B, mult, dev, pad_to(E, 64))
         mem_enc = memory_f[:, :, :E].to(mdt).contiguous()
         mem_const = memory_f[:, 0, E:].contiguous() if E < D else torch.zeros(B, 1, device=dev)
         pm_k = pm.to(mdt).contiguous()
@@ -445,7 +448,7 @@ class _DecoderTrainFn(torch.autograd.Function):
             gates_a=e(T, B, 4 * d.att_rnn), c_a_all=e(T, B, d.att_rnn), h_a_buf=z(T + 1, B, d.att_rnn),
             gates_d=e(T, B, 4 * d.dec_rnn), c_d_all=e(T, B, d.dec_rnn), h_d_buf=z(T + 1, B, d.dec_rnn),
             ctx_buf=z(T + 1, B, D), q_all=e(T, B, d.att_dim), th_all=e(T, B, Tin, d.att_dim),
-            f_all=e(T, B, Tin, d.loc_filters) if not v2 else e(1), cum_all=e(T, B, Tin), align=z(B, T, Tin))
+            f_all=e(1), cum_all=e(T, B, Tin), align=z(B, T, Tin))
         p.mem_enc, p.pm, p.mem_const, p.lengths = mem_enc.data_ptr(), pm_k.data_ptr(), mem_const.data_ptr(), lengths.data_ptr()
         p.pre_all = pre_x.data_ptr()
         p.align_out = sv["align"].data_ptr()
@@ -454,12 +457,9 @@ class _DecoderTrainFn(torch.autograd.Function):
         p.ctx_all = sv["ctx_buf"][1:].data_ptr()
         p.q_all, p.th_all, p.f_all, p.cum_all = (sv["q_all"].data_ptr(), sv["th_all"].data_ptr(), sv["f_all"].data_ptr(),
                                                  sv["cum_all"].data_ptr())
-        if v2:
-            keep = _fill_v2(p, pack_v2(dec, pk, E), mem_const[:, :D - E], prec, B, False)   # noqa: F841 (kept alive)
-            _lib.check(_timed_call("decoder_fwd2_kernel", lambda: _lib.load().gtn_decoder_forward2(C.byref(p), _lib.stream())),
-                       "gtn_decoder_forward2")
-        else:
-            _lib.check(_lib.load().gtn_decoder_forward(C.byref(p), _lib.stream()), "gtn_decoder_forward")
+        keep = _fill_v2(p, pack_v2(dec, pk, E), mem_const[:, :D - E], prec, B, False)   # noqa: F841 (kept alive)
+        _lib.check(_timed_call("decoder_fwd2_kernel", lambda: _lib.load().gtn_decoder_forward2(C.byref(p), _lib.stream())),
+                   "gtn_decoder_forward2")
 
         # ---- deferred mel/gate projection over all frames (model.py:411-416): batched over b so the output is
         # written directly as [B][T][n_mel+1] (channels-last); the API tensors are views of it
@@ -477,7 +477,6 @@ class _DecoderTrainFn(torch.autograd.Function):
 
         ctx.dec, ctx.seed, ctx.training = dec, seed, training
         ctx.dims = (B, Tin, D, T, E, prec)
-        ctx.v2 = v2
         ctx.saved = dict(sv=sv, frames2=frames2, h1=h1, pre=pre, memory_f=memory_f, mem_enc=mem_enc, mem_const=mem_const,
                          lengths=lengths, out_cl=out_cl)
         return mel, gate, align
@@ -486,7 +485,7 @@ class _DecoderTrainFn(torch.autograd.Function):
     def backward(ctx, d_mel, d_gate, d_align):
         dec = ctx.dec
         pk = dec.packed()
-        pb = _packed_bwd(dec, pk, v1=not ctx.v2)
+        pb = _packed_bwd(dec, pk)
         d = pk.dims
         B, Tin, D, T, E, prec = ctx.dims
         mult = packing.mult_of(prec)
@@ -506,44 +505,7 @@ class _DecoderTrainFn(torch.autograd.Function):
         # hoisted projection backward: d[h_dec'|ctx'] for every frame
         dproj = linear_nt(dout2, pb.wpgT, prec)                                   # [TB][Hd+D]
 
-        if ctx.v2:
-            wk = _bptt_v2(dec, pk, d, ctx, S, sv, dproj, d_align, prec)
-        else:
-            q = _lib.DecoderBwdParams()
-            q.B, q.Tin, q.ldT, q.T = B, Tin, pad_to(Tin, 4), T
-            q.E, q.Cc, q.D, q.Ha, q.Hd, q.P, q.A, q.Ap, q.F, q.KS = (E, D - E, D, d.att_rnn, d.dec_rnn, d.prenet, d.att_dim,
-                                                                   pb.Ap, d.loc_filters, d.loc_kernel)
-            q.prec = prec
-            q.use_dropout = int(ctx.training)
-            q.mem_bf16 = int(S["mem_enc"].dtype == BF16)
-            q.p_att, q.p_dec, q.seed = dec.p_attention_dropout, dec.p_decoder_dropout, ctx.seed
-            grid = _lib.load().gtn_decoder_bwd_grid()
-            q.grid = grid
-            wk = dict(
-                xdg_a=z(B, mult * 4 * d.att_rnn, dt=BF16), xdg_d=z(B, mult * 4 * d.dec_rnn, dt=BF16), xdq=z(B, mult * pb.Ap, dt=BF16),
-                carry_ha=z(B, d.att_rnn), dha_dec=z(B, d.att_rnn), dc_a=z(B, d.att_rnn), carry_hd=z(B, d.dec_rnn),
-                dc_d=z(B, d.dec_rnn), dctx_att=z(B, D), dctx_dec=z(B, D), dwprev=z(B, q.ldT), dcum=z(B, q.ldT),
-                barrier=z(4, dt=torch.int32),
-                dga_all=torch.empty(T, B, 4 * d.att_rnn, device=dev), dgd_all=torch.empty(T, B, 4 * d.dec_rnn, device=dev),
-                dq_all=torch.empty(T, B, d.att_dim, device=dev), dpre_all=torch.empty(T, B, d.prenet, device=dev),
-                dctx_all=torch.empty(B, T, D, device=dev), dpm=z(B, Tin, d.att_dim),
-                dv_part=z(grid, d.att_dim), dwd_part=z(grid, d.att_dim * d.loc_filters),
-                dwc_part=z(grid, 2 * d.loc_filters * d.loc_kernel))
-            for k, v in wk.items():
-                setattr(q, k, v.data_ptr())
-            q.wT_att, q.wT_dec, q.wqT = pb.wT_att.data_ptr(), pb.wT_dec.data_ptr(), pb.wqT.data_ptr()
-            q.v, q.wconv, q.wdense = pk.v.data_ptr(), pk.wconv.data_ptr(), pk.wdense.data_ptr()
-            q.mem_enc, q.mem_const, q.lengths = S["mem_enc"].data_ptr(), S["mem_const"].data_ptr(), S["lengths"].data_ptr()
-            q.gates_a, q.c_a_all, q.gates_d, q.c_d_all = (sv["gates_a"].data_ptr(), sv["c_a_all"].data_ptr(),
-                                                          sv["gates_d"].data_ptr(), sv["c_d_all"].data_ptr())
-            q.align, q.th_all, q.f_all, q.cum_all = (sv["align"].data_ptr(), sv["th_all"].data_ptr(), sv["f_all"].data_ptr(),
-                                                     sv["cum_all"].data_ptr())
-            q.dproj_all = dproj.data_ptr()
-            d_align_c = None
-            if d_align is not None:
-                d_align_c = d_align.float().contiguous()
-                q.dalign = d_align_c.data_ptr()
-            _lib.check(_lib.load().gtn_decoder_backward(C.byref(q), _lib.stream()), "gtn_decoder_backward")
+        wk = _bptt_v2(dec, pk, d, ctx, S, sv, dproj, d_align, prec)
 
         # ---- deferred weight gradients: K = T*B GEMMs on MN-major operands --------------------------------
         TB = T * B
@@ -600,14 +562,10 @@ class _DecoderTrainFn(torch.autograd.Function):
             g_memory = linear_nt(dpm2, pb.wmemT, prec).reshape(B, Tin, D)        # through processed_memory
             _ctx_memory_grad(sv["align"], wk["dctx_all"], g_memory, prec)        # through the context bmm
         g_v = wk["dv_part"].sum(0).reshape(1, -1)
-        if ctx.v2:
-            # chain rule through the pre-multiplied location filter U[a][ch*KS+k] = sum_c dense[a][c] conv[c][ch][k]
-            dU = wk["dU_part"].sum(0)[:d.att_dim, :2 * d.loc_kernel]
-            g_wd = dU @ pk.wconv.reshape(d.loc_filters, 2 * d.loc_kernel).t()
-            g_wc = (pk.wdense.t() @ dU).reshape(d.loc_filters, 2, d.loc_kernel)
-        else:
-            g_wd = wk["dwd_part"].sum(0).reshape(d.att_dim, d.loc_filters)
-            g_wc = wk["dwc_part"].sum(0).reshape(d.loc_filters, 2, d.loc_kernel)
+        # chain rule through the pre-multiplied location filter U[a][ch*KS+k] = sum_c dense[a][c] conv[c][ch][k]
+        dU = wk["dU_part"].sum(0)[:d.att_dim, :2 * d.loc_kernel]
+        g_wd = dU @ pk.wconv.reshape(d.loc_filters, 2 * d.loc_kernel).t()
+        g_wc = (pk.wdense.t() @ dU).reshape(d.loc_filters, 2, d.loc_kernel)
         grads = [g_w_ih_a, g_w_hh_a, g_b_a, g_b_a.clone(), g_w_ih_d, g_w_hh_d, g_b_d, g_b_d.clone(),
                  g_wpg[:d.n_mel].contiguous(), g_bpg[:d.n_mel].contiguous(), g_wpg[d.n_mel:].contiguous(),
                  g_bpg[d.n_mel:].contiguous(), g_w_pre1, g_w_pre2, g_wq, g_wmem, g_v, g_wc, g_wd]

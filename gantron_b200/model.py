@@ -64,7 +64,7 @@ class LocationLayer(nn.Module):
         self.location_dense = LinearNorm(attention_n_filters, attention_dim, bias=False, w_init_gain='tanh')
 
     def forward(self, attention_weights_cat):
-        # stand-alone convenience (the decoder kernels fuse this layer; see gtn_decoder_fwd.cu phase B)
+        # stand-alone convenience (the decoder kernels fuse this layer; see gtn_decoder_fwd2.cu phase B)
         return self.location_dense(self.location_conv(attention_weights_cat).transpose(1, 2))
 
 
@@ -100,11 +100,12 @@ class Prenet(nn.Module):
     def __init__(self, in_dim, sizes):
         super().__init__()
         self.layers = nn.ModuleList([LinearNorm(i, o, bias=False) for i, o in zip([in_dim] + sizes[:-1], sizes)])
+        self._prec = _precision_of(None)       # the owning Decoder overwrites this with its hparams' precision
 
     def forward(self, x):
         from . import decoder_ops
         _require_cuda(x, "Prenet")
-        return decoder_ops.prenet_forward(self, x, seed=_new_seed(self))
+        return decoder_ops.prenet_forward(self, x, seed=_new_seed(self), prec=self._prec)
 
 
 class Postnet(nn.Module):
@@ -178,7 +179,7 @@ class Encoder(nn.Module):
 
 class Decoder(nn.Module):
     """Tacotron2 decoder (model.py:227-497).  Parameters as in the reference; both loops run as a single
-    persistent cooperative sm_100a kernel (gtn_decoder_fwd.cu / gtn_decoder_bwd.cu)."""
+    persistent clustered sm_100a kernel (gtn_decoder_fwd2.cu / gtn_decoder_bwd2.cu)."""
 
     def __init__(self, hparams):
         super().__init__()
@@ -211,6 +212,7 @@ class Decoder(nn.Module):
         self.linear_projection = LinearNorm(hp.decoder_rnn_dim + d_mem, hp.n_mel_channels * hp.n_frames_per_step)
         self.gate_layer = LinearNorm(hp.decoder_rnn_dim + d_mem, 1, bias=True, w_init_gain='sigmoid')
         self._prec = _precision_of(hp)
+        self.prenet._prec = self._prec
         self._attention_dim = hp.attention_dim
         self._loc = (hp.attention_location_n_filters, hp.attention_location_kernel_size)
         self._packed = None
@@ -263,7 +265,7 @@ class Decoder(nn.Module):
         if self.noise_size > 0 or style.numel() > 0:
             memory = torch.cat([memory, style.to(memory.dtype)], dim=-1)
         mel, gate, align, lengths, steps = decoder_ops.decoder_inference(
-            self.packed(), memory, max_steps=self.max_decoder_steps, gate_threshold=self.gate_threshold,
+            self, memory, max_steps=self.max_decoder_steps, gate_threshold=self.gate_threshold,
             seed=_new_seed(self), prec=self._prec, const_tail=const_tail)
         self.last_lengths = lengths
         if steps == self.max_decoder_steps and bool((lengths >= steps).any()) and not bool(

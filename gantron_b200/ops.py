@@ -202,7 +202,7 @@ def bn_act_fwd(y: torch.Tensor, mean, rstd, gamma, beta, act: int, dropout: Tupl
 
 
 def bn_act_bwd(dx: torch.Tensor, y: torch.Tensor, mean, rstd, gamma, beta, act: int, dropout: Tuple[float, int, int],
-               dy: torch.Tensor, want_dbias: bool = True):
+               dy: torch.Tensor, want_dbias: bool = True, batch_stats: bool = True):
     rows, C, lddx = _rows_c(dx, "dx")
     r2, C2, ldy = _rows_c(y, "y")
     r3, C3, lddy = _rows_c(dy, "dy")
@@ -211,7 +211,8 @@ def bn_act_bwd(dx: torch.Tensor, y: torch.Tensor, mean, rstd, gamma, beta, act: 
     dgamma, dbeta = torch.empty(C, device=dev), torch.empty(C, device=dev)
     dbias = torch.empty(C, device=dev) if want_dbias else None
     p, seed, site = dropout
-    rc = _lib.load().gtn_bn_act_bwd(_lib.ptr(dx), _dt(dx), lddx, _lib.ptr(y), _dt(y), ldy, rows, C, _lib.ptr(mean),
+    fn = _lib.load().gtn_bn_act_bwd if batch_stats else _lib.load().gtn_bn_act_bwd_eval
+    rc = fn(_lib.ptr(dx), _dt(dx), lddx, _lib.ptr(y), _dt(y), ldy, rows, C, _lib.ptr(mean),
                                     _lib.ptr(rstd), _lib.ptr(gamma), _lib.ptr(beta), act, float(p), int(seed), int(site),
                                     _lib.ptr(dgamma), _lib.ptr(dbeta), _lib.ptr(dy), _dt(dy), lddy, _lib.ptr(dbias),
                                     _lib.stream())

@@ -88,8 +88,6 @@ class _PostnetFn(torch.autograd.Function):
     @once_differentiable
     def backward(ctx, g):
         postnet, prec, saved = ctx.postnet, ctx.prec, ctx.saved
-        if not ctx.training:
-            raise RuntimeError("gantron_b200 Postnet: backward through eval-mode BatchNorm is not implemented")
         B, C0, T = ctx.shape
         dev = g.device
         adt = BF16 if prec == 1 else torch.float32
@@ -106,7 +104,9 @@ class _PostnetFn(torch.autograd.Function):
             k, pad = conv.kernel_size[0], conv.padding[0]
             cout, cin = w.shape[0], w.shape[1]
             dy = torch.empty(B, T, cout, device=dev, dtype=adt)
-            dgamma, dbeta, dbias = ops.bn_act_bwd(dx, y, mean, rstd, gamma.detach(), beta.detach(), act, drop, dy)
+            # eval mode: running statistics are constants (no batch-coupling terms)
+            dgamma, dbeta, dbias = ops.bn_act_bwd(dx, y, mean, rstd, gamma.detach(), beta.detach(), act, drop, dy,
+                                                  batch_stats=ctx.training)
             grads[4 * i + 1], grads[4 * i + 2], grads[4 * i + 3] = dbias, dgamma, dbeta
             dyo, xo = wgrad_operands(dy, x_in, prec)
             dw = torch.empty(k, cout, cin, device=dev)

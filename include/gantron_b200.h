@@ -91,12 +91,17 @@ int gtn_bn_finalize(const float* stats, int C, long long count, float eps, float
 int gtn_bn_act_fwd(const void* y, int y_dtype, long long ldy, long long rows, int C, const float* mean, const float* rstd,
                    const float* gamma, const float* beta, int act, float drop_p, unsigned long long seed, int site,
                    void* out, int out_dtype, long long ldo, void* stream);
-/* Backward of the same through batch statistics: given dx (gradient w.r.t. `out`) and the saved conv output y,
+/* Backward of the same through batch statistics (gtn_bn_act_bwd) or through fixed running statistics
+ * (gtn_bn_act_bwd_eval: module.eval(), mean / rstd are constants: dy = gamma * rstd * dz): given dx (gradient w.r.t. `out`) and the saved conv output y,
  * writes dgamma, dbeta [C], dy (gradient w.r.t. y) and optionally dbias[c] = sum_rows dy (conv bias gradient). */
 int gtn_bn_act_bwd(const void* dx, int dx_dtype, long long lddx, const void* y, int y_dtype, long long ldy, long long rows,
                    int C, const float* mean, const float* rstd, const float* gamma, const float* beta, int act,
                    float drop_p, unsigned long long seed, int site, float* dgamma, float* dbeta, void* dy, int dy_dtype,
                    long long lddy, float* dbias, void* stream);
+int gtn_bn_act_bwd_eval(const void* dx, int dx_dtype, long long lddx, const void* y, int y_dtype, long long ldy,
+                        long long rows, int C, const float* mean, const float* rstd, const float* gamma,
+                        const float* beta, int act, float drop_p, unsigned long long seed, int site, float* dgamma,
+                        float* dbeta, void* dy, int dy_dtype, long long lddy, float* dbias, void* stream);
 /* DiscConv1d backward through Tanh(Dropout(pre)) (layers.py:53-57): dpre = dout * (1 - a^2) * keep / (1 - p), a = the
  * saved layer output; dbias[c] = sum_rows dpre (optional). */
 int gtn_drop_tanh_bwd(const void* dout, int dout_dtype, long long lddo, const void* a, int a_dtype, long long lda,
@@ -128,7 +133,7 @@ int gtn_attn_guide_loss_fwd(const float* align, int B, int T, int Tin, const lon
 int gtn_attn_guide_loss_bwd(const float* align, int B, int T, int Tin, const long long* enc_len, const long long* dec_len,
                             float width, const float* gloss, float* dalign, void* stream);
 
-/* ---- persistent cooperative decoder, forward (gtn_decoder_fwd.cu) ------------------------------
+/* ---- persistent clustered decoder, forward (gtn_decoder_fwd2.cu) --------------------------------
  * One launch = all frames of Decoder.inference (model.py:456-497; train = 0) or of the teacher-forced
  * loop of Decoder.forward (model.py:419-454; train = 1).  The struct lives in HOST memory.
  *
@@ -201,65 +206,14 @@ typedef struct gtn_decoder_fwd_params {
   int Ep, reserved0;
 } gtn_decoder_fwd_params;
 
-int gtn_decoder_forward(const gtn_decoder_fwd_params* params, void* stream);
-/* Same contract, second generation: clusters of 4 CTAs split K of every per-frame GEMM and run it on tcgen05 with
- * TMA-fed operands (gtn_decoder_fwd2.cu); requires all K pads to be multiples of 64 and qpart sized [Ha/32][B][A].
+/* Clusters of 4 CTAs split K of every per-frame GEMM and run it on tcgen05 with TMA-fed operands
+ * (gtn_decoder_fwd2.cu); requires all K pads to be multiples of 64 and qpart sized [Ha/32][B][A].
  * Does not write f_all (the location filter is pre-multiplied; the backward pass works on U); gates_a / gates_d are
- * saved as [T][B][H][4] (i,f,g,o per unit). */
+ * saved as [T][B][H][4] (i,f,g,o per unit).  (The mma.sync first generation of these kernels, gtn_decoder_forward /
+ * gtn_decoder_backward, was removed in round 2; the entry points keep their "2" suffix.) */
 int gtn_decoder_forward2(const gtn_decoder_fwd_params* params, void* stream);
 
-/* ---- persistent cooperative decoder, backward through time (gtn_decoder_bwd.cu) -----------------
- * Replaces autograd's replay of the ~22k-node tape of model.py:444-449 (BPTT over T frames) with one
- * cooperative launch.  Per frame (t = T-1 .. 0), three grid-synchronised phases:
- *   1  data-gradient GEMMs  dX = dGates . W  for decoder_rnn(t) and attention_rnn(t+1)
- *   2  attention backward per sequence (context, softmax, energies, location dense + conv)
- *   3  query backward GEMM + attention LSTM cell backward  ||  decoder LSTM cell backward of frame t-1
- * All WEIGHT gradients are deferred: the kernel only stores per-frame gate / query gradients, and the
- * host issues a handful of K = T*B tcgen05 GEMMs afterwards (gtn_gemm_tn_bf16). */
-typedef struct gtn_decoder_bwd_params {
-  int B, Tin, ldT, T;
-  int E, Cc, D, Ha, Hd, P, A, Ap, F, KS;
-  int prec, mult;
-  int use_dropout, mem_bf16;
-  float p_att, p_dec;
-  unsigned int thr_att, thr_dec;
-  unsigned long long seed;
-  /* transposed packed weights: rows = LSTM input features, K = mult * 4H gate rows (padded to 32 rows) */
-  const void *wT_att;        /* [pad32(P+D+Ha)][mult*4Ha]  rows = [prenet | ctx | h_att] */
-  const void *wT_dec;        /* [pad32(Ha+D+Hd)][mult*4Hd] rows = [h_att | ctx | h_dec]  */
-  const void *wqT;           /* [Ha][mult*Ap]   wqT[u][a] = query_layer[a][u] */
-  const float *v, *wconv, *wdense;
-  /* forward inputs */
-  const void *mem_enc; const float *mem_const; const int *lengths;
-  /* saved by the forward kernel */
-  const float *gates_a, *c_a_all, *gates_d, *c_d_all;
-  const float *align;        /* [B][T][Tin] */
-  const float *th_all, *f_all, *cum_all;
-  /* upstream gradients */
-  const float *dproj_all;    /* [T][B][Hd + D]: d(loss)/d[h_dec' | ctx'] through the mel/gate projection */
-  const float *dalign;       /* [B][T][Tin] or NULL */
-  /* carried state / workspace (zero-initialised) */
-  void *xdg_a, *xdg_d;       /* bf16 [B][mult*4Ha], [B][mult*4Hd]: gate gradients as GEMM operands */
-  void *xdq;                 /* bf16 [B][mult*Ap] */
-  float *carry_ha, *dha_dec, *dc_a;     /* [B][Ha] */
-  float *carry_hd, *dc_d;               /* [B][Hd] */
-  float *dctx_att, *dctx_dec;           /* [B][D] */
-  float *dwprev, *dcum;                 /* [B][ldT] */
-  unsigned int *barrier;
-  /* outputs */
-  float *dga_all, *dgd_all;  /* [T][B][4Ha], [T][B][4Hd] pre-activation gate gradients */
-  float *dq_all;             /* [T][B][A] */
-  float *dpre_all;           /* [T][B][P] gradient w.r.t. the prenet outputs */
-  float *dctx_all;           /* [B][T][D] total context gradient per frame */
-  float *dpm;                /* [B][Tin][A] gradient w.r.t. processed_memory (accumulated over frames) */
-  float *dv_part, *dwd_part, *dwc_part; /* per-CTA partial sums: [grid][A], [grid][A*F], [grid][F*2*KS] */
-  int grid;                  /* filled in by gtn_decoder_bwd_grid() so the caller can size the partials */
-} gtn_decoder_bwd_params;
-
-int gtn_decoder_bwd_grid(void);   /* number of CTAs gtn_decoder_backward launches on the current device */
-int gtn_decoder_backward(const gtn_decoder_bwd_params* params, void* stream);
-
-/* ---- persistent clustered decoder, backward through time, second generation (gtn_decoder_bwd2.cu) ----
+/* ---- persistent clustered decoder, backward through time (gtn_decoder_bwd2.cu) --------------------
  * Counterpart of gtn_decoder_forward2 (same cluster-split tcgen05 GEMM engine).  Per frame t = T-1 .. 0:
  *   P1  dX_dec = W_dec^T dGates_dec(t) (rows [h_att | ctx_enc | h_dec]) and dX_att = W_att^T dGates_att(t+1)
  *       (rows [ctx_enc | h_att]); the decoder LSTM cell backward of frame t-1 is fused into the h_dec rows' epilogue

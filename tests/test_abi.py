@@ -26,7 +26,7 @@ def lib():
 
 def test_header_declares_the_expected_families():
     names = declared_functions()
-    for must in ("gtn_decoder_forward", "gtn_decoder_backward", "gtn_gemm_bf16", "gtn_conv1d_bf16", "gtn_last_error"):
+    for must in ("gtn_decoder_forward2", "gtn_decoder_backward2", "gtn_gemm_bf16", "gtn_conv1d_bf16", "gtn_last_error"):
         assert must in names
     assert len(names) >= 25
 
@@ -44,14 +44,13 @@ def test_binding_signatures_cover_the_header():
 def test_struct_sizes_match_the_binding(lib):
     from gantron_b200 import _lib
     assert lib.gtn_sizeof(0) == C.sizeof(_lib.DecoderFwdParams)
-    assert lib.gtn_sizeof(1) == C.sizeof(_lib.DecoderBwdParams)
     assert lib.gtn_sizeof(2) == C.sizeof(_lib.DecoderBwd2Params)
     assert lib.gtn_version() >= 100
 
 
 def test_errors_are_reported_not_swallowed(lib):
     from gantron_b200 import _lib
-    rc = lib.gtn_decoder_forward(None, None)
+    rc = lib.gtn_decoder_forward2(None, None)
     assert rc != 0 and "null" in _lib.last_error().lower()
 
 

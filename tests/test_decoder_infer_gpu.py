@@ -49,7 +49,7 @@ def test_infer_fp32_mode_matches_oracle(B, T_in, steps):
     hp, dec, memory = _setup(B, T_in, steps, "fp32")
     seed = 0xABCDEF12345
     mel, gate, align, lengths, n = decoder_ops.decoder_inference(
-        dec.packed(), memory.cuda(), max_steps=steps, gate_threshold=0.5, seed=seed, prec=3, ignore_stop=True)
+        dec, memory.cuda(), max_steps=steps, gate_threshold=0.5, seed=seed, prec=3, ignore_stop=True)
     om, og, oa, ol, _ = _oracle(hp, dec, memory, steps, seed)
     assert n == steps
     assert_close(align, oa, "alignments", atol=2e-5, rtol=1e-3)
@@ -62,7 +62,7 @@ def test_infer_nonconstant_style_uses_full_memory():
     hp, dec, memory = _setup(2, 19, 4, "fp32", style_const=False)
     seed = 77
     mel, gate, align, lengths, n = decoder_ops.decoder_inference(
-        dec.packed(), memory.cuda(), max_steps=4, gate_threshold=0.5, seed=seed, prec=3, ignore_stop=True)
+        dec, memory.cuda(), max_steps=4, gate_threshold=0.5, seed=seed, prec=3, ignore_stop=True)
     om, og, oa, _, _ = _oracle(hp, dec, memory, 4, seed)
     assert_close(align, oa, "alignments", atol=2e-5, rtol=1e-3)
     assert_close(mel, om, "mel", atol=2e-4, rtol=1e-3)
@@ -74,7 +74,7 @@ def test_infer_bf16_mode_close_to_oracle():
     hp, dec, memory = _setup(4, 31, 5, "bf16")
     seed = 4242
     mel, gate, align, lengths, n = decoder_ops.decoder_inference(
-        dec.packed(), memory.cuda(), max_steps=5, gate_threshold=0.5, seed=seed, prec=1, ignore_stop=True)
+        dec, memory.cuda(), max_steps=5, gate_threshold=0.5, seed=seed, prec=1, ignore_stop=True)
     om, og, oa, _, _ = _oracle(hp, dec, memory, 5, seed)
     assert_close(align, oa, "alignments bf16", atol=2e-2, rtol=0)
     assert_close(mel, om, "mel bf16", atol=3e-2, rtol=3e-2)
@@ -87,7 +87,7 @@ def test_infer_stops_on_gate_like_reference():
     hp, dec, memory = _setup(1, 17, 8, "fp32")
     dec.gate_layer.linear_layer.bias.data.fill_(30.0)
     mel, gate, align, lengths, n = decoder_ops.decoder_inference(
-        dec.packed(), memory.cuda(), max_steps=8, gate_threshold=0.5, seed=5, prec=3)
+        dec, memory.cuda(), max_steps=8, gate_threshold=0.5, seed=5, prec=3)
     om, og, oa, ol, _ = _oracle(hp, dec, memory, 8, 5, force=False)
     assert n == om.shape[-1] == 1 and tuple(mel.shape) == tuple(om.shape)
     assert int(lengths[0]) == int(ol[0]) == 1

@@ -146,7 +146,7 @@ def test_infer_b1_1000_forced_steps(prec):
     steps, seed = 1000, 0x1000
     hp, dec, memory = TI._setup(1, 150, steps, prec, seed=5)
     mel, gate, align, lengths, n = decoder_ops.decoder_inference(
-        dec.packed(), memory.cuda(), max_steps=steps, gate_threshold=0.5, seed=seed, prec=3 if prec == "fp32" else 1,
+        dec, memory.cuda(), max_steps=steps, gate_threshold=0.5, seed=seed, prec=3 if prec == "fp32" else 1,
         ignore_stop=True)
     key = "infer1000"
     if key not in _ORACLE_CACHE:
@@ -212,7 +212,7 @@ def test_infer_batch8_rows_stop_independently():
     B, T_in, steps, seed = 8, 37, 24, 21
     hp, dec, memory, plan = _gate_setup(B, T_in, steps, seed, 3)
     mel, gate, align, lengths, n = decoder_ops.decoder_inference(
-        dec.packed(), memory.cuda(), max_steps=steps, gate_threshold=0.5, seed=seed, prec=3)
+        dec, memory.cuda(), max_steps=steps, gate_threshold=0.5, seed=seed, prec=3)
     d = O.Dims.from_hparams(hp)
     d.spk = d.emo = 0
     sd = {"decoder." + k: v.detach().float().cpu() for k, v in dec.state_dict().items()}
@@ -241,7 +241,7 @@ def test_infer_batch8_loop_ends_when_all_rows_fired():
     om, og, oa, ol, _ = TI._oracle(hp, dec, memory, steps, seed, force=False)
     assert ol.tolist() == plan
     mel, gate, align, lengths, n = decoder_ops.decoder_inference(
-        dec.packed(), memory.cuda(), max_steps=steps, gate_threshold=0.5, seed=seed, prec=3)
+        dec, memory.cuda(), max_steps=steps, gate_threshold=0.5, seed=seed, prec=3)
     assert n == om.shape[2] == int(ol.max()) and n < steps
     assert lengths.cpu().tolist() == ol.tolist() and len(set(ol.tolist())) > 1
     assert_close(mel, om, "mel", atol=2e-4, rtol=1e-3)

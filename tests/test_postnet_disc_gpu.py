@@ -108,6 +108,61 @@ def test_postnet_eval_mode_uses_running_stats():
     assert_close(y, yo, "postnet eval", atol=2e-4, rtol=1e-3)
 
 
+def test_postnet_eval_mode_backward():
+    """Backward through eval-mode BatchNorm (running statistics are constants): the reference supports it
+    (autograd through model.py:146-151 with self.training False)."""
+    from gantron_b200.model import Postnet
+    from oracle import gantron_oracle as O
+    torch.manual_seed(4)
+    hp = _hp("fp32")
+    net = Postnet(hp).cuda().eval()
+    with torch.no_grad():
+        for seq in net.convolutions:
+            seq[1].running_mean.uniform_(-0.2, 0.2); seq[1].running_var.uniform_(0.5, 1.5)
+            seq[1].weight.uniform_(0.5, 1.5); seq[1].bias.uniform_(-0.3, 0.3)
+    g = torch.Generator().manual_seed(6)
+    x, R = torch.randn(2, 80, 41, generator=g), torch.randn(2, 80, 41, generator=g)
+    sd = _sd_cpu(net, "postnet.")
+    xg = x.cuda().requires_grad_(True)
+    (net(xg) * R.cuda()).sum().backward()
+    xo = x.clone().requires_grad_(True)
+    (O.postnet(sd, xo, O.Dims.from_hparams(hp), None, False) * R).sum().backward()
+    assert _rel(xg.grad, xo.grad) <= 1e-3, f"d(input) {_rel(xg.grad, xo.grad):.3e}"
+    worst = sorted(((_rel(p.grad, sd['postnet.' + k].grad), k) for k, p in net.named_parameters()), reverse=True)
+    assert worst[0][0] <= 1e-3, "postnet eval grads: " + "; ".join(f"{k} {e:.2e}" for e, k in worst[:6])
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+def test_prenet_module_forward_backward(prec):
+    """Stand-alone Prenet.forward (model.py:102-105): honours b200_precision and is differentiable (input + weights)."""
+    from gantron_b200.model import Decoder
+    from oracle import gantron_oracle as O, philox as PX
+    torch.manual_seed(8)
+    dec = Decoder(_hp(prec)).cuda()
+    pre = dec.prenet
+    assert pre._prec == (3 if prec == "fp32" else 1)
+    pre._forced_seed = 4242
+    g = torch.Generator().manual_seed(9)
+    x, R = torch.randn(5, 3, 80, generator=g), torch.randn(5, 3, 256, generator=g)
+    xg = x.cuda().requires_grad_(True)
+    y = pre(xg)
+    (y * R.cuda()).sum().backward()
+    w1 = pre.layers[0].linear_layer.weight.detach().cpu().clone().requires_grad_(True)
+    w2 = pre.layers[1].linear_layer.weight.detach().cpu().clone().requires_grad_(True)
+    k1 = torch.from_numpy(PX.keep_mask(4242, PX.SITE_PRENET1, 0, (15, 256), 0.5)).reshape(5, 3, 256)
+    k2 = torch.from_numpy(PX.keep_mask(4242, PX.SITE_PRENET2, 0, (15, 256), 0.5)).reshape(5, 3, 256)
+    xo = x.clone().requires_grad_(True)
+    yo = O.prenet(xo, w1, w2, k1, k2)
+    (yo * R).sum().backward()
+    # bf16: relu decisions of bf16-rounded pre-activations near 0 flip (same bound as the decoder tests: 8e-2 Frobenius)
+    tol, gtol = (1e-3, 1e-3) if prec == "fp32" else (3e-2, 8e-2)
+    l2 = prec != "fp32"
+    assert _rel(y, yo, l2) <= tol, f"prenet out {_rel(y, yo, l2):.3e}"
+    assert _rel(xg.grad, xo.grad, l2) <= gtol, f"d(input) {_rel(xg.grad, xo.grad, l2):.3e}"
+    assert _rel(pre.layers[0].linear_layer.weight.grad, w1.grad, l2) <= gtol
+    assert _rel(pre.layers[1].linear_layer.weight.grad, w2.grad, l2) <= gtol
+
+
 @pytest.mark.parametrize("prec,B,T,train_d", [("fp32", 3, 173, True), ("fp32", 2, 200, False), ("bf16", 4, 415, True)])
 def test_discriminator_adversarial_loss(prec, B, T, train_d):
     """adversarial_loss incl. the tail-window cat (T % 20 != 0), the raw reshape, dropout -> tanh order, masked mean."""

@@ -40,7 +40,7 @@ def main():
         mem = torch.cat((torch.randn(Bi, Tin, 512).cuda() * 0.5, torch.rand(Bi, 1, 512).repeat_interleave(Tin, 1).cuda()), -1)
         for it in range(2):
             torch.cuda.synchronize(); t0 = time.perf_counter()
-            out = decoder_ops.decoder_inference(dec.packed(), mem, max_steps=1000, gate_threshold=0.5, seed=7, prec=1,
+            out = decoder_ops.decoder_inference(dec, mem, max_steps=1000, gate_threshold=0.5, seed=7, prec=1,
                                                 const_tail=True, ignore_stop=True)
             torch.cuda.synchronize(); t1 = time.perf_counter()
             print(f"infer B={Bi}: {1e3*(t1-t0):.1f} ms for {out[4]} steps -> {1e6*(t1-t0)/out[4]:.1f} us/step, {Bi*out[4]/(t1-t0):.0f} frames/s", flush=True)

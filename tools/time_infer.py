@@ -22,7 +22,7 @@ for ver in ("2",):
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             torch.cuda.synchronize()
             e0.record()
-            r = decoder_ops.decoder_inference(dec.packed(), mem, max_steps=steps, gate_threshold=0.5, seed=7, prec=1,
+            r = decoder_ops.decoder_inference(dec, mem, max_steps=steps, gate_threshold=0.5, seed=7, prec=1,
                                               const_tail=True, ignore_stop=True)
             e1.record()
             torch.cuda.synchronize()
@@ -52,7 +52,7 @@ if os.environ.get("GTN_PROF"):
         else:
             dec.eval()
             mem = torch.cat((torch.randn(B, 150, 512).cuda() * 0.5, torch.rand(B, 1, 512).repeat_interleave(150, 1).cuda()), -1)
-            decoder_ops.decoder_inference(dec.packed(), mem, max_steps=16, gate_threshold=0.5, seed=7, prec=1, const_tail=True,
+            decoder_ops.decoder_inference(dec, mem, max_steps=16, gate_threshold=0.5, seed=7, prec=1, const_tail=True,
                                           ignore_stop=True)
         torch.cuda.synchronize()
         pr = prof.cpu().view(16, 32)
