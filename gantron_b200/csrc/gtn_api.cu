@@ -1,6 +1,8 @@
 // C-ABI entry points (library plumbing + the GEMM family).  See include/gantron_b200.h.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <atomic>
 #include "gtn_common.cuh"
 #include "gtn_internal.h"
@@ -18,6 +20,17 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+bool profiler_attached() {
+  static const bool on = [] {
+    for (const char* v : {"GTN_NO_COOP", "CUDA_INJECTION64_PATH", "NV_NSIGHT_INJECTION_PORT_BASE", "NV_NSIGHT_INJECTION_TRANSPORT_TYPE",
+                          "NV_COMPUTE_PROFILER_PERFWORKS_DIR", "NVTX_INJECTION64_PATH"})
+      if (getenv(v) != nullptr) return true;
+    const char* pre = getenv("LD_PRELOAD");
+    return pre != nullptr && (strstr(pre, "nsight") != nullptr || strstr(pre, "ncu") != nullptr || strstr(pre, "nvperf") != nullptr);
+  }();
+  return on;
+}
 
 }  // namespace gtn
 

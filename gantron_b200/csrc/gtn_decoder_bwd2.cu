@@ -925,7 +925,7 @@ static int launch_bwd2(const Bwd2Maps& maps, const DecBwd2& p, int ncl, cudaStre
   int rc = bwd2_config<N>(cfg, attrs, S, smem);
   if (rc) return rc;
   cfg.stream = st;
-  cfg.numAttrs = getenv("GTN_NO_COOP") ? 1 : 2;   // profilers that cannot replay cooperative launches
+  cfg.numAttrs = profiler_attached() ? 1 : 2;   // profilers that cannot replay cooperative launches
   // each CTA pair stages the encoder lengths of at most 8 sequences (scr + 48): B <= 16 * clusters
   GTN_REQUIRE((p.B + 2 * ncl - 1) / (2 * ncl) <= 8, "decoder backward: batch %d needs more than 8 sequences per CTA pair on %d clusters",
               p.B, ncl);

@@ -19,20 +19,9 @@
 // Grid barriers: after A, after B (training: C(t) and A(t+1) share an interval since A does not read h_dec).
 // Training additionally saves what the backward kernel needs.  The time-constant columns of `memory`
 // (noise / speaker / emotion: model.py:275-278,655-663) are not re-read per frame: context = const * sum_j w_j.
-#include <cstdlib>
-#include "gtn_decoder2.cuh"
-#include "gtn_internal.h"
-#include "../../include/gantron_b200.h"
+#include "gtn_decoder_fwd.cuh"
 
 namespace gtn {
-
-typedef gtn_decoder_fwd_params DecFwd;
-#define BFP(x) (reinterpret_cast<bf16*>(const_cast<void*>(static_cast<const void*>(x))))
-
-struct Fwd2Maps {
-  CUtensorMap w_att, w_dec, w_pre1, w_pre2, w_proj, uloc;
-  CUtensorMap pre, ctx, ha, hd, xmel, xp1, xp2;
-};
 
 #define PROF(slot)                                                                          \
   do {                                                                                      \
@@ -65,10 +54,6 @@ struct Smem2 {
   uint32_t* tmem_slot;
   int res_a, res_d;    // weight k-blocks of this CTA's attention / decoder LSTM K quarter that are resident in TMEM
 };
-
-static constexpr int JH_MAX = 128;     // encoder positions per CTA of a pair (T_in <= 256)
-static constexpr int TIN_MAX = 256;
-static constexpr int KS_MAX = 63;
 
 template <int N>
 __host__ __device__ constexpr size_t fwd2_fixed_bytes() {
@@ -110,18 +95,6 @@ GTN_DEVICE Smem2 carve2(uint8_t* base, int S) {
   m.recv_full = b; b += 2;
   m.tmem_slot = reinterpret_cast<uint32_t*>(b + 1);
   return m;
-}
-
-GTN_DEVICE float block_reduce2(float v, float* scr, bool is_max) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  v = is_max ? warp_max(v) : warp_sum(v);
-  __syncthreads();
-  if (lane == 0) scr[warp] = v;
-  __syncthreads();
-  float r = scr[0];
-#pragma unroll
-  for (int w = 1; w < 8; ++w) r = is_max ? fmaxf(r, scr[w]) : r + scr[w];
-  return r;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -454,24 +427,6 @@ GTN_DEVICE void prenet_local(const DecFwd& p, Smem2& sm, int t, int rank) {
 // ------------------------------------------------------------------------------------------------
 // attention phase: one CTA pair per sequence
 // ------------------------------------------------------------------------------------------------
-template <typename MT>
-GTN_DEVICE void ld8(const MT* p, float (&o)[8]);
-template <>
-GTN_DEVICE void ld8<float>(const float* p, float (&o)[8]) {
-  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
-  o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w; o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
-}
-template <>
-GTN_DEVICE void ld8<bf16>(const bf16* p, float (&o)[8]) {
-  const uint4 q = __ldg(reinterpret_cast<const uint4*>(p));
-  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    o[2 * i] = __uint_as_float(w[i] << 16);
-    o[2 * i + 1] = __uint_as_float(w[i] & 0xFFFF0000u);
-  }
-}
-
 template <typename MT>
 GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, int cid, int ncl, uint32_t tmem_att,
                                  uint32_t& att_par, uint32_t& eround) {
@@ -848,14 +803,11 @@ static int launch_fwd2(const Fwd2Maps& maps, const DecFwd& p, int max_clusters_w
   GTN_REQUIRE((p.B + 2 * ncl - 1) / (2 * ncl) <= 8, "decoder forward: batch %d needs more than 8 sequences per CTA pair on %d clusters",
               p.B, ncl);
   cfg.gridDim = dim3(CL * ncl);
-  cfg.numAttrs = getenv("GTN_NO_COOP") ? 1 : 2;   // profilers that cannot replay cooperative launches
+  cfg.numAttrs = profiler_attached() ? 1 : 2;   // profilers that cannot replay cooperative launches
   GTN_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, maps, p, S));
   count_launch();
   return 0;
 }
-
-int make_tma_map_3d(CUtensorMap* out, const void* base, long long d0, long long d1, long long d2, long long stride1_elems,
-                    long long stride2_elems, int box1);
 
 }  // namespace gtn
 
@@ -889,7 +841,8 @@ extern "C" int gtn_decoder_forward2(const gtn_decoder_fwd_params* hp, void* stre
   rc |= make_tma_map_3d(&maps.w_att, p.w_att2, Ka, 4 * p.Ha, 1, Ka, 0, TILE_M);
   rc |= make_tma_map_3d(&maps.w_dec, p.w_dec2, Kd, 4 * p.Hd, 1, Kd, 0, TILE_M);
   rc |= make_tma_map_3d(&maps.uloc, p.u_loc, 2 * KB, p.A, 1, 2 * KB, 0, TILE_M);
-  rc |= make_tma_map_3d(&maps.ctx, p.xctx, (long long)m * p.Ep, p.B, 1, (long long)m * p.Ep, 0, N);
+  // xctx is double buffered [2][B][m Ep] (the pipelined training kernel alternates; this file's kernel uses buffer 0)
+  rc |= make_tma_map_3d(&maps.ctx, p.xctx, (long long)m * p.Ep, p.B, 2, (long long)m * p.Ep, (long long)p.B * m * p.Ep, N);
   rc |= make_tma_map_3d(&maps.ha, p.xh_a, (long long)m * p.Hap, p.B, 2, (long long)m * p.Hap, (long long)p.B * m * p.Hap, N);
   rc |= make_tma_map_3d(&maps.hd, p.xh_d, (long long)m * p.Hdp, p.B, 2, (long long)m * p.Hdp, (long long)p.B * m * p.Hdp, N);
   if (p.train) {
@@ -910,6 +863,11 @@ extern "C" int gtn_decoder_forward2(const gtn_decoder_fwd_params* hp, void* stre
   if (rc) return rc;
   const int want = (p.Ha > p.Hd ? p.Ha : p.Hd) / 32;
   cudaStream_t st = (cudaStream_t)stream;
+  if (p.train) {
+    // teacher-forced pass: the software-pipelined kernel when the shape is covered (B <= 64, one LSTM tile pair per cluster)
+    const int rc3 = launch_train_fwd3(maps, p, st);
+    if (rc3 != FWD3_NOT_COVERED) return rc3;
+  }
   if (N == 32) return launch_fwd2<32>(maps, p, want, st);
   if (N == 64) return launch_fwd2<64>(maps, p, want, st);
   if (N == 128) return launch_fwd2<128>(maps, p, want, st);

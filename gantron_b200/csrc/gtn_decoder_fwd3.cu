@@ -1,0 +1,861 @@
+// Persistent clustered decoder kernel, teacher-forced TRAINING forward, software-pipelined (third generation).
+// Same arithmetic, operands, saves and Philox sites as the train = 1 path of gtn_decoder_fwd2.cu (Decoder.forward,
+// reference model.py:419-454; decode() model.py:378-417), but the frame is scheduled around its ONLY serial chain:
+//
+//     attention LSTM A(t)  ->  all CTAs  ->  attention B(t)  ->  all CTAs  ->  A(t+1) ...
+//
+// The decoder LSTM C(t) (model.py:404-409) feeds nothing but C(t+1) and the mel/gate projection (which runs after the
+// loop), so it is taken off that chain and executed one frame late in the shadow of the grid barriers:
+//
+//   W1  wait barrier 2 of frame t-1           (ctx(t-1), h_dec(t-2) visible)
+//       issue the LATE k-blocks of A(t)       (context columns: the only operand that barrier protects) -> acc_A
+//       issue the LATE k-blocks of C(t-1)     (context + h_dec(t-2))                                      -> acc_C
+//   W2  A(t): split-K exchange, LSTM cells, dropout, saves, partial attention query
+//   W3  ARRIVE barrier 1 of frame t
+//   W4  C(t-1): split-K exchange, LSTM cells, saves          } work that does not depend on barrier 1, done while the
+//   W5  B(t) preparation: im2col of [prev | cum] weights     } other CTAs arrive
+//       (kept in shared memory), location GEMM on tcgen05
+//   W6  WAIT barrier 1
+//   W7  B(t): query gather (bulk copies), energies, masked softmax, context
+//   W8  ARRIVE barrier 2 of frame t
+//       issue the EARLY k-blocks of A(t+1) and C(t): prenet(t+1), h_att(t) -- operands that were complete before
+//       barrier 2 -- while the other CTAs arrive
+//
+// Every per-frame GEMM keeps its cluster split (4 CTAs x K quarter, gtn_decoder2.cuh) but a CTA's quarter is now made of
+// a quarter of EVERY activation segment, ordered early -> late, so that only 2 (A) + 6 (C) k-blocks per CTA remain behind
+// barrier 2; their weight k-blocks are the ones parked in tensor memory, so the post-barrier chain of A(t) is one 16 KB
+// activation load + 8 MMAs.  acc_C aliases the tensor-memory columns of the location GEMM (their lifetimes are disjoint).
+//
+// Covers B <= 64 (one sequence per CTA pair), attention_rnn_dim / 32 == decoder_rnn_dim / 32 == number of clusters;
+// anything else runs the sequential kernel of gtn_decoder_fwd2.cu.
+#include "gtn_decoder_fwd.cuh"
+
+namespace gtn {
+
+#define PROF3(slot)                                                                         \
+  do {                                                                                      \
+    if (p.prof != nullptr && blockIdx.x == 0 && threadIdx.x == 0 && t < 16) p.prof[t * 32 + (slot)] = clock64(); \
+  } while (0)
+
+static constexpr int KMAX = 64;        // k-blocks of one GEMM per CTA (fp32 mode: 6 planes x 10)
+
+struct KSched {            // this CTA's k-blocks of one per-frame GEMM, in issue order
+  int n, n_early;          // [0, n_early): operands complete before the barrier that precedes the GEMM's late part
+  short wk[KMAX];          // k-block column in the packed weight matrix
+  short xk[KMAX];          // k-block inside its activation segment
+  signed char seg[KMAX];   // activation segment 0..2
+  signed char slot[KMAX];  // tensor-memory slot of a resident weight k-block, -1 = streamed by TMA
+};
+
+struct Smem3 {
+  Ring ring;
+  uint8_t* u_s;        // [2][16 KB]  U_hi, U_lo (UMMA B operand of the location GEMM)
+  float* recv;         // [2][4][128][NC4]
+  float* hs;           // [32][NC4]
+  float* q_s;          // [128]
+  float* v_s;          // [128]
+  float* wcat;         // [2][JH + KS - 1]
+  float* e_buf;        // [2][Tin_pad]
+  float* e_part;       // [2][128]
+  float* w_s;          // [Tin_pad]
+  float* red_s;        // [8][256]
+  float* scr;          // [64]
+  float* wprev_s;      // [Tin_pad]  attention weights of the previous frame (all positions, both CTAs of the pair)
+  float* wcum_s;       // [Tin_pad]  cumulative attention weights
+  KSched* ks_a;
+  KSched* ks_c;
+  uint64_t* accA_full;
+  uint64_t* accC_full;
+  uint64_t* att_full;
+  uint64_t* u_full;
+  uint64_t* qg_full;
+  uint64_t* recv_full;  // [2]
+  uint32_t* tmem_slot;
+};
+
+template <int N>
+__host__ __device__ constexpr size_t fwd3_fixed_bytes() {
+  constexpr int NC4 = (N < 64 ? N : 64) / 4;
+  return (size_t)2 * W_TILE_BYTES + (size_t)2 * 4 * TILE_M * NC4 * 4 +
+         (size_t)(NC4 * 32 + 128 + 128 + 2 * (JH_MAX + KS_MAX - 1) + 2 * TIN_MAX + 2 * 128 + TIN_MAX + 8 * 256 + 64 + 2 * TIN_MAX) * 4 +
+         2 * ((sizeof(KSched) + 15) / 16 * 16) + 64 * 8 + 64;
+}
+
+template <int N>
+GTN_DEVICE Smem3 carve3(uint8_t* base, int S) {
+  constexpr int NC4 = (N < 64 ? N : 64) / 4;
+  Smem3 m;
+  m.ring.base = base;
+  m.ring.S = S;
+  m.ring.stage_bytes = W_TILE_BYTES + N * KB * 2;
+  m.ring.prod_it = m.ring.mma_it = 0;
+  uint8_t* p = base + (size_t)S * m.ring.stage_bytes;
+  m.u_s = p; p += 2 * W_TILE_BYTES;
+  float* f = reinterpret_cast<float*>(p);
+  m.recv = f; f += 2 * 4 * TILE_M * NC4;
+  m.hs = f; f += NC4 * 32;
+  m.q_s = f; f += 128;
+  m.v_s = f; f += 128;
+  m.wcat = f; f += 2 * (JH_MAX + KS_MAX - 1);
+  m.e_buf = f; f += 2 * TIN_MAX;
+  m.e_part = f; f += 2 * 128;
+  m.w_s = f; f += TIN_MAX;
+  m.red_s = f; f += 8 * 256;
+  m.scr = f; f += 64;
+  m.wprev_s = f; f += TIN_MAX;
+  m.wcum_s = f; f += TIN_MAX;
+  uint8_t* q = reinterpret_cast<uint8_t*>(f);
+  m.ks_a = reinterpret_cast<KSched*>(q); q += (sizeof(KSched) + 15) / 16 * 16;
+  m.ks_c = reinterpret_cast<KSched*>(q); q += (sizeof(KSched) + 15) / 16 * 16;
+  uint64_t* b = reinterpret_cast<uint64_t*>(q);
+  m.ring.full = b; b += 16;
+  m.ring.empty = b; b += 16;
+  m.accA_full = b++;
+  m.accC_full = b++;
+  m.att_full = b++;
+  m.u_full = b++;
+  m.qg_full = b++;
+  m.recv_full = b; b += 2;
+  m.tmem_slot = reinterpret_cast<uint32_t*>(b + 1);
+  return m;
+}
+
+// ---- split grid barrier (co-resident launch): thread 64 (warp 2) carries the release / acquire and the proxy fences, so
+// that the TMA / MMA warps 0 and 1 are free to issue between ARRIVE and WAIT ------------------------------------------
+GTN_DEVICE void grid_arrive(unsigned int* counter) {
+  __syncthreads();
+  if (threadIdx.x == 64) {
+    fence_proxy_async();
+    red_release_add(counter, 1u);
+  }
+}
+GTN_DEVICE void grid_wait(unsigned int* counter, unsigned int target) {
+  if (threadIdx.x == 64) {
+    long long t0 = clock64();
+    while (ld_acquire_u32(counter) < target) {
+      if (clock64() - t0 > 20000000000LL) __trap();
+    }
+    fence_proxy_async();
+  }
+  __syncthreads();
+}
+
+// ---- k-block schedule of one GEMM for this CTA -------------------------------------------------------------------------
+// Activation segments s = 0..nseg-1 with nkb[s] k-blocks each; rank r takes k-blocks [r nkb / 4, (r + 1) nkb / 4) of EVERY
+// segment; early segments first.  wbase[s] = first k-block column of the segment in the packed weight matrix.
+GTN_DEVICE void build_sched(KSched& ks, int nseg, const int* nkb, const int* wbase, const bool* late, int rank) {
+  int n = 0;
+  for (int pass = 0; pass < 2; ++pass) {
+    for (int s = 0; s < nseg; ++s) {
+      if ((int)late[s] != pass) continue;
+      const int lo = rank * nkb[s] / CL, hi = (rank + 1) * nkb[s] / CL;
+      for (int k = lo; k < hi && n < KMAX; ++k) {
+        ks.wk[n] = (short)(wbase[s] + k); ks.xk[n] = (short)k; ks.seg[n] = (signed char)s; ks.slot[n] = -1;
+        ++n;
+      }
+    }
+    if (pass == 0) ks.n_early = n;
+  }
+  ks.n = n;
+}
+
+struct XOps {                       // activation operands of one GEMM at one frame
+  const CUtensorMap* map[3];
+  int z[3];
+};
+
+// Issue k-blocks [i0, i1) of the schedule: producer = warp 0, MMA issuer = warp 1, both in warp-uniform control flow (see
+// gemm_issue in gtn_decoder2.cuh).  Consecutive resident k-blocks share a ring stage (activation tiles only).
+template <int N>
+GTN_DEVICE void issue_kblocks(const KSched& ks, int i0, int i1, const CUtensorMap* wmap, int row0, const XOps& x, Ring& rg,
+                              uint32_t tmem_acc, uint32_t tmem_base, uint32_t& started, uint64_t* commit_bar) {
+  constexpr uint32_t X_BYTES = N * KB * 2;
+  constexpr int G = (W_TILE_BYTES + X_BYTES) / X_BYTES;
+  const int warp_u = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  if (warp_u > 1) return;
+  const int S = rg.S;
+  const uint32_t stage_bytes = rg.stage_bytes;
+  uint8_t* const base = rg.base;
+  uint64_t* const full = rg.full;
+  uint64_t* const empty = rg.empty;
+  if (warp_u == 0) {
+    const uint32_t it0 = rg.prod_it;
+    int s = (int)(it0 % (uint32_t)S);
+    uint32_t par = (it0 / (uint32_t)S) & 1u;
+    uint32_t nst = 0;
+    for (int i = i0; i < i1;) {
+      const bool res = ks.slot[i] >= 0;
+      int n = 1;
+      if (res) while (n < G && i + n < i1 && ks.slot[i + n] >= 0) ++n;
+      wait_bar(&empty[s], par ^ 1u);
+      uint8_t* st = base + (size_t)s * stage_bytes;
+      if (elect_one()) {
+        if (res) {
+          mbar_expect_tx(&full[s], (uint32_t)n * X_BYTES);
+          for (int j = 0; j < n; ++j) {
+            const int sg = ks.seg[i + j];
+            tma_load_3d(st + (size_t)j * X_BYTES, x.map[sg], &full[s], ks.xk[i + j] * KB, 0, x.z[sg]);
+          }
+        } else {
+          const int sg = ks.seg[i];
+          mbar_expect_tx(&full[s], W_TILE_BYTES + X_BYTES);
+          tma_load_3d(st, wmap, &full[s], ks.wk[i] * KB, row0, 0);
+          tma_load_3d(st + W_TILE_BYTES, x.map[sg], &full[s], ks.xk[i] * KB, 0, x.z[sg]);
+        }
+      }
+      __syncwarp();
+      if (++s == S) { s = 0; par ^= 1u; }
+      i += n;
+      ++nst;
+    }
+    rg.prod_it = it0 + nst;
+  } else {
+    const uint32_t idesc = umma_idesc_bf16(TILE_M, N);
+    const uint32_t it0 = rg.mma_it;
+    int s = (int)(it0 % (uint32_t)S);
+    uint32_t par = (it0 / (uint32_t)S) & 1u;
+    uint32_t nst = 0;
+    for (int i = i0; i < i1;) {
+      const bool res = ks.slot[i] >= 0;
+      int n = 1;
+      if (res) while (n < G && i + n < i1 && ks.slot[i + n] >= 0) ++n;
+      wait_bar(&full[s], par);
+      tc_fence_after();
+      const uint32_t a = smem_u32(base + (size_t)s * stage_bytes);
+      if (res) {
+        for (int j = 0; j < n; ++j) {
+          const uint32_t ta = tmem_base + res_col<N>(ks.slot[i + j]);
+          const uint64_t db = umma_desc_sw128(a + (uint32_t)j * X_BYTES);
+          if (elect_one()) {
+#pragma unroll
+            for (int k = 0; k < KB / 16; ++k)
+              umma_bf16_ts(tmem_acc, ta + (uint32_t)(8 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)(started | (k > 0)));
+          }
+          started = 1u;
+        }
+      } else {
+        const uint64_t da = umma_desc_sw128(a), db = umma_desc_sw128(a + W_TILE_BYTES);
+        if (elect_one()) {
+#pragma unroll
+          for (int k = 0; k < KB / 16; ++k)
+            umma_bf16(tmem_acc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)(started | (k > 0)));
+        }
+        started = 1u;
+      }
+      if (elect_one()) umma_commit(&empty[s]);
+      __syncwarp();
+      if (++s == S) { s = 0; par ^= 1u; }
+      i += n;
+      ++nst;
+    }
+    if (commit_bar != nullptr && elect_one()) umma_commit(commit_bar);
+    rg.mma_it = it0 + nst;
+    __syncwarp();
+  }
+}
+
+// ---- LSTM epilogue of one GEMM tile: split-K exchange, cell, dropout, saves, next-frame operand ---------------------------
+// tc = frame index of the cell.  c_reg: this thread's cell states, carried in registers over the whole launch (a thread owns
+// the same (unit, sequence) pairs in every frame).
+template <int N, bool IS_ATT>
+GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int rank, bool has_work, uint32_t tmem_acc,
+                              uint64_t* acc_full, uint32_t& acc_par, uint32_t& round, float (&c_reg)[32 * (N < 64 ? N : 64) / 4 / 256],
+                              float (&wqr)[32]) {
+  constexpr int CH = N < 64 ? N : 64;
+  constexpr int NC4 = CH / 4;
+  constexpr int CPT = 32 * NC4 / 256;
+  static_assert(N <= 64, "one exchange chunk per tile");
+  const int mult = p.mult, nxt = (tc & 1) ^ 1;
+  const int H = IS_ATT ? p.Ha : p.Hd, Hp = IS_ATT ? p.Hap : p.Hdp;
+  const int t = tc;                                  // (PROF3)
+  if ((threadIdx.x >> 5) >= 4 && has_work) {
+    wait_bar(acc_full, acc_par);
+    tc_fence_after();
+  }
+  if (has_work) acc_par ^= 1u;
+  PROF3(IS_ATT ? 2 : 10);
+  float* recv = sm.recv + (size_t)(round & 1u) * 4 * TILE_M * NC4;
+  const uint32_t xr = round;
+  ++round;
+  const int bbase = rank * NC4;
+  float4 gb[CPT];
+  {
+    const float4* gbias = reinterpret_cast<const float4*>(IS_ATT ? p.gbias_a : p.gbias_d);
+    const float* b0 = IS_ATT ? p.b_att : p.b_dec;
+#pragma unroll
+    for (int q = 0; q < CPT; ++q) {
+      const int idx = threadIdx.x + q * 256;
+      const int ul = idx & 31, bl = idx >> 5, b = bbase + bl, unit = tile * 32 + ul;
+      gb[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (b < p.B) {
+        // frame 0 of the attention LSTM sees the zero initial context (model.py:314-316): no constant-column term
+        if (IS_ATT && tc == 0) gb[q] = make_float4(b0[unit], b0[H + unit], b0[2 * H + unit], b0[3 * H + unit]);
+        else gb[q] = __ldg(&gbias[(size_t)b * H + unit]);
+      }
+    }
+  }
+  {
+    float* stage = sm.recv + (size_t)((xr & 1u) ^ 1u) * 4 * TILE_M * NC4;
+    exchange_bulk<CH>(has_work, tmem_acc, 0, recv, stage, &sm.recv_full[xr & 1u], (xr >> 1) & 1u, rank);
+  }
+  PROF3(IS_ATT ? 3 : 11);
+  const float pdrop = IS_ATT ? p.p_att : p.p_dec;
+  const unsigned thr = IS_ATT ? p.thr_att : p.thr_dec;
+  const float dscale = 1.0f / (1.0f - pdrop);
+  const unsigned site = IS_ATT ? 3u : 4u;
+  bf16* xh_next = (IS_ATT ? BFP(p.xh_a) : BFP(p.xh_d)) + (size_t)nxt * p.B * mult * Hp;
+  float* gates_all = IS_ATT ? p.gates_a : p.gates_d;
+  float* c_all = IS_ATT ? p.c_a_all : p.c_d_all;
+  float* h_all = IS_ATT ? p.h_a_all : p.h_d_all;
+#pragma unroll
+  for (int q = 0; q < CPT; ++q) {
+    const int idx = threadIdx.x + q * 256;
+    const int ul = idx & 31, bl = idx >> 5, b = bbase + bl, unit = tile * 32 + ul;
+    float h = 0.f;
+    if (b < p.B) {
+      const bool fast = p.prec == 1;
+      const float zi = recv_sum<NC4, true>(recv, ul, bl) + gb[q].x, zf = recv_sum<NC4, true>(recv, 32 + ul, bl) + gb[q].y;
+      const float zg = recv_sum<NC4, true>(recv, 64 + ul, bl) + gb[q].z, zo = recv_sum<NC4, true>(recv, 96 + ul, bl) + gb[q].w;
+      const float i_ = fast ? 0.5f * tanh_fast(0.5f * zi) + 0.5f : sigmoid_acc(zi);
+      const float f_ = fast ? 0.5f * tanh_fast(0.5f * zf) + 0.5f : sigmoid_acc(zf);
+      const float g_ = fast ? tanh_fast(zg) : tanh_acc(zg);
+      const float o_ = fast ? 0.5f * tanh_fast(0.5f * zo) + 0.5f : sigmoid_acc(zo);
+      const size_t ci = (size_t)b * H + unit;
+      const float c_new = f_ * c_reg[q] + i_ * g_;
+      c_reg[q] = c_new;
+      h = o_ * (fast ? tanh_fast(c_new) : tanh_acc(c_new));
+      if (p.use_dropout && thr != 0u) {
+        const uint32_t bits = philox_bits(p.seed, site, (uint32_t)tc, (uint32_t)ci);
+        h = bits >= thr ? h * dscale : 0.f;
+      }
+      store_act(xh_next + (size_t)b * mult * Hp, unit, Hp, p.prec, h);
+      const size_t cell = ((size_t)tc * p.B + b) * H + unit;
+      reinterpret_cast<float4*>(gates_all)[cell] = make_float4(i_, f_, g_, o_);
+      c_all[cell] = c_new;
+      h_all[cell] = h;
+    }
+    if (IS_ATT) sm.hs[ul * NC4 + bl] = h;
+  }
+  if (IS_ATT) {
+    __syncthreads();
+    // partial query of this tile: qpart[tile][b][a] = sum_u Wq[a][32 tile + u] h[b][u]; thread = (a, half of the columns)
+    constexpr int HB = NC4 / 2;
+    const int a = threadIdx.x & 127, g = threadIdx.x >> 7;
+    float acc[HB];
+#pragma unroll
+    for (int j = 0; j < HB; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int u = 0; u < 32; ++u) {
+      const float4* hr = reinterpret_cast<const float4*>(sm.hs + u * NC4 + g * HB);
+#pragma unroll
+      for (int j4 = 0; j4 < HB / 4; ++j4) {
+        const float4 hv = hr[j4];
+        acc[4 * j4] += wqr[u] * hv.x; acc[4 * j4 + 1] += wqr[u] * hv.y;
+        acc[4 * j4 + 2] += wqr[u] * hv.z; acc[4 * j4 + 3] += wqr[u] * hv.w;
+      }
+    }
+    if (a < p.A) {
+#pragma unroll
+      for (int j = 0; j < HB; ++j) {
+        const int b = bbase + g * HB + j;
+        if (b < p.B) p.qpart[((size_t)tile * p.B + b) * p.A + a] = acc[j];
+      }
+    }
+  }
+}
+
+GTN_DEVICE void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// ---- attention of frame t for the sequence of this CTA pair --------------------------------------------------------------
+struct AttnCtx {
+  int b, L, half, peer, j0, jn, Wd;
+  bool active;
+};
+
+// Part 1 (does not depend on the attention LSTM of this frame): window of the previous / cumulative weights out of shared
+// memory, im2col tile, location GEMM on tcgen05, processed_memory prefetch into registers.
+template <typename MT>
+GTN_DEVICE void attn_prepare(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, uint32_t tmem_att, uint4 (&pmq)[8]) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int Tin = p.Tin, A = p.A, KS = p.KS, hk = (p.KS - 1) / 2;
+  uint8_t* a_hi = sm.ring.base;                          // im2col tiles alias the (idle) TMA ring
+  uint8_t* a_lo = sm.ring.base + W_TILE_BYTES;
+  {
+    const int wq_ = warp & 3, a0_ = (warp >> 2) * 64, jl_ = wq_ * 32 + lane;
+    if (sizeof(MT) == 2 && c.active && jl_ < c.jn && (c.j0 + jl_) < c.L) {
+      const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const MT*>(p.pm) + ((size_t)c.b * Tin + (c.j0 + jl_)) * A + a0_);
+#pragma unroll
+      for (int g = 0; g < 8; ++g)
+        if (a0_ + g * 8 < A) pmq[g] = __ldg(src + g);
+    }
+  }
+  if (c.active) {
+    for (int i = threadIdx.x; i < 2 * c.Wd; i += 256) {
+      const int ch = i / c.Wd, jj = i - ch * c.Wd, j = c.j0 + jj - hk;
+      const float val = (j >= 0 && j < Tin) ? (ch == 0 ? sm.wprev_s[j] : sm.wcum_s[j]) : 0.f;
+      sm.wcat[i] = val;
+      if (ch == 1 && jj >= hk && jj < hk + c.jn) p.cum_all[((size_t)t * p.B + c.b) * Tin + j] = val;
+    }
+  }
+  __syncthreads();
+  if (c.active) {
+    build_im2col(sm.wcat, c.Wd, KS, c.jn, a_hi, a_lo);
+    fence_proxy_async_smem();
+  }
+  __syncthreads();
+  if (c.active && __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0) == 1) {
+    tc_fence_after();
+    const uint32_t idesc = umma_idesc_bf16(TILE_M, 128);
+    const uint64_t dah = umma_desc_sw128(smem_u32(a_hi)), dal = umma_desc_sw128(smem_u32(a_lo));
+    const uint64_t duh = umma_desc_sw128(smem_u32(sm.u_s)), dul = umma_desc_sw128(smem_u32(sm.u_s + W_TILE_BYTES));
+    if (elect_one()) {
+#pragma unroll
+      for (int k = 0; k < KB / 16; ++k) umma_bf16(tmem_att, dah + (uint64_t)(2 * k), duh + (uint64_t)(2 * k), idesc, (uint32_t)(k > 0));
+#pragma unroll
+      for (int k = 0; k < KB / 16; ++k) umma_bf16(tmem_att, dal + (uint64_t)(2 * k), duh + (uint64_t)(2 * k), idesc, 1u);
+#pragma unroll
+      for (int k = 0; k < KB / 16; ++k) umma_bf16(tmem_att, dah + (uint64_t)(2 * k), dul + (uint64_t)(2 * k), idesc, 1u);
+      umma_commit(sm.att_full);
+    }
+  }
+  __syncwarp();
+}
+
+// Part 2 (after barrier 1): query, energies, masked softmax, context, weight state update.
+template <typename MT>
+GTN_DEVICE void attn_main(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, uint32_t tmem_att, uint32_t& att_par,
+                          uint32_t& qg_par, uint32_t& eround, const uint4 (&pmq)[8]) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int Tin = p.Tin, A = p.A;
+  const MT* mem = reinterpret_cast<const MT*>(p.mem_enc);
+  const MT* pm = reinterpret_cast<const MT*>(p.pm);
+  float* e_buf = sm.e_buf + (size_t)(eround & 1u) * TIN_MAX;
+  ++eround;
+  float* qg = reinterpret_cast<float*>(sm.ring.base + 2 * W_TILE_BYTES);      // [ntq][128], behind the im2col tiles
+  const int ntq = p.Ha / 32;
+  constexpr bool PM_PRE = sizeof(MT) == 2;
+  if (c.active) {
+    // the 32 partial queries of this sequence (one per attention-LSTM cluster): one 512-byte bulk copy each
+    if (warp == 0) {
+      if (lane == 0) mbar_expect_tx(sm.qg_full, (uint32_t)(ntq * A * 4));
+      __syncwarp();
+      for (int c0 = lane; c0 < ntq; c0 += 32)
+        bulk_g2s(qg + (size_t)c0 * 128, p.qpart + ((size_t)c0 * p.B + c.b) * A, (uint32_t)(A * 4), sm.qg_full);
+    }
+    wait_bar(sm.qg_full, qg_par);
+    qg_par ^= 1u;
+    if (threadIdx.x < 128) {
+      const int a = threadIdx.x;
+      float s = 0.f;
+      if (a < A) {
+        // fixed summation tree over the partials (same order as the sequential kernel: 32 -> 16 -> 8 -> 4 -> pairs)
+        for (int c0 = 0; c0 < ntq; c0 += 32) {
+          float qv[32];
+#pragma unroll
+          for (int k = 0; k < 32; ++k) qv[k] = (c0 + k < ntq) ? qg[(size_t)(c0 + k) * 128 + a] : 0.f;
+#pragma unroll
+          for (int k = 0; k < 16; ++k) qv[k] += qv[k + 16];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) qv[k] += qv[k + 8];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) qv[k] += qv[k + 4];
+          s += (qv[0] + qv[1]) + (qv[2] + qv[3]);
+        }
+        if (c.half == 0) p.q_all[((size_t)t * p.B + c.b) * A + a] = s;
+      }
+      sm.q_s[a] = s;
+    }
+  }
+  __syncthreads();
+  PROF3(16);
+  if (c.active) {
+    wait_bar(sm.att_full, att_par);
+    att_par ^= 1u;
+    tc_fence_after();
+    // thread = (row j = TMEM lane, 64-column half of the attention dimension)
+    const int wq = warp & 3, a0 = (warp >> 2) * 64;
+    const int jl = wq * 32 + lane;
+    const bool valid = jl < c.jn && (c.j0 + jl) < c.L;
+    float part = 0.f;
+    const MT* pmj = pm + ((size_t)c.b * Tin + (c.j0 + jl)) * A + a0;
+    float* thj = p.th_all + (((size_t)t * p.B + c.b) * Tin + (c.j0 + jl)) * A + a0;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      uint32_t r[32];
+      tmem_ld_32x32(tmem_att + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a0 + h * 32), r);
+      tmem_ld_wait();
+      if (valid) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int ab = h * 32 + g * 8;
+          if (a0 + ab < A) {
+            float pmv[8];
+            if (PM_PRE) {
+              const uint4 qq = pmq[h * 4 + g];
+              const uint32_t ww[4] = {qq.x, qq.y, qq.z, qq.w};
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                pmv[2 * i] = __uint_as_float(ww[i] << 16);
+                pmv[2 * i + 1] = __uint_as_float(ww[i] & 0xFFFF0000u);
+              }
+            } else {
+              ld8<MT>(pmj + ab, pmv);
+            }
+            float th[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const float s = __uint_as_float(r[g * 8 + e]) + sm.q_s[a0 + ab + e] + pmv[e];
+              th[e] = p.prec == 1 ? tanh_fast(s) : tanh_acc(s);
+              part += sm.v_s[a0 + ab + e] * th[e];
+            }
+            *reinterpret_cast<float4*>(thj + ab) = make_float4(th[0], th[1], th[2], th[3]);
+            *reinterpret_cast<float4*>(thj + ab + 4) = make_float4(th[4], th[5], th[6], th[7]);
+          }
+        }
+      }
+    }
+    sm.e_part[(warp >> 2) * 128 + jl] = valid ? part : -INFINITY;
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (c.active) {
+    const uint32_t peer_e = map_to_rank(smem_u32(e_buf), (uint32_t)c.peer);
+    for (int jl = threadIdx.x; jl < c.jn; jl += 256) {
+      const float e = sm.e_part[jl] + sm.e_part[128 + jl];      // -inf + -inf = -inf for masked positions
+      e_buf[c.j0 + jl] = e;
+      st_cluster_f1(peer_e + (uint32_t)((c.j0 + jl) * 4), e);
+    }
+  }
+  PROF3(17);
+  cluster_sync_all();
+  PROF3(18);
+  if (c.active) {
+    // masked softmax over all encoder positions (both halves compute it redundantly, so that each CTA of the pair holds
+    // the complete previous / cumulative weights for the next frame's location window)
+    float mx = -INFINITY;
+    for (int j = threadIdx.x; j < Tin; j += 256) mx = fmaxf(mx, e_buf[j]);
+    mx = block_reduce2(mx, sm.scr, true);
+    float sum = 0.f;
+    for (int j = threadIdx.x; j < Tin; j += 256) {
+      const float e = e_buf[j] == -INFINITY ? 0.f : expf(e_buf[j] - mx);
+      sm.w_s[j] = e;
+      sum += e;
+    }
+    sum = block_reduce2(sum, sm.scr, false);
+    const float inv = 1.0f / sum;
+    float wsum = 0.f;
+    for (int j = threadIdx.x; j < Tin; j += 256) {
+      const float w = sm.w_s[j] * inv;
+      sm.w_s[j] = w;
+      sm.wprev_s[j] = w;
+      sm.wcum_s[j] += w;                                  // model.py:403
+      wsum += w;
+    }
+    wsum = block_reduce2(wsum, sm.scr, false);     // also orders the w_s writes before the reads below
+    float* aout = p.align_out + ((size_t)c.b * p.n_steps + t) * Tin;
+    for (int jl = threadIdx.x; jl < c.jn; jl += 256) aout[c.j0 + jl] = sm.w_s[c.j0 + jl];
+    PROF3(19);
+    // context over this CTA's half of the time-varying columns: 8 columns per thread, warps split j
+    const int E8 = p.E / 8, Eh8 = (E8 + 1) / 2;
+    const int c8_0 = c.half * Eh8, c8_n = min(E8, c8_0 + Eh8) - c8_0;      // in units of 8 columns
+    const int mult = p.mult;
+    bf16* xc = BFP(p.xctx) + ((size_t)(t & 1) * p.B + c.b) * mult * p.Ep;    // ctx(t) -> buffer t & 1
+    float* call = p.ctx_all + ((size_t)t * p.B + c.b) * p.D;
+    for (int cb = 0; cb < c8_n; cb += 32) {
+      const int c8 = cb + lane;
+      float acc[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+      if (c8 < c8_n) {
+        const MT* mp = mem + (size_t)c.b * Tin * p.E + (size_t)(c8_0 + c8) * 8;
+        int j = warp;
+        for (; j + 24 < c.L; j += 32) {              // four rows of this warp in flight
+          float mv[4][8];
+#pragma unroll
+          for (int r = 0; r < 4; ++r) ld8<MT>(mp + (size_t)(j + 8 * r) * p.E, mv[r]);
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+            const float w = sm.w_s[j + 8 * r];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[e] += w * mv[r][e];
+          }
+        }
+        for (; j < c.L; j += 8) {
+          float mv[8];
+          ld8<MT>(mp + (size_t)j * p.E, mv);
+          const float w = sm.w_s[j];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc[e] += w * mv[e];
+        }
+      }
+      __syncthreads();
+#pragma unroll
+      for (int e = 0; e < 8; ++e) sm.red_s[warp * 256 + lane * 8 + e] = acc[e];
+      __syncthreads();
+      for (int i = threadIdx.x; i < 256; i += 256) {
+        const int c8i = cb + (i >> 3);
+        if (c8i < c8_n) {
+          float s = 0.f;
+#pragma unroll
+          for (int w = 0; w < 8; ++w) s += sm.red_s[w * 256 + i];
+          const int d = (c8_0 + c8i) * 8 + (i & 7);
+          store_act(xc, d, p.Ep, p.prec, s);
+          call[d] = s;
+        }
+      }
+    }
+    // time-constant columns: context = const * sum_j w_j  (second CTA of the pair; saved for the weight-gradient GEMMs
+    // only: the per-frame GEMMs see these columns as a per-sequence bias)
+    if (c.half == 1 || Tin == 1) {
+      for (int i = threadIdx.x; i < p.Cc; i += 256) call[p.E + i] = p.mem_const[(size_t)c.b * p.Cc + i] * wsum;
+    }
+  }
+  __syncthreads();
+}
+
+template <int N>
+__global__ void __launch_bounds__(256, 1)
+decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const int S) {
+  constexpr int NC4 = (N < 64 ? N : 64) / 4;
+  constexpr int CPT = 32 * NC4 / 256;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  Smem3 sm = carve3<N>(base, S);
+  const int warp = threadIdx.x >> 5;
+  const int rank = (int)cluster_ctarank(), cid = (int)cluster_idx(), ncl = (int)cluster_count();
+  const int mult = p.mult;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) { mbar_init(&sm.ring.full[s], 1); mbar_init(&sm.ring.empty[s], 1); }
+    mbar_init(sm.accA_full, 1);
+    mbar_init(sm.accC_full, 1);
+    mbar_init(sm.att_full, 1);
+    mbar_init(sm.u_full, 1);
+    mbar_init(sm.qg_full, 1);
+    mbar_init(&sm.recv_full[0], 1);
+    mbar_init(&sm.recv_full[1], 1);
+    mbar_fence_init();
+    // k-block schedules.  A(t): [prenet(t) | ctx(t-1) | h_att(t-1)], ctx behind barrier 2; C(t): [h_att(t) | ctx(t) | h_dec(t-1)],
+    // ctx and h_dec behind barrier 2 (h_dec(t-1) is produced in the shadow of barrier 1 of frame t).
+    {
+      const int nkb[3] = {mult * p.Pp / KB, mult * p.Ep / KB, mult * p.Hap / KB};
+      const int wb[3] = {0, nkb[0], nkb[0] + nkb[1]};
+      const bool late[3] = {false, true, false};
+      build_sched(*sm.ks_a, 3, nkb, wb, late, rank);
+    }
+    {
+      const int nkb[3] = {mult * p.Hap / KB, mult * p.Ep / KB, mult * p.Hdp / KB};
+      const int wb[3] = {0, nkb[0], nkb[0] + nkb[1]};
+      const bool late[3] = {false, true, true};
+      build_sched(*sm.ks_c, 3, nkb, wb, late, rank);
+    }
+    // resident weight k-blocks (tensor memory): the late k-blocks of A first (they sit on the serial chain), then the late
+    // k-blocks of C, then early ones
+    int slot = 0;
+    const int nslots = res_slots<N>();
+    KSched* order[4] = {sm.ks_a, sm.ks_c, sm.ks_a, sm.ks_c};
+    for (int q = 0; q < 4; ++q) {
+      KSched& ks = *order[q];
+      const int lo = q < 2 ? ks.n_early : 0, hi = q < 2 ? ks.n : ks.n_early;
+      for (int i = lo; i < hi && slot < nslots; ++i) ks.slot[i] = (signed char)slot++;
+    }
+  }
+  if (warp == 2) tmem_alloc(sm.tmem_slot, 512);
+  for (int i = threadIdx.x; i < 128; i += 256) sm.v_s[i] = i < p.A ? p.v[i] : 0.f;
+  for (int i = threadIdx.x; i < TIN_MAX; i += 256) { sm.wprev_s[i] = 0.f; sm.wcum_s[i] = 0.f; }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *sm.tmem_slot;
+  const uint32_t tmem_att = tmem_base + 256u;
+  const uint32_t tmem_accA = tmem_base, tmem_accC = tmem_base + 256u;      // acc_C aliases the location GEMM's columns
+  if (threadIdx.x == 0) {
+    mbar_expect_tx(sm.u_full, 2 * W_TILE_BYTES);
+    tma_load_3d(sm.u_s, &maps.uloc, sm.u_full, 0, 0, 0);
+    tma_load_3d(sm.u_s + W_TILE_BYTES, &maps.uloc, sm.u_full, KB, 0, 0);
+    wait_bar(sm.u_full, 0);
+  }
+  {
+    const long long lda = (long long)mult * (p.Pp + p.Ep + p.Hap), ldd = (long long)mult * (p.Hap + p.Ep + p.Hdp);
+    for (int i = 0; i < sm.ks_a->n; ++i)
+      if (sm.ks_a->slot[i] >= 0) load_resident<N>(p.w_att2, lda, 4 * p.Ha, cid * TILE_M, sm.ks_a->wk[i], 1, sm.ks_a->slot[i], tmem_base);
+    for (int i = 0; i < sm.ks_c->n; ++i)
+      if (sm.ks_c->slot[i] >= 0) load_resident<N>(p.w_dec2, ldd, 4 * p.Hd, cid * TILE_M, sm.ks_c->wk[i], 1, sm.ks_c->slot[i], tmem_base);
+  }
+  // the sequence of this CTA pair
+  AttnCtx ac;
+  ac.half = rank & 1; ac.peer = rank ^ 1;
+  ac.b = cid * 2 + (rank >> 1);
+  ac.active = ac.b < p.B;
+  ac.L = ac.active ? (p.lengths ? min(p.lengths[ac.b], p.Tin) : p.Tin) : 0;
+  {
+    const int JH = (p.Tin + 1) / 2;
+    ac.j0 = ac.half * JH;
+    ac.jn = min(p.Tin, ac.j0 + JH) - ac.j0;
+    ac.Wd = ac.jn + p.KS - 1;
+  }
+  float wqr[32];
+  {
+    // query-weight column of this thread (a = tid % 128) for the cluster's 32 attention-LSTM units: Wq[a][32 cid + u]
+    const int a = threadIdx.x & 127;
+#pragma unroll
+    for (int u = 0; u < 32; ++u) wqr[u] = a < p.A ? p.wq_t[((size_t)cid * 32 + u) * p.A + a] : 0.f;
+  }
+  tc_fence_before();
+  cluster_sync_all();     // peers' barriers / smem are initialised before any DSMEM traffic
+  tc_fence_after();
+
+  const KSched& ka = *sm.ks_a;
+  const KSched& kc = *sm.ks_c;
+  const bool workA = ka.n > 0, workC = kc.n > 0;
+  unsigned int epoch = 0;
+  const unsigned int nblocks = gridDim.x;
+  uint32_t accA_par = 0, accC_par = 0, att_par = 0, qg_par = 0, round = 0, eround = 0;
+  uint32_t startedA = 0, startedC = 0;
+  float cA[CPT], cC[CPT];
+#pragma unroll
+  for (int q = 0; q < CPT; ++q) { cA[q] = 0.f; cC[q] = 0.f; }
+  uint4 pmq[8];
+  const int T = p.n_steps;
+
+  auto opsA = [&](int t) {           // A(t): pre(t), ctx(t-1) -> buffer (t-1)&1 = (t&1)^1, h_att(t-1) -> buffer t&1
+    XOps x;
+    x.map[0] = &maps.pre; x.z[0] = t;
+    x.map[1] = &maps.ctx; x.z[1] = (t & 1) ^ 1;
+    x.map[2] = &maps.ha;  x.z[2] = t & 1;
+    return x;
+  };
+  auto opsC = [&](int t) {           // C(t): h_att(t) -> buffer (t&1)^1, ctx(t) -> buffer t&1, h_dec(t-1) -> buffer t&1
+    XOps x;
+    x.map[0] = &maps.ha;  x.z[0] = (t & 1) ^ 1;
+    x.map[1] = &maps.ctx; x.z[1] = t & 1;
+    x.map[2] = &maps.hd;  x.z[2] = t & 1;
+    return x;
+  };
+
+  // prologue: early k-blocks of A(0) (prenet(0) and the zero initial h_att)
+  {
+    startedA = 0;
+    const XOps x = opsA(0);
+    issue_kblocks<N>(ka, 0, ka.n_early, &maps.w_att, cid * TILE_M, x, sm.ring, tmem_accA, tmem_base, startedA, nullptr);
+  }
+  for (int t = 0; t < T; ++t) {
+    PROF3(0);
+    // ---- W1: late parts (operands protected by barrier 2 of the previous frame)
+    {
+      const XOps x = opsA(t);
+      issue_kblocks<N>(ka, ka.n_early, ka.n, &maps.w_att, cid * TILE_M, x, sm.ring, tmem_accA, tmem_base, startedA, sm.accA_full);
+    }
+    if (t > 0) {
+      const XOps x = opsC(t - 1);
+      issue_kblocks<N>(kc, kc.n_early, kc.n, &maps.w_dec, cid * TILE_M, x, sm.ring, tmem_accC, tmem_base, startedC, sm.accC_full);
+    }
+    PROF3(1);
+    // ---- W2: attention LSTM cells of frame t
+    lstm_epilogue<N, true>(p, sm, t, cid, rank, workA, tmem_accA, sm.accA_full, accA_par, round, cA, wqr);
+    PROF3(4);
+    // ---- W3
+    grid_arrive(p.barrier);
+    epoch += nblocks;
+    PROF3(5);
+    // ---- W4: decoder LSTM cells of frame t - 1
+    if (t > 0) lstm_epilogue<N, false>(p, sm, t - 1, cid, rank, workC, tmem_accC, sm.accC_full, accC_par, round, cC, wqr);
+    PROF3(12);
+    // ---- W5 (the tensor-memory columns of acc_C are free again: every warp passed the exchange's thread syncs)
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (p.mem_bf16) attn_prepare<bf16>(p, sm, ac, t, tmem_att, pmq);
+    else attn_prepare<float>(p, sm, ac, t, tmem_att, pmq);
+    PROF3(13);
+    // ---- W6
+    grid_wait(p.barrier, epoch);
+    PROF3(14);
+    // ---- W7
+    if (p.mem_bf16) attn_main<bf16>(p, sm, ac, t, tmem_att, att_par, qg_par, eround, pmq);
+    else attn_main<float>(p, sm, ac, t, tmem_att, att_par, qg_par, eround, pmq);
+    PROF3(20);
+    // ---- W8
+    tc_fence_before();
+    grid_arrive(p.barrier);
+    epoch += nblocks;
+    tc_fence_after();
+    PROF3(21);
+    if (t + 1 < T) {
+      startedA = 0;
+      const XOps x = opsA(t + 1);
+      issue_kblocks<N>(ka, 0, ka.n_early, &maps.w_att, cid * TILE_M, x, sm.ring, tmem_accA, tmem_base, startedA, nullptr);
+    }
+    {
+      startedC = 0;
+      const XOps x = opsC(t);
+      issue_kblocks<N>(kc, 0, kc.n_early, &maps.w_dec, cid * TILE_M, x, sm.ring, tmem_accC, tmem_base, startedC, nullptr);
+    }
+    PROF3(22);
+    grid_wait(p.barrier, epoch);
+    PROF3(23);
+  }
+  // epilogue: C(T-1)
+  {
+    const int t = T;      // (PROF3 guard)
+    (void)t;
+    const XOps x = opsC(T - 1);
+    issue_kblocks<N>(kc, kc.n_early, kc.n, &maps.w_dec, cid * TILE_M, x, sm.ring, tmem_accC, tmem_base, startedC, sm.accC_full);
+    lstm_epilogue<N, false>(p, sm, T - 1, cid, rank, workC, tmem_accC, sm.accC_full, accC_par, round, cC, wqr);
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && p.steps_done) *p.steps_done = T;
+  tc_fence_before();
+  cluster_sync_all();     // no CTA exits while a peer may still write into its shared memory
+  if (warp == 2) tmem_dealloc(tmem_base, 512);
+  (void)ncl;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+template <int N>
+static int launch_fwd3_n(const Fwd2Maps& maps, const DecFwd& p, cudaStream_t st) {
+  const size_t stage = (size_t)W_TILE_BYTES + (size_t)N * KB * 2;
+  const size_t fixed = fwd3_fixed_bytes<N>() + 1024;
+  int S = (int)((227 * 1024 - fixed) / stage);
+  if (S > 12) S = 12;
+  if (S < 3 || (size_t)S * stage < (size_t)3 * W_TILE_BYTES) return FWD3_NOT_COVERED;      // im2col tiles + query partials alias the ring
+  const size_t smem = fixed + (size_t)S * stage;
+  auto kern = decoder_fwd3_kernel<N>;
+  GTN_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(256);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attrs[2];
+  attrs[0].id = cudaLaunchAttributeClusterDimension;
+  attrs[0].val.clusterDim.x = CL; attrs[0].val.clusterDim.y = 1; attrs[0].val.clusterDim.z = 1;
+  attrs[1].id = cudaLaunchAttributeCooperative;
+  attrs[1].val.cooperative = 1;
+  cfg.attrs = attrs;
+  cfg.numAttrs = 1;
+  const int want = p.Ha / 32;
+  cfg.gridDim = dim3(CL * want);
+  int max_cl = 0;
+  GTN_CUDA_OK(cudaOccupancyMaxActiveClusters(&max_cl, kern, &cfg));
+  if (max_cl < want) return FWD3_NOT_COVERED;                    // one attention tile + one decoder tile per cluster, all co-resident
+  cfg.numAttrs = profiler_attached() ? 1 : 2;       // profilers cannot replay cooperative launches
+  GTN_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, maps, p, S));
+  count_launch();
+  return 0;
+}
+
+int launch_train_fwd3(const Fwd2Maps& maps, const DecFwd& p, cudaStream_t st) {
+  if (!p.train || getenv("GTN_FWD_SEQUENTIAL")) return FWD3_NOT_COVERED;
+  const int ncl = p.Ha / 32;
+  if (p.Hd / 32 != ncl || p.B > 2 * ncl || p.B > 64 || p.Ha > 1024) return FWD3_NOT_COVERED;
+  const int m = p.mult;
+  // every CTA's k-block list must fit the schedule table
+  if ((m * (p.Pp + p.Ep + p.Hap) / KB + CL - 1) / CL + 3 > KMAX || (m * (p.Hap + p.Ep + p.Hdp) / KB + CL - 1) / CL + 3 > KMAX) return FWD3_NOT_COVERED;
+  return p.B <= 32 ? launch_fwd3_n<32>(maps, p, st) : launch_fwd3_n<64>(maps, p, st);
+}
+
+}  // namespace gtn

@@ -28,5 +28,8 @@ int gemm_launch(const GemmDesc& g, cudaStream_t st);
 
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
+// true when a profiler / injection library is attached to the process (Nsight Compute cannot replay cooperative
+// launches: the persistent kernels then drop the cooperative attribute; co-residency still holds on an idle GPU)
+bool profiler_attached();
 
 }  // namespace gtn

@@ -235,7 +235,7 @@ def _alloc_state(p: _lib.DecoderFwdParams, d: DecoderDims, B: int, mult: int, de
     z = lambda *s, dt=torch.float32: torch.zeros(*s, device=dev, dtype=dt)
     st = dict(
         xh_a=z(2, B, mult * d.Hap, dt=BF16), xh_d=z(2, B, mult * d.Hdp, dt=BF16),
-        xctx=z(B, mult * (ctx_cols or d.Dp), dt=BF16),
+        xctx=z(2, B, mult * (ctx_cols or d.Dp), dt=BF16),
         xmel=z(B, mult * d.NMp, dt=BF16), xp1=z(B, mult * d.Pp, dt=BF16), xp2=z(B, mult * d.Pp, dt=BF16),
         c_a=z(B, d.att_rnn), c_d=z(B, d.dec_rnn), w_prev=z(B, p.ldT), w_cum=z(B, p.ldT),
         qpart=z(d.att_rnn // 8, B, d.att_dim), barrier=z(4, dt=torch.int32), done=z(B, dt=torch.int32),

@@ -173,7 +173,7 @@ typedef struct gtn_decoder_fwd_params {
   const void *pre_all;       /* train: prenet outputs, bf16 [n_steps+1][B][mult*Pp] */
   /* state / workspace (zero-initialised by the caller) */
   void *xh_a, *xh_d;         /* bf16 [2][B][mult*Hap], [2][B][mult*Hdp] */
-  void *xctx, *xmel, *xp1, *xp2; /* bf16 [B][mult*Dp], [B][mult*NMp], [B][mult*Pp] x2 */
+  void *xctx, *xmel, *xp1, *xp2; /* bf16 [2][B][mult*Ep] (double buffered), [B][mult*NMp], [B][mult*Pp] x2 */
   float *c_a, *c_d;          /* [B][Ha], [B][Hd] */
   float *w_prev, *w_cum;     /* [B][ldT] */
   float *qpart;              /* [Ha/8][B][A] */
@@ -200,7 +200,7 @@ typedef struct gtn_decoder_fwd_params {
   /* forward2 drops the time-constant memory columns from every per-frame GEMM: their contribution to the LSTM
    * gates / projection is a per-sequence bias computed once (context_const = mem_const * sum_j w_j, sum_j w_j = 1):
    *   K(att) = [prenet Pp | ctx_enc Ep | h_att Hap], K(dec) = [h_att | ctx_enc Ep | h_dec], K(proj) = [h_dec | ctx_enc Ep],
-   *   xctx is [B][mult*Ep], Ep = pad64(E). */
+   *   xctx is [2][B][mult*Ep], Ep = pad64(E): the training kernel alternates the two buffers by frame parity. */
   const float *gbias_a, *gbias_d;       /* [B][H][4] (i,f,g,o): bias_ih + bias_hh + W[:, const cols] . mem_const[b] */
   const float *pbias;                   /* [B][NM+1]: projection / gate bias + W[:, const cols] . mem_const[b] (inference) */
   int Ep, reserved0;
