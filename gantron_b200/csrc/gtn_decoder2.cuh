@@ -97,8 +97,9 @@ GTN_DEVICE uint32_t sw128_off(int r, int chunk) {
 
 // im2col tile of the location conv input for rows r < jn: K index kk = ch*KS + k  ->  wcat[ch*Wd + r + k]; written as
 // two K-major SWIZZLE_128B bf16 tiles (hi plane, lo = residual plane).  Doubles as an MN-major operand with K = rows.
-GTN_DEVICE void build_im2col(const float* wcat, int Wd, int KS, int jn, uint8_t* a_hi, uint8_t* a_lo) {
-  for (int i = threadIdx.x; i < jn * 8; i += blockDim.x) {
+GTN_DEVICE void build_im2col(const float* wcat, int Wd, int KS, int jn, uint8_t* a_hi, uint8_t* a_lo, int nthreads = 0) {
+  if (nthreads == 0) nthreads = (int)blockDim.x;
+  for (int i = threadIdx.x; i < jn * 8; i += nthreads) {
     const int r = i >> 3, chunk = i & 7;
     uint32_t hi[4], lo[4];
 #pragma unroll
@@ -196,7 +197,7 @@ template <int N>
 GTN_DEVICE void load_resident(const void* W, long long ldw, int nrows, int row0, int kb_first, int count, int slot0,
                               uint32_t tmem_base) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (warp < 4) return;
+  if (warp < 4 || warp >= 8) return;
   const int q = warp & 3, row = row0 + q * 32 + lane;
   for (int i = 0; i < count; ++i) {
     uint32_t r[32];
@@ -379,6 +380,14 @@ GTN_DEVICE void exchange_chunk(bool has_work, uint32_t tmem_acc, int c0, float* 
   tc_fence_after();
 }
 
+// CTA-wide thread sync of the exchange: bar.sync 0 over the whole CTA, or (WB) named barrier 1 over the first 256 threads
+// for kernels whose warps 8+ are dedicated TMA / MMA issuers that never join the workers' syncs.
+template <bool WB>
+GTN_DEVICE void cta_sync() {
+  if (WB) asm volatile("bar.sync 1, 256;" ::: "memory");
+  else __syncthreads();
+}
+
 // Same exchange through the bulk-copy engine.  Individual st.shared::cluster stores move the 24 KB a CTA owes its peers at
 // ~10 B/clk, and the cluster barrier behind them adds ~1k cycles.  Here warps 4..7 drop the three peer-bound blocks into a
 // local staging area (plain st.shared), ONE thread sends each as a cp.async.bulk shared::cta -> shared::cluster copy that
@@ -388,13 +397,13 @@ GTN_DEVICE void exchange_chunk(bool has_work, uint32_t tmem_acc, int c0, float* 
 // stage[q] block only in its NEXT exchange, which it enters after it has received this exchange's blocks (mine included, so
 // my copy out of stage[q] has completed); and I overwrite a peer's buffer only two exchanges after it was filled, which I
 // reach only after that peer has sent the exchange in between, i.e. after it finished reading.
-template <int CH>
+template <int CH, bool WB = false>
 GTN_DEVICE void exchange_bulk(bool has_work, uint32_t tmem_acc, int c0, float* recv, float* stage, uint64_t* full_bar,
                               uint32_t parity, int rank) {
   constexpr int NC4 = CH / 4;
   constexpr uint32_t BLK = (uint32_t)TILE_M * NC4 * 4;           // bytes of one [128 rows][NC4] block
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  __syncthreads();        // stage is the buffer the previous exchange's epilogue read: every warp is done with it
+  cta_sync<WB>();         // stage is the buffer the previous exchange's epilogue read: every warp is done with it
   if (threadIdx.x == 0) mbar_expect_tx(full_bar, 3u * BLK);       // arm this exchange's receive (may trail the first bytes)
   if (warp >= 4) {
     const int wq = warp & 3;
@@ -423,7 +432,7 @@ GTN_DEVICE void exchange_bulk(bool has_work, uint32_t tmem_acc, int c0, float* r
     fence_proxy_async_smem();                                     // staging writes -> bulk-copy (async proxy) reads
   }
   tc_fence_before();
-  __syncthreads();
+  cta_sync<WB>();
   if (__shfl_sync(0xffffffffu, warp, 0) == 0) {
     if (elect_one()) {
 #pragma unroll

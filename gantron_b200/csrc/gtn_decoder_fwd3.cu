@@ -21,6 +21,11 @@
 //       issue the EARLY k-blocks of A(t+1) and C(t): prenet(t+1), h_att(t) -- operands that were complete before
 //       barrier 2 -- while the other CTAs arrive
 //
+// The TMA loads and tcgen05.mma of the per-frame GEMMs are issued by two DEDICATED warps (8: producer, 9: MMA issuer) that run
+// their own instruction stream, gated by "go" mbarriers the workers arrive on; the eight worker warps synchronise among
+// themselves on named barrier 1 and only ever wait for a finished accumulator.  So the operand streaming of C(t-1) (10
+// k-blocks per CTA) runs underneath the attention-LSTM epilogue W2 instead of in front of it.
+//
 // Every per-frame GEMM keeps its cluster split (4 CTAs x K quarter, gtn_decoder2.cuh) but a CTA's quarter is now made of
 // a quarter of EVERY activation segment, ordered early -> late, so that only 2 (A) + 6 (C) k-blocks per CTA remain behind
 // barrier 2; their weight k-blocks are the ones parked in tensor memory, so the post-barrier chain of A(t) is one 16 KB
@@ -28,6 +33,7 @@
 //
 // Covers B <= 64 (one sequence per CTA pair), attention_rnn_dim / 32 == decoder_rnn_dim / 32 == number of clusters;
 // anything else runs the sequential kernel of gtn_decoder_fwd2.cu.
+#include <type_traits>
 #include "gtn_decoder_fwd.cuh"
 
 namespace gtn {
@@ -37,6 +43,9 @@ namespace gtn {
     if (p.prof != nullptr && blockIdx.x == 0 && threadIdx.x == 0 && t < 16) p.prof[t * 32 + (slot)] = clock64(); \
   } while (0)
 
+#define WSYNC() asm volatile("bar.sync 1, 256;" ::: "memory")      /* the eight worker warps */
+static constexpr int NWORK = 256;      // worker threads; warps 8 and 9 are the TMA producer and the MMA issuer
+static constexpr int NTHREADS = 384;   // three warpgroups: two of workers (232 registers), one of issuers (40 registers)
 static constexpr int KMAX = 64;        // k-blocks of one GEMM per CTA (fp32 mode: 6 planes x 10)
 
 struct KSched {            // this CTA's k-blocks of one per-frame GEMM, in issue order
@@ -62,6 +71,9 @@ struct Smem3 {
   float* scr;          // [64]
   float* wprev_s;      // [Tin_pad]  attention weights of the previous frame (all positions, both CTAs of the pair)
   float* wcum_s;       // [Tin_pad]  cumulative attention weights
+  float* qg_s;         // [32][128]  partial queries of this sequence (bulk-copied)
+  float* wq_s;         // [32][128]  Wq^T rows of the cluster's 32 attention-LSTM units
+  uint8_t* im_s;       // [2][16 KB] im2col tiles when they cannot alias a receive buffer (N < 64), else nullptr
   KSched* ks_a;
   KSched* ks_c;
   uint64_t* accA_full;
@@ -69,6 +81,10 @@ struct Smem3 {
   uint64_t* att_full;
   uint64_t* u_full;
   uint64_t* qg_full;
+  uint64_t* e_full;     // energies of the peer half have arrived (remote arrive by the peer CTA)
+  uint64_t* go_late;    // workers -> issuers: barrier 2 passed (context / h_dec operands visible)
+  uint64_t* go_early;   // workers -> issuers: acc_A is free and h_att(t) is visible
+  uint64_t* go_c;       // workers -> issuers: the split-K exchange of A(t) is over (C's operand stream would slow it down)
   uint64_t* recv_full;  // [2]
   uint32_t* tmem_slot;
 };
@@ -77,8 +93,9 @@ template <int N>
 __host__ __device__ constexpr size_t fwd3_fixed_bytes() {
   constexpr int NC4 = (N < 64 ? N : 64) / 4;
   return (size_t)2 * W_TILE_BYTES + (size_t)2 * 4 * TILE_M * NC4 * 4 +
-         (size_t)(NC4 * 32 + 128 + 128 + 2 * (JH_MAX + KS_MAX - 1) + 2 * TIN_MAX + 2 * 128 + TIN_MAX + 8 * 256 + 64 + 2 * TIN_MAX) * 4 +
-         2 * ((sizeof(KSched) + 15) / 16 * 16) + 64 * 8 + 64;
+         (size_t)(NC4 * 32 + 128 + 128 + 2 * (JH_MAX + KS_MAX - 1) + 2 * TIN_MAX + 2 * 128 + TIN_MAX + 8 * 256 + 64 + 2 * TIN_MAX +
+                  2 * 32 * 128) * 4 +
+         (N < 64 ? (size_t)2 * W_TILE_BYTES : 0) + 2 * ((sizeof(KSched) + 15) / 16 * 16) + 64 * 8 + 64;
 }
 
 template <int N>
@@ -91,8 +108,12 @@ GTN_DEVICE Smem3 carve3(uint8_t* base, int S) {
   m.ring.prod_it = m.ring.mma_it = 0;
   uint8_t* p = base + (size_t)S * m.ring.stage_bytes;
   m.u_s = p; p += 2 * W_TILE_BYTES;
+  m.im_s = nullptr;
+  if (N < 64) { m.im_s = p; p += 2 * W_TILE_BYTES; }
   float* f = reinterpret_cast<float*>(p);
   m.recv = f; f += 2 * 4 * TILE_M * NC4;
+  m.qg_s = f; f += 32 * 128;
+  m.wq_s = f; f += 32 * 128;
   m.hs = f; f += NC4 * 32;
   m.q_s = f; f += 128;
   m.v_s = f; f += 128;
@@ -115,6 +136,10 @@ GTN_DEVICE Smem3 carve3(uint8_t* base, int S) {
   m.att_full = b++;
   m.u_full = b++;
   m.qg_full = b++;
+  m.e_full = b++;
+  m.go_late = b++;
+  m.go_early = b++;
+  m.go_c = b++;
   m.recv_full = b; b += 2;
   m.tmem_slot = reinterpret_cast<uint32_t*>(b + 1);
   return m;
@@ -123,21 +148,50 @@ GTN_DEVICE Smem3 carve3(uint8_t* base, int S) {
 // ---- split grid barrier (co-resident launch): thread 64 (warp 2) carries the release / acquire and the proxy fences, so
 // that the TMA / MMA warps 0 and 1 are free to issue between ARRIVE and WAIT ------------------------------------------
 GTN_DEVICE void grid_arrive(unsigned int* counter) {
-  __syncthreads();
+  WSYNC();
   if (threadIdx.x == 64) {
     fence_proxy_async();
     red_release_add(counter, 1u);
   }
 }
-GTN_DEVICE void grid_wait(unsigned int* counter, unsigned int target) {
+// `go`: mbarrier of the issuer warps to arrive on as soon as the barrier is seen complete (before the workers' own sync)
+GTN_DEVICE void grid_wait(unsigned int* counter, unsigned int target, uint64_t* go = nullptr) {
   if (threadIdx.x == 64) {
     long long t0 = clock64();
     while (ld_acquire_u32(counter) < target) {
       if (clock64() - t0 > 20000000000LL) __trap();
     }
     fence_proxy_async();
+    if (go != nullptr) mbar_arrive(go);
   }
-  __syncthreads();
+  WSYNC();
+}
+GTN_DEVICE void mbar_arrive_remote(uint32_t remote_bar) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote_bar) : "memory");
+}
+GTN_DEVICE void wait_bar_cluster(uint64_t* bar, uint32_t parity) {      // acquire at cluster scope: pairs with mbar_arrive_remote
+  long long t0 = clock64();
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    if (ok) return;
+    if (clock64() - t0 > 8000000000LL) __trap();
+  }
+}
+GTN_DEVICE float block_reduce_w(float v, float* scr, bool is_max) {       // block_reduce2 over the worker warps
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  v = is_max ? warp_max(v) : warp_sum(v);
+  WSYNC();
+  if (lane == 0) scr[warp] = v;
+  WSYNC();
+  float r = scr[0];
+#pragma unroll
+  for (int w = 1; w < 8; ++w) r = is_max ? fmaxf(r, scr[w]) : r + scr[w];
+  return r;
 }
 
 // ---- k-block schedule of one GEMM for this CTA -------------------------------------------------------------------------
@@ -164,15 +218,15 @@ struct XOps {                       // activation operands of one GEMM at one fr
   int z[3];
 };
 
-// Issue k-blocks [i0, i1) of the schedule: producer = warp 0, MMA issuer = warp 1, both in warp-uniform control flow (see
+// Issue k-blocks [i0, i1) of the schedule: producer = warp 8, MMA issuer = warp 9, both in warp-uniform control flow (see
 // gemm_issue in gtn_decoder2.cuh).  Consecutive resident k-blocks share a ring stage (activation tiles only).
 template <int N>
 GTN_DEVICE void issue_kblocks(const KSched& ks, int i0, int i1, const CUtensorMap* wmap, int row0, const XOps& x, Ring& rg,
                               uint32_t tmem_acc, uint32_t tmem_base, uint32_t& started, uint64_t* commit_bar) {
   constexpr uint32_t X_BYTES = N * KB * 2;
   constexpr int G = (W_TILE_BYTES + X_BYTES) / X_BYTES;
-  const int warp_u = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
-  if (warp_u > 1) return;
+  const int warp_u = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0) - 8;
+  if (warp_u < 0 || warp_u > 1) return;
   const int S = rg.S;
   const uint32_t stage_bytes = rg.stage_bytes;
   uint8_t* const base = rg.base;
@@ -257,15 +311,15 @@ GTN_DEVICE void issue_kblocks(const KSched& ks, int i0, int i1, const CUtensorMa
 // ---- LSTM epilogue of one GEMM tile: split-K exchange, cell, dropout, saves, next-frame operand ---------------------------
 // tc = frame index of the cell.  c_reg: this thread's cell states, carried in registers over the whole launch (a thread owns
 // the same (unit, sequence) pairs in every frame).
-template <int N, bool IS_ATT>
+template <int N, bool F32, bool IS_ATT>
 GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int rank, bool has_work, uint32_t tmem_acc,
-                              uint64_t* acc_full, uint32_t& acc_par, uint32_t& round, float (&c_reg)[32 * (N < 64 ? N : 64) / 4 / 256],
-                              float (&wqr)[32]) {
+                              uint64_t* acc_full, uint32_t& acc_par, uint32_t& round, float (&c_reg)[32 * (N < 64 ? N : 64) / 4 / 256]) {
   constexpr int CH = N < 64 ? N : 64;
   constexpr int NC4 = CH / 4;
   constexpr int CPT = 32 * NC4 / 256;
   static_assert(N <= 64, "one exchange chunk per tile");
-  const int mult = p.mult, nxt = (tc & 1) ^ 1;
+  constexpr int mult = F32 ? 6 : 1, PREC = F32 ? 3 : 1;
+  const int nxt = (tc & 1) ^ 1;
   const int H = IS_ATT ? p.Ha : p.Hd, Hp = IS_ATT ? p.Hap : p.Hdp;
   const int t = tc;                                  // (PROF3)
   if ((threadIdx.x >> 5) >= 4 && has_work) {
@@ -296,8 +350,9 @@ GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int 
   }
   {
     float* stage = sm.recv + (size_t)((xr & 1u) ^ 1u) * 4 * TILE_M * NC4;
-    exchange_bulk<CH>(has_work, tmem_acc, 0, recv, stage, &sm.recv_full[xr & 1u], (xr >> 1) & 1u, rank);
+    exchange_bulk<CH, true>(has_work, tmem_acc, 0, recv, stage, &sm.recv_full[xr & 1u], (xr >> 1) & 1u, rank);
   }
+  if (IS_ATT && threadIdx.x == 64) mbar_arrive(sm.go_c);       // the decoder LSTM's operand stream may start
   PROF3(IS_ATT ? 3 : 11);
   const float pdrop = IS_ATT ? p.p_att : p.p_dec;
   const unsigned thr = IS_ATT ? p.thr_att : p.thr_dec;
@@ -313,7 +368,7 @@ GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int 
     const int ul = idx & 31, bl = idx >> 5, b = bbase + bl, unit = tile * 32 + ul;
     float h = 0.f;
     if (b < p.B) {
-      const bool fast = p.prec == 1;
+      constexpr bool fast = !F32;
       const float zi = recv_sum<NC4, true>(recv, ul, bl) + gb[q].x, zf = recv_sum<NC4, true>(recv, 32 + ul, bl) + gb[q].y;
       const float zg = recv_sum<NC4, true>(recv, 64 + ul, bl) + gb[q].z, zo = recv_sum<NC4, true>(recv, 96 + ul, bl) + gb[q].w;
       const float i_ = fast ? 0.5f * tanh_fast(0.5f * zi) + 0.5f : sigmoid_acc(zi);
@@ -328,7 +383,7 @@ GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int 
         const uint32_t bits = philox_bits(p.seed, site, (uint32_t)tc, (uint32_t)ci);
         h = bits >= thr ? h * dscale : 0.f;
       }
-      store_act(xh_next + (size_t)b * mult * Hp, unit, Hp, p.prec, h);
+      store_act(xh_next + (size_t)b * mult * Hp, unit, Hp, PREC, h);
       const size_t cell = ((size_t)tc * p.B + b) * H + unit;
       reinterpret_cast<float4*>(gates_all)[cell] = make_float4(i_, f_, g_, o_);
       c_all[cell] = c_new;
@@ -337,7 +392,7 @@ GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int 
     if (IS_ATT) sm.hs[ul * NC4 + bl] = h;
   }
   if (IS_ATT) {
-    __syncthreads();
+    WSYNC();
     // partial query of this tile: qpart[tile][b][a] = sum_u Wq[a][32 tile + u] h[b][u]; thread = (a, half of the columns)
     constexpr int HB = NC4 / 2;
     const int a = threadIdx.x & 127, g = threadIdx.x >> 7;
@@ -347,11 +402,12 @@ GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int 
 #pragma unroll
     for (int u = 0; u < 32; ++u) {
       const float4* hr = reinterpret_cast<const float4*>(sm.hs + u * NC4 + g * HB);
+      const float wq = sm.wq_s[u * 128 + a];
 #pragma unroll
       for (int j4 = 0; j4 < HB / 4; ++j4) {
         const float4 hv = hr[j4];
-        acc[4 * j4] += wqr[u] * hv.x; acc[4 * j4 + 1] += wqr[u] * hv.y;
-        acc[4 * j4 + 2] += wqr[u] * hv.z; acc[4 * j4 + 3] += wqr[u] * hv.w;
+        acc[4 * j4] += wq * hv.x; acc[4 * j4 + 1] += wq * hv.y;
+        acc[4 * j4 + 2] += wq * hv.z; acc[4 * j4 + 3] += wq * hv.w;
       }
     }
     if (a < p.A) {
@@ -377,12 +433,13 @@ struct AttnCtx {
 
 // Part 1 (does not depend on the attention LSTM of this frame): window of the previous / cumulative weights out of shared
 // memory, im2col tile, location GEMM on tcgen05, processed_memory prefetch into registers.
-template <typename MT>
-GTN_DEVICE void attn_prepare(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, uint32_t tmem_att, uint4 (&pmq)[8]) {
+template <bool F32>
+GTN_DEVICE void attn_prepare(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, uint32_t tmem_att, uint4 (&pmq)[8], uint8_t* im) {
+  typedef typename std::conditional<F32, float, bf16>::type MT;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int Tin = p.Tin, A = p.A, KS = p.KS, hk = (p.KS - 1) / 2;
-  uint8_t* a_hi = sm.ring.base;                          // im2col tiles alias the (idle) TMA ring
-  uint8_t* a_lo = sm.ring.base + W_TILE_BYTES;
+  uint8_t* a_hi = im;                                    // im2col tiles, bf16 hi / lo planes (32 KB)
+  uint8_t* a_lo = im + W_TILE_BYTES;
   {
     const int wq_ = warp & 3, a0_ = (warp >> 2) * 64, jl_ = wq_ * 32 + lane;
     if (sizeof(MT) == 2 && c.active && jl_ < c.jn && (c.j0 + jl_) < c.L) {
@@ -400,12 +457,12 @@ GTN_DEVICE void attn_prepare(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t
       if (ch == 1 && jj >= hk && jj < hk + c.jn) p.cum_all[((size_t)t * p.B + c.b) * Tin + j] = val;
     }
   }
-  __syncthreads();
+  WSYNC();
   if (c.active) {
-    build_im2col(sm.wcat, c.Wd, KS, c.jn, a_hi, a_lo);
+    build_im2col(sm.wcat, c.Wd, KS, c.jn, a_hi, a_lo, NWORK);
     fence_proxy_async_smem();
   }
-  __syncthreads();
+  WSYNC();
   if (c.active && __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0) == 1) {
     tc_fence_after();
     const uint32_t idesc = umma_idesc_bf16(TILE_M, 128);
@@ -425,16 +482,19 @@ GTN_DEVICE void attn_prepare(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t
 }
 
 // Part 2 (after barrier 1): query, energies, masked softmax, context, weight state update.
-template <typename MT>
+template <bool F32>
 GTN_DEVICE void attn_main(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, uint32_t tmem_att, uint32_t& att_par,
                           uint32_t& qg_par, uint32_t& eround, const uint4 (&pmq)[8]) {
+  // (eround doubles as the phase counter of e_full: one remote arrival per frame)
+  typedef typename std::conditional<F32, float, bf16>::type MT;
+  constexpr int PREC = F32 ? 3 : 1;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int Tin = p.Tin, A = p.A;
   const MT* mem = reinterpret_cast<const MT*>(p.mem_enc);
   const MT* pm = reinterpret_cast<const MT*>(p.pm);
   float* e_buf = sm.e_buf + (size_t)(eround & 1u) * TIN_MAX;
   ++eround;
-  float* qg = reinterpret_cast<float*>(sm.ring.base + 2 * W_TILE_BYTES);      // [ntq][128], behind the im2col tiles
+  float* qg = sm.qg_s;                                                        // [ntq][128]
   const int ntq = p.Ha / 32;
   constexpr bool PM_PRE = sizeof(MT) == 2;
   if (c.active) {
@@ -445,8 +505,10 @@ GTN_DEVICE void attn_main(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, u
       for (int c0 = lane; c0 < ntq; c0 += 32)
         bulk_g2s(qg + (size_t)c0 * 128, p.qpart + ((size_t)c0 * p.B + c.b) * A, (uint32_t)(A * 4), sm.qg_full);
     }
+    PROF3(15);
     wait_bar(sm.qg_full, qg_par);
     qg_par ^= 1u;
+    PROF3(24);
     if (threadIdx.x < 128) {
       const int a = threadIdx.x;
       float s = 0.f;
@@ -469,7 +531,7 @@ GTN_DEVICE void attn_main(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, u
       sm.q_s[a] = s;
     }
   }
-  __syncthreads();
+  WSYNC();
   PROF3(16);
   if (c.active) {
     wait_bar(sm.att_full, att_par);
@@ -508,7 +570,7 @@ GTN_DEVICE void attn_main(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, u
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
               const float s = __uint_as_float(r[g * 8 + e]) + sm.q_s[a0 + ab + e] + pmv[e];
-              th[e] = p.prec == 1 ? tanh_fast(s) : tanh_acc(s);
+              th[e] = F32 ? tanh_acc(s) : tanh_fast(s);
               part += sm.v_s[a0 + ab + e] * th[e];
             }
             *reinterpret_cast<float4*>(thj + ab) = make_float4(th[0], th[1], th[2], th[3]);
@@ -520,7 +582,7 @@ GTN_DEVICE void attn_main(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, u
     sm.e_part[(warp >> 2) * 128 + jl] = valid ? part : -INFINITY;
   }
   tc_fence_before();
-  __syncthreads();
+  WSYNC();
   if (c.active) {
     const uint32_t peer_e = map_to_rank(smem_u32(e_buf), (uint32_t)c.peer);
     for (int jl = threadIdx.x; jl < c.jn; jl += 256) {
@@ -530,21 +592,27 @@ GTN_DEVICE void attn_main(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, u
     }
   }
   PROF3(17);
-  cluster_sync_all();
+  // the peer half's energies: remote arrive on the peer's mbarrier instead of a cluster barrier (the issuer warps do not
+  // take part in the frame loop's synchronisation)
+  WSYNC();
+  if (c.active) {
+    if (threadIdx.x == 0) mbar_arrive_remote(map_to_rank(smem_u32(sm.e_full), (uint32_t)c.peer));
+    wait_bar_cluster(sm.e_full, (eround - 1u) & 1u);
+  }
   PROF3(18);
   if (c.active) {
     // masked softmax over all encoder positions (both halves compute it redundantly, so that each CTA of the pair holds
     // the complete previous / cumulative weights for the next frame's location window)
     float mx = -INFINITY;
     for (int j = threadIdx.x; j < Tin; j += 256) mx = fmaxf(mx, e_buf[j]);
-    mx = block_reduce2(mx, sm.scr, true);
+    mx = block_reduce_w(mx, sm.scr, true);
     float sum = 0.f;
     for (int j = threadIdx.x; j < Tin; j += 256) {
       const float e = e_buf[j] == -INFINITY ? 0.f : expf(e_buf[j] - mx);
       sm.w_s[j] = e;
       sum += e;
     }
-    sum = block_reduce2(sum, sm.scr, false);
+    sum = block_reduce_w(sum, sm.scr, false);
     const float inv = 1.0f / sum;
     float wsum = 0.f;
     for (int j = threadIdx.x; j < Tin; j += 256) {
@@ -554,14 +622,14 @@ GTN_DEVICE void attn_main(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, u
       sm.wcum_s[j] += w;                                  // model.py:403
       wsum += w;
     }
-    wsum = block_reduce2(wsum, sm.scr, false);     // also orders the w_s writes before the reads below
+    wsum = block_reduce_w(wsum, sm.scr, false);     // also orders the w_s writes before the reads below
     float* aout = p.align_out + ((size_t)c.b * p.n_steps + t) * Tin;
     for (int jl = threadIdx.x; jl < c.jn; jl += 256) aout[c.j0 + jl] = sm.w_s[c.j0 + jl];
     PROF3(19);
     // context over this CTA's half of the time-varying columns: 8 columns per thread, warps split j
     const int E8 = p.E / 8, Eh8 = (E8 + 1) / 2;
     const int c8_0 = c.half * Eh8, c8_n = min(E8, c8_0 + Eh8) - c8_0;      // in units of 8 columns
-    const int mult = p.mult;
+    constexpr int mult = F32 ? 6 : 1;
     bf16* xc = BFP(p.xctx) + ((size_t)(t & 1) * p.B + c.b) * mult * p.Ep;    // ctx(t) -> buffer t & 1
     float* call = p.ctx_all + ((size_t)t * p.B + c.b) * p.D;
     for (int cb = 0; cb < c8_n; cb += 32) {
@@ -591,10 +659,10 @@ GTN_DEVICE void attn_main(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, u
           for (int e = 0; e < 8; ++e) acc[e] += w * mv[e];
         }
       }
-      __syncthreads();
+      WSYNC();
 #pragma unroll
       for (int e = 0; e < 8; ++e) sm.red_s[warp * 256 + lane * 8 + e] = acc[e];
-      __syncthreads();
+      WSYNC();
       for (int i = threadIdx.x; i < 256; i += 256) {
         const int c8i = cb + (i >> 3);
         if (c8i < c8_n) {
@@ -602,7 +670,7 @@ GTN_DEVICE void attn_main(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, u
 #pragma unroll
           for (int w = 0; w < 8; ++w) s += sm.red_s[w * 256 + i];
           const int d = (c8_0 + c8i) * 8 + (i & 7);
-          store_act(xc, d, p.Ep, p.prec, s);
+          store_act(xc, d, p.Ep, PREC, s);
           call[d] = s;
         }
       }
@@ -613,11 +681,11 @@ GTN_DEVICE void attn_main(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, u
       for (int i = threadIdx.x; i < p.Cc; i += 256) call[p.E + i] = p.mem_const[(size_t)c.b * p.Cc + i] * wsum;
     }
   }
-  __syncthreads();
+  WSYNC();
 }
 
-template <int N>
-__global__ void __launch_bounds__(256, 1)
+template <int N, bool F32>
+__global__ void __launch_bounds__(NTHREADS, 1)
 decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const int S) {
   constexpr int NC4 = (N < 64 ? N : 64) / 4;
   constexpr int CPT = 32 * NC4 / 256;
@@ -625,8 +693,9 @@ decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
   uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   Smem3 sm = carve3<N>(base, S);
   const int warp = threadIdx.x >> 5;
-  const int rank = (int)cluster_ctarank(), cid = (int)cluster_idx(), ncl = (int)cluster_count();
-  const int mult = p.mult;
+  const int rank = (int)cluster_ctarank(), cid = (int)cluster_idx();
+  constexpr int mult = F32 ? 6 : 1;
+  const int T = p.n_steps;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < S; ++s) { mbar_init(&sm.ring.full[s], 1); mbar_init(&sm.ring.empty[s], 1); }
@@ -635,6 +704,10 @@ decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
     mbar_init(sm.att_full, 1);
     mbar_init(sm.u_full, 1);
     mbar_init(sm.qg_full, 1);
+    mbar_init(sm.e_full, 1);
+    mbar_init(sm.go_late, 1);
+    mbar_init(sm.go_early, 1);
+    mbar_init(sm.go_c, 1);
     mbar_init(&sm.recv_full[0], 1);
     mbar_init(&sm.recv_full[1], 1);
     mbar_fence_init();
@@ -652,20 +725,23 @@ decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
       const bool late[3] = {false, true, true};
       build_sched(*sm.ks_c, 3, nkb, wb, late, rank);
     }
-    // resident weight k-blocks (tensor memory): the late k-blocks of A first (they sit on the serial chain), then the late
-    // k-blocks of C, then early ones
+    // resident weight k-blocks (tensor memory): all of A first -- its late k-blocks sit on the serial chain and its early
+    // ones are streamed in the shadow of barrier 2 only -- then C (streamed underneath the attention-LSTM epilogue)
     int slot = 0;
     const int nslots = res_slots<N>();
-    KSched* order[4] = {sm.ks_a, sm.ks_c, sm.ks_a, sm.ks_c};
-    for (int q = 0; q < 4; ++q) {
-      KSched& ks = *order[q];
-      const int lo = q < 2 ? ks.n_early : 0, hi = q < 2 ? ks.n : ks.n_early;
-      for (int i = lo; i < hi && slot < nslots; ++i) ks.slot[i] = (signed char)slot++;
-    }
+    for (int i = sm.ks_a->n - 1; i >= 0 && slot < nslots; --i) sm.ks_a->slot[i] = (signed char)slot++;
+    for (int i = sm.ks_c->n - 1; i >= 0 && slot < nslots; --i) sm.ks_c->slot[i] = (signed char)slot++;
   }
   if (warp == 2) tmem_alloc(sm.tmem_slot, 512);
-  for (int i = threadIdx.x; i < 128; i += 256) sm.v_s[i] = i < p.A ? p.v[i] : 0.f;
-  for (int i = threadIdx.x; i < TIN_MAX; i += 256) { sm.wprev_s[i] = 0.f; sm.wcum_s[i] = 0.f; }
+  if (threadIdx.x < NWORK) {
+    for (int i = threadIdx.x; i < 128; i += NWORK) sm.v_s[i] = i < p.A ? p.v[i] : 0.f;
+    for (int i = threadIdx.x; i < TIN_MAX; i += NWORK) { sm.wprev_s[i] = 0.f; sm.wcum_s[i] = 0.f; }
+    // Wq^T rows of the cluster's 32 attention-LSTM units: wq_s[u][a] = Wq[a][32 cid + u]
+    for (int i = threadIdx.x; i < 32 * 128; i += NWORK) {
+      const int u = i >> 7, a = i & 127;
+      sm.wq_s[i] = a < p.A ? p.wq_t[((size_t)cid * 32 + u) * p.A + a] : 0.f;
+    }
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -685,149 +761,149 @@ decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
     for (int i = 0; i < sm.ks_c->n; ++i)
       if (sm.ks_c->slot[i] >= 0) load_resident<N>(p.w_dec2, ldd, 4 * p.Hd, cid * TILE_M, sm.ks_c->wk[i], 1, sm.ks_c->slot[i], tmem_base);
   }
-  // the sequence of this CTA pair
-  AttnCtx ac;
-  ac.half = rank & 1; ac.peer = rank ^ 1;
-  ac.b = cid * 2 + (rank >> 1);
-  ac.active = ac.b < p.B;
-  ac.L = ac.active ? (p.lengths ? min(p.lengths[ac.b], p.Tin) : p.Tin) : 0;
-  {
-    const int JH = (p.Tin + 1) / 2;
-    ac.j0 = ac.half * JH;
-    ac.jn = min(p.Tin, ac.j0 + JH) - ac.j0;
-    ac.Wd = ac.jn + p.KS - 1;
-  }
-  float wqr[32];
-  {
-    // query-weight column of this thread (a = tid % 128) for the cluster's 32 attention-LSTM units: Wq[a][32 cid + u]
-    const int a = threadIdx.x & 127;
-#pragma unroll
-    for (int u = 0; u < 32; ++u) wqr[u] = a < p.A ? p.wq_t[((size_t)cid * 32 + u) * p.A + a] : 0.f;
-  }
   tc_fence_before();
   cluster_sync_all();     // peers' barriers / smem are initialised before any DSMEM traffic
   tc_fence_after();
 
   const KSched& ka = *sm.ks_a;
   const KSched& kc = *sm.ks_c;
-  const bool workA = ka.n > 0, workC = kc.n > 0;
-  unsigned int epoch = 0;
-  const unsigned int nblocks = gridDim.x;
-  uint32_t accA_par = 0, accC_par = 0, att_par = 0, qg_par = 0, round = 0, eround = 0;
-  uint32_t startedA = 0, startedC = 0;
-  float cA[CPT], cC[CPT];
+
+  if (warp >= 8) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    // =====================================================================================================================
+    // issuer warps: 8 = TMA producer, 9 = tcgen05.mma issuer.  Per frame t:
+    //   go_late(t)  -> late k-blocks of A(t) (commit acc_A), then ALL k-blocks of C(t-1) (commit acc_C)
+    //   go_early(t) -> early k-blocks of A(t+1)
+    // =====================================================================================================================
+    // One call site of issue_kblocks in a loop over "commands" (k = 0: early A(0); then per frame t: late A(t), all of
+    // C(t-1), early A(t+1)), each behind the go barrier that makes its operands visible.
+    uint32_t startedA = 0, startedC = 0;
+    // (warps 10 and 11 only exist to complete the third warpgroup: they go straight to the final cluster barrier)
+#pragma unroll 1
+    for (int k = 0; k <= 3 * (T + 1) && warp < 10; ++k) {
+      const int t = k == 0 ? 0 : (k - 1) / 3, ph = k == 0 ? 2 : (k - 1) % 3;       // ph 0: late A, 1: C, 2: early A
+      const int ta = k == 0 ? 0 : (ph == 2 ? t + 1 : t);                           // frame of the A job
+      bool run;
+      if (ph == 0) {
+        wait_bar(sm.go_late, (uint32_t)(t & 1));
+        run = t < T;
+      } else if (ph == 1) {
+        run = t > 0;
+        if (run && t < T) wait_bar(sm.go_c, (uint32_t)(t & 1));      // after the split-K exchange of A(t)
+      } else {
+        run = k == 0 || t + 1 < T;
+        if (run && k > 0) wait_bar(sm.go_early, (uint32_t)(t & 1));
+      }
+      if (!run) continue;
+      fence_proxy_async();
+      tc_fence_after();
+      XOps x;
+      if (ph == 1) {        // C(t-1): h_att(t-1) -> buffer ((t-1)&1)^1, ctx(t-1) -> buffer (t-1)&1, h_dec(t-2) -> buffer (t-1)&1
+        const int tc = t - 1;
+        x.map[0] = &maps.ha;  x.z[0] = (tc & 1) ^ 1;
+        x.map[1] = &maps.ctx; x.z[1] = tc & 1;
+        x.map[2] = &maps.hd;  x.z[2] = tc & 1;
+        startedC = 0;
+      } else {              // A(ta): pre(ta), ctx(ta-1) -> buffer (ta&1)^1, h_att(ta-1) -> buffer ta&1
+        x.map[0] = &maps.pre; x.z[0] = ta;
+        x.map[1] = &maps.ctx; x.z[1] = (ta & 1) ^ 1;
+        x.map[2] = &maps.ha;  x.z[2] = ta & 1;
+        if (ph == 2) startedA = 0;
+      }
+      const KSched& ks = ph == 1 ? kc : ka;
+      const int i0 = ph == 0 ? ks.n_early : 0, i1 = ph == 2 ? ks.n_early : ks.n;
+      issue_kblocks<N>(ks, i0, i1, ph == 1 ? &maps.w_dec : &maps.w_att, cid * TILE_M, x, sm.ring, ph == 1 ? tmem_accC : tmem_accA,
+                       tmem_base, ph == 1 ? startedC : startedA, ph == 0 ? sm.accA_full : (ph == 1 ? sm.accC_full : nullptr));
+    }
+  } else {
+    // =====================================================================================================================
+    // worker warps 0..7
+    // =====================================================================================================================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+    AttnCtx ac;                       // the sequence of this CTA pair
+    ac.half = rank & 1; ac.peer = rank ^ 1;
+    ac.b = cid * 2 + (rank >> 1);
+    ac.active = ac.b < p.B;
+    ac.L = ac.active ? (p.lengths ? min(p.lengths[ac.b], p.Tin) : p.Tin) : 0;
+    {
+      const int JH = (p.Tin + 1) / 2;
+      ac.j0 = ac.half * JH;
+      ac.jn = min(p.Tin, ac.j0 + JH) - ac.j0;
+      ac.Wd = ac.jn + p.KS - 1;
+    }
+    const bool workA = ka.n > 0, workC = kc.n > 0;
+    unsigned int epoch = 0;
+    const unsigned int nblocks = gridDim.x;
+    uint32_t accA_par = 0, accC_par = 0, att_par = 0, qg_par = 0, round = 0, eround = 0;
+    float cA[CPT], cC[CPT];
 #pragma unroll
-  for (int q = 0; q < CPT; ++q) { cA[q] = 0.f; cC[q] = 0.f; }
-  uint4 pmq[8];
-  const int T = p.n_steps;
-
-  auto opsA = [&](int t) {           // A(t): pre(t), ctx(t-1) -> buffer (t-1)&1 = (t&1)^1, h_att(t-1) -> buffer t&1
-    XOps x;
-    x.map[0] = &maps.pre; x.z[0] = t;
-    x.map[1] = &maps.ctx; x.z[1] = (t & 1) ^ 1;
-    x.map[2] = &maps.ha;  x.z[2] = t & 1;
-    return x;
-  };
-  auto opsC = [&](int t) {           // C(t): h_att(t) -> buffer (t&1)^1, ctx(t) -> buffer t&1, h_dec(t-1) -> buffer t&1
-    XOps x;
-    x.map[0] = &maps.ha;  x.z[0] = (t & 1) ^ 1;
-    x.map[1] = &maps.ctx; x.z[1] = t & 1;
-    x.map[2] = &maps.hd;  x.z[2] = t & 1;
-    return x;
-  };
-
-  // prologue: early k-blocks of A(0) (prenet(0) and the zero initial h_att)
-  {
-    startedA = 0;
-    const XOps x = opsA(0);
-    issue_kblocks<N>(ka, 0, ka.n_early, &maps.w_att, cid * TILE_M, x, sm.ring, tmem_accA, tmem_base, startedA, nullptr);
+    for (int q = 0; q < CPT; ++q) { cA[q] = 0.f; cC[q] = 0.f; }
+    uint4 pmq[8];
+    if (threadIdx.x == 64) mbar_arrive(sm.go_late);                 // frame 0 has no barrier in front of it
+    // one extra trip (t == T) runs the decoder LSTM cells of the last frame: every phase has ONE call site, which keeps the
+    // per-frame code path small (it is instruction-cache cold every frame)
+#pragma unroll 1
+    for (int t = 0; t <= T; ++t) {
+      PROF3(0);
+      if (t < T) {
+        // ---- W2: attention LSTM cells of frame t
+        lstm_epilogue<N, F32, true>(p, sm, t, cid, rank, workA, tmem_accA, sm.accA_full, accA_par, round, cA);
+        PROF3(4);
+        // ---- W3
+        grid_arrive(p.barrier);
+        epoch += nblocks;
+        PROF3(5);
+      }
+      // ---- W4: decoder LSTM cells of frame t - 1
+      if (t > 0) lstm_epilogue<N, F32, false>(p, sm, t - 1, cid, rank, workC, tmem_accC, sm.accC_full, accC_par, round, cC);
+      if (t == T) break;
+      PROF3(12);
+      // ---- W5.  The im2col tiles go into the receive buffer of the latest split-K exchange (its sums have been consumed,
+      // and no peer sends into it before the exchange after next); acc_C's tensor-memory columns are free again.
+      tc_fence_before();
+      WSYNC();
+      tc_fence_after();
+      uint8_t* im = N < 64 ? sm.im_s : reinterpret_cast<uint8_t*>(sm.recv + (size_t)((round - 1u) & 1u) * 4 * TILE_M * NC4);
+      attn_prepare<F32>(p, sm, ac, t, tmem_att, pmq, im);
+      PROF3(13);
+      // ---- W6
+      grid_wait(p.barrier, epoch);
+      PROF3(14);
+      // ---- W7
+      attn_main<F32>(p, sm, ac, t, tmem_att, att_par, qg_par, eround, pmq);
+      PROF3(20);
+      // ---- W8
+      tc_fence_before();
+      grid_arrive(p.barrier);
+      epoch += nblocks;
+      if (threadIdx.x == 64 && t + 1 < T) mbar_arrive(sm.go_early);
+      PROF3(21);
+      grid_wait(p.barrier, epoch, sm.go_late);
+      tc_fence_after();
+      PROF3(23);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && p.steps_done) *p.steps_done = T;
   }
-  for (int t = 0; t < T; ++t) {
-    PROF3(0);
-    // ---- W1: late parts (operands protected by barrier 2 of the previous frame)
-    {
-      const XOps x = opsA(t);
-      issue_kblocks<N>(ka, ka.n_early, ka.n, &maps.w_att, cid * TILE_M, x, sm.ring, tmem_accA, tmem_base, startedA, sm.accA_full);
-    }
-    if (t > 0) {
-      const XOps x = opsC(t - 1);
-      issue_kblocks<N>(kc, kc.n_early, kc.n, &maps.w_dec, cid * TILE_M, x, sm.ring, tmem_accC, tmem_base, startedC, sm.accC_full);
-    }
-    PROF3(1);
-    // ---- W2: attention LSTM cells of frame t
-    lstm_epilogue<N, true>(p, sm, t, cid, rank, workA, tmem_accA, sm.accA_full, accA_par, round, cA, wqr);
-    PROF3(4);
-    // ---- W3
-    grid_arrive(p.barrier);
-    epoch += nblocks;
-    PROF3(5);
-    // ---- W4: decoder LSTM cells of frame t - 1
-    if (t > 0) lstm_epilogue<N, false>(p, sm, t - 1, cid, rank, workC, tmem_accC, sm.accC_full, accC_par, round, cC, wqr);
-    PROF3(12);
-    // ---- W5 (the tensor-memory columns of acc_C are free again: every warp passed the exchange's thread syncs)
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    if (p.mem_bf16) attn_prepare<bf16>(p, sm, ac, t, tmem_att, pmq);
-    else attn_prepare<float>(p, sm, ac, t, tmem_att, pmq);
-    PROF3(13);
-    // ---- W6
-    grid_wait(p.barrier, epoch);
-    PROF3(14);
-    // ---- W7
-    if (p.mem_bf16) attn_main<bf16>(p, sm, ac, t, tmem_att, att_par, qg_par, eround, pmq);
-    else attn_main<float>(p, sm, ac, t, tmem_att, att_par, qg_par, eround, pmq);
-    PROF3(20);
-    // ---- W8
-    tc_fence_before();
-    grid_arrive(p.barrier);
-    epoch += nblocks;
-    tc_fence_after();
-    PROF3(21);
-    if (t + 1 < T) {
-      startedA = 0;
-      const XOps x = opsA(t + 1);
-      issue_kblocks<N>(ka, 0, ka.n_early, &maps.w_att, cid * TILE_M, x, sm.ring, tmem_accA, tmem_base, startedA, nullptr);
-    }
-    {
-      startedC = 0;
-      const XOps x = opsC(t);
-      issue_kblocks<N>(kc, 0, kc.n_early, &maps.w_dec, cid * TILE_M, x, sm.ring, tmem_accC, tmem_base, startedC, nullptr);
-    }
-    PROF3(22);
-    grid_wait(p.barrier, epoch);
-    PROF3(23);
-  }
-  // epilogue: C(T-1)
-  {
-    const int t = T;      // (PROF3 guard)
-    (void)t;
-    const XOps x = opsC(T - 1);
-    issue_kblocks<N>(kc, kc.n_early, kc.n, &maps.w_dec, cid * TILE_M, x, sm.ring, tmem_accC, tmem_base, startedC, sm.accC_full);
-    lstm_epilogue<N, false>(p, sm, T - 1, cid, rank, workC, tmem_accC, sm.accC_full, accC_par, round, cC, wqr);
-  }
-  if (blockIdx.x == 0 && threadIdx.x == 0 && p.steps_done) *p.steps_done = T;
   tc_fence_before();
   cluster_sync_all();     // no CTA exits while a peer may still write into its shared memory
   if (warp == 2) tmem_dealloc(tmem_base, 512);
-  (void)ncl;
 }
 
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
-template <int N>
+template <int N, bool F32>
 static int launch_fwd3_n(const Fwd2Maps& maps, const DecFwd& p, cudaStream_t st) {
   const size_t stage = (size_t)W_TILE_BYTES + (size_t)N * KB * 2;
   const size_t fixed = fwd3_fixed_bytes<N>() + 1024;
   int S = (int)((227 * 1024 - fixed) / stage);
   if (S > 12) S = 12;
-  if (S < 3 || (size_t)S * stage < (size_t)3 * W_TILE_BYTES) return FWD3_NOT_COVERED;      // im2col tiles + query partials alias the ring
+  if (S < 2) return FWD3_NOT_COVERED;
   const size_t smem = fixed + (size_t)S * stage;
-  auto kern = decoder_fwd3_kernel<N>;
+  auto kern = decoder_fwd3_kernel<N, F32>;
   GTN_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg = {};
-  cfg.blockDim = dim3(256);
+  cfg.blockDim = dim3(NTHREADS);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cudaLaunchAttribute attrs[2];
@@ -855,7 +931,9 @@ int launch_train_fwd3(const Fwd2Maps& maps, const DecFwd& p, cudaStream_t st) {
   const int m = p.mult;
   // every CTA's k-block list must fit the schedule table
   if ((m * (p.Pp + p.Ep + p.Hap) / KB + CL - 1) / CL + 3 > KMAX || (m * (p.Hap + p.Ep + p.Hdp) / KB + CL - 1) / CL + 3 > KMAX) return FWD3_NOT_COVERED;
-  return p.B <= 32 ? launch_fwd3_n<32>(maps, p, st) : launch_fwd3_n<64>(maps, p, st);
+  if ((p.prec == 3) != (p.mem_bf16 == 0)) return FWD3_NOT_COVERED;      // fp32 mode <-> fp32 encoder memory
+  if (p.prec == 3) return p.B <= 32 ? launch_fwd3_n<32, true>(maps, p, st) : launch_fwd3_n<64, true>(maps, p, st);
+  return p.B <= 32 ? launch_fwd3_n<32, false>(maps, p, st) : launch_fwd3_n<64, false>(maps, p, st);
 }
 
 }  // namespace gtn

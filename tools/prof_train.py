@@ -17,12 +17,12 @@ dec = Decoder(hp).cuda().train()
 mem = torch.cat((torch.randn(B, 150, 512).cuda() * 0.5, torch.rand(B, 1, 512).repeat_interleave(150, 1).cuda()), -1).requires_grad_(True)
 mels = (torch.randn(B, 80, T) * 2 - 5).clamp(-11.5, 2).cuda()
 # slots of the pipelined training kernel (gtn_decoder_fwd3.cu, PROF3)
-FW = {0: "step start (gsync2 of t-1 done)", 1: "late k-blocks issued (A, C)", 2: "A: acc done", 3: "A: exchange done",
+FW = {0: "step start (gsync2 of t-1 done)", 2: "A: acc done", 3: "A: exchange done",
       4: "A: cells + qpart done", 5: "arrived barrier 1", 10: "C(t-1): acc done", 11: "C(t-1): exchange done",
-      12: "C(t-1): cells done", 13: "attn prep (im2col, loc MMA) done", 14: "barrier 1 wait done", 16: "attn: q gathered",
-      17: "attn: energies", 18: "attn: cluster sync", 19: "attn: softmax", 20: "attn done (context)",
-      21: "arrived barrier 2", 22: "early k-blocks issued (A(t+1), C(t))", 23: "barrier 2 wait done"}
-FO = [0, 1, 2, 3, 4, 5, 10, 11, 12, 13, 14, 16, 17, 18, 19, 20, 21, 22, 23]
+      12: "C(t-1): cells done", 13: "attn prep (im2col, loc MMA) done", 14: "barrier 1 wait done", 15: "attn: q bulk copies issued",
+      24: "attn: q partials landed", 16: "attn: q summed", 17: "attn: energies", 18: "attn: pair exchange", 19: "attn: softmax",
+      20: "attn done (context)", 21: "arrived barrier 2", 23: "barrier 2 wait done"}
+FO = [0, 2, 3, 4, 5, 10, 11, 12, 13, 14, 15, 24, 16, 17, 18, 19, 20, 21, 23]
 BW = {0: "step start", 1: "P1: TMA issued", 2: "P1: acc done", 3: "P1: exchange done", 4: "P1: epilogue done", 5: "gsync done",
       10: "P2: loads + window", 11: "P2: dw + dot", 12: "P2: cluster sync 1", 13: "P2: dth tiles + dq/dv", 15: "P2: MMA + G to smem",
       16: "P2: d wcat", 17: "P2: cluster sync 2", 18: "P2 done", 19: "P2: dq in smem", 20: "cells done", 21: "gsync done"}
