@@ -16,6 +16,7 @@ typedef gtn_decoder_fwd_params DecFwd;
 struct Fwd2Maps {
   CUtensorMap w_att, w_dec, w_pre1, w_pre2, w_proj, uloc;
   CUtensorMap pre, ctx, ha, hd, xmel, xp1, xp2;
+  CUtensorMap qpart;      // fp32 [Ha/32][B][A] partial attention queries (pipelined training kernel: one box per sequence)
 };
 
 static constexpr int JH_MAX = 128;     // encoder positions per CTA of a pair (T_in <= 256)
@@ -54,6 +55,8 @@ GTN_DEVICE void ld8<bf16>(const bf16* p, float (&o)[8]) {
 
 int make_tma_map_3d(CUtensorMap* out, const void* base, long long d0, long long d1, long long d2, long long stride1_elems,
                     long long stride2_elems, int box1);
+int make_tma_map_f32_3d(CUtensorMap* out, const void* base, long long d0, long long d1, long long d2, long long stride1_elems,
+                        long long stride2_elems, int box0, int box1, int box2);
 
 // teacher-forced pass, pipelined kernel (gtn_decoder_fwd3.cu); FWD3_NOT_COVERED when the configuration is not covered by it
 static constexpr int FWD3_NOT_COVERED = 0x7fff0001;

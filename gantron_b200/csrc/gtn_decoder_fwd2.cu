@@ -848,6 +848,8 @@ extern "C" int gtn_decoder_forward2(const gtn_decoder_fwd_params* hp, void* stre
   if (p.train) {
     rc |= make_tma_map_3d(&maps.pre, p.pre_all, (long long)m * p.Pp, p.B, p.n_steps + 1, (long long)m * p.Pp,
                           (long long)p.B * m * p.Pp, N);
+    if (p.Ha / 32 <= 256)
+      rc |= make_tma_map_f32_3d(&maps.qpart, p.qpart, p.A, p.B, p.Ha / 32, p.A, (long long)p.B * p.A, p.A, 1, p.Ha / 32);
     maps.w_pre1 = maps.w_pre2 = maps.w_proj = maps.w_att;
     maps.xmel = maps.xp1 = maps.xp2 = maps.ctx;
   } else {
@@ -859,6 +861,7 @@ extern "C" int gtn_decoder_forward2(const gtn_decoder_fwd_params* hp, void* stre
     rc |= make_tma_map_3d(&maps.xp1, p.xp1, (long long)m * p.Pp, p.B, 1, (long long)m * p.Pp, 0, N);
     rc |= make_tma_map_3d(&maps.xp2, p.xp2, (long long)m * p.Pp, p.B, 1, (long long)m * p.Pp, 0, N);
     maps.pre = maps.xp2;
+    maps.qpart = maps.ctx;
   }
   if (rc) return rc;
   const int want = (p.Ha > p.Hd ? p.Ha : p.Hd) / 32;

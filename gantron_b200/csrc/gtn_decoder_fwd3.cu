@@ -84,7 +84,6 @@ struct Smem3 {
   uint64_t* e_full;     // energies of the peer half have arrived (remote arrive by the peer CTA)
   uint64_t* go_late;    // workers -> issuers: barrier 2 passed (context / h_dec operands visible)
   uint64_t* go_early;   // workers -> issuers: acc_A is free and h_att(t) is visible
-  uint64_t* go_c;       // workers -> issuers: the split-K exchange of A(t) is over (C's operand stream would slow it down)
   uint64_t* recv_full;  // [2]
   uint32_t* tmem_slot;
 };
@@ -139,7 +138,6 @@ GTN_DEVICE Smem3 carve3(uint8_t* base, int S) {
   m.e_full = b++;
   m.go_late = b++;
   m.go_early = b++;
-  m.go_c = b++;
   m.recv_full = b; b += 2;
   m.tmem_slot = reinterpret_cast<uint32_t*>(b + 1);
   return m;
@@ -278,7 +276,7 @@ GTN_DEVICE void issue_kblocks(const KSched& ks, int i0, int i1, const CUtensorMa
       const uint32_t a = smem_u32(base + (size_t)s * stage_bytes);
       if (res) {
         for (int j = 0; j < n; ++j) {
-          const uint32_t ta = tmem_base + res_col<N>(ks.slot[i + j]);
+          const uint32_t ta = tmem_base + res_col<2 * N>(ks.slot[i + j]);     // (acc_A and acc_C take 2 N columns)
           const uint64_t db = umma_desc_sw128(a + (uint32_t)j * X_BYTES);
           if (elect_one()) {
 #pragma unroll
@@ -352,7 +350,6 @@ GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int 
     float* stage = sm.recv + (size_t)((xr & 1u) ^ 1u) * 4 * TILE_M * NC4;
     exchange_bulk<CH, true>(has_work, tmem_acc, 0, recv, stage, &sm.recv_full[xr & 1u], (xr >> 1) & 1u, rank);
   }
-  if (IS_ATT && threadIdx.x == 64) mbar_arrive(sm.go_c);       // the decoder LSTM's operand stream may start
   PROF3(IS_ATT ? 3 : 11);
   const float pdrop = IS_ATT ? p.p_att : p.p_dec;
   const unsigned thr = IS_ATT ? p.thr_att : p.thr_dec;
@@ -420,35 +417,19 @@ GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int 
   }
 }
 
-GTN_DEVICE void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-               ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-
 // ---- attention of frame t for the sequence of this CTA pair --------------------------------------------------------------
 struct AttnCtx {
   int b, L, half, peer, j0, jn, Wd;
   bool active;
 };
 
-// Part 1 (does not depend on the attention LSTM of this frame): window of the previous / cumulative weights out of shared
-// memory, im2col tile, location GEMM on tcgen05, processed_memory prefetch into registers.
+// Part 1 (depends on nothing but the previous frame's attention weights, so it runs in the shadow of barrier 2 of the
+// previous frame): window of the previous / cumulative weights out of shared memory, im2col tile, location GEMM on tcgen05.
 template <bool F32>
-GTN_DEVICE void attn_prepare(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, uint32_t tmem_att, uint4 (&pmq)[8], uint8_t* im) {
-  typedef typename std::conditional<F32, float, bf16>::type MT;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int Tin = p.Tin, A = p.A, KS = p.KS, hk = (p.KS - 1) / 2;
+GTN_DEVICE void attn_prepare(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, uint32_t tmem_att, uint8_t* im) {
+  const int Tin = p.Tin, KS = p.KS, hk = (p.KS - 1) / 2;
   uint8_t* a_hi = im;                                    // im2col tiles, bf16 hi / lo planes (32 KB)
   uint8_t* a_lo = im + W_TILE_BYTES;
-  {
-    const int wq_ = warp & 3, a0_ = (warp >> 2) * 64, jl_ = wq_ * 32 + lane;
-    if (sizeof(MT) == 2 && c.active && jl_ < c.jn && (c.j0 + jl_) < c.L) {
-      const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const MT*>(p.pm) + ((size_t)c.b * Tin + (c.j0 + jl_)) * A + a0_);
-#pragma unroll
-      for (int g = 0; g < 8; ++g)
-        if (a0_ + g * 8 < A) pmq[g] = __ldg(src + g);
-    }
-  }
   if (c.active) {
     for (int i = threadIdx.x; i < 2 * c.Wd; i += 256) {
       const int ch = i / c.Wd, jj = i - ch * c.Wd, j = c.j0 + jj - hk;
@@ -483,8 +464,8 @@ GTN_DEVICE void attn_prepare(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t
 
 // Part 2 (after barrier 1): query, energies, masked softmax, context, weight state update.
 template <bool F32>
-GTN_DEVICE void attn_main(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, uint32_t tmem_att, uint32_t& att_par,
-                          uint32_t& qg_par, uint32_t& eround, const uint4 (&pmq)[8]) {
+GTN_DEVICE void attn_main(const DecFwd& p, const CUtensorMap* qmap, Smem3& sm, const AttnCtx& c, int t, uint32_t tmem_att,
+                          uint32_t& qg_par, uint32_t& eround) {
   // (eround doubles as the phase counter of e_full: one remote arrival per frame)
   typedef typename std::conditional<F32, float, bf16>::type MT;
   constexpr int PREC = F32 ? 3 : 1;
@@ -497,13 +478,26 @@ GTN_DEVICE void attn_main(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, u
   float* qg = sm.qg_s;                                                        // [ntq][128]
   const int ntq = p.Ha / 32;
   constexpr bool PM_PRE = sizeof(MT) == 2;
+  uint4 pmq[8];
   if (c.active) {
-    // the 32 partial queries of this sequence (one per attention-LSTM cluster): one 512-byte bulk copy each
-    if (warp == 0) {
-      if (lane == 0) mbar_expect_tx(sm.qg_full, (uint32_t)(ntq * A * 4));
-      __syncwarp();
-      for (int c0 = lane; c0 < ntq; c0 += 32)
-        bulk_g2s(qg + (size_t)c0 * 128, p.qpart + ((size_t)c0 * p.B + c.b) * A, (uint32_t)(A * 4), sm.qg_full);
+    // the partial queries of this sequence (one per attention-LSTM cluster): ONE TMA box [ntq][1][A] (per-lane bulk copies
+    // are serialised by the uniform datapath: 32 of them cost 3k cycles)
+    if (__shfl_sync(0xffffffffu, warp, 0) == 0 && elect_one()) {
+      mbar_expect_tx(sm.qg_full, (uint32_t)(ntq * A * 4));
+      asm volatile(
+          "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+          ::"r"(smem_u32(qg)), "l"(reinterpret_cast<uint64_t>(qmap)), "r"(smem_u32(sm.qg_full)), "r"(0), "r"(c.b), "r"(0)
+          : "memory");
+    }
+    // this thread's slice of processed_memory (row = encoder position, 64 attention columns): latency hidden by the gather
+    {
+      const int wq_ = warp & 3, a0_ = (warp >> 2) * 64, jl_ = wq_ * 32 + lane;
+      if (sizeof(MT) == 2 && jl_ < c.jn && (c.j0 + jl_) < c.L) {
+        const uint4* src = reinterpret_cast<const uint4*>(pm + ((size_t)c.b * Tin + (c.j0 + jl_)) * A + a0_);
+#pragma unroll
+        for (int g = 0; g < 8; ++g)
+          if (a0_ + g * 8 < A) pmq[g] = __ldg(src + g);
+      }
     }
     PROF3(15);
     wait_bar(sm.qg_full, qg_par);
@@ -517,7 +511,7 @@ GTN_DEVICE void attn_main(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, u
         for (int c0 = 0; c0 < ntq; c0 += 32) {
           float qv[32];
 #pragma unroll
-          for (int k = 0; k < 32; ++k) qv[k] = (c0 + k < ntq) ? qg[(size_t)(c0 + k) * 128 + a] : 0.f;
+          for (int k = 0; k < 32; ++k) qv[k] = (c0 + k < ntq) ? qg[(size_t)(c0 + k) * A + a] : 0.f;
 #pragma unroll
           for (int k = 0; k < 16; ++k) qv[k] += qv[k + 16];
 #pragma unroll
@@ -534,9 +528,7 @@ GTN_DEVICE void attn_main(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t, u
   WSYNC();
   PROF3(16);
   if (c.active) {
-    wait_bar(sm.att_full, att_par);
-    att_par ^= 1u;
-    tc_fence_after();
+    // (the location GEMM of this frame was issued and waited for in the shadow of the previous barrier 2)
     // thread = (row j = TMEM lane, 64-column half of the attention dimension)
     const int wq = warp & 3, a0 = (warp >> 2) * 64;
     const int jl = wq * 32 + lane;
@@ -707,7 +699,6 @@ decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
     mbar_init(sm.e_full, 1);
     mbar_init(sm.go_late, 1);
     mbar_init(sm.go_early, 1);
-    mbar_init(sm.go_c, 1);
     mbar_init(&sm.recv_full[0], 1);
     mbar_init(&sm.recv_full[1], 1);
     mbar_fence_init();
@@ -728,7 +719,7 @@ decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
     // resident weight k-blocks (tensor memory): all of A first -- its late k-blocks sit on the serial chain and its early
     // ones are streamed in the shadow of barrier 2 only -- then C (streamed underneath the attention-LSTM epilogue)
     int slot = 0;
-    const int nslots = res_slots<N>();
+    const int nslots = res_slots<2 * N>();
     for (int i = sm.ks_a->n - 1; i >= 0 && slot < nslots; --i) sm.ks_a->slot[i] = (signed char)slot++;
     for (int i = sm.ks_c->n - 1; i >= 0 && slot < nslots; --i) sm.ks_c->slot[i] = (signed char)slot++;
   }
@@ -747,7 +738,7 @@ decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
   tc_fence_after();
   const uint32_t tmem_base = *sm.tmem_slot;
   const uint32_t tmem_att = tmem_base + 256u;
-  const uint32_t tmem_accA = tmem_base, tmem_accC = tmem_base + 256u;      // acc_C aliases the location GEMM's columns
+  const uint32_t tmem_accA = tmem_base, tmem_accC = tmem_base + (uint32_t)N;
   if (threadIdx.x == 0) {
     mbar_expect_tx(sm.u_full, 2 * W_TILE_BYTES);
     tma_load_3d(sm.u_s, &maps.uloc, sm.u_full, 0, 0, 0);
@@ -757,9 +748,9 @@ decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
   {
     const long long lda = (long long)mult * (p.Pp + p.Ep + p.Hap), ldd = (long long)mult * (p.Hap + p.Ep + p.Hdp);
     for (int i = 0; i < sm.ks_a->n; ++i)
-      if (sm.ks_a->slot[i] >= 0) load_resident<N>(p.w_att2, lda, 4 * p.Ha, cid * TILE_M, sm.ks_a->wk[i], 1, sm.ks_a->slot[i], tmem_base);
+      if (sm.ks_a->slot[i] >= 0) load_resident<2 * N>(p.w_att2, lda, 4 * p.Ha, cid * TILE_M, sm.ks_a->wk[i], 1, sm.ks_a->slot[i], tmem_base);
     for (int i = 0; i < sm.ks_c->n; ++i)
-      if (sm.ks_c->slot[i] >= 0) load_resident<N>(p.w_dec2, ldd, 4 * p.Hd, cid * TILE_M, sm.ks_c->wk[i], 1, sm.ks_c->slot[i], tmem_base);
+      if (sm.ks_c->slot[i] >= 0) load_resident<2 * N>(p.w_dec2, ldd, 4 * p.Hd, cid * TILE_M, sm.ks_c->wk[i], 1, sm.ks_c->slot[i], tmem_base);
   }
   tc_fence_before();
   cluster_sync_all();     // peers' barriers / smem are initialised before any DSMEM traffic
@@ -789,7 +780,6 @@ decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
         run = t < T;
       } else if (ph == 1) {
         run = t > 0;
-        if (run && t < T) wait_bar(sm.go_c, (uint32_t)(t & 1));      // after the split-K exchange of A(t)
       } else {
         run = k == 0 || t + 1 < T;
         if (run && k > 0) wait_bar(sm.go_early, (uint32_t)(t & 1));
@@ -838,8 +828,18 @@ decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
     float cA[CPT], cC[CPT];
 #pragma unroll
     for (int q = 0; q < CPT; ++q) { cA[q] = 0.f; cC[q] = 0.f; }
-    uint4 pmq[8];
     if (threadIdx.x == 64) mbar_arrive(sm.go_late);                 // frame 0 has no barrier in front of it
+    // The im2col tiles live in the receive buffer of the latest split-K exchange (its sums have been consumed, and no peer
+    // sends into it before the exchange after next; before the first exchange: buffer 1) -- or in their own region (N < 64).
+    auto im2col_buf = [&]() -> uint8_t* {
+      return N < 64 ? sm.im_s : reinterpret_cast<uint8_t*>(sm.recv + (size_t)((round - 1u) & 1u) * 4 * TILE_M * NC4);
+    };
+    {
+      const int t = 0;
+      attn_prepare<F32>(p, sm, ac, 0, tmem_att, im2col_buf());       // zero initial weights (model.py:317-320)
+      if (ac.active) { wait_bar(sm.att_full, att_par); att_par ^= 1u; }
+      PROF3(13);
+    }
     // one extra trip (t == T) runs the decoder LSTM cells of the last frame: every phase has ONE call site, which keeps the
     // per-frame code path small (it is instruction-cache cold every frame)
 #pragma unroll 1
@@ -854,31 +854,32 @@ decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
         epoch += nblocks;
         PROF3(5);
       }
-      // ---- W4: decoder LSTM cells of frame t - 1
+      // ---- W4: decoder LSTM cells of frame t - 1, while the other CTAs arrive at barrier 1
       if (t > 0) lstm_epilogue<N, F32, false>(p, sm, t - 1, cid, rank, workC, tmem_accC, sm.accC_full, accC_par, round, cC);
       if (t == T) break;
       PROF3(12);
-      // ---- W5.  The im2col tiles go into the receive buffer of the latest split-K exchange (its sums have been consumed,
-      // and no peer sends into it before the exchange after next); acc_C's tensor-memory columns are free again.
-      tc_fence_before();
-      WSYNC();
-      tc_fence_after();
-      uint8_t* im = N < 64 ? sm.im_s : reinterpret_cast<uint8_t*>(sm.recv + (size_t)((round - 1u) & 1u) * 4 * TILE_M * NC4);
-      attn_prepare<F32>(p, sm, ac, t, tmem_att, pmq, im);
-      PROF3(13);
       // ---- W6
       grid_wait(p.barrier, epoch);
+      tc_fence_after();
       PROF3(14);
       // ---- W7
-      attn_main<F32>(p, sm, ac, t, tmem_att, att_par, qg_par, eround, pmq);
+      attn_main<F32>(p, &maps.qpart, sm, ac, t, tmem_att, qg_par, eround);
       PROF3(20);
-      // ---- W8
+      // ---- W8: barrier 2; in its shadow the issuers stream the early k-blocks of A(t+1) and the workers prepare the
+      // attention of frame t + 1 (the location GEMM only needs this frame's weights)
       tc_fence_before();
       grid_arrive(p.barrier);
       epoch += nblocks;
       if (threadIdx.x == 64 && t + 1 < T) mbar_arrive(sm.go_early);
       PROF3(21);
+      if (t + 1 < T) {
+        tc_fence_after();
+        attn_prepare<F32>(p, sm, ac, t + 1, tmem_att, im2col_buf());
+      }
+      PROF3(13);
       grid_wait(p.barrier, epoch, sm.go_late);
+      // the location GEMM is complete (its im2col tiles are in a receive buffer the next exchange stages into)
+      if (t + 1 < T && ac.active) { wait_bar(sm.att_full, att_par); att_par ^= 1u; }
       tc_fence_after();
       PROF3(23);
     }

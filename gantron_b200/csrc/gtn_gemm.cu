@@ -366,6 +366,25 @@ int make_tma_map_3d(CUtensorMap* out, const void* base, long long d0, long long 
   return make_map(out, base, d0, d1, d2, stride1_elems, stride2_elems, box1);
 }
 
+// 3-D fp32 tensor map without swizzle: dims (d0 inner, d1, d2), element strides of d1 / d2, box (box0, box1, box2)
+int make_tma_map_f32_3d(CUtensorMap* out, const void* base, long long d0, long long d1, long long d2, long long stride1_elems,
+                        long long stride2_elems, int box0, int box1, int box2) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return -3;
+  GTN_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base %p not 16-byte aligned", base);
+  GTN_REQUIRE((stride1_elems % 4) == 0 && (stride2_elems % 4) == 0 && (box0 % 4) == 0 && box0 <= 256 && box1 <= 256 && box2 <= 256,
+              "fp32 TMA map: strides / inner box must be multiples of 4 floats, boxes <= 256");
+  cuuint64_t dims[3] = {(cuuint64_t)d0, (cuuint64_t)d1, (cuuint64_t)d2};
+  cuuint64_t strides[2] = {(cuuint64_t)stride1_elems * 4, (cuuint64_t)stride2_elems * 4};
+  cuuint32_t box[3] = {(cuuint32_t)box0, (cuuint32_t)box1, (cuuint32_t)box2};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  GTN_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (fp32) failed with CUresult %d", (int)r);
+  return 0;
+}
+
 template <int BN>
 static int launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, GemmKernelParams kp, dim3 grid, cudaStream_t st) {
   // BN <= 128: shallow ring (<= 112 KB) so that TWO CTAs share an SM and one tile's epilogue overlaps the other's main
