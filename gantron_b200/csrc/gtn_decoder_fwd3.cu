@@ -46,6 +46,15 @@ namespace gtn {
 #define WSYNC() asm volatile("bar.sync 1, 256;" ::: "memory")      /* the eight worker warps */
 static constexpr int NWORK = 256;      // worker threads; warps 8 and 9 are the TMA producer and the MMA issuer
 static constexpr int NTHREADS = 384;   // three warpgroups: two of workers (232 registers), one of issuers (40 registers)
+// per-CTA skew probe: %globaltimer of every CTA at four points of frame 8 -> prof[512 + 4 cta + k]
+#define PROFG(k)                                                                            \
+  do {                                                                                      \
+    if (p.prof != nullptr && threadIdx.x == 0 && t == 8) {                                  \
+      unsigned long long gt_;                                                               \
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(gt_));                                \
+      p.prof[512 + 4 * blockIdx.x + (k)] = (long long)gt_;                                  \
+    }                                                                                       \
+  } while (0)
 static constexpr int KMAX = 64;        // k-blocks of one GEMM per CTA (fp32 mode: 6 planes x 10)
 
 struct KSched {            // this CTA's k-blocks of one per-frame GEMM, in issue order
@@ -164,6 +173,23 @@ GTN_DEVICE void grid_wait(unsigned int* counter, unsigned int target, uint64_t* 
   }
   WSYNC();
 }
+template <int N>
+GTN_DEVICE void flush_cell_saves(const DecFwd& p, int tc, int tile, int rank, const float (&sv)[32 * (N < 64 ? N : 64) / 4 / 256][6]) {
+  constexpr int NC4 = (N < 64 ? N : 64) / 4;
+  constexpr int CPT = 32 * NC4 / 256;
+#pragma unroll
+  for (int q = 0; q < CPT; ++q) {
+    const int idx = threadIdx.x + q * 256;
+    const int ul = idx & 31, bl = idx >> 5, b = rank * NC4 + bl, unit = tile * 32 + ul;
+    if (b < p.B) {
+      const size_t cell = ((size_t)tc * p.B + b) * p.Ha + unit;
+      reinterpret_cast<float4*>(p.gates_a)[cell] = make_float4(sv[q][0], sv[q][1], sv[q][2], sv[q][3]);
+      p.c_a_all[cell] = sv[q][4];
+      p.h_a_all[cell] = sv[q][5];
+    }
+  }
+}
+
 GTN_DEVICE void mbar_arrive_remote(uint32_t remote_bar) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote_bar) : "memory");
 }
@@ -311,7 +337,8 @@ GTN_DEVICE void issue_kblocks(const KSched& ks, int i0, int i1, const CUtensorMa
 // the same (unit, sequence) pairs in every frame).
 template <int N, bool F32, bool IS_ATT>
 GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int rank, bool has_work, uint32_t tmem_acc,
-                              uint64_t* acc_full, uint32_t& acc_par, uint32_t& round, float (&c_reg)[32 * (N < 64 ? N : 64) / 4 / 256]) {
+                              uint64_t* acc_full, uint32_t& acc_par, uint32_t& round, float (&c_reg)[32 * (N < 64 ? N : 64) / 4 / 256],
+                              float (&sv)[32 * (N < 64 ? N : 64) / 4 / 256][6]) {
   constexpr int CH = N < 64 ? N : 64;
   constexpr int NC4 = CH / 4;
   constexpr int CPT = 32 * NC4 / 256;
@@ -381,10 +408,16 @@ GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int 
         h = bits >= thr ? h * dscale : 0.f;
       }
       store_act(xh_next + (size_t)b * mult * Hp, unit, Hp, PREC, h);
-      const size_t cell = ((size_t)tc * p.B + b) * H + unit;
-      reinterpret_cast<float4*>(gates_all)[cell] = make_float4(i_, f_, g_, o_);
-      c_all[cell] = c_new;
-      h_all[cell] = h;
+      if (IS_ATT) {
+        // the saves for the backward pass are not needed by any other CTA: they are written AFTER this CTA has arrived at
+        // barrier 1 (flush_cell_saves), so that the barrier's release does not have to wait for them
+        sv[q][0] = i_; sv[q][1] = f_; sv[q][2] = g_; sv[q][3] = o_; sv[q][4] = c_new; sv[q][5] = h;
+      } else {
+        const size_t cell = ((size_t)tc * p.B + b) * H + unit;
+        reinterpret_cast<float4*>(gates_all)[cell] = make_float4(i_, f_, g_, o_);
+        c_all[cell] = c_new;
+        h_all[cell] = h;
+      }
     }
     if (IS_ATT) sm.hs[ul * NC4 + bl] = h;
   }
@@ -465,7 +498,7 @@ GTN_DEVICE void attn_prepare(const DecFwd& p, Smem3& sm, const AttnCtx& c, int t
 // Part 2 (after barrier 1): query, energies, masked softmax, context, weight state update.
 template <bool F32>
 GTN_DEVICE void attn_main(const DecFwd& p, const CUtensorMap* qmap, Smem3& sm, const AttnCtx& c, int t, uint32_t tmem_att,
-                          uint32_t& qg_par, uint32_t& eround) {
+                          uint32_t& qg_par, uint32_t& eround, float& ctx_save, float& wsum_out) {
   // (eround doubles as the phase counter of e_full: one remote arrival per frame)
   typedef typename std::conditional<F32, float, bf16>::type MT;
   constexpr int PREC = F32 ? 3 : 1;
@@ -623,7 +656,7 @@ GTN_DEVICE void attn_main(const DecFwd& p, const CUtensorMap* qmap, Smem3& sm, c
     const int c8_0 = c.half * Eh8, c8_n = min(E8, c8_0 + Eh8) - c8_0;      // in units of 8 columns
     constexpr int mult = F32 ? 6 : 1;
     bf16* xc = BFP(p.xctx) + ((size_t)(t & 1) * p.B + c.b) * mult * p.Ep;    // ctx(t) -> buffer t & 1
-    float* call = p.ctx_all + ((size_t)t * p.B + c.b) * p.D;
+    wsum_out = wsum;
     for (int cb = 0; cb < c8_n; cb += 32) {
       const int c8 = cb + lane;
       float acc[8];
@@ -663,17 +696,27 @@ GTN_DEVICE void attn_main(const DecFwd& p, const CUtensorMap* qmap, Smem3& sm, c
           for (int w = 0; w < 8; ++w) s += sm.red_s[w * 256 + i];
           const int d = (c8_0 + c8i) * 8 + (i & 7);
           store_act(xc, d, p.Ep, PREC, s);
-          call[d] = s;
+          if (c8_n <= 32) ctx_save = s;                    // saved after the barrier arrive (attn_flush_saves)
+          else p.ctx_all[((size_t)t * p.B + c.b) * p.D + d] = s;
         }
       }
     }
-    // time-constant columns: context = const * sum_j w_j  (second CTA of the pair; saved for the weight-gradient GEMMs
-    // only: the per-frame GEMMs see these columns as a per-sequence bias)
-    if (c.half == 1 || Tin == 1) {
-      for (int i = threadIdx.x; i < p.Cc; i += 256) call[p.E + i] = p.mem_const[(size_t)c.b * p.Cc + i] * wsum;
-    }
   }
   WSYNC();
+}
+
+// The context save of frame t (weight-gradient GEMM operand of the backward pass): written after the CTA has arrived at
+// barrier 2.  Time-constant columns: context = const * sum_j w_j (second CTA of the pair; the per-frame GEMMs see these
+// columns as a per-sequence bias).
+GTN_DEVICE void attn_flush_saves(const DecFwd& p, const AttnCtx& c, int t, float ctx_save, float wsum) {
+  if (!c.active) return;
+  const int E8 = p.E / 8, Eh8 = (E8 + 1) / 2;
+  const int c8_0 = c.half * Eh8, c8_n = min(E8, c8_0 + Eh8) - c8_0;
+  float* call = p.ctx_all + ((size_t)t * p.B + c.b) * p.D;
+  if (c8_n <= 32 && (int)(threadIdx.x >> 3) < c8_n) call[(c8_0 + (threadIdx.x >> 3)) * 8 + (threadIdx.x & 7)] = ctx_save;
+  if (c.half == 1 || p.Tin == 1) {
+    for (int i = threadIdx.x; i < p.Cc; i += 256) call[p.E + i] = p.mem_const[(size_t)c.b * p.Cc + i] * wsum;
+  }
 }
 
 template <int N, bool F32>
@@ -825,7 +868,8 @@ decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
     unsigned int epoch = 0;
     const unsigned int nblocks = gridDim.x;
     uint32_t accA_par = 0, accC_par = 0, att_par = 0, qg_par = 0, round = 0, eround = 0;
-    float cA[CPT], cC[CPT];
+    float cA[CPT], cC[CPT], svA[CPT][6];
+    float ctx_save = 0.f, wsum = 0.f;
 #pragma unroll
     for (int q = 0; q < CPT; ++q) { cA[q] = 0.f; cC[q] = 0.f; }
     if (threadIdx.x == 64) mbar_arrive(sm.go_late);                 // frame 0 has no barrier in front of it
@@ -845,32 +889,38 @@ decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
 #pragma unroll 1
     for (int t = 0; t <= T; ++t) {
       PROF3(0);
+      PROFG(0);
       if (t < T) {
         // ---- W2: attention LSTM cells of frame t
-        lstm_epilogue<N, F32, true>(p, sm, t, cid, rank, workA, tmem_accA, sm.accA_full, accA_par, round, cA);
+        lstm_epilogue<N, F32, true>(p, sm, t, cid, rank, workA, tmem_accA, sm.accA_full, accA_par, round, cA, svA);
         PROF3(4);
+        PROFG(1);
         // ---- W3
         grid_arrive(p.barrier);
         epoch += nblocks;
+        flush_cell_saves<N>(p, t, cid, rank, svA);
         PROF3(5);
       }
       // ---- W4: decoder LSTM cells of frame t - 1, while the other CTAs arrive at barrier 1
-      if (t > 0) lstm_epilogue<N, F32, false>(p, sm, t - 1, cid, rank, workC, tmem_accC, sm.accC_full, accC_par, round, cC);
+      if (t > 0) lstm_epilogue<N, F32, false>(p, sm, t - 1, cid, rank, workC, tmem_accC, sm.accC_full, accC_par, round, cC, svA);
       if (t == T) break;
       PROF3(12);
       // ---- W6
       grid_wait(p.barrier, epoch);
       tc_fence_after();
       PROF3(14);
+      PROFG(2);
       // ---- W7
-      attn_main<F32>(p, &maps.qpart, sm, ac, t, tmem_att, qg_par, eround);
+      attn_main<F32>(p, &maps.qpart, sm, ac, t, tmem_att, qg_par, eround, ctx_save, wsum);
       PROF3(20);
+      PROFG(3);
       // ---- W8: barrier 2; in its shadow the issuers stream the early k-blocks of A(t+1) and the workers prepare the
       // attention of frame t + 1 (the location GEMM only needs this frame's weights)
       tc_fence_before();
       grid_arrive(p.barrier);
       epoch += nblocks;
       if (threadIdx.x == 64 && t + 1 < T) mbar_arrive(sm.go_early);
+      attn_flush_saves(p, ac, t, ctx_save, wsum);
       PROF3(21);
       if (t + 1 < T) {
         tc_fence_after();

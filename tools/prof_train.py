@@ -28,14 +28,14 @@ BW = {0: "step start", 1: "P1: TMA issued", 2: "P1: acc done", 3: "P1: exchange 
       16: "P2: d wcat", 17: "P2: cluster sync 2", 18: "P2 done", 19: "P2: dq in smem", 20: "cells done", 21: "gsync done"}
 BO = [0, 1, 2, 3, 4, 5, 10, 11, 12, 13, 15, 16, 17, 19, 20, 21]
 for rep in range(2):
-    pf = torch.zeros(16 * 32, dtype=torch.int64, device="cuda")
+    pf = torch.zeros(16 * 32 + 4 * 160, dtype=torch.int64, device="cuda")
     pb = torch.zeros(2 * 16 * 32, dtype=torch.int64, device="cuda")
     decoder_ops.PROF_BUFFER, decoder_ops.PROF_BUFFER_BWD = pf, pb
     dec.zero_grad()
     mel, gate, align = decoder_ops.decoder_train_forward(dec, mem, mels, torch.full((B,), 150).cuda(), 5)
     (mel.square().mean() + gate.square().mean()).backward()
     torch.cuda.synchronize()
-for name, buf, names, order in (("forward", pf, FW, FO), ("backward CTA 0", pb[:512], BW, BO), ("backward CTA 48", pb[512:], BW, BO)):
+for name, buf, names, order in (("forward", pf[:512], FW, FO), ("backward CTA 0", pb[:512], BW, BO), ("backward CTA 48", pb[512:], BW, BO)):
     pr = buf.cpu().view(16, 32)
     t = 8
     print(f"--- {name} B={B}: cycles since step start (frame slot {t})")
@@ -46,3 +46,17 @@ for name, buf, names, order in (("forward", pf, FW, FO), ("backward CTA 0", pb[:
             print(f"   {names[sl]:40s} {v:8d}  (+{v - prev})")
             prev = v
     print(f"   next step start          {int(pr[t + 1, 0] - pr[t, 0]):8d}")
+
+# per-CTA skew of the forward kernel at frame 8 (%globaltimer, ns): loop top, barrier-1 arrive, barrier-1 done, barrier-2 arrive
+g = pf[512:512 + 4 * 128].cpu().view(128, 4).double()
+if float(g.abs().sum()) > 0:
+    base = g[:, 0].min()
+    names = ["frame start", "arrive barrier 1", "barrier 1 passed", "arrive barrier 2"]
+    for k in range(4):
+        col = g[:, k] - base
+        print(f"   skew {names[k]:20s}: min {col.min():8.0f} ns  median {col.median():8.0f}  max {col.max():8.0f}  (CTA of max: {int(col.argmax())})")
+    late = (g[:, 3] - g[:, 3].min())
+    print("   arrive-2 lateness by rank (ns):", [round(float(late[r::4].mean())) for r in range(4)])
+    print("   arrive-2 lateness by cluster (ns):", [round(float(late[4 * c:4 * c + 4].mean())) for c in range(32)])
+    late1 = (g[:, 1] - g[:, 1].min())
+    print("   arrive-1 lateness by cluster (ns):", [round(float(late1[4 * c:4 * c + 4].mean())) for c in range(32)])
