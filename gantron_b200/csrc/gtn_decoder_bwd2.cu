@@ -18,6 +18,7 @@
 // All WEIGHT gradients are deferred: the kernel stores per-frame gate / query gradients and the host issues a
 // handful of K = T*B tcgen05 GEMMs afterwards (gtn_gemm_tn_bf16).
 #include <cstdlib>
+#include <type_traits>
 #include "gtn_decoder2.cuh"
 #include "gtn_internal.h"
 #include "../../include/gantron_b200.h"
@@ -69,7 +70,9 @@ struct SmemB {
   uint64_t* g_full;
   uint64_t* ut_full;
   uint64_t* recv_full;  // [2] bulk-copy exchange: one per receive buffer
+  uint64_t* mem_full;   // the encoder-memory tile of this CTA's positions has landed in the ring (bulk copy)
   uint32_t* tmem_slot;
+  uint32_t ring_bytes;
 };
 
 template <int N>
@@ -93,6 +96,7 @@ GTN_DEVICE SmemB carveB(uint8_t* base, int S) {
   m.ring.prod_it = m.ring.mma_it = 0;
   size_t ring_b = (size_t)S * m.ring.stage_bytes;
   if (ring_b < (size_t)P2_RING_BYTES) ring_b = P2_RING_BYTES;
+  m.ring_bytes = (uint32_t)ring_b;
   uint8_t* p = base + ring_b;
   m.recv = reinterpret_cast<float*>(p); p += (recv_b < 32768 ? 32768 : recv_b);
   m.ut_s = p; p += 4 * 8192;
@@ -117,9 +121,35 @@ GTN_DEVICE SmemB carveB(uint8_t* base, int S) {
   m.g_full = b++;
   m.ut_full = b++;
   m.recv_full = b; b += 2;
+  m.mem_full = b++;
   m.tmem_slot = reinterpret_cast<uint32_t*>(b + 1);
   return m;
 }
+
+// split grid barrier: ARRIVE, then work that does not depend on the other CTAs, then WAIT (thread 0 carries the fences)
+GTN_DEVICE void grid_arrive2(unsigned int* counter) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    fence_proxy_async();
+    red_release_add(counter, 1u);
+  }
+}
+GTN_DEVICE void grid_wait2(unsigned int* counter, unsigned int target) {
+  if (threadIdx.x == 0) {
+    long long t0 = clock64();
+    while (ld_acquire_u32(counter) < target) {
+      if (clock64() - t0 > 20000000000LL) __trap();
+    }
+    fence_proxy_async();
+  }
+  __syncthreads();
+}
+
+// Where the attention backward keeps its tiles inside the (then idle) TMA ring.  `fast` layout (one sequence per CTA pair):
+// im2col tiles at the END of the ring and the bf16 encoder-memory tile of this CTA's positions (bulk-copied once per frame,
+// while P1's epilogue and barrier 1 are in flight) from byte 32 K on -- behind the staging area of P1's split-K exchange;
+// the dth tiles overwrite it after the d(weights) reduction has consumed it.
+static constexpr uint32_t MEM_TILE_OFF = 2 * W_TILE_BYTES;
 
 GTN_DEVICE void red_add_f2(float* addr, float a, float b) {
   asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(a), "f"(b) : "memory");
@@ -154,15 +184,17 @@ GTN_DEVICE CellIn cell_load(const DecBwd2& p, int t, int b, int unit, int H, con
   return in;
 }
 // Writes the four pre-activation gate gradients (gate-major K order g*H + unit) as GEMM operand and as fp32 save.
+template <bool F32>
 GTN_DEVICE void cell_apply(const DecBwd2& p, const CellIn& in, int t, int b, int unit, int H, float dh, float* dc_carry,
                            float* dg_all, bf16* xdg, unsigned site, unsigned thr, float pdrop) {
+  constexpr int PREC = F32 ? 3 : 1, MULT = F32 ? 6 : 1;
   const size_t ci = (size_t)b * H + unit;
   if (p.use_dropout && thr != 0u) {
     const uint32_t bits = philox_bits(p.seed, site, (uint32_t)t, (uint32_t)ci);
     dh = bits >= thr ? dh * (1.0f / (1.0f - pdrop)) : 0.f;
   }
   const float4 g = in.g;
-  const float tc = p.prec == 1 ? tanh_fast(in.c) : tanh_acc(in.c);
+  const float tc = F32 ? tanh_acc(in.c) : tanh_fast(in.c);
   const float d_o = dh * tc;
   const float dc = dh * g.w * (1.f - tc * tc) + in.dc;
   dc_carry[ci] = dc * g.y;
@@ -171,22 +203,23 @@ GTN_DEVICE void cell_apply(const DecBwd2& p, const CellIn& in, int t, int b, int
   const float dgg = dc * g.x * (1.f - g.z * g.z);
   const float dgo = d_o * g.w * (1.f - g.w);
   const size_t g0 = ((size_t)t * p.B + b) * 4 * H + unit;
-  if (p.flags & 2) {
+  if (!F32) {
     bf16* dgb = reinterpret_cast<bf16*>(dg_all);          // bf16 mode: the saves are GEMM operands only
     dgb[g0] = __float2bfloat16_rn(dgi); dgb[g0 + H] = __float2bfloat16_rn(dgf);
     dgb[g0 + 2 * H] = __float2bfloat16_rn(dgg); dgb[g0 + 3 * H] = __float2bfloat16_rn(dgo);
   } else {
     dg_all[g0] = dgi; dg_all[g0 + H] = dgf; dg_all[g0 + 2 * H] = dgg; dg_all[g0 + 3 * H] = dgo;
   }
-  bf16* xr = xdg + (size_t)b * p.mult * 4 * H;
-  store_act(xr, unit, 4 * H, p.prec, dgi);
-  store_act(xr, H + unit, 4 * H, p.prec, dgf);
-  store_act(xr, 2 * H + unit, 4 * H, p.prec, dgg);
-  store_act(xr, 3 * H + unit, 4 * H, p.prec, dgo);
+  bf16* xr = xdg + (size_t)b * MULT * 4 * H;
+  store_act(xr, unit, 4 * H, PREC, dgi);
+  store_act(xr, H + unit, 4 * H, PREC, dgf);
+  store_act(xr, 2 * H + unit, 4 * H, PREC, dgg);
+  store_act(xr, 3 * H + unit, 4 * H, PREC, dgo);
 }
 // Two ADJACENT units (unit even) at once: in bf16 mode the eight bf16 saves / GEMM operands of the pair go out as four + four
 // 32-bit stores instead of sixteen 16-bit ones, and the carried dc as one float2.
 struct CellGrad { float dgi, dgf, dgg, dgo, dcn; };
+template <bool F32>
 GTN_DEVICE CellGrad cell_math(const DecBwd2& p, const CellIn& in, int t, size_t ci, float dh, unsigned site, unsigned thr,
                               float pdrop) {
   if (p.use_dropout && thr != 0u) {
@@ -194,7 +227,7 @@ GTN_DEVICE CellGrad cell_math(const DecBwd2& p, const CellIn& in, int t, size_t 
     dh = bits >= thr ? dh * (1.0f / (1.0f - pdrop)) : 0.f;
   }
   const float4 g = in.g;
-  const float tc = p.prec == 1 ? tanh_fast(in.c) : tanh_acc(in.c);
+  const float tc = F32 ? tanh_acc(in.c) : tanh_fast(in.c);
   const float d_o = dh * tc;
   const float dc = dh * g.w * (1.f - tc * tc) + in.dc;
   CellGrad r;
@@ -205,15 +238,16 @@ GTN_DEVICE CellGrad cell_math(const DecBwd2& p, const CellIn& in, int t, size_t 
   r.dgo = d_o * g.w * (1.f - g.w);
   return r;
 }
+template <bool F32>
 GTN_DEVICE void cell_apply2(const DecBwd2& p, const CellIn (&in)[2], int t, int b, int unit, int H, float dh0, float dh1,
                             float* dc_carry, float* dg_all, bf16* xdg, unsigned site, unsigned thr, float pdrop) {
-  if (!(p.prec == 1 && (p.flags & 2))) {          // fp32 mode: per-unit path (three planes per operand)
-    cell_apply(p, in[0], t, b, unit, H, dh0, dc_carry, dg_all, xdg, site, thr, pdrop);
-    cell_apply(p, in[1], t, b, unit + 1, H, dh1, dc_carry, dg_all, xdg, site, thr, pdrop);
+  if (F32) {                                      // fp32 mode: per-unit path (three planes per operand)
+    cell_apply<F32>(p, in[0], t, b, unit, H, dh0, dc_carry, dg_all, xdg, site, thr, pdrop);
+    cell_apply<F32>(p, in[1], t, b, unit + 1, H, dh1, dc_carry, dg_all, xdg, site, thr, pdrop);
     return;
   }
   const size_t ci = (size_t)b * H + unit;
-  const CellGrad a = cell_math(p, in[0], t, ci, dh0, site, thr, pdrop), c = cell_math(p, in[1], t, ci + 1, dh1, site, thr, pdrop);
+  const CellGrad a = cell_math<F32>(p, in[0], t, ci, dh0, site, thr, pdrop), c = cell_math<F32>(p, in[1], t, ci + 1, dh1, site, thr, pdrop);
   *reinterpret_cast<float2*>(dc_carry + ci) = make_float2(a.dcn, c.dcn);
   const uint32_t pi = pack_bf16x2(a.dgi, c.dgi), pf = pack_bf16x2(a.dgf, c.dgf), pg = pack_bf16x2(a.dgg, c.dgg),
                  po = pack_bf16x2(a.dgo, c.dgo);
@@ -222,27 +256,29 @@ GTN_DEVICE void cell_apply2(const DecBwd2& p, const CellIn (&in)[2], int t, int 
   uint32_t* xr = reinterpret_cast<uint32_t*>(xdg + (size_t)b * 4 * H + unit);
   xr[0] = pi; xr[H >> 1] = pf; xr[H] = pg; xr[3 * (H >> 1)] = po;
 }
+template <bool F32>
 GTN_DEVICE void cell_backward2(const DecBwd2& p, int t, int b, int unit, int H, float dh, const float* gates_all,
                                const float* c_all, float* dc_carry, float* dg_all, bf16* xdg, unsigned site, unsigned thr,
                                float pdrop) {
   const CellIn in = cell_load(p, t, b, unit, H, gates_all, c_all, dc_carry);
-  cell_apply(p, in, t, b, unit, H, dh, dc_carry, dg_all, xdg, site, thr, pdrop);
+  cell_apply<F32>(p, in, t, b, unit, H, dh, dc_carry, dg_all, xdg, site, thr, pdrop);
 }
 
 // decoder LSTM cell backward of frame t (prologue only: frame T-1 has no recurrent carry), spread over the grid
+template <bool F32>
 GTN_DEVICE void dec_cell_prologue(const DecBwd2& p, int t) {
   const int n = p.B * p.Hd;
   for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
     const int b = idx / p.Hd, u = idx - b * p.Hd;
     const float dh = p.dproj_all[((size_t)t * p.B + b) * (p.Hd + p.D) + u];
-    cell_backward2(p, t, b, u, p.Hd, dh, p.gates_d, p.c_d_all, p.dc_d, p.dgd_all, BFP(p.xdg_d), 4u, p.thr_dec, p.p_dec);
+    cell_backward2<F32>(p, t, b, u, p.Hd, dh, p.gates_d, p.c_d_all, p.dc_d, p.dgd_all, BFP(p.xdg_d), 4u, p.thr_dec, p.p_dec);
   }
 }
 
 // ------------------------------------------------------------------------------------------------
 // P1: data-gradient GEMM tiles
 // ------------------------------------------------------------------------------------------------
-template <int N>
+template <int N, bool F32>
 GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, int t, int it, int rank, int cid, int ncl,
                              uint32_t tmem_base, uint32_t& acc_par, uint32_t& round, int res_n) {
   constexpr int CH = N < 64 ? N : 64;
@@ -258,7 +294,7 @@ GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, 
     job.wmap = dec ? &maps.wT_dec : &maps.wT_att;
     job.row0 = row0;
     job.nseg = 1;
-    job.seg[0] = dec ? XSeg{&maps.xdg_d, p.mult * 4 * p.Hd / KB, cur} : XSeg{&maps.xdg_a, p.mult * 4 * p.Ha / KB, 0};
+    job.seg[0] = dec ? XSeg{&maps.xdg_d, (F32 ? 6 : 1) * 4 * p.Hd / KB, cur} : XSeg{&maps.xdg_a, (F32 ? 6 : 1) * 4 * p.Ha / KB, 0};
     job.nkb = job.seg[0].nkb;
     job.res_n = tile == cid ? res_n : 0;
     job.res_slot0 = 0;
@@ -274,7 +310,7 @@ GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, 
     for (int c0 = 0; c0 < N; c0 += CH) {
       float* recv = sm.recv + (size_t)(N > 64 ? (round & 1u) : 0u) * 4 * TILE_M * NC4;
       const int bbase = c0 + rank * NC4;
-      if (N > 64) {
+      if constexpr (N > 64) {
         // two receive buffers: the other one is the staging area (see exchange_bulk)
         exchange_bulk<CH>(has_work, tmem_base, c0, recv, sm.recv + (size_t)((round & 1u) ^ 1u) * 4 * TILE_M * NC4,
                           &sm.recv_full[round & 1u], (round >> 1) & 1u, rank);
@@ -316,9 +352,10 @@ GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, 
 // 128 KB per CTA per frame through a ~30 B/clk port; 64 KB this way).  Thread = (unit pair pr, half h): during the Wq
 // product h selects the half of the attention dimension (both sequences), partial sums meet in shared memory, and for the
 // cell arithmetic h selects the sequence.  dq2 = [2][128] full d query of the two sequences, part = [2][2][128][2] scratch.
+template <bool F32>
 GTN_DEVICE void quad_cells(const DecBwd2& p, const float* dq2, float* part, int t, int it, int b0, int b1, int rank) {
   const int nxt = (it & 1) ^ 1;
-  bf16* xnext_d = BFP(p.xdg_d) + (size_t)nxt * p.B * p.mult * 4 * p.Hd;
+  bf16* xnext_d = BFP(p.xdg_d) + (size_t)nxt * p.B * (F32 ? 6 : 1) * 4 * p.Hd;
   const int Hq_a = ((p.Ha / CL + 1) / 2) * 2, ua_beg = rank * Hq_a, ua_end = min(p.Ha, (rank + 1) * Hq_a);
   const int Hq_d = ((p.Hd / CL + 1) / 2) * 2, ud_beg = rank * Hq_d, ud_end = min(p.Hd, (rank + 1) * Hq_d);
   const int na = (max(ua_end - ua_beg, 0) + 255) / 256, nd = t > 0 ? (max(ud_end - ud_beg, 0) + 255) / 256 : 0;
@@ -353,7 +390,7 @@ GTN_DEVICE void quad_cells(const DecBwd2& p, const float* dq2, float* part, int 
       const float* d0 = dq2 + a_lo;
       const float* d1 = dq2 + 128 + a_lo;
       const int ld = p.Ha >> 1;
-      if (p.prec == 1) {
+      if constexpr (!F32) {
         const uint32_t* w = reinterpret_cast<const uint32_t*>(p.wq_au) + (size_t)a_lo * ld + (ua >> 1);
 #pragma unroll 32
         for (int a = 0; a < A2; ++a) {
@@ -375,6 +412,7 @@ GTN_DEVICE void quad_cells(const DecBwd2& p, const float* dq2, float* part, int 
         }
       }
     }
+    PROFB(25);
     // part[h][seq][pr] (float2): this thread's half-sums for both sequences
     __syncthreads();                                                 // previous round's readers are done
     reinterpret_cast<float2*>(part)[(h * 2 + 0) * 128 + pr] = make_float2(s00, s01);
@@ -383,11 +421,12 @@ GTN_DEVICE void quad_cells(const DecBwd2& p, const float* dq2, float* part, int 
     const float2 h0 = reinterpret_cast<const float2*>(part)[(0 * 2 + h) * 128 + pr];
     const float2 h1 = reinterpret_cast<const float2*>(part)[(1 * 2 + h) * 128 + pr];
     const float s0 = h0.x + h1.x, s1 = h0.y + h1.y;                  // sequence h, units ua, ua + 1
+    PROFB(26);
     if (okd) {
-      cell_apply2(p, cd, t - 1, b, ud, p.Hd, addd.x, addd.y, p.dc_d, p.dgd_all, xnext_d, 4u, p.thr_dec, p.p_dec);
+      cell_apply2<F32>(p, cd, t - 1, b, ud, p.Hd, addd.x, addd.y, p.dc_d, p.dgd_all, xnext_d, 4u, p.thr_dec, p.p_dec);
     }
     if (oka) {
-      cell_apply2(p, ca, t, b, ua, p.Ha, s0 + adda.x, s1 + adda.y, p.dc_a, p.dga_all, BFP(p.xdg_a), 3u, p.thr_att, p.p_att);
+      cell_apply2<F32>(p, ca, t, b, ua, p.Ha, s0 + adda.x, s1 + adda.y, p.dc_a, p.dga_all, BFP(p.xdg_a), 3u, p.thr_att, p.p_att);
     }
   }
 }
@@ -413,9 +452,39 @@ GTN_DEVICE void ld8b<bf16>(const bf16* p, float (&o)[8]) {
   }
 }
 
-template <typename MT>
+// Window, im2col tiles and the frame's alignment row of ONE sequence: everything of the attention backward that depends on
+// the forward pass's saves only.  In the `fast` layout it runs between ARRIVE and WAIT of barrier 1.
+GTN_DEVICE void attn_bwd_prepare(const DecBwd2& p, SmemB& sm, int t, int b, bool active, int j0, int jn, uint8_t* im_hi, uint8_t* im_lo) {
+  const int Tin = p.Tin, KS = p.KS, hk = (p.KS - 1) / 2;
+  const int Wd = jn + KS - 1;
+  const size_t tb = (size_t)t * p.B + b, bt = (size_t)b * p.T + t;
+  if (active) {
+    for (int j = threadIdx.x; j < Tin; j += blockDim.x) sm.w_s[j] = p.align[bt * Tin + j];
+    for (int i = threadIdx.x; i < 2 * Wd; i += blockDim.x) {
+      const int ch = i / Wd, jj = i - ch * Wd, j = j0 + jj - hk;
+      float val = 0.f;
+      if (j >= 0 && j < Tin) val = ch == 0 ? (t > 0 ? p.align[(bt - 1) * Tin + j] : 0.f) : p.cum_all[tb * Tin + j];
+      sm.wcat[i] = val;
+    }
+  }
+  __syncthreads();
+  if (active) {
+    build_im2col(sm.wcat, Wd, KS, jn, im_hi, im_lo);
+    // zero the K-rows of the im2col tiles beyond jn (they are the K extent of dU += dth^T . im2col)
+    for (int i = threadIdx.x; i < (TILE_M - jn) * 8; i += blockDim.x) {
+      const int r = jn + (i >> 3), chunk = i & 7;
+      const uint32_t off = sw128_off(r, chunk);
+      *reinterpret_cast<uint4*>(im_hi + off) = make_uint4(0u, 0u, 0u, 0u);
+      *reinterpret_cast<uint4*>(im_lo + off) = make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
+}
+
+// prepared: attn_bwd_prepare already ran for this frame (fast layout); mem_tile: the encoder-memory tile is in the ring
+template <bool F32>
 GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int rank, int cid, int ncl, uint32_t tmem_g,
-                                uint32_t tmem_du, uint32_t& g_par, uint32_t& xround) {
+                                uint32_t tmem_du, uint32_t& g_par, uint32_t& xround, bool prepared, bool mem_tile, uint32_t& mem_par) {
+  typedef typename std::conditional<F32, float, bf16>::type MT;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int Tin = p.Tin, A = p.A, KS = p.KS, hk = (p.KS - 1) / 2, E = p.E;
   const int half = rank & 1, peer = rank ^ 1;
@@ -426,8 +495,8 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
   const MT* mem = reinterpret_cast<const MT*>(p.mem_enc);
   uint8_t* dth_hi = sm.ring.base;                        // 2 blocks of [128 rows j][64 a] (a < 64, a >= 64)
   uint8_t* dth_lo = sm.ring.base + 2 * W_TILE_BYTES;
-  uint8_t* im_hi = sm.ring.base + 4 * W_TILE_BYTES;
-  uint8_t* im_lo = sm.ring.base + 5 * W_TILE_BYTES;
+  uint8_t* im_hi = sm.ring.base + (prepared ? sm.ring_bytes - 2 * W_TILE_BYTES : 4 * W_TILE_BYTES);
+  uint8_t* im_lo = im_hi + W_TILE_BYTES;
   float* G_s = sm.recv;                                  // [128][64], column index XOR (row & 31)
   const int niter = (p.B + npairs - 1) / npairs;
   for (int itb = 0; itb < niter; ++itb) {
@@ -438,32 +507,63 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
     const uint32_t xb = xround & 1u;
     ++xround;
     if (active) {
-      for (int j = threadIdx.x; j < Tin; j += blockDim.x) sm.w_s[j] = p.align[bt * Tin + j];
       for (int d = threadIdx.x; d < E; d += blockDim.x) {
         const float val = p.dproj_all[tb * (p.Hd + p.D) + p.Hd + d] + __ldcg(&p.dctx_dec[(size_t)b * p.Ep + d]) +
                           __ldcg(&p.dctx_att[(size_t)b * p.Ep + d]);
         sm.dctx_s[d] = val;
         if (half == 0) p.dctx_all[bt * E + d] = val;
       }
-      for (int i = threadIdx.x; i < 2 * Wd; i += blockDim.x) {
-        const int ch = i / Wd, jj = i - ch * Wd, j = j0 + jj - hk;
-        float val = 0.f;
-        if (j >= 0 && j < Tin) val = ch == 0 ? (t > 0 ? p.align[(bt - 1) * Tin + j] : 0.f) : p.cum_all[tb * Tin + j];
-        sm.wcat[i] = val;
-      }
     }
+    if (!prepared) attn_bwd_prepare(p, sm, t, b, active, j0, jn, im_hi, im_lo);
     __syncthreads();
     PROFB(10);
     float dot_part = 0.f;
-    if (active) {
-      build_im2col(sm.wcat, Wd, KS, jn, im_hi, im_lo);
-      // zero the K-rows of the im2col tiles beyond jn (they are the K extent of dU += dth^T . im2col)
-      for (int i = threadIdx.x; i < (TILE_M - jn) * 8; i += blockDim.x) {
-        const int r = jn + (i >> 3), chunk = i & 7;
-        const uint32_t off = sw128_off(r, chunk);
-        *reinterpret_cast<uint4*>(im_hi + off) = make_uint4(0u, 0u, 0u, 0u);
-        *reinterpret_cast<uint4*>(im_lo + off) = make_uint4(0u, 0u, 0u, 0u);
+    if (active && mem_tile) {
+      // d w_j = mem[j][:] . dctx over this CTA's positions, from the tile in shared memory: one warp per position, lanes over
+      // the columns (16 bytes per lane and trip: conflict-free)
+      wait_bar(sm.mem_full, mem_par);
+      PROFB(22);
+      const bf16* mt = reinterpret_cast<const bf16*>(sm.ring.base + MEM_TILE_OFF);
+      // warp w owns positions w, w + 8, ... (at most 16): ALL of its rows accumulate at once (independent FMA chains; the
+      // one-row-at-a-time version spent 6.7k cycles in dependent FMAs and shuffles), then one 16-value butterfly
+      float acc[16];
+#pragma unroll
+      for (int r = 0; r < 16; ++r) acc[r] = 0.f;
+      for (int d = lane * 8; d < E; d += 256) {
+        const float4 c0 = *reinterpret_cast<const float4*>(sm.dctx_s + d), c1 = *reinterpret_cast<const float4*>(sm.dctx_s + d + 4);
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+          const int jl = warp + 8 * r;
+          if (jl < jn && j0 + jl < L) {
+            const uint4 q = *reinterpret_cast<const uint4*>(mt + (size_t)jl * E + d);
+            const float s0 = __uint_as_float(q.x << 16) * c0.x + __uint_as_float(q.y << 16) * c0.z;
+            const float s1 = __uint_as_float(q.x & 0xFFFF0000u) * c0.y + __uint_as_float(q.y & 0xFFFF0000u) * c0.w;
+            const float s2 = __uint_as_float(q.z << 16) * c1.x + __uint_as_float(q.w << 16) * c1.z;
+            const float s3 = __uint_as_float(q.z & 0xFFFF0000u) * c1.y + __uint_as_float(q.w & 0xFFFF0000u) * c1.w;
+            acc[r] += (s0 + s1) + (s2 + s3);
+          }
+        }
       }
+      // butterfly reduce-scatter of the 16 row sums over the 32 lanes: lane l ends up with row ((l >> 1) & 15)
+#define GTN_BFLY(OFF, NN)                                                                   \
+      {                                                                                     \
+        const bool up = (lane & (OFF)) != 0;                                                \
+        _Pragma("unroll") for (int i = 0; i < (NN); ++i) {                                  \
+          const float keep = up ? acc[i + (NN)] : acc[i];                                   \
+          const float send = up ? acc[i] : acc[i + (NN)];                                   \
+          acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, (OFF));                        \
+        }                                                                                   \
+      }
+      GTN_BFLY(16, 8) GTN_BFLY(8, 4) GTN_BFLY(4, 2) GTN_BFLY(2, 1)
+#undef GTN_BFLY
+      acc[0] += __shfl_xor_sync(0xffffffffu, acc[0], 1);
+      {
+        // bits of the row index, most significant first, were chosen by lane bits 4, 3, 2, 1
+        const int r = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+        const int jl = warp + 8 * r;
+        if ((lane & 1) == 0 && jl < jn) sm.dw_s[j0 + jl] = acc[0];
+      }
+    } else if (active) {
       // d w_j over this CTA's positions: one warp per position, lanes over the time-varying columns
       constexpr int RD = 4;
       for (int jl0 = warp; jl0 < jn; jl0 += 8 * RD) {
@@ -496,6 +596,8 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
         }
       }
     }
+    if (mem_tile) mem_par ^= 1u;
+    PROFB(23);
     __syncthreads();
     if (active) {
       // + what reaches w_j through the next frame's location features and the upstream alignment gradient
@@ -512,6 +614,7 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
     if (active) {
       for (int jl = threadIdx.x; jl < jn; jl += blockDim.x) dot_part += sm.w_s[j0 + jl] * sm.dw_s[j0 + jl];
     }
+    PROFB(24);
     dot_part = block_sum2(dot_part, sm.scr);
     if (active && threadIdx.x == 0) {
       sm.dot_s[xb * 2] = dot_part;
@@ -722,7 +825,7 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
     PROFB(19);
     {
       const int b0 = cid * 2 + itb * npairs, b1 = b0 + 1;
-      if (b0 < p.B) quad_cells(p, sm.dqf_s, sm.dctx_s, t, it, b0, b1, rank);
+      if (b0 < p.B) quad_cells<F32>(p, sm.dqf_s, sm.dctx_s, t, it, b0, b1, rank);
     }
     __syncthreads();
   }
@@ -773,7 +876,7 @@ GTN_DEVICE void prefetch_frame(const DecBwd2& p, int t, int rank, int cid, int n
   }
 }
 
-template <int N>
+template <int N, bool F32>
 __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_constant__ Bwd2Maps maps, const DecBwd2 p, const int S) {
   extern __shared__ uint8_t smem_raw[];
   // align by pointer arithmetic (no integer round trip) so that the compiler keeps the shared address space: LDS / STS, not generic LD / ST
@@ -788,6 +891,7 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
     mbar_init(sm.ut_full, 1);
     mbar_init(&sm.recv_full[0], 1);
     mbar_init(&sm.recv_full[1], 1);
+    mbar_init(sm.mem_full, 1);
     mbar_fence_init();
   }
   if (warp == 2) tmem_alloc(sm.tmem_slot, 512);
@@ -813,7 +917,7 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
     if (nD + nA <= ncl && cid < nD + nA) {
       const bool dec = cid < nD;
       const int H = dec ? p.Hd : p.Ha;
-      const int nkb = p.mult * 4 * H / KB, kb0 = rank * nkb / CL;
+      const int nkb = (F32 ? 6 : 1) * 4 * H / KB, kb0 = rank * nkb / CL;
       res_n = min((rank + 1) * nkb / CL - kb0, res_slots<N>());
       load_resident<N>(dec ? p.wT_dec2 : p.wT_att2, (long long)nkb * KB, dec ? R_dec : R_att, (dec ? cid : cid - nD) * TILE_M, kb0,
                        res_n, 0, tmem_base);
@@ -829,20 +933,48 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
   tc_fence_after();
 
   unsigned int epoch = 0;
-  uint32_t acc_par = 0, g_par = 0, round = 0, xround = 0;
+  uint32_t acc_par = 0, g_par = 0, round = 0, xround = 0, mem_par = 0;
   const unsigned int nblocks = gridDim.x;
-  dec_cell_prologue(p, p.T - 1);
+  // `fast` layout: one data-gradient tile per cluster and one sequence per CTA pair.  Then the part of the attention backward
+  // that only reads the forward pass's saves runs between ARRIVE and WAIT of barrier 1, and (bf16 memory) the encoder-memory
+  // tile of this CTA's positions -- 75 x 512 x 2 B, constant over the frames but too big to stay on chip next to the TMA ring --
+  // is bulk-copied into the idle ring once per frame instead of being read row by row through L1 (dw: 7.2k -> ~1k cycles).
+  const int R_dec_ = p.Ha + p.E + p.Hd, R_att_ = p.E + p.Ha;
+  const bool fast = ((R_dec_ + TILE_M - 1) / TILE_M + (R_att_ + TILE_M - 1) / TILE_M) <= ncl && p.B <= 2 * ncl;
+  const int fJH = (p.Tin + 1) / 2, fj0 = (rank & 1) * fJH, fjn = min(p.Tin, fj0 + fJH) - fj0;
+  const int fb = cid * 2 + (rank >> 1);
+  const bool factive = fb < p.B;
+  const bool mem_tile = !F32 && fast && (p.E % 8) == 0 &&
+                        MEM_TILE_OFF + (uint32_t)fJH * p.E * 2u + 2u * W_TILE_BYTES <= sm.ring_bytes;
+  uint8_t* const f_im = sm.ring.base + sm.ring_bytes - 2 * W_TILE_BYTES;
+  dec_cell_prologue<F32>(p, p.T - 1);
   grid_sync2(p.barrier, epoch, nblocks);
   int it = 0;
   for (int t = p.T - 1; t >= 0; --t, ++it) {
     PROFB(0);
     if (p.flags & 1) prefetch_frame(p, t, rank, cid, ncl);
-    dgrad_phase2<N>(p, maps, sm, t, it, rank, cid, ncl, tmem_base, acc_par, round, res_n);
+    dgrad_phase2<N, F32>(p, maps, sm, t, it, rank, cid, ncl, tmem_base, acc_par, round, res_n);
+    if (mem_tile && factive && threadIdx.x == 0 && fjn > 0) {
+      // (P1's MMAs have drained the ring: every thread passed the exchange's syncs behind the accumulator wait)
+      const uint32_t bytes = (uint32_t)fjn * p.E * 2u;
+      mbar_expect_tx(sm.mem_full, bytes);
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(smem_u32(sm.ring.base + MEM_TILE_OFF)),
+                     "l"(reinterpret_cast<const bf16*>(p.mem_enc) + ((size_t)fb * p.Tin + fj0) * p.E), "r"(bytes),
+                     "r"(smem_u32(sm.mem_full)) : "memory");
+    }
     PROFB(4);
-    grid_sync2(p.barrier, epoch, nblocks);
+    if (fast) {
+      grid_arrive2(p.barrier);
+      epoch += nblocks;
+      attn_bwd_prepare(p, sm, t, fb, factive, fj0, fjn, f_im, f_im + W_TILE_BYTES);
+      PROFB(6);
+      grid_wait2(p.barrier, epoch);
+    } else {
+      grid_sync2(p.barrier, epoch, nblocks);
+    }
     PROFB(5);
-    if (p.mem_bf16) attn_bwd_phase2<bf16>(p, sm, t, it, rank, cid, ncl, tmem_g, tmem_du, g_par, xround);
-    else attn_bwd_phase2<float>(p, sm, t, it, rank, cid, ncl, tmem_g, tmem_du, g_par, xround);
+    attn_bwd_phase2<F32>(p, sm, t, it, rank, cid, ncl, tmem_g, tmem_du, g_par, xround, fast, !F32 && mem_tile && fjn > 0, mem_par);
     PROFB(20);
     grid_sync2(p.barrier, epoch, nblocks);
     PROFB(21);
@@ -882,7 +1014,7 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
 int make_tma_map_3d(CUtensorMap* out, const void* base, long long d0, long long d1, long long d2, long long stride1_elems,
                     long long stride2_elems, int box1);
 
-template <int N>
+template <int N, bool F32>
 static int bwd2_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attrs, int& S, size_t& smem) {
   const size_t stage = (size_t)W_TILE_BYTES + (size_t)N * KB * 2;
   const size_t fixed = bwd2_fixed_bytes<N>() + 1024;
@@ -893,7 +1025,7 @@ static int bwd2_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attrs, int&
   if (ring_b < (size_t)P2_RING_BYTES) ring_b = P2_RING_BYTES;
   smem = fixed + ring_b;
   GTN_REQUIRE(smem <= 227 * 1024, "decoder backward: shared memory budget exceeded (%zu B, N=%d)", smem, N);
-  GTN_CUDA_OK(cudaFuncSetAttribute(decoder_bwd2_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  GTN_CUDA_OK(cudaFuncSetAttribute(decoder_bwd2_kernel<N, F32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cfg = cudaLaunchConfig_t{};
   cfg.blockDim = dim3(256);
   cfg.dynamicSmemBytes = smem;
@@ -908,21 +1040,21 @@ static int bwd2_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attrs, int&
 template <int N>
 static int bwd2_grid(int want, int* ncl_out) {
   cudaLaunchConfig_t cfg; cudaLaunchAttribute attrs[2]; int S; size_t smem;
-  int rc = bwd2_config<N>(cfg, attrs, S, smem);
+  int rc = bwd2_config<N, false>(cfg, attrs, S, smem);
   if (rc) return rc;
   cfg.numAttrs = 1;
   cfg.gridDim = dim3(CL * want);
   int max_cl = 0;
-  GTN_CUDA_OK(cudaOccupancyMaxActiveClusters(&max_cl, decoder_bwd2_kernel<N>, &cfg));
+  GTN_CUDA_OK(cudaOccupancyMaxActiveClusters(&max_cl, decoder_bwd2_kernel<N, false>, &cfg));
   GTN_REQUIRE(max_cl >= 1, "decoder backward: no cluster of %d CTAs fits on this device", CL);
   *ncl_out = max_cl < want ? max_cl : want;
   return 0;
 }
 
-template <int N>
+template <int N, bool F32>
 static int launch_bwd2(const Bwd2Maps& maps, const DecBwd2& p, int ncl, cudaStream_t st) {
   cudaLaunchConfig_t cfg; cudaLaunchAttribute attrs[2]; int S; size_t smem;
-  int rc = bwd2_config<N>(cfg, attrs, S, smem);
+  int rc = bwd2_config<N, F32>(cfg, attrs, S, smem);
   if (rc) return rc;
   cfg.stream = st;
   cfg.numAttrs = profiler_attached() ? 1 : 2;   // profilers that cannot replay cooperative launches
@@ -930,7 +1062,7 @@ static int launch_bwd2(const Bwd2Maps& maps, const DecBwd2& p, int ncl, cudaStre
   GTN_REQUIRE((p.B + 2 * ncl - 1) / (2 * ncl) <= 8, "decoder backward: batch %d needs more than 8 sequences per CTA pair on %d clusters",
               p.B, ncl);
   cfg.gridDim = dim3(CL * ncl);
-  GTN_CUDA_OK(cudaLaunchKernelEx(&cfg, decoder_bwd2_kernel<N>, maps, p, S));
+  GTN_CUDA_OK(cudaLaunchKernelEx(&cfg, decoder_bwd2_kernel<N, F32>, maps, p, S));
   count_launch();
   return 0;
 }
@@ -981,8 +1113,17 @@ extern "C" int gtn_decoder_backward2(const gtn_decoder_bwd2_params* hp, void* st
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const int ncl = grid / CL;
-  if (N == 32) return launch_bwd2<32>(maps, p, ncl, st);
-  if (N == 64) return launch_bwd2<64>(maps, p, ncl, st);
-  if (N == 128) return launch_bwd2<128>(maps, p, ncl, st);
-  return launch_bwd2<256>(maps, p, ncl, st);
+  // precision is a compile-time property of the kernels (half the code: the per-frame path is instruction-cache cold every frame)
+  GTN_REQUIRE((p.prec == 3) == (p.mem_bf16 == 0) && ((p.flags & 2) != 0) == (p.prec == 1),
+              "decoder backward: fp32 mode <-> fp32 encoder memory and fp32 gate-gradient saves");
+  if (p.prec == 3) {
+    if (N == 32) return launch_bwd2<32, true>(maps, p, ncl, st);
+    if (N == 64) return launch_bwd2<64, true>(maps, p, ncl, st);
+    if (N == 128) return launch_bwd2<128, true>(maps, p, ncl, st);
+    return launch_bwd2<256, true>(maps, p, ncl, st);
+  }
+  if (N == 32) return launch_bwd2<32, false>(maps, p, ncl, st);
+  if (N == 64) return launch_bwd2<64, false>(maps, p, ncl, st);
+  if (N == 128) return launch_bwd2<128, false>(maps, p, ncl, st);
+  return launch_bwd2<256, false>(maps, p, ncl, st);
 }

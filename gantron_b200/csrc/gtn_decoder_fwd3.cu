@@ -237,9 +237,11 @@ GTN_DEVICE void build_sched(KSched& ks, int nseg, const int* nkb, const int* wba
   ks.n = n;
 }
 
-struct XOps {                       // activation operands of one GEMM at one frame
-  const CUtensorMap* map[3];
-  int z[3];
+struct XOps {                       // activation operands of one GEMM at one frame (no arrays: the segment index is a run-time
+  const CUtensorMap *m0, *m1, *m2;  // value, and an indexed array would live in local memory)
+  int z0, z1, z2;
+  GTN_DEVICE const CUtensorMap* map(int s) const { return s == 0 ? m0 : (s == 1 ? m1 : m2); }
+  GTN_DEVICE int z(int s) const { return s == 0 ? z0 : (s == 1 ? z1 : z2); }
 };
 
 // Issue k-blocks [i0, i1) of the schedule: producer = warp 8, MMA issuer = warp 9, both in warp-uniform control flow (see
@@ -272,13 +274,13 @@ GTN_DEVICE void issue_kblocks(const KSched& ks, int i0, int i1, const CUtensorMa
           mbar_expect_tx(&full[s], (uint32_t)n * X_BYTES);
           for (int j = 0; j < n; ++j) {
             const int sg = ks.seg[i + j];
-            tma_load_3d(st + (size_t)j * X_BYTES, x.map[sg], &full[s], ks.xk[i + j] * KB, 0, x.z[sg]);
+            tma_load_3d(st + (size_t)j * X_BYTES, x.map(sg), &full[s], ks.xk[i + j] * KB, 0, x.z(sg));
           }
         } else {
           const int sg = ks.seg[i];
           mbar_expect_tx(&full[s], W_TILE_BYTES + X_BYTES);
           tma_load_3d(st, wmap, &full[s], ks.wk[i] * KB, row0, 0);
-          tma_load_3d(st + W_TILE_BYTES, x.map[sg], &full[s], ks.xk[i] * KB, 0, x.z[sg]);
+          tma_load_3d(st + W_TILE_BYTES, x.map(sg), &full[s], ks.xk[i] * KB, 0, x.z(sg));
         }
       }
       __syncwarp();
@@ -833,14 +835,14 @@ decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
       XOps x;
       if (ph == 1) {        // C(t-1): h_att(t-1) -> buffer ((t-1)&1)^1, ctx(t-1) -> buffer (t-1)&1, h_dec(t-2) -> buffer (t-1)&1
         const int tc = t - 1;
-        x.map[0] = &maps.ha;  x.z[0] = (tc & 1) ^ 1;
-        x.map[1] = &maps.ctx; x.z[1] = tc & 1;
-        x.map[2] = &maps.hd;  x.z[2] = tc & 1;
+        x.m0 = &maps.ha;  x.z0 = (tc & 1) ^ 1;
+        x.m1 = &maps.ctx; x.z1 = tc & 1;
+        x.m2 = &maps.hd;  x.z2 = tc & 1;
         startedC = 0;
       } else {              // A(ta): pre(ta), ctx(ta-1) -> buffer (ta&1)^1, h_att(ta-1) -> buffer ta&1
-        x.map[0] = &maps.pre; x.z[0] = ta;
-        x.map[1] = &maps.ctx; x.z[1] = (ta & 1) ^ 1;
-        x.map[2] = &maps.ha;  x.z[2] = ta & 1;
+        x.m0 = &maps.pre; x.z0 = ta;
+        x.m1 = &maps.ctx; x.z1 = (ta & 1) ^ 1;
+        x.m2 = &maps.ha;  x.z2 = ta & 1;
         if (ph == 2) startedA = 0;
       }
       const KSched& ks = ph == 1 ? kc : ka;
