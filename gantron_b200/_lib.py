@@ -62,6 +62,8 @@ SIGNATURES = {
     "gtn_attn_guide_loss_bwd": (c_i, [c_p, c_i, c_i, c_i, c_p, c_p, c_f, c_p, c_p, c_p]),
     "gtn_decoder_forward2": (c_i, [c_p, c_p]),
     "gtn_sizeof": (c_i, [c_i]),
+    "gtn_decoder_infer1_ctas": (c_i, []),
+    "gtn_decoder_infer1": (c_i, [c_p, c_p]),
     "gtn_decoder_bwd2_grid": (c_i, [c_i, c_i, c_i, c_i]),
     "gtn_decoder_backward2": (c_i, [c_p, c_p]),
 }
@@ -87,6 +89,18 @@ class DecoderFwdParams(C.Structure):
                               "q_all", "th_all", "f_all", "cum_all",
                               "w_att2", "w_dec2", "u_loc", "wq_t", "prof", "gbias_a", "gbias_d", "pbias")]
         + [("Ep", c_i), ("reserved0", c_i)]
+    )
+
+
+class DecoderInfer1Params(C.Structure):
+    """Mirror of `gtn_decoder_infer1_params` (include/gantron_b200.h)."""
+    _fields_ = (
+        [(n, c_i) for n in ("Tin", "Tp", "n_steps", "Ha", "Hd", "P", "A", "KS", "NM", "NMp", "nu", "ncta", "cols_a", "cols_d",
+                            "ignore_stop", "reserved0")]
+        + [("gate_threshold", c_f), ("reserved1", c_f), ("seed", c_ull)]
+        + [(n, c_p) for n in ("wimg", "w1", "w2", "u", "wq", "v", "wp_h", "pc", "pbias", "b_att", "gbias_a", "gbias_d", "pm",
+                              "h_att_g", "h_dec_g", "e_g", "qacc", "macc", "barrier", "mel_out", "gate_out", "align_out",
+                              "steps_done", "done", "lengths_out")]
     )
 
 

@@ -46,6 +46,7 @@ void gtn_reset_launch_count(void) { g_launches.store(0); }
 int gtn_sizeof(int which) {
   if (which == 0) return (int)sizeof(gtn_decoder_fwd_params);
   if (which == 2) return (int)sizeof(gtn_decoder_bwd2_params);
+  if (which == 3) return (int)sizeof(gtn_decoder_infer1_params);
   return -1;
 }
 

@@ -257,6 +257,112 @@ def split_memory(memory: torch.Tensor, enc_dim: int, const_tail: Optional[bool])
     return enc_dim if const_tail else memory.shape[2]
 
 
+def _infer1_packs(dec, pk: "PackedDecoder", E: int, ncta: int):
+    """Utterance-independent operands of the batch-1 decode kernel (gtn_decoder_infer1.cu), cached per weight version."""
+    cache = getattr(pk, "_i1", None)
+    key = (pk._versions, E, ncta)
+    if cache is not None and cache["key"] == key:
+        return cache
+    d = pk.dims
+    P = PackedDecoder._params(dec)
+    f = lambda t: t.detach().float()
+    Pn, Ha, Hd = d.prenet, d.att_rnn, d.dec_rnn
+    wa, wha, wd, whd = f(P["w_ih_a"]), f(P["w_hh_a"]), f(P["w_ih_d"]), f(P["w_hh_d"])
+    wpg = torch.cat((f(P["w_proj"]), f(P["w_gate"])), 0)
+    nu = (max(Ha, Hd) + ncta - 1) // ncta
+    dev = wa.device
+    # gate rows of CTA c in tensor-memory order: rho = gate * nu + local unit (32 lanes, unused ones point at a zero row)
+    def row_index(H):
+        idx = torch.full((ncta, 32), 4 * H, dtype=torch.long, device=dev)
+        c = torch.arange(ncta, device=dev)[:, None, None]
+        g = torch.arange(4, device=dev)[None, :, None]
+        u = torch.arange(nu, device=dev)[None, None, :]
+        unit = c * nu + u
+        rows = torch.where(unit < H, g * H + unit, torch.full_like(unit + g, 4 * H))
+        idx[:, :4 * nu] = rows.reshape(ncta, 4 * nu)
+        return idx.reshape(-1)
+    nm1 = pad_to(d.n_mel, 8)
+    w1 = torch.zeros(Pn, nm1, device=dev)
+    w1[:, :d.n_mel] = f(P["w_pre1"])
+    U = torch.zeros(128, 64, device=dev)
+    U[:d.att_dim, :2 * d.loc_kernel] = pk.wdense @ pk.wconv.reshape(d.loc_filters, 2 * d.loc_kernel)
+    cache = dict(key=key, nu=nu, idx_a=row_index(Ha), idx_d=row_index(Hd),
+                 wa_pre=wa[:, :Pn].to(BF16), wa_ctx=wa[:, Pn:Pn + E].contiguous(), wha=wha.to(BF16),
+                 wd_h=wd[:, :Ha].to(BF16), wd_ctx=wd[:, Ha:Ha + E].contiguous(), whd=whd.to(BF16),
+                 wp_h=wpg[:, :Hd].to(BF16).float().contiguous(), wp_ctx=wpg[:, Hd:Hd + E].contiguous(),
+                 w1=w1.to(BF16).contiguous(), w2=f(P["w_pre2"]).to(BF16).contiguous(), U=U.contiguous(), nm1=nm1)
+    pk._i1 = cache
+    return cache
+
+
+def infer1_supported(d: "DecoderDims", B: int, Tin: int, prec: int) -> bool:
+    """Whether the batch-1 on-chip-weights kernel covers this call (else the clustered kernel runs it)."""
+    if B != 1 or prec != 1 or os.environ.get("GANTRON_B200_INFER1", "1") == "0":
+        return False
+    ncta = _lib.load().gtn_decoder_infer1_ctas()
+    if ncta <= 0:
+        return False
+    Tp = pad_to(Tin, 64)
+    cols_a = pad_to(d.prenet + Tp + d.att_rnn, 256) // 8
+    cols_d = pad_to(d.att_rnn + Tp + d.dec_rnn, 256) // 8
+    nu = (max(d.att_rnn, d.dec_rnn) + ncta - 1) // ncta
+    smem = d.prenet * d.prenet * 2 + 4 * (128 * 64 + 8 * (cols_a + cols_d) + 4 * Tp + 4096)
+    return (nu <= 8 and cols_a + cols_d <= 512 and Tin <= min(2 * ncta, 512) and d.prenet % 64 == 0 and 2 * d.prenet <= 512
+            and d.n_mel + 1 <= min(96, ncta) and d.att_dim <= 128 and d.loc_kernel % 2 == 1 and 2 * d.loc_kernel <= 64
+            and d.att_rnn % 64 == 0 and d.dec_rnn % 64 == 0 and smem <= 226 * 1024)
+
+
+def _decoder_inference_b1(dec, pk, memory, E, max_steps, gate_threshold, seed, ignore_stop):
+    """Batch 1: every LSTM weight on chip (tensor memory) for the whole utterance; see gtn_decoder_infer1.cu."""
+    d = pk.dims
+    lib = _lib.load()
+    ncta = lib.gtn_decoder_infer1_ctas()
+    _, Tin, D = memory.shape
+    dev = memory.device
+    w = _infer1_packs(dec, pk, E, ncta)
+    v2 = pack_v2(dec, pk, E)
+    Pn, Ha, Hd, A, n_out = d.prenet, d.att_rnn, d.dec_rnn, d.att_dim, d.n_mel + 1
+    Tp = pad_to(Tin, 64)
+    Ka, Kd = pad_to(Pn + Tp + Ha, 256), pad_to(Ha + Tp + Hd, 256)
+    mem = memory[0].float()
+    mem_enc = mem[:, :E].contiguous()
+    mem_const = mem[0:1, E:].contiguous() if E < D else torch.zeros(1, 1, device=dev)
+    ga, gd, pb = v2.seq_biases(mem_const[:, :D - E], 1, 1, True)
+    # everything linear in the attention context, pre-multiplied with the encoder memory (bf16 operands, fp32 accumulate)
+    m_a = linear_nt(w["wa_ctx"], mem_enc, 1)                     # [4Ha][Tin]
+    m_d = linear_nt(w["wd_ctx"], mem_enc, 1)                     # [4Hd][Tin]
+    pc = linear_nt(w["wp_ctx"], mem_enc, 1).contiguous()         # [n_mel + 1][Tin]
+    pm = linear_nt(mem, pk.wmem, 1).contiguous()                 # processed_memory [Tin][A] (model.py:326)
+    z = lambda *s, dt=torch.float32: torch.zeros(*s, device=dev, dtype=dt)
+
+    def image(pre, m, hh, K, idx):
+        full = z(pre.shape[0] + 1, K, dt=BF16)                   # (+ one zero row for unused lanes)
+        n0, n1 = pre.shape[1], pre.shape[1] + Tp
+        full[:-1, :n0] = pre
+        full[:-1, n0:n0 + Tin] = m.to(BF16)
+        full[:-1, n1:n1 + hh.shape[1]] = hh
+        return full[idx].view(ncta, 32, 4, K // 4).permute(0, 2, 1, 3)
+    wimg = torch.cat((image(w["wa_pre"], m_a, w["wha"], Ka, w["idx_a"]), image(w["wd_h"], m_d, w["whd"], Kd, w["idx_d"])),
+                     3).contiguous()
+    q = _lib.DecoderInfer1Params()
+    q.Tin, q.Tp, q.n_steps, q.Ha, q.Hd, q.P, q.A, q.KS, q.NM, q.NMp = Tin, Tp, max_steps, Ha, Hd, Pn, A, d.loc_kernel, d.n_mel, w["nm1"]
+    q.nu, q.ncta, q.cols_a, q.cols_d = w["nu"], ncta, Ka // 8, Kd // 8
+    q.ignore_stop, q.gate_threshold, q.seed = int(ignore_stop), gate_threshold, seed
+    ws = dict(h_att_g=z(2, Ha), h_dec_g=z(2, Hd), e_g=z(2, Tp), qacc=z(2, 128, dt=torch.int64), macc=z(2, 96, dt=torch.int64),
+              barrier=z(4, dt=torch.int32), mel_out=z(d.n_mel, max_steps), gate_out=z(max_steps), align_out=z(max_steps, Tin),
+              steps_done=z(4, dt=torch.int32), done=z(4, dt=torch.int32), lengths_out=z(4, dt=torch.int32))
+    for k, t in ws.items():
+        setattr(q, k, t.data_ptr())
+    keep = dict(wimg=wimg, w1=w["w1"], w2=w["w2"], u=w["U"], wq=pk.wq, v=pk.v, wp_h=w["wp_h"], pc=pc, pbias=pb.contiguous(),
+                b_att=pk.b_att, gbias_a=ga.contiguous(), gbias_d=gd.contiguous(), pm=pm)
+    for k, t in keep.items():
+        setattr(q, k, t.data_ptr())
+    _lib.check(lib.gtn_decoder_infer1(C.byref(q), _lib.stream()), "gtn_decoder_infer1")
+    steps = int(ws["steps_done"][0].item())          # the single host sync of the whole decode
+    lengths = torch.full((1,), steps, device=dev, dtype=torch.int32)
+    return (ws["mel_out"][None, :, :steps], ws["gate_out"][None, :steps, None], ws["align_out"][None, :steps], lengths, steps)
+
+
 @torch.no_grad()
 def decoder_inference(dec, memory: torch.Tensor, *, max_steps: int, gate_threshold: float,
                       seed: int, prec: int, const_tail: Optional[bool] = None, ignore_stop: bool = False,
@@ -274,6 +380,8 @@ def decoder_inference(dec, memory: torch.Tensor, *, max_steps: int, gate_thresho
     mult = packing.mult_of(prec)
     E = split_memory(memory, d.enc_dim, const_tail)
     mdt = mem_dtype or (torch.float32 if prec == 3 else BF16)
+    if mdt == BF16 and infer1_supported(d, B, Tin, prec):
+        return _decoder_inference_b1(dec, pk, memory, E, max_steps, gate_threshold, seed, ignore_stop)
     p = _lib.DecoderFwdParams()
     _fill_common(p, d, pk, B, Tin, max_steps, E, prec)
     p.train, p.use_dropout, p.mem_bf16, p.ignore_stop = 0, 0, int(mdt == BF16), int(ignore_stop)

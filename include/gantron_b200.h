@@ -213,6 +213,40 @@ typedef struct gtn_decoder_fwd_params {
  * gtn_decoder_backward, was removed in round 2; the entry points keep their "2" suffix.) */
 int gtn_decoder_forward2(const gtn_decoder_fwd_params* params, void* stream);
 
+/* ---- batch-1 autoregressive decode with every weight on chip (gtn_decoder_infer1.cu) ---------------
+ * Decoder.inference (model.py:456-497) for ONE sequence, bf16 weights / fp32 activations.  All CTAs of the device take
+ * part (gtn_decoder_infer1_ctas() = SM count); CTA c owns hidden units [c nu, (c + 1) nu) of both LSTM cells.  The caller
+ * pre-multiplies everything linear in the attention context with the encoder memory once per utterance:
+ *   wimg   bf16 image of the gate rows for tensor memory, [ncta][4 K-quarters][32 rows][cols_a + cols_d] 32-bit words
+ *          (row rho = gate * nu + local unit; K layout of the attention LSTM [prenet P | M_a Tp | W_hh Ha | 0],
+ *          M_a = W_ih[:, ctx_enc] . memory_enc^T; decoder LSTM [W_ih[:, :Ha] | M_d Tp | W_hh Hd | 0]; quarter q holds
+ *          K in [q K/4, (q + 1) K/4))
+ *   pc     fp32 [NM + 1][Tin] = W_proj|gate[:, ctx_enc] . memory_enc^T;  wp_h fp32 [NM + 1][Hd] = W_proj|gate[:, :Hd]
+ *   gbias_a / gbias_d [H][4], pbias [NM + 1]: biases + time-constant memory columns (as gtn_decoder_fwd_params)
+ * Workspace (zero-initialised): h_att_g / h_dec_g [2][H], e_g [2][Tp], qacc [2][128] / macc [2][96] (64-bit fixed-point
+ * cross-CTA sums), barrier. */
+typedef struct gtn_decoder_infer1_params {
+  int Tin, Tp, n_steps, Ha, Hd, P, A, KS, NM, NMp;
+  int nu, ncta, cols_a, cols_d;
+  int ignore_stop, reserved0;
+  float gate_threshold, reserved1;
+  unsigned long long seed;
+  const void *wimg, *w1, *w2;            /* w1 bf16 [P][NMp], w2 bf16 [P][P] (prenet.layers.0 / .1) */
+  const float *u;                        /* [128][64] location filter U[a][ch * KS + k] */
+  const float *wq, *v;                   /* query_layer [A][Ha], v [A] */
+  const float *wp_h, *pc, *pbias;
+  const float *b_att, *gbias_a, *gbias_d;
+  const float *pm;                       /* processed_memory [Tin][A] */
+  float *h_att_g, *h_dec_g, *e_g;
+  long long *qacc, *macc;
+  unsigned int *barrier;
+  float *mel_out, *gate_out, *align_out; /* [NM][n_steps], [n_steps], [n_steps][Tin] */
+  int *steps_done, *done, *lengths_out;
+} gtn_decoder_infer1_params;
+
+int gtn_decoder_infer1_ctas(void);        /* CTAs (= SMs) gtn_decoder_infer1 launches, or -1 */
+int gtn_decoder_infer1(const gtn_decoder_infer1_params* params, void* stream);
+
 /* ---- persistent clustered decoder, backward through time (gtn_decoder_bwd2.cu) --------------------
  * Counterpart of gtn_decoder_forward2 (same cluster-split tcgen05 GEMM engine).  Per frame t = T-1 .. 0:
  *   P1  dX_dec = W_dec^T dGates_dec(t) (rows [h_att | ctx_enc | h_dec]) and dX_att = W_att^T dGates_att(t+1)

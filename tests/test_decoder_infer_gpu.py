@@ -92,3 +92,49 @@ def test_infer_stops_on_gate_like_reference():
     assert n == om.shape[-1] == 1 and tuple(mel.shape) == tuple(om.shape)
     assert int(lengths[0]) == int(ol[0]) == 1
     assert_close(mel, om, "mel", atol=2e-4, rtol=1e-3)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# batch 1: the on-chip-weights kernel (gtn_decoder_infer1.cu)
+# ---------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("T_in,steps", [(17, 8), (150, 12), (211, 6)])
+def test_infer1_batch1_kernel_matches_oracle(T_in, steps):
+    """bf16 weights / fp32 activations; stated tolerance as the other bf16 inference tests (mel 1e-2 abs on |mel| ~ 1)."""
+    from gantron_b200 import decoder_ops
+    hp, dec, memory = _setup(1, T_in, steps, "bf16", seed=T_in)
+    assert decoder_ops.infer1_supported(dec.packed().dims, 1, T_in, 1), "the batch-1 kernel should cover this shape"
+    seed = 0x1B1
+    mel, gate, align, lengths, n = decoder_ops.decoder_inference(
+        dec, memory.cuda(), max_steps=steps, gate_threshold=0.5, seed=seed, prec=1, ignore_stop=True)
+    om, og, oa, ol, _ = _oracle(hp, dec, memory, steps, seed)
+    assert n == steps and mel.shape == (1, 80, steps) and gate.shape == (1, steps, 1) and align.shape == (1, steps, T_in)
+    assert_close(align, oa, "alignments", atol=1e-3, rtol=0)
+    assert_close(mel, om, "mel", atol=1e-2, rtol=1e-2)
+    assert_close(gate, og, "gate", atol=1e-2, rtol=1e-2)
+
+
+def test_infer1_batch1_kernel_vs_clustered_kernel_and_reproducible(monkeypatch):
+    """Same call through both decode kernels (bf16): they agree to bf16 accuracy, and the batch-1 kernel is bit-reproducible
+    (its cross-CTA sums are fixed-point)."""
+    from gantron_b200 import decoder_ops
+    hp, dec, memory = _setup(1, 150, 20, "bf16", seed=3)
+    kw = dict(max_steps=20, gate_threshold=0.5, seed=99, prec=1, ignore_stop=True)
+    a = decoder_ops.decoder_inference(dec, memory.cuda(), **kw)
+    b = decoder_ops.decoder_inference(dec, memory.cuda(), **kw)
+    assert torch.equal(a[0], b[0]) and torch.equal(a[2], b[2]), "batch-1 kernel is not bit-reproducible"
+    monkeypatch.setenv("GANTRON_B200_INFER1", "0")
+    c = decoder_ops.decoder_inference(dec, memory.cuda(), **kw)
+    assert_close(a[0], c[0], "mel infer1 vs clustered", atol=1e-2, rtol=1e-2)
+    assert_close(a[2], c[2], "alignments infer1 vs clustered", atol=1e-3, rtol=0)
+
+
+def test_infer1_batch1_stops_on_gate():
+    from gantron_b200 import decoder_ops
+    hp, dec, memory = _setup(1, 33, 9, "bf16", seed=4)
+    dec.gate_layer.linear_layer.bias.data.fill_(30.0)
+    mel, gate, align, lengths, n = decoder_ops.decoder_inference(
+        dec, memory.cuda(), max_steps=9, gate_threshold=0.5, seed=5, prec=1)
+    assert n == 1 and tuple(mel.shape) == (1, 80, 1) and int(lengths[0]) == 1
+    om, og, oa, ol, _ = _oracle(hp, dec, memory, 9, 5, force=False)
+    assert om.shape[-1] == 1
+    assert_close(mel, om, "mel", atol=1e-2, rtol=1e-2)
