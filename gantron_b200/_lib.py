@@ -100,7 +100,7 @@ class DecoderInfer1Params(C.Structure):
         + [("gate_threshold", c_f), ("reserved1", c_f), ("seed", c_ull)]
         + [(n, c_p) for n in ("wimg", "w1", "w2", "u", "wq", "v", "wp_h", "pc", "pbias", "b_att", "gbias_a", "gbias_d", "pm",
                               "h_att_g", "h_dec_g", "e_g", "qacc", "macc", "barrier", "mel_out", "gate_out", "align_out",
-                              "steps_done", "done", "lengths_out")]
+                              "steps_done", "done", "lengths_out", "prof")]
     )
 
 

@@ -27,13 +27,17 @@ namespace gtn {
 
 typedef gtn_decoder_infer1_params Inf1;
 
+#define PROFI(slot)                                                                         \
+  do {                                                                                      \
+    if (p.prof != nullptr && blockIdx.x == 0 && threadIdx.x == 0 && t < 16) p.prof[t * 16 + (slot)] = clock64(); \
+  } while (0)
 static constexpr int I1_THREADS = 512;
 static constexpr int I1_WARPS = I1_THREADS / 32;
 static constexpr double I1_FIX = 4294967296.0;          // 2^32: fixed-point scale of the cross-CTA sums
 
 struct SmemI1 {
   uint8_t* w2;        // bf16, chunked [P/8][P][8]: row-contiguous 16-byte chunks (conflict-free with lanes over rows)
-  float* u;           // [128][64] location filter U[a][ch * KS + k] (conv x dense pre-multiplied), fp32
+  float* u;           // [64][128] location filter, transposed: u[ch * KS + k][a] (lanes over a: conflict-free), fp32
   float* xa;          // [Ka] = [prenet P | w(t-1) Tp64 | h_att(t-1) Ha | 0]
   float* xd;          // [Kd] = [h_att(t) Ha | w(t) Tp64 | h_dec(t-1) Hd | 0]
   float* part;        // [16][32] per-warp partial gate sums
@@ -165,7 +169,7 @@ __global__ void __launch_bounds__(I1_THREADS, 1) decoder_infer1_kernel(const Inf
       const int r = i / nck, kc = i - r * nck;
       dst[(size_t)kc * P + r] = __ldg(src + i);
     }
-    for (int i = tid; i < 128 * 64; i += I1_THREADS) sm.u[i] = p.u[i];
+    for (int i = tid; i < 128 * 64; i += I1_THREADS) sm.u[(i & 63) * 128 + (i >> 6)] = p.u[i];      // [a][kk] -> [kk][a]
     for (int i = tid; i < Ka; i += I1_THREADS) sm.xa[i] = 0.f;
     for (int i = tid; i < Kd; i += I1_THREADS) sm.xd[i] = 0.f;
     for (int i = tid; i < Tp + 64; i += I1_THREADS) { sm.wprev[i] = 0.f; sm.wcum[i] = 0.f; }
@@ -229,6 +233,7 @@ __global__ void __launch_bounds__(I1_THREADS, 1) decoder_infer1_kernel(const Inf
   bool stopped = false;
   for (; t < p.n_steps && !stopped; ++t) {
     const int cur = t & 1;
+    PROFI(0);
     // ---- (1) prenet of the previous mel frame (model.py:102-105): both layers in every CTA --------------------------------
     {
       const int r = tid % P, half = tid / P;
@@ -270,9 +275,11 @@ __global__ void __launch_bounds__(I1_THREADS, 1) decoder_infer1_kernel(const Inf
       }
       __syncthreads();
     }
+    PROFI(1);
     // ---- (2) attention LSTM (model.py:391-394) ---------------------------------------------------------------------------
     matvec_tmem(tmem, 0, nch_a, sm.xa, sm.part);
     __syncthreads();
+    PROFI(2);
     if (tid < 32) {
       float s = 0.f;
 #pragma unroll
@@ -299,7 +306,9 @@ __global__ void __launch_bounds__(I1_THREADS, 1) decoder_infer1_kernel(const Inf
       for (int u = 0; u < nua; ++u) s += sm.wq[tid * 8 + u] * sm.red[u];
       red_add_s64(p.qacc + (size_t)cur * 128 + tid, (long long)llrint((double)s * I1_FIX));
     }
+    PROFI(3);
     grid_sync_i1(p.barrier, epoch, nblocks);
+    PROFI(4);
     if (cta == 0 && tid < 128 + 96) {
       // zero the accumulators of the NEXT frame: every CTA is past this frame's barrier 1, hence done reading the previous
       // frame's sums; the next adds come after two more barriers
@@ -314,6 +323,7 @@ __global__ void __launch_bounds__(I1_THREADS, 1) decoder_infer1_kernel(const Inf
     }
     if (tid < 128) sm.q[tid] = (float)((double)__ldcg(&p.qacc[(size_t)cur * 128 + tid]) * (1.0 / I1_FIX));
     __syncthreads();
+    PROFI(5);
     // ---- (5) energies of this CTA's encoder positions (model.py:62-68): e_j = v . tanh(q + loc_j + pm_j) ---------------------
     for (int s = 0; s < 2; ++s) {
       const int j = cta + s * ncta;
@@ -321,12 +331,12 @@ __global__ void __launch_bounds__(I1_THREADS, 1) decoder_infer1_kernel(const Inf
       float val = 0.f;
       if (tid < 2 * 128) {
         const int a = tid & 127, ch = tid >> 7;
-        const float* urow = sm.u + a * 64 + ch * KS;
+        const float* ucol = sm.u + (size_t)ch * KS * 128 + a;
         const float* win = (ch == 0 ? sm.wprev : sm.wcum) + 32 + j - hk;       // zero halo of 32 on both sides
         float l0 = 0.f, l1 = 0.f;
         int k = 0;
-        for (; k + 1 < KS; k += 2) { l0 += urow[k] * win[k]; l1 += urow[k + 1] * win[k + 1]; }
-        if (k < KS) l0 += urow[k] * win[k];
+        for (; k + 1 < KS; k += 2) { l0 += ucol[k * 128] * win[k]; l1 += ucol[(k + 1) * 128] * win[k + 1]; }
+        if (k < KS) l0 += ucol[k * 128] * win[k];
         val = l0 + l1;
       }
       sm.part[tid] = val;
@@ -337,7 +347,9 @@ __global__ void __launch_bounds__(I1_THREADS, 1) decoder_infer1_kernel(const Inf
       if (tid == 0) p.e_g[(size_t)cur * Tp + j] = ej;
       __syncthreads();
     }
+    PROFI(6);
     grid_sync_i1(p.barrier, epoch, nblocks);
+    PROFI(7);
     // ---- (7) softmax over the encoder positions (model.py:84-89), redundantly in every CTA ------------------------------------
     {
       float ev = -INFINITY;
@@ -357,9 +369,11 @@ __global__ void __launch_bounds__(I1_THREADS, 1) decoder_infer1_kernel(const Inf
       }
       __syncthreads();
     }
+    PROFI(8);
     // ---- (8) decoder LSTM (model.py:404-409) and the mel / gate projection partials (model.py:411-416) -------------------------
     matvec_tmem(tmem, p.cols_a, nch_d, sm.xd, sm.part);
     __syncthreads();
+    PROFI(9);
     if (tid < 32) {
       float s = 0.f;
 #pragma unroll
@@ -390,7 +404,9 @@ __global__ void __launch_bounds__(I1_THREADS, 1) decoder_infer1_kernel(const Inf
       const float cs = block_sum_i1(c, sm.red);
       if (cta <= NM && tid == 0) red_add_s64(p.macc + (size_t)cur * 96 + cta, (long long)llrint((double)cs * I1_FIX));
     }
+    PROFI(10);
     grid_sync_i1(p.barrier, epoch, nblocks);
+    PROFI(11);
     // ---- (0') h_dec(t), mel(t), gate(t), stop test (model.py:486) ---------------------------------------------------------------
     for (int i = tid; i < Hd; i += I1_THREADS) xd_hd[i] = __ldcg(&p.h_dec_g[(size_t)cur * Hd + i]);
     if (tid < 96) {

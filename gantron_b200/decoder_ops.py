@@ -357,6 +357,7 @@ def _decoder_inference_b1(dec, pk, memory, E, max_steps, gate_threshold, seed, i
                 b_att=pk.b_att, gbias_a=ga.contiguous(), gbias_d=gd.contiguous(), pm=pm)
     for k, t in keep.items():
         setattr(q, k, t.data_ptr())
+    q.prof = PROF_BUFFER.data_ptr() if PROF_BUFFER is not None else None
     _lib.check(lib.gtn_decoder_infer1(C.byref(q), _lib.stream()), "gtn_decoder_infer1")
     steps = int(ws["steps_done"][0].item())          # the single host sync of the whole decode
     lengths = torch.full((1,), steps, device=dev, dtype=torch.int32)

@@ -242,6 +242,7 @@ typedef struct gtn_decoder_infer1_params {
   unsigned int *barrier;
   float *mel_out, *gate_out, *align_out; /* [NM][n_steps], [n_steps], [n_steps][Tin] */
   int *steps_done, *done, *lengths_out;
+  long long *prof;                       /* optional [16][16] clock64() stamps of CTA 0 (dev tool), NULL = off */
 } gtn_decoder_infer1_params;
 
 int gtn_decoder_infer1_ctas(void);        /* CTAs (= SMs) gtn_decoder_infer1 launches, or -1 */

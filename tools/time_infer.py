@@ -31,40 +31,21 @@ for ver in ("2",):
         print(f"v{ver} B={B}: {1e3 * best / steps:.1f} us/frame-step  ({B * steps / best * 1e3:.0f} frames/s) "
               f"mel absmax {float(r[0].abs().max()):.3f}", flush=True)
 
-# ---- per-phase clock64() profile of CTA 0 (v2 only) ----
+# ---- per-phase clock64() profile of CTA 0 of the batch-1 kernel ----
 if os.environ.get("GTN_PROF"):
-    os.environ["GANTRON_B200_DECODER"] = "2"
-    names = {0: "step start", 1: "att: TMA issued", 2: "att: acc done", 3: "att: exchange done", 4: "att: epilogue done",
-             5: "gsync1 done", 24: "attn: mma issued", 25: "attn: energies", 26: "attn: cluster sync", 27: "attn: softmax",
-             6: "attn done", 8: "gsync2 done", 9: "dec: TMA issued", 10: "dec: acc done", 11: "dec: exchange done",
-             13: "dec done", 28: "frame start (pre1)", 29: "pre1 done", 30: "gsync done", 31: "pre2 done",
-             18: "gsync3 done", 14: "proj: TMA issued", 15: "proj: acc done", 16: "proj: exchange done", 19: "proj done", 23: "gsync4 done"}
-    order = [28, 29, 30, 31, 0, 1, 2, 3, 4, 5, 24, 25, 26, 27, 6, 8, 9, 10, 11, 13, 18, 14, 15, 16, 19, 23]
-    for B, train in ((1, False), (64, False), (64, True)):
-        prof = torch.zeros(16 * 32, dtype=torch.int64, device="cuda")
-        decoder_ops.PROF_BUFFER = prof
-        if train:
-            dec.train()
-            mem = torch.cat((torch.randn(B, 150, 512).cuda() * 0.5, torch.rand(B, 1, 512).repeat_interleave(150, 1).cuda()), -1)
-            mels = (torch.randn(B, 80, 16) * 2 - 5).clamp(-11.5, 2).cuda()
-            with torch.no_grad():
-                decoder_ops.decoder_train_forward(dec, mem, mels, torch.full((B,), 150).cuda(), 5)
-        else:
-            dec.eval()
-            mem = torch.cat((torch.randn(B, 150, 512).cuda() * 0.5, torch.rand(B, 1, 512).repeat_interleave(150, 1).cuda()), -1)
-            decoder_ops.decoder_inference(dec, mem, max_steps=16, gate_threshold=0.5, seed=7, prec=1, const_tail=True,
-                                          ignore_stop=True)
-        torch.cuda.synchronize()
-        pr = prof.cpu().view(16, 32)
-        print(f"--- B={B} train={train}: cycles since step start, frame 8 (and frame 9 start)")
-        t = 8
-        base = int(pr[t, 28]) if int(pr[t, 28]) else int(pr[t, 0])
-        prev = base
-        for sl in order:
-            if int(pr[t, sl]):
-                v = int(pr[t, sl])
-                print(f"   {names[sl]:22s} {v - base:8d}  (+{v - prev})")
-                prev = v
-        nxt = int(pr[t + 1, 28]) if int(pr[t + 1, 28]) else int(pr[t + 1, 0])
-        print(f"   next frame start       {nxt - base:8d}")
-    decoder_ops.PROF_BUFFER = None
+    names = ["frame start", "prenet done", "att LSTM mat-vec done", "att cells + q partial published", "barrier 1 done",
+             "h_att / q gathered", "energies published", "barrier E done", "softmax done", "dec LSTM mat-vec done",
+             "dec cells + mel partials published", "barrier 2 done"]
+    pf = torch.zeros(16 * 16, dtype=torch.int64, device="cuda")
+    decoder_ops.PROF_BUFFER = pf
+    mem = torch.cat((torch.randn(1, 150, 512).cuda() * 0.5, torch.rand(1, 1, 512).repeat_interleave(150, 1).cuda()), -1)
+    decoder_ops.decoder_inference(dec, mem, max_steps=16, gate_threshold=0.5, seed=7, prec=1, const_tail=True, ignore_stop=True)
+    torch.cuda.synchronize()
+    pr = pf.cpu().view(16, 16)
+    t = 8
+    prev = 0
+    for i, n in enumerate(names):
+        v = int(pr[t, i] - pr[t, 0])
+        print(f"   {n:40s} {v:8d}  (+{v - prev})")
+        prev = v
+    print(f"   next frame start                         {int(pr[t + 1, 0] - pr[t, 0]):8d}")
