@@ -567,7 +567,7 @@ class _DecoderTrainFn(torch.autograd.Function):
         p.q_all, p.th_all, p.f_all, p.cum_all = (sv["q_all"].data_ptr(), sv["th_all"].data_ptr(), sv["f_all"].data_ptr(),
                                                  sv["cum_all"].data_ptr())
         keep = _fill_v2(p, pack_v2(dec, pk, E), mem_const[:, :D - E], prec, B, False)   # noqa: F841 (kept alive)
-        _lib.check(_timed_call("decoder_fwd2_kernel", lambda: _lib.load().gtn_decoder_forward2(C.byref(p), _lib.stream())),
+        _lib.check(_timed_call("decoder_fwd3_kernel", lambda: _lib.load().gtn_decoder_forward2(C.byref(p), _lib.stream())),
                    "gtn_decoder_forward2")
 
         # ---- deferred mel/gate projection over all frames (model.py:411-416): batched over b so the output is
