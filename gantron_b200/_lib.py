@@ -62,6 +62,8 @@ SIGNATURES = {
     "gtn_attn_guide_loss_bwd": (c_i, [c_p, c_i, c_i, c_i, c_p, c_p, c_f, c_p, c_p, c_p]),
     "gtn_decoder_forward2": (c_i, [c_p, c_p]),
     "gtn_sizeof": (c_i, [c_i]),
+    "gtn_bilstm_forward": (c_i, [c_p, c_p]),
+    "gtn_bilstm_backward": (c_i, [c_p, c_p]),
     "gtn_decoder_infer1_ctas": (c_i, []),
     "gtn_decoder_infer1": (c_i, [c_p, c_p]),
     "gtn_decoder_bwd2_grid": (c_i, [c_i, c_i, c_i, c_i]),
@@ -90,6 +92,12 @@ class DecoderFwdParams(C.Structure):
                               "w_att2", "w_dec2", "u_loc", "wq_t", "prof", "gbias_a", "gbias_d", "pbias")]
         + [("Ep", c_i), ("reserved0", c_i)]
     )
+
+
+class BiLstmParams(C.Structure):
+    """Mirror of `gtn_bilstm_params` (include/gantron_b200.h)."""
+    _fields_ = ([(n, c_i) for n in ("B", "T", "H", "reserved0")]
+                + [(n, c_p) for n in ("xproj", "whh", "lengths", "out", "gates", "c_all", "dout", "dgates")])
 
 
 class DecoderInfer1Params(C.Structure):

@@ -47,6 +47,7 @@ int gtn_sizeof(int which) {
   if (which == 0) return (int)sizeof(gtn_decoder_fwd_params);
   if (which == 2) return (int)sizeof(gtn_decoder_bwd2_params);
   if (which == 3) return (int)sizeof(gtn_decoder_infer1_params);
+  if (which == 4) return (int)sizeof(gtn_bilstm_params);
   return -1;
 }
 

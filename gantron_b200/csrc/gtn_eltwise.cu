@@ -118,6 +118,7 @@ bn_act_fwd_kernel(const void* __restrict__ y, int y_bf16, long long ldy, EltGeom
     for (int i = 0; i < 8; ++i) {
       float z = x.v[i] * sc[i] + sh[i];
       if (act == 2) z = tanhf(z);
+      else if (act == 1) z = fmaxf(z, 0.f);
       x.v[i] = (keep >> i) & 1u ? z * dscale : 0.f;
     }
     store8(out, out_bf16, (size_t)row * ldo + c0, x);
@@ -167,6 +168,7 @@ bn_act_bwd_reduce_kernel(const void* __restrict__ dx, int dx_bf16, long long ldd
         const float yh = (yy.v[i] - m[i]) * rs[i];
         float dz = (keep >> i) & 1u ? d.v[i] * dscale : 0.f;
         if (act == 2) { const float a = tanhf(yh * ga[i] + be[i]); dz *= 1.f - a * a; }
+        else if (act == 1) { if (yh * ga[i] + be[i] <= 0.f) dz = 0.f; }
         sg[i] += dz * yh;
         sb[i] += dz;
       }
@@ -202,6 +204,7 @@ bn_act_bwd_apply_kernel(const void* __restrict__ dx, int dx_bf16, long long lddx
         const float yh = (yy.v[i] - m[i]) * rs[i];
         float dz = (keep >> i) & 1u ? d.v[i] * dscale : 0.f;
         if (act == 2) { const float a = tanhf(yh * ga[i] + be[i]); dz *= 1.f - a * a; }
+        else if (act == 1) { if (yh * ga[i] + be[i] <= 0.f) dz = 0.f; }
         o.v[i] = ga[i] * rs[i] * (dz - k1[i] - yh * k2[i]);
         sb[i] += o.v[i];
       }

@@ -132,8 +132,11 @@ class Postnet(nn.Module):
 
 
 class Encoder(nn.Module):
-    """Text encoder: 3 x (conv k5 + BN + relu + dropout) + BiLSTM (model.py:154-224).
-    OUT OF SCOPE for the B200 kernels (north star): stock PyTorch ops, kept for state_dict / API parity."""
+    """Text encoder: 3 x (conv k5 + BN + relu + dropout) + BiLSTM (model.py:154-224), SURVEY 8f1.
+    On CUDA tensors the convolution bank runs on the implicit-GEMM conv + fused BN / ReLU / dropout kernels and (bf16 mode,
+    256 units per direction) the BiLSTM on the persistent kernel of gtn_bilstm.cu (encoder_ops.py); packed-sequence
+    semantics without the reference's `input_lengths.cpu().numpy()` host sync (model.py:202).  CPU tensors, fp32 mode or
+    other LSTM sizes take the stock PyTorch ops of the reference (the encoder is not part of the north star's hot path)."""
 
     def __init__(self, hparams):
         super().__init__()
@@ -150,6 +153,8 @@ class Encoder(nn.Module):
                 nn.BatchNorm1d(dim)))
         self.convolutions = nn.ModuleList(convs)
         self.lstm = nn.LSTM(dim, int(dim / 2), 1, batch_first=True, bidirectional=True)
+        self._prec = _precision_of(hparams)
+        self._gtn_act, self._gtn_site0 = "relu", 60        # conv stack: relu, dropout sites 60.. (postnet_ops._PostnetFn)
 
     def append_noise(self, x, noise=None):
         if self.noise_size > 0:
@@ -158,23 +163,37 @@ class Encoder(nn.Module):
             x = torch.cat([x, noise.to(x.dtype)], dim=1)
         return x
 
+    def _use_kernels(self, x):
+        return x.is_cuda and os.environ.get("GANTRON_B200_ENCODER", "1") != "0"
+
     def _convs(self, x):
+        if self._use_kernels(x):
+            from . import postnet_ops
+            return postnet_ops.postnet_forward(self, x, seed=_new_seed(self), prec=self._prec).transpose(1, 2)
         for conv in self.convolutions:
             x = F.dropout(F.relu(conv(x)), 0.5, self.training)
         return x.transpose(1, 2)
 
-    def forward(self, x, input_lengths):
-        x = self._convs(self.append_noise(x))
-        packed = nn.utils.rnn.pack_padded_sequence(x, input_lengths.cpu().numpy(), batch_first=True)
+    def _lstm(self, x, lengths):
+        """x (B,T,E) -> (B,T,2H), zero beyond `lengths` (None: every position is valid)."""
+        from . import encoder_ops
+        if self._use_kernels(x) and encoder_ops.bilstm_supported(self.lstm, self._prec):
+            if lengths is None:
+                lengths = torch.full((x.size(0),), x.size(1), device=x.device, dtype=torch.int32)
+            return encoder_ops.bilstm_forward(self.lstm, x, lengths)
+        x = x.float()
         self.lstm.flatten_parameters()
+        if lengths is None:
+            return self.lstm(x)[0]
+        packed = nn.utils.rnn.pack_padded_sequence(x, lengths.cpu().numpy(), batch_first=True)
         out, _ = self.lstm(packed)
-        out, _ = nn.utils.rnn.pad_packed_sequence(out, batch_first=True)
-        return out
+        return nn.utils.rnn.pad_packed_sequence(out, batch_first=True)[0]
+
+    def forward(self, x, input_lengths):
+        return self._lstm(self._convs(self.append_noise(x)), input_lengths)
 
     def inference(self, x, style=None):
-        x = self._convs(self.append_noise(x, style))
-        self.lstm.flatten_parameters()
-        return self.lstm(x)[0]
+        return self._lstm(self._convs(self.append_noise(x, style)), None)
 
 
 class Decoder(nn.Module):

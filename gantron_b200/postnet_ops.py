@@ -39,11 +39,25 @@ def _layer_params(postnet):
     return out
 
 
+def _stack_acts(postnet):
+    """Activation per layer.  Postnet (model.py:146-151): tanh on all but the last; text-encoder convolutions
+    (model.py:196-197, 216-217; `_gtn_act = 'relu'` on the owning module): relu on every layer."""
+    n = len(postnet.convolutions)
+    if getattr(postnet, "_gtn_act", "tanh") == "relu":
+        return [ops.ACT_RELU] * n
+    return [ops.ACT_TANH] * (n - 1) + [ops.ACT_NONE]
+
+
 class _PostnetFn(torch.autograd.Function):
+    """[conv1d -> BatchNorm1d -> activation -> dropout(0.5)] x n on the implicit-GEMM conv; shared by the Postnet and the
+    text encoder's convolution bank (dropout sites `_gtn_site0` + layer, default SITE_POSTNET0)."""
+
     @staticmethod
     def forward(ctx, postnet, seed, prec, x, wgrad_input, *params):
         n_layers = len(postnet.convolutions)
         training = postnet.training
+        acts = _stack_acts(postnet)
+        site0 = getattr(postnet, "_gtn_site0", SITE_POSTNET0)
         B, C0, T = x.shape
         dev = x.device
         adt = BF16 if prec == 1 else torch.float32          # storage type of activations between layers
@@ -59,7 +73,7 @@ class _PostnetFn(torch.autograd.Function):
             wp, cin_eff, cin_pad = cache.get(("fwd", i, prec), w, lambda w=w: pack_conv_weight(w, prec))
             xop = act_operand(cur, prec)
             last = i == n_layers - 1
-            act = ops.ACT_NONE if last else ops.ACT_TANH
+            act = acts[i]
             y = torch.empty(B, T, cout, device=dev, dtype=adt)
             if training:
                 stats = torch.zeros(2, cout, device=dev)
@@ -67,12 +81,12 @@ class _PostnetFn(torch.autograd.Function):
                 mean, rstd = ops.bn_finalize(stats, B * T, bn.eps, bn.momentum if bn.momentum is not None else 0.1,
                                              bn.running_mean, bn.running_var)
                 bn.num_batches_tracked += 1
-                drop = (0.5, seed, SITE_POSTNET0 + i)
+                drop = (0.5, seed, site0 + i)
             else:
                 ops.conv1d(wp, cin_eff, cin_pad, k, 1, pad, xop, y, None, bias=b.detach())
                 mean, rstd = bn.running_mean, torch.rsqrt(bn.running_var + bn.eps)
                 drop = (0.0, 0, 0)
-            out = torch.empty(B, T, cout, device=dev, dtype=torch.float32 if last else adt)
+            out = torch.empty(B, T, cout, device=dev, dtype=torch.float32 if (last and site0 == SITE_POSTNET0) else adt)
             ops.bn_act_fwd(y, mean, rstd, gamma.detach(), beta.detach(), act, drop, out)
             saved.append((cur, y, mean, rstd, act, drop))
             cur = out

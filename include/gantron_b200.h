@@ -87,7 +87,7 @@ int gtn_gemm_tn_bf16(const void* A, const void* B, int M, int N, int K, long lon
  * running_mean != NULL also the momentum update of the running statistics (unbiased variance). */
 int gtn_bn_finalize(const float* stats, int C, long long count, float eps, float momentum, float* mean, float* rstd,
                     float* running_mean, float* running_var, void* stream);
-/* out = dropout(act((y - mean) * rstd * gamma + beta)); act 0 none / 2 tanh; mean == NULL skips the affine. */
+/* out = dropout(act((y - mean) * rstd * gamma + beta)); act 0 none / 1 relu / 2 tanh; mean == NULL skips the affine. */
 int gtn_bn_act_fwd(const void* y, int y_dtype, long long ldy, long long rows, int C, const float* mean, const float* rstd,
                    const float* gamma, const float* beta, int act, float drop_p, unsigned long long seed, int site,
                    void* out, int out_dtype, long long ldo, void* stream);
@@ -212,6 +212,27 @@ typedef struct gtn_decoder_fwd_params {
  * saved as [T][B][H][4] (i,f,g,o per unit).  (The mma.sync first generation of these kernels, gtn_decoder_forward /
  * gtn_decoder_backward, was removed in round 2; the entry points keep their "2" suffix.) */
 int gtn_decoder_forward2(const gtn_decoder_fwd_params* params, void* stream);
+
+/* ---- bidirectional LSTM of the text encoder (gtn_bilstm.cu; reference model.py:183-185, 199-213) -------------
+ * nn.LSTM(E, H = 256, bidirectional, batch_first) on packed sequences, one persistent launch per pass.  The caller provides
+ * the input projection xproj = x W_ih^T + b_ih + b_hh of both directions, fp32 [B][T][2][4][H] (columns dir * 4H + gate * H +
+ * unit, gates i, f, g, o as in torch) and whh = bf16 [2][4H][H] (weight_hh_l0, weight_hh_l0_reverse).
+ * forward:  out fp32 [B][T][2H] (zero beyond lengths[b]); training saves gates fp32 [2][T][B][H][4] (post-activation) and
+ *           c_all fp32 [2][T][B][H] (both NULL at inference).
+ * backward: dout fp32 [B][T][2H] -> dgates bf16 [B][T][2][4][H] (pre-activation gate gradients; zero beyond the lengths); the
+ *           caller derives dx, dW_ih, dW_hh and the bias gradients from it with batched GEMMs. */
+typedef struct gtn_bilstm_params {
+  int B, T, H, reserved0;
+  const float *xproj;
+  const void *whh;
+  const int *lengths;
+  float *out, *gates, *c_all;
+  const float *dout;
+  void *dgates;
+} gtn_bilstm_params;
+
+int gtn_bilstm_forward(const gtn_bilstm_params* params, void* stream);
+int gtn_bilstm_backward(const gtn_bilstm_params* params, void* stream);
 
 /* ---- batch-1 autoregressive decode with every weight on chip (gtn_decoder_infer1.cu) ---------------
  * Decoder.inference (model.py:456-497) for ONE sequence, bf16 weights / fp32 activations.  All CTAs of the device take

@@ -345,6 +345,38 @@ def postnet(sd: Dict[str, Tensor], x: Tensor, d: Dims, keeps: Optional[Sequence[
 
 
 # ----------------------------------------------------------------------------------------
+# Text encoder  (model.py:154-224) -- SURVEY 8f1
+# ----------------------------------------------------------------------------------------
+def encoder_forward(sd: Dict[str, Tensor], emb: Tensor, lengths: Optional[Tensor], keeps: Optional[Sequence[Tensor]],
+                    training: bool, prefix: str = "encoder.", n_conv: int = 3) -> Tensor:
+    """emb (B,C,T) embedded text -> (B,T,2H).  Three conv k5 + BatchNorm1d + relu + dropout(0.5) (model.py:196-197), then the
+    bidirectional LSTM on PACKED sequences (model.py:199-213; `lengths` None = Encoder.inference, model.py:216-224).
+    keeps: one (B,C,T) mask per conv layer or None."""
+    x = emb
+    for i in range(n_conv):
+        w, b = sd[f"{prefix}convolutions.{i}.0.conv.weight"], sd[f"{prefix}convolutions.{i}.0.conv.bias"]
+        y = F.conv1d(x, w, b, padding=(w.shape[-1] - 1) // 2)
+        gam, bet = sd[f"{prefix}convolutions.{i}.1.weight"], sd[f"{prefix}convolutions.{i}.1.bias"]
+        if training:
+            y, _, _ = batch_norm_train(y, gam, bet)
+        else:
+            rm, rv = sd[f"{prefix}convolutions.{i}.1.running_mean"], sd[f"{prefix}convolutions.{i}.1.running_var"]
+            y = (y - rm[None, :, None]) * torch.rsqrt(rv[None, :, None] + 1e-5) * gam[None, :, None] + bet[None, :, None]
+        x = _drop(torch.relu(y), keeps[i] if (training and keeps is not None) else None, 0.5)
+    x = x.transpose(1, 2)
+    H = sd[f"{prefix}lstm.weight_hh_l0"].shape[1]
+    lstm = torch.nn.LSTM(x.shape[2], H, 1, batch_first=True, bidirectional=True)
+    params = {k: sd[f"{prefix}lstm.{k}"] for k in ("weight_ih_l0", "weight_hh_l0", "bias_ih_l0", "bias_hh_l0",
+                                                   "weight_ih_l0_reverse", "weight_hh_l0_reverse", "bias_ih_l0_reverse",
+                                                   "bias_hh_l0_reverse")}
+    if lengths is None:
+        return torch.func.functional_call(lstm, params, (x,))[0]
+    packed = torch.nn.utils.rnn.pack_padded_sequence(x, lengths.cpu(), batch_first=True, enforce_sorted=False)
+    out, _ = torch.func.functional_call(lstm, params, (packed,))
+    return torch.nn.utils.rnn.pad_packed_sequence(out, batch_first=True, total_length=x.shape[1])[0]
+
+
+# ----------------------------------------------------------------------------------------
 # Output masking  (model.py:632-642)
 # ----------------------------------------------------------------------------------------
 def parse_output(mel: Tensor, mel_post: Tensor, gate: Tensor, output_lengths: Optional[Tensor]):

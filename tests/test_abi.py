@@ -46,6 +46,7 @@ def test_struct_sizes_match_the_binding(lib):
     assert lib.gtn_sizeof(0) == C.sizeof(_lib.DecoderFwdParams)
     assert lib.gtn_sizeof(2) == C.sizeof(_lib.DecoderBwd2Params)
     assert lib.gtn_sizeof(3) == C.sizeof(_lib.DecoderInfer1Params)
+    assert lib.gtn_sizeof(4) == C.sizeof(_lib.BiLstmParams)
     assert lib.gtn_version() >= 100
 
 

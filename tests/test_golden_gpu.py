@@ -250,3 +250,32 @@ def test_tacotron2_inference_wrapper_str_and_explicit_inputs():
     for n, t in (("mel", mel), ("gate", gate), ("align", align), ("mel_post", mel_post)):
         e = _rel(t, z[f"out/{n}"])
         assert e <= REL, f"{n} rel err {e:.3e}"
+
+
+@pytest.mark.parametrize("name", ["train_vanilla", "train_combined"])
+def test_encoder_matches_reference_golden(name):
+    """the text encoder itself (embedding -> conv bank on the sm_100a kernels -> BiLSTM) on the fixture's text batch
+    against what the unmodified reference's encoder produced.  fp32 mode: conv bank in 3-plane arithmetic, LSTM on the stock
+    op (1e-3); bf16 mode: conv bank + the persistent BiLSTM kernel (stated bf16 tolerance 3e-2 relative Frobenius)."""
+    from oracle import gantron_oracle as O
+    from gantron_b200.hparams import HParams
+    from gantron_b200 import model as M
+    z = _load(name)
+    ref = torch.from_numpy(z["in/memory"])[:, :, :512]
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        for prec, tol, l2 in (("fp32", 1e-3, False), ("bf16", 3e-2, True)):
+            hp = HParams(str(z["hp_string"]) + f",b200_precision={prec}")
+            G = M.Tacotron2(hp)
+            G.load_state_dict(O.seeded_state_dict({k: tuple(v) for k, v in json.loads(str(z["sd/G"])).items()}, seed=int(z["wseed"])))
+            G = G.cuda().train()
+            G.encoder._forced_seed = int(z["mseed"])
+            text, in_len = torch.from_numpy(z["in/text"]).cuda(), torch.from_numpy(z["in/in_len"]).cuda()
+            with torch.no_grad():
+                enc = G.encoder(G.embedding(text).transpose(1, 2), in_len)
+            got = enc.float().cpu()
+            err = float((got - ref).norm() / ref.norm()) if l2 else float((got - ref).abs().max() / ref.abs().max())
+            assert err <= tol, f"{name}: encoder outputs ({prec} mode) err {err:.3e}"
+    finally:
+        torch.backends.cudnn.allow_tf32 = old

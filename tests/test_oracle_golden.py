@@ -241,3 +241,19 @@ def test_oracle_wrapper_inference_matches_reference_golden():
     _close(gate, z["out/gate"], "gate")
     _close(align, z["out/align"], "align")
     _close(mel + O.postnet(sd, mel, d, None, training=False), z["out/mel_post"], "mel_post")
+
+
+@pytest.mark.parametrize("name", ["train_vanilla", "train_combined"])
+def test_oracle_encoder_matches_reference_golden(name):
+    """Text encoder: oracle.encoder_forward on the fixture's text batch reproduces the encoder outputs the
+    unmodified reference fed to its decoder (the first 512 columns of the captured `memory`)."""
+    z = _load(name)
+    hp = HParams(str(z["hp_string"]))
+    shapes_g = {k: tuple(v) for k, v in json.loads(str(z["sd/G"])).items()}
+    sd = O.seeded_state_dict(shapes_g, seed=int(z["wseed"]))
+    masks = unpack_masks(z)[:3]
+    text, in_len = torch.from_numpy(z["in/text"]), torch.from_numpy(z["in/in_len"])
+    emb = torch.nn.functional.embedding(text, sd["embedding.weight"]).transpose(1, 2)
+    with torch.no_grad():
+        enc = O.encoder_forward(sd, emb, in_len, masks, training=True)
+    _close(enc, z["in/memory"][:, :, :hp.encoder_embedding_dim], f"{name}: encoder outputs")
