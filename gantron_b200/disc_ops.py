@@ -76,7 +76,7 @@ class _DiscFn(torch.autograd.Function):
     @staticmethod
     @once_differentiable
     def backward(ctx, g):
-        # NOTE: double backward (train.py:32-69 gradient_penalty, lambda = 0 by default) is not implemented: SURVEY 8 f2
+        # (double backward -- gradient_penalty, train.py:32-69 -- never reaches this node: see discriminator_forward)
         disc, prec, saved = ctx.disc, ctx.prec, ctx.saved
         convs, head = _convs(disc)
         params = _params(disc)
@@ -115,6 +115,31 @@ class _DiscFn(torch.autograd.Function):
         return (None, None, None, gx) + tuple(grads)
 
 
+def _keep_scale_mask(B: int, P: int, C: int, drop, dev) -> torch.Tensor:
+    """(B,P,C) tensor holding keep / (1 - p) of the kernels' Philox stream for `drop` = (p, seed, site)."""
+    ones = torch.ones(B, P, C, device=dev)
+    out = torch.empty_like(ones)
+    ops.bn_act_fwd(ones, None, None, None, None, ops.ACT_NONE, drop, out)
+    return out
+
+
+def _discriminator_composite(disc, x: torch.Tensor, seed: int) -> torch.Tensor:
+    """The same network as ordinary differentiable torch ops (conv1d -> Philox dropout mask -> tanh, layers.py:53-57), for
+    the one caller that differentiates TWICE through the Discriminator: gradient_penalty (train.py:32-69, create_graph=True
+    at :55-57).  Same dropout stream as the kernel path; fp32 arithmetic."""
+    import torch.nn.functional as F
+    convs, head = _convs(disc)
+    B, _, P = x.shape
+    cur = x.float()
+    for i, conv in enumerate(convs):
+        dmod = disc.discriminator[i].module[1]
+        y = F.conv1d(cur, conv.weight, conv.bias, padding=conv.padding[0], dilation=conv.dilation[0])
+        if dmod.training and dmod.p > 0:
+            y = y * _keep_scale_mask(B, P, conv.weight.shape[0], (dmod.p, seed, SITE_DISC0 + i), x.device).transpose(1, 2)
+        cur = torch.tanh(y)
+    return F.conv1d(cur, head.weight, head.bias).squeeze(1)
+
+
 def discriminator_forward(disc, inputs: torch.Tensor, seed: int, prec: int) -> torch.Tensor:
     """inputs (B, frames, n_mel) -> (B, positions); tail handling and raw reshape as model.py:521-526."""
     win = disc.window
@@ -122,7 +147,16 @@ def discriminator_forward(disc, inputs: torch.Tensor, seed: int, prec: int) -> t
     if r != 0:
         inputs = torch.cat((inputs[:, :-r], inputs[:, -win:]), dim=1)
     x = inputs.reshape(inputs.shape[0], disc.in_dim, -1)          # raw memory reinterpretation (copy if strided)
-    return _DiscFn.apply(disc, seed, prec, x, *_params(disc))
+    params = _params(disc)
+    if (getattr(disc, "_gp_lambda", 0) > 0 and torch.is_grad_enabled() and x.requires_grad
+            and any(p.requires_grad for p in params)):
+        # hparams.gradient_penalty_lambda > 0 and input AND parameters want gradients: in the reference's schedule that is
+        # gradient_penalty only (the generator step freezes D, train.py:366-367; the discriminator step feeds detached mels,
+        # train.py:313-321), and it goes on to differentiate the input gradient again.  The fused kernels are
+        # once-differentiable, so this call takes the composite (fp32, TF32 off).
+        with torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+            return _discriminator_composite(disc, x, seed)
+    return _DiscFn.apply(disc, seed, prec, x, *params)
 
 
 class _WindowMean(torch.autograd.Function):

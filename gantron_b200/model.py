@@ -309,6 +309,8 @@ class Discriminator(nn.Module):
             DiscConv1d(dd, hparams.n_mel_channels, 5, dilation=2),
             nn.Conv1d(hparams.n_mel_channels, 1, 1, bias=True))
         self._prec = _precision_of(hparams)
+        self._gp_lambda = getattr(hparams, "gradient_penalty_lambda", 0)     # > 0: gradient_penalty calls get a twice-
+                                                                             # differentiable composite (disc_ops)
 
     def forward(self, inputs):
         """inputs (B, frames, n_mel) -> (B, positions)."""

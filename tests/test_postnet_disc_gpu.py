@@ -253,3 +253,52 @@ def test_tacotron2_loss_and_attention_loss(ragged):
     assert_close(bufc.grad, bo.grad, "d(mel|gate)", atol=1e-7, rtol=1e-4)
     assert_close(postc.grad, po.grad, "d(mel_post)", atol=1e-7, rtol=1e-4)
     assert_close(alignc.grad, ao.grad, "d(align)", atol=1e-7, rtol=1e-4)
+
+
+def test_gradient_penalty_double_backward():
+    """gradient_penalty (train.py:32-69) differentiates twice through the Discriminator (create_graph=True at
+    train.py:55-57).  The drop-in routes that one call through a twice-differentiable composite with the kernels' own Philox
+    dropout stream; value and D-parameter gradients against the CPU oracle."""
+    from gantron_b200.model import Discriminator, get_mask_from_lengths
+    from oracle import gantron_oracle as O, philox as PX
+    from torch.autograd import grad as torch_grad
+    torch.manual_seed(21)
+    hp = _hp("fp32", ",gradient_penalty_lambda=10,clipping_value=0")
+    D = Discriminator(hp).cuda().train()
+    D._forced_seed = 31337
+    B, T = 3, 60
+    g = torch.Generator().manual_seed(2)
+    real = (torch.randn(B, 80, T, generator=g) * 2 - 5).clamp(-11.5, 2)
+    fake = (torch.randn(B, 80, T, generator=g) * 2 - 5).clamp(-11.5, 2)
+    lens = torch.tensor([60, 47, 40])
+    alpha = torch.rand(B, 1, 1, generator=g)
+
+    def penalty(disc_fn, real, fake, lens, alpha, mask_fn):
+        # train.py:32-69, equal widths (generated_data has the width of real_data)
+        a = alpha.expand_as(fake)
+        inter = a * real + (1 - a) * fake
+        mask = mask_fn(lens).unsqueeze(1).expand_as(inter)
+        inter = inter.masked_fill(mask == False, 0).detach().requires_grad_(True)      # noqa: E712 (as the reference)
+        prob = disc_fn(inter.transpose(1, 2))
+        grads = torch_grad(outputs=prob, inputs=inter, grad_outputs=torch.ones_like(prob), create_graph=True, retain_graph=True)[0]
+        grads = grads.masked_fill(mask == False, 0).reshape(B, -1)                     # noqa: E712
+        return ((torch.sqrt(torch.sum(grads ** 2, dim=1) + 1e-12) - 1) ** 2).mean()
+
+    # (the double backward of the convolutions runs outside the forward's no-TF32 scope: switch it off here too)
+    with torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+        gp = penalty(D, real.cuda(), fake.cuda(), lens.cuda(), alpha.cuda(), get_mask_from_lengths)
+        gp.backward()
+    sd = _sd_cpu(D)
+    P = T // 20
+    chans = [c[1] for c in O.disc_layer_dims(O.Dims.from_hparams(hp))[:4]]
+    keeps = _masks_cl(31337, PX.SITE_DISC0, 4, B, P, chans)
+    d = O.Dims.from_hparams(hp)
+    gpo = penalty(lambda x: O.discriminator_forward(sd, x, d, keeps), real, fake, lens, alpha,
+                  lambda L: torch.arange(T)[None, :] < L[:, None])
+    gpo.backward()
+    assert abs(float(gp) - float(gpo)) <= 1e-3 * abs(float(gpo)) + 1e-6, f"gradient penalty {float(gp)} vs {float(gpo)}"
+    # (the head's bias does not reach the input gradient: its gradient is None on both sides)
+    pairs = [(k, p.grad, sd[k].grad) for k, p in D.named_parameters()]
+    assert all((a is None) == (b is None) for _, a, b in pairs), [k for k, a, b in pairs if (a is None) != (b is None)]
+    worst = sorted(((_rel(a, b), k) for k, a, b in pairs if a is not None), reverse=True)
+    assert len(worst) >= 9 and worst[0][0] <= 2e-3, "gradient-penalty grads: " + "; ".join(f"{k} {e:.2e}" for e, k in worst[:5])
