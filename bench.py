@@ -268,8 +268,15 @@ class Trainer:
         self.G.train(); self.D.train()
         self.real, self.fake = 1.0, -1.0
 
-    def step(self, x, y):
+    def step(self, x, y, marks=None):
+        """marks: optional list receiving CUDA events at the segment boundaries of the step (scaling probe)."""
+        def mark():
+            if marks is not None:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record()
+                marks.append(e)
         hp, G, D = self.hp, self.G, self.D
+        mark()
         # ---- generator iteration (train.py:362-406)
         for p in D.parameters():
             p.requires_grad = False
@@ -279,9 +286,12 @@ class Trainer:
         mel_loss, gate_loss, attn_loss = self.criterion(y_pred, y, x[1], x[-1])
         adv = self.real * D.adversarial_loss(generated_mel, lengths)
         total = mel_loss + gate_loss + adv + 10 * attn_loss
+        mark()
         total.backward()
+        mark()
         torch.nn.utils.clip_grad_norm_(G.parameters(), hp.grad_clip_thresh)
         self.g_opt.step()
+        mark()
         # ---- discriminator iteration (train.py:301-345)
         for p in D.parameters():
             p.requires_grad = True
@@ -292,6 +302,7 @@ class Trainer:
         torch.nn.utils.clip_grad_norm_(D.parameters(), hp.clipping_value)     # before backward, as train.py:326-327
         d_loss.backward()
         self.d_opt.step()
+        mark()
         return total.detach()
 
 
@@ -496,6 +507,26 @@ def run_ours(args):
     clocks = sampler.stop() if rank == 0 else None
     ms_e2e, last_loss = timed(args.steps, True)
 
+    probe = None
+    if args.scale_probe:
+        # per-rank segment times of the step (forward+losses | G backward incl. gradient all-reduce | clip + Adam | D step)
+        x, y = tr.G.parse_batch(batch)
+        seg = [[] for _ in range(4)]
+        for _ in range(6):
+            marks = []
+            barrier()
+            tr.step(x, y, marks)
+            torch.cuda.synchronize()
+            for i in range(4):
+                seg[i].append(marks[i].elapsed_time(marks[i + 1]))
+        mine = torch.tensor([sum(s_[1:]) / len(s_[1:]) for s_ in seg], device="cuda")
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        if distributed:
+            dist.all_gather(allr, mine)
+        else:
+            allr = [mine]
+        probe = {"segments": ["G forward + losses", "G backward (+ gradient all-reduce)", "clip + Adam (G)", "D step"],
+                 "ms_per_rank": [[round(float(v), 3) for v in r_] for r_ in allr]}
     value = frames * world * args.steps / (ms_total * 1e-3)
     e2e_val = frames * world * args.steps / (ms_e2e * 1e-3)
     line = None
@@ -518,6 +549,8 @@ def run_ours(args):
                                   "peak": pk["tf_sust"], "unit": "TFLOP/s",
                                   "frac": MFLOP_PER_FRAME_TRAIN * 1e6 * (value / world) / 1e12 / pk["tf_sust"],
                                   "peak_source": pk["src"], "note": "whole G+D step, algorithmic 169.6 MFLOP/frame"}}
+    if rank == 0 and probe is not None:
+        line["scale_probe"] = probe
     if world == 1 and rank == 0:
         del tr
         torch.cuda.empty_cache()
@@ -621,6 +654,7 @@ def main():
     ap.add_argument("--no-infer", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the configs[3] and eager-PyTorch-on-B200 legs")
+    ap.add_argument("--scale-probe", action="store_true", help="add per-rank segment times of the step (profiles/r2_scale_breakdown.md)")
     ap.add_argument("--global-batch", type=int, default=0, help="configs[4] as written: global batch split over the GPUs (strong scaling)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -634,6 +668,10 @@ def main():
                "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup)]
         if args.global_batch:
             cmd += ["--global-batch", str(args.global_batch)]
+        for flag, on in (("--scale-probe", args.scale_probe), ("--no-infer", args.no_infer), ("--no-cpu", args.no_cpu),
+                         ("--no-extra", args.no_extra)):
+            if on:
+                cmd.append(flag)
         sys.exit(subprocess.call(cmd))
     run_ours(args)
 

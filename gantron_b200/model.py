@@ -48,9 +48,12 @@ def _require_cuda(t: torch.Tensor, what: str) -> None:
         raise RuntimeError(f"gantron_b200.{what}: the sm_100a kernels need CUDA tensors; there is no CPU fallback")
 
 
-def get_mask_from_lengths(lengths: torch.Tensor) -> torch.Tensor:
-    """True at valid positions (utils.py:20-24), device-agnostic."""
-    max_len = int(torch.max(lengths).item())
+def get_mask_from_lengths(lengths: torch.Tensor, max_len=None) -> torch.Tensor:
+    """True at valid positions (utils.py:20-24), device-agnostic.  Callers that already know the padded length (the
+    time axis of the tensor they mask) pass it as max_len: the reference's max(lengths).item() is a host<->device
+    synchronisation in the middle of the training step, and the result is the same mask."""
+    if max_len is None:
+        max_len = int(torch.max(lengths).item())
     return torch.arange(max_len, device=lengths.device)[None, :] < lengths[:, None]
 
 
@@ -261,8 +264,10 @@ class Decoder(nn.Module):
         """cat a per-sequence U(0,1) noise vector to every encoder position (model.py:273-279); drawn on the
         CPU generator like the reference so seeds reproduce."""
         if self.noise_size > 0:
-            noise = torch.rand(x.size(0), 1, self.noise_size).repeat_interleave(x.size(1), dim=1).to(x.device)
-            x = torch.cat([x, noise.to(x.dtype)], dim=-1)
+            noise = torch.rand(x.size(0), 1, self.noise_size)
+            if x.is_cuda:
+                noise = noise.pin_memory().to(x.device, non_blocking=True)   # no host stall behind the encoder
+            x = torch.cat([x, noise.to(x.dtype).expand(-1, x.size(1), -1)], dim=-1)
         return x
 
     def forward(self, memory, decoder_inputs, memory_lengths):
@@ -399,9 +404,7 @@ class Tacotron2(nn.Module):
         """Padding frames -> mel 0 / gate 1e3, written through .data like the reference (model.py:632-642):
         values change, the autograd graph does not see it."""
         if self.mask_padding and output_lengths is not None:
-            pad = ~get_mask_from_lengths(output_lengths)
-            if pad.shape[1] < outputs[0].shape[-1]:
-                pad = F.pad(pad, (0, outputs[0].shape[-1] - pad.shape[1]), value=True)
+            pad = ~get_mask_from_lengths(output_lengths, outputs[0].shape[-1])
             outputs[0].data.masked_fill_(pad[:, None, :], 0.0)
             outputs[1].data.masked_fill_(pad[:, None, :], 0.0)
             outputs[2].data.masked_fill_(pad, 1e3)
@@ -427,9 +430,7 @@ class Tacotron2(nn.Module):
         # the reference's conv0 weight gradient sees the MASKED mel
         wgrad_in = None
         if self.mask_padding:
-            pad = ~get_mask_from_lengths(output_lengths)
-            if pad.shape[1] < mel.shape[-1]:
-                pad = F.pad(pad, (0, mel.shape[-1] - pad.shape[1]), value=True)
+            pad = ~get_mask_from_lengths(output_lengths, mel.shape[-1])
             wgrad_in = mel.detach().masked_fill(pad[:, None, :], 0.0)
         mel_post = mel + self.postnet(mel, wgrad_input=wgrad_in)
         return self.parse_output([mel, mel_post, gate, align], output_lengths)
