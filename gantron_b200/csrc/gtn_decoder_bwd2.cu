@@ -18,6 +18,7 @@
 // All WEIGHT gradients are deferred: the kernel stores per-frame gate / query gradients and the host issues a
 // handful of K = T*B tcgen05 GEMMs afterwards (gtn_gemm_tn_bf16).
 #include <cstdlib>
+#include <cstring>
 #include <type_traits>
 #include "gtn_decoder2.cuh"
 #include "gtn_internal.h"
@@ -42,6 +43,7 @@ typedef gtn_decoder_bwd2_params DecBwd2;
 struct Bwd2Maps {
   CUtensorMap wT_att, wT_dec, ut;      // weights (A operands) and U^T (B operand of d[prev|cum] = dth . U)
   CUtensorMap xdg_a, xdg_d;            // gate gradients as X operands
+  CUtensorMap wq;                      // bf16 Wq [A][Ha] seen as fp32 pairs: box = one rank's quarter of the units x all A rows
 };
 
 static constexpr int B2_TIN_MAX = 256;
@@ -71,6 +73,9 @@ struct SmemB {
   uint64_t* ut_full;
   uint64_t* recv_full;  // [2] bulk-copy exchange: one per receive buffer
   uint64_t* mem_full;   // the encoder-memory tile of this CTA's positions has landed in the ring (bulk copy)
+  uint64_t* th_full;    // the frame's tanh tile (th_all rows of this CTA's positions) has landed in the ring
+  uint64_t* wq_full;    // this rank's quarter of Wq has landed in the ring
+  uint64_t* du_done;    // the dU MMAs of the frame have retired (their operand tiles in the ring may be overwritten)
   uint32_t* tmem_slot;
   uint32_t ring_bytes;
 };
@@ -122,6 +127,9 @@ GTN_DEVICE SmemB carveB(uint8_t* base, int S) {
   m.ut_full = b++;
   m.recv_full = b; b += 2;
   m.mem_full = b++;
+  m.th_full = b++;
+  m.wq_full = b++;
+  m.du_done = b++;
   m.tmem_slot = reinterpret_cast<uint32_t*>(b + 1);
   return m;
 }
@@ -150,6 +158,13 @@ GTN_DEVICE void grid_wait2(unsigned int* counter, unsigned int target) {
 // while P1's epilogue and barrier 1 are in flight) from byte 32 K on -- behind the staging area of P1's split-K exchange;
 // the dth tiles overwrite it after the d(weights) reduction has consumed it.
 static constexpr uint32_t MEM_TILE_OFF = 2 * W_TILE_BYTES;
+// The frame's tanh tile (fp32 [positions][A], one contiguous run of th_all) is bulk-copied behind the dth tiles once the
+// d(weights) reduction has consumed the memory tile: the dth stage then reads shared memory instead of waiting three
+// dependent L2 round trips (7.5k -> ~3k cycles).  This rank's quarter of Wq (bf16, A rows x units/4) lands at the start of
+// the ring by ONE TMA box once the attention MMAs have retired: the cells' Wq^T dq product reads it from shared memory
+// instead of streaming 64 KB per frame through the LSU (6k -> ~1.5k cycles).
+static constexpr uint32_t TH_TILE_OFF = 4 * W_TILE_BYTES;
+struct P2Tiles { bool th; bool wq; };
 
 GTN_DEVICE void red_add_f2(float* addr, float a, float b) {
   asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(a), "f"(b) : "memory");
@@ -353,7 +368,8 @@ GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, 
 // product h selects the half of the attention dimension (both sequences), partial sums meet in shared memory, and for the
 // cell arithmetic h selects the sequence.  dq2 = [2][128] full d query of the two sequences, part = [2][2][128][2] scratch.
 template <bool F32>
-GTN_DEVICE void quad_cells(const DecBwd2& p, const float* dq2, float* part, int t, int it, int b0, int b1, int rank) {
+GTN_DEVICE void quad_cells(const DecBwd2& p, const float* dq2, float* part, int t, int it, int b0, int b1, int rank,
+                           const uint32_t* wq_s, uint64_t* wq_full, uint32_t wq_par) {
   const int nxt = (it & 1) ^ 1;
   bf16* xnext_d = BFP(p.xdg_d) + (size_t)nxt * p.B * (F32 ? 6 : 1) * 4 * p.Hd;
   const int Hq_a = ((p.Ha / CL + 1) / 2) * 2, ua_beg = rank * Hq_a, ua_end = min(p.Ha, (rank + 1) * Hq_a);
@@ -386,7 +402,24 @@ GTN_DEVICE void quad_cells(const DecBwd2& p, const float* dq2, float* part, int 
     }
     // Wq^T dq over this thread's half of the attention dimension, for both sequences
     float s00 = 0.f, s01 = 0.f, s10 = 0.f, s11 = 0.f;                // [sequence][unit of the pair]
-    if (oka_u) {
+    if (!F32 && wq_s != nullptr) {
+      // Wq quarter in shared memory: [A][Hq / 2] words, word pr = this thread's unit pair (a warp reads 128 contiguous bytes)
+      wait_bar(wq_full, wq_par);
+      PROFB(27);
+      if (oka_u) {
+        const int ldw = (((p.Ha / CL + 1) / 2) * 2) >> 1;
+        const uint32_t* w = wq_s + (size_t)a_lo * ldw + pr;
+        const float* d0 = dq2 + a_lo;
+        const float* d1 = dq2 + 128 + a_lo;
+#pragma unroll 16
+        for (int a = 0; a < A2; ++a) {
+          const uint32_t wv = w[a * ldw];
+          const float w0 = __uint_as_float(wv << 16), w1 = __uint_as_float(wv & 0xFFFF0000u);
+          s00 += w0 * d0[a]; s01 += w1 * d0[a];
+          s10 += w0 * d1[a]; s11 += w1 * d1[a];
+        }
+      }
+    } else if (oka_u) {
       const float* d0 = dq2 + a_lo;
       const float* d1 = dq2 + 128 + a_lo;
       const int ld = p.Ha >> 1;
@@ -482,8 +515,9 @@ GTN_DEVICE void attn_bwd_prepare(const DecBwd2& p, SmemB& sm, int t, int b, bool
 
 // prepared: attn_bwd_prepare already ran for this frame (fast layout); mem_tile: the encoder-memory tile is in the ring
 template <bool F32>
-GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int rank, int cid, int ncl, uint32_t tmem_g,
-                                uint32_t tmem_du, uint32_t& g_par, uint32_t& xround, bool prepared, bool mem_tile, uint32_t& mem_par) {
+GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, int t, int it, int rank, int cid, int ncl,
+                                uint32_t tmem_g, uint32_t tmem_du, uint32_t& g_par, uint32_t& xround, bool prepared, bool mem_tile,
+                                uint32_t& mem_par, const P2Tiles tiles, uint32_t& tile_par) {
   typedef typename std::conditional<F32, float, bf16>::type MT;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int Tin = p.Tin, A = p.A, KS = p.KS, hk = (p.KS - 1) / 2, E = p.E;
@@ -513,6 +547,14 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
         sm.dctx_s[d] = val;
         if (half == 0) p.dctx_all[bt * E + d] = val;
       }
+    }
+    // what reaches w_j through the next frame's location features and the upstream alignment gradient: fetched together with
+    // the context gradient (one L2 round trip instead of two); this CTA wrote dwprev / dcum of its positions itself
+    float dw_extra = 0.f;
+    if (active && (int)threadIdx.x < jn && j0 + (int)threadIdx.x < L) {
+      const int j = j0 + threadIdx.x;
+      dw_extra = __ldcg(&p.dwprev[(size_t)b * p.ldT + j]) + __ldcg(&p.dcum[(size_t)b * p.ldT + j]);
+      if (p.dalign) dw_extra += p.dalign[bt * Tin + j];
     }
     if (!prepared) attn_bwd_prepare(p, sm, t, b, active, j0, jn, im_hi, im_lo);
     __syncthreads();
@@ -599,17 +641,16 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
     if (mem_tile) mem_par ^= 1u;
     PROFB(23);
     __syncthreads();
-    if (active) {
-      // + what reaches w_j through the next frame's location features and the upstream alignment gradient
-      for (int jl = threadIdx.x; jl < jn; jl += blockDim.x) {
-        const int j = j0 + jl;
-        if (j < L) {
-          float s = sm.dw_s[j] + __ldcg(&p.dwprev[(size_t)b * p.ldT + j]) + __ldcg(&p.dcum[(size_t)b * p.ldT + j]);
-          if (p.dalign) s += p.dalign[bt * Tin + j];
-          sm.dw_s[j] = s;
-        }
-      }
+    if (tiles.th && active && threadIdx.x == 0 && jn > 0) {
+      // the memory tile has been consumed (generic-proxy reads, ordered by the barrier above): the tanh tile takes its place
+      fence_proxy_async_smem();
+      const uint32_t bytes = (uint32_t)jn * A * 4u;
+      mbar_expect_tx(sm.th_full, bytes);
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(smem_u32(sm.ring.base + TH_TILE_OFF)), "l"(p.th_all + (tb * Tin + j0) * A), "r"(bytes),
+                     "r"(smem_u32(sm.th_full)) : "memory");
     }
+    if (active && (int)threadIdx.x < jn && j0 + (int)threadIdx.x < L) sm.dw_s[j0 + threadIdx.x] += dw_extra;   // (jn <= 128 < blockDim)
     __syncthreads();
     if (active) {
       for (int jl = threadIdx.x; jl < jn; jl += blockDim.x) dot_part += sm.w_s[j0 + jl] * sm.dw_s[j0 + jl];
@@ -643,48 +684,86 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
       const uint32_t toff = (uint32_t)(ap >> 6) * W_TILE_BYTES + (uint32_t)((ap & 7) * 2);
       const int chunk = (ap & 63) >> 3;
       float dq0 = 0.f, dq1 = 0.f, dv0 = 0.f, dv1 = 0.f;
-      for (int jb = rg; jb < TILE_M; jb += 32) {
-        // eight rows per trip (jb, jb + 4, ..., jb + 28): all of their loads are issued before any is consumed
-        constexpr int RW = 8;
-        if (jb >= jn) {
-          // a whole trip beyond this CTA's positions (warp-uniform): the tile rows only need their zeros
-#pragma unroll
-          for (int r = 0; r < RW; ++r) {
-            const uint32_t off = toff + sw128_off(jb + 4 * r, chunk);
-            *reinterpret_cast<uint32_t*>(dth_hi + off) = 0u;
-            *reinterpret_cast<uint32_t*>(dth_lo + off) = 0u;
-          }
-          continue;
-        }
+      PROFB(7);
+      if (tiles.th && jn > 0) wait_bar(sm.th_full, tile_par & 1u);
+      PROFB(8);
+      // A thread's rows are jr + 8 k with jr = rg or rg + 4: (row & 7) is then fixed, so the swizzled tile offset, the tanh
+      // tile, the d(energies) and the d(processed memory) addresses all advance by constants (this loop was a fifth of the
+      // kernel's instructions).  Rows at or beyond nvalid (padding / the other half / beyond Tin) hold zeros.
+      const int nvalid = max(0, min(jn, L - j0));
+      const int row8 = 8 * A;
+      // rows(TH, FULL): RW rows k0 .. k0 + RW - 1 of residue jr; TH = tanh tile in shared memory, FULL = all RW rows valid
+      constexpr int RW = 5;
+      auto rows = [&](auto TH, auto FULL, int k0, int nr, uint8_t* hi, uint8_t* lo, const float* th_g, uint32_t th_sa,
+                      float* dpmp, const float* dep) {
         float2 th[RW];
         float de[RW];
-        bool ok[RW];
 #pragma unroll
         for (int r = 0; r < RW; ++r) {
-          const int jl = jb + 4 * r, j = j0 + jl;
-          ok[r] = a_ok && jl < jn && j < L;
+          const bool ok = FULL.value || k0 + r < nr;
           th[r] = make_float2(0.f, 0.f);
           de[r] = 0.f;
-          if (ok[r]) {
-            th[r] = __ldg(reinterpret_cast<const float2*>(p.th_all + ((tb * Tin + j) * A + ap)));
-            de[r] = sm.dw_s[j];
+          if (ok) {
+            if (TH.value) {
+              asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(th[r].x), "=f"(th[r].y) : "r"(th_sa));
+            } else {
+              th[r] = __ldg(reinterpret_cast<const float2*>(th_g));
+            }
+            de[r] = dep[r * 8];
           }
+          th_sa += (uint32_t)row8 * 4u;
+          th_g += row8;
         }
 #pragma unroll
         for (int r = 0; r < RW; ++r) {
-          const int jl = jb + 4 * r;
-          const float d0 = de[r] * v0 * (1.f - th[r].x * th[r].x), d1 = de[r] * v1 * (1.f - th[r].y * th[r].y);
+          const float e0 = de[r] * v0, e1 = de[r] * v1;
+          const float d0 = e0 * (1.f - th[r].x * th[r].x), d1 = e1 * (1.f - th[r].y * th[r].y);
           // d processed_memory accumulates over the frames: a fire-and-forget L2 reduction instead of load + add + store
           // (this thread is the only writer of the address, frames are ordered by the grid barriers: same sums, no read)
-          if (ok[r]) red_add_f2(p.dpm + (((size_t)b * Tin + (j0 + jl)) * A + ap), d0, d1);
+          if (FULL.value || k0 + r < nr) red_add_f2(dpmp, d0, d1);
+          dpmp += row8;
           dq0 += d0; dq1 += d1;
           dv0 += de[r] * th[r].x; dv1 += de[r] * th[r].y;
-          const float h0 = bf16_round(d0), h1 = bf16_round(d1);
-          const uint32_t off = toff + sw128_off(jl, chunk);
-          *reinterpret_cast<uint32_t*>(dth_hi + off) = pack_bf16x2(h0, h1);
-          *reinterpret_cast<uint32_t*>(dth_lo + off) = pack_bf16x2(d0 - h0, d1 - h1);
+          const uint32_t hp = pack_bf16x2(d0, d1);
+          const float h0 = __uint_as_float(hp << 16), h1 = __uint_as_float(hp & 0xFFFF0000u);
+          if (FULL.value || k0 + r < TILE_M / 8) {
+            *reinterpret_cast<uint32_t*>(hi + r * 1024) = hp;
+            *reinterpret_cast<uint32_t*>(lo + r * 1024) = pack_bf16x2(d0 - h0, d1 - h1);
+          }
+        }
+      };
+#pragma unroll 1
+      for (int s = 0; s < 2; ++s) {
+        const int jr = rg + 4 * s;
+        const uint32_t sw = toff + (uint32_t)(jr * 128 + ((chunk ^ jr) << 4));
+        const int nr = a_ok ? (nvalid - jr + 7) >> 3 : 0;              // this thread's valid rows: k < nr (warp-uniform but for a_ok)
+#pragma unroll 1
+        for (int k0 = 0; k0 < TILE_M / 8; k0 += RW) {
+          uint8_t* hi = dth_hi + sw + k0 * 1024;
+          uint8_t* lo = dth_lo + sw + k0 * 1024;
+          const int row = jr + 8 * k0;
+          const float* th_g = p.th_all + ((tb * Tin + j0 + row) * A + ap);
+          const uint32_t th_sa = smem_u32(sm.ring.base + TH_TILE_OFF) + (uint32_t)(row * A + ap) * 4u;
+          float* dpmp = p.dpm + (((size_t)b * Tin + j0 + row) * A + ap);
+          const float* dep = sm.dw_s + j0 + row;
+          if (k0 + RW <= nr) {
+            if (tiles.th) rows(std::true_type{}, std::true_type{}, k0, nr, hi, lo, th_g, th_sa, dpmp, dep);
+            else rows(std::false_type{}, std::true_type{}, k0, nr, hi, lo, th_g, th_sa, dpmp, dep);
+          } else if (k0 < nr) {
+            if (tiles.th) rows(std::true_type{}, std::false_type{}, k0, nr, hi, lo, th_g, th_sa, dpmp, dep);
+            else rows(std::false_type{}, std::false_type{}, k0, nr, hi, lo, th_g, th_sa, dpmp, dep);
+          } else {
+#pragma unroll
+            for (int r = 0; r < RW; ++r) {
+              if (k0 + r < TILE_M / 8) {
+                *reinterpret_cast<uint32_t*>(hi + r * 1024) = 0u;
+                *reinterpret_cast<uint32_t*>(lo + r * 1024) = 0u;
+              }
+            }
+          }
         }
       }
+      PROFB(9);
       fence_proxy_async_smem();
       // combine the four row groups: part_s[rg][0..127] (dq), then the same for dv
       sm.part_s[rg * 128 + ap] = dq0;
@@ -748,7 +827,8 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
             umma_bf16(tmem_du, da, db, idesc_mn, (pl | k) != 0 ? 1u : acc_du);
           }
         }
-        // (no commit needed for dU: it is only read at the very end, after later commits / barriers)
+        // (dU itself is only read at the very end; the commit tells when its operand tiles in the ring may be overwritten)
+        if (tiles.wq) umma_commit(sm.du_done);
       }
     }
     __syncwarp();
@@ -771,6 +851,14 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
     }
     tc_fence_before();
     __syncthreads();
+    if (tiles.wq && threadIdx.x == 0) {
+      // this rank's quarter of Wq -> start of the ring (the dth / im2col tiles are dead once the dU MMAs have retired)
+      if (active) wait_bar(sm.du_done, (tile_par >> 1) & 1u);
+      fence_proxy_async_smem();
+      const int Hq = ((p.Ha / CL + 1) / 2) * 2;
+      mbar_expect_tx(sm.wq_full, (uint32_t)A * Hq * 2u);
+      tma_load_3d(sm.ring.base, &maps.wq, sm.wq_full, rank * (Hq / 2), 0, 0);
+    }
     PROFB(15);
     if (active) {
       // d wcat[ch][jj] = sum_k G[jj - k][ch*KS + k]  over this CTA's positions
@@ -825,8 +913,15 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, SmemB& sm, int t, int it, int 
     PROFB(19);
     {
       const int b0 = cid * 2 + itb * npairs, b1 = b0 + 1;
-      if (b0 < p.B) quad_cells<F32>(p, sm.dqf_s, sm.dctx_s, t, it, b0, b1, rank);
+      if (b0 < p.B)
+        quad_cells<F32>(p, sm.dqf_s, sm.dctx_s, t, it, b0, b1, rank,
+                        tiles.wq ? reinterpret_cast<const uint32_t*>(sm.ring.base) : nullptr, sm.wq_full, (tile_par >> 2) & 1u);
+      else if (tiles.wq) wait_bar(sm.wq_full, (tile_par >> 2) & 1u);     // the copy must not outlive the frame
     }
+    // parities of the three tile barriers: bit 0 tanh tile, bit 1 dU commit, bit 2 Wq tile (each completes once per frame when used)
+    if (tiles.th && active && jn > 0) tile_par ^= 1u;
+    if (tiles.wq && active) tile_par ^= 2u;
+    if (tiles.wq) tile_par ^= 4u;
     __syncthreads();
   }
 }
@@ -892,6 +987,9 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
     mbar_init(&sm.recv_full[0], 1);
     mbar_init(&sm.recv_full[1], 1);
     mbar_init(sm.mem_full, 1);
+    mbar_init(sm.th_full, 1);
+    mbar_init(sm.wq_full, 1);
+    mbar_init(sm.du_done, 1);
     mbar_fence_init();
   }
   if (warp == 2) tmem_alloc(sm.tmem_slot, 512);
@@ -947,6 +1045,10 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
   const bool mem_tile = !F32 && fast && (p.E % 8) == 0 &&
                         MEM_TILE_OFF + (uint32_t)fJH * p.E * 2u + 2u * W_TILE_BYTES <= sm.ring_bytes;
   uint8_t* const f_im = sm.ring.base + sm.ring_bytes - 2 * W_TILE_BYTES;
+  P2Tiles tiles;
+  tiles.th = fast && (p.A % 4) == 0 && TH_TILE_OFF + (uint32_t)fJH * p.A * 4u + 2u * W_TILE_BYTES <= sm.ring_bytes;
+  tiles.wq = !F32 && fast && (p.flags & 4) != 0 && (uint32_t)p.A * (((p.Ha / CL + 1) / 2) * 2) * 2u <= sm.ring_bytes;
+  uint32_t tile_par = 0;
   dec_cell_prologue<F32>(p, p.T - 1);
   grid_sync2(p.barrier, epoch, nblocks);
   int it = 0;
@@ -974,7 +1076,8 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
       grid_sync2(p.barrier, epoch, nblocks);
     }
     PROFB(5);
-    attn_bwd_phase2<F32>(p, sm, t, it, rank, cid, ncl, tmem_g, tmem_du, g_par, xround, fast, !F32 && mem_tile && fjn > 0, mem_par);
+    attn_bwd_phase2<F32>(p, maps, sm, t, it, rank, cid, ncl, tmem_g, tmem_du, g_par, xround, fast, !F32 && mem_tile && fjn > 0, mem_par,
+                         tiles, tile_par);
     PROFB(20);
     grid_sync2(p.barrier, epoch, nblocks);
     PROFB(21);
@@ -1013,6 +1116,8 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
 // ------------------------------------------------------------------------------------------------
 int make_tma_map_3d(CUtensorMap* out, const void* base, long long d0, long long d1, long long d2, long long stride1_elems,
                     long long stride2_elems, int box1);
+int make_tma_map_f32_3d(CUtensorMap* out, const void* base, long long d0, long long d1, long long d2, long long stride1_elems,
+                        long long stride2_elems, int box0, int box1, int box2);
 
 template <int N, bool F32>
 static int bwd2_config(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attrs, int& S, size_t& smem) {
@@ -1104,6 +1209,7 @@ extern "C" int gtn_decoder_backward2(const gtn_decoder_bwd2_params* hp, void* st
   const int N = pick_n(p.B);
   const int m = p.mult;
   Bwd2Maps maps;
+  memset(&maps, 0, sizeof(maps));
   int rc = 0;
   rc |= make_tma_map_3d(&maps.wT_att, p.wT_att2, (long long)m * 4 * p.Ha, p.E + p.Ha, 1, (long long)m * 4 * p.Ha, 0, TILE_M);
   rc |= make_tma_map_3d(&maps.wT_dec, p.wT_dec2, (long long)m * 4 * p.Hd, p.Ha + p.E + p.Hd, 1, (long long)m * 4 * p.Hd, 0, TILE_M);
@@ -1111,6 +1217,16 @@ extern "C" int gtn_decoder_backward2(const gtn_decoder_bwd2_params* hp, void* st
   rc |= make_tma_map_3d(&maps.xdg_a, p.xdg_a, (long long)m * 4 * p.Ha, p.B, 1, (long long)m * 4 * p.Ha, 0, N);
   rc |= make_tma_map_3d(&maps.xdg_d, p.xdg_d, (long long)m * 4 * p.Hd, p.B, 2, (long long)m * 4 * p.Hd, (long long)p.B * m * 4 * p.Hd, N);
   if (rc) return rc;
+  {
+    // Wq quarter box (bf16 pairs as fp32 words): one rank's units x all A rows, see TH_TILE_OFF
+    const int Hq = ((p.Ha / CL + 1) / 2) * 2;
+    p.flags &= ~4;
+    if (p.prec == 1 && Hq % 8 == 0 && Hq <= 256 && p.Ha % 8 == 0) {
+      rc = make_tma_map_f32_3d(&maps.wq, p.wq_au, p.Ha / 2, p.A, 1, p.Ha / 2, (long long)(p.Ha / 2) * p.A, Hq / 2, p.A, 1);
+      if (rc) return rc;
+      p.flags |= 4;
+    }
+  }
   cudaStream_t st = (cudaStream_t)stream;
   const int ncl = grid / CL;
   // precision is a compile-time property of the kernels (half the code: the per-frame path is instruction-cache cold every frame)

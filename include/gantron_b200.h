@@ -319,7 +319,7 @@ typedef struct gtn_decoder_bwd2_params {
   float *dv_part;            /* [grid][A] */
   float *dU_part;            /* [grid][128][64]: per-CTA partial of dU[a][ch*KS+k] */
   long long *prof;           /* optional [16][32] clock64() stamps of CTA 0 for the first 16 processed frames (NULL = off) */
-  int flags;                 /* bit 0: prefetch each frame's saves into L2 one frame ahead; bit 1: dga_all / dgd_all are bf16 */
+  int flags;                 /* bit 0: prefetch each frame's saves into L2 one frame ahead; bit 1: dga_all / dgd_all are bf16; bit 2 is the library's (cleared on entry) */
 } gtn_decoder_bwd2_params;
 
 int gtn_decoder_bwd2_grid(int B, int Ha, int Hd, int E);   /* CTAs gtn_decoder_backward2 launches, or -1 */
