@@ -135,11 +135,16 @@ GTN_DEVICE SmemB carveB(uint8_t* base, int S) {
 }
 
 // split grid barrier: ARRIVE, then work that does not depend on the other CTAs, then WAIT (thread 0 carries the fences)
-GTN_DEVICE void grid_arrive2(unsigned int* counter) {
+// proxy_fence: this CTA wrote global data with ordinary stores that ANOTHER CTA reads through TMA after the barrier (the gate
+// gradients, barrier 2).  P1's results (barrier 1) are only read by ordinary loads; skipping the fence there matters because a
+// fence.proxy.async issued while the memory tile's bulk copy is in flight waits for it (3.3k cycles per frame).
+GTN_DEVICE void grid_arrive2(unsigned int* counter, bool proxy_fence = true, long long* stamp = nullptr) {
   __syncthreads();
   if (threadIdx.x == 0) {
-    fence_proxy_async();
+    if (stamp) stamp[0] = clock64();
+    if (proxy_fence) fence_proxy_async();
     red_release_add(counter, 1u);
+    if (stamp) stamp[1] = clock64();
   }
 }
 GTN_DEVICE void grid_wait2(unsigned int* counter, unsigned int target) {
@@ -290,12 +295,14 @@ GTN_DEVICE void dec_cell_prologue(const DecBwd2& p, int t) {
   }
 }
 
+GTN_DEVICE void attn_bwd_window(const DecBwd2& p, SmemB& sm, int t, int b, int j0, int jn, int tid, int nthr);
+
 // ------------------------------------------------------------------------------------------------
 // P1: data-gradient GEMM tiles
 // ------------------------------------------------------------------------------------------------
 template <int N, bool F32>
 GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, int t, int it, int rank, int cid, int ncl,
-                             uint32_t tmem_base, uint32_t& acc_par, uint32_t& round, int res_n) {
+                             uint32_t tmem_base, uint32_t& acc_par, uint32_t& round, int res_n, int win_b, int win_j0, int win_jn) {
   constexpr int CH = N < 64 ? N : 64;
   constexpr int NC4 = CH / 4;
   const int R_dec = p.Ha + p.E + p.Hd, R_att = p.E + p.Ha;
@@ -316,6 +323,9 @@ GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, 
     const bool has_work = gemm_issue<N>(job, sm.ring, tmem_base, sm.acc_full, rank, tmem_base);
     PROFB(1);
     __syncwarp();
+    // warps 4..7 have nothing to do until the accumulator is complete: they fetch the attention backward's window meanwhile
+    // (fast layout; ordered before its readers by the barriers of the exchange below)
+    if ((threadIdx.x >> 5) >= 4 && win_b >= 0 && tile == cid) attn_bwd_window(p, sm, t, win_b, win_j0, win_jn, threadIdx.x - 128, 128);
     if ((threadIdx.x >> 5) >= 4 && has_work) {
       wait_bar(sm.acc_full, acc_par);
       tc_fence_after();
@@ -367,9 +377,44 @@ GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, 
 // 128 KB per CTA per frame through a ~30 B/clk port; 64 KB this way).  Thread = (unit pair pr, half h): during the Wq
 // product h selects the half of the attention dimension (both sequences), partial sums meet in shared memory, and for the
 // cell arithmetic h selects the sequence.  dq2 = [2][128] full d query of the two sequences, part = [2][2][128][2] scratch.
+// operands of one round of quad_cells: fetched ahead of the pair's second cluster barrier (none of them depends on it)
+struct QuadOps {
+  CellIn ca[2], cd[2];
+  float2 adda, addd;
+};
+GTN_DEVICE void quad_cells_load(const DecBwd2& p, int t, int b0, int b1, int rank, int rd, QuadOps& o) {
+  const int Hq_a = ((p.Ha / CL + 1) / 2) * 2, ua_beg = rank * Hq_a, ua_end = min(p.Ha, (rank + 1) * Hq_a);
+  const int Hq_d = ((p.Hd / CL + 1) / 2) * 2, ud_beg = rank * Hq_d, ud_end = min(p.Hd, (rank + 1) * Hq_d);
+  const int pr = threadIdx.x & 127, h = threadIdx.x >> 7;
+  const int b = h == 0 ? b0 : b1;
+  const bool seq_ok = b < p.B;
+  const int ua = ua_beg + rd * 256 + 2 * pr, ud = ud_beg + rd * 256 + 2 * pr;
+  o.adda = make_float2(0.f, 0.f);
+  o.addd = make_float2(0.f, 0.f);
+  if (t > 0 && ud < ud_end && seq_ok) {
+    o.cd[0] = cell_load(p, t - 1, b, ud, p.Hd, p.gates_d, p.c_d_all, p.dc_d);
+    o.cd[1] = cell_load(p, t - 1, b, ud + 1, p.Hd, p.gates_d, p.c_d_all, p.dc_d);
+    const float2 r = __ldcg(reinterpret_cast<const float2*>(p.dhd_rec + (size_t)b * p.Hd + ud));
+    const float* q = p.dproj_all + ((size_t)(t - 1) * p.B + b) * (p.Hd + p.D) + ud;     // row stride Hd + D may be odd
+    o.addd = make_float2(r.x + __ldg(q), r.y + __ldg(q + 1));
+  }
+  if (ua < ua_end && seq_ok) {
+    o.ca[0] = cell_load(p, t, b, ua, p.Ha, p.gates_a, p.c_a_all, p.dc_a);
+    o.ca[1] = cell_load(p, t, b, ua + 1, p.Ha, p.gates_a, p.c_a_all, p.dc_a);
+    const size_t ci = (size_t)b * p.Ha + ua;
+    const float2 x = __ldcg(reinterpret_cast<const float2*>(p.dha_dec + ci)), y = __ldcg(reinterpret_cast<const float2*>(p.carry_ha + ci));
+    o.adda = make_float2(x.x + y.x, x.y + y.y);
+  }
+}
+// rounds of 256 units per rank the cells need (1 at the default dims: then the operands can be fetched early)
+GTN_DEVICE int quad_rounds(const DecBwd2& p, int t) {
+  const int Hq_a = ((p.Ha / CL + 1) / 2) * 2, Hq_d = ((p.Hd / CL + 1) / 2) * 2;
+  return max((Hq_a + 255) / 256, t > 0 ? (Hq_d + 255) / 256 : 0);
+}
+
 template <bool F32>
 GTN_DEVICE void quad_cells(const DecBwd2& p, const float* dq2, float* part, int t, int it, int b0, int b1, int rank,
-                           const uint32_t* wq_s, uint64_t* wq_full, uint32_t wq_par) {
+                           const uint32_t* wq_s, uint64_t* wq_full, uint32_t wq_par, const QuadOps* pre) {
   const int nxt = (it & 1) ^ 1;
   bf16* xnext_d = BFP(p.xdg_d) + (size_t)nxt * p.B * (F32 ? 6 : 1) * 4 * p.Hd;
   const int Hq_a = ((p.Ha / CL + 1) / 2) * 2, ua_beg = rank * Hq_a, ua_end = min(p.Ha, (rank + 1) * Hq_a);
@@ -384,22 +429,9 @@ GTN_DEVICE void quad_cells(const DecBwd2& p, const float* dq2, float* part, int 
     const int ud = ud_beg + rd * 256 + 2 * pr;
     const bool oka_u = rd < na && ua < ua_end;                       // unit pair exists (Wq product: both sequences)
     const bool oka = oka_u && seq_ok, okd = rd < nd && ud < ud_end && seq_ok;
-    CellIn ca[2], cd[2];
-    float2 adda = make_float2(0.f, 0.f), addd = make_float2(0.f, 0.f);
-    if (okd) {
-      cd[0] = cell_load(p, t - 1, b, ud, p.Hd, p.gates_d, p.c_d_all, p.dc_d);
-      cd[1] = cell_load(p, t - 1, b, ud + 1, p.Hd, p.gates_d, p.c_d_all, p.dc_d);
-      const float2 r = __ldcg(reinterpret_cast<const float2*>(p.dhd_rec + (size_t)b * p.Hd + ud));
-      const float* q = p.dproj_all + ((size_t)(t - 1) * p.B + b) * (p.Hd + p.D) + ud;     // row stride Hd + D may be odd
-      addd = make_float2(r.x + __ldg(q), r.y + __ldg(q + 1));
-    }
-    if (oka) {
-      ca[0] = cell_load(p, t, b, ua, p.Ha, p.gates_a, p.c_a_all, p.dc_a);
-      ca[1] = cell_load(p, t, b, ua + 1, p.Ha, p.gates_a, p.c_a_all, p.dc_a);
-      const size_t ci = (size_t)b * p.Ha + ua;
-      const float2 x = __ldcg(reinterpret_cast<const float2*>(p.dha_dec + ci)), y = __ldcg(reinterpret_cast<const float2*>(p.carry_ha + ci));
-      adda = make_float2(x.x + y.x, x.y + y.y);
-    }
+    QuadOps o;
+    if (rd == 0 && pre != nullptr) o = *pre;
+    else quad_cells_load(p, t, b0, b1, rank, rd, o);
     // Wq^T dq over this thread's half of the attention dimension, for both sequences
     float s00 = 0.f, s01 = 0.f, s10 = 0.f, s11 = 0.f;                // [sequence][unit of the pair]
     if (!F32 && wq_s != nullptr) {
@@ -456,10 +488,10 @@ GTN_DEVICE void quad_cells(const DecBwd2& p, const float* dq2, float* part, int 
     const float s0 = h0.x + h1.x, s1 = h0.y + h1.y;                  // sequence h, units ua, ua + 1
     PROFB(26);
     if (okd) {
-      cell_apply2<F32>(p, cd, t - 1, b, ud, p.Hd, addd.x, addd.y, p.dc_d, p.dgd_all, xnext_d, 4u, p.thr_dec, p.p_dec);
+      cell_apply2<F32>(p, o.cd, t - 1, b, ud, p.Hd, o.addd.x, o.addd.y, p.dc_d, p.dgd_all, xnext_d, 4u, p.thr_dec, p.p_dec);
     }
     if (oka) {
-      cell_apply2<F32>(p, ca, t, b, ua, p.Ha, s0 + adda.x, s1 + adda.y, p.dc_a, p.dga_all, BFP(p.xdg_a), 3u, p.thr_att, p.p_att);
+      cell_apply2<F32>(p, o.ca, t, b, ua, p.Ha, s0 + o.adda.x, s1 + o.adda.y, p.dc_a, p.dga_all, BFP(p.xdg_a), 3u, p.thr_att, p.p_att);
     }
   }
 }
@@ -487,20 +519,27 @@ GTN_DEVICE void ld8b<bf16>(const bf16* p, float (&o)[8]) {
 
 // Window, im2col tiles and the frame's alignment row of ONE sequence: everything of the attention backward that depends on
 // the forward pass's saves only.  In the `fast` layout it runs between ARRIVE and WAIT of barrier 1.
-GTN_DEVICE void attn_bwd_prepare(const DecBwd2& p, SmemB& sm, int t, int b, bool active, int j0, int jn, uint8_t* im_hi, uint8_t* im_lo) {
+// the frame's alignment row and the location-conv window [prev | cum] of one sequence -> shared memory (threads tid of nthr)
+GTN_DEVICE void attn_bwd_window(const DecBwd2& p, SmemB& sm, int t, int b, int j0, int jn, int tid, int nthr) {
   const int Tin = p.Tin, KS = p.KS, hk = (p.KS - 1) / 2;
   const int Wd = jn + KS - 1;
   const size_t tb = (size_t)t * p.B + b, bt = (size_t)b * p.T + t;
-  if (active) {
-    for (int j = threadIdx.x; j < Tin; j += blockDim.x) sm.w_s[j] = p.align[bt * Tin + j];
-    for (int i = threadIdx.x; i < 2 * Wd; i += blockDim.x) {
-      const int ch = i / Wd, jj = i - ch * Wd, j = j0 + jj - hk;
-      float val = 0.f;
-      if (j >= 0 && j < Tin) val = ch == 0 ? (t > 0 ? p.align[(bt - 1) * Tin + j] : 0.f) : p.cum_all[tb * Tin + j];
-      sm.wcat[i] = val;
-    }
+  for (int j = tid; j < Tin; j += nthr) sm.w_s[j] = p.align[bt * Tin + j];
+  for (int i = tid; i < 2 * Wd; i += nthr) {
+    const int ch = i / Wd, jj = i - ch * Wd, j = j0 + jj - hk;
+    float val = 0.f;
+    if (j >= 0 && j < Tin) val = ch == 0 ? (t > 0 ? p.align[(bt - 1) * Tin + j] : 0.f) : p.cum_all[tb * Tin + j];
+    sm.wcat[i] = val;
   }
-  __syncthreads();
+}
+// window_loaded: attn_bwd_window already ran for this frame (warps 4..7, while P1's operands stream)
+GTN_DEVICE void attn_bwd_prepare(const DecBwd2& p, SmemB& sm, int t, int b, bool active, int j0, int jn, uint8_t* im_hi, uint8_t* im_lo,
+                                 bool window_loaded = false) {
+  const int KS = p.KS;
+  const int Wd = jn + KS - 1;
+  if (active && !window_loaded) attn_bwd_window(p, sm, t, b, j0, jn, threadIdx.x, blockDim.x);
+  if (!window_loaded) __syncthreads();
+  if (p.prof != nullptr && blockIdx.x == 0 && threadIdx.x == 0 && (p.T - 1 - t) < 16) p.prof[(p.T - 1 - t) * 32 + 14] = clock64();
   if (active) {
     build_im2col(sm.wcat, Wd, KS, jn, im_hi, im_lo);
     // zero the K-rows of the im2col tiles beyond jn (they are the K extent of dU += dth^T . im2col)
@@ -531,7 +570,7 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& s
   uint8_t* dth_lo = sm.ring.base + 2 * W_TILE_BYTES;
   uint8_t* im_hi = sm.ring.base + (prepared ? sm.ring_bytes - 2 * W_TILE_BYTES : 4 * W_TILE_BYTES);
   uint8_t* im_lo = im_hi + W_TILE_BYTES;
-  float* G_s = sm.recv;                                  // [128][64], column index XOR (row & 31)
+  float* G_s = sm.recv;                                  // [128][63]: odd row stride = conflict-free for row-per-lane stores and the diagonal reads (2 KS <= 62 columns are used)
   const int niter = (p.B + npairs - 1) / npairs;
   for (int itb = 0; itb < niter; ++itb) {
     const int b = pair + itb * npairs;
@@ -845,7 +884,8 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& s
           tmem_ld_32x32(tmem_g + ((uint32_t)(wq * 32) << 16) + (uint32_t)(h * 32), r);
           tmem_ld_wait();
 #pragma unroll
-          for (int c = 0; c < 32; ++c) G_s[jl * 64 + ((h * 32 + c) ^ (jl & 31))] = __uint_as_float(r[c]);
+          for (int c = 0; c < 32; ++c)
+            if (h * 32 + c < 62) G_s[jl * 63 + h * 32 + c] = __uint_as_float(r[c]);
         }
       }
     }
@@ -864,12 +904,14 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& s
       // d wcat[ch][jj] = sum_k G[jj - k][ch*KS + k]  over this CTA's positions
       for (int i = threadIdx.x; i < 2 * Wd; i += blockDim.x) {
         const int ch = i / Wd, jj = i - ch * Wd;
-        float s = 0.f;
-        for (int k = 0; k < KS; ++k) {
-          const int jl = jj - k;
-          if (jl >= 0 && jl < jn) s += G_s[jl * 64 + ((ch * KS + k) ^ (jl & 31))];
-        }
-        sm.dwc_s[i] = s;
+        // G[jj - k][ch KS + k] for the k that keep the row inside [0, jn): a run of addresses 62 words apart
+        const int klo = max(0, jj - jn + 1), khi = min(KS - 1, jj);
+        const float* q = G_s + (jj - klo) * 63 + ch * KS + klo;
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        int k = klo;
+        for (; k + 3 <= khi; k += 4, q -= 4 * 62) { s0 += q[0]; s1 += q[-62]; s2 += q[-124]; s3 += q[-186]; }
+        for (; k <= khi; ++k, q -= 62) s0 += q[0];
+        sm.dwc_s[i] = (s0 + s1) + (s2 + s3);
       }
     }
     __syncthreads();
@@ -885,6 +927,10 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& s
       }
     }
     PROFB(16);
+    QuadOps qops;
+    const int qb0 = cid * 2 + itb * npairs;
+    const bool qpre = qb0 < p.B && quad_rounds(p, t) == 1;
+    if (qpre) quad_cells_load(p, t, qb0, qb0 + 1, rank, 0, qops);
     cluster_sync_all();                                              // #2: halos and dq partials of the pair
     PROFB(17);
     if (active) {
@@ -915,7 +961,8 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& s
       const int b0 = cid * 2 + itb * npairs, b1 = b0 + 1;
       if (b0 < p.B)
         quad_cells<F32>(p, sm.dqf_s, sm.dctx_s, t, it, b0, b1, rank,
-                        tiles.wq ? reinterpret_cast<const uint32_t*>(sm.ring.base) : nullptr, sm.wq_full, (tile_par >> 2) & 1u);
+                        tiles.wq ? reinterpret_cast<const uint32_t*>(sm.ring.base) : nullptr, sm.wq_full, (tile_par >> 2) & 1u,
+                        qpre ? &qops : nullptr);
       else if (tiles.wq) wait_bar(sm.wq_full, (tile_par >> 2) & 1u);     // the copy must not outlive the frame
     }
     // parities of the three tile barriers: bit 0 tanh tile, bit 1 dU commit, bit 2 Wq tile (each completes once per frame when used)
@@ -1055,21 +1102,24 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
   for (int t = p.T - 1; t >= 0; --t, ++it) {
     PROFB(0);
     if (p.flags & 1) prefetch_frame(p, t, rank, cid, ncl);
-    dgrad_phase2<N, F32>(p, maps, sm, t, it, rank, cid, ncl, tmem_base, acc_par, round, res_n);
-    if (mem_tile && factive && threadIdx.x == 0 && fjn > 0) {
-      // (P1's MMAs have drained the ring: every thread passed the exchange's syncs behind the accumulator wait)
-      const uint32_t bytes = (uint32_t)fjn * p.E * 2u;
-      mbar_expect_tx(sm.mem_full, bytes);
-      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                   ::"r"(smem_u32(sm.ring.base + MEM_TILE_OFF)),
-                     "l"(reinterpret_cast<const bf16*>(p.mem_enc) + ((size_t)fb * p.Tin + fj0) * p.E), "r"(bytes),
-                     "r"(smem_u32(sm.mem_full)) : "memory");
-    }
+    // (this cluster runs a P1 tile this frame <=> its idle warps can fetch the attention window there)
+    const bool win_p1 = fast && factive &&
+                        cid < (R_dec_ + TILE_M - 1) / TILE_M + (t + 1 < p.T ? (R_att_ + TILE_M - 1) / TILE_M : 0);
+    dgrad_phase2<N, F32>(p, maps, sm, t, it, rank, cid, ncl, tmem_base, acc_par, round, res_n, win_p1 ? fb : -1, fj0, fjn);
     PROFB(4);
     if (fast) {
-      grid_arrive2(p.barrier);
+      grid_arrive2(p.barrier, /*proxy_fence=*/false, (p.prof != nullptr && blockIdx.x == 0 && it < 16) ? p.prof + it * 32 + 28 : nullptr);
       epoch += nblocks;
-      attn_bwd_prepare(p, sm, t, fb, factive, fj0, fjn, f_im, f_im + W_TILE_BYTES);
+      if (mem_tile && factive && threadIdx.x == 0 && fjn > 0) {
+        // (P1's MMAs have drained the ring: every thread passed the exchange's syncs behind the accumulator wait)
+        const uint32_t bytes = (uint32_t)fjn * p.E * 2u;
+        mbar_expect_tx(sm.mem_full, bytes);
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(smem_u32(sm.ring.base + MEM_TILE_OFF)),
+                       "l"(reinterpret_cast<const bf16*>(p.mem_enc) + ((size_t)fb * p.Tin + fj0) * p.E), "r"(bytes),
+                       "r"(smem_u32(sm.mem_full)) : "memory");
+      }
+      attn_bwd_prepare(p, sm, t, fb, factive, fj0, fjn, f_im, f_im + W_TILE_BYTES, /*window_loaded=*/win_p1);
       PROFB(6);
       grid_wait2(p.barrier, epoch);
     } else {
