@@ -297,9 +297,6 @@ GTN_DEVICE void dec_cell_prologue(const DecBwd2& p, int t) {
 
 GTN_DEVICE void attn_bwd_window(const DecBwd2& p, SmemB& sm, int t, int b, int j0, int jn, int tid, int nthr);
 
-// ------------------------------------------------------------------------------------------------
-// P1: data-gradient GEMM tiles
-// ------------------------------------------------------------------------------------------------
 template <int N, bool F32>
 GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, int t, int it, int rank, int cid, int ncl,
                              uint32_t tmem_base, uint32_t& acc_par, uint32_t& round, int res_n, int win_b, int win_j0, int win_jn) {
@@ -580,11 +577,23 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& s
     const uint32_t xb = xround & 1u;
     ++xround;
     if (active) {
-      for (int d = threadIdx.x; d < E; d += blockDim.x) {
-        const float val = p.dproj_all[tb * (p.Hd + p.D) + p.Hd + d] + __ldcg(&p.dctx_dec[(size_t)b * p.Ep + d]) +
-                          __ldcg(&p.dctx_att[(size_t)b * p.Ep + d]);
-        sm.dctx_s[d] = val;
-        if (half == 0) p.dctx_all[bt * E + d] = val;
+      // all loads of the (up to four) elements a thread owns are issued before the first store: one L2 round trip, not one per trip
+      float cv[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int d = threadIdx.x + q * 256;
+        cv[q] = 0.f;
+        if (d < E)
+          cv[q] = p.dproj_all[tb * (p.Hd + p.D) + p.Hd + d] + __ldcg(&p.dctx_dec[(size_t)b * p.Ep + d]) +
+                  __ldcg(&p.dctx_att[(size_t)b * p.Ep + d]);
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int d = threadIdx.x + q * 256;
+        if (d < E) {
+          sm.dctx_s[d] = cv[q];
+          if (half == 0) p.dctx_all[bt * E + d] = cv[q];
+        }
       }
     }
     // what reaches w_j through the next frame's location features and the upstream alignment gradient: fetched together with
@@ -875,6 +884,7 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& s
       wait_bar(sm.g_full, g_par);
       g_par ^= 1u;
       tc_fence_after();
+      PROFB(30);
       if (warp >= 4) {
         const int wq = warp & 3;
         const int jl = wq * 32 + lane;
@@ -959,11 +969,13 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& s
     PROFB(19);
     {
       const int b0 = cid * 2 + itb * npairs, b1 = b0 + 1;
-      if (b0 < p.B)
+      if (b0 < p.B) {
         quad_cells<F32>(p, sm.dqf_s, sm.dctx_s, t, it, b0, b1, rank,
                         tiles.wq ? reinterpret_cast<const uint32_t*>(sm.ring.base) : nullptr, sm.wq_full, (tile_par >> 2) & 1u,
                         qpre ? &qops : nullptr);
-      else if (tiles.wq) wait_bar(sm.wq_full, (tile_par >> 2) & 1u);     // the copy must not outlive the frame
+      } else if (tiles.wq) {
+        wait_bar(sm.wq_full, (tile_par >> 2) & 1u);                      // the copy must not outlive the frame
+      }
     }
     // parities of the three tile barriers: bit 0 tanh tile, bit 1 dU commit, bit 2 Wq tile (each completes once per frame when used)
     if (tiles.th && active && jn > 0) tile_par ^= 1u;

@@ -24,9 +24,9 @@ FW = {0: "step start (gsync2 of t-1 done)", 2: "A: acc done", 3: "A: exchange do
       20: "attn done (context)", 21: "arrived barrier 2", 23: "barrier 2 wait done"}
 FO = [0, 2, 3, 4, 5, 10, 11, 12, 13, 14, 15, 24, 16, 17, 18, 19, 20, 21, 23]
 BW = {0: "step start", 1: "P1: TMA issued", 2: "P1: acc done", 3: "P1: exchange done", 4: "P1: epilogue done", 28: "barrier 1: CTA synced", 29: "barrier 1: release done", 14: "P2 prepare: window loaded", 6: "P2 prepare (in barrier shadow)", 5: "gsync done",
-      10: "P2: loads + window", 22: "P2: memory tile landed", 23: "P2: dw done", 24: "P2: dw totals done", 11: "P2: dot (block sum)", 12: "P2: cluster sync 1", 7: "P2: softmax backward", 8: "P2: tanh tile landed", 9: "P2: dth rows done", 13: "P2: dq/dv combined", 15: "P2: MMA + G to smem",
+      10: "P2: loads + window", 22: "P2: memory tile landed", 23: "P2: dw done", 24: "P2: dw totals done", 11: "P2: dot (block sum)", 12: "P2: cluster sync 1", 7: "P2: softmax backward", 8: "P2: tanh tile landed", 9: "P2: dth rows done", 13: "P2: dq/dv combined", 30: "P2: G accumulator complete", 15: "P2: G to smem",
       16: "P2: d wcat", 17: "P2: cluster sync 2", 18: "P2 done", 19: "P2: dq in smem", 27: "cells: operands loaded, Wq tile landed", 25: "cells: Wq^T dq product done", 26: "cells: partials combined", 20: "cells done", 21: "gsync done"}
-BO = [0, 1, 2, 3, 4, 28, 29, 14, 6, 5, 10, 22, 23, 24, 11, 12, 7, 8, 9, 13, 15, 16, 17, 19, 27, 25, 26, 20, 21]
+BO = [0, 1, 2, 3, 4, 28, 29, 14, 6, 5, 10, 22, 23, 24, 11, 12, 7, 8, 9, 13, 30, 15, 16, 17, 19, 27, 25, 26, 20, 21]
 for rep in range(2):
     pf = torch.zeros(16 * 32 + 4 * 160, dtype=torch.int64, device="cuda")
     pb = torch.zeros(2 * 16 * 32, dtype=torch.int64, device="cuda")
