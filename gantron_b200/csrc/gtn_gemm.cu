@@ -61,6 +61,47 @@ GTN_DEVICE void wait_or_trap(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// Epilogue store of one warp's 32 x 32 sub-tile through shared memory.  After tcgen05.ld a lane owns one output ROW, so a
+// direct store instruction touches 32 different rows (32 partial sectors per instruction, or 32 scalar stores per chunk for a
+// transposed output).  Staged, every store instruction writes 16 bytes per lane along the output's contiguous direction:
+// four full 128-byte lines (fp32) or eight 64-byte runs (bf16) per instruction.  st = this warp's [32][36] float scratch in
+// the (idle) TMA ring; org = element index of the sub-tile's first element along the contiguous direction, ld = stride of
+// the other direction.  trans: the contiguous direction is the tile's ROW (m) index.
+GTN_DEVICE void store_tile32(float* st, const float (&v)[32], int lane, void* C, bool bf16o, bool trans, long long org, long long ld) {
+  if (!trans) {
+    float4* row = reinterpret_cast<float4*>(st + lane * 36);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) row[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) st[j * 36 + lane] = v[j];
+  }
+  __syncwarp();
+  if (!bf16o) {
+    float* Cf = reinterpret_cast<float*>(C);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r = i * 4 + (lane >> 3), c4 = (lane & 7) * 4;
+      *reinterpret_cast<float4*>(Cf + org + (long long)r * ld + c4) = *reinterpret_cast<const float4*>(st + r * 36 + c4);
+    }
+  } else {
+    __nv_bfloat16* Cb = reinterpret_cast<__nv_bfloat16*>(C);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int r = i * 8 + (lane >> 2), c8 = (lane & 3) * 8;
+      const float4 a = *reinterpret_cast<const float4*>(st + r * 36 + c8), b = *reinterpret_cast<const float4*>(st + r * 36 + c8 + 4);
+      *reinterpret_cast<uint4*>(Cb + org + (long long)r * ld + c8) =
+          make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
+    }
+  }
+  __syncwarp();
+}
+// the staged path needs 16-byte aligned runs: element alignment of every run start
+GTN_DEVICE bool tile32_aligned(const void* C, bool bf16o, long long org, long long ld) {
+  const long long a = bf16o ? 7 : 3;
+  return (reinterpret_cast<uintptr_t>(C) & 15) == 0 && (org & a) == 0 && (ld & a) == 0;
+}
+
 template <int BN>
 __global__ void __launch_bounds__(256, 2)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -185,8 +226,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     if (elect_one()) umma_commit(accum_full);       // accumulator complete
     __syncwarp();
-  } else if (warp >= 4) {
+  }
+  {
     // ------------------------------ epilogue ------------------------------
+    // ALL eight warps: a warp may only read its own TMEM lane quarter (warp % 4), so warps 4..7 take the even 32-column
+    // chunks and warps 0..3 -- whose producer / issuer / allocator roles are over by now -- the odd ones.  With four
+    // epilogue warps there was one warp per scheduler and the stores of output-bound shapes ran at ~1.1 TB/s.
     wait_or_trap(accum_full, 0);
     tc_fence_after();
     const int wq = warp & 3;                 // TMEM lane quarter this warp may touch
@@ -199,8 +244,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     float* C2f = reinterpret_cast<float*>(p.C2);
     __nv_bfloat16* C2b = reinterpret_cast<__nv_bfloat16*>(p.C2);
     const long long zc = (long long)z * p.strideC, zc2 = (long long)z * p.strideC2;
+    // (the ring is idle once the accumulator is complete: its first bytes are the epilogue warps' staging tiles)
+    float* stage = reinterpret_cast<float*>(smem) + warp * (32 * 36);
+    const int mt0 = m0 + wq * 32;
+    const bool rows_full = mt0 + 32 <= p.M;                 // warp-uniform
 #pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
+    for (int c = warp >= 4 ? 0 : 1; c < BN / 32; c += 2) {
       uint32_t r[32];
       tmem_ld_32x32(tmem_acc + ((uint32_t)(wq * 32) << 16) + (uint32_t)(c * 32), r);
       tmem_ld_wait();
@@ -254,9 +303,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int j = 0; j < 32; ++j)
           if (nb + j < p.N) { s1 += v[j]; s2 += v[j] * v[j]; }
       }
+      const bool tile_full = rows_full && nb + 32 <= p.N;
+      bool c_done = false, c2_done = false;
+      if (tile_full && p.C != nullptr) {
+        const long long org = p.c_trans ? zc + (long long)nb * p.ldc + mt0 : zc + (long long)mt0 * p.ldc + nb;
+        if (tile32_aligned(p.C, p.c_bf16 != 0, org, p.ldc)) {
+          store_tile32(stage, v, lane, p.C, p.c_bf16 != 0, p.c_trans != 0, org, p.ldc);
+          c_done = true;
+        }
+      }
+      if (tile_full && p.C2 != nullptr) {
+        const long long org = p.c2_trans ? zc2 + (long long)nb * p.ldc2 + mt0 : zc2 + (long long)mt0 * p.ldc2 + nb;
+        if (tile32_aligned(p.C2, p.c2_bf16 != 0, org, p.ldc2)) {
+          store_tile32(stage, v, lane, p.C2, p.c2_bf16 != 0, p.c2_trans != 0, org, p.ldc2);
+          c2_done = true;
+        }
+      }
       if (!m_ok) continue;
       // primary output
-      if (p.C != nullptr) {
+      if (p.C != nullptr && !c_done) {
         if (!p.c_trans) {
           const long long base = zc + (long long)m * p.ldc + nb;
           const bool full32 = (nb + 32 <= p.N);
@@ -292,7 +357,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       }
       // secondary output (other layout / dtype of the same values)
-      if (p.C2 != nullptr) {
+      if (p.C2 != nullptr && !c2_done) {
         if (!p.c2_trans) {
           const long long base = zc2 + (long long)m * p.ldc2 + nb;
           for (int j = 0; j < 32; ++j)

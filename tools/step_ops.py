@@ -17,15 +17,17 @@ torch.cuda.synchronize()
 with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], with_stack=True) as prof:
     tr.step(x, y)
     torch.cuda.synchronize()
-ka = prof.key_averages(group_by_stack_n=6)
+ka = prof.key_averages(group_by_stack_n=30)
 rows = []
 for e in ka:
     dt = getattr(e, "self_device_time_total", 0)
-    if dt > 20:
-        stack = [s for s in e.stack if "gantron_b200" in s or "bench.py" in s][:2]
+    if dt > 8:
+        stack = [s for s in e.stack if ("gantron_b200/" in s or "bench.py" in s) and "tools/" not in s][:2]
+        if not e.key.startswith("aten::") and not e.key.startswith("Mem"):
+            continue
         rows.append((dt, e.count, e.key, " <- ".join(s.split("/")[-1] for s in stack)))
 rows.sort(reverse=True)
 tot = sum(r[0] for r in rows)
 print(f"total device self time of listed ops {tot / 1e3:.2f} ms")
-for dt, n, k, st in rows[:70]:
+for dt, n, k, st in rows[:90]:
     print(f"{dt / 1e3:8.3f} ms {n:4d}  {k[:48]:48s} {st}")
