@@ -262,8 +262,9 @@ class Trainer:
             from gantron_b200.distributed import apply_gradient_allreduce
             self.G = apply_gradient_allreduce(self.G)
             self.D = apply_gradient_allreduce(self.D)
-        self.g_opt = torch.optim.Adam(self.G.parameters(), lr=self.hp.g_learning_rate, weight_decay=self.hp.weight_decay)
-        self.d_opt = torch.optim.Adam(self.D.parameters(), lr=self.hp.d_learning_rate, weight_decay=self.hp.weight_decay)
+        # train.py:243-250's optimizers; fused=True is the same update as one multi-tensor kernel per step
+        self.g_opt = torch.optim.Adam(self.G.parameters(), lr=self.hp.g_learning_rate, weight_decay=self.hp.weight_decay, fused=True)
+        self.d_opt = torch.optim.Adam(self.D.parameters(), lr=self.hp.d_learning_rate, weight_decay=self.hp.weight_decay, fused=True)
         self.criterion = Tacotron2Loss()
         self.G.train(); self.D.train()
         self.real, self.fake = 1.0, -1.0

@@ -266,6 +266,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         continue;
       }
       float v[32];
+      // (warp-uniform) nothing fused but the row bias: skip the per-element tests of the general path
+      const bool simple = p.bias_n == nullptr && !p.accumulate && p.act == 0 && p.drop_thr == 0u && p.stats == nullptr;
+      if (simple) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + bm;
+      } else {
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
         float x = __uint_as_float(r[j]) + bm;
@@ -302,6 +308,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
         for (int j = 0; j < 32; ++j)
           if (nb + j < p.N) { s1 += v[j]; s2 += v[j] * v[j]; }
+      }
       }
       const bool tile_full = rows_full && nb + 32 <= p.N;
       bool c_done = false, c2_done = false;
