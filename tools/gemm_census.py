@@ -15,7 +15,7 @@ ON = [False]
 
 def caller():
     for fs in reversed(traceback.extract_stack()[:-2]):
-        if "gantron_b200" in fs.filename and not fs.filename.endswith("ops.py"):
+        if "gantron_b200" in fs.filename and os.path.basename(fs.filename) != "ops.py":
             return f"{os.path.basename(fs.filename)}:{fs.lineno}"
     return "?"
 
