@@ -584,7 +584,7 @@ def run_ours(args):
 BWD_KERNEL_MAC = (2560 + 1536) * 4096 + 131_072 + 2 * 912_000 + 2 * 172_800
 FWD_KERNEL_MAC = DEC_STEP_MAC - 86_016 - 165_888 - 4096 * 256 - 4096 * 1024 - 0   # minus prenet, projection, hoisted prenet/constant columns
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` captures (profiles/r2_ncu_decoder.md)
-NCU_TRAFFIC = {"decoder_fwd3_kernel": 6.94e9, "decoder_bwd2_kernel": 7.63e9}   # B = 64, T_in = 150, T_out = 800
+NCU_TRAFFIC = {"decoder_fwd3_kernel": 6.92e9, "decoder_bwd2_kernel": 7.51e9}   # B = 64, T_in = 150, T_out = 800
 # cycles-per-frame floors of the two recurrent kernels: L2 -> SM stream of the operands that cannot stay
 # on chip at the measured ~30 B/clk/SM plus two grid barriers of ~2k cycles
 FLOOR_CYCLES_PER_FRAME = {"decoder_fwd3_kernel": 11_000, "decoder_bwd2_kernel": 13_000}
