@@ -267,7 +267,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       float v[32];
       // (warp-uniform) nothing fused but the row bias: skip the per-element tests of the general path
-      const bool simple = p.bias_n == nullptr && !p.accumulate && p.act == 0 && p.drop_thr == 0u && p.stats == nullptr;
+      const bool simple = p.bias_n == nullptr && !p.accumulate && p.act == 0 && p.drop_thr == 0u;
       if (simple) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + bm;
@@ -304,11 +304,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           else if (p.act == 2) v[j] = tanhf(v[j]);
         }
       }
-      if (p.stats != nullptr) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (nb + j < p.N) { s1 += v[j]; s2 += v[j] * v[j]; }
       }
+      if (p.stats != nullptr) {
+        if (nb + 32 <= p.N) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { s1 += v[j]; s2 += v[j] * v[j]; }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (nb + j < p.N) { s1 += v[j]; s2 += v[j] * v[j]; }
+        }
       }
       const bool tile_full = rows_full && nb + 32 <= p.N;
       bool c_done = false, c2_done = false;
