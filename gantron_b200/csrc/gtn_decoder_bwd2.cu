@@ -44,6 +44,7 @@ struct Bwd2Maps {
   CUtensorMap wT_att, wT_dec, ut;      // weights (A operands) and U^T (B operand of d[prev|cum] = dth . U)
   CUtensorMap xdg_a, xdg_d;            // gate gradients as X operands
   CUtensorMap wq;                      // bf16 Wq [A][Ha] seen as fp32 pairs: box = one rank's quarter of the units x all A rows
+  CUtensorMap mem;                     // bf16 encoder memory [B][Tin][E]: box = 64 columns x (half a sequence rounded up to 8 rows)
 };
 
 static constexpr int B2_TIN_MAX = 256;
@@ -76,6 +77,7 @@ struct SmemB {
   uint64_t* th_full;    // the frame's tanh tile (th_all rows of this CTA's positions) has landed in the ring
   uint64_t* wq_full;    // this rank's quarter of Wq has landed in the ring
   uint64_t* du_done;    // the dU MMAs of the frame have retired (their operand tiles in the ring may be overwritten)
+  uint64_t* dw_done;    // dw = mem . dctx on the tensor core has retired
   uint32_t* tmem_slot;
   uint32_t ring_bytes;
 };
@@ -130,6 +132,7 @@ GTN_DEVICE SmemB carveB(uint8_t* base, int S) {
   m.th_full = b++;
   m.wq_full = b++;
   m.du_done = b++;
+  m.dw_done = b++;
   m.tmem_slot = reinterpret_cast<uint32_t*>(b + 1);
   return m;
 }
@@ -169,7 +172,9 @@ static constexpr uint32_t MEM_TILE_OFF = 2 * W_TILE_BYTES;
 // the ring by ONE TMA box once the attention MMAs have retired: the cells' Wq^T dq product reads it from shared memory
 // instead of streaming 64 KB per frame through the LSU (6k -> ~1.5k cycles).
 static constexpr uint32_t TH_TILE_OFF = 4 * W_TILE_BYTES;
-struct P2Tiles { bool th; bool wq; };
+// mma: the encoder-memory tile arrives as SWIZZLE_128B k-block tiles (TMA) and dw = mem . dctx runs on tcgen05 (M = positions,
+// N = 8: the context gradient as hi / lo bf16 rows, K = E) instead of 16 FMA chains per warp (3.7k -> ~1k cycles)
+struct P2Tiles { bool th; bool wq; bool mma; };
 
 GTN_DEVICE void red_add_f2(float* addr, float a, float b) {
   asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(a), "f"(b) : "memory");
@@ -593,8 +598,18 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& s
         if (d < E) {
           sm.dctx_s[d] = cv[q];
           if (half == 0) p.dctx_all[bt * E + d] = cv[q];
+          if (tiles.mma) {
+            // B operand of dw: per 64-column k-block an [8 rows][64] K-major SWIZZLE_128B tile in the (idle) receive buffer,
+            // row 0 = bf16(dctx), row 1 = the residual; rows 2..7 are never read back (their D columns are ignored)
+            uint8_t* bt_ = reinterpret_cast<uint8_t*>(sm.recv) + (d >> 6) * 1024 + (d & 7) * 2;
+            const int c = (d & 63) >> 3;
+            const float hi = bf16_round(cv[q]);
+            *reinterpret_cast<__nv_bfloat16*>(bt_ + (c << 4)) = __float2bfloat16_rn(hi);
+            *reinterpret_cast<__nv_bfloat16*>(bt_ + 128 + ((c ^ 1) << 4)) = __float2bfloat16_rn(cv[q] - hi);
+          }
         }
       }
+      if (tiles.mma) fence_proxy_async_smem();
     }
     // what reaches w_j through the next frame's location features and the upstream alignment gradient: fetched together with
     // the context gradient (one L2 round trip instead of two); this CTA wrote dwprev / dcum of its positions itself
@@ -608,7 +623,40 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& s
     __syncthreads();
     PROFB(10);
     float dot_part = 0.f;
-    if (active && mem_tile) {
+    if (tiles.mma && mem_tile) {
+      // dw[j] = sum_d mem[j][d] dctx[d] on tcgen05: A = the memory tiles (128 rows from each tile base: the rows beyond the
+      // box belong to the next tile, their results are not read), B = the context gradient tiles, D = first columns of tmem_g
+      const int box1 = ((((Tin + 1) / 2) + 7) / 8) * 8;
+      if (active && __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0) == 1) {
+        wait_bar(sm.mem_full, mem_par);
+        tc_fence_after();
+        const uint32_t idesc = umma_idesc_bf16(TILE_M, 8);
+        const uint32_t a0 = smem_u32(sm.ring.base + MEM_TILE_OFF), b0 = smem_u32(sm.recv);
+        if (elect_one()) {
+          for (int kb = 0; kb < E / KB; ++kb) {
+            const uint64_t da = umma_desc_sw128(a0 + (uint32_t)kb * box1 * 128u), db = umma_desc_sw128(b0 + (uint32_t)kb * 1024u);
+#pragma unroll
+            for (int k = 0; k < KB / 16; ++k)
+              umma_bf16(tmem_g, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (uint32_t)((kb | k) != 0));
+          }
+          umma_commit(sm.dw_done);
+        }
+        __syncwarp();
+      }
+      PROFB(22);
+      if (active) {
+        wait_bar(sm.dw_done, (tile_par >> 3) & 1u);
+        tc_fence_after();
+        if (warp >= 4) {
+          const int wq = warp & 3, jl = wq * 32 + lane;
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_g + ((uint32_t)(wq * 32) << 16), r);
+          tmem_ld_wait();
+          if (jl < jn) sm.dw_s[j0 + jl] = (j0 + jl < L) ? __uint_as_float(r[0]) + __uint_as_float(r[1]) : 0.f;
+        }
+        tc_fence_before();
+      }
+    } else if (active && mem_tile) {
       // d w_j = mem[j][:] . dctx over this CTA's positions, from the tile in shared memory: one warp per position, lanes over
       // the columns (16 bytes per lane and trip: conflict-free)
       wait_bar(sm.mem_full, mem_par);
@@ -981,6 +1029,7 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& s
     if (tiles.th && active && jn > 0) tile_par ^= 1u;
     if (tiles.wq && active) tile_par ^= 2u;
     if (tiles.wq) tile_par ^= 4u;
+    if (tiles.mma && mem_tile && active) tile_par ^= 8u;
     __syncthreads();
   }
 }
@@ -1049,6 +1098,7 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
     mbar_init(sm.th_full, 1);
     mbar_init(sm.wq_full, 1);
     mbar_init(sm.du_done, 1);
+    mbar_init(sm.dw_done, 1);
     mbar_fence_init();
   }
   if (warp == 2) tmem_alloc(sm.tmem_slot, 512);
@@ -1101,12 +1151,16 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
   const int fJH = (p.Tin + 1) / 2, fj0 = (rank & 1) * fJH, fjn = min(p.Tin, fj0 + fJH) - fj0;
   const int fb = cid * 2 + (rank >> 1);
   const bool factive = fb < p.B;
-  const bool mem_tile = !F32 && fast && (p.E % 8) == 0 &&
-                        MEM_TILE_OFF + (uint32_t)fJH * p.E * 2u + 2u * W_TILE_BYTES <= sm.ring_bytes;
+  const bool mem_tile_bulk = !F32 && fast && (p.E % 8) == 0 &&
+                             MEM_TILE_OFF + (uint32_t)fJH * p.E * 2u + 2u * W_TILE_BYTES <= sm.ring_bytes;
   uint8_t* const f_im = sm.ring.base + sm.ring_bytes - 2 * W_TILE_BYTES;
   P2Tiles tiles;
   tiles.th = fast && (p.A % 4) == 0 && TH_TILE_OFF + (uint32_t)fJH * p.A * 4u + 2u * W_TILE_BYTES <= sm.ring_bytes;
   tiles.wq = !F32 && fast && (p.flags & 4) != 0 && (uint32_t)p.A * (((p.Ha / CL + 1) / 2) * 2) * 2u <= sm.ring_bytes;
+  const int mem_box1 = ((fJH + 7) / 8) * 8;
+  tiles.mma = !F32 && fast && (p.flags & 8) != 0 && (p.E % KB) == 0 &&
+              MEM_TILE_OFF + (uint32_t)(p.E / KB) * mem_box1 * 128u + 2u * W_TILE_BYTES <= sm.ring_bytes;
+  const bool mem_tile = mem_tile_bulk || tiles.mma;
   uint32_t tile_par = 0;
   dec_cell_prologue<F32>(p, p.T - 1);
   grid_sync2(p.barrier, epoch, nblocks);
@@ -1122,7 +1176,17 @@ __global__ void __launch_bounds__(256, 1) decoder_bwd2_kernel(const __grid_const
     if (fast) {
       grid_arrive2(p.barrier, /*proxy_fence=*/false, (p.prof != nullptr && blockIdx.x == 0 && it < 16) ? p.prof + it * 32 + 28 : nullptr);
       epoch += nblocks;
-      if (mem_tile && factive && threadIdx.x == 0 && fjn > 0) {
+      if (tiles.mma && factive && fjn > 0) {
+        // the memory tile as E / 64 SWIZZLE_128B k-block tiles of mem_box1 rows (warp 0, one elected lane, uniform control flow)
+        if (__shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0) == 0) {
+          if (elect_one()) {
+            mbar_expect_tx(sm.mem_full, (uint32_t)(p.E / KB) * mem_box1 * 128u);
+            for (int kb = 0; kb < p.E / KB; ++kb)
+              tma_load_3d(sm.ring.base + MEM_TILE_OFF + (size_t)kb * mem_box1 * 128, &maps.mem, sm.mem_full, kb * KB, fj0, fb);
+          }
+          __syncwarp();
+        }
+      } else if (mem_tile && factive && threadIdx.x == 0 && fjn > 0) {
         // (P1's MMAs have drained the ring: every thread passed the exchange's syncs behind the accumulator wait)
         const uint32_t bytes = (uint32_t)fjn * p.E * 2u;
         mbar_expect_tx(sm.mem_full, bytes);
@@ -1287,6 +1351,14 @@ extern "C" int gtn_decoder_backward2(const gtn_decoder_bwd2_params* hp, void* st
       rc = make_tma_map_f32_3d(&maps.wq, p.wq_au, p.Ha / 2, p.A, 1, p.Ha / 2, (long long)(p.Ha / 2) * p.A, Hq / 2, p.A, 1);
       if (rc) return rc;
       p.flags |= 4;
+    }
+    // encoder-memory k-block tiles for dw on the tensor core (bf16 memory only)
+    p.flags &= ~8;
+    const int box1 = ((((p.Tin + 1) / 2) + 7) / 8) * 8;
+    if (p.prec == 1 && p.mem_bf16 && p.E % KB == 0 && box1 <= 256) {
+      rc = make_tma_map_3d(&maps.mem, p.mem_enc, p.E, p.Tin, p.B, p.E, (long long)p.Tin * p.E, box1);
+      if (rc) return rc;
+      p.flags |= 8;
     }
   }
   cudaStream_t st = (cudaStream_t)stream;
