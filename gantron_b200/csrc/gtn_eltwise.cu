@@ -272,24 +272,26 @@ __global__ void __launch_bounds__(256)
 disc_head_bwd_kernel(const float* __restrict__ dout, const void* __restrict__ x, int x_bf16, long long ldx, long long rows,
                      int C, const float* __restrict__ w, void* dx, int dx_bf16, long long lddx, float* dw, float* db) {
   // thread -> channel c = threadIdx.x % Cp, row lane = threadIdx.x / Cp  (Cp = C rounded to... simple 1 elem/thread)
-  const int tpr = C;                        // threads per row
+  const int tpr = C < 256 ? C : 256;        // threads per row; wider heads (LinearDiscriminator: 512) loop over the channels
   const int rpi = blockDim.x / tpr;
-  const int c = threadIdx.x % tpr, r0 = threadIdx.x / tpr;
-  float acc_w = 0.f, acc_b = 0.f;
+  const int c0 = threadIdx.x % tpr, r0 = threadIdx.x / tpr;
   if (r0 < rpi) {
-    const float wc = w[c];
-    for (long long row = (long long)blockIdx.x * rpi + r0; row < rows; row += (long long)gridDim.x * rpi) {
-      const float g = dout[row];
-      const float xv = x_bf16 ? __bfloat162float(reinterpret_cast<const bf16*>(x)[row * ldx + c])
-                              : reinterpret_cast<const float*>(x)[row * ldx + c];
-      acc_w += g * xv;
-      if (c == 0) acc_b += g;
-      const float d = g * wc;
-      if (dx_bf16) reinterpret_cast<bf16*>(dx)[row * lddx + c] = __float2bfloat16_rn(d);
-      else reinterpret_cast<float*>(dx)[row * lddx + c] = d;
+    for (int c = c0; c < C; c += tpr) {
+      float acc_w = 0.f, acc_b = 0.f;
+      const float wc = w[c];
+      for (long long row = (long long)blockIdx.x * rpi + r0; row < rows; row += (long long)gridDim.x * rpi) {
+        const float g = dout[row];
+        const float xv = x_bf16 ? __bfloat162float(reinterpret_cast<const bf16*>(x)[row * ldx + c])
+                                : reinterpret_cast<const float*>(x)[row * ldx + c];
+        acc_w += g * xv;
+        if (c == 0) acc_b += g;
+        const float d = g * wc;
+        if (dx_bf16) reinterpret_cast<bf16*>(dx)[row * lddx + c] = __float2bfloat16_rn(d);
+        else reinterpret_cast<float*>(dx)[row * lddx + c] = d;
+      }
+      if (dw != nullptr) atomicAdd(&dw[c], acc_w);
+      if (db != nullptr && c == 0) atomicAdd(db, acc_b);
     }
-    if (dw != nullptr) atomicAdd(&dw[c], acc_w);
-    if (db != nullptr && c == 0) atomicAdd(db, acc_b);
   }
 }
 
@@ -568,11 +570,11 @@ int gtn_disc_head_fwd(const void* x, int x_dtype, long long ldx, long long rows,
 
 int gtn_disc_head_bwd(const float* dout, const void* x, int x_dtype, long long ldx, long long rows, int C, const float* w,
                       void* dx, int dx_dtype, long long lddx, float* dw, float* db, void* stream) {
-  GTN_REQUIRE(rows > 0 && C > 0 && C <= 256, "head width must be <= 256");
+  GTN_REQUIRE(rows > 0 && C > 0 && C <= 8192, "head width must be <= 8192");
   cudaStream_t st = (cudaStream_t)stream;
   if (dw) GTN_CUDA_OK(cudaMemsetAsync(dw, 0, C * sizeof(float), st));
   if (db) GTN_CUDA_OK(cudaMemsetAsync(db, 0, sizeof(float), st));
-  const int rpi = 256 / C;
+  const int rpi = 256 / (C < 256 ? C : 256);
   long long blocks = (rows + rpi - 1) / rpi;
   const long long cap = (long long)sm_count() * 4;
   if (blocks > cap) blocks = cap;

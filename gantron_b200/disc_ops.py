@@ -36,6 +36,18 @@ def _convs(disc):
     return [seq[i].module[0] for i in range(len(seq) - 1)], seq[len(seq) - 1]
 
 
+def _geom(layer):
+    """(kernel, dilation, padding) of a DiscConv1d conv, or of a DiscDense linear seen as a one-tap conv (layers.py:63-73:
+    Linear -> Dropout -> Tanh is the same bias -> dropout -> tanh epilogue over rows instead of positions)."""
+    if isinstance(layer, torch.nn.Linear):
+        return 1, 1, 0
+    return layer.kernel_size[0], layer.dilation[0], layer.padding[0]
+
+
+def _w3(w: torch.Tensor) -> torch.Tensor:
+    return w if w.dim() == 3 else w.unsqueeze(-1)
+
+
 def _params(disc):
     convs, head = _convs(disc)
     out = []
@@ -45,7 +57,8 @@ def _params(disc):
 
 
 class _DiscFn(torch.autograd.Function):
-    """x (B, window*n_mel, P) [the raw-reshaped input] -> (B, P)."""
+    """x (B, window*n_mel, P) [the raw-reshaped input] -> (B, P).  Serves the conv Discriminator and, with one-tap layers
+    and P = stacked windows, the LinearDiscriminator (model.py:543-583); dropout sites disc._gtn_site0 + layer."""
 
     @staticmethod
     def forward(ctx, disc, seed, prec, x, *params):
@@ -59,11 +72,11 @@ class _DiscFn(torch.autograd.Function):
         saved = []
         for i, conv in enumerate(convs):
             w, b = params[2 * i], params[2 * i + 1]
-            k, dil, pad = conv.kernel_size[0], conv.dilation[0], conv.padding[0]
-            wp, cin_eff, cin_pad = cache.get(("fwd", i, prec), w, lambda w=w: pack_conv_weight(w, prec))
+            k, dil, pad = _geom(conv)
+            wp, cin_eff, cin_pad = cache.get(("fwd", i, prec), w, lambda w=w: pack_conv_weight(_w3(w), prec))
             a = torch.empty(B, P, w.shape[0], device=dev, dtype=adt)
             p_drop = disc.discriminator[i].module[1].p if disc.discriminator[i].module[1].training else 0.0
-            drop = (p_drop, seed, SITE_DISC0 + i)
+            drop = (p_drop, seed, getattr(disc, "_gtn_site0", SITE_DISC0) + i)
             ops.conv1d(wp, cin_eff, cin_pad, k, dil, pad, act_operand(cur, prec), a, None, bias=b.detach(),
                        act=ops.ACT_TANH, dropout=drop, drop_first=True, block_n=64)
             saved.append((cur, a, drop))
@@ -97,7 +110,7 @@ class _DiscFn(torch.autograd.Function):
             conv = convs[i]
             w = params[2 * i]
             x_in, a, drop = saved[i]
-            k, dil, pad = conv.kernel_size[0], conv.dilation[0], conv.padding[0]
+            k, dil, pad = _geom(conv)
             cout, cin = w.shape[0], w.shape[1]
             dpre = torch.empty(B, P, cout, device=dev, dtype=adt)
             dbias = ops.drop_tanh_bwd(dcur, a, drop, dpre, want_dbias=need_w)
@@ -105,9 +118,9 @@ class _DiscFn(torch.autograd.Function):
                 dyo, xo = wgrad_operands(dpre, x_in, prec)
                 dwt = torch.empty(k, cout, cin, device=dev)
                 ops.conv1d_wgrad(dyo, xo, cin, k, dil, pad, dwt, block_n=128)
-                grads[2 * i], grads[2 * i + 1] = dwt.permute(1, 2, 0).contiguous(), dbias
+                grads[2 * i], grads[2 * i + 1] = dwt.permute(1, 2, 0).reshape(w.shape).contiguous(), dbias
             if i > 0 or ctx.needs_input_grad[3]:
-                wT, ce, cp = cache.get(("dgrad", i, prec), w, lambda w=w: pack_conv_weight(w, prec, dgrad=True))
+                wT, ce, cp = cache.get(("dgrad", i, prec), w, lambda w=w: pack_conv_weight(_w3(w), prec, dgrad=True))
                 dcur = torch.empty(B, P, cin, device=dev, dtype=torch.float32)
                 ops.conv1d(wT, ce, cp, k, dil, dil * (k - 1) - pad, act_operand(dpre, prec), dcur, None, block_n=64)
         ctx.saved = None
@@ -185,3 +198,52 @@ class _WindowMean(torch.autograd.Function):
 def masked_window_mean(out: torch.Tensor, target_length: torch.Tensor, window: int) -> torch.Tensor:
     """mean_b mean(out[b, :ceil(len_b / window)])  (model.py:531-540) as one kernel, lengths stay on the device."""
     return _WindowMean.apply(out, target_length, window)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# LinearDiscriminator (reference model.py:543-583; SURVEY 8f4)
+# ------------------------------------------------------------------------------------------------------------
+SITE_LIN0 = 40
+
+
+def linear_discriminator_forward(disc, windows: torch.Tensor, seed: int, prec: int) -> torch.Tensor:
+    """windows (R, window*n_mel) -> (R, 1): three DiscDense layers and the final Linear as one-tap layers of _DiscFn."""
+    x = windows.t().unsqueeze(0)                                   # (1, C0, R); _DiscFn makes the (R, C0) bf16 operand
+    return _DiscFn.apply(disc, seed, prec, x, *_params(disc)).reshape(-1, 1)
+
+
+def linear_window_plan(lengths, window: int, max_overlap: int):
+    """Window starts of every sample, drawn exactly like model.py:572-577 (module-level `random`, sample by sample, the last
+    window aligned to the end) -> (sample index per window, start per window, 1 / (windows of the sample * B) per window)."""
+    import random
+    owner, starts, wts = [], [], []
+    B = len(lengths)
+    for i, n in enumerate(lengths):
+        n = int(n)
+        mine, start = [], 0
+        while start + window < n:
+            mine.append(start)
+            start += window - random.randint(0, max_overlap)
+        mine.append(n - window)
+        owner += [i] * len(mine)
+        starts += mine
+        wts += [1.0 / (len(mine) * B)] * len(mine)
+    return owner, starts, wts
+
+
+def linear_adversarial_loss(disc, inputs: torch.Tensor, target_length: torch.Tensor, seed: int, prec: int) -> torch.Tensor:
+    """mean_b mean_w D(window_w of sample b) (model.py:567-583).  The reference slices, stacks and runs the MLP once per
+    sample with a host sync per window test; here the lengths come to the host ONCE, the window plan goes up as three small
+    pinned tensors, one gather builds all windows of the batch and the MLP runs once over the stacked rows."""
+    n_mel, W = disc.n_mel_channels, disc.windows_size
+    x = inputs.transpose(1, 2) if inputs.size(1) == n_mel else inputs          # (B, T, n_mel), like model.py:570-571
+    lens = target_length.tolist()
+    assert min(lens) >= W, "LinearDiscriminator: every sample must be at least one window long"
+    owner, starts, wts = linear_window_plan(lens, W, disc.max_window_overlap)
+    dev = x.device
+    up = lambda v, dt: torch.tensor(v, dtype=dt).pin_memory().to(dev, non_blocking=True)
+    owner_t, starts_t, wts_t = up(owner, torch.int64), up(starts, torch.int64), up(wts, torch.float32)
+    t_idx = starts_t[:, None] + torch.arange(W, device=dev)[None, :]
+    windows = x[owner_t[:, None], t_idx].reshape(len(owner), W * n_mel)       # one gather (and one scatter-add backward)
+    out = linear_discriminator_forward(disc, windows, seed, prec)
+    return (out[:, 0] * wts_t).sum()

@@ -333,8 +333,8 @@ class Discriminator(nn.Module):
 
 
 class LinearDiscriminator(nn.Module):
-    """MLP discriminator over random overlapping windows (model.py:543-583).  Not on the B200 path
-    (hparams.discriminator_type defaults to 'conv'); stock PyTorch, kept so `train.py:22,116` imports work."""
+    """MLP discriminator over random overlapping windows (model.py:543-583; `discriminator_type='linear'`).
+    Same kernels as the conv Discriminator: a DiscDense (Linear -> Dropout -> Tanh) is a one-tap layer of disc_ops._DiscFn."""
 
     def __init__(self, hparams):
         super().__init__()
@@ -344,22 +344,19 @@ class LinearDiscriminator(nn.Module):
         self.n_mel_channels = hparams.n_mel_channels
         self.windows_size = hparams.discriminator_window
         self.max_window_overlap = 6
+        self._prec = _precision_of(hparams)
+        self._gtn_site0 = 40                                               # disc_ops.SITE_LIN0
 
     def forward(self, inputs):
-        return self.discriminator(inputs)
+        """inputs (rows, window * n_mel) -> (rows, 1)."""
+        from . import disc_ops
+        _require_cuda(inputs, "LinearDiscriminator.forward")
+        return disc_ops.linear_discriminator_forward(self, inputs, seed=_new_seed(self), prec=self._prec)
 
     def adversarial_loss(self, inputs, target_length):
-        total = 0
-        for i, x in enumerate(inputs):
-            if x.size(0) == self.n_mel_channels:
-                x = x.T
-            n, start, wins = int(target_length[i]), 0, []
-            while start + self.windows_size < n:
-                wins.append(x[start:start + self.windows_size].flatten())
-                start += self.windows_size - random.randint(0, self.max_window_overlap)
-            wins.append(x[n - self.windows_size:n].flatten())
-            total = total + torch.mean(self.forward(torch.stack(wins)))
-        return total / target_length.size(0)
+        from . import disc_ops
+        _require_cuda(inputs, "LinearDiscriminator.adversarial_loss")
+        return disc_ops.linear_adversarial_loss(self, inputs, target_length, seed=_new_seed(self), prec=self._prec)
 
 
 class Tacotron2(nn.Module):

@@ -448,6 +448,50 @@ def adversarial_loss(sd: Dict[str, Tensor], mel: Tensor, lengths: Tensor, d: Dim
 
 
 # ----------------------------------------------------------------------------------------
+# LinearDiscriminator  (model.py:543-583, layers.py:63-73)
+# ----------------------------------------------------------------------------------------
+def linear_window_plan(lengths: Sequence[int], window: int, max_overlap: int = 6) -> List[List[int]]:
+    """Window start frames per sample, drawn like model.py:572-577: module-level `random.randint`, sample by sample; the
+    last window is aligned to the end of the sample."""
+    import random
+    plan = []
+    for n in lengths:
+        n, start, mine = int(n), 0, []
+        while start + window < n:
+            mine.append(start)
+            start += window - random.randint(0, max_overlap)
+        mine.append(n - window)
+        plan.append(mine)
+    return plan
+
+
+def linear_discriminator_forward(sd: Dict[str, Tensor], windows: Tensor, keeps: Optional[Sequence[Tensor]],
+                                 prefix: str = "") -> Tensor:
+    """windows (R, window*n_mel) -> (R, 1): three DiscDense = Linear -> Dropout(0.5) -> Tanh, then Linear (model.py:546-551)."""
+    x = windows
+    for i in range(3):
+        w, b = sd[f"{prefix}discriminator.{i}.module.0.weight"], sd[f"{prefix}discriminator.{i}.module.0.bias"]
+        x = torch.tanh(_drop(F.linear(x, w, b), None if keeps is None else keeps[i], 0.5))
+    return F.linear(x, sd[f"{prefix}discriminator.3.weight"], sd[f"{prefix}discriminator.3.bias"])
+
+
+def linear_adversarial_loss(sd: Dict[str, Tensor], mel: Tensor, lengths: Tensor, d: Dims, keeps: Optional[Sequence[Tensor]],
+                            prefix: str = "") -> Tensor:
+    """mean_b mean_w D(window_w of sample b) (model.py:567-583).  `keeps[l]` is the dropout mask of layer l over ALL windows of
+    the batch stacked sample after sample (the numbering of the kernels, which run the MLP once over the stacked rows); the
+    reference runs sample by sample, which is the same arithmetic on row slices."""
+    x = mel.transpose(1, 2) if mel.size(1) == d.n_mel else mel
+    plan = linear_window_plan([int(v) for v in lengths], d.disc_window)
+    rows = [x[i, s:s + d.disc_window].flatten() for i, starts in enumerate(plan) for s in starts]
+    out = linear_discriminator_forward(sd, torch.stack(rows), keeps, prefix)[:, 0]
+    total, r0 = 0.0, 0
+    for starts in plan:
+        total = total + out[r0:r0 + len(starts)].mean()
+        r0 += len(starts)
+    return total / lengths.shape[0]
+
+
+# ----------------------------------------------------------------------------------------
 # Losses  (loss_function.py:6-52)
 # ----------------------------------------------------------------------------------------
 def tacotron2_losses(mel: Tensor, mel_post: Tensor, gate: Tensor, mel_target: Tensor, gate_target: Tensor):

@@ -36,6 +36,7 @@ SITE_ATT_H = 3        # model.py:393 attention_hidden dropout
 SITE_DEC_H = 4        # model.py:408 decoder_hidden dropout
 SITE_POSTNET0 = 16    # model.py:148/149, + layer index
 SITE_DISC0 = 32       # layers.py:55, + layer index
+SITE_LIN0 = 40        # layers.py:68 DiscDense dropout of the LinearDiscriminator, + layer index
 SITE_ENC0 = 60        # model.py:197 / 217 encoder convolutions, + layer index
 
 

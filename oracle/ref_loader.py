@@ -47,7 +47,7 @@ def _install_stubs():
     mod("inflect", engine=lambda: types.SimpleNamespace(number_to_words=lambda *a, **k: ""))
 
 
-_REF_MODULE_NAMES = ("model", "layers", "utils", "hparams", "loss_function", "distributed", "stft",
+_REF_MODULE_NAMES = ("model", "layers", "utils", "hparams", "loss_function", "distributed", "stft", "data_utils",
                      "audio_processing", "text", "text.cleaners", "text.numbers", "text.symbols",
                      "text.cmudict")
 

@@ -140,6 +140,65 @@ def test_discriminator_matches_reference_golden():
     assert _check_grads(z, grads) == 11
 
 
+def test_linear_discriminator_matches_reference_golden():
+    """the LinearDiscriminator on the kernels (one gather + one pass of the MLP over all windows of the batch)
+    against the unmodified reference's per-sample loop, same `random` seed, same dropout stream; fp32-accurate mode."""
+    import random
+    from oracle import gantron_oracle as O
+    from gantron_b200.hparams import HParams
+    from gantron_b200 import model as M
+    z = _load("lin_disc_vanilla")
+    D = M.LinearDiscriminator(HParams("use_noise=True,use_labels=False,b200_precision=fp32"))
+    D.load_state_dict(O.seeded_state_dict({k: tuple(v.shape) for k, v in D.state_dict().items()}, seed=int(z["wseed"])))
+    D = D.cuda().train()
+    D._forced_seed = int(z["mseed"])
+    mel = torch.from_numpy(z["in/mel"]).cuda().requires_grad_(True)
+    random.seed(int(z["pyseed"]))
+    loss = D.adversarial_loss(mel, torch.from_numpy(z["in/lengths"]).cuda())
+    ref = float(z["out/loss"])
+    assert abs(float(loss) - ref) <= REL * abs(ref) + 1e-6, f"{float(loss)} vs {ref}"
+    loss.backward()
+    grads = {k: p.grad for k, p in D.named_parameters()}
+    grads["mel"] = mel.grad
+    assert _check_grads(z, grads) == 9
+
+
+def test_linear_discriminator_bf16_and_frozen():
+    """bf16 mode against the oracle (loss 3e-2 abs, gradients 8e-2 relative Frobenius), and the generator-step use: frozen
+    parameters, gradient to the mel only (train.py:366-378 with discriminator_type='linear')."""
+    import random
+    from oracle import gantron_oracle as O, philox as PX
+    from gantron_b200.hparams import HParams
+    from gantron_b200 import model as M
+    hp = HParams("use_noise=True,use_labels=False")
+    D = M.LinearDiscriminator(hp)
+    sd = O.seeded_state_dict({k: tuple(v.shape) for k, v in D.state_dict().items()}, seed=5)
+    D.load_state_dict(sd)
+    D = D.cuda().train()
+    for p in D.parameters():
+        p.requires_grad = False
+    D._forced_seed = 77
+    g = torch.Generator().manual_seed(3)
+    B, T = 5, 131
+    mel = (torch.randn(B, 80, T, generator=g) * 2 - 5).clamp(-11.5, 2.0)
+    lengths = torch.tensor([131, 120, 99, 64, 20])
+    mel_c = mel.cuda().requires_grad_(True)
+    random.seed(11)
+    loss = D.adversarial_loss(mel_c, lengths.cuda())
+    loss.backward()
+    assert all(p.grad is None for p in D.parameters())
+    random.seed(11)
+    rows = sum(len(s_) for s_ in O.linear_window_plan(lengths.tolist(), 20))
+    keeps = [torch.from_numpy(PX.keep_mask(77, PX.SITE_LIN0 + i, 0, (rows, 512), 0.5)) for i in range(3)]
+    mel_o = mel.clone().requires_grad_(True)
+    random.seed(11)
+    ref = O.linear_adversarial_loss({k: v for k, v in sd.items()}, mel_o, lengths, O.Dims.from_hparams(hp), keeps)
+    ref.backward()
+    assert abs(float(loss) - float(ref)) <= 3e-2, f"{float(loss)} vs {float(ref)}"
+    err = float((mel_c.grad.cpu() - mel_o.grad).norm() / mel_o.grad.norm())
+    assert err <= 8e-2, f"d mel rel err {err:.3e}"
+
+
 def test_training_step_benchmark_shape_matches_reference_golden():
     """T_in = 150 (ragged), 208 frames, fp32-accurate mode, against the unmodified reference (train_vanilla_long):
     75 encoder positions per CTA of a sequence pair, multi-trip attention-backward loops, long-T accumulation."""

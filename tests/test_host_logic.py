@@ -75,3 +75,25 @@ def test_parse_output_masks_through_data():
     assert float(out[0][1, :, 4:].abs().sum()) == 0 and float(out[1][1, :, 4:].abs().sum()) == 0
     assert float(out[2][1, 4:].min()) == 1e3 and float(out[2][0].abs().sum()) == 0
     out[1].sum().backward()            # `.data` masking: the graph does not see it (model.py:638-640)
+
+
+def test_collate_pads_sorts_and_marks_the_stop_frames():
+    """gantron_b200.data_utils.TextMelCollate (reference data_utils.py:82-131): decreasing text length, zero padding, frames
+    rounded up to n_frames_per_step, gate = 1 from the last real frame on."""
+    import torch
+    from gantron_b200.data_utils import TextMelCollate
+    g = torch.Generator().manual_seed(0)
+    items = [[torch.randint(1, 50, (L,), generator=g), torch.randn(80, F_, generator=g), float(i), torch.rand(5, generator=g)]
+             for i, (L, F_) in enumerate([(5, 30), (9, 44), (2, 21), (9, 25)])]
+    text, in_len, mel, gate, spk, emo, out_len = TextMelCollate(4, pin_memory=False)(items)
+    assert in_len.tolist() == sorted([5, 9, 2, 9], reverse=True)
+    assert mel.shape == (4, 80, 44) and text.shape == (4, 9) and gate.shape == (4, 44)
+    order = [int(s) for s in spk.tolist()]
+    assert sorted(order) == [0, 1, 2, 3] and [items[o][0].numel() for o in order] == in_len.tolist()
+    for row, o in enumerate(order):
+        L, F_ = items[o][0].numel(), items[o][1].size(1)
+        assert torch.equal(text[row, :L], items[o][0]) and int(text[row, L:].abs().sum()) == 0
+        assert torch.equal(mel[row, :, :F_], items[o][1]) and float(mel[row, :, F_:].abs().sum()) == 0.0
+        assert gate[row, :F_ - 1].sum() == 0 and bool((gate[row, F_ - 1:] == 1).all())
+        assert int(out_len[row]) == F_ and torch.equal(emo[row], items[o][3])
+    assert TextMelCollate(5, pin_memory=False)(items)[2].shape[-1] == 45

@@ -161,6 +161,27 @@ def test_oracle_discriminator_matches_reference_golden():
     assert _check_grads(z, grads) == 11
 
 
+def test_oracle_linear_discriminator_matches_reference_golden():
+    """LinearDiscriminator.adversarial_loss (model.py:567-583), windows drawn with the seeded module-level `random`."""
+    import random
+    z = _load("lin_disc_vanilla")
+    hp = HParams("use_noise=True,use_labels=False")
+    d = O.Dims.from_hparams(hp)
+    import gantron_b200.model as M
+    shapes = {k: tuple(v.shape) for k, v in M.LinearDiscriminator(hp).state_dict().items()}
+    sd = {k: v.clone().requires_grad_(True) for k, v in O.seeded_state_dict(shapes, seed=int(z["wseed"])).items()}
+    keeps = unpack_masks(z)
+    assert len(keeps) == 3 and keeps[0].shape[0] == int(z["out/rows"])
+    mel = torch.from_numpy(z["in/mel"]).requires_grad_(True)
+    random.seed(int(z["pyseed"]))
+    loss = O.linear_adversarial_loss(sd, mel, torch.from_numpy(z["in/lengths"]), d, keeps)
+    _close(loss, z["out/loss"], "loss", atol=1e-7, rtol=1e-4)
+    loss.backward()
+    grads = {k: v.grad for k, v in sd.items()}
+    grads["mel"] = mel.grad
+    assert _check_grads(z, grads) == 9
+
+
 def test_state_dict_contract_matches_reference_golden():
     """The drop-in boundary: gantron_b200.model has exactly the reference's state_dict keys and shapes
     (strict load_state_dict of reference checkpoints, train.py:139,147; hparams.ignore_layers names)."""

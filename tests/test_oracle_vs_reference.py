@@ -44,3 +44,34 @@ def test_drop_in_surface_matches_live_reference():
                     obj_r, obj_o = getattr(obj_r, part), getattr(obj_o, part)
         # reference HParams objects are accepted as-is (duck typing)
         M.Tacotron2(ref.hparams.HParams("use_noise=True,use_labels=False"))
+
+
+def _items(n, seed, labelled):
+    g = torch.Generator().manual_seed(seed)
+    items = []
+    for i in range(n):
+        L = int(torch.randint(3, 40, (1,), generator=g))
+        F_ = int(torch.randint(21, 90, (1,), generator=g))
+        it = [torch.randint(1, 100, (L,), generator=g), torch.randn(80, F_, generator=g)]
+        if labelled:
+            it += [float(i % 3), torch.rand(5, generator=g)]
+        items.append(it)
+    return items
+
+
+@pytest.mark.parametrize("labelled", [False, True])
+@pytest.mark.parametrize("step", [1, 3])
+def test_collate_matches_live_reference(labelled, step):
+    """gantron_b200.data_utils.TextMelCollate against data_utils.py:82-131 on the same items."""
+    from gantron_b200.data_utils import TextMelCollate
+    items = _items(7, 5 + step, labelled)
+    with RL.reference_modules(), RL.cpu_shims():
+        import data_utils as ref_du
+        want = ref_du.TextMelCollate(step)(items)
+    got = TextMelCollate(step, pin_memory=False)(items)
+    names = ("text", "input_lengths", "mel", "gate", "speaker", "emotions", "output_lengths")
+    for name, a, b in zip(names, got, want):
+        if not labelled and name in ("speaker", "emotions"):
+            continue                                   # uninitialised in the reference without labels
+        assert a.dtype == b.dtype and a.shape == b.shape, name
+        assert torch.equal(a, b), name
