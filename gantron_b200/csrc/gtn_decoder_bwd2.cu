@@ -824,7 +824,7 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& s
           const float h0 = __uint_as_float(hp << 16), h1 = __uint_as_float(hp & 0xFFFF0000u);
           if (FULL.value || k0 + r < TILE_M / 8) {
             *reinterpret_cast<uint32_t*>(hi + r * 1024) = hp;
-            *reinterpret_cast<uint32_t*>(lo + r * 1024) = pack_bf16x2(d0 - h0, d1 - h1);
+            if (F32) *reinterpret_cast<uint32_t*>(lo + r * 1024) = pack_bf16x2(d0 - h0, d1 - h1);
           }
         }
       };
@@ -853,7 +853,7 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& s
             for (int r = 0; r < RW; ++r) {
               if (k0 + r < TILE_M / 8) {
                 *reinterpret_cast<uint32_t*>(hi + r * 1024) = 0u;
-                *reinterpret_cast<uint32_t*>(lo + r * 1024) = 0u;
+                if (F32) *reinterpret_cast<uint32_t*>(lo + r * 1024) = 0u;
               }
             }
           }
@@ -900,7 +900,10 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& s
       const uint32_t b_hi = smem_u32(im_hi), b_lo = smem_u32(im_lo);
       if (elect_one()) {
 #pragma unroll
+        // bf16 mode: dth enters as ONE bf16 plane (like every other gradient operand of the mode: the gate gradients of P1, the
+        // deferred weight-gradient GEMMs); the filter / im2col operands keep their residual planes.  fp32 mode: three products.
         for (int pl = 0; pl < 3; ++pl) {             // (dth_hi, U_hi), (dth_lo, U_hi), (dth_hi, U_lo)
+          if (!F32 && pl == 1) continue;
           const uint32_t abase = pl == 1 ? a_lo : a_hi;
           const uint32_t bbase = uts + (pl == 2 ? 2u * 8192u : 0u);
 #pragma unroll
@@ -914,6 +917,7 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& s
         umma_commit(sm.g_full);
 #pragma unroll
         for (int pl = 0; pl < 3; ++pl) {             // (dth_hi, im_hi), (dth_lo, im_hi), (dth_hi, im_lo)
+          if (!F32 && pl == 1) continue;
           const uint32_t abase = pl == 1 ? a_lo : a_hi;
           const uint32_t bbase = pl == 2 ? b_lo : b_hi;
 #pragma unroll

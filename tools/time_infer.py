@@ -49,3 +49,26 @@ if os.environ.get("GTN_PROF"):
         print(f"   {n:40s} {v:8d}  (+{v - prev})")
         prev = v
     print(f"   next frame start                         {int(pr[t + 1, 0] - pr[t, 0]):8d}")
+
+# ---- per-phase clock64() profile of CTA 0 of the general kernel (decoder_fwd2_kernel, inference) at B = 64 / 256 ----
+if os.environ.get("GTN_PROF2"):
+    os.environ["GANTRON_B200_INFER1"] = "0"
+    order = [(28, "frame start (prenet 1 GEMM)"), (29, "prenet 1 done"), (30, "barrier"), (31, "prenet 2 done"), (0, "barrier; att LSTM start"),
+             (4, "att LSTM done"), (5, "barrier"), (24, "attn: q / im2col / MMA issued"), (25, "attn: energies"), (27, "attn: softmax"),
+             (6, "attention done"), (8, "barrier"), (13, "dec LSTM done"), (18, "barrier"), (19, "projection + gate done"), (23, "barrier")]
+    for B in (64, 256):
+        pf = torch.zeros(16 * 32, dtype=torch.int64, device="cuda")
+        decoder_ops.PROF_BUFFER = pf
+        mem = torch.cat((torch.randn(B, 150, 512).cuda() * 0.5, torch.rand(B, 1, 512).repeat_interleave(150, 1).cuda()), -1)
+        decoder_ops.decoder_inference(dec, mem, max_steps=16, gate_threshold=0.5, seed=7, prec=1, const_tail=True, ignore_stop=True)
+        torch.cuda.synchronize()
+        decoder_ops.PROF_BUFFER = None
+        pr = pf.cpu().view(16, 32)
+        t = 8
+        print(f"--- decoder_fwd2_kernel inference B={B}: cycles since frame start (frame slot {t})")
+        prev = 0
+        for sl, n in order:
+            v = int(pr[t, sl] - pr[t, 28])
+            print(f"   {n:40s} {v:8d}  (+{v - prev})")
+            prev = v
+        print(f"   next frame start                         {int(pr[t + 1, 28] - pr[t, 28]):8d}")
