@@ -244,13 +244,10 @@ GTN_DEVICE void cell_apply(const DecBwd2& p, const CellIn& in, int t, int b, int
 // Two ADJACENT units (unit even) at once: in bf16 mode the eight bf16 saves / GEMM operands of the pair go out as four + four
 // 32-bit stores instead of sixteen 16-bit ones, and the carried dc as one float2.
 struct CellGrad { float dgi, dgf, dgg, dgo, dcn; };
+// bits: the element's 32 random bits (the caller draws one Philox block for the pair of adjacent units)
 template <bool F32>
-GTN_DEVICE CellGrad cell_math(const DecBwd2& p, const CellIn& in, int t, size_t ci, float dh, unsigned site, unsigned thr,
-                              float pdrop) {
-  if (p.use_dropout && thr != 0u) {
-    const uint32_t bits = philox_bits(p.seed, site, (uint32_t)t, (uint32_t)ci);
-    dh = bits >= thr ? dh * (1.0f / (1.0f - pdrop)) : 0.f;
-  }
+GTN_DEVICE CellGrad cell_math(const DecBwd2& p, const CellIn& in, uint32_t bits, float dh, unsigned thr, float pdrop) {
+  if (p.use_dropout && thr != 0u) dh = bits >= thr ? dh * (1.0f / (1.0f - pdrop)) : 0.f;
   const float4 g = in.g;
   const float tc = F32 ? tanh_acc(in.c) : tanh_fast(in.c);
   const float d_o = dh * tc;
@@ -272,7 +269,15 @@ GTN_DEVICE void cell_apply2(const DecBwd2& p, const CellIn (&in)[2], int t, int 
     return;
   }
   const size_t ci = (size_t)b * H + unit;
-  const CellGrad a = cell_math<F32>(p, in[0], t, ci, dh0, site, thr, pdrop), c = cell_math<F32>(p, in[1], t, ci + 1, dh1, site, thr, pdrop);
+  // ci is even, so ci and ci + 1 share one Philox block (element e = component e & 3 of block e >> 2): one draw for the pair
+  uint32_t bits0 = 0u, bits1 = 0u;
+  if (p.use_dropout && thr != 0u) {
+    const uint4 r = philox_bits4(p.seed, site, (uint32_t)t, (uint32_t)(ci >> 2));
+    const bool lo = (ci & 2) == 0;
+    bits0 = lo ? r.x : r.z;
+    bits1 = lo ? r.y : r.w;
+  }
+  const CellGrad a = cell_math<F32>(p, in[0], bits0, dh0, thr, pdrop), c = cell_math<F32>(p, in[1], bits1, dh1, thr, pdrop);
   *reinterpret_cast<float2*>(dc_carry + ci) = make_float2(a.dcn, c.dcn);
   const uint32_t pi = pack_bf16x2(a.dgi, c.dgi), pf = pack_bf16x2(a.dgf, c.dgf), pg = pack_bf16x2(a.dgg, c.dgg),
                  po = pack_bf16x2(a.dgo, c.dgo);
