@@ -66,6 +66,7 @@ SIGNATURES = {
     "gtn_bilstm_backward": (c_i, [c_p, c_p]),
     "gtn_decoder_infer1_ctas": (c_i, []),
     "gtn_decoder_infer1": (c_i, [c_p, c_p]),
+    "gtn_decoder_infer1_static": (c_i, [c_p, c_p]),
     "gtn_decoder_bwd2_grid": (c_i, [c_i, c_i, c_i, c_i]),
     "gtn_decoder_backward2": (c_i, [c_p, c_p]),
 }

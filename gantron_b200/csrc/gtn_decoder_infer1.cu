@@ -485,3 +485,68 @@ extern "C" int gtn_decoder_infer1(const gtn_decoder_infer1_params* hp, void* str
   count_launch();
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------------------------------
+// gtn_decoder_infer1_static: the same decode for callers that cannot allocate device memory (CUDA graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The kernel's cross-CTA workspace (hidden-state exchange, energies, fixed-point sums, barrier counter) lives in
+// ONE file-scope device array of a stated maximum size; every GPU that loads the library holds it (40,704 bytes) until exit.
+// Every call on a device shares the array: it is cleared at the start of each call (the kernel's barrier epochs and sums
+// start at zero), and two calls that overlap on the GPU (different streams) RACE -- serialise them.
+// ------------------------------------------------------------------------------------------------------------------------
+namespace gtn {
+
+static constexpr int I1S_HMAX = GTN_INFER1_STATIC_MAX_H;        // max attention_rnn_dim / decoder_rnn_dim
+static constexpr int I1S_TPMAX = GTN_INFER1_STATIC_MAX_TP;      // max T_in rounded up to 64
+struct Inf1Scratch {                // (the kernel indexes [2][Ha] / [2][Hd] / [2][Tp] densely from each member's start)
+  float h_att[2][I1S_HMAX];
+  float h_dec[2][I1S_HMAX];
+  float e[2][I1S_TPMAX];
+  long long qacc[2][128];
+  long long macc[2][96];
+  unsigned int barrier[64];
+};
+static __device__ __align__(256) unsigned char g_infer1_scratch[sizeof(Inf1Scratch)];
+
+// The array's NAME is a host-side stand-in in host code, not a device address: its address on the CURRENT device comes from
+// cudaGetSymbolAddress, once per device.
+static int infer1_scratch_ptr(Inf1Scratch** out) {
+  static void* ptrs[64] = {};
+  int dev = 0;
+  GTN_CUDA_OK(cudaGetDevice(&dev));
+  GTN_REQUIRE(dev >= 0 && dev < 64, "device ordinal %d out of range", dev);
+  if (ptrs[dev] == nullptr) {
+    void* ptr = nullptr;
+    GTN_CUDA_OK(cudaGetSymbolAddress(&ptr, g_infer1_scratch));
+    GTN_REQUIRE(ptr != nullptr, "cudaGetSymbolAddress returned a null scratch address");
+    ptrs[dev] = ptr;
+  }
+  *out = reinterpret_cast<Inf1Scratch*>(ptrs[dev]);
+  return 0;
+}
+
+}  // namespace gtn
+
+extern "C" int gtn_decoder_infer1_static(const gtn_decoder_infer1_params* hp, void* stream) {
+  using namespace gtn;
+  GTN_REQUIRE(hp != nullptr, "null params");
+  GTN_REQUIRE(hp->Ha >= 1 && hp->Ha <= I1S_HMAX && hp->Hd >= 1 && hp->Hd <= I1S_HMAX,
+              "gtn_decoder_infer1_static: LSTM widths (%d, %d) exceed the static scratch maximum of %d units; use gtn_decoder_infer1",
+              hp->Ha, hp->Hd, I1S_HMAX);
+  GTN_REQUIRE(hp->Tp >= 1 && hp->Tp <= I1S_TPMAX,
+              "gtn_decoder_infer1_static: padded encoder length %d exceeds the static scratch maximum of %d positions; use gtn_decoder_infer1",
+              hp->Tp, I1S_TPMAX);
+  Inf1Scratch* s = nullptr;
+  int rc = infer1_scratch_ptr(&s);
+  if (rc) return rc;
+  // the array keeps the previous call's contents: exchange buffers, sums and the barrier counter must start at zero
+  GTN_CUDA_OK(cudaMemsetAsync(s, 0, sizeof(Inf1Scratch), (cudaStream_t)stream));
+  gtn_decoder_infer1_params q = *hp;
+  q.h_att_g = &s->h_att[0][0];
+  q.h_dec_g = &s->h_dec[0][0];
+  q.e_g = &s->e[0][0];
+  q.qacc = &s->qacc[0][0];
+  q.macc = &s->macc[0][0];
+  q.barrier = &s->barrier[0];
+  return gtn_decoder_infer1(&q, stream);
+}

@@ -269,6 +269,20 @@ typedef struct gtn_decoder_infer1_params {
 int gtn_decoder_infer1_ctas(void);        /* CTAs (= SMs) gtn_decoder_infer1 launches, or -1 */
 int gtn_decoder_infer1(const gtn_decoder_infer1_params* params, void* stream);
 
+/* gtn_decoder_infer1 for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  It has NO counterpart in the reference.
+ * The workspace members of `params` (h_att_g, h_dec_g, e_g, qacc, macc, barrier) are IGNORED (may be NULL): the
+ * kernel's cross-CTA workspace lives in one file-scope `static __device__` array inside the library (40,704 bytes on every GPU that
+ * loads the library, held until exit), whose address is taken once per device with cudaGetSymbolAddress.  The caller still
+ * passes every input and output.  Limits: Ha, Hd <= GTN_INFER1_STATIC_MAX_H and Tp <= GTN_INFER1_STATIC_MAX_TP, larger sizes
+ * are rejected with an error (use gtn_decoder_infer1).  The call allocates nothing (no cudaMalloc / cudaFree): one
+ * cudaMemsetAsync of the array on `stream` (sums, exchange buffers and the barrier counter must start at zero; the array
+ * keeps the previous call's contents), then the launch.  Every call on a device shares the array: calls that overlap on the
+ * GPU (different streams, or a second process thread) RACE -- serialise them on one stream. */
+#define GTN_INFER1_STATIC_MAX_H 2048
+#define GTN_INFER1_STATIC_MAX_TP 512
+int gtn_decoder_infer1_static(const gtn_decoder_infer1_params* params, void* stream);
+
 /* ---- persistent clustered decoder, backward through time (gtn_decoder_bwd2.cu) --------------------
  * Counterpart of gtn_decoder_forward2 (same cluster-split tcgen05 GEMM engine).  Per frame t = T-1 .. 0:
  *   P1  dX_dec = W_dec^T dGates_dec(t) (rows [h_att | ctx_enc | h_dec]) and dX_att = W_att^T dGates_att(t+1)
