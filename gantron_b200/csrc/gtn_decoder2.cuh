@@ -176,6 +176,7 @@ struct GemmJob {
   XSeg seg[3];
   int res_n = 0;          // leading k-blocks of THIS CTA's K range whose weights are resident in TMEM (no W load)
   int res_slot0 = 0;      // first resident slot
+  int x_row0 = 0;         // first activation row (batch index) of the tile: batch-chunked phases load 64-row boxes
 };
 
 // ---- TMEM-resident weight k-blocks -------------------------------------------------------------------------------
@@ -271,7 +272,7 @@ GTN_DEVICE bool gemm_issue(const GemmJob& job, Ring& rg, uint32_t tmem_acc, uint
     int xz = job.seg[si].z, xn = job.seg[si].nkb;
     // every lane of every producer warp advances the cursor; one elected lane of the stage's warp issues
     auto load_x = [&](bool mine, uint8_t* dst, uint64_t* bar) {
-      if (mine && elect_one()) tma_load_3d(dst, xmap, bar, kk * KB, 0, xz);
+      if (mine && elect_one()) tma_load_3d(dst, xmap, bar, kk * KB, job.x_row0, xz);
       ++kk;
       while (si < job.nseg - 1 && kk >= xn) { kk -= xn; ++si; xmap = job.seg[si].map; xz = job.seg[si].z; xn = job.seg[si].nkb; }
     };

@@ -17,6 +17,7 @@ struct Fwd2Maps {
   CUtensorMap w_att, w_dec, w_pre1, w_pre2, w_proj, uloc;
   CUtensorMap pre, ctx, ha, hd, xmel, xp1, xp2;
   CUtensorMap qpart;      // fp32 [Ha/32][B][A] partial attention queries (pipelined training kernel: one box per sequence)
+  CUtensorMap xmel_c, xp1_c, hd_c, ctx_c;   // 64-row boxes of the same buffers (batch-chunked prenet / projection phases, B > 64)
 };
 
 static constexpr int JH_MAX = 128;     // encoder positions per CTA of a pair (T_in <= 256)

@@ -136,11 +136,75 @@ GTN_DEVICE int make_job(const DecFwd& p, const Fwd2Maps& maps, int kind, int t, 
   return ntiles;
 }
 
+// Prenet layers and mel / gate projection of autoregressive inference at B > 64, BATCH-CHUNKED: these phases have only 2
+// (prenet: 256 rows) and 1 (projection: 81 rows) row tiles, so with one tile per cluster 30 / 31 of the 32 clusters idle while
+// one cluster streams a 128 x 256 tile (28k / 54k cycles per phase at B = 256).  Here a work item is (row tile, 64 sequences):
+// MMA N = 64 on 64-row boxes of the same activation buffers, one split-K exchange and one 128 x 16 epilogue per CTA and item.
+// The stop decision moves behind the phase's grid barrier (every CTA evaluates done[] itself, see the main loop).
+GTN_DEVICE void gemm_phase_chunked(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int kind, int t, int rank, int cid, int ncl,
+                                   uint32_t tmem_base, uint32_t& acc_par, uint32_t& round, float* recv_base) {
+  constexpr int CH = 64, NC4 = CH / 4;
+  const int mult = p.mult;
+  GemmJob job;
+  const int ntiles = make_job(p, maps, kind, t, job);
+  for (int i = 0; i < job.nseg; ++i) {
+    const CUtensorMap* mp = job.seg[i].map;
+    job.seg[i].map = mp == &maps.xmel ? &maps.xmel_c : (mp == &maps.xp1 ? &maps.xp1_c : (mp == &maps.hd ? &maps.hd_c : &maps.ctx_c));
+  }
+  job.res_n = 0;
+  const int nch = (p.B + CH - 1) / CH;
+  const int rows = kind == K_PROJ ? p.NM + 1 : p.P;
+  for (int item = cid; item < ntiles * nch; item += ncl) {
+    const int tile = item / nch, chunk = item - tile * nch;
+    job.row0 = tile * TILE_M;
+    job.x_row0 = chunk * CH;
+    const bool has_work = gemm_issue<CH>(job, sm.ring, tmem_base, sm.acc_full, rank, tmem_base);
+    __syncwarp();
+    if ((threadIdx.x >> 5) >= 4 && has_work) {
+      wait_bar(sm.acc_full, acc_par);
+      tc_fence_after();
+    }
+    if (has_work) acc_par ^= 1u;
+    float* recv = recv_base + (size_t)(round & 1u) * 4 * TILE_M * NC4;
+    const uint32_t xr = round;
+    ++round;
+    float* stage = recv_base + (size_t)((xr & 1u) ^ 1u) * 4 * TILE_M * NC4;
+    exchange_bulk<CH>(has_work, tmem_base, 0, recv, stage, &sm.recv_full[xr & 1u], (xr >> 1) & 1u, rank);
+    const int bbase = chunk * CH + rank * NC4;
+    for (int idx = threadIdx.x; idx < TILE_M * NC4; idx += blockDim.x) {
+      const int bl = idx % NC4, r = idx / NC4, b = bbase + bl, row = tile * TILE_M + r;
+      if (b >= p.B || row >= rows) continue;
+      float val = recv_sum<NC4, true>(recv, r, bl);
+      if (kind != K_PROJ) {
+        val = fmaxf(val, 0.f);
+        const uint32_t bits = philox_bits(p.seed, kind == K_PRE1 ? 1u : 2u, (uint32_t)t, (uint32_t)(b * p.P + row));
+        val = bits >= 0x80000000u ? val * 2.0f : 0.f;     // p = 0.5, always on (model.py:104)
+        store_act((kind == K_PRE1 ? BFP(p.xp1) : BFP(p.xp2)) + (size_t)b * mult * p.Pp, row, p.Pp, p.prec, val);
+      } else {
+        val += p.pbias[(size_t)b * (p.NM + 1) + row];
+        if (row < p.NM) {
+          p.mel_out[((size_t)b * p.NM + row) * p.n_steps + t] = val;
+          store_act(BFP(p.xmel) + (size_t)b * mult * p.NMp, row, p.NMp, p.prec, val);
+        } else {
+          p.gate_out[(size_t)b * p.n_steps + t] = val;
+          if (sigmoid_acc(val) > p.gate_threshold && p.done[b] == 0) { p.done[b] = 1; p.lengths_out[b] = t + 1; }
+        }
+      }
+    }
+  }
+}
+
 template <int N>
 GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int kind, int t, int rank, int cid, int ncl,
                            uint32_t tmem_base, uint32_t& acc_par, uint32_t& round, float (&wqr)[32]) {
   constexpr int CH = N < 64 ? N : 64;
   constexpr int NC4 = CH / 4;
+  if constexpr (N > 64) {
+    if (kind != K_ATT && kind != K_DEC) {
+      gemm_phase_chunked(p, maps, sm, kind, t, rank, cid, ncl, tmem_base, acc_par, round, sm.recv);
+      return;
+    }
+  }
   const int mult = p.mult, cur = t & 1, nxt = cur ^ 1;
   GemmJob job;
   const int ntiles = make_job(p, maps, kind, t, job);
@@ -761,7 +825,20 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
         grid_sync2(p.barrier, epoch, nblocks);
         PROF(8);
       }
-      if (kind == K_PROJ && __ldcg(p.stop) != 0) stopped = true;
+      if (kind == K_PROJ) {
+        if constexpr (N > 64) {
+          // batch-chunked projection: done[] was written by several clusters before the barrier above; every CTA decides
+          int all = 1;
+          for (int b = threadIdx.x; b < p.B; b += blockDim.x) all &= (__ldcg(&p.done[b]) != 0);
+          all = __syncthreads_and(all);
+          if (all && !p.ignore_stop) {
+            stopped = true;
+            if (blockIdx.x == 0 && threadIdx.x == 0) *p.stop = 1;
+          }
+        } else if (__ldcg(p.stop) != 0) {
+          stopped = true;
+        }
+      }
     }
   }
   if (blockIdx.x == 0 && threadIdx.x == 0 && p.steps_done) *p.steps_done = t;
@@ -862,6 +939,13 @@ extern "C" int gtn_decoder_forward2(const gtn_decoder_fwd_params* hp, void* stre
     rc |= make_tma_map_3d(&maps.xp2, p.xp2, (long long)m * p.Pp, p.B, 1, (long long)m * p.Pp, 0, N);
     maps.pre = maps.xp2;
     maps.qpart = maps.ctx;
+  }
+  maps.xmel_c = maps.xmel; maps.xp1_c = maps.xp1; maps.hd_c = maps.hd; maps.ctx_c = maps.ctx;
+  if (!p.train && N > 64) {
+    rc |= make_tma_map_3d(&maps.xmel_c, p.xmel, (long long)m * p.NMp, p.B, 1, (long long)m * p.NMp, 0, 64);
+    rc |= make_tma_map_3d(&maps.xp1_c, p.xp1, (long long)m * p.Pp, p.B, 1, (long long)m * p.Pp, 0, 64);
+    rc |= make_tma_map_3d(&maps.hd_c, p.xh_d, (long long)m * p.Hdp, p.B, 2, (long long)m * p.Hdp, (long long)p.B * m * p.Hdp, 64);
+    rc |= make_tma_map_3d(&maps.ctx_c, p.xctx, (long long)m * p.Ep, p.B, 2, (long long)m * p.Ep, (long long)p.B * m * p.Ep, 64);
   }
   if (rc) return rc;
   const int want = (p.Ha > p.Hd ? p.Ha : p.Hd) / 32;
