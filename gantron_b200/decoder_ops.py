@@ -573,8 +573,12 @@ class _DecoderTrainFn(torch.autograd.Function):
         # ---- deferred mel/gate projection over all frames (model.py:411-416): batched over b so the output is
         # written directly as [B][T][n_mel+1] (channels-last); the API tensors are views of it
         n_out = d.n_mel + 1
-        hd = sv["h_d_buf"][1:]            # [T][B][Hd]
-        cx = sv["ctx_buf"][1:]            # [T][B][D]
+        # bf16 mode: the hidden-state and context saves are converted ONCE here, for the projection now and for the deferred
+        # weight-gradient GEMMs of the backward pass
+        hd_b = sv["h_d_buf"].to(BF16) if prec == 1 else None
+        cx_b = sv["ctx_buf"].to(BF16) if prec == 1 else None
+        hd = (hd_b if prec == 1 else sv["h_d_buf"])[1:]            # [T][B][Hd]
+        cx = (cx_b if prec == 1 else sv["ctx_buf"])[1:]            # [T][B][D]
         out_cl = torch.empty(B, T, n_out, device=dev)
         wpg = torch.cat((params[8].detach().float(), params[10].detach().float()), 0)
         bpg = pk.b_proj
@@ -587,7 +591,7 @@ class _DecoderTrainFn(torch.autograd.Function):
         ctx.dec, ctx.seed, ctx.training = dec, seed, training
         ctx.dims = (B, Tin, D, T, E, prec)
         ctx.saved = dict(sv=sv, frames2=frames2, h1=h1, pre=pre, memory_f=memory_f, mem_enc=mem_enc, mem_const=mem_const,
-                         lengths=lengths, out_cl=out_cl)
+                         lengths=lengths, out_cl=out_cl, hd_b=hd_b, cx_b=cx_b)
         return mel, gate, align
 
     @staticmethod
@@ -623,7 +627,9 @@ class _DecoderTrainFn(torch.autograd.Function):
         pre_T = S["pre"][:TB]                                   # prenet outputs of frames 0..T-1
         bf = (lambda x: x.to(BF16)) if prec == 1 else (lambda x: x)    # bf16 mode: every GEMM operand is converted ONCE
         dga_o, dgd_o, dout_o = bf(dga), bf(dgd), bf(dout2)
-        ha_o, hd_o, cx_o = bf(sv["h_a_buf"]), bf(sv["h_d_buf"]), bf(sv["ctx_buf"])
+        ha_o = bf(sv["h_a_buf"])
+        hd_o = S["hd_b"] if S.get("hd_b") is not None else bf(sv["h_d_buf"])
+        cx_o = S["cx_b"] if S.get("cx_b") is not None else bf(sv["ctx_buf"])
         h_a_prev, h_a_cur = ha_o[:T].reshape(TB, -1), ha_o[1:].reshape(TB, -1)
         h_d_prev, h_d_cur = hd_o[:T].reshape(TB, -1), hd_o[1:].reshape(TB, -1)
         ctx_prev, ctx_cur = cx_o[:T].reshape(TB, -1), cx_o[1:].reshape(TB, -1)
@@ -654,13 +660,17 @@ class _DecoderTrainFn(torch.autograd.Function):
         g_wq = torch.empty(d.att_dim, Ha, device=dev)
         _wgrad_tn(wk["dq_all"].reshape(TB, -1), h_a_cur, g_wq, prec)
         # prenet backward (relu + always-on dropout: y = relu(x) * keep * 2  =>  dx = dy * 2 * [y > 0])
-        d2 = wk["dpre_all"].reshape(TB, P) * 2.0 * (pre_T > 0)
+        # The factors 2 (exact in floating point) are applied to the small weight-gradient matrices instead of the [TB][P]
+        # activations: one masked copy per layer instead of a compare, two multiplies and two conversions; same bits.
+        tb = torch.ops.aten.threshold_backward
+        d2 = bf(tb(wk["dpre_all"].reshape(TB, P), pre_T, 0.0))                    # = true d2 / 2
         g_w_pre2 = torch.empty(P, P, device=dev)
         _wgrad_tn(d2, S["h1"][:TB], g_w_pre2, prec)
-        dh1 = linear_nt(d2, pb.w2T, prec)
-        d1 = dh1 * 2.0 * (S["h1"][:TB] > 0)
+        g_w_pre2.mul_(2.0)
+        d1 = bf(tb(linear_nt(d2, pb.w2T, prec), S["h1"][:TB], 0.0))               # = true d1 / 4
         g_w_pre1 = torch.empty(P, d.n_mel, device=dev)
         _wgrad_tn(d1, S["frames2"][:TB], g_w_pre1, prec)
+        g_w_pre1.mul_(4.0)
         # memory layer and memory gradients
         dpm2 = wk["dpm"].reshape(B * Tin, d.att_dim)
         mem2 = S["memory_f"].reshape(B * Tin, D)
