@@ -260,24 +260,30 @@ GTN_DEVICE CellGrad cell_math(const DecBwd2& p, const CellIn& in, uint32_t bits,
   r.dgo = d_o * g.w * (1.f - g.w);
   return r;
 }
+GTN_DEVICE uint2 cell_pair_bits(const DecBwd2& p, int t, int b, int unit, int H, unsigned site, unsigned thr) {
+  // ci is even, so ci and ci + 1 share one Philox block (element e = component e & 3 of block e >> 2): one draw for the pair
+  const size_t ci = (size_t)b * H + unit;
+  uint2 bits = make_uint2(0u, 0u);
+  if (p.use_dropout && thr != 0u) {
+    const uint4 r = philox_bits4(p.seed, site, (uint32_t)t, (uint32_t)(ci >> 2));
+    const bool lo = (ci & 2) == 0;
+    bits = make_uint2(lo ? r.x : r.z, lo ? r.y : r.w);
+  }
+  return bits;
+}
+// pre: the pair's dropout bits drawn earlier by the caller (cell_pair_bits; bf16 mode only), or nullptr
 template <bool F32>
 GTN_DEVICE void cell_apply2(const DecBwd2& p, const CellIn (&in)[2], int t, int b, int unit, int H, float dh0, float dh1,
-                            float* dc_carry, float* dg_all, bf16* xdg, unsigned site, unsigned thr, float pdrop) {
+                            float* dc_carry, float* dg_all, bf16* xdg, unsigned site, unsigned thr, float pdrop,
+                            const uint2* pre = nullptr) {
   if (F32) {                                      // fp32 mode: per-unit path (three planes per operand)
     cell_apply<F32>(p, in[0], t, b, unit, H, dh0, dc_carry, dg_all, xdg, site, thr, pdrop);
     cell_apply<F32>(p, in[1], t, b, unit + 1, H, dh1, dc_carry, dg_all, xdg, site, thr, pdrop);
     return;
   }
   const size_t ci = (size_t)b * H + unit;
-  // ci is even, so ci and ci + 1 share one Philox block (element e = component e & 3 of block e >> 2): one draw for the pair
-  uint32_t bits0 = 0u, bits1 = 0u;
-  if (p.use_dropout && thr != 0u) {
-    const uint4 r = philox_bits4(p.seed, site, (uint32_t)t, (uint32_t)(ci >> 2));
-    const bool lo = (ci & 2) == 0;
-    bits0 = lo ? r.x : r.z;
-    bits1 = lo ? r.y : r.w;
-  }
-  const CellGrad a = cell_math<F32>(p, in[0], bits0, dh0, thr, pdrop), c = cell_math<F32>(p, in[1], bits1, dh1, thr, pdrop);
+  const uint2 bits = pre != nullptr ? *pre : cell_pair_bits(p, t, b, unit, H, site, thr);
+  const CellGrad a = cell_math<F32>(p, in[0], bits.x, dh0, thr, pdrop), c = cell_math<F32>(p, in[1], bits.y, dh1, thr, pdrop);
   *reinterpret_cast<float2*>(dc_carry + ci) = make_float2(a.dcn, c.dcn);
   const uint32_t pi = pack_bf16x2(a.dgi, c.dgi), pf = pack_bf16x2(a.dgf, c.dgf), pg = pack_bf16x2(a.dgg, c.dgg),
                  po = pack_bf16x2(a.dgo, c.dgo);
@@ -439,6 +445,12 @@ GTN_DEVICE void quad_cells(const DecBwd2& p, const float* dq2, float* part, int 
     QuadOps o;
     if (rd == 0 && pre != nullptr) o = *pre;
     else quad_cells_load(p, t, b0, b1, rank, rd, o);
+    // the cells' dropout bits depend on (seed, site, frame, element) only: drawn here, in the shadow of the Wq tile's arrival
+    uint2 bits_a = make_uint2(0u, 0u), bits_d = make_uint2(0u, 0u);
+    if (!F32) {
+      if (oka) bits_a = cell_pair_bits(p, t, b, ua, p.Ha, 3u, p.thr_att);
+      if (okd) bits_d = cell_pair_bits(p, t - 1, b, ud, p.Hd, 4u, p.thr_dec);
+    }
     // Wq^T dq over this thread's half of the attention dimension, for both sequences
     float s00 = 0.f, s01 = 0.f, s10 = 0.f, s11 = 0.f;                // [sequence][unit of the pair]
     if (!F32 && wq_s != nullptr) {
@@ -495,10 +507,12 @@ GTN_DEVICE void quad_cells(const DecBwd2& p, const float* dq2, float* part, int 
     const float s0 = h0.x + h1.x, s1 = h0.y + h1.y;                  // sequence h, units ua, ua + 1
     PROFB(26);
     if (okd) {
-      cell_apply2<F32>(p, o.cd, t - 1, b, ud, p.Hd, o.addd.x, o.addd.y, p.dc_d, p.dgd_all, xnext_d, 4u, p.thr_dec, p.p_dec);
+      cell_apply2<F32>(p, o.cd, t - 1, b, ud, p.Hd, o.addd.x, o.addd.y, p.dc_d, p.dgd_all, xnext_d, 4u, p.thr_dec, p.p_dec,
+                       F32 ? nullptr : &bits_d);
     }
     if (oka) {
-      cell_apply2<F32>(p, o.ca, t, b, ua, p.Ha, s0 + o.adda.x, s1 + o.adda.y, p.dc_a, p.dga_all, BFP(p.xdg_a), 3u, p.thr_att, p.p_att);
+      cell_apply2<F32>(p, o.ca, t, b, ua, p.Ha, s0 + o.adda.x, s1 + o.adda.y, p.dc_a, p.dga_all, BFP(p.xdg_a), 3u, p.thr_att, p.p_att,
+                       F32 ? nullptr : &bits_a);
     }
   }
 }

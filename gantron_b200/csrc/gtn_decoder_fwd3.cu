@@ -349,6 +349,21 @@ GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int 
   const int nxt = (tc & 1) ^ 1;
   const int H = IS_ATT ? p.Ha : p.Hd, Hp = IS_ATT ? p.Hap : p.Hdp;
   const int t = tc;                                  // (PROF3)
+  const float pdrop = IS_ATT ? p.p_att : p.p_dec;
+  const unsigned thr = IS_ATT ? p.thr_att : p.thr_dec;
+  const float dscale = 1.0f / (1.0f - pdrop);
+  const unsigned site = IS_ATT ? 3u : 4u;
+  // the dropout bits of this thread's cells depend on (seed, site, frame, element) only: drawn BEFORE the wait for the
+  // accumulator (the workers idle ~2k cycles there while the late k-blocks land) instead of ~70 dependent instructions per cell
+  // behind the exchange
+  uint32_t dbits[CPT];
+#pragma unroll
+  for (int q = 0; q < CPT; ++q) {
+    const int idx = threadIdx.x + q * 256;
+    const int ul = idx & 31, bl = idx >> 5, b = rank * NC4 + bl, unit = tile * 32 + ul;
+    dbits[q] = 0xFFFFFFFFu;
+    if (b < p.B && p.use_dropout && thr != 0u) dbits[q] = philox_bits(p.seed, site, (uint32_t)tc, (uint32_t)((size_t)b * H + unit));
+  }
   if ((threadIdx.x >> 5) >= 4 && has_work) {
     wait_bar(acc_full, acc_par);
     tc_fence_after();
@@ -380,10 +395,6 @@ GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int 
     exchange_bulk<CH, true>(has_work, tmem_acc, 0, recv, stage, &sm.recv_full[xr & 1u], (xr >> 1) & 1u, rank);
   }
   PROF3(IS_ATT ? 3 : 11);
-  const float pdrop = IS_ATT ? p.p_att : p.p_dec;
-  const unsigned thr = IS_ATT ? p.thr_att : p.thr_dec;
-  const float dscale = 1.0f / (1.0f - pdrop);
-  const unsigned site = IS_ATT ? 3u : 4u;
   bf16* xh_next = (IS_ATT ? BFP(p.xh_a) : BFP(p.xh_d)) + (size_t)nxt * p.B * mult * Hp;
   float* gates_all = IS_ATT ? p.gates_a : p.gates_d;
   float* c_all = IS_ATT ? p.c_a_all : p.c_d_all;
@@ -405,10 +416,7 @@ GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int 
       const float c_new = f_ * c_reg[q] + i_ * g_;
       c_reg[q] = c_new;
       h = o_ * (fast ? tanh_fast(c_new) : tanh_acc(c_new));
-      if (p.use_dropout && thr != 0u) {
-        const uint32_t bits = philox_bits(p.seed, site, (uint32_t)tc, (uint32_t)ci);
-        h = bits >= thr ? h * dscale : 0.f;
-      }
+      if (p.use_dropout && thr != 0u) h = dbits[q] >= thr ? h * dscale : 0.f;
       store_act(xh_next + (size_t)b * mult * Hp, unit, Hp, PREC, h);
       if (IS_ATT) {
         // the saves for the backward pass are not needed by any other CTA: they are written AFTER this CTA has arrived at
