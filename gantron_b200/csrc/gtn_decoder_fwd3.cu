@@ -334,13 +334,34 @@ GTN_DEVICE void issue_kblocks(const KSched& ks, int i0, int i1, const CUtensorMa
   }
 }
 
+// Dropout bits of this thread's LSTM cells of frame tc (Philox is a function of (seed, site, frame, element) only, so they
+// can be drawn whenever the thread is idle: ~70 dependent instructions per cell).
+template <int N, bool IS_ATT>
+GTN_DEVICE void draw_cell_bits(const DecFwd& p, int tc, int tile, int rank, uint32_t (&bits)[32 * (N < 64 ? N : 64) / 4 / 256]) {
+  constexpr int NC4 = (N < 64 ? N : 64) / 4;
+  constexpr int CPT = 32 * NC4 / 256;
+  const int H = IS_ATT ? p.Ha : p.Hd;
+  const unsigned thr = IS_ATT ? p.thr_att : p.thr_dec;
+#pragma unroll
+  for (int q = 0; q < CPT; ++q) {
+    const int idx = threadIdx.x + q * 256;
+    const int ul = idx & 31, bl = idx >> 5, b = rank * NC4 + bl, unit = tile * 32 + ul;
+    bits[q] = 0xFFFFFFFFu;
+    if (b < p.B && p.use_dropout && thr != 0u)
+      bits[q] = philox_bits(p.seed, IS_ATT ? 3u : 4u, (uint32_t)tc, (uint32_t)((size_t)b * H + unit));
+  }
+}
+
 // ---- LSTM epilogue of one GEMM tile: split-K exchange, cell, dropout, saves, next-frame operand ---------------------------
+// pre_bits: the cells' dropout bits if the caller drew them earlier (draw_cell_bits), else nullptr (drawn here, before the
+// wait for the accumulator).
 // tc = frame index of the cell.  c_reg: this thread's cell states, carried in registers over the whole launch (a thread owns
 // the same (unit, sequence) pairs in every frame).
 template <int N, bool F32, bool IS_ATT>
 GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int rank, bool has_work, uint32_t tmem_acc,
                               uint64_t* acc_full, uint32_t& acc_par, uint32_t& round, float (&c_reg)[32 * (N < 64 ? N : 64) / 4 / 256],
-                              float (&sv)[32 * (N < 64 ? N : 64) / 4 / 256][6]) {
+                              float (&sv)[32 * (N < 64 ? N : 64) / 4 / 256][6],
+                              const uint32_t (*pre_bits)[32 * (N < 64 ? N : 64) / 4 / 256] = nullptr) {
   constexpr int CH = N < 64 ? N : 64;
   constexpr int NC4 = CH / 4;
   constexpr int CPT = 32 * NC4 / 256;
@@ -353,16 +374,14 @@ GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int 
   const unsigned thr = IS_ATT ? p.thr_att : p.thr_dec;
   const float dscale = 1.0f / (1.0f - pdrop);
   const unsigned site = IS_ATT ? 3u : 4u;
-  // the dropout bits of this thread's cells depend on (seed, site, frame, element) only: drawn BEFORE the wait for the
-  // accumulator (the workers idle ~2k cycles there while the late k-blocks land) instead of ~70 dependent instructions per cell
-  // behind the exchange
+  // dropout bits: drawn BEFORE the wait for the accumulator (the workers idle ~2k cycles there while the late k-blocks
+  // land) instead of ~70 dependent instructions per cell behind the exchange -- unless the caller already has them
   uint32_t dbits[CPT];
+  if (pre_bits != nullptr) {
 #pragma unroll
-  for (int q = 0; q < CPT; ++q) {
-    const int idx = threadIdx.x + q * 256;
-    const int ul = idx & 31, bl = idx >> 5, b = rank * NC4 + bl, unit = tile * 32 + ul;
-    dbits[q] = 0xFFFFFFFFu;
-    if (b < p.B && p.use_dropout && thr != 0u) dbits[q] = philox_bits(p.seed, site, (uint32_t)tc, (uint32_t)((size_t)b * H + unit));
+    for (int q = 0; q < CPT; ++q) dbits[q] = (*pre_bits)[q];
+  } else {
+    draw_cell_bits<N, IS_ATT>(p, tc, tile, rank, dbits);
   }
   if ((threadIdx.x >> 5) >= 4 && has_work) {
     wait_bar(acc_full, acc_par);
@@ -879,6 +898,7 @@ decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
     const unsigned int nblocks = gridDim.x;
     uint32_t accA_par = 0, accC_par = 0, att_par = 0, qg_par = 0, round = 0, eround = 0;
     float cA[CPT], cC[CPT], svA[CPT][6];
+    uint32_t bitsC[CPT];              // dropout bits of the decoder LSTM cells of the frame whose epilogue runs next
     float ctx_save = 0.f, wsum = 0.f;
 #pragma unroll
     for (int q = 0; q < CPT; ++q) { cA[q] = 0.f; cC[q] = 0.f; }
@@ -912,7 +932,7 @@ decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
         PROF3(5);
       }
       // ---- W4: decoder LSTM cells of frame t - 1, while the other CTAs arrive at barrier 1
-      if (t > 0) lstm_epilogue<N, F32, false>(p, sm, t - 1, cid, rank, workC, tmem_accC, sm.accC_full, accC_par, round, cC, svA);
+      if (t > 0) lstm_epilogue<N, F32, false>(p, sm, t - 1, cid, rank, workC, tmem_accC, sm.accC_full, accC_par, round, cC, svA, &bitsC);
       if (t == T) break;
       PROF3(12);
       // ---- W6
@@ -936,6 +956,7 @@ decoder_fwd3_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
         tc_fence_after();
         attn_prepare<F32>(p, sm, ac, t + 1, tmem_att, im2col_buf());
       }
+      draw_cell_bits<N, false>(p, t, cid, rank, bitsC);     // for C(t), whose epilogue runs in the shadow of the next barrier 1
       PROF3(13);
       grid_wait(p.barrier, epoch, sm.go_late);
       // the location GEMM is complete (its im2col tiles are in a receive buffer the next exchange stages into)
