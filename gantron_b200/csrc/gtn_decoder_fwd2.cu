@@ -53,7 +53,17 @@ struct Smem2 {
   uint64_t* recv_full;  // [2] bulk-copy exchange: one per receive buffer
   uint32_t* tmem_slot;
   int res_a, res_d;    // weight k-blocks of this CTA's attention / decoder LSTM K quarter that are resident in TMEM
+  // batched attention of autoregressive inference (attention_infer_multi): up to AM sequences per CTA pair at once
+  float* am_wcat;      // [AM][2][JH + KS - 1]
+  float* am_ebuf;      // [AM][Tin_pad]   (the peer CTA writes its half)
+  uint64_t* am_att_full;   // [AM]
+  uint64_t* am_mem_full;   // [3]
 };
+
+// sequences per CTA pair the batched attention holds at once (accumulators: tensor-memory columns 256, 0, 128, 384)
+template <int N>
+__host__ __device__ constexpr int am_max() { return N >= 256 ? 4 : (N >= 128 ? 2 : 1); }
+static constexpr int AM_WCAT = 2 * (JH_MAX + KS_MAX - 1);
 
 template <int N>
 __host__ __device__ constexpr size_t fwd2_fixed_bytes() {
@@ -61,6 +71,7 @@ __host__ __device__ constexpr size_t fwd2_fixed_bytes() {
   return (size_t)2 * W_TILE_BYTES                        // u_s
          + (size_t)2 * 4 * TILE_M * NC4 * 4               // recv
          + (size_t)(NC4 * 32 + 128 + 128 + 2 * (JH_MAX + KS_MAX - 1) + 2 * TIN_MAX + 2 * 128 + TIN_MAX + 8 * 256 + 64) * 4
+         + (size_t)am_max<N>() * (AM_WCAT + TIN_MAX) * 4  // am_wcat, am_ebuf
          + 64 * 8 + 64;                                   // barriers + tmem slot
 }
 
@@ -86,6 +97,8 @@ GTN_DEVICE Smem2 carve2(uint8_t* base, int S) {
   m.w_s = f; f += TIN_MAX;
   m.red_s = f; f += 8 * 256;
   m.scr = f; f += 64;
+  m.am_wcat = f; f += am_max<N>() * AM_WCAT;
+  m.am_ebuf = f; f += am_max<N>() * TIN_MAX;
   uint64_t* b = reinterpret_cast<uint64_t*>(f);
   m.ring.full = b; b += 16;
   m.ring.empty = b; b += 16;
@@ -93,6 +106,8 @@ GTN_DEVICE Smem2 carve2(uint8_t* base, int S) {
   m.att_full = b++;
   m.u_full = b++;
   m.recv_full = b; b += 2;
+  m.am_att_full = b; b += 4;
+  m.am_mem_full = b; b += 3;
   m.tmem_slot = reinterpret_cast<uint32_t*>(b + 1);
   return m;
 }
@@ -489,6 +504,134 @@ GTN_DEVICE void prenet_local(const DecFwd& p, Smem2& sm, int t, int rank) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// "Tail" of a frame of batched autoregressive inference (bf16 mode, B > PRE_LOCAL_BMAX): mel / gate projection of frame t
+// and both prenet layers of frame t + 1 INSIDE each cluster for the cluster's own ceil(B / clusters) <= 8 sequences
+// (model.py:411-416, 486, 97-106).  As three grid-wide GEMM phases these cost three TMA -> tcgen05 -> DSMEM chains and three
+// grid barriers per frame (47k of 221k cycles at B = 256) although they are three small products whose inputs, once
+// h_dec(t) is complete, never leave the sequence.  Here they are warp-level tensor-core products (mma.sync m16n8k16: 16
+// weight rows x the cluster's 8 sequences, fp32 accumulate) with BOTH operands loaded straight from L2 in fragment order
+// -- a lane's 16 bytes of a row are 8 consecutive K elements, used as the k-pairs of two consecutive MMAs; weights and
+// activations use the same permutation of K, so the sum is unchanged -- every load of a warp in flight at once, no shared
+// memory staging.  The four CTAs of a cluster split the 16-row tiles, the warps of a CTA split K (partials summed through
+// shared memory), the layers meet in global memory behind two cluster barriers, and ONE grid barrier follows (xp2 is a
+// TMA operand of every cluster's next GEMM).  A first version with FMA mat-vecs unrolled over rows x sequences was 3x
+// SLOWER than the GEMM phases: 90 KB of straight-line code that runs once per frame is bound by instruction fetch.
+// Same operands as the GEMM path (bf16 weights and activations, fp32 accumulate); only the summation order differs.
+// ------------------------------------------------------------------------------------------------
+static constexpr int TAIL_BMAX = 8;     // sequences per cluster = N of the MMA
+static constexpr int TAIL_UNITS = 16;   // (tile, K part) partial tiles of one layer per CTA (red_s holds 16 x 128 floats)
+
+GTN_DEVICE void mma_bf16_16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// c[16 rows][8 sequences] += sum over K slabs [s0, s1) (32 elements each) of W[row0 + r][k] x[n][k]; rows >= nrows and
+// sequences >= nb contribute zeros.  x[n][k] = k < ksplit ? xa[n * lda + k] : xb[n * ldb + k - ksplit] (bf16, written by other
+// CTAs during this launch: L2 loads).  Fragment owner: g = lane / 4 (row g and g + 8 of A, column g of B), q = lane % 4.
+GTN_DEVICE void tail_mma_rows(float (&c)[4], const bf16* W, int ldw, int row0, int nrows, const bf16* xa, int lda, const bf16* xb,
+                              int ldb, int ksplit, int nb, int s0, int s1) {
+  constexpr int UB = 6;                                    // slabs in flight per lane (18 x 16-byte loads)
+  const int lane = threadIdx.x & 31, g = lane >> 2, q = lane & 3;
+  const bool r0ok = row0 + g < nrows, r1ok = row0 + g + 8 < nrows, nok = g < nb;
+  const bf16* w0 = W + (size_t)(row0 + g) * ldw + 8 * q;
+  const bf16* w1 = w0 + (size_t)8 * ldw;
+  const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll 1
+  for (int sb = s0; sb < s1; sb += UB) {
+    uint4 wa[UB], wb[UB], xv[UB];
+#pragma unroll
+    for (int j = 0; j < UB; ++j) {
+      const int k = (sb + j) * 32;
+      const bool on = sb + j < s1;
+      wa[j] = (on && r0ok) ? __ldg(reinterpret_cast<const uint4*>(w0 + k)) : z4;
+      wb[j] = (on && r1ok) ? __ldg(reinterpret_cast<const uint4*>(w1 + k)) : z4;
+      const bf16* xs = k < ksplit ? xa + (size_t)g * lda + k : xb + (size_t)g * ldb + (k - ksplit);
+      xv[j] = (on && nok) ? __ldcg(reinterpret_cast<const uint4*>(xs + 8 * q)) : z4;
+    }
+#pragma unroll
+    for (int j = 0; j < UB; ++j) {
+      mma_bf16_16816(c, wa[j].x, wb[j].x, wa[j].y, wb[j].y, xv[j].x, xv[j].y);
+      mma_bf16_16816(c, wa[j].z, wb[j].z, wa[j].w, wb[j].w, xv[j].z, xv[j].w);
+    }
+  }
+}
+
+// One layer for this CTA: tiles [tile0, tile0 + ntl) of 16 rows (tile index step tstep between them), K split into KP parts
+// over the warps; partial tiles -> part[unit][16][8] (unit = kp * ntl + tl).  Ends with a CTA barrier.
+GTN_DEVICE void tail_layer(float* part, const bf16* W, int ldw, int nrows, int tile0, int tstep, int ntl, int KP, const bf16* xa,
+                           int lda, const bf16* xb, int ldb, int ksplit, int K, int nb) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, q = lane & 3;
+  const int nsl = K / 32;
+  for (int unit = warp; unit < ntl * KP; unit += 8) {
+    const int tl = unit % ntl, kp = unit / ntl;
+    float c[4] = {0.f, 0.f, 0.f, 0.f};
+    tail_mma_rows(c, W, ldw, (tile0 + tl * tstep) * 16, nrows, xa, lda, xb, ldb, ksplit, nb, kp * nsl / KP, (kp + 1) * nsl / KP);
+    float* d = part + (size_t)unit * 128;
+    *reinterpret_cast<float2*>(d + g * 8 + 2 * q) = make_float2(c[0], c[1]);
+    *reinterpret_cast<float2*>(d + (g + 8) * 8 + 2 * q) = make_float2(c[2], c[3]);
+  }
+  __syncthreads();
+}
+
+// Can the tail run for this configuration?  (bf16 planes only; K segments in 32-element slabs; tile counts within part[])
+GTN_DEVICE bool tail_covers(const DecFwd& p, int nbc) {
+  const int ntp = ((p.P + 15) / 16 + CL - 1) / CL;         // prenet tiles per CTA
+  return p.prec == 1 && nbc <= TAIL_BMAX && (p.NM + 1 + 15) / 16 <= 2 * CL && 2 * ntp <= TAIL_UNITS && p.Hdp % 32 == 0 &&
+         p.Ep % 32 == 0 && p.NMp % 32 == 0 && p.Pp % 32 == 0;
+}
+
+// do_proj: projection + gate test of frame t, then the prenet of frame t + 1 (skipped behind the last frame);
+// !do_proj: only the prenet of frame 0 (go frame, xmel is zero).
+GTN_DEVICE void tail_phase(const DecFwd& p, Smem2& sm, int t, bool do_proj, int rank, int cid, int ncl) {
+  const int nbc = (p.B + ncl - 1) / ncl;
+  const int b0 = cid * nbc;
+  const int nb = min(p.B, b0 + nbc) - b0;
+  if (nb <= 0) return;                                     // (cluster-uniform)
+  const int P = p.P, R = p.NM + 1, Kp = p.Hdp + p.Ep;
+  float* part = sm.red_s;                                  // [TAIL_UNITS][16][8]
+  if (do_proj) {
+    // 16-row tiles rank, rank + 4 of the R = n_mel + 1 rows; K in four parts over the warps
+    const int nt = (R + 15) / 16, ntl = rank + CL < nt ? 2 : (rank < nt ? 1 : 0);
+    tail_layer(part, BFP(p.w_proj), Kp, R, rank, CL, ntl, 4, BFP(p.xh_d) + ((size_t)((t & 1) ^ 1) * p.B + b0) * p.Hdp, p.Hdp,
+               BFP(p.xctx) + (size_t)b0 * p.Ep, p.Ep, p.Hdp, Kp, nb);
+    for (int i = threadIdx.x; i < ntl * 128; i += blockDim.x) {
+      const int tl = i >> 7, r = (i >> 3) & 15, n = i & 7, row = (rank + tl * CL) * 16 + r, b = b0 + n;
+      if (row >= R || n >= nb) continue;
+      float val = p.pbias[(size_t)b * R + row];
+#pragma unroll
+      for (int kp = 0; kp < 4; ++kp) val += part[(size_t)(kp * ntl + tl) * 128 + r * 8 + n];
+      if (row < p.NM) {
+        p.mel_out[((size_t)b * p.NM + row) * p.n_steps + t] = val;
+        BFP(p.xmel)[(size_t)b * p.NMp + row] = __float2bfloat16_rn(val);
+      } else {
+        p.gate_out[(size_t)b * p.n_steps + t] = val;
+        if (sigmoid_acc(val) > p.gate_threshold && p.done[b] == 0) { p.done[b] = 1; p.lengths_out[b] = t + 1; }
+      }
+    }
+    cluster_sync_all();                                    // the row tiles of mel(t) meet in global memory
+    if (t + 1 >= p.n_steps) return;
+  }
+  const int tp = do_proj ? t + 1 : 0;                      // frame the prenet output belongs to (Philox step)
+  const int nt = (P + 15) / 16, tpr = (nt + CL - 1) / CL, tile0 = rank * tpr, ntl = max(0, min(nt, tile0 + tpr) - tile0);
+  for (int layer = 0; layer < 2; ++layer) {
+    const int K = layer == 0 ? p.NMp : p.Pp;
+    const bf16* xin = layer == 0 ? BFP(p.xmel) + (size_t)b0 * p.NMp : BFP(p.xp1) + (size_t)b0 * p.Pp;
+    tail_layer(part, layer == 0 ? BFP(p.w_pre1) : BFP(p.w_pre2), K, P, tile0, 1, ntl, 2, xin, K, xin, K, K, K, nb);
+    bf16* xout = layer == 0 ? BFP(p.xp1) : BFP(p.xp2);
+    for (int i = threadIdx.x; i < ntl * 128; i += blockDim.x) {
+      const int tl = i >> 7, r = (i >> 3) & 15, n = i & 7, row = (tile0 + tl) * 16 + r, b = b0 + n;
+      if (row >= P || n >= nb) continue;
+      float v = fmaxf(part[(size_t)tl * 128 + r * 8 + n] + part[(size_t)(ntl + tl) * 128 + r * 8 + n], 0.f);
+      const uint32_t bits = philox_bits(p.seed, layer == 0 ? 1u : 2u, (uint32_t)tp, (uint32_t)(b * P + row));
+      v = bits >= 0x80000000u ? v * 2.0f : 0.f;            // p = 0.5, always on (model.py:104)
+      xout[(size_t)b * p.Pp + row] = __float2bfloat16_rn(v);
+    }
+    if (layer == 0) cluster_sync_all();                    // layer 2 reads every row of layer 1 (also fences part[])
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // attention phase: one CTA pair per sequence
 // ------------------------------------------------------------------------------------------------
 template <typename MT>
@@ -739,6 +882,320 @@ GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, in
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Attention phase of autoregressive inference, ALL sequences of the CTA pair at once (bf16 memory).  attention_phase2 serves
+// its sequences one after the other, each through a dozen latency-bound stages with CTA / cluster barriers between them, and
+// reads the encoder-memory tile row by row through L1 with four rows per warp in flight (9 B/clk per SM): 22k cycles per
+// sequence, 87k of a 221k-cycle frame at B = 256.  Here every stage runs once for all sequences:
+//   Q  queries (32 partials per element in flight) and [prev | cum] windows of all sequences        1 barrier
+//   I  im2col tiles of all sequences (idle ring / receive buffers)                                   1 barrier
+//   M  location GEMMs of all sequences (one accumulator each); the first encoder-memory chunks are requested
+//   E  energies per sequence as its accumulator completes (next sequence's processed_memory rows prefetched)
+//      pair exchange of all energies through DSMEM                                                   1 cluster barrier
+//   S  masked softmax: one WARP per sequence (shuffles only); weight state, alignments               1 barrier
+//   C  context: a CTA takes its HALF OF THE POSITIONS (a contiguous run of memory rows) for all columns, streamed through
+//      three shared-memory slots by bulk copies (chunks of a third of the rows, issued as slots free up), so the phase is
+//      bound by the SM's L2 port instead of by load latency; partial sums to the column's owner       1 cluster barrier
+//   X  pair sum, context columns written as the next GEMM's operand
+// Same operands as attention_phase2 (hi / lo planes of the window, bf16 memory, fp32 accumulate); the softmax and context
+// sums run in a different order.  (model.py:62-89, 403)
+// ------------------------------------------------------------------------------------------------
+struct AttnMulti {
+  bool on;
+  int nmax;                 // sequences per pair this launch needs
+  int cr;                   // memory rows per chunk
+  uint32_t slot_bytes;
+  uint8_t* slot0;           // [3][slot_bytes]
+  uint8_t *im0, *im1, *im2, *im3;   // im2col tiles, hi plane; the lo plane follows at + plane_bytes (no array: a run-time index
+  uint32_t plane_bytes;             // would put the struct in local memory)
+  GTN_DEVICE uint8_t* im(int it) const { return it == 0 ? im0 : (it == 1 ? im1 : (it == 2 ? im2 : im3)); }
+};
+
+template <int N>
+GTN_DEVICE AttnMulti attn_multi_layout(const DecFwd& p, const Smem2& sm, int S, int ncl) {
+  constexpr int NC4 = (N < 64 ? N : 64) / 4;
+  AttnMulti am;
+  am.nmax = (p.B + 2 * ncl - 1) / (2 * ncl);
+  const int JH = (p.Tin + 1) / 2, rows8 = (JH + 7) & ~7;
+  am.cr = (JH + 2) / 3;
+  am.slot_bytes = (uint32_t)(am.cr * p.E * 2 + 127) & ~127u;
+  am.plane_bytes = (uint32_t)rows8 * 128u;
+  am.slot0 = sm.ring.base;
+  am.on = !p.train && p.mem_bf16 && p.prec == 1 && (p.reserved0 & 2) == 0 && am.nmax <= am_max<N>() && p.E <= 512 && p.E % 8 == 0 &&
+          p.Ha / 32 <= 32;
+  // im2col tiles: behind the memory slots in the ring, then in the receive buffers (both idle during the phase); a tile is
+  // read as 128 rows by the MMA whatever its row count, so 16 KB behind its base must lie inside the CTA's shared memory
+  uint8_t* r1 = sm.ring.base + ((3u * am.slot_bytes + 1023u) & ~1023u);
+  uint8_t* r1_end = sm.ring.base + (size_t)S * sm.ring.stage_bytes;
+  uint8_t* r2 = reinterpret_cast<uint8_t*>(sm.recv);
+  uint8_t* r2_end = r2 + (size_t)2 * 4 * TILE_M * NC4 * 4;
+  auto place = [&](int it) -> uint8_t* {
+    uint8_t* r = nullptr;
+    if (it >= am.nmax) return r;
+    if (r1 + 2 * am.plane_bytes <= r1_end) { r = r1; r1 += 2 * am.plane_bytes; }
+    else if (r2 + 2 * am.plane_bytes <= r2_end) { r = r2; r2 += 2 * am.plane_bytes; }
+    else am.on = false;
+    return r;
+  };
+  am.im0 = place(0); am.im1 = place(1); am.im2 = place(2); am.im3 = place(3);
+  if (3u * am.slot_bytes > (uint32_t)S * sm.ring.stage_bytes) am.on = false;
+  return am;
+}
+
+GTN_DEVICE uint32_t am_tmem_col(int it) { return it == 0 ? 256u : (it == 1 ? 0u : (it == 2 ? 128u : 384u)); }
+
+template <int N>
+GTN_DEVICE void attention_infer_multi(const DecFwd& p, Smem2& sm, const AttnMulti& am, int t, int rank, int cid, int ncl,
+                                      uint32_t tmem_base, uint32_t& att_par, uint32_t& mc) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int Tin = p.Tin, A = p.A, KS = p.KS, hk = (p.KS - 1) / 2, E = p.E;
+  const int half = rank & 1, peer = rank ^ 1;
+  const int pair = cid * 2 + (rank >> 1), npairs = ncl * 2;
+  const int JH = (Tin + 1) / 2;
+  const int j0 = half * JH, jn = min(Tin, j0 + JH) - j0;
+  const int Wd = jn + KS - 1;
+  const bf16* mem = reinterpret_cast<const bf16*>(p.mem_enc);
+  const bf16* pm = reinterpret_cast<const bf16*>(p.pm);
+  int nact = 0;                                            // sequences of this pair (a prefix of the slots)
+  for (int it = 0; it < am.nmax; ++it) nact += (pair + it * npairs) < p.B ? 1 : 0;
+  // (a pair without sequences still walks through the phase: the cluster barriers below are shared with the other pair)
+  float* q_m = sm.hs;                                      // [AM][128]        (idle outside the attention-LSTM epilogue)
+  float* w_m = sm.wcat;                                    // [AM][Tin_pad]    (wcat | e_buf | e_part | w_s of the one-at-a-time path)
+  float* epart = sm.red_s;                                 // [AM][2][128]     (dead before the context partials land)
+  float* ctx_own = sm.red_s;                               // [AM][256]
+  float* ctx_peer = sm.red_s + 4 * 256;                    // [AM][256]        (written by the peer CTA)
+  const int* len_s = reinterpret_cast<const int*>(sm.scr + 48);
+  const int nchunk = jn > 0 ? (jn + am.cr - 1) / am.cr : 0, total = nact * nchunk;
+  const uint32_t mc0 = mc;
+
+  // ---- Q: queries and windows of all sequences
+  const int wq = warp & 3, a0 = (warp >> 2) * 64, jl = wq * 32 + lane;         // energies: thread = (position, 64-column half)
+  uint4 pmn[8];
+  auto pm_fetch = [&](int it) {
+    const int b = pair + it * npairs;
+    if (it < nact && jl < jn && (j0 + jl) < len_s[it]) {
+      const uint4* src = reinterpret_cast<const uint4*>(pm + ((size_t)b * Tin + (j0 + jl)) * A + a0);
+#pragma unroll
+      for (int g = 0; g < 8; ++g)
+        if (a0 + g * 8 < A) pmn[g] = __ldg(src + g);
+    }
+  };
+  pm_fetch(0);
+  {
+    const int ntq = p.Ha / 32;
+    const size_t qs = (size_t)p.B * A;
+    for (int i = threadIdx.x; i < nact * 128; i += blockDim.x) {
+      const int it = i >> 7, a = i & 127, b = pair + it * npairs;
+      float s = 0.f;
+      if (a < A) {
+        const float* qp = p.qpart + (size_t)b * A + a;
+        float qv[32];
+#pragma unroll
+        for (int c = 0; c < 32; ++c) qv[c] = c < ntq ? __ldcg(qp + (size_t)c * qs) : 0.f;
+#pragma unroll
+        for (int c = 0; c < 16; ++c) qv[c] += qv[c + 16];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) qv[c] += qv[c + 8];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) qv[c] += qv[c + 4];
+        s = (qv[0] + qv[1]) + (qv[2] + qv[3]);
+      }
+      q_m[i] = s;
+    }
+    for (int i = threadIdx.x; i < nact * 2 * Wd; i += blockDim.x) {
+      const int it = i / (2 * Wd), r = i - it * 2 * Wd, ch = r / Wd, jj = r - ch * Wd, j = j0 + jj - hk;
+      const int b = pair + it * npairs;
+      const float* src = (ch == 0 ? p.w_prev : p.w_cum) + (size_t)b * p.ldT;
+      sm.am_wcat[it * AM_WCAT + r] = (j >= 0 && j < Tin) ? __ldcg(src + j) : 0.f;
+    }
+  }
+  __syncthreads();
+  // ---- I: im2col tiles
+  for (int it = 0; it < nact; ++it) build_im2col(sm.am_wcat + it * AM_WCAT, Wd, KS, jn, am.im(it), am.im(it) + am.plane_bytes);
+  fence_proxy_async_smem();
+  __syncthreads();
+  // ---- M: location GEMMs (warp 1), first memory chunks (warp 0); warp-uniform control flow, one elected lane issues
+  auto issue_chunk = [&](int gi) {                         // chunk gi of this frame: sequence gi / nchunk, rows (gi % nchunk) cr ..
+    const int it = gi / nchunk, ch = gi - it * nchunk, b = pair + it * npairs;
+    const int r0 = ch * am.cr, nr = min(am.cr, jn - r0);
+    const uint32_t slot = (mc0 + (uint32_t)gi) % 3u, bytes = (uint32_t)nr * (uint32_t)E * 2u;
+    mbar_expect_tx(&sm.am_mem_full[slot], bytes);
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(am.slot0 + (size_t)slot * am.slot_bytes)), "l"(mem + ((size_t)b * Tin + j0 + r0) * E), "r"(bytes),
+                   "r"(smem_u32(&sm.am_mem_full[slot])) : "memory");
+  };
+  {
+    const int warp_u = __shfl_sync(0xffffffffu, warp, 0);
+    if (warp_u == 1) {
+      tc_fence_after();
+      const uint32_t idesc = umma_idesc_bf16(TILE_M, 128);
+      const uint64_t duh = umma_desc_sw128(smem_u32(sm.u_s)), dul = umma_desc_sw128(smem_u32(sm.u_s + W_TILE_BYTES));
+      for (int it = 0; it < nact; ++it) {
+        const uint32_t tacc = tmem_base + am_tmem_col(it);
+        const uint64_t dah = umma_desc_sw128(smem_u32(am.im(it))), dal = umma_desc_sw128(smem_u32(am.im(it) + am.plane_bytes));
+        if (elect_one()) {
+#pragma unroll
+          for (int k = 0; k < KB / 16; ++k) umma_bf16(tacc, dah + (uint64_t)(2 * k), duh + (uint64_t)(2 * k), idesc, (uint32_t)(k > 0));
+#pragma unroll
+          for (int k = 0; k < KB / 16; ++k) umma_bf16(tacc, dal + (uint64_t)(2 * k), duh + (uint64_t)(2 * k), idesc, 1u);
+#pragma unroll
+          for (int k = 0; k < KB / 16; ++k) umma_bf16(tacc, dah + (uint64_t)(2 * k), dul + (uint64_t)(2 * k), idesc, 1u);
+          umma_commit(&sm.am_att_full[it]);
+        }
+        __syncwarp();
+      }
+    } else if (warp_u == 0) {
+      if (elect_one())
+        for (int gi = 0; gi < total && gi < 3; ++gi) issue_chunk(gi);
+      __syncwarp();
+    }
+  }
+  PROF(24);
+  // ---- E: energies, sequence by sequence as the accumulators complete
+  for (int it = 0; it < nact; ++it) {
+    uint4 pmq[8];
+#pragma unroll
+    for (int g = 0; g < 8; ++g) pmq[g] = pmn[g];
+    pm_fetch(it + 1);
+    wait_bar(&sm.am_att_full[it], att_par);
+    tc_fence_after();
+    const bool valid = jl < jn && (j0 + jl) < len_s[it];
+    const float* qv = q_m + it * 128;
+    float part = 0.f;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      uint32_t r[32];
+      tmem_ld_32x32(tmem_base + am_tmem_col(it) + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a0 + h * 32), r);
+      tmem_ld_wait();
+      if (valid) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int ab = h * 32 + g * 8;
+          if (a0 + ab < A) {
+            const uint4 qq = pmq[h * 4 + g];
+            const uint32_t ww[4] = {qq.x, qq.y, qq.z, qq.w};
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const float pmv = (e & 1) ? __uint_as_float(ww[e >> 1] & 0xFFFF0000u) : __uint_as_float(ww[e >> 1] << 16);
+              const float sv = __uint_as_float(r[g * 8 + e]) + qv[a0 + ab + e] + pmv;
+              part += sm.v_s[a0 + ab + e] * tanh_fast(sv);
+            }
+          }
+        }
+      }
+    }
+    epart[(it * 2 + (warp >> 2)) * 128 + jl] = valid ? part : -INFINITY;
+  }
+  att_par ^= 1u;
+  tc_fence_before();
+  __syncthreads();
+  {
+    const uint32_t peer_e = map_to_rank(smem_u32(sm.am_ebuf), (uint32_t)peer);
+    for (int i = threadIdx.x; i < nact * jn; i += blockDim.x) {
+      const int it = i / jn, l = i - it * jn;
+      const float e = epart[(it * 2) * 128 + l] + epart[(it * 2 + 1) * 128 + l];      // -inf + -inf = -inf for masked positions
+      sm.am_ebuf[it * TIN_MAX + j0 + l] = e;
+      st_cluster_f1(peer_e + (uint32_t)((it * TIN_MAX + j0 + l) * 4), e);
+    }
+  }
+  PROF(25);
+  cluster_sync_all();
+  PROF(26);
+  // ---- S: masked softmax over all encoder positions, one warp per sequence (both CTAs of the pair compute it redundantly)
+  if (warp < nact) {
+    const int it = warp, b = pair + it * npairs;
+    const float* eb = sm.am_ebuf + it * TIN_MAX;
+    float ev[TIN_MAX / 32];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < TIN_MAX / 32; ++i) {
+      const int j = lane + 32 * i;
+      ev[i] = j < Tin ? eb[j] : -INFINITY;
+      mx = fmaxf(mx, ev[i]);
+    }
+    mx = warp_max(mx);
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < TIN_MAX / 32; ++i) {
+      ev[i] = ev[i] == -INFINITY ? 0.f : expf(ev[i] - mx);
+      sum += ev[i];
+    }
+    sum = warp_sum(sum);
+    const float inv = 1.0f / sum;
+    float* wprev = p.w_prev + (size_t)b * p.ldT;
+    float* wcum = p.w_cum + (size_t)b * p.ldT;
+    float* aout = p.align_out + ((size_t)b * p.n_steps + t) * Tin;
+    const float* cum_before = sm.am_wcat + it * AM_WCAT + Wd + hk;        // channel 1 of the window, position j0 + l
+#pragma unroll
+    for (int i = 0; i < TIN_MAX / 32; ++i) {
+      const int j = lane + 32 * i;
+      if (j < Tin) {
+        const float w = ev[i] * inv;
+        w_m[it * TIN_MAX + j] = w;
+        if (j >= j0 && j < j0 + jn) {
+          wprev[j] = w;
+          wcum[j] = cum_before[j - j0] + w;                               // model.py:403
+          aout[j] = w;
+        }
+      }
+    }
+  }
+  __syncthreads();
+  PROF(27);
+  // ---- C: partial context over this CTA's positions, all E columns: thread = one bf16 column pair
+  {
+    const int E2 = E >> 1;                                 // 32-bit words per memory row
+    const int Eh = ((E / 8 + 1) / 2) * 8;                  // columns [0, Eh) belong to half 0, [Eh, E) to half 1
+    const bool has_col = (int)threadIdx.x < E2;
+    const int c = 2 * threadIdx.x;
+    const uint32_t peer_ctx = map_to_rank(smem_u32(ctx_peer), (uint32_t)peer);
+    int gi = 0;
+    for (int it = 0; it < nact; ++it) {
+      float acc0 = 0.f, acc1 = 0.f;
+      const float* wv = w_m + it * TIN_MAX + j0;
+      for (int ch = 0; ch < nchunk; ++ch, ++gi) {
+        const uint32_t k = mc0 + (uint32_t)gi, slot = k % 3u;
+        wait_bar(&sm.am_mem_full[slot], (k / 3u) & 1u);
+        const uint32_t* rows = reinterpret_cast<const uint32_t*>(am.slot0 + (size_t)slot * am.slot_bytes) + threadIdx.x;
+        const int r0 = ch * am.cr, nr = min(am.cr, jn - r0);
+        if (has_col) {
+#pragma unroll 5
+          for (int r = 0; r < nr; ++r) {
+            const uint32_t m2 = rows[(size_t)r * E2];
+            const float w = wv[r0 + r];
+            acc0 += w * __uint_as_float(m2 << 16);
+            acc1 += w * __uint_as_float(m2 & 0xFFFF0000u);
+          }
+        }
+        __syncthreads();                                   // the slot has been read by every thread
+        if (gi + 3 < total && __shfl_sync(0xffffffffu, warp, 0) == 0) {
+          if (elect_one()) issue_chunk(gi + 3);
+          __syncwarp();
+        }
+      }
+      if (has_col) {
+        const bool mine = (c < Eh) == (half == 0);
+        const int cl = c < Eh ? c : c - Eh;                // index inside the owner's column range
+        if (mine) { ctx_own[it * 256 + cl] = acc0; ctx_own[it * 256 + cl + 1] = acc1; }
+        else {
+          st_cluster_f1(peer_ctx + (uint32_t)((it * 256 + cl) * 4), acc0);
+          st_cluster_f1(peer_ctx + (uint32_t)((it * 256 + cl + 1) * 4), acc1);
+        }
+      }
+    }
+    mc = mc0 + (uint32_t)total;
+    cluster_sync_all();
+    // ---- X: pair sum -> context operand of the next GEMMs
+    const int c_lo = half == 0 ? 0 : Eh, ncol = half == 0 ? Eh : E - Eh;
+    for (int i = threadIdx.x; i < nact * ncol; i += blockDim.x) {
+      const int it = i / ncol, cl = i - it * ncol, b = pair + it * npairs;
+      const float sv = half == 0 ? ctx_own[it * 256 + cl] + ctx_peer[it * 256 + cl] : ctx_peer[it * 256 + cl] + ctx_own[it * 256 + cl];
+      BFP(p.xctx)[(size_t)b * p.Ep + c_lo + cl] = __float2bfloat16_rn(sv);
+    }
+  }
+  __syncthreads();
+}
+
 template <int N>
 __global__ void __launch_bounds__(256, 1)
 decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const int S) {
@@ -772,7 +1229,14 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
     tma_load_3d(sm.u_s + W_TILE_BYTES, &maps.uloc, sm.u_full, KB, 0, 0);
     wait_bar(sm.u_full, 0);
   }
-  if (p.Ha / 32 == ncl && p.Hd / 32 == ncl) {
+  const AttnMulti am = attn_multi_layout<N>(p, sm, S, ncl);
+  if (threadIdx.x == 0 && am.on) {
+    for (int i = 0; i < 4; ++i) mbar_init(&sm.am_att_full[i], 1);
+    for (int i = 0; i < 3; ++i) mbar_init(&sm.am_mem_full[i], 1);
+    mbar_fence_init();
+  }
+  // (the batched attention's fourth accumulator takes the tensor-memory columns of the last four resident slots)
+  if (p.Ha / 32 == ncl && p.Hd / 32 == ncl && !(am.on && am.nmax > 3)) {
     // one attention-LSTM tile and one decoder-LSTM tile per cluster for the whole launch: park weight k-blocks of this
     // CTA's K quarters in the free TMEM columns, split so that each phase's remaining stages fit the ring in one round
     const int nka = p.mult * (p.Pp + p.Ep + p.Hap) / KB, nkd = p.mult * (p.Hap + p.Ep + p.Hdp) / KB;
@@ -792,7 +1256,7 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
   tc_fence_after();
 
   unsigned int epoch = 0;
-  uint32_t acc_par = 0, att_par = 0, round = 0, eround = 0;
+  uint32_t acc_par = 0, att_par = 0, round = 0, eround = 0, am_par = 0, am_mc = 0;
   float wqr[32];
 #pragma unroll
   for (int u = 0; u < 32; ++u) wqr[u] = 0.f;
@@ -801,9 +1265,17 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
   // The GEMM phases of a frame go through ONE call site of gemm_phase (runtime `kind`): five specialised inlined copies made
   // the per-frame code path larger than the instruction cache holds, and a phase that runs once per frame then runs cold.
   const bool pre_local = !p.train && p.B <= PRE_LOCAL_BMAX;
-  const int k_first = (p.train || pre_local) ? K_ATT : K_PRE1, k_last = p.train ? K_DEC : K_PROJ;
+  // batched inference, bf16 mode: projection + prenet inside each cluster for its own sequences (tail_phase)
+  const int nbc = (p.B + ncl - 1) / ncl;
+  const bool tail = !p.train && !pre_local && (p.reserved0 & 1) == 0 && tail_covers(p, nbc);
+  const int k_first = (p.train || pre_local || tail) ? K_ATT : K_PRE1, k_last = (p.train || tail) ? K_DEC : K_PROJ;
   bool stopped = false;
+  if (tail) {
+    tail_phase(p, sm, 0, false, rank, cid, ncl);           // prenet of the go frame
+    grid_sync2(p.barrier, epoch, nblocks);
+  }
   for (; t < p.n_steps && !stopped; ++t) {
+    if (tail) PROF(28);
     if (pre_local) {
       PROF(28);
       prenet_local(p, sm, t, rank);
@@ -819,7 +1291,8 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
       grid_sync2(p.barrier, epoch, nblocks);
       PROF(kind == K_PRE1 ? 30 : (kind == K_ATT ? 5 : (kind == K_DEC ? 18 : 23)));
       if (kind == K_ATT) {
-        if (p.mem_bf16) attention_phase2<bf16>(p, sm, t, rank, cid, ncl, tmem_att, att_par, eround);
+        if (am.on) attention_infer_multi<N>(p, sm, am, t, rank, cid, ncl, tmem_base, am_par, am_mc);
+        else if (p.mem_bf16) attention_phase2<bf16>(p, sm, t, rank, cid, ncl, tmem_att, att_par, eround);
         else attention_phase2<float>(p, sm, t, rank, cid, ncl, tmem_att, att_par, eround);
         PROF(6);
         grid_sync2(p.barrier, epoch, nblocks);
@@ -838,6 +1311,20 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
         } else if (__ldcg(p.stop) != 0) {
           stopped = true;
         }
+      }
+    }
+    if (tail) {
+      tail_phase(p, sm, t, true, rank, cid, ncl);
+      PROF(19);
+      grid_sync2(p.barrier, epoch, nblocks);
+      PROF(23);
+      // done[] was written by every cluster before the barrier above; every CTA decides (model.py:486)
+      int all = 1;
+      for (int b = threadIdx.x; b < p.B; b += blockDim.x) all &= (__ldcg(&p.done[b]) != 0);
+      all = __syncthreads_and(all);
+      if (all && !p.ignore_stop) {
+        stopped = true;
+        if (blockIdx.x == 0 && threadIdx.x == 0) *p.stop = 1;
       }
     }
   }
@@ -910,6 +1397,9 @@ extern "C" int gtn_decoder_forward2(const gtn_decoder_fwd_params* hp, void* stre
   auto thr = [](float pr) -> unsigned { double t = (double)pr * 4294967296.0; return t >= 4294967295.0 ? 0xFFFFFFFFu : (unsigned)t; };
   p.thr_att = p.use_dropout ? thr(p.p_att) : 0u;
   p.thr_dec = p.use_dropout ? thr(p.p_dec) : 0u;
+  p.reserved0 = 0;                                  // kernel feature switches (A/B measurements, parity tests between the paths)
+  if (getenv("GTN_INFER_NO_TAIL")) p.reserved0 |= 1;
+  if (getenv("GTN_INFER_NO_MULTI_ATTN")) p.reserved0 |= 2;
   const int N = p.B <= 32 ? 32 : (p.B <= 64 ? 64 : (p.B <= 128 ? 128 : 256));
   const int m = p.mult;
   const long long Ka = (long long)m * (p.Pp + p.Ep + p.Hap), Kd = (long long)m * (p.Hap + p.Ep + p.Hdp);

@@ -80,6 +80,42 @@ def test_infer_bf16_mode_close_to_oracle():
     assert_close(mel, om, "mel bf16", atol=3e-2, rtol=3e-2)
 
 
+@pytest.mark.parametrize("B,T_in,steps", [(6, 21, 4), (70, 12, 4), (130, 11, 3), (256, 9, 3)])
+def test_infer_bf16_batched_paths_close_to_oracle(B, T_in, steps):
+    """Batched decode in bf16 mode (B > 4: projection + prenet inside the clusters; B > 64: the 128 / 256 column tiles),
+    same bf16 tolerance as above."""
+    from gantron_b200 import decoder_ops
+    hp, dec, memory = _setup(B, T_in, steps, "bf16")
+    seed = 991
+    mel, gate, align, lengths, n = decoder_ops.decoder_inference(
+        dec, memory.cuda(), max_steps=steps, gate_threshold=0.5, seed=seed, prec=1, ignore_stop=True)
+    om, og, oa, _, _ = _oracle(hp, dec, memory, steps, seed)
+    assert n == steps
+    assert_close(align, oa, "alignments bf16", atol=2e-2, rtol=0)
+    assert_close(mel, om, "mel bf16", atol=3e-2, rtol=3e-2)
+    assert_close(gate, og, "gate bf16", atol=3e-2, rtol=3e-2)
+
+
+@pytest.mark.parametrize("flag", ["GTN_INFER_NO_TAIL", "GTN_INFER_NO_MULTI_ATTN"])
+@pytest.mark.parametrize("B,T_in", [(37, 33), (100, 1), (130, 64), (256, 150), (256, 211)])
+def test_infer_bf16_batched_paths_vs_the_paths_they_replace(B, T_in, flag, monkeypatch):
+    """The cluster-local projection / prenet (tail_phase) against the grid-wide GEMM phases, and the all-sequences-at-once
+    attention (attention_infer_multi) against the one-at-a-time phase: same operands, different summation order.  Frame 0
+    must agree to fp32 rounding; three frames so that one bf16 rounding flip cannot run away."""
+    from gantron_b200 import decoder_ops
+    hp, dec, memory = _setup(B, T_in, 3, "bf16")
+    run = lambda: decoder_ops.decoder_inference(dec, memory.cuda(), max_steps=3, gate_threshold=0.5, seed=31, prec=1,
+                                                ignore_stop=True)
+    a = run()
+    monkeypatch.setenv(flag, "1")
+    b = run()
+    monkeypatch.delenv(flag)
+    assert_close(a[2][:, 0], b[2][:, 0].cpu(), "alignments frame 0", atol=1e-6, rtol=1e-4)
+    assert_close(a[0][:, :, 0], b[0][:, :, 0].cpu(), "mel frame 0", atol=2e-3, rtol=2e-3)
+    assert_close(a[0], b[0].cpu(), "mel", atol=2e-2, rtol=2e-2)
+    assert_close(a[2], b[2].cpu(), "alignments", atol=1e-2, rtol=0)
+
+
 def test_infer_stops_on_gate_like_reference():
     """gate bias pushed high -> sigmoid(gate) > 0.5 on the first frame: output has exactly 1 frame (the frame
     on which the gate fired is kept, model.py:482-487)."""

@@ -72,3 +72,4 @@ if os.environ.get("GTN_PROF2"):
             print(f"   {n:40s} {v:8d}  (+{v - prev})")
             prev = v
         print(f"   next frame start                         {int(pr[t + 1, 28] - pr[t, 28]):8d}")
+        print("   raw slots:", [int(pr[t, s] - pr[t, 28]) for s in range(32)])
