@@ -177,6 +177,10 @@ struct GemmJob {
   int res_n = 0;          // leading k-blocks of THIS CTA's K range whose weights are resident in TMEM (no W load)
   int res_slot0 = 0;      // first resident slot
   int x_row0 = 0;         // first activation row (batch index) of the tile: batch-chunked phases load 64-row boxes
+  // segment fields by RUN-TIME index through selects: an indexed array access would put the whole struct in local memory
+  GTN_DEVICE const CUtensorMap* seg_map(int i) const { return i == 0 ? seg[0].map : (i == 1 ? seg[1].map : seg[2].map); }
+  GTN_DEVICE int seg_nkb(int i) const { return i == 0 ? seg[0].nkb : (i == 1 ? seg[1].nkb : seg[2].nkb); }
+  GTN_DEVICE int seg_z(int i) const { return i == 0 ? seg[0].z : (i == 1 ? seg[1].z : seg[2].z); }
 };
 
 // ---- TMEM-resident weight k-blocks -------------------------------------------------------------------------------
@@ -222,8 +226,8 @@ GTN_DEVICE void load_resident(const void* W, long long ldw, int nrows, int row0,
 template <int N>
 GTN_DEVICE void load_x_kblock(const GemmJob& job, uint8_t* dst, uint64_t* bar, int kb) {
   int kk = kb, si = 0;
-  while (si < job.nseg - 1 && kk >= job.seg[si].nkb) { kk -= job.seg[si].nkb; ++si; }
-  tma_load_3d(dst, job.seg[si].map, bar, kk * KB, 0, job.seg[si].z);
+  while (si < job.nseg - 1 && kk >= job.seg_nkb(si)) { kk -= job.seg_nkb(si); ++si; }
+  tma_load_3d(dst, job.seg_map(si), bar, kk * KB, 0, job.seg_z(si));
 }
 
 // Issue one cluster-split GEMM: this CTA's quarter of K.  Producer = warp 0, MMA issuer = warp 1 (one elected lane each).
@@ -267,14 +271,14 @@ GTN_DEVICE bool gemm_issue(const GemmJob& job, Ring& rg, uint32_t tmem_acc, uint
     uint32_t par = (it0 / (uint32_t)S) & 1u;
     // activation cursor: segment si, k-block kk inside it, for global k-block kb0
     int si = 0, kk = kb0;
-    while (si < job.nseg - 1 && kk >= job.seg[si].nkb) { kk -= job.seg[si].nkb; ++si; }
-    const CUtensorMap* xmap = job.seg[si].map;
-    int xz = job.seg[si].z, xn = job.seg[si].nkb;
+    while (si < job.nseg - 1 && kk >= job.seg_nkb(si)) { kk -= job.seg_nkb(si); ++si; }
+    const CUtensorMap* xmap = job.seg_map(si);
+    int xz = job.seg_z(si), xn = job.seg_nkb(si);
     // every lane of every producer warp advances the cursor; one elected lane of the stage's warp issues
     auto load_x = [&](bool mine, uint8_t* dst, uint64_t* bar) {
       if (mine && elect_one()) tma_load_3d(dst, xmap, bar, kk * KB, job.x_row0, xz);
       ++kk;
-      while (si < job.nseg - 1 && kk >= xn) { kk -= xn; ++si; xmap = job.seg[si].map; xz = job.seg[si].z; xn = job.seg[si].nkb; }
+      while (si < job.nseg - 1 && kk >= xn) { kk -= xn; ++si; xmap = job.seg_map(si); xz = job.seg_z(si); xn = job.seg_nkb(si); }
     };
     for (int sg = 0; sg < nstages; ++sg) {
       const bool mine = (sg % NPROD) == pw;

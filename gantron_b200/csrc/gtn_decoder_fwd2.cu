@@ -146,8 +146,7 @@ GTN_DEVICE int make_job(const DecFwd& p, const Fwd2Maps& maps, int kind, int t, 
       job.seg[1] = {&maps.ctx, mult * p.Ep / KB, 0};
       break;
   }
-  job.nkb = 0;
-  for (int i = 0; i < job.nseg; ++i) job.nkb += job.seg[i].nkb;
+  job.nkb = job.seg[0].nkb + (job.nseg > 1 ? job.seg[1].nkb : 0) + (job.nseg > 2 ? job.seg[2].nkb : 0);
   return ntiles;
 }
 
@@ -162,9 +161,9 @@ GTN_DEVICE void gemm_phase_chunked(const DecFwd& p, const Fwd2Maps& maps, Smem2&
   const int mult = p.mult;
   GemmJob job;
   const int ntiles = make_job(p, maps, kind, t, job);
-  for (int i = 0; i < job.nseg; ++i) {
-    const CUtensorMap* mp = job.seg[i].map;
-    job.seg[i].map = mp == &maps.xmel ? &maps.xmel_c : (mp == &maps.xp1 ? &maps.xp1_c : (mp == &maps.hd ? &maps.hd_c : &maps.ctx_c));
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    if (i < job.nseg) { const CUtensorMap* mp = job.seg[i].map; job.seg[i].map = mp == &maps.xmel ? &maps.xmel_c : (mp == &maps.xp1 ? &maps.xp1_c : (mp == &maps.hd ? &maps.hd_c : &maps.ctx_c)); }
   }
   job.res_n = 0;
   const int nch = (p.B + CH - 1) / CH;
@@ -211,7 +210,7 @@ GTN_DEVICE void gemm_phase_chunked(const DecFwd& p, const Fwd2Maps& maps, Smem2&
 
 template <int N>
 GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int kind, int t, int rank, int cid, int ncl,
-                           uint32_t tmem_base, uint32_t& acc_par, uint32_t& round, float (&wqr)[32]) {
+                           uint32_t tmem_base, uint32_t& acc_par, uint32_t& round) {
   constexpr int CH = N < 64 ? N : 64;
   constexpr int NC4 = CH / 4;
   if constexpr (N > 64) {
@@ -229,12 +228,6 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
 
   for (int tile = cid; tile < ntiles; tile += ncl) {
     job.row0 = tile * TILE_M;
-    if (is_att && (ntiles > ncl || t == 0)) {
-      // query-weight column of this thread (a = tid % 128) for the tile's 32 units, kept in registers: Wq[a][32 tile + u]
-      const int a = threadIdx.x & 127;
-#pragma unroll
-      for (int u = 0; u < 32; ++u) wqr[u] = a < p.A ? p.wq_t[((size_t)tile * 32 + u) * p.A + a] : 0.f;
-    }
     const int ps = kind == K_ATT ? 1 : (kind == K_DEC ? 9 : (kind == K_PROJ ? 14 : 20));
     if (tile == cid && kind == K_ATT) { job.res_n = sm.res_a; job.res_slot0 = 0; }
     else if (tile == cid && kind == K_DEC) { job.res_n = sm.res_d; job.res_slot0 = sm.res_a; }
@@ -242,6 +235,15 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
     const bool has_work = gemm_issue<N>(job, sm.ring, tmem_base, sm.acc_full, rank, tmem_base);
     PROF(ps);                                    // producer: all TMA loads issued
     __syncwarp();
+    float wqr[32];
+    if (is_att) {
+      // query-weight column of this thread (a = tid % 128) for the tile's 32 units: Wq[a][32 tile + u].  Fetched every frame
+      // underneath the accumulator wait (L1 / L2 hits): held across the frame it costs 32 registers in every other phase,
+      // and this kernel's spills go to L2 (the shared-memory carve-out leaves the local-memory window almost no L1)
+      const int a = threadIdx.x & 127;
+#pragma unroll
+      for (int u = 0; u < 32; ++u) wqr[u] = a < p.A ? __ldg(&p.wq_t[((size_t)tile * 32 + u) * p.A + a]) : 0.f;
+    }
     if ((threadIdx.x >> 5) >= 4 && has_work) {
       wait_bar(sm.acc_full, acc_par);
       tc_fence_after();
@@ -945,8 +947,11 @@ GTN_DEVICE AttnMulti attn_multi_layout(const DecFwd& p, const Smem2& sm, int S, 
 GTN_DEVICE uint32_t am_tmem_col(int it) { return it == 0 ? 256u : (it == 1 ? 0u : (it == 2 ? 128u : 384u)); }
 
 template <int N>
-GTN_DEVICE void attention_infer_multi(const DecFwd& p, Smem2& sm, const AttnMulti& am, int t, int rank, int cid, int ncl,
+GTN_DEVICE void attention_infer_multi(const DecFwd& p, Smem2& sm, int S, int t, int rank, int cid, int ncl,
                                       uint32_t tmem_base, uint32_t& att_par, uint32_t& mc) {
+  // (the layout is a few integer operations: recomputed per frame instead of ten values living in registers / local memory
+  // across the whole frame)
+  const AttnMulti am = attn_multi_layout<N>(p, sm, S, ncl);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int Tin = p.Tin, A = p.A, KS = p.KS, hk = (p.KS - 1) / 2, E = p.E;
   const int half = rank & 1, peer = rank ^ 1;
@@ -1229,14 +1234,19 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
     tma_load_3d(sm.u_s + W_TILE_BYTES, &maps.uloc, sm.u_full, KB, 0, 0);
     wait_bar(sm.u_full, 0);
   }
-  const AttnMulti am = attn_multi_layout<N>(p, sm, S, ncl);
-  if (threadIdx.x == 0 && am.on) {
+  bool am_on;
+  int am_nmax;
+  {
+    const AttnMulti am0 = attn_multi_layout<N>(p, sm, S, ncl);
+    am_on = am0.on; am_nmax = am0.nmax;
+  }
+  if (threadIdx.x == 0 && am_on) {
     for (int i = 0; i < 4; ++i) mbar_init(&sm.am_att_full[i], 1);
     for (int i = 0; i < 3; ++i) mbar_init(&sm.am_mem_full[i], 1);
     mbar_fence_init();
   }
   // (the batched attention's fourth accumulator takes the tensor-memory columns of the last four resident slots)
-  if (p.Ha / 32 == ncl && p.Hd / 32 == ncl && !(am.on && am.nmax > 3)) {
+  if (p.Ha / 32 == ncl && p.Hd / 32 == ncl && !(am_on && am_nmax > 3)) {
     // one attention-LSTM tile and one decoder-LSTM tile per cluster for the whole launch: park weight k-blocks of this
     // CTA's K quarters in the free TMEM columns, split so that each phase's remaining stages fit the ring in one round
     const int nka = p.mult * (p.Pp + p.Ep + p.Hap) / KB, nkd = p.mult * (p.Hap + p.Ep + p.Hdp) / KB;
@@ -1257,9 +1267,6 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
 
   unsigned int epoch = 0;
   uint32_t acc_par = 0, att_par = 0, round = 0, eround = 0, am_par = 0, am_mc = 0;
-  float wqr[32];
-#pragma unroll
-  for (int u = 0; u < 32; ++u) wqr[u] = 0.f;
   const unsigned int nblocks = gridDim.x;
   int t = 0;
   // The GEMM phases of a frame go through ONE call site of gemm_phase (runtime `kind`): five specialised inlined copies made
@@ -1285,13 +1292,13 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
     for (int kind = k_first; kind <= k_last; ++kind) {
       if (kind == K_PRE1) PROF(28);
       if (kind == K_ATT) PROF(0);
-      gemm_phase<N>(p, maps, sm, kind, t, rank, cid, ncl, tmem_base, acc_par, round, wqr);
+      gemm_phase<N>(p, maps, sm, kind, t, rank, cid, ncl, tmem_base, acc_par, round);
       PROF(kind == K_PRE1 ? 29 : (kind == K_PRE2 ? 31 : (kind == K_ATT ? 4 : (kind == K_DEC ? 13 : 19))));
       if (kind == K_DEC && p.train) break;        // C(t) and A(t+1) share an interval: no barrier in between
       grid_sync2(p.barrier, epoch, nblocks);
       PROF(kind == K_PRE1 ? 30 : (kind == K_ATT ? 5 : (kind == K_DEC ? 18 : 23)));
       if (kind == K_ATT) {
-        if (am.on) attention_infer_multi<N>(p, sm, am, t, rank, cid, ncl, tmem_base, am_par, am_mc);
+        if (am_on) attention_infer_multi<N>(p, sm, S, t, rank, cid, ncl, tmem_base, am_par, am_mc);
         else if (p.mem_bf16) attention_phase2<bf16>(p, sm, t, rank, cid, ncl, tmem_att, att_par, eround);
         else attention_phase2<float>(p, sm, t, rank, cid, ncl, tmem_att, att_par, eround);
         PROF(6);
