@@ -23,6 +23,13 @@
 
 namespace gtn {
 
+// experiment switch: compile the kernel for inference only (measures what the unexecuted training code costs)
+#ifdef GTN_FWD2_INFER_ONLY
+#define P_TRAIN false
+#else
+#define P_TRAIN p.train
+#endif
+
 #define PROF(slot)                                                                          \
   do {                                                                                      \
     if (p.prof != nullptr && blockIdx.x == 0 && threadIdx.x == 0 && t < 16) p.prof[t * 32 + (slot)] = clock64(); \
@@ -130,7 +137,7 @@ GTN_DEVICE int make_job(const DecFwd& p, const Fwd2Maps& maps, int kind, int t, 
       break;
     case K_ATT:
       job.wmap = &maps.w_att; ntiles = p.Ha / 32; job.nseg = 3;
-      job.seg[0] = p.train ? XSeg{&maps.pre, mult * p.Pp / KB, t} : XSeg{&maps.xp2, mult * p.Pp / KB, 0};
+      job.seg[0] = P_TRAIN ? XSeg{&maps.pre, mult * p.Pp / KB, t} : XSeg{&maps.xp2, mult * p.Pp / KB, 0};
       job.seg[1] = {&maps.ctx, mult * p.Ep / KB, 0};
       job.seg[2] = {&maps.ha, mult * p.Hap / KB, cur};
       break;
@@ -315,7 +322,7 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
               h = bits >= thr ? h * dscale : 0.f;
             }
             store_act(xh_next + (size_t)b * mult * Hp, unit, Hp, p.prec, h);
-            if (p.train) {
+            if (P_TRAIN) {
               const size_t cell = ((size_t)t * p.B + b) * H + unit;
               reinterpret_cast<float4*>(gates_all)[cell] = make_float4(i_, f_, g_, o_);
               c_all[cell] = c_new;
@@ -325,9 +332,9 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
           if (is_att) sm.hs[ul * NC4 + bl] = h;
         }
         if (is_att) {
-          if (p.train) PROF(14);
+          if (P_TRAIN) PROF(14);
           __syncthreads();
-          if (p.train) PROF(15);
+          if (P_TRAIN) PROF(15);
           // partial query of this tile: qpart[tile][b][a] = sum_u Wq[a][32 tile + u] h[b][u]; thread = (a, half of the columns)
           constexpr int HB = NC4 / 2;
           const int a = threadIdx.x & 127, g = threadIdx.x >> 7;
@@ -344,7 +351,7 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
               acc[4 * j4 + 2] += wqr[u] * hv.z; acc[4 * j4 + 3] += wqr[u] * hv.w;
             }
           }
-          if (p.train) PROF(16);
+          if (P_TRAIN) PROF(16);
           if (a < p.A) {
 #pragma unroll
             for (int j = 0; j < HB; ++j) {
@@ -690,29 +697,29 @@ GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, in
           s += (qv[0] + qv[1]) + (qv[2] + qv[3]);
         }
         sm.q_s[a] = s;
-        if (p.train && half == 0) p.q_all[((size_t)t * p.B + b) * A + a] = s;
+        if (P_TRAIN && half == 0) p.q_all[((size_t)t * p.B + b) * A + a] = s;
       }
-      if (p.train) PROF(7);
+      if (P_TRAIN) PROF(7);
       const float* wprev = p.w_prev + (size_t)b * p.ldT;
       const float* wcum = p.w_cum + (size_t)b * p.ldT;
       for (int i = threadIdx.x; i < 2 * Wd; i += blockDim.x) {
         const int ch = i / Wd, jj = i - ch * Wd, j = j0 + jj - hk;
         const float val = (j >= 0 && j < Tin) ? __ldcg(ch == 0 ? &wprev[j] : &wcum[j]) : 0.f;
         sm.wcat[i] = val;
-        if (p.train && ch == 1 && jj >= hk && jj < hk + jn) p.cum_all[((size_t)t * p.B + b) * Tin + j] = val;
+        if (P_TRAIN && ch == 1 && jj >= hk && jj < hk + jn) p.cum_all[((size_t)t * p.B + b) * Tin + j] = val;
       }
     }
-    if (p.train) PROF(12);
+    if (P_TRAIN) PROF(12);
     __syncthreads();
-    if (p.train) PROF(20);
+    if (P_TRAIN) PROF(20);
     if (active) {
       // im2col: row r = local encoder position, K index kk = ch*KS + k  ->  wcat[ch][r + k]; bf16 hi / lo planes
       build_im2col(sm.wcat, Wd, KS, jn, a_hi, a_lo);
       fence_proxy_async_smem();
     }
-    if (p.train) PROF(21);
+    if (P_TRAIN) PROF(21);
     __syncthreads();
-    if (p.train) PROF(22);
+    if (P_TRAIN) PROF(22);
     // warp 1 issues in warp-uniform control flow (one elected lane; see gemm_issue)
     if (active && __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0) == 1) {
       tc_fence_after();
@@ -741,7 +748,7 @@ GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, in
       const bool valid = jl < jn && (j0 + jl) < L;
       float part = 0.f;
       const MT* pmj = pm + ((size_t)b * Tin + (j0 + jl)) * A + a0;
-      float* thj = p.train ? p.th_all + (((size_t)t * p.B + b) * Tin + (j0 + jl)) * A + a0 : nullptr;
+      float* thj = P_TRAIN ? p.th_all + (((size_t)t * p.B + b) * Tin + (j0 + jl)) * A + a0 : nullptr;
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         uint32_t r[32];
@@ -830,7 +837,7 @@ GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, in
       const int c8_0 = half * Eh8, c8_n = min(E8, c8_0 + Eh8) - c8_0;      // in units of 8 columns
       const int mult = p.mult;
       bf16* xc = BFP(p.xctx) + (size_t)b * mult * p.Ep;
-      float* call = p.train ? p.ctx_all + ((size_t)t * p.B + b) * p.D : nullptr;
+      float* call = P_TRAIN ? p.ctx_all + ((size_t)t * p.B + b) * p.D : nullptr;
       for (int cb = 0; cb < c8_n; cb += 32) {
         const int c8 = cb + lane;
         float acc[8];
@@ -923,7 +930,7 @@ GTN_DEVICE AttnMulti attn_multi_layout(const DecFwd& p, const Smem2& sm, int S, 
   am.slot_bytes = (uint32_t)(am.cr * p.E * 2 + 127) & ~127u;
   am.plane_bytes = (uint32_t)rows8 * 128u;
   am.slot0 = sm.ring.base;
-  am.on = !p.train && p.mem_bf16 && p.prec == 1 && (p.reserved0 & 2) == 0 && am.nmax <= am_max<N>() && p.E <= 512 && p.E % 8 == 0 &&
+  am.on = !P_TRAIN && p.mem_bf16 && p.prec == 1 && (p.reserved0 & 2) == 0 && am.nmax <= am_max<N>() && p.E <= 512 && p.E % 8 == 0 &&
           p.Ha / 32 <= 32;
   // im2col tiles: behind the memory slots in the ring, then in the receive buffers (both idle during the phase); a tile is
   // read as 128 rows by the MMA whatever its row count, so 16 KB behind its base must lie inside the CTA's shared memory
@@ -1271,11 +1278,11 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
   int t = 0;
   // The GEMM phases of a frame go through ONE call site of gemm_phase (runtime `kind`): five specialised inlined copies made
   // the per-frame code path larger than the instruction cache holds, and a phase that runs once per frame then runs cold.
-  const bool pre_local = !p.train && p.B <= PRE_LOCAL_BMAX;
+  const bool pre_local = !P_TRAIN && p.B <= PRE_LOCAL_BMAX;
   // batched inference, bf16 mode: projection + prenet inside each cluster for its own sequences (tail_phase)
   const int nbc = (p.B + ncl - 1) / ncl;
-  const bool tail = !p.train && !pre_local && (p.reserved0 & 1) == 0 && tail_covers(p, nbc);
-  const int k_first = (p.train || pre_local || tail) ? K_ATT : K_PRE1, k_last = (p.train || tail) ? K_DEC : K_PROJ;
+  const bool tail = !P_TRAIN && !pre_local && (p.reserved0 & 1) == 0 && tail_covers(p, nbc);
+  const int k_first = (P_TRAIN || pre_local || tail) ? K_ATT : K_PRE1, k_last = (P_TRAIN || tail) ? K_DEC : K_PROJ;
   bool stopped = false;
   if (tail) {
     tail_phase(p, sm, 0, false, rank, cid, ncl);           // prenet of the go frame
@@ -1294,13 +1301,15 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
       if (kind == K_ATT) PROF(0);
       gemm_phase<N>(p, maps, sm, kind, t, rank, cid, ncl, tmem_base, acc_par, round);
       PROF(kind == K_PRE1 ? 29 : (kind == K_PRE2 ? 31 : (kind == K_ATT ? 4 : (kind == K_DEC ? 13 : 19))));
-      if (kind == K_DEC && p.train) break;        // C(t) and A(t+1) share an interval: no barrier in between
+      if (kind == K_DEC && P_TRAIN) break;        // C(t) and A(t+1) share an interval: no barrier in between
       grid_sync2(p.barrier, epoch, nblocks);
       PROF(kind == K_PRE1 ? 30 : (kind == K_ATT ? 5 : (kind == K_DEC ? 18 : 23)));
       if (kind == K_ATT) {
         if (am_on) attention_infer_multi<N>(p, sm, S, t, rank, cid, ncl, tmem_base, am_par, am_mc);
+#ifndef GTN_FWD2_INFER_ONLY
         else if (p.mem_bf16) attention_phase2<bf16>(p, sm, t, rank, cid, ncl, tmem_att, att_par, eround);
         else attention_phase2<float>(p, sm, t, rank, cid, ncl, tmem_att, att_par, eround);
+#endif
         PROF(6);
         grid_sync2(p.barrier, epoch, nblocks);
         PROF(8);
