@@ -23,12 +23,12 @@
 
 namespace gtn {
 
-// experiment switch: compile the kernel for inference only (measures what the unexecuted training code costs)
-#ifdef GTN_FWD2_INFER_ONLY
-#define P_TRAIN false
-#else
-#define P_TRAIN p.train
-#endif
+// FAST = the kernel instantiation for batched bf16 inference on the cluster-local tail + all-at-once attention paths (the host
+// checks the conditions): everything else -- training saves, the one-at-a-time attention, the grid-wide prenet / projection
+// phases, the small-batch prenet -- is compiled out.  Half the code, 5 % faster: this kernel's per-frame path is several
+// times the instruction cache, and unexecuted code still spreads it out.
+#define P_TRAIN (!FAST && p.train)
+#define GTN_HD __host__ __device__ __forceinline__
 
 #define PROF(slot)                                                                          \
   do {                                                                                      \
@@ -123,6 +123,7 @@ GTN_DEVICE Smem2 carve2(uint8_t* base, int S) {
 // GEMM phases: prenet layers, the two LSTM cells, the mel/gate projection
 // ------------------------------------------------------------------------------------------------
 // Operands of the GEMM phase `kind` of frame t; returns the number of 128-row tiles.
+template <bool FAST>
 GTN_DEVICE int make_job(const DecFwd& p, const Fwd2Maps& maps, int kind, int t, GemmJob& job) {
   const int mult = p.mult, cur = t & 1, nxt = cur ^ 1;
   int ntiles;
@@ -167,7 +168,7 @@ GTN_DEVICE void gemm_phase_chunked(const DecFwd& p, const Fwd2Maps& maps, Smem2&
   constexpr int CH = 64, NC4 = CH / 4;
   const int mult = p.mult;
   GemmJob job;
-  const int ntiles = make_job(p, maps, kind, t, job);
+  const int ntiles = make_job<false>(p, maps, kind, t, job);
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
     if (i < job.nseg) { const CUtensorMap* mp = job.seg[i].map; job.seg[i].map = mp == &maps.xmel ? &maps.xmel_c : (mp == &maps.xp1 ? &maps.xp1_c : (mp == &maps.hd ? &maps.hd_c : &maps.ctx_c)); }
@@ -215,12 +216,12 @@ GTN_DEVICE void gemm_phase_chunked(const DecFwd& p, const Fwd2Maps& maps, Smem2&
   }
 }
 
-template <int N>
+template <int N, bool FAST>
 GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int kind, int t, int rank, int cid, int ncl,
                            uint32_t tmem_base, uint32_t& acc_par, uint32_t& round) {
   constexpr int CH = N < 64 ? N : 64;
   constexpr int NC4 = CH / 4;
-  if constexpr (N > 64) {
+  if constexpr (N > 64 && !FAST) {
     if (kind != K_ATT && kind != K_DEC) {
       gemm_phase_chunked(p, maps, sm, kind, t, rank, cid, ncl, tmem_base, acc_par, round, sm.recv);
       return;
@@ -228,8 +229,8 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
   }
   const int mult = p.mult, cur = t & 1, nxt = cur ^ 1;
   GemmJob job;
-  const int ntiles = make_job(p, maps, kind, t, job);
-  const bool is_lstm = kind == K_ATT || kind == K_DEC;
+  const int ntiles = make_job<FAST>(p, maps, kind, t, job);
+  const bool is_lstm = FAST || kind == K_ATT || kind == K_DEC;
   const bool is_att = kind == K_ATT;
   const int H = is_att ? p.Ha : p.Hd, Hp = is_att ? p.Hap : p.Hdp;
 
@@ -306,7 +307,7 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
           if (b < p.B) {
             // bf16 mode: hardware tanh (tanh.approx, rel. error ~2^-11, below the bf16 rounding of every operand; the energies
             // and the backward's tanh(c) use it too); fp32 mode: libm
-            const bool fast = p.prec == 1;
+            const bool fast = FAST || p.prec == 1;
             const float zi = recv_sum<NC4, true>(recv, ul, bl) + gb[q].x, zf = recv_sum<NC4, true>(recv, 32 + ul, bl) + gb[q].y;
             const float zg = recv_sum<NC4, true>(recv, 64 + ul, bl) + gb[q].z, zo = recv_sum<NC4, true>(recv, 96 + ul, bl) + gb[q].w;
             const float i_ = fast ? 0.5f * tanh_fast(0.5f * zi) + 0.5f : sigmoid_acc(zi);
@@ -384,7 +385,7 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
         }
       }
     }
-    if (kind == K_PROJ) {
+    if (!FAST && kind == K_PROJ) {
       // the cluster that owns the projection decides whether every sequence has fired its gate (model.py:486)
       cluster_sync_all();                                  // the four ranks' done[] writes
       if (rank == 0) {
@@ -584,7 +585,7 @@ GTN_DEVICE void tail_layer(float* part, const bf16* W, int ldw, int nrows, int t
 }
 
 // Can the tail run for this configuration?  (bf16 planes only; K segments in 32-element slabs; tile counts within part[])
-GTN_DEVICE bool tail_covers(const DecFwd& p, int nbc) {
+GTN_HD bool tail_covers(const DecFwd& p, int nbc) {
   const int ntp = ((p.P + 15) / 16 + CL - 1) / CL;         // prenet tiles per CTA
   return p.prec == 1 && nbc <= TAIL_BMAX && (p.NM + 1 + 15) / 16 <= 2 * CL && 2 * ntp <= TAIL_UNITS && p.Hdp % 32 == 0 &&
          p.Ep % 32 == 0 && p.NMp % 32 == 0 && p.Pp % 32 == 0;
@@ -646,6 +647,7 @@ GTN_DEVICE void tail_phase(const DecFwd& p, Smem2& sm, int t, bool do_proj, int 
 template <typename MT>
 GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, int cid, int ncl, uint32_t tmem_att,
                                  uint32_t& att_par, uint32_t& eround) {
+  constexpr bool FAST = false;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int Tin = p.Tin, A = p.A, KS = p.KS, hk = (p.KS - 1) / 2;
   const int half = rank & 1, peer = rank ^ 1;
@@ -920,34 +922,54 @@ struct AttnMulti {
   GTN_DEVICE uint8_t* im(int it) const { return it == 0 ? im0 : (it == 1 ? im1 : (it == 2 ? im2 : im3)); }
 };
 
+// Placement of the batched attention's buffers as OFFSETS (ring base / receive-buffer base), computable on the host too:
+// the launcher picks the FAST kernel instantiation only if the phase fits.
+struct AttnPlan {
+  bool on;
+  int nmax, cr;
+  uint32_t slot_bytes, plane_bytes;
+  int o0, o1, o2, o3;       // im2col tile of sequence i: >= 0 offset in the ring, < 0: -(offset in the receive buffers) - 1
+};
 template <int N>
-GTN_DEVICE AttnMulti attn_multi_layout(const DecFwd& p, const Smem2& sm, int S, int ncl) {
+GTN_HD AttnPlan attn_multi_plan(const DecFwd& p, int S, int ncl) {
   constexpr int NC4 = (N < 64 ? N : 64) / 4;
-  AttnMulti am;
-  am.nmax = (p.B + 2 * ncl - 1) / (2 * ncl);
+  AttnPlan a;
+  a.nmax = (p.B + 2 * ncl - 1) / (2 * ncl);
   const int JH = (p.Tin + 1) / 2, rows8 = (JH + 7) & ~7;
-  am.cr = (JH + 2) / 3;
-  am.slot_bytes = (uint32_t)(am.cr * p.E * 2 + 127) & ~127u;
-  am.plane_bytes = (uint32_t)rows8 * 128u;
-  am.slot0 = sm.ring.base;
-  am.on = !P_TRAIN && p.mem_bf16 && p.prec == 1 && (p.reserved0 & 2) == 0 && am.nmax <= am_max<N>() && p.E <= 512 && p.E % 8 == 0 &&
-          p.Ha / 32 <= 32;
+  a.cr = (JH + 2) / 3;
+  a.slot_bytes = (uint32_t)(a.cr * p.E * 2 + 127) & ~127u;
+  a.plane_bytes = (uint32_t)rows8 * 128u;
+  a.on = !p.train && p.mem_bf16 && p.prec == 1 && (p.reserved0 & 2) == 0 && a.nmax <= am_max<N>() && p.E <= 512 && p.E % 8 == 0 &&
+         p.Ha / 32 <= 32;
   // im2col tiles: behind the memory slots in the ring, then in the receive buffers (both idle during the phase); a tile is
   // read as 128 rows by the MMA whatever its row count, so 16 KB behind its base must lie inside the CTA's shared memory
-  uint8_t* r1 = sm.ring.base + ((3u * am.slot_bytes + 1023u) & ~1023u);
-  uint8_t* r1_end = sm.ring.base + (size_t)S * sm.ring.stage_bytes;
-  uint8_t* r2 = reinterpret_cast<uint8_t*>(sm.recv);
-  uint8_t* r2_end = r2 + (size_t)2 * 4 * TILE_M * NC4 * 4;
-  auto place = [&](int it) -> uint8_t* {
-    uint8_t* r = nullptr;
-    if (it >= am.nmax) return r;
-    if (r1 + 2 * am.plane_bytes <= r1_end) { r = r1; r1 += 2 * am.plane_bytes; }
-    else if (r2 + 2 * am.plane_bytes <= r2_end) { r = r2; r2 += 2 * am.plane_bytes; }
-    else am.on = false;
-    return r;
-  };
-  am.im0 = place(0); am.im1 = place(1); am.im2 = place(2); am.im3 = place(3);
-  if (3u * am.slot_bytes > (uint32_t)S * sm.ring.stage_bytes) am.on = false;
+  const uint32_t ring_bytes = (uint32_t)S * (uint32_t)(W_TILE_BYTES + N * KB * 2), recv_bytes = 2u * 4u * TILE_M * NC4 * 4u;
+  uint32_t r1 = (3u * a.slot_bytes + 1023u) & ~1023u, r2 = 0u;
+  int o[4];
+#pragma unroll
+  for (int it = 0; it < 4; ++it) {
+    o[it] = 0;
+    if (it >= a.nmax) continue;
+    if (r1 + 2 * a.plane_bytes <= ring_bytes) { o[it] = (int)r1; r1 += 2 * a.plane_bytes; }
+    else if (r2 + 2 * a.plane_bytes <= recv_bytes) { o[it] = -(int)r2 - 1; r2 += 2 * a.plane_bytes; }
+    else a.on = false;
+  }
+  a.o0 = o[0]; a.o1 = o[1]; a.o2 = o[2]; a.o3 = o[3];
+  if (3u * a.slot_bytes > ring_bytes) a.on = false;
+  return a;
+}
+
+template <int N>
+GTN_DEVICE AttnMulti attn_multi_layout(const DecFwd& p, const Smem2& sm, int S, int ncl) {
+  const AttnPlan a = attn_multi_plan<N>(p, S, ncl);
+  AttnMulti am;
+  am.on = a.on; am.nmax = a.nmax; am.cr = a.cr; am.slot_bytes = a.slot_bytes; am.plane_bytes = a.plane_bytes;
+  am.slot0 = sm.ring.base;
+  uint8_t* rb = reinterpret_cast<uint8_t*>(sm.recv);
+  am.im0 = a.o0 >= 0 ? sm.ring.base + a.o0 : rb + (-a.o0 - 1);
+  am.im1 = a.o1 >= 0 ? sm.ring.base + a.o1 : rb + (-a.o1 - 1);
+  am.im2 = a.o2 >= 0 ? sm.ring.base + a.o2 : rb + (-a.o2 - 1);
+  am.im3 = a.o3 >= 0 ? sm.ring.base + a.o3 : rb + (-a.o3 - 1);
   return am;
 }
 
@@ -1208,7 +1230,14 @@ GTN_DEVICE void attention_infer_multi(const DecFwd& p, Smem2& sm, int S, int t, 
   __syncthreads();
 }
 
+// Host and device agree on what the FAST instantiation covers
 template <int N>
+GTN_HD bool fwd2_fast_covers(const DecFwd& p, int S, int ncl) {
+  return !p.train && p.B > 4 /* PRE_LOCAL_BMAX */ && (p.reserved0 & 3) == 0 && tail_covers(p, (p.B + ncl - 1) / ncl) &&
+         attn_multi_plan<N>(p, S, ncl).on;
+}
+
+template <int N, bool FAST>
 __global__ void __launch_bounds__(256, 1)
 decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const int S) {
   extern __shared__ uint8_t smem_raw[];
@@ -1278,10 +1307,11 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
   int t = 0;
   // The GEMM phases of a frame go through ONE call site of gemm_phase (runtime `kind`): five specialised inlined copies made
   // the per-frame code path larger than the instruction cache holds, and a phase that runs once per frame then runs cold.
-  const bool pre_local = !P_TRAIN && p.B <= PRE_LOCAL_BMAX;
+  const bool pre_local = !FAST && !P_TRAIN && p.B <= PRE_LOCAL_BMAX;
   // batched inference, bf16 mode: projection + prenet inside each cluster for its own sequences (tail_phase)
   const int nbc = (p.B + ncl - 1) / ncl;
-  const bool tail = !P_TRAIN && !pre_local && (p.reserved0 & 1) == 0 && tail_covers(p, nbc);
+  const bool tail = FAST || (!P_TRAIN && !pre_local && (p.reserved0 & 1) == 0 && tail_covers(p, nbc));
+  if (FAST && !fwd2_fast_covers<N>(p, S, ncl)) __trap();   // (the launcher checked the same predicate)
   const int k_first = (P_TRAIN || pre_local || tail) ? K_ATT : K_PRE1, k_last = (P_TRAIN || tail) ? K_DEC : K_PROJ;
   bool stopped = false;
   if (tail) {
@@ -1290,31 +1320,34 @@ decoder_fwd2_kernel(const __grid_constant__ Fwd2Maps maps, const DecFwd p, const
   }
   for (; t < p.n_steps && !stopped; ++t) {
     if (tail) PROF(28);
-    if (pre_local) {
-      PROF(28);
-      prenet_local(p, sm, t, rank);
-      PROF(31);
+    if constexpr (!FAST) {
+      if (pre_local) {
+        PROF(28);
+        prenet_local(p, sm, t, rank);
+        PROF(31);
+      }
     }
 #pragma unroll 1
     for (int kind = k_first; kind <= k_last; ++kind) {
       if (kind == K_PRE1) PROF(28);
       if (kind == K_ATT) PROF(0);
-      gemm_phase<N>(p, maps, sm, kind, t, rank, cid, ncl, tmem_base, acc_par, round);
+      gemm_phase<N, FAST>(p, maps, sm, kind, t, rank, cid, ncl, tmem_base, acc_par, round);
       PROF(kind == K_PRE1 ? 29 : (kind == K_PRE2 ? 31 : (kind == K_ATT ? 4 : (kind == K_DEC ? 13 : 19))));
       if (kind == K_DEC && P_TRAIN) break;        // C(t) and A(t+1) share an interval: no barrier in between
       grid_sync2(p.barrier, epoch, nblocks);
       PROF(kind == K_PRE1 ? 30 : (kind == K_ATT ? 5 : (kind == K_DEC ? 18 : 23)));
       if (kind == K_ATT) {
-        if (am_on) attention_infer_multi<N>(p, sm, S, t, rank, cid, ncl, tmem_base, am_par, am_mc);
-#ifndef GTN_FWD2_INFER_ONLY
-        else if (p.mem_bf16) attention_phase2<bf16>(p, sm, t, rank, cid, ncl, tmem_att, att_par, eround);
-        else attention_phase2<float>(p, sm, t, rank, cid, ncl, tmem_att, att_par, eround);
-#endif
+        if (FAST || am_on) attention_infer_multi<N>(p, sm, S, t, rank, cid, ncl, tmem_base, am_par, am_mc);
+        if constexpr (!FAST) {
+          if (am_on) {}
+          else if (p.mem_bf16) attention_phase2<bf16>(p, sm, t, rank, cid, ncl, tmem_att, att_par, eround);
+          else attention_phase2<float>(p, sm, t, rank, cid, ncl, tmem_att, att_par, eround);
+        }
         PROF(6);
         grid_sync2(p.barrier, epoch, nblocks);
         PROF(8);
       }
-      if (kind == K_PROJ) {
+      if (!FAST && kind == K_PROJ) {
         if constexpr (N > 64) {
           // batch-chunked projection: done[] was written by several clusters before the barrier above; every CTA decides
           int all = 1;
@@ -1361,8 +1394,10 @@ static int launch_fwd2(const Fwd2Maps& maps, const DecFwd& p, int max_clusters_w
   if (S > 12) S = 12;
   GTN_REQUIRE(S >= 2, "decoder forward: not enough shared memory for the TMA ring (N=%d)", N);
   const size_t smem = fixed + (size_t)S * stage;
-  auto kern = decoder_fwd2_kernel<N>;
+  auto kern = decoder_fwd2_kernel<N, false>;
+  auto kern_fast = decoder_fwd2_kernel<N, true>;
   GTN_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  GTN_CUDA_OK(cudaFuncSetAttribute(kern_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg = {};
   cfg.blockDim = dim3(256);
   cfg.dynamicSmemBytes = smem;
@@ -1375,8 +1410,9 @@ static int launch_fwd2(const Fwd2Maps& maps, const DecFwd& p, int max_clusters_w
   cfg.attrs = attrs;
   cfg.numAttrs = 1;
   cfg.gridDim = dim3(CL * max_clusters_wanted);
-  int max_cl = 0;
+  int max_cl = 0, max_cl_fast = 0;
   GTN_CUDA_OK(cudaOccupancyMaxActiveClusters(&max_cl, kern, &cfg));
+  GTN_CUDA_OK(cudaOccupancyMaxActiveClusters(&max_cl_fast, kern_fast, &cfg));
   GTN_REQUIRE(max_cl >= 1, "decoder forward: no cluster of %d CTAs fits on this device", CL);
   const int ncl = max_cl < max_clusters_wanted ? max_cl : max_clusters_wanted;
   // each CTA pair stages the encoder lengths of at most 8 sequences (scr + 48): B <= 16 * clusters
@@ -1384,7 +1420,9 @@ static int launch_fwd2(const Fwd2Maps& maps, const DecFwd& p, int max_clusters_w
               p.B, ncl);
   cfg.gridDim = dim3(CL * ncl);
   cfg.numAttrs = profiler_attached() ? 1 : 2;   // profilers that cannot replay cooperative launches
-  GTN_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, maps, p, S));
+  // batched bf16 inference on the cluster-local tail and the all-at-once attention: the instantiation without the rest
+  const bool fast = max_cl_fast >= ncl && !getenv("GTN_FWD2_GENERIC") && fwd2_fast_covers<N>(p, S, ncl);
+  GTN_CUDA_OK(cudaLaunchKernelEx(&cfg, fast ? kern_fast : kern, maps, p, S));
   count_launch();
   return 0;
 }

@@ -96,7 +96,7 @@ def test_infer_bf16_batched_paths_close_to_oracle(B, T_in, steps):
     assert_close(gate, og, "gate bf16", atol=3e-2, rtol=3e-2)
 
 
-@pytest.mark.parametrize("flag", ["GTN_INFER_NO_TAIL", "GTN_INFER_NO_MULTI_ATTN"])
+@pytest.mark.parametrize("flag", ["GTN_INFER_NO_TAIL", "GTN_INFER_NO_MULTI_ATTN", "GTN_FWD2_GENERIC"])
 @pytest.mark.parametrize("B,T_in", [(37, 33), (100, 1), (130, 64), (256, 150), (256, 211)])
 def test_infer_bf16_batched_paths_vs_the_paths_they_replace(B, T_in, flag, monkeypatch):
     """The cluster-local projection / prenet (tail_phase) against the grid-wide GEMM phases, and the all-sequences-at-once
