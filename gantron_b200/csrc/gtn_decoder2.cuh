@@ -455,6 +455,60 @@ GTN_DEVICE void exchange_bulk(bool has_work, uint32_t tmem_acc, int c0, float* r
   tc_fence_after();
 }
 
+// First half of exchange_bulk (everything but the wait for this CTA's own receive), with an explicit staging area: lets a
+// caller send chunk c + 1 before it consumes chunk c.  `stage` must not be a receive buffer a peer may write into.
+template <int CH, bool WB = false>
+GTN_DEVICE void exchange_send(bool has_work, uint32_t tmem_acc, int c0, float* recv, float* stage, uint64_t* full_bar, int rank) {
+  constexpr int NC4 = CH / 4;
+  constexpr uint32_t BLK = (uint32_t)TILE_M * NC4 * 4;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  cta_sync<WB>();
+  if (threadIdx.x == 0) mbar_expect_tx(full_bar, 3u * BLK);
+  // all eight warps stage when the chunk has two 32-column halves (a warp reaches TMEM lane quarter warp % 4): warps 0..3
+  // take the first half, warps 4..7 the second
+  if (warp >= 4 || CH == 64) {
+    const int wq = warp & 3;
+    const int row = wq * 32 + lane;
+    const int h_lo = CH == 64 ? (warp >> 2) : 0, h_hi = CH == 64 ? (warp >> 2) + 1 : CH / 32;
+    for (int h = h_lo; h < h_hi; ++h) {
+      uint32_t r[32];
+      if (has_work) {
+        tmem_ld_32x32(tmem_acc + ((uint32_t)(wq * 32) << 16) + (uint32_t)(c0 + h * 32), r);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) r[j] = 0u;
+      }
+#pragma unroll
+      for (int g = 0; g < 32 / NC4; ++g) {
+        const int dst = (h * 32 + g * NC4) / NC4;
+        float* blk = (dst == rank ? recv + (size_t)rank * TILE_M * NC4 : stage + (size_t)dst * TILE_M * NC4) + (size_t)row * NC4;
+#pragma unroll
+        for (int v = 0; v < NC4; v += 4)
+          *reinterpret_cast<float4*>(blk + (v ^ (((row >> 1) & (NC4 / 4 - 1)) << 2))) =
+              make_float4(__uint_as_float(r[g * NC4 + v]), __uint_as_float(r[g * NC4 + v + 1]),
+                          __uint_as_float(r[g * NC4 + v + 2]), __uint_as_float(r[g * NC4 + v + 3]));
+      }
+    }
+    fence_proxy_async_smem();
+  }
+  tc_fence_before();
+  cta_sync<WB>();
+  if (__shfl_sync(0xffffffffu, warp, 0) == 0) {
+    if (elect_one()) {
+#pragma unroll
+      for (int d = 1; d < CL; ++d) {
+        const uint32_t dst = (uint32_t)((rank + d) % CL);
+        asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(map_to_rank(smem_u32(recv + (size_t)rank * TILE_M * NC4), dst)),
+                       "r"(smem_u32(stage + (size_t)dst * TILE_M * NC4)), "r"(BLK), "r"(map_to_rank(smem_u32(full_bar), dst))
+                     : "memory");
+      }
+    }
+    __syncwarp();
+  }
+}
+
 // sum of the four partials of element (row, col) of this CTA's slice
 template <int NC4, bool SWZ = false>
 GTN_DEVICE float recv_sum(const float* recv, int row, int col) {

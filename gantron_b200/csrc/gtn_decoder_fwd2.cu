@@ -258,15 +258,13 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
     }
     PROF_T(128, ps + 1);                         // epilogue warp: accumulator complete
     if (has_work) acc_par ^= 1u;
-    for (int c0 = 0; c0 < N; c0 += CH) {
-      float* recv = sm.recv + (size_t)(round & 1u) * 4 * TILE_M * NC4;
-      ++round;
+    // operands of the fused epilogue that do not depend on the GEMM are fetched while the exchange is in flight
+    constexpr int CPT = 32 * NC4 / 256;          // LSTM cells per thread (NC4 = 8 or 16)
+    float4 gb[CPT];
+    float cprev[CPT];
+    float* cst = is_att ? p.c_a : p.c_d;
+    auto prefetch = [&](int c0) {
       const int bbase = c0 + rank * NC4;
-      // operands of the fused epilogue that do not depend on the GEMM are fetched while the exchange is in flight
-      constexpr int CPT = 32 * NC4 / 256;          // LSTM cells per thread (NC4 = 8 or 16)
-      float4 gb[CPT];
-      float cprev[CPT];
-      float* cst = is_att ? p.c_a : p.c_d;
       if (is_lstm) {
         const float4* gbias = reinterpret_cast<const float4*>(is_att ? p.gbias_a : p.gbias_d);
 #pragma unroll
@@ -283,11 +281,37 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
           }
         }
       }
-      {
+    };
+    // PIPE (batched inference, more than one 64-column chunk per tile): chunk c + 1 is on its way while the cells of chunk c
+    // run.  The sends are staged in the idle TMA ring (the accumulator is complete, so every stage has been consumed)
+    // instead of the other receive buffer; a cluster barrier behind the cells of chunk c tells every CTA that receive buffer
+    // c & 1 and staging area c & 1 are free for chunk c + 2.
+    constexpr bool PIPE = FAST && N > 64;
+    const uint32_t round0 = round;
+    auto send = [&](int ci) {
+      const uint32_t xr = round0 + (uint32_t)ci;
+      exchange_send<CH>(has_work, tmem_base, ci * CH, sm.recv + (size_t)(xr & 1u) * 4 * TILE_M * NC4,
+                        reinterpret_cast<float*>(sm.ring.base) + (size_t)(ci & 1) * 4 * TILE_M * NC4, &sm.recv_full[xr & 1u], rank);
+    };
+    if (PIPE) {
+      prefetch(0);
+      send(0);
+      if (N > CH) send(1);
+    }
+    for (int c0 = 0; c0 < N; c0 += CH) {
+      float* recv = sm.recv + (size_t)(round & 1u) * 4 * TILE_M * NC4;
+      ++round;
+      const int bbase = c0 + rank * NC4;
+      if (!PIPE) {
+        prefetch(c0);
         // (`round` was advanced when recv was picked: this exchange is number round - 1)
         const uint32_t xr = round - 1u;
         float* stage = sm.recv + (size_t)((xr & 1u) ^ 1u) * 4 * TILE_M * NC4;
         exchange_bulk<CH>(has_work, tmem_base, c0, recv, stage, &sm.recv_full[xr & 1u], (xr >> 1) & 1u, rank);
+      } else {
+        const uint32_t xr = round - 1u;
+        wait_bar(&sm.recv_full[xr & 1u], (xr >> 1) & 1u);
+        tc_fence_after();
       }
       PROF(ps + 2);                              // DSMEM exchange + cluster barrier done
       if (is_lstm) {
@@ -384,7 +408,13 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
           }
         }
       }
+      if (PIPE && c0 + CH < N) {
+        prefetch(c0 + CH);
+        if (c0 + 2 * CH < N) { cluster_sync_all(); send(c0 / CH + 2); }
+        else __syncthreads();                      // sm.hs of this chunk has been read
+      }
     }
+    if (PIPE && tile + ncl < ntiles) cluster_sync_all();   // the peers have received out of the ring before it is refilled
     if (!FAST && kind == K_PROJ) {
       // the cluster that owns the projection decides whether every sequence has fired its gate (model.py:486)
       cluster_sync_all();                                  // the four ranks' done[] writes
