@@ -240,7 +240,7 @@ GTN_DEVICE void load_x_kblock(const GemmJob& job, uint8_t* dst, uint64_t* bar, i
 #endif
 template <int N>
 GTN_DEVICE bool gemm_issue(const GemmJob& job, Ring& rg, uint32_t tmem_acc, uint64_t* acc_full, int rank,
-                           uint32_t tmem_res = 0u) {
+                           uint32_t tmem_res = 0u, uint64_t w_policy = 0ull) {
   constexpr uint32_t X_BYTES = N * KB * 2;
   constexpr int G = (W_TILE_BYTES + X_BYTES) / X_BYTES;       // resident k-blocks per stage
   const int kb0 = rank * job.nkb / CL, kb1 = (rank + 1) * job.nkb / CL;
@@ -292,7 +292,9 @@ GTN_DEVICE bool gemm_issue(const GemmJob& job, Ring& rg, uint32_t tmem_acc, uint
         const int kb = kb0 + res_n + (sg - res_stages);
         if (mine && elect_one()) {
           mbar_expect_tx(&full[s], W_TILE_BYTES + X_BYTES);
-          tma_load_3d(st, job.wmap, &full[s], kb * KB, job.row0, 0);
+          // w_policy: the caller knows the weights' reuse distance (one frame) against what else streams through L2
+          if (w_policy != 0ull) tma_load_3d_hint(st, job.wmap, &full[s], kb * KB, job.row0, 0, w_policy);
+          else tma_load_3d(st, job.wmap, &full[s], kb * KB, job.row0, 0);
         }
         load_x(mine, st + W_TILE_BYTES, &full[s]);
       }

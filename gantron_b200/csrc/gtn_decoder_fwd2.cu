@@ -240,7 +240,10 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
     if (tile == cid && kind == K_ATT) { job.res_n = sm.res_a; job.res_slot0 = 0; }
     else if (tile == cid && kind == K_DEC) { job.res_n = sm.res_d; job.res_slot0 = sm.res_a; }
     else job.res_n = 0;
-    const bool has_work = gemm_issue<N>(job, sm.ring, tmem_base, sm.acc_full, rank, tmem_base);
+    // batched decode at B > 64: weights + encoder memory + processed memory (~90 MB per frame) do not all stay in L2 (ncu: 50 %
+    // hit rate, 68 MB per frame from DRAM); the weights are kept (evict_last), the memory chunks stream (evict_first)
+    const bool has_work = gemm_issue<N>(job, sm.ring, tmem_base, sm.acc_full, rank, tmem_base,
+                                        (FAST && N > 64 && (p.reserved0 & 8) == 0) ? l2_policy_evict_last() : 0ull);
     PROF(ps);                                    // producer: all TMA loads issued
     __syncwarp();
     float wqr[32];
@@ -1084,9 +1087,15 @@ GTN_DEVICE void attention_infer_multi(const DecFwd& p, Smem2& sm, int S, int t, 
     const int r0 = ch * am.cr, nr = min(am.cr, jn - r0);
     const uint32_t slot = (mc0 + (uint32_t)gi) % 3u, bytes = (uint32_t)nr * (uint32_t)E * 2u;
     mbar_expect_tx(&sm.am_mem_full[slot], bytes);
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(smem_u32(am.slot0 + (size_t)slot * am.slot_bytes)), "l"(mem + ((size_t)b * Tin + j0 + r0) * E), "r"(bytes),
-                   "r"(smem_u32(&sm.am_mem_full[slot])) : "memory");
+    if (N > 64 && (p.reserved0 & 8) == 0) {
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                   ::"r"(smem_u32(am.slot0 + (size_t)slot * am.slot_bytes)), "l"(mem + ((size_t)b * Tin + j0 + r0) * E), "r"(bytes),
+                     "r"(smem_u32(&sm.am_mem_full[slot])), "l"(l2_policy_evict_first()) : "memory");
+    } else {
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(smem_u32(am.slot0 + (size_t)slot * am.slot_bytes)), "l"(mem + ((size_t)b * Tin + j0 + r0) * E), "r"(bytes),
+                     "r"(smem_u32(&sm.am_mem_full[slot])) : "memory");
+    }
   };
   {
     const int warp_u = __shfl_sync(0xffffffffu, warp, 0);
@@ -1484,6 +1493,7 @@ extern "C" int gtn_decoder_forward2(const gtn_decoder_fwd_params* hp, void* stre
   p.reserved0 = 0;                                  // kernel feature switches (A/B measurements, parity tests between the paths)
   if (getenv("GTN_INFER_NO_TAIL")) p.reserved0 |= 1;
   if (getenv("GTN_INFER_NO_MULTI_ATTN")) p.reserved0 |= 2;
+  if (getenv("GTN_INFER_NO_L2_HINTS")) p.reserved0 |= 8;
   const int N = p.B <= 32 ? 32 : (p.B <= 64 ? 64 : (p.B <= 128 ? 128 : 256));
   const int m = p.mult;
   const long long Ka = (long long)m * (p.Pp + p.Ep + p.Hap), Kd = (long long)m * (p.Hap + p.Ep + p.Hdp);
