@@ -1073,12 +1073,37 @@ GTN_DEVICE void attention_infer_multi(const DecFwd& p, Smem2& sm, int S, int t, 
       const int it = i / (2 * Wd), r = i - it * 2 * Wd, ch = r / Wd, jj = r - ch * Wd, j = j0 + jj - hk;
       const int b = pair + it * npairs;
       const float* src = (ch == 0 ? p.w_prev : p.w_cum) + (size_t)b * p.ldT;
-      sm.am_wcat[it * AM_WCAT + r] = (j >= 0 && j < Tin) ? __ldcg(src + j) : 0.f;
+      const float wv = (j >= 0 && j < Tin) ? __ldcg(src + j) : 0.f;
+      sm.am_wcat[it * AM_WCAT + r] = wv;
+      // hi / lo bf16 planes of the window element, split ONCE (an element appears in ~KS rows of the im2col tile):
+      // low half = hi plane bits, high half = lo plane bits.  The memory slots are free until the chunks are requested.
+      const bf16 whi = __float2bfloat16_rn(wv);
+      const bf16 wlo = __float2bfloat16_rn(wv - __bfloat162float(whi));
+      reinterpret_cast<uint32_t*>(am.slot0)[it * AM_WCAT + r] = (uint32_t)__bfloat16_as_ushort(whi) | ((uint32_t)__bfloat16_as_ushort(wlo) << 16);
     }
   }
   __syncthreads();
   // ---- I: im2col tiles
-  for (int it = 0; it < nact; ++it) build_im2col(sm.am_wcat + it * AM_WCAT, Wd, KS, jn, am.im(it), am.im(it) + am.plane_bytes);
+  // row r = local encoder position, K index kk = ch KS + k  ->  window element ch Wd + r + k; 16-byte chunk = 8 K elements
+  for (int i = threadIdx.x; i < nact * jn * 8; i += blockDim.x) {
+    const int it = i / (jn * 8), rc = i - it * jn * 8, r = rc >> 3, chunk = rc & 7;
+    const uint32_t* sp = reinterpret_cast<const uint32_t*>(am.slot0) + it * AM_WCAT + r;
+    uint32_t sv[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int kk = chunk * 8 + e;
+      sv[e] = kk < 2 * KS ? sp[kk + (kk >= KS ? Wd - KS : 0)] : 0u;
+    }
+    uint4 hi, lo;
+    hi.x = __byte_perm(sv[0], sv[1], 0x5410); lo.x = __byte_perm(sv[0], sv[1], 0x7632);
+    hi.y = __byte_perm(sv[2], sv[3], 0x5410); lo.y = __byte_perm(sv[2], sv[3], 0x7632);
+    hi.z = __byte_perm(sv[4], sv[5], 0x5410); lo.z = __byte_perm(sv[4], sv[5], 0x7632);
+    hi.w = __byte_perm(sv[6], sv[7], 0x5410); lo.w = __byte_perm(sv[6], sv[7], 0x7632);
+    uint8_t* tile = am.im(it);
+    const uint32_t off = sw128_off(r, chunk);
+    *reinterpret_cast<uint4*>(tile + off) = hi;
+    *reinterpret_cast<uint4*>(tile + am.plane_bytes + off) = lo;
+  }
   fence_proxy_async_smem();
   __syncthreads();
   // ---- M: location GEMMs (warp 1), first memory chunks (warp 0); warp-uniform control flow, one elected lane issues
