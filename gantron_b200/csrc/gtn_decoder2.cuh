@@ -44,6 +44,13 @@ GTN_DEVICE void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
+// cluster barrier WITHOUT memory ordering: enough where it only has to keep a peer from overwriting shared memory this CTA
+// has finished READING (the loads' values have been consumed, so they have completed); the release form waits for every
+// earlier global store of the CTA to be performed (1.7k cycles behind the LSTM cells' stores)
+GTN_DEVICE void cluster_sync_relaxed() {
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
+}
 GTN_DEVICE uint32_t map_to_rank(uint32_t smem_addr, uint32_t rank) {
   uint32_t r;
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));

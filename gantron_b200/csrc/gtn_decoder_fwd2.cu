@@ -413,7 +413,7 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
       }
       if (PIPE && c0 + CH < N) {
         prefetch(c0 + CH);
-        if (c0 + 2 * CH < N) { cluster_sync_all(); send(c0 / CH + 2); }
+        if (c0 + 2 * CH < N) { cluster_sync_relaxed(); send(c0 / CH + 2); }
         else __syncthreads();                      // sm.hs of this chunk has been read
       }
     }
