@@ -116,6 +116,35 @@ def test_infer_bf16_batched_paths_vs_the_paths_they_replace(B, T_in, flag, monke
     assert_close(a[2], b[2].cpu(), "alignments", atol=1e-2, rtol=0)
 
 
+@pytest.mark.parametrize("B,T_in", [(8, 23), (70, 17), (200, 9)])
+def test_infer_bf16_batched_stop_logic_fast_vs_generic(B, T_in, monkeypatch):
+    """Per-row stop frames and the end of the loop in the FAST instantiation (gate test inside the clusters' tail, every CTA
+    evaluates done[] behind the tail's grid barrier) against the generic instantiation (gate test in the projection GEMM
+    phase).  Gate weights scaled so that rows fire at different frames; both sides see the same operands."""
+    from gantron_b200 import decoder_ops
+    steps = 12
+    hp, dec, memory = _setup(B, T_in, steps, "bf16", seed=5)
+    with torch.no_grad():
+        dec.gate_layer.linear_layer.weight.mul_(40.0)
+        dec.gate_layer.linear_layer.bias.zero_()
+    # the gate feeds nothing back (model.py:411-417): a forced run gives every row's logit trajectory, and a bias at the 80 %
+    # quantile of all logits makes a row fire at the first frame it exceeds it (different frames for different rows)
+    g0 = decoder_ops.decoder_inference(dec, memory.cuda(), max_steps=steps, gate_threshold=0.5, seed=123, prec=1,
+                                       ignore_stop=True)[1][:, :, 0].float().cpu()
+    with torch.no_grad():
+        dec.gate_layer.linear_layer.bias.fill_(-float(torch.quantile(g0.flatten(), 0.8)))
+    run = lambda: decoder_ops.decoder_inference(dec, memory.cuda(), max_steps=steps, gate_threshold=0.5, seed=123, prec=1)
+    mel, gate, align, lengths, n = run()
+    monkeypatch.setenv("GTN_FWD2_GENERIC", "1")
+    mel_g, gate_g, align_g, lengths_g, n_g = run()
+    monkeypatch.delenv("GTN_FWD2_GENERIC")
+    assert n == n_g and lengths.cpu().tolist() == lengths_g.cpu().tolist()
+    assert len(set(lengths.cpu().tolist())) > 1, "rows should fire at different frames"
+    assert int(lengths.max()) == n
+    assert_close(mel, mel_g.cpu(), "mel", atol=2e-2, rtol=2e-2)
+    assert_close(gate, gate_g.cpu(), "gate", atol=5e-2, rtol=5e-2)
+
+
 def test_infer_stops_on_gate_like_reference():
     """gate bias pushed high -> sigmoid(gate) > 0.5 on the first frame: output has exactly 1 frame (the frame
     on which the gate fired is kept, model.py:482-487)."""
