@@ -411,7 +411,7 @@ GTN_DEVICE void cta_sync() {
 // stage[q] block only in its NEXT exchange, which it enters after it has received this exchange's blocks (mine included, so
 // my copy out of stage[q] has completed); and I overwrite a peer's buffer only two exchanges after it was filled, which I
 // reach only after that peer has sent the exchange in between, i.e. after it finished reading.
-template <int CH, bool WB = false>
+template <int CH, bool WB = false, bool CM = false>
 GTN_DEVICE void exchange_bulk(bool has_work, uint32_t tmem_acc, int c0, float* recv, float* stage, uint64_t* full_bar,
                               uint32_t parity, int rank) {
   constexpr int NC4 = CH / 4;
@@ -435,12 +435,20 @@ GTN_DEVICE void exchange_bulk(bool has_work, uint32_t tmem_acc, int c0, float* r
 #pragma unroll
       for (int g = 0; g < 32 / NC4; ++g) {
         const int dst = (h * 32 + g * NC4) / NC4;
-        float* blk = (dst == rank ? recv + (size_t)rank * TILE_M * NC4 : stage + (size_t)dst * TILE_M * NC4) + (size_t)row * NC4;
+        float* blk0 = dst == rank ? recv + (size_t)rank * TILE_M * NC4 : stage + (size_t)dst * TILE_M * NC4;
+        if (CM) {
+          // column-major block [NC4][128 rows]: a warp's lanes (consecutive rows) write consecutive words, and the LSTM epilogue
+          // (lanes over hidden units = rows) reads consecutive words: no bank conflicts on either side
 #pragma unroll
-        for (int v = 0; v < NC4; v += 4)
-          *reinterpret_cast<float4*>(blk + (v ^ (((row >> 1) & (NC4 / 4 - 1)) << 2))) =
-              make_float4(__uint_as_float(r[g * NC4 + v]), __uint_as_float(r[g * NC4 + v + 1]),
-                          __uint_as_float(r[g * NC4 + v + 2]), __uint_as_float(r[g * NC4 + v + 3]));
+          for (int v = 0; v < NC4; ++v) blk0[(size_t)v * TILE_M + row] = __uint_as_float(r[g * NC4 + v]);
+        } else {
+          float* blk = blk0 + (size_t)row * NC4;
+#pragma unroll
+          for (int v = 0; v < NC4; v += 4)
+            *reinterpret_cast<float4*>(blk + (v ^ (((row >> 1) & (NC4 / 4 - 1)) << 2))) =
+                make_float4(__uint_as_float(r[g * NC4 + v]), __uint_as_float(r[g * NC4 + v + 1]),
+                            __uint_as_float(r[g * NC4 + v + 2]), __uint_as_float(r[g * NC4 + v + 3]));
+        }
       }
     }
     fence_proxy_async_smem();                                     // staging writes -> bulk-copy (async proxy) reads
@@ -466,7 +474,7 @@ GTN_DEVICE void exchange_bulk(bool has_work, uint32_t tmem_acc, int c0, float* r
 
 // First half of exchange_bulk (everything but the wait for this CTA's own receive), with an explicit staging area: lets a
 // caller send chunk c + 1 before it consumes chunk c.  `stage` must not be a receive buffer a peer may write into.
-template <int CH, bool WB = false>
+template <int CH, bool WB = false, bool CM = false>
 GTN_DEVICE void exchange_send(bool has_work, uint32_t tmem_acc, int c0, float* recv, float* stage, uint64_t* full_bar, int rank) {
   constexpr int NC4 = CH / 4;
   constexpr uint32_t BLK = (uint32_t)TILE_M * NC4 * 4;
@@ -491,12 +499,20 @@ GTN_DEVICE void exchange_send(bool has_work, uint32_t tmem_acc, int c0, float* r
 #pragma unroll
       for (int g = 0; g < 32 / NC4; ++g) {
         const int dst = (h * 32 + g * NC4) / NC4;
-        float* blk = (dst == rank ? recv + (size_t)rank * TILE_M * NC4 : stage + (size_t)dst * TILE_M * NC4) + (size_t)row * NC4;
+        float* blk0 = dst == rank ? recv + (size_t)rank * TILE_M * NC4 : stage + (size_t)dst * TILE_M * NC4;
+        if (CM) {
+          // column-major block [NC4][128 rows]: a warp's lanes (consecutive rows) write consecutive words, and the LSTM epilogue
+          // (lanes over hidden units = rows) reads consecutive words: no bank conflicts on either side
 #pragma unroll
-        for (int v = 0; v < NC4; v += 4)
-          *reinterpret_cast<float4*>(blk + (v ^ (((row >> 1) & (NC4 / 4 - 1)) << 2))) =
-              make_float4(__uint_as_float(r[g * NC4 + v]), __uint_as_float(r[g * NC4 + v + 1]),
-                          __uint_as_float(r[g * NC4 + v + 2]), __uint_as_float(r[g * NC4 + v + 3]));
+          for (int v = 0; v < NC4; ++v) blk0[(size_t)v * TILE_M + row] = __uint_as_float(r[g * NC4 + v]);
+        } else {
+          float* blk = blk0 + (size_t)row * NC4;
+#pragma unroll
+          for (int v = 0; v < NC4; v += 4)
+            *reinterpret_cast<float4*>(blk + (v ^ (((row >> 1) & (NC4 / 4 - 1)) << 2))) =
+                make_float4(__uint_as_float(r[g * NC4 + v]), __uint_as_float(r[g * NC4 + v + 1]),
+                            __uint_as_float(r[g * NC4 + v + 2]), __uint_as_float(r[g * NC4 + v + 3]));
+        }
       }
     }
     fence_proxy_async_smem();
@@ -519,6 +535,12 @@ GTN_DEVICE void exchange_send(bool has_work, uint32_t tmem_acc, int c0, float* r
 }
 
 // sum of the four partials of element (row, col) of this CTA's slice
+// column-major receive blocks (exchange_bulk / exchange_send with CM)
+template <int NC4>
+GTN_DEVICE float recv_sum_cm(const float* recv, int row, int col) {
+  const float* p = recv + (size_t)col * TILE_M + row;
+  return (p[0] + p[(size_t)TILE_M * NC4]) + (p[(size_t)2 * TILE_M * NC4] + p[(size_t)3 * TILE_M * NC4]);
+}
 template <int NC4, bool SWZ = false>
 GTN_DEVICE float recv_sum(const float* recv, int row, int col) {
   const float* p = recv + (size_t)row * NC4 + (SWZ ? (col ^ (((row >> 1) & (NC4 / 4 - 1)) << 2)) : col);

@@ -293,7 +293,7 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
     const uint32_t round0 = round;
     auto send = [&](int ci) {
       const uint32_t xr = round0 + (uint32_t)ci;
-      exchange_send<CH>(has_work, tmem_base, ci * CH, sm.recv + (size_t)(xr & 1u) * 4 * TILE_M * NC4,
+      exchange_send<CH, false, true>(has_work, tmem_base, ci * CH, sm.recv + (size_t)(xr & 1u) * 4 * TILE_M * NC4,
                         reinterpret_cast<float*>(sm.ring.base) + (size_t)(ci & 1) * 4 * TILE_M * NC4, &sm.recv_full[xr & 1u], rank);
     };
     if (PIPE) {
@@ -310,7 +310,8 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
         // (`round` was advanced when recv was picked: this exchange is number round - 1)
         const uint32_t xr = round - 1u;
         float* stage = sm.recv + (size_t)((xr & 1u) ^ 1u) * 4 * TILE_M * NC4;
-        exchange_bulk<CH>(has_work, tmem_base, c0, recv, stage, &sm.recv_full[xr & 1u], (xr >> 1) & 1u, rank);
+        if (FAST) exchange_bulk<CH, false, true>(has_work, tmem_base, c0, recv, stage, &sm.recv_full[xr & 1u], (xr >> 1) & 1u, rank);
+        else exchange_bulk<CH>(has_work, tmem_base, c0, recv, stage, &sm.recv_full[xr & 1u], (xr >> 1) & 1u, rank);
       } else {
         const uint32_t xr = round - 1u;
         wait_bar(&sm.recv_full[xr & 1u], (xr >> 1) & 1u);
@@ -335,8 +336,11 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
             // bf16 mode: hardware tanh (tanh.approx, rel. error ~2^-11, below the bf16 rounding of every operand; the energies
             // and the backward's tanh(c) use it too); fp32 mode: libm
             const bool fast = FAST || p.prec == 1;
-            const float zi = recv_sum<NC4, true>(recv, ul, bl) + gb[q].x, zf = recv_sum<NC4, true>(recv, 32 + ul, bl) + gb[q].y;
-            const float zg = recv_sum<NC4, true>(recv, 64 + ul, bl) + gb[q].z, zo = recv_sum<NC4, true>(recv, 96 + ul, bl) + gb[q].w;
+            // (FAST: column-major receive blocks, conflict-free for lanes over units)
+            const float zi = (FAST ? recv_sum_cm<NC4>(recv, ul, bl) : recv_sum<NC4, true>(recv, ul, bl)) + gb[q].x;
+            const float zf = (FAST ? recv_sum_cm<NC4>(recv, 32 + ul, bl) : recv_sum<NC4, true>(recv, 32 + ul, bl)) + gb[q].y;
+            const float zg = (FAST ? recv_sum_cm<NC4>(recv, 64 + ul, bl) : recv_sum<NC4, true>(recv, 64 + ul, bl)) + gb[q].z;
+            const float zo = (FAST ? recv_sum_cm<NC4>(recv, 96 + ul, bl) : recv_sum<NC4, true>(recv, 96 + ul, bl)) + gb[q].w;
             const float i_ = fast ? 0.5f * tanh_fast(0.5f * zi) + 0.5f : sigmoid_acc(zi);
             const float f_ = fast ? 0.5f * tanh_fast(0.5f * zf) + 0.5f : sigmoid_acc(zf);
             const float g_ = fast ? tanh_fast(zg) : tanh_acc(zg);

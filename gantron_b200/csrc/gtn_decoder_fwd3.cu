@@ -411,7 +411,7 @@ GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int 
   }
   {
     float* stage = sm.recv + (size_t)((xr & 1u) ^ 1u) * 4 * TILE_M * NC4;
-    exchange_bulk<CH, true>(has_work, tmem_acc, 0, recv, stage, &sm.recv_full[xr & 1u], (xr >> 1) & 1u, rank);
+    exchange_bulk<CH, true, true>(has_work, tmem_acc, 0, recv, stage, &sm.recv_full[xr & 1u], (xr >> 1) & 1u, rank);
   }
   PROF3(IS_ATT ? 3 : 11);
   bf16* xh_next = (IS_ATT ? BFP(p.xh_a) : BFP(p.xh_d)) + (size_t)nxt * p.B * mult * Hp;
@@ -425,8 +425,8 @@ GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int 
     float h = 0.f;
     if (b < p.B) {
       constexpr bool fast = !F32;
-      const float zi = recv_sum<NC4, true>(recv, ul, bl) + gb[q].x, zf = recv_sum<NC4, true>(recv, 32 + ul, bl) + gb[q].y;
-      const float zg = recv_sum<NC4, true>(recv, 64 + ul, bl) + gb[q].z, zo = recv_sum<NC4, true>(recv, 96 + ul, bl) + gb[q].w;
+      const float zi = recv_sum_cm<NC4>(recv, ul, bl) + gb[q].x, zf = recv_sum_cm<NC4>(recv, 32 + ul, bl) + gb[q].y;
+      const float zg = recv_sum_cm<NC4>(recv, 64 + ul, bl) + gb[q].z, zo = recv_sum_cm<NC4>(recv, 96 + ul, bl) + gb[q].w;
       const float i_ = fast ? 0.5f * tanh_fast(0.5f * zi) + 0.5f : sigmoid_acc(zi);
       const float f_ = fast ? 0.5f * tanh_fast(0.5f * zf) + 0.5f : sigmoid_acc(zf);
       const float g_ = fast ? tanh_fast(zg) : tanh_acc(zg);
