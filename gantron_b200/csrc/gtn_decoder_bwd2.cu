@@ -350,11 +350,11 @@ GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, 
       const int bbase = c0 + rank * NC4;
       if constexpr (N > 64) {
         // two receive buffers: the other one is the staging area (see exchange_bulk)
-        exchange_bulk<CH>(has_work, tmem_base, c0, recv, sm.recv + (size_t)((round & 1u) ^ 1u) * 4 * TILE_M * NC4,
-                          &sm.recv_full[round & 1u], (round >> 1) & 1u, rank);
+        exchange_bulk<CH, false, true>(has_work, tmem_base, c0, recv, sm.recv + (size_t)((round & 1u) ^ 1u) * 4 * TILE_M * NC4,
+                                       &sm.recv_full[round & 1u], (round >> 1) & 1u, rank);
       } else if (nD + nA <= ncl) {
         // one receive buffer, one exchange per frame with grid barriers in between: stage in the (idle) TMA ring
-        exchange_bulk<CH>(has_work, tmem_base, c0, recv, reinterpret_cast<float*>(sm.ring.base), &sm.recv_full[0], round & 1u, rank);
+        exchange_bulk<CH, false, true>(has_work, tmem_base, c0, recv, reinterpret_cast<float*>(sm.ring.base), &sm.recv_full[0], round & 1u, rank);
       } else {
         exchange_chunk<CH, true>(has_work, tmem_base, c0, recv, rank);
       }
@@ -363,7 +363,9 @@ GTN_DEVICE void dgrad_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& sm, 
       for (int idx = threadIdx.x; idx < TILE_M * NC4; idx += blockDim.x) {
         const int r = idx % TILE_M, bl = idx / TILE_M, b = bbase + bl, row = row0 + r;
         if (b >= p.B) continue;
-        const float val = recv_sum<NC4, true>(recv, r, bl);
+        // (bulk exchanges deliver column-major blocks: lanes over rows read consecutive words; the DSMEM-store fall-back
+        // keeps the swizzled row-major layout)
+        const float val = (N > 64 || nD + nA <= ncl) ? recv_sum_cm<NC4>(recv, r, bl) : recv_sum<NC4, true>(recv, r, bl);
         if (dec) {
           if (row < p.Ha) p.dha_dec[(size_t)b * p.Ha + row] = val;
           else if (row < p.Ha + p.E) p.dctx_dec[(size_t)b * p.Ep + row - p.Ha] = val;
