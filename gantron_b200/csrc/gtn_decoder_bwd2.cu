@@ -828,8 +828,8 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& s
             }
             de[r] = dep[r * 8];
           }
-          th_sa += (uint32_t)row8 * 4u;
-          th_g += row8;
+          th_sa += 8u * 16u;                 // (chunk-major tanh tile: 8 rows further = 8 x 16 bytes)
+          th_g += 8 * 4;
         }
 #pragma unroll
         for (int r = 0; r < RW; ++r) {
@@ -859,8 +859,10 @@ GTN_DEVICE void attn_bwd_phase2(const DecBwd2& p, const Bwd2Maps& maps, SmemB& s
           uint8_t* hi = dth_hi + sw + k0 * 1024;
           uint8_t* lo = dth_lo + sw + k0 * 1024;
           const int row = jr + 8 * k0;
-          const float* th_g = p.th_all + ((tb * Tin + j0 + row) * A + ap);
-          const uint32_t th_sa = smem_u32(sm.ring.base + TH_TILE_OFF) + (uint32_t)(row * A + ap) * 4u;
+          // tanh tile of the half, chunk-major as the forward kernels save it: element (row, a) at ((a / 4) jn + row) 4 + a % 4
+          const size_t th_el = ((size_t)(ap >> 2) * jn + row) * 4 + (ap & 3);
+          const float* th_g = p.th_all + (tb * Tin + j0) * A + th_el;
+          const uint32_t th_sa = smem_u32(sm.ring.base + TH_TILE_OFF) + (uint32_t)th_el * 4u;
           float* dpmp = p.dpm + (((size_t)b * Tin + j0 + row) * A + ap);
           const float* dep = sm.dw_s + j0 + row;
           if (k0 + RW <= nr) {

@@ -787,7 +787,8 @@ GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, in
       const bool valid = jl < jn && (j0 + jl) < L;
       float part = 0.f;
       const MT* pmj = pm + ((size_t)b * Tin + (j0 + jl)) * A + a0;
-      float* thj = P_TRAIN ? p.th_all + (((size_t)t * p.B + b) * Tin + (j0 + jl)) * A + a0 : nullptr;
+      // (tanh save: chunk-major inside the half's block, see gtn_decoder_fwd3.cu)
+      float* thb = P_TRAIN ? p.th_all + (((size_t)t * p.B + b) * Tin + j0) * A : nullptr;
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         uint32_t r[32];
@@ -817,9 +818,10 @@ GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, in
                 th[e] = p.prec == 1 ? tanh_fast(s) : tanh_acc(s);
                 part += sm.v_s[a0 + ab + e] * th[e];
               }
-              if (thj) {
-                *reinterpret_cast<float4*>(thj + ab) = make_float4(th[0], th[1], th[2], th[3]);
-                *reinterpret_cast<float4*>(thj + ab + 4) = make_float4(th[4], th[5], th[6], th[7]);
+              if (thb) {
+                float4* thc = reinterpret_cast<float4*>(thb) + (size_t)((a0 + ab) >> 2) * jn + jl;
+                thc[0] = make_float4(th[0], th[1], th[2], th[3]);
+                thc[jn] = make_float4(th[4], th[5], th[6], th[7]);
               }
             }
           }

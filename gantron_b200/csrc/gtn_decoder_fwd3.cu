@@ -597,7 +597,11 @@ GTN_DEVICE void attn_main(const DecFwd& p, const CUtensorMap* qmap, Smem3& sm, c
     const bool valid = jl < c.jn && (c.j0 + jl) < c.L;
     float part = 0.f;
     const MT* pmj = pm + ((size_t)c.b * Tin + (c.j0 + jl)) * A + a0;
-    float* thj = p.th_all + (((size_t)t * p.B + c.b) * Tin + (c.j0 + jl)) * A + a0;
+    // tanh save of this CTA's positions: CHUNK-major inside the half's block, element (jl, a) at ((a / 4) jn + jl) 4 + a % 4.  A
+    // thread owns a position, so in a row-major block every 16-byte store of a warp went to 32 different rows (32 tags, half
+    // sectors); chunk-major, the 32 positions of a warp are 512 contiguous bytes.  (The backward kernel copies the half's
+    // block as one run and indexes it the same way.)
+    float* thb = p.th_all + (((size_t)t * p.B + c.b) * Tin + c.j0) * A;
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
       uint32_t r[32];
@@ -627,8 +631,9 @@ GTN_DEVICE void attn_main(const DecFwd& p, const CUtensorMap* qmap, Smem3& sm, c
               th[e] = F32 ? tanh_acc(s) : tanh_fast(s);
               part += sm.v_s[a0 + ab + e] * th[e];
             }
-            *reinterpret_cast<float4*>(thj + ab) = make_float4(th[0], th[1], th[2], th[3]);
-            *reinterpret_cast<float4*>(thj + ab + 4) = make_float4(th[4], th[5], th[6], th[7]);
+            float4* thc = reinterpret_cast<float4*>(thb) + (size_t)((a0 + ab) >> 2) * c.jn + jl;
+            thc[0] = make_float4(th[0], th[1], th[2], th[3]);
+            thc[c.jn] = make_float4(th[4], th[5], th[6], th[7]);
           }
         }
       }

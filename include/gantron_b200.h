@@ -189,7 +189,9 @@ typedef struct gtn_decoder_fwd_params {
   float *gates_d, *c_d_all, *h_d_all;
   float *ctx_all;                       /* [T][B][D] */
   float *q_all;                         /* [T][B][A]       attention query */
-  float *th_all;                        /* [T][B][Tin][A]  tanh(q + loc + processed_memory) */
+  float *th_all;                        /* [T][B][Tin][A]  tanh(q + loc + processed_memory); inside a (t, b) block the rows of each
+                                         * CTA half (j0 = 0 / ceil(Tin/2), jn rows) are stored chunk-major: element (jl, a) at
+                                         * j0*A + ((a/4)*jn + jl)*4 + a%4 (written and read by the kernels only) */
   float *f_all;                         /* [T][B][Tin][F]  location-conv outputs */
   float *cum_all;                       /* [T][B][Tin]     cumulative weights BEFORE the step (conv input ch. 1) */
   /* second-generation (clustered tcgen05) kernel: gtn_decoder_forward2 */
@@ -311,7 +313,7 @@ typedef struct gtn_decoder_bwd2_params {
   const void *mem_enc; const int *lengths;
   const float *gates_a, *c_a_all, *gates_d, *c_d_all;    /* [T][B][H][4], [T][B][H] */
   const float *align;        /* [B][T][Tin] */
-  const float *th_all;       /* [T][B][Tin][A] */
+  const float *th_all;       /* [T][B][Tin][A], chunk-major inside each half as gtn_decoder_forward2 saves it */
   const float *cum_all;      /* [T][B][Tin] */
   /* upstream gradients */
   const float *dproj_all;    /* [T][B][Hd + D]: d(loss)/d[h_dec' | ctx'] through the mel/gate projection */
