@@ -710,10 +710,17 @@ GTN_DEVICE void attention_phase2(const DecFwd& p, Smem2& sm, int t, int rank, in
     {
       const int wq_ = warp & 3, a0_ = (warp >> 2) * 64, jl_ = wq_ * 32 + lane;
       if (PM_PRE && active && jl_ < jn && (j0 + jl_) < L) {
-        const uint4* src = reinterpret_cast<const uint4*>(pm + ((size_t)b * Tin + (j0 + jl_)) * A + a0_);
+        if (p.reserved0 & 32) {             // chunk-major [B][A / 8][Tin][8]: a warp's positions are contiguous
+          const uint4* src = reinterpret_cast<const uint4*>(pm) + ((size_t)b * (A >> 3) + (a0_ >> 3)) * Tin + (j0 + jl_);
 #pragma unroll
-        for (int g = 0; g < 8; ++g)
-          if (a0_ + g * 8 < A) pmq[g] = __ldg(src + g);
+          for (int g = 0; g < 8; ++g)
+            if (a0_ + g * 8 < A) pmq[g] = __ldg(src + (size_t)g * Tin);
+        } else {
+          const uint4* src = reinterpret_cast<const uint4*>(pm + ((size_t)b * Tin + (j0 + jl_)) * A + a0_);
+#pragma unroll
+          for (int g = 0; g < 8; ++g)
+            if (a0_ + g * 8 < A) pmq[g] = __ldg(src + g);
+        }
       }
     }
     if (active) {
@@ -1047,10 +1054,17 @@ GTN_DEVICE void attention_infer_multi(const DecFwd& p, Smem2& sm, int S, int t, 
   auto pm_fetch = [&](int it) {
     const int b = pair + it * npairs;
     if (it < nact && jl < jn && (j0 + jl) < len_s[it]) {
-      const uint4* src = reinterpret_cast<const uint4*>(pm + ((size_t)b * Tin + (j0 + jl)) * A + a0);
+      if (p.reserved0 & 32) {               // chunk-major [B][A / 8][Tin][8]
+        const uint4* src = reinterpret_cast<const uint4*>(pm) + ((size_t)b * (A >> 3) + (a0 >> 3)) * Tin + (j0 + jl);
 #pragma unroll
-      for (int g = 0; g < 8; ++g)
-        if (a0 + g * 8 < A) pmn[g] = __ldg(src + g);
+        for (int g = 0; g < 8; ++g)
+          if (a0 + g * 8 < A) pmn[g] = __ldg(src + (size_t)g * Tin);
+      } else {
+        const uint4* src = reinterpret_cast<const uint4*>(pm + ((size_t)b * Tin + (j0 + jl)) * A + a0);
+#pragma unroll
+        for (int g = 0; g < 8; ++g)
+          if (a0 + g * 8 < A) pmn[g] = __ldg(src + g);
+      }
     }
   };
   pm_fetch(0);
@@ -1521,7 +1535,8 @@ extern "C" int gtn_decoder_forward2(const gtn_decoder_fwd_params* hp, void* stre
   auto thr = [](float pr) -> unsigned { double t = (double)pr * 4294967296.0; return t >= 4294967295.0 ? 0xFFFFFFFFu : (unsigned)t; };
   p.thr_att = p.use_dropout ? thr(p.p_att) : 0u;
   p.thr_dec = p.use_dropout ? thr(p.p_dec) : 0u;
-  p.reserved0 = 0;                                  // kernel feature switches (A/B measurements, parity tests between the paths)
+  p.reserved0 = hp->reserved0 & 32;                 // caller flag: chunk-major pm; the other bits are kernel feature switches
+  GTN_REQUIRE(!(p.reserved0 & 32) || (p.mem_bf16 && p.A % 8 == 0), "chunk-major pm needs bf16 pm and attention_dim % 8 == 0");
   if (getenv("GTN_INFER_NO_TAIL")) p.reserved0 |= 1;
   if (getenv("GTN_INFER_NO_MULTI_ATTN")) p.reserved0 |= 2;
   if (getenv("GTN_INFER_NO_L2_HINTS")) p.reserved0 |= 8;

@@ -555,10 +555,17 @@ GTN_DEVICE void attn_main(const DecFwd& p, const CUtensorMap* qmap, Smem3& sm, c
     {
       const int wq_ = warp & 3, a0_ = (warp >> 2) * 64, jl_ = wq_ * 32 + lane;
       if (sizeof(MT) == 2 && jl_ < c.jn && (c.j0 + jl_) < c.L) {
-        const uint4* src = reinterpret_cast<const uint4*>(pm + ((size_t)c.b * Tin + (c.j0 + jl_)) * A + a0_);
+        if (p.reserved0 & 32) {             // chunk-major [B][A / 8][Tin][8]: a warp's positions are contiguous
+          const uint4* src = reinterpret_cast<const uint4*>(pm) + ((size_t)c.b * (A >> 3) + (a0_ >> 3)) * Tin + (c.j0 + jl_);
 #pragma unroll
-        for (int g = 0; g < 8; ++g)
-          if (a0_ + g * 8 < A) pmq[g] = __ldg(src + g);
+          for (int g = 0; g < 8; ++g)
+            if (a0_ + g * 8 < A) pmq[g] = __ldg(src + (size_t)g * Tin);
+        } else {
+          const uint4* src = reinterpret_cast<const uint4*>(pm + ((size_t)c.b * Tin + (c.j0 + jl_)) * A + a0_);
+#pragma unroll
+          for (int g = 0; g < 8; ++g)
+            if (a0_ + g * 8 < A) pmq[g] = __ldg(src + g);
+        }
       }
     }
     PROF3(15);

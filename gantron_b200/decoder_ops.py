@@ -364,6 +364,9 @@ def _decoder_inference_b1(dec, pk, memory, E, max_steps, gate_threshold, seed, i
     return (ws["mel_out"][None, :, :steps], ws["gate_out"][None, :steps, None], ws["align_out"][None, :steps], lengths, steps)
 
 
+PM_CHUNK_MAJOR = 32      # gtn_decoder_fwd_params.reserved0 flag: `pm` is bf16 [B][A/8][T_in][8]
+
+
 @torch.no_grad()
 def decoder_inference(dec, memory: torch.Tensor, *, max_steps: int, gate_threshold: float,
                       seed: int, prec: int, const_tail: Optional[bool] = None, ignore_stop: bool = False,
@@ -395,6 +398,9 @@ def decoder_inference(dec, memory: torch.Tensor, *, max_steps: int, gate_thresho
     mem_enc = memory[:, :, :E].to(mdt).contiguous()
     mem_const = memory[:, 0, E:].contiguous() if E < D else torch.zeros(B, 1, device=dev)
     pm = pm.to(mdt).contiguous()
+    if mdt == BF16 and d.att_dim % 8 == 0:
+        pm = pm.view(B, Tin, d.att_dim // 8, 8).permute(0, 2, 1, 3).contiguous()      # chunk-major, see decoder_train_forward
+        p.reserved0 = PM_CHUNK_MAJOR
     align = torch.zeros(B, max_steps, Tin, device=dev)
     mel = torch.zeros(B, d.n_mel, max_steps, device=dev)
     gate = torch.zeros(B, max_steps, device=dev)
@@ -550,6 +556,11 @@ class _DecoderTrainFn(torch.autograd.Function):
         mem_enc = memory_f[:, :, :E].to(mdt).contiguous()
         mem_const = memory_f[:, 0, E:].contiguous() if E < D else torch.zeros(B, 1, device=dev)
         pm_k = pm.to(mdt).contiguous()
+        if mdt == BF16 and d.att_dim % 8 == 0:
+            # chunk-major processed_memory [B][A / 8][T_in][8] (flag PM_CHUNK_MAJOR): an attention thread owns one encoder
+            # position, so its 16-byte loads are contiguous across a warp in this order (32 different rows otherwise)
+            pm_k = pm_k.view(B, Tin, d.att_dim // 8, 8).permute(0, 2, 1, 3).contiguous()
+            p.reserved0 = PM_CHUNK_MAJOR
         lengths = memory_lengths.to(device=dev, dtype=torch.int32).contiguous()
         z = lambda *s: torch.zeros(*s, device=dev)
         e = lambda *s: torch.empty(*s, device=dev)

@@ -205,7 +205,8 @@ typedef struct gtn_decoder_fwd_params {
    *   xctx is [2][B][mult*Ep], Ep = pad64(E): the training kernel alternates the two buffers by frame parity. */
   const float *gbias_a, *gbias_d;       /* [B][H][4] (i,f,g,o): bias_ih + bias_hh + W[:, const cols] . mem_const[b] */
   const float *pbias;                   /* [B][NM+1]: projection / gate bias + W[:, const cols] . mem_const[b] (inference) */
-  int Ep, reserved0;
+  int Ep, reserved0;                    /* reserved0: flags; bit 5 (32): `pm` is bf16 in chunk-major order [B][A/8][Tin][8]; other bits
+                                         * are set by the library */
 } gtn_decoder_fwd_params;
 
 /* Clusters of 4 CTAs split K of every per-frame GEMM and run it on tcgen05 with TMA-fed operands
