@@ -361,7 +361,8 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
               h_all[cell] = h;
             }
           }
-          if (is_att) sm.hs[ul * NC4 + bl] = h;
+          // (float4 column groups XOR-permuted by the unit: the lanes of a warp run over units, 16-way bank conflict otherwise)
+          if (is_att) sm.hs[ul * NC4 + (bl ^ (((ul >> 1) & (NC4 / 4 - 1)) << 2))] = h;
         }
         if (is_att) {
           if (P_TRAIN) PROF(14);
@@ -375,10 +376,10 @@ GTN_DEVICE void gemm_phase(const DecFwd& p, const Fwd2Maps& maps, Smem2& sm, int
           for (int j = 0; j < HB; ++j) acc[j] = 0.f;
 #pragma unroll
           for (int u = 0; u < 32; ++u) {
-            const float4* hr = reinterpret_cast<const float4*>(sm.hs + u * NC4 + g * HB);
+            const float4* hr = reinterpret_cast<const float4*>(sm.hs + u * NC4);
 #pragma unroll
             for (int j4 = 0; j4 < HB / 4; ++j4) {
-              const float4 hv = hr[j4];
+              const float4 hv = hr[(g * (HB / 4) + j4) ^ ((u >> 1) & (NC4 / 4 - 1))];
               acc[4 * j4] += wqr[u] * hv.x; acc[4 * j4 + 1] += wqr[u] * hv.y;
               acc[4 * j4 + 2] += wqr[u] * hv.z; acc[4 * j4 + 3] += wqr[u] * hv.w;
             }

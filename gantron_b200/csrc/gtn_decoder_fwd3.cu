@@ -448,7 +448,8 @@ GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int 
         h_all[cell] = h;
       }
     }
-    if (IS_ATT) sm.hs[ul * NC4 + bl] = h;
+    // (float4 column groups XOR-permuted by the unit: the lanes of a warp run over units, 16-way bank conflict otherwise)
+    if (IS_ATT) sm.hs[ul * NC4 + (bl ^ (((ul >> 1) & (NC4 / 4 - 1)) << 2))] = h;
   }
   if (IS_ATT) {
     WSYNC();
@@ -460,11 +461,11 @@ GTN_DEVICE void lstm_epilogue(const DecFwd& p, Smem3& sm, int tc, int tile, int 
     for (int j = 0; j < HB; ++j) acc[j] = 0.f;
 #pragma unroll
     for (int u = 0; u < 32; ++u) {
-      const float4* hr = reinterpret_cast<const float4*>(sm.hs + u * NC4 + g * HB);
+      const float4* hr = reinterpret_cast<const float4*>(sm.hs + u * NC4);
       const float wq = sm.wq_s[u * 128 + a];
 #pragma unroll
       for (int j4 = 0; j4 < HB / 4; ++j4) {
-        const float4 hv = hr[j4];
+        const float4 hv = hr[(g * (HB / 4) + j4) ^ ((u >> 1) & (NC4 / 4 - 1))];
         acc[4 * j4] += wq * hv.x; acc[4 * j4 + 1] += wq * hv.y;
         acc[4 * j4 + 2] += wq * hv.z; acc[4 * j4 + 3] += wq * hv.w;
       }
