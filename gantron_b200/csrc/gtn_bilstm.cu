@@ -245,6 +245,25 @@ __global__ void __launch_bounds__(256, 1) bilstm_bwd_kernel(const gtn_bilstm_par
     const int t = dir == 0 ? T - 1 - s : s;
     const int tprev = dir == 0 ? t - 1 : t + 1;            // the step whose cell state fed this one
     const int cur = s & 1, nxt = cur ^ 1;
+    // operands of this step's cell backward: saves of the forward pass and the incoming gradient.  Their addresses depend on
+    // (t, sequence, unit) only, so they are requested BEFORE the wait for the previous step's gate gradients: the HBM / L2
+    // round trip runs underneath the exchange and the MMAs instead of behind them (ncu: 38 % of the kernel's stall samples
+    // sat on the first use of c)
+    float4 g4[4];
+    float ccv[4], cpv[4], dov[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int b = b0 + bq + j;
+      g4[j] = make_float4(0.f, 0.f, 0.f, 0.f); ccv[j] = 0.f; cpv[j] = 0.f; dov[j] = 0.f;
+      if (t < len[j]) {
+        const size_t cell = (((size_t)dir * T + t) * B + b) * LH + u;
+        g4[j] = __ldg(reinterpret_cast<const float4*>(p.gates) + cell);
+        ccv[j] = __ldg(p.c_all + cell);
+        const bool first = dir == 0 ? t == 0 : t == len[j] - 1;       // the step that started from the zero state
+        cpv[j] = first ? 0.f : __ldg(p.c_all + (((size_t)dir * T + tprev) * B + b) * LH + u);
+        dov[j] = __ldg(p.dout + ((size_t)b * T + t) * (2 * LH) + dir * LH + u);
+      }
+    }
     // ---- W_hh^T dG(step processed before)
     float acc[2][4];
 #pragma unroll
@@ -279,12 +298,11 @@ __global__ void __launch_bounds__(256, 1) bilstm_bwd_kernel(const gtn_bilstm_par
       const int bl = bq + j, b = b0 + bl;
       float dgi = 0.f, dgf = 0.f, dgg = 0.f, dgo = 0.f;
       if (t < len[j]) {
-        const size_t cell = (((size_t)dir * T + t) * B + b) * LH + u;
-        const float4 g = __ldg(reinterpret_cast<const float4*>(p.gates) + cell);
-        const float cc = __ldg(p.c_all + cell);
+        const float4 g = g4[j];
+        const float cc = ccv[j];
         const bool first = dir == 0 ? t == 0 : t == len[j] - 1;       // the step that started from the zero state
-        const float cp = first ? 0.f : __ldg(p.c_all + (((size_t)dir * T + tprev) * B + b) * LH + u);
-        const float dh = part[0][ul][bl] + part[1][ul][bl] + __ldg(p.dout + ((size_t)b * T + t) * (2 * LH) + dir * LH + u);
+        const float cp = cpv[j];
+        const float dh = part[0][ul][bl] + part[1][ul][bl] + dov[j];
         const float tc = tanhf_(cc);
         const float d_o = dh * tc;
         const float dcc = dh * g.w * (1.f - tc * tc) + dc[j];
