@@ -110,6 +110,10 @@ __global__ void __launch_bounds__(256, 1) bilstm_fwd_kernel(const gtn_bilstm_par
   for (int s = 0; s < T; ++s) {
     const int t = dir == 0 ? s : T - 1 - s;
     const int cur = s & 1, nxt = cur ^ 1;
+    // the next step's input projection is requested at the top of the step: its round trip runs underneath the wait for the
+    // peers' hidden state, the MMAs and the cells (requested behind the MMAs, a third of the kernel's stall samples sat on it)
+    float xn[2][2][4];
+    if (s + 1 < T) load_x(dir == 0 ? t + 1 : t - 1, xn);
     // ---- gates = xproj + W_hh h(previous step)
     float acc[2][2][4];
 #pragma unroll
@@ -134,8 +138,6 @@ __global__ void __launch_bounds__(256, 1) bilstm_fwd_kernel(const gtn_bilstm_par
         }
       }
     }
-    float xn[2][2][4];
-    if (s + 1 < T) load_x(dir == 0 ? t + 1 : t - 1, xn);
     // ---- cells (all four gates of a cell sit in this thread: rows r4 / r4 + 8 of the two tiles)
     bf16* hown = &hs[nxt][rank * HBLK];
 #pragma unroll
