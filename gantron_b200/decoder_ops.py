@@ -565,10 +565,14 @@ class _DecoderTrainFn(torch.autograd.Function):
         z = lambda *s: torch.zeros(*s, device=dev)
         e = lambda *s: torch.empty(*s, device=dev)
         sv = dict(
-            gates_a=e(T, B, 4 * d.att_rnn), c_a_all=e(T, B, d.att_rnn), h_a_buf=z(T + 1, B, d.att_rnn),
-            gates_d=e(T, B, 4 * d.dec_rnn), c_d_all=e(T, B, d.dec_rnn), h_d_buf=z(T + 1, B, d.dec_rnn),
-            ctx_buf=z(T + 1, B, D), q_all=e(T, B, d.att_dim), th_all=e(T, B, Tin, d.att_dim),
+            # (rows 1 .. T of the three state buffers are written by the kernel for every (frame, sequence, column): only row 0,
+            # the zero initial state, is cleared -- three 210 MB fills per step otherwise)
+            gates_a=e(T, B, 4 * d.att_rnn), c_a_all=e(T, B, d.att_rnn), h_a_buf=e(T + 1, B, d.att_rnn),
+            gates_d=e(T, B, 4 * d.dec_rnn), c_d_all=e(T, B, d.dec_rnn), h_d_buf=e(T + 1, B, d.dec_rnn),
+            ctx_buf=e(T + 1, B, D), q_all=e(T, B, d.att_dim), th_all=e(T, B, Tin, d.att_dim),
             f_all=e(1), cum_all=e(T, B, Tin), align=z(B, T, Tin))
+        for k in ("h_a_buf", "h_d_buf", "ctx_buf"):
+            sv[k][0].zero_()
         p.mem_enc, p.pm, p.mem_const, p.lengths = mem_enc.data_ptr(), pm_k.data_ptr(), mem_const.data_ptr(), lengths.data_ptr()
         p.pre_all = pre_x.data_ptr()
         p.align_out = sv["align"].data_ptr()
