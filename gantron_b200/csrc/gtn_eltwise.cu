@@ -97,6 +97,18 @@ __global__ void bn_finalize_kernel(const float* __restrict__ stats, int C, float
 // ------------------------------------------------------------------------------------------------
 // forward: out = dropout(act(y * scale[c] + shift[c]))   (scale/shift fold BatchNorm; act 0 none / 2 tanh)
 // ------------------------------------------------------------------------------------------------
+// tanh of the BatchNorm + tanh layers.  bf16 activations (bf16 mode): the hardware approximation (relative error ~2^-11,
+// below the bf16 rounding of the stored activation; the decoder kernels use it too) -- libm's tanhf made these kernels
+// instruction-bound (50 % issue utilisation at a quarter of the HBM rate).  fp32 activations (fp32 mode): libm.
+GTN_DEVICE float tanh_mode(float x, int approx) {
+  if (approx) {
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+  }
+  return tanhf(x);
+}
+
 __global__ void __launch_bounds__(256)
 bn_act_fwd_kernel(const void* __restrict__ y, int y_bf16, long long ldy, EltGeom g, const float* __restrict__ mean,
                   const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ beta,
@@ -117,7 +129,7 @@ bn_act_fwd_kernel(const void* __restrict__ y, int y_bf16, long long ldy, EltGeom
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       float z = x.v[i] * sc[i] + sh[i];
-      if (act == 2) z = tanhf(z);
+      if (act == 2) z = tanh_mode(z, out_bf16);
       else if (act == 1) z = fmaxf(z, 0.f);
       x.v[i] = (keep >> i) & 1u ? z * dscale : 0.f;
     }
@@ -167,7 +179,7 @@ bn_act_bwd_reduce_kernel(const void* __restrict__ dx, int dx_bf16, long long ldd
       for (int i = 0; i < 8; ++i) {
         const float yh = (yy.v[i] - m[i]) * rs[i];
         float dz = (keep >> i) & 1u ? d.v[i] * dscale : 0.f;
-        if (act == 2) { const float a = tanhf(yh * ga[i] + be[i]); dz *= 1.f - a * a; }
+        if (act == 2) { const float a = tanh_mode(yh * ga[i] + be[i], y_bf16); dz *= 1.f - a * a; }
         else if (act == 1) { if (yh * ga[i] + be[i] <= 0.f) dz = 0.f; }
         sg[i] += dz * yh;
         sb[i] += dz;
@@ -203,7 +215,7 @@ bn_act_bwd_apply_kernel(const void* __restrict__ dx, int dx_bf16, long long lddx
       for (int i = 0; i < 8; ++i) {
         const float yh = (yy.v[i] - m[i]) * rs[i];
         float dz = (keep >> i) & 1u ? d.v[i] * dscale : 0.f;
-        if (act == 2) { const float a = tanhf(yh * ga[i] + be[i]); dz *= 1.f - a * a; }
+        if (act == 2) { const float a = tanh_mode(yh * ga[i] + be[i], y_bf16); dz *= 1.f - a * a; }
         else if (act == 1) { if (yh * ga[i] + be[i] <= 0.f) dz = 0.f; }
         o.v[i] = ga[i] * rs[i] * (dz - k1[i] - yh * k2[i]);
         sb[i] += o.v[i];
