@@ -707,7 +707,18 @@ GTN_DEVICE void attn_main(const DecFwd& p, const CUtensorMap* qmap, Smem3& sm, c
       if (c8 < c8_n) {
         const MT* mp = mem + (size_t)c.b * Tin * p.E + (size_t)(c8_0 + c8) * 8;
         int j = warp;
-        for (; j + 24 < c.L; j += 32) {              // four rows of this warp in flight
+        for (; j + 56 < c.L; j += 64) {              // eight rows of this warp in flight
+          float mv[8][8];
+#pragma unroll
+          for (int r = 0; r < 8; ++r) ld8<MT>(mp + (size_t)(j + 8 * r) * p.E, mv[r]);
+#pragma unroll
+          for (int r = 0; r < 8; ++r) {
+            const float w = sm.w_s[j + 8 * r];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[e] += w * mv[r][e];
+          }
+        }
+        for (; j + 24 < c.L; j += 32) {              // four rows in flight
           float mv[4][8];
 #pragma unroll
           for (int r = 0; r < 4; ++r) ld8<MT>(mp + (size_t)(j + 8 * r) * p.E, mv[r]);
@@ -718,12 +729,18 @@ GTN_DEVICE void attn_main(const DecFwd& p, const CUtensorMap* qmap, Smem3& sm, c
             for (int e = 0; e < 8; ++e) acc[e] += w * mv[r][e];
           }
         }
-        for (; j < c.L; j += 8) {
-          float mv[8];
-          ld8<MT>(mp + (size_t)j * p.E, mv);
-          const float w = sm.w_s[j];
+        if (j < c.L) {
+          // ragged tail (up to three rows) as ONE trip: rows past the end re-read the last row with weight zero (no branches
+          // between the loads; one-row trips were dependent L2 round trips)
+          float mv[3][8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) acc[e] += w * mv[e];
+          for (int r = 0; r < 3; ++r) ld8<MT>(mp + (size_t)min(j + 8 * r, c.L - 1) * p.E, mv[r]);
+#pragma unroll
+          for (int r = 0; r < 3; ++r) {
+            const float w = j + 8 * r < c.L ? sm.w_s[j + 8 * r] : 0.f;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[e] += w * mv[r][e];
+          }
         }
       }
       WSYNC();
